@@ -1,0 +1,221 @@
+"""ctypes wrapper over oracle/liboracle.so — the CPU restatement of the reference's
+arithmetic for matmul / batch_matmul / attention.
+
+TEST INFRASTRUCTURE ONLY. Importable from tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs; never from iree_b200/.
+See oracle/oracle.c for the per-function reference citations and parity status.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "liboracle.so")
+
+I8, F16, BF16, F32, I32 = 0, 1, 2, 3, 4
+_TYPE_BY_NAME = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "i32": I32}
+_NP_STORAGE = {I8: np.int8, F16: np.uint16, BF16: np.uint16, F32: np.float32, I32: np.int32}
+
+
+def build(force: bool = False) -> str:
+    """Compiles liboracle.so (gcc, OpenMP). Building the checker is not using it."""
+    src = os.path.join(_HERE, "oracle.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.run(["make", "-C", _HERE, "liboracle.so"], check=True,
+                       stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        _lib = ctypes.CDLL(_LIB_PATH)
+        _lib.oracle_bf16_to_f32.restype = ctypes.c_float
+        _lib.oracle_f16_to_f32.restype = ctypes.c_float
+        _lib.oracle_f32_to_bf16.restype = ctypes.c_uint16
+        _lib.oracle_f32_to_f16.restype = ctypes.c_uint16
+        _lib.oracle_f32_to_bf16.argtypes = [ctypes.c_float]
+        _lib.oracle_f32_to_f16.argtypes = [ctypes.c_float]
+        _lib.oracle_matmul_f32acc_element.restype = ctypes.c_float
+        _lib.oracle_matmul_i8_i32_element.restype = ctypes.c_int32
+        _lib.oracle_calculate_check_every.restype = ctypes.c_int
+    return _lib
+
+
+def type_id(t) -> int:
+    return _TYPE_BY_NAME[t] if isinstance(t, str) else int(t)
+
+
+def _ptr(a):
+    if a is None:
+        return ctypes.c_void_p(0)
+    assert a.flags["C_CONTIGUOUS"]
+    return ctypes.c_void_p(a.ctypes.data)
+
+
+# ----------------------------------------------------------------------------
+# bf16 / f16 bit helpers (numpy has no bf16; narrow floats travel as uint16 bits).
+# ----------------------------------------------------------------------------
+
+def f32_to_bf16_bits(x: np.ndarray) -> np.ndarray:
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32).astype(np.uint64)
+    nan = (u & 0x7F800000) == 0x7F800000
+    r = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16).astype(np.uint16)
+    r = np.where(nan, (u >> 16).astype(np.uint16), r)
+    return r
+
+
+def bf16_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    return (b.astype(np.uint32) << 16).view(np.float32)
+
+
+def f32_to_f16_bits(x: np.ndarray) -> np.ndarray:
+    return np.ascontiguousarray(x, dtype=np.float32).astype(np.float16).view(np.uint16)
+
+
+def f16_bits_to_f32(b: np.ndarray) -> np.ndarray:
+    return b.view(np.float16).astype(np.float32)
+
+
+def to_f32(t, a: np.ndarray) -> np.ndarray:
+    t = type_id(t)
+    if t == BF16:
+        return bf16_bits_to_f32(a)
+    if t == F16:
+        return f16_bits_to_f32(a)
+    return a.astype(np.float32)
+
+
+def from_f32(t, a: np.ndarray) -> np.ndarray:
+    t = type_id(t)
+    if t == BF16:
+        return f32_to_bf16_bits(a)
+    if t == F16:
+        return f32_to_f16_bits(a)
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+# ----------------------------------------------------------------------------
+# Reference input generator.
+# ----------------------------------------------------------------------------
+
+def generate_random_matrix(t, shape, seed: int) -> np.ndarray:
+    """iree-e2e-matmul-test.cc:694-736 GenerateRandomMatrix (see oracle.c)."""
+    t = type_id(t)
+    out = np.empty(shape, dtype=_NP_STORAGE[t])
+    lib().oracle_generate_random_matrix(ctypes.c_int(t), ctypes.c_int64(out.size),
+                                        ctypes.c_int32(seed), _ptr(out))
+    return out
+
+
+def calculate_check_every(tot_elements: int, no_div_of: int, max_elements: int = 10000) -> int:
+    return lib().oracle_calculate_check_every(ctypes.c_int64(tot_elements),
+                                              ctypes.c_int64(no_div_of),
+                                              ctypes.c_int32(max_elements))
+
+
+# ----------------------------------------------------------------------------
+# matmul / batch_matmul
+# ----------------------------------------------------------------------------
+
+def matmul(t, lhs: np.ndarray, rhs: np.ndarray, acc=None, transpose_rhs: bool = False) -> np.ndarray:
+    """C = acc + A.B with the reference's per-element k-ascending accumulation.
+
+    lhs [.., M, K]; rhs [.., K, N] (or [.., N, K] when transpose_rhs). A leading
+    batch dim makes it batch_matmul. t in {"i8","f16","bf16"}; result i32 / f32.
+    """
+    t = type_id(t)
+    batched = lhs.ndim == 3
+    B = lhs.shape[0] if batched else 1
+    M, K = lhs.shape[-2:]
+    N = rhs.shape[-2] if transpose_rhs else rhs.shape[-1]
+    lhs = np.ascontiguousarray(lhs)
+    rhs = np.ascontiguousarray(rhs)
+    oshape = (B, M, N) if batched else (M, N)
+    if t == I8:
+        out = np.empty(oshape, dtype=np.int32)
+        acc_c = None if acc is None else np.ascontiguousarray(acc, dtype=np.int32)
+        lib().oracle_matmul_i8_i32(ctypes.c_int64(B), ctypes.c_int64(M), ctypes.c_int64(N),
+                                   ctypes.c_int64(K), ctypes.c_int(int(transpose_rhs)),
+                                   _ptr(lhs), _ptr(rhs), _ptr(acc_c), _ptr(out))
+    else:
+        out = np.empty(oshape, dtype=np.float32)
+        acc_c = None if acc is None else np.ascontiguousarray(acc, dtype=np.float32)
+        lib().oracle_matmul_f32acc(ctypes.c_int(t), ctypes.c_int64(B), ctypes.c_int64(M),
+                                   ctypes.c_int64(N), ctypes.c_int64(K),
+                                   ctypes.c_int(int(transpose_rhs)), _ptr(lhs), _ptr(rhs),
+                                   _ptr(acc_c), _ptr(out))
+    return out
+
+
+def matmul_element(t, lhs: np.ndarray, rhs: np.ndarray, m: int, n: int, transpose_rhs: bool = False):
+    t = type_id(t)
+    M, K = lhs.shape
+    N = rhs.shape[0] if transpose_rhs else rhs.shape[1]
+    args = [ctypes.c_int64(M), ctypes.c_int64(N), ctypes.c_int64(K),
+            ctypes.c_int(int(transpose_rhs)), _ptr(lhs), _ptr(rhs),
+            ctypes.c_int64(m), ctypes.c_int64(n)]
+    if t == I8:
+        return lib().oracle_matmul_i8_i32_element(*args)
+    return lib().oracle_matmul_f32acc_element(ctypes.c_int(t), *args)
+
+
+def sampled_indices(M: int, N: int, max_elements: int = 10000):
+    """Flat indices the reference's checker visits (test_utils.c:41-68)."""
+    every = calculate_check_every(M * N, N, max_elements)
+    return np.arange(0, M * N, every, dtype=np.int64), every
+
+
+# ----------------------------------------------------------------------------
+# attention
+# ----------------------------------------------------------------------------
+
+def attention(t, q: np.ndarray, k: np.ndarray, v: np.ndarray, scale: float, *, mask=None,
+              scale_type=None, region: str = "identity", region_param: float = 0.0,
+              k2_tile: int = 0, oneshot: bool = False) -> np.ndarray:
+    """iree_linalg_ext.attention as the llvm-cpu path evaluates it (see oracle.c).
+
+    q [B,M,K1], k [B,K2,K1], v [B,K2,N] in storage dtype of t (uint16 bits for
+    f16/bf16, float32 for f32). mask: None | bool [B,M,K2] | float32 [B,M,K2].
+    """
+    t = type_id(t)
+    st = t if scale_type is None else type_id(scale_type)
+    B, M, K1 = q.shape
+    K2 = k.shape[1]
+    N = v.shape[2]
+    q, k, v = (np.ascontiguousarray(x) for x in (q, k, v))
+    out = np.empty((B, M, N), dtype=_NP_STORAGE[t])
+    mask_kind, mask_c = 0, None
+    if mask is not None:
+        if mask.dtype == np.bool_:
+            mask_kind, mask_c = 1, np.ascontiguousarray(mask, dtype=np.uint8)
+        else:
+            mask_kind, mask_c = 2, np.ascontiguousarray(mask, dtype=np.float32)
+        assert mask_c.shape == (B, M, K2)
+    region_kind = {"identity": 0, "softcap": 1}[region]
+    common = [ctypes.c_int(t), ctypes.c_int(st), ctypes.c_int64(B), ctypes.c_int64(M),
+              ctypes.c_int64(K1), ctypes.c_int64(K2), ctypes.c_int64(N), _ptr(q), _ptr(k),
+              _ptr(v), ctypes.c_float(scale), ctypes.c_int(mask_kind), _ptr(mask_c),
+              ctypes.c_int(region_kind), ctypes.c_float(region_param)]
+    if oneshot:
+        lib().oracle_attention_oneshot(*common, _ptr(out))
+    else:
+        lib().oracle_attention_online(*common, ctypes.c_int64(k2_tile), _ptr(out))
+    return out
+
+
+def all_reduce_sum_f32(parts: np.ndarray) -> np.ndarray:
+    parts = np.ascontiguousarray(parts, dtype=np.float32)
+    out = np.empty(parts.shape[1:], dtype=np.float32)
+    lib().oracle_all_reduce_sum_f32(ctypes.c_int(parts.shape[0]),
+                                    ctypes.c_int64(out.size), _ptr(parts), _ptr(out))
+    return out
