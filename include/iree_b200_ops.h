@@ -1,0 +1,103 @@
+// iree_b200_ops.h — C ABI of the dense-contraction dispatches themselves.
+//
+// What a compiled IREE module does for a matched op is: look up the export in the
+// executable, evaluate the export's `count` region on the host to get the workgroup
+// count, and record hal.command_buffer.dispatch with (constants…, bindings…)
+// (compiler/src/iree/compiler/Dialect/HAL/Conversion/StreamToHAL/Patterns.cpp:977-1021).
+// The selection guards live in the match-and-replace spec (compiler_plugin/). These entry
+// points are that logic as host calls, so a runtime without `iree-compile` (this
+// container has none) drives exactly the dispatches the plugin would emit:
+//   * iree_b200_ops_select_*   : matcher guards + count region → (export, workgroup count)
+//   * iree_b200_ops_record_*   : select + iree_b200_command_buffer_dispatch
+//   * iree_b200_ops_*_host     : the `iree-run-module` shaped call — host buffers in,
+//                                host buffer out, synchronous (H2D, dispatch, D2H).
+// Op semantics are the reference's:
+//   matmul / batch_matmul  tools/testing/e2e/iree-e2e-matmul-test.cc:28-121,810-919
+//   attention              compiler/src/iree/compiler/Dialect/LinalgExt/IR/AggregatedOpInterfaceImpl.cpp:323-412,533-632
+//                          compiler/src/iree/compiler/Dialect/LinalgExt/Transforms/TileAttention.cpp:35-155
+// There is no CPU fallback: every entry point fails with a status when no B200 is present.
+
+#ifndef IREE_B200_OPS_H_
+#define IREE_B200_OPS_H_
+
+#include "iree_b200_hal.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct iree_b200_ops_t iree_b200_ops_t;
+
+// Element types of the operands (result type is implied: f32 for floats, i32 for i8;
+// attention returns the operand type).
+enum {
+  IREE_B200_ELEMENT_TYPE_I8 = 0,
+  IREE_B200_ELEMENT_TYPE_F16 = 1,
+  IREE_B200_ELEMENT_TYPE_BF16 = 2,
+};
+
+enum {
+  IREE_B200_MATMUL_FLAG_ACCUMULATE = 1u << 0,     // out = out + lhs·rhs (linalg outs operand)
+  IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS = 1u << 1,  // rhs is [N, K] (generate_code.py:172-174)
+  // Diagnostics: force a kernel family regardless of the shape heuristics.
+  IREE_B200_MATMUL_FLAG_FORCE_GENERIC = 1u << 8,
+  IREE_B200_MATMUL_FLAG_FORCE_1CTA = 1u << 9,
+  IREE_B200_MATMUL_FLAG_FORCE_2CTA = 1u << 10,
+};
+
+// The builtin executable ("CDA1" blob linked into this library: one cubin per kernel
+// family, built for sm_100a) and its size; also written to disk by the build as
+// iree_b200/_build/iree_b200_kernels.cda1 for use as a #hal.executable.object.
+IREE_B200_API const void* iree_b200_ops_builtin_executable_data(size_t* out_size);
+
+// Loads the builtin executable through the executable cache (PTXE path).
+IREE_B200_API iree_b200_status_t iree_b200_ops_create(iree_b200_device_t* device,
+                                                      iree_b200_ops_t** out_ops);
+// Same, from a caller-provided CDA1 blob (e.g. read from the .cda1 file).
+IREE_B200_API iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device,
+                                                                const void* data, size_t size,
+                                                                iree_b200_ops_t** out_ops);
+IREE_B200_API void iree_b200_ops_release(iree_b200_ops_t* ops);
+IREE_B200_API iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* ops);
+
+// Number of dispatches recorded through this object since creation (each is one kernel
+// launch when the command buffer executes).
+IREE_B200_API uint64_t iree_b200_ops_dispatch_count(const iree_b200_ops_t* ops);
+
+//===----------------------------------------------------------------------===//
+// linalg.matmul / linalg.batch_matmul
+//===----------------------------------------------------------------------===//
+
+typedef struct iree_b200_matmul_selection_t {
+  int32_t export_ordinal;
+  uint32_t workgroup_count[3];
+  uint32_t constants[5];  // M, N, K, batch, kernel flags
+} iree_b200_matmul_selection_t;
+
+// Picks the export and grid for C[batch,M,N] = A[batch,M,K]·B[batch,K,N].
+// |alignment| = the largest power of two (≤ 256) dividing all three binding addresses.
+// TMA-fed tcgen05 kernels need 16-byte aligned bases and row pitches; everything else
+// goes to the generic kernel. Pure host logic (no GPU needed beyond |ops| existing).
+IREE_B200_API iree_b200_status_t iree_b200_ops_select_matmul(
+    const iree_b200_ops_t* ops, int32_t element_type, int64_t batch, int64_t M, int64_t N,
+    int64_t K, uint32_t flags, uint32_t alignment, iree_b200_matmul_selection_t* out_selection);
+
+// Records the dispatch into |cb| (which must be recording). batch == 1 is linalg.matmul.
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t batch,
+    int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out);
+
+// Host-buffer form. |out| holds batch*M*N f32 / i32 values; with FLAG_ACCUMULATE it is
+// also the accumulator input.
+IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops,
+                                                           int32_t element_type, int64_t batch,
+                                                           int64_t M, int64_t N, int64_t K,
+                                                           uint32_t flags, const void* lhs,
+                                                           const void* rhs, void* out);
+
+#ifdef __cplusplus
+}  // extern "C"
+#endif
+
+#endif  // IREE_B200_OPS_H_

@@ -1,0 +1,761 @@
+// command_buffer.cc — recording and submission of dispatches, transfers and collectives.
+//
+// Stands in for runtime/src/iree/hal/drivers/cuda/{stream_command_buffer.c,
+// graph_command_buffer.c}, hal/utils/{deferred_command_buffer.c, collective_batch.c} and
+// the queue_execute/submit path of cuda_device.c:1168-1196,260-281.
+//
+// A command buffer is a recorded command list. In STREAM mode queue_execute replays it
+// onto the dispatch stream (what the reference does with a deferred command buffer,
+// hal/utils/deferred_work_queue.c:1198-1214 → stream_command_buffer.c); in GRAPH mode
+// end() lowers the list to a CUgraph (kernel / memset / memcpy nodes, execution barriers
+// as empty join nodes, graph_command_buffer.c:413-439) and queue_execute launches the
+// instantiated graph.
+//
+// Kernel parameter packing is the reference's (stream_command_buffer.c:532-587): one
+// device pointer per binding in layout order, then one slot per 32-bit push constant.
+// For exports that ship a TMA recipe the encoded CUtensorMaps follow as trailing
+// parameters (include/iree_b200_tma_recipe.h).
+
+#include <cstdlib>
+#include <memory>
+
+#include "internal.h"
+
+using namespace b200hal;
+
+namespace {
+
+struct AlignedFree {
+  void operator()(void* p) const { free(p); }
+};
+
+enum class CommandKind { kDispatch, kFill, kUpdate, kCopy, kCollective, kBarrier };
+
+struct Command {
+  CommandKind kind = CommandKind::kBarrier;
+  // dispatch
+  CUfunction function = nullptr;
+  uint32_t grid[3] = {1, 1, 1};
+  uint32_t block[3] = {1, 1, 1};
+  uint32_t shared_memory = 0;
+  std::unique_ptr<uint8_t, AlignedFree> storage;  // payload slots / captured bytes
+  void** params = nullptr;                        // points into |storage|
+  // fill / update / copy
+  CUdeviceptr target = 0;
+  CUdeviceptr source = 0;
+  uint64_t length = 0;
+  uint32_t pattern = 0;
+  uint32_t pattern_length = 0;
+  // collective
+  iree_b200_channel_t* channel = nullptr;
+  uint32_t op = 0;
+  uint32_t param = 0;
+  uint64_t element_count = 0;
+};
+
+enum class State { kInitial, kRecording, kExecutable };
+
+}  // namespace
+
+struct iree_b200_command_buffer_t : b200hal::RefCounted {
+  iree_b200_device_t* device = nullptr;
+  int32_t mode = IREE_B200_COMMAND_BUFFER_MODE_STREAM;
+  State state = State::kInitial;
+  std::vector<Command> commands;
+  // resource_set (stream_command_buffer.c:528-530,569-571)
+  std::vector<iree_b200_buffer_t*> buffers;
+  std::vector<iree_b200_executable_t*> executables;
+  std::vector<iree_b200_channel_t*> channels;
+  CUgraph graph = nullptr;
+  CUgraphExec graph_exec = nullptr;
+};
+
+namespace {
+
+iree_b200_status_t resolve_ref(iree_b200_command_buffer_t* cb, const iree_b200_buffer_ref_t& ref,
+                               bool allow_null, CUdeviceptr* out_ptr, uint64_t* out_length) {
+  *out_ptr = 0;
+  *out_length = 0;
+  if (!ref.buffer) {
+    if (allow_null) return IREE_B200_STATUS_OK;
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "buffer reference is NULL");
+  }
+  const uint64_t total = ref.buffer->byte_length;
+  if (ref.offset > total) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "binding offset %llu exceeds buffer of %llu bytes",
+                       (unsigned long long)ref.offset, (unsigned long long)total);
+  }
+  uint64_t length = ref.length == UINT64_MAX ? total - ref.offset : ref.length;
+  if (length > total - ref.offset) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "binding range [%llu, +%llu) exceeds buffer of %llu bytes",
+                       (unsigned long long)ref.offset, (unsigned long long)length,
+                       (unsigned long long)total);
+  }
+  *out_ptr = ref.buffer->device_ptr + ref.offset;
+  *out_length = length;
+  iree_b200_buffer_retain(ref.buffer);
+  cb->buffers.push_back(ref.buffer);
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t require_recording(iree_b200_command_buffer_t* cb) {
+  if (!cb) return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "command buffer is NULL");
+  if (cb->state != State::kRecording) {
+    return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
+                       "command buffer is not in the recording state (begin/end mismatch)");
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+uint32_t collective_element_size(uint32_t element_type) {
+  switch (element_type) {
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_8:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_8:
+      return 1;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_16:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_16:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_16:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_BFLOAT_16:
+      return 2;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_32:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_32:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_32:
+      return 4;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_64:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_64:
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_64:
+      return 8;
+    default:
+      return 0;
+  }
+}
+
+// nccl_channel.c:255-299 with BFLOAT_16 → ncclBfloat16.
+iree_b200_status_t to_nccl_type(uint32_t element_type, ncclDataType_t* out) {
+  switch (element_type) {
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_8: *out = ncclInt8; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_8: *out = ncclUint8; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_32: *out = ncclInt32; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_32: *out = ncclUint32; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_SINT_64: *out = ncclInt64; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_UINT_64: *out = ncclUint64; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_16: *out = ncclFloat16; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_32: *out = ncclFloat32; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_64: *out = ncclFloat64; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_BFLOAT_16: *out = ncclBfloat16; break;
+    default:
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "unhandled element type for NCCL: %u", element_type);
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+// nccl_channel.c:301-325.
+iree_b200_status_t to_nccl_redop(uint32_t reduction, ncclRedOp_t* out) {
+  switch (reduction) {
+    case IREE_B200_COLLECTIVE_REDUCTION_SUM: *out = ncclSum; break;
+    case IREE_B200_COLLECTIVE_REDUCTION_PRODUCT: *out = ncclProd; break;
+    case IREE_B200_COLLECTIVE_REDUCTION_MINIMUM: *out = ncclMin; break;
+    case IREE_B200_COLLECTIVE_REDUCTION_MAXIMUM: *out = ncclMax; break;
+    case IREE_B200_COLLECTIVE_REDUCTION_AVERAGE: *out = ncclAvg; break;
+    default:
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "unhandled reduction operation for NCCL: %u", reduction);
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+// One entry of a batch (nccl_channel.c:327-540).
+iree_b200_status_t issue_collective(const Command& c, CUstream stream) {
+  const NcclSymbols* nccl = c.channel->nccl;
+  const CudaSymbols* cu = c.channel->device->cu;
+  ncclComm_t comm = c.channel->comm;
+  const uint32_t kind = c.op & 0xff;
+  const uint32_t reduction = (c.op >> 8) & 0xff;
+  const uint32_t element_type = (c.op >> 16) & 0xff;
+  ncclDataType_t dtype;
+  B200_RETURN_IF_ERROR(to_nccl_type(element_type, &dtype));
+  const void* send = reinterpret_cast<const void*>(c.source);
+  void* recv = reinterpret_cast<void*>(c.target);
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  switch (kind) {
+    case IREE_B200_COLLECTIVE_KIND_ALL_GATHER:
+      B200_NCCL(nccl, ncclAllGather(send, recv, c.element_count, dtype, comm, s));
+      break;
+    case IREE_B200_COLLECTIVE_KIND_ALL_REDUCE: {
+      ncclRedOp_t redop;
+      B200_RETURN_IF_ERROR(to_nccl_redop(reduction, &redop));
+      B200_NCCL(nccl, ncclAllReduce(send, recv, c.element_count, dtype, redop, comm, s));
+      break;
+    }
+    case IREE_B200_COLLECTIVE_KIND_ALL_TO_ALL: {
+      // send/recv loop, element_count/count per peer (nccl_channel.c:381-410).
+      const int count = c.channel->count;
+      const uint64_t per_rank = c.element_count / (uint64_t)count;
+      const uint64_t bytes = per_rank * collective_element_size(element_type);
+      for (int r = 0; r < count; ++r) {
+        B200_NCCL(nccl, ncclSend(static_cast<const uint8_t*>(send) + r * bytes, per_rank, dtype, r,
+                                 comm, s));
+        B200_NCCL(nccl,
+                  ncclRecv(static_cast<uint8_t*>(recv) + r * bytes, per_rank, dtype, r, comm, s));
+      }
+      break;
+    }
+    case IREE_B200_COLLECTIVE_KIND_BROADCAST:
+      B200_NCCL(nccl, ncclBroadcast(send, recv, c.element_count, dtype, (int)c.param, comm, s));
+      break;
+    case IREE_B200_COLLECTIVE_KIND_REDUCE: {
+      ncclRedOp_t redop;
+      B200_RETURN_IF_ERROR(to_nccl_redop(reduction, &redop));
+      B200_NCCL(nccl, ncclReduce(send, recv, c.element_count, dtype, redop, (int)c.param, comm, s));
+      break;
+    }
+    case IREE_B200_COLLECTIVE_KIND_REDUCE_SCATTER: {
+      ncclRedOp_t redop;
+      B200_RETURN_IF_ERROR(to_nccl_redop(reduction, &redop));
+      B200_NCCL(nccl, ncclReduceScatter(send, recv, c.element_count, dtype, redop, comm, s));
+      break;
+    }
+    case IREE_B200_COLLECTIVE_KIND_SEND:
+      B200_NCCL(nccl, ncclSend(send, c.element_count, dtype, (int)c.param, comm, s));
+      break;
+    case IREE_B200_COLLECTIVE_KIND_RECV:
+      B200_NCCL(nccl, ncclRecv(recv, c.element_count, dtype, (int)c.param, comm, s));
+      break;
+    case IREE_B200_COLLECTIVE_KIND_SEND_RECV: {
+      // param: target rank in the low 16 bits, source rank in the high 16; -1 = none,
+      // and a missing source zero-fills the receive buffer (nccl_channel.c:491-537).
+      const int16_t send_rank = (int16_t)(c.param & 0xffff);
+      const int16_t recv_rank = (int16_t)(c.param >> 16);
+      if (send_rank != -1) {
+        B200_NCCL(nccl, ncclSend(send, c.element_count, dtype, send_rank, comm, s));
+      }
+      if (recv_rank != -1) {
+        B200_NCCL(nccl, ncclRecv(recv, c.element_count, dtype, recv_rank, comm, s));
+      } else {
+        B200_CU(cu, cuMemsetD8Async(c.target, 0,
+                                    c.element_count * collective_element_size(element_type),
+                                    stream));
+      }
+      break;
+    }
+    default:
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "unhandled collective kind %u", kind);
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+// iree_hal_cuda_nccl_submit_batch (nccl_channel.c:542-588): one group per flushed batch.
+// With a collective stream the batch is ordered after everything already on the dispatch
+// stream and left running; |*pending_join| tells the caller to join before the next
+// dependent command (the next execution barrier or the end of the command buffer).
+iree_b200_status_t flush_collectives(iree_b200_device_t* device, std::vector<const Command*>* batch,
+                                     bool* pending_join, CUevent fork_event) {
+  if (batch->empty()) return IREE_B200_STATUS_OK;
+  const CudaSymbols* cu = device->cu;
+  CUstream stream = device->dispatch_stream;
+  if (device->collective_stream) {
+    B200_CU(cu, cuEventRecord(fork_event, device->dispatch_stream));
+    B200_CU(cu, cuStreamWaitEvent(device->collective_stream, fork_event, 0));
+    stream = device->collective_stream;
+    *pending_join = true;
+  }
+  const NcclSymbols* nccl = batch->front()->channel->nccl;
+  B200_NCCL(nccl, ncclGroupStart());
+  iree_b200_status_t status = IREE_B200_STATUS_OK;
+  for (const Command* c : *batch) {
+    status = issue_collective(*c, stream);
+    if (status != IREE_B200_STATUS_OK) break;
+  }
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  ncclResult_t end_result = nccl->ncclGroupEnd();
+  batch->clear();
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  if (end_result != ncclSuccess) {
+    return nccl_status(nccl, end_result, "ncclGroupEnd()", __FILE__, __LINE__);
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t join_collectives(iree_b200_device_t* device, bool* pending_join,
+                                    CUevent join_event) {
+  if (!*pending_join) return IREE_B200_STATUS_OK;
+  const CudaSymbols* cu = device->cu;
+  B200_CU(cu, cuEventRecord(join_event, device->collective_stream));
+  B200_CU(cu, cuStreamWaitEvent(device->dispatch_stream, join_event, 0));
+  *pending_join = false;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
+  iree_b200_device_t* device = cb->device;
+  const CudaSymbols* cu = device->cu;
+  CUstream stream = device->dispatch_stream;
+  std::vector<const Command*> batch;
+  bool pending_join = false;
+  CUevent fork_event = nullptr, join_event = nullptr;
+  if (device->collective_stream) {
+    B200_CU(cu, cuEventCreate(&fork_event, CU_EVENT_DISABLE_TIMING));
+    B200_CU(cu, cuEventCreate(&join_event, CU_EVENT_DISABLE_TIMING));
+  }
+  iree_b200_status_t status = IREE_B200_STATUS_OK;
+  auto run = [&]() -> iree_b200_status_t {
+    for (const Command& c : cb->commands) {
+      if (c.kind == CommandKind::kCollective) {
+        batch.push_back(&c);
+        continue;
+      }
+      // Every other command flushes the batch first (stream_command_buffer.c:154-171).
+      B200_RETURN_IF_ERROR(flush_collectives(device, &batch, &pending_join, fork_event));
+      switch (c.kind) {
+        case CommandKind::kBarrier:
+          B200_RETURN_IF_ERROR(join_collectives(device, &pending_join, join_event));
+          break;
+        case CommandKind::kDispatch:
+          B200_CU(cu, cuLaunchKernel(c.function, c.grid[0], c.grid[1], c.grid[2], c.block[0],
+                                     c.block[1], c.block[2], c.shared_memory, stream, c.params,
+                                     nullptr));
+          break;
+        case CommandKind::kFill:
+          if (c.pattern_length == 4) {
+            B200_CU(cu, cuMemsetD32Async(c.target, c.pattern, c.length / 4, stream));
+          } else if (c.pattern_length == 2) {
+            B200_CU(cu, cuMemsetD16Async(c.target, (uint16_t)c.pattern, c.length / 2, stream));
+          } else {
+            B200_CU(cu, cuMemsetD8Async(c.target, (uint8_t)c.pattern, c.length, stream));
+          }
+          break;
+        case CommandKind::kUpdate:
+          B200_CU(cu, cuMemcpyHtoDAsync(c.target, c.storage.get(), c.length, stream));
+          break;
+        case CommandKind::kCopy:
+          B200_CU(cu, cuMemcpyAsync(c.target, c.source, c.length, stream));
+          break;
+        default:
+          break;
+      }
+    }
+    B200_RETURN_IF_ERROR(flush_collectives(device, &batch, &pending_join, fork_event));
+    B200_RETURN_IF_ERROR(join_collectives(device, &pending_join, join_event));
+    return IREE_B200_STATUS_OK;
+  };
+  status = run();
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (fork_event) cu->cuEventDestroy(fork_event);
+  if (join_event) cu->cuEventDestroy(join_event);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
+  iree_b200_device_t* device = cb->device;
+  const CudaSymbols* cu = device->cu;
+  B200_CU(cu, cuGraphCreate(&cb->graph, 0));
+  std::vector<CUgraphNode> group;   // nodes recorded since the last barrier
+  CUgraphNode barrier = nullptr;    // join node of the previous barrier
+  for (const Command& c : cb->commands) {
+    const CUgraphNode* deps = barrier ? &barrier : nullptr;
+    const size_t dep_count = barrier ? 1 : 0;
+    CUgraphNode node = nullptr;
+    switch (c.kind) {
+      case CommandKind::kBarrier: {
+        if (group.empty()) break;
+        B200_CU(cu, cuGraphAddEmptyNode(&node, cb->graph, group.data(), group.size()));
+        barrier = node;
+        group.clear();
+        continue;
+      }
+      case CommandKind::kDispatch: {
+        CUDA_KERNEL_NODE_PARAMS p;
+        memset(&p, 0, sizeof(p));
+        p.func = c.function;
+        p.gridDimX = c.grid[0];
+        p.gridDimY = c.grid[1];
+        p.gridDimZ = c.grid[2];
+        p.blockDimX = c.block[0];
+        p.blockDimY = c.block[1];
+        p.blockDimZ = c.block[2];
+        p.sharedMemBytes = c.shared_memory;
+        p.kernelParams = c.params;
+        B200_CU(cu, cuGraphAddKernelNode(&node, cb->graph, deps, dep_count, &p));
+        break;
+      }
+      case CommandKind::kFill: {
+        CUDA_MEMSET_NODE_PARAMS p;
+        memset(&p, 0, sizeof(p));
+        p.dst = c.target;
+        p.elementSize = c.pattern_length;
+        p.value = c.pattern;
+        p.width = c.length / c.pattern_length;
+        p.height = 1;
+        B200_CU(cu, cuGraphAddMemsetNode(&node, cb->graph, deps, dep_count, &p, device->cu_context));
+        break;
+      }
+      case CommandKind::kUpdate:
+      case CommandKind::kCopy: {
+        CUDA_MEMCPY3D p;
+        memset(&p, 0, sizeof(p));
+        if (c.kind == CommandKind::kUpdate) {
+          p.srcMemoryType = CU_MEMORYTYPE_HOST;
+          p.srcHost = c.storage.get();
+        } else {
+          p.srcMemoryType = CU_MEMORYTYPE_DEVICE;
+          p.srcDevice = c.source;
+        }
+        p.dstMemoryType = CU_MEMORYTYPE_DEVICE;
+        p.dstDevice = c.target;
+        p.WidthInBytes = c.length;
+        p.Height = 1;
+        p.Depth = 1;
+        B200_CU(cu, cuGraphAddMemcpyNode(&node, cb->graph, deps, dep_count, &p, device->cu_context));
+        break;
+      }
+      case CommandKind::kCollective:
+        // graph_command_buffer.c:291-327: collectives in graphs are unimplemented in the
+        // reference as well.
+        return make_status(IREE_B200_STATUS_UNIMPLEMENTED,
+                           "collectives are not supported in graph command buffers; create the "
+                           "device with IREE_B200_COMMAND_BUFFER_MODE_STREAM");
+    }
+    if (node) group.push_back(node);
+  }
+  B200_CU(cu, cuGraphInstantiateWithFlags(&cb->graph_exec, cb->graph, 0));
+  return IREE_B200_STATUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+iree_b200_status_t iree_b200_command_buffer_create(iree_b200_device_t* device,
+                                                   iree_b200_command_buffer_t** out_command_buffer) {
+  B200_REQUIRE_ARG(device && out_command_buffer);
+  auto* cb = new iree_b200_command_buffer_t();
+  cb->device = device;
+  cb->mode = device->params.command_buffer_mode;
+  iree_b200_device_retain(device);
+  *out_command_buffer = cb;
+  return IREE_B200_STATUS_OK;
+}
+
+void iree_b200_command_buffer_retain(iree_b200_command_buffer_t* cb) {
+  if (cb) cb->ref_count.fetch_add(1);
+}
+
+void iree_b200_command_buffer_release(iree_b200_command_buffer_t* cb) {
+  if (!cb || cb->ref_count.fetch_sub(1) != 1) return;
+  iree_b200_device_t* device = cb->device;
+  device->cu->cuCtxSetCurrent(device->cu_context);
+  if (cb->graph_exec) device->cu->cuGraphExecDestroy(cb->graph_exec);
+  if (cb->graph) device->cu->cuGraphDestroy(cb->graph);
+  for (auto* b : cb->buffers) iree_b200_buffer_release(b);
+  for (auto* e : cb->executables) iree_b200_executable_release(e);
+  for (auto* c : cb->channels) iree_b200_channel_release(c);
+  delete cb;
+  iree_b200_device_release(device);
+}
+
+iree_b200_status_t iree_b200_command_buffer_begin(iree_b200_command_buffer_t* cb) {
+  B200_REQUIRE_ARG(cb);
+  if (cb->state != State::kInitial) {
+    return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
+                       "command buffer is already recording or has been recorded");
+  }
+  cb->state = State::kRecording;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_end(iree_b200_command_buffer_t* cb) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  if (cb->mode == IREE_B200_COMMAND_BUFFER_MODE_GRAPH) {
+    cb->device->cu->cuCtxSetCurrent(cb->device->cu_context);
+    B200_RETURN_IF_ERROR(build_graph(cb));
+  }
+  cb->state = State::kExecutable;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_execution_barrier(iree_b200_command_buffer_t* cb) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  Command c;
+  c.kind = CommandKind::kBarrier;
+  cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_fill_buffer(iree_b200_command_buffer_t* cb,
+                                                        iree_b200_buffer_ref_t target,
+                                                        const void* pattern,
+                                                        size_t pattern_length) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  B200_REQUIRE_ARG(pattern);
+  if (pattern_length != 1 && pattern_length != 2 && pattern_length != 4) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "fill patterns must be 1, 2 or 4 bytes (got %zu)", pattern_length);
+  }
+  Command c;
+  c.kind = CommandKind::kFill;
+  B200_RETURN_IF_ERROR(resolve_ref(cb, target, false, &c.target, &c.length));
+  if (c.target % pattern_length != 0 || c.length % pattern_length != 0) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "fill range must be aligned to the pattern length %zu", pattern_length);
+  }
+  memcpy(&c.pattern, pattern, pattern_length);
+  c.pattern_length = (uint32_t)pattern_length;
+  if (c.length) cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_update_buffer(iree_b200_command_buffer_t* cb,
+                                                          const void* source, size_t source_offset,
+                                                          iree_b200_buffer_ref_t target) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  B200_REQUIRE_ARG(source);
+  Command c;
+  c.kind = CommandKind::kUpdate;
+  B200_RETURN_IF_ERROR(resolve_ref(cb, target, false, &c.target, &c.length));
+  if (!c.length) return IREE_B200_STATUS_OK;
+  // The source is captured: callers may reuse their memory as soon as this returns
+  // (stream_command_buffer.c:383-392).
+  c.storage.reset(static_cast<uint8_t*>(aligned_alloc(64, (c.length + 63) / 64 * 64)));
+  if (!c.storage) return make_status(IREE_B200_STATUS_RESOURCE_EXHAUSTED, "out of host memory");
+  memcpy(c.storage.get(), static_cast<const uint8_t*>(source) + source_offset, c.length);
+  cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_copy_buffer(iree_b200_command_buffer_t* cb,
+                                                        iree_b200_buffer_ref_t source,
+                                                        iree_b200_buffer_ref_t target) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  Command c;
+  c.kind = CommandKind::kCopy;
+  uint64_t source_length = 0;
+  B200_RETURN_IF_ERROR(resolve_ref(cb, source, false, &c.source, &source_length));
+  B200_RETURN_IF_ERROR(resolve_ref(cb, target, false, &c.target, &c.length));
+  if (source_length != c.length) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "copy source (%llu bytes) and target (%llu bytes) lengths differ",
+                       (unsigned long long)source_length, (unsigned long long)c.length);
+  }
+  if (c.length) cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_dispatch(
+    iree_b200_command_buffer_t* cb, iree_b200_executable_t* executable, int32_t export_ordinal,
+    const uint32_t workgroup_count[3], const uint32_t* constants, size_t constant_count,
+    const iree_b200_buffer_ref_t* bindings, size_t binding_count, uint64_t flags) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  B200_REQUIRE_ARG(executable && workgroup_count);
+  B200_REQUIRE_ARG(constants || !constant_count);
+  B200_REQUIRE_ARG(bindings || !binding_count);
+  if (flags != 0) {
+    // Indirect / custom-argument dispatches are rejected (stream_command_buffer.c:495-503).
+    return make_status(IREE_B200_STATUS_UNIMPLEMENTED, "dispatch flags 0x%llx are not supported",
+                       (unsigned long long)flags);
+  }
+  if (export_ordinal < 0 || (size_t)export_ordinal >= executable->exports.size()) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "export ordinal %d out of range; executable has %zu exports",
+                       export_ordinal, executable->exports.size());
+  }
+  const KernelParams& k = executable->exports[export_ordinal];
+  if (constant_count != k.constant_count) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "dispatch of `%s` requires %u constants but %zu were provided", k.name.c_str(),
+                       k.constant_count, constant_count);
+  }
+  if (binding_count != k.binding_count) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "dispatch of `%s` requires %u bindings but %zu were provided", k.name.c_str(),
+                       k.binding_count, binding_count);
+  }
+  // A zero-sized grid is a no-op (hal/command_buffer.c treats it as such).
+  if (!workgroup_count[0] || !workgroup_count[1] || !workgroup_count[2]) {
+    return IREE_B200_STATUS_OK;
+  }
+
+  const uint32_t map_count = k.has_recipe ? k.recipe.map_count : 0;
+  const size_t slot_count = binding_count + constant_count;
+  const size_t maps_bytes = (size_t)map_count * sizeof(CUtensorMap);
+  const size_t slots_bytes = slot_count * 8;
+  const size_t params_bytes = (slot_count + map_count) * sizeof(void*);
+  const size_t total = (maps_bytes + slots_bytes + params_bytes + 63) / 64 * 64 + 64;
+
+  Command c;
+  c.kind = CommandKind::kDispatch;
+  c.function = k.function;
+  for (int d = 0; d < 3; ++d) {
+    c.grid[d] = workgroup_count[d];
+    c.block[d] = k.block_dims[d];
+  }
+  c.shared_memory = k.block_shared_memory_size;
+  c.storage.reset(static_cast<uint8_t*>(aligned_alloc(64, total)));
+  if (!c.storage) return make_status(IREE_B200_STATUS_RESOURCE_EXHAUSTED, "out of host memory");
+  memset(c.storage.get(), 0, total);
+  CUtensorMap* maps = reinterpret_cast<CUtensorMap*>(c.storage.get());
+  uint64_t* slots = reinterpret_cast<uint64_t*>(c.storage.get() + maps_bytes);
+  c.params = reinterpret_cast<void**>(c.storage.get() + maps_bytes + slots_bytes);
+
+  uint64_t binding_ptrs[IREE_B200_MAX_DISPATCH_BINDING_COUNT] = {0};
+  for (size_t i = 0; i < binding_count; ++i) {
+    CUdeviceptr ptr = 0;
+    uint64_t length = 0;
+    B200_RETURN_IF_ERROR(resolve_ref(cb, bindings[i], /*allow_null=*/true, &ptr, &length));
+    binding_ptrs[i] = ptr;
+    slots[i] = ptr;
+    c.params[i] = &slots[i];
+  }
+  for (size_t i = 0; i < constant_count; ++i) {
+    slots[binding_count + i] = constants[i];  // low 32 bits are the value
+    c.params[binding_count + i] = &slots[binding_count + i];
+  }
+  if (map_count) {
+    cb->device->cu->cuCtxSetCurrent(cb->device->cu_context);
+    for (uint32_t m = 0; m < map_count; ++m) {
+      const iree_b200_tma_map_t& map = k.recipe.maps[m];
+      B200_RETURN_IF_ERROR(encode_tensor_map(cb->device->cu, map, binding_ptrs[map.binding],
+                                             constants, constant_count, &maps[m]));
+      c.params[slot_count + m] = &maps[m];
+    }
+  }
+  iree_b200_executable_retain(executable);
+  cb->executables.push_back(executable);
+  cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_command_buffer_collective(
+    iree_b200_command_buffer_t* cb, iree_b200_channel_t* channel, uint32_t packed_op,
+    uint32_t param, iree_b200_buffer_ref_t send_binding, iree_b200_buffer_ref_t recv_binding,
+    uint64_t element_count) {
+  B200_RETURN_IF_ERROR(require_recording(cb));
+  B200_REQUIRE_ARG(channel);
+  const uint32_t kind = packed_op & 0xff;
+  const uint32_t element_type = (packed_op >> 16) & 0xff;
+  if (kind > IREE_B200_COLLECTIVE_KIND_SEND_RECV) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "unhandled collective kind %u", kind);
+  }
+  const uint32_t element_size = collective_element_size(element_type);
+  if (!element_size) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "unhandled collective element type %u",
+                       element_type);
+  }
+  ncclDataType_t dtype;
+  B200_RETURN_IF_ERROR(to_nccl_type(element_type, &dtype));
+  Command c;
+  c.kind = CommandKind::kCollective;
+  c.channel = channel;
+  c.op = packed_op;
+  c.param = param;
+  c.element_count = element_count;
+  uint64_t send_length = 0, recv_length = 0;
+  B200_RETURN_IF_ERROR(resolve_ref(cb, send_binding, true, &c.source, &send_length));
+  B200_RETURN_IF_ERROR(resolve_ref(cb, recv_binding, true, &c.target, &recv_length));
+  // Binding requirements per kind (command_buffer.h:300-400).
+  const bool needs_send = kind != IREE_B200_COLLECTIVE_KIND_RECV &&
+                          kind != IREE_B200_COLLECTIVE_KIND_SEND_RECV;
+  const bool needs_recv = kind != IREE_B200_COLLECTIVE_KIND_SEND &&
+                          kind != IREE_B200_COLLECTIVE_KIND_SEND_RECV;
+  if ((needs_send && !c.source) || (needs_recv && !c.target)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "collective kind %u is missing a required binding", kind);
+  }
+  uint64_t send_elements = element_count, recv_elements = element_count;
+  if (kind == IREE_B200_COLLECTIVE_KIND_ALL_GATHER) recv_elements *= (uint64_t)channel->count;
+  if (kind == IREE_B200_COLLECTIVE_KIND_REDUCE_SCATTER) send_elements *= (uint64_t)channel->count;
+  if (c.source && send_length < send_elements * element_size) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "collective send binding holds %llu bytes but %llu are required",
+                       (unsigned long long)send_length,
+                       (unsigned long long)(send_elements * element_size));
+  }
+  if (c.target && recv_length < recv_elements * element_size) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "collective recv binding holds %llu bytes but %llu are required",
+                       (unsigned long long)recv_length,
+                       (unsigned long long)(recv_elements * element_size));
+  }
+  iree_b200_channel_retain(channel);
+  cb->channels.push_back(channel);
+  cb->commands.push_back(std::move(c));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_device_queue_execute(
+    iree_b200_device_t* device, size_t wait_count, iree_b200_semaphore_t* const* wait_semaphores,
+    const uint64_t* wait_values, size_t signal_count,
+    iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
+    iree_b200_command_buffer_t* command_buffer) {
+  B200_REQUIRE_ARG(device);
+  B200_REQUIRE_ARG(!wait_count || (wait_semaphores && wait_values));
+  B200_REQUIRE_ARG(!signal_count || (signal_semaphores && signal_values));
+  if (command_buffer && command_buffer->state != State::kExecutable) {
+    return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
+                       "command buffer has not been ended (state is not executable)");
+  }
+  const CudaSymbols* cu = device->cu;
+  std::lock_guard<std::mutex> lock(device->mutex);
+  B200_CU(cu, cuCtxSetCurrent(device->cu_context));
+
+  // Device-side waits (cuda_device.c:148-158,229-240).
+  for (size_t i = 0; i < wait_count; ++i) {
+    iree_b200_semaphore_t* s = wait_semaphores[i];
+    std::lock_guard<std::mutex> sem_lock(s->mutex);
+    if (s->failure != IREE_B200_STATUS_OK) {
+      return make_status(s->failure, "wait semaphore has failed: %s", s->failure_message.c_str());
+    }
+    if (s->host_value >= wait_values[i]) continue;
+    CUevent event = nullptr;
+    for (auto& tp : s->timepoints) {
+      if (tp.value >= wait_values[i]) {
+        event = tp.event;
+        break;
+      }
+    }
+    if (!event) {
+      return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
+                         "wait on semaphore value %llu that no queued operation signals",
+                         (unsigned long long)wait_values[i]);
+    }
+    B200_CU(cu, cuStreamWaitEvent(device->dispatch_stream, event, 0));
+  }
+
+  iree_b200_status_t status = IREE_B200_STATUS_OK;
+  if (command_buffer) {
+    if (command_buffer->mode == IREE_B200_COMMAND_BUFFER_MODE_GRAPH) {
+      CUresult r = cu->cuGraphLaunch(command_buffer->graph_exec, device->dispatch_stream);
+      if (r != CUDA_SUCCESS) status = cu_status(cu, r, "cuGraphLaunch", __FILE__, __LINE__);
+    } else {
+      status = replay_on_stream(command_buffer);
+    }
+  }
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+
+  for (size_t i = 0; i < signal_count; ++i) {
+    iree_b200_semaphore_t* s = signal_semaphores[i];
+    std::lock_guard<std::mutex> sem_lock(s->mutex);
+    if (status != IREE_B200_STATUS_OK) {
+      // Async failure delivery (cuda_device.c:1187-1191).
+      s->failure = status;
+      s->failure_message = message;
+      continue;
+    }
+    CUevent event = nullptr;
+    CUresult r = cu->cuEventCreate(&event, CU_EVENT_DISABLE_TIMING);
+    if (r == CUDA_SUCCESS) r = cu->cuEventRecord(event, device->dispatch_stream);
+    if (r != CUDA_SUCCESS) {
+      status = cu_status(cu, r, "cuEventCreate/Record", __FILE__, __LINE__);
+      message = iree_b200_status_message();
+      s->failure = status;
+      s->failure_message = message;
+      continue;
+    }
+    s->timepoints.push_back({signal_values[i], event});
+  }
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
+
+}  // extern "C"

@@ -16,6 +16,8 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+#include "gemm_config.h"
+
 namespace b200 {
 
 // 128-byte opaque TMA descriptor (same size/alignment as CUtensorMap).
@@ -234,8 +236,6 @@ B200_DEVICE void tcgen05_fence_after() {
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 }
 
-// MMA kinds.
-enum : int { KIND_F16 = 0, KIND_I8 = 1 };
 
 // D[tmem] (+)= A[smem desc] * B[smem desc]. Issued by ONE thread.
 template <int kCtaGroup, int kKind>
@@ -382,20 +382,6 @@ B200_DEVICE uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes
   d |= 1ull << 46;
   d |= 2ull << 61;
   return d;
-}
-
-enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_U8 = 0, FMT_S8 = 1 };
-enum : uint32_t { CFMT_F16 = 0, CFMT_F32 = 1, CFMT_S32 = 2 };
-enum : uint32_t { MAJOR_K = 0, MAJOR_MN = 1 };
-
-// 32-bit instruction descriptor:
-//   [4,6) D format  [7,10) A format  [10,13) B format  [15] A major  [16] B major
-//   [17,23) N>>3    [24,29) M>>4
-__host__ __device__ constexpr uint32_t make_idesc(uint32_t c_fmt, uint32_t a_fmt, uint32_t b_fmt,
-                                                  uint32_t a_major, uint32_t b_major, uint32_t m,
-                                                  uint32_t n) {
-  return (c_fmt << 4) | (a_fmt << 7) | (b_fmt << 10) | (a_major << 15) | (b_major << 16) |
-         ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
 B200_DEVICE void named_barrier_sync(uint32_t id, uint32_t threads) {

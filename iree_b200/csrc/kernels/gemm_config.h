@@ -1,0 +1,83 @@
+// gemm_config.h — compile-time geometry of the tcgen05 GEMM family.
+//
+// Pure constexpr arithmetic with no CUDA dependency, so the same definitions feed the
+// kernels (gemm_sm100.cuh) and the host-side manifest tool that writes the export table
+// of the CDA1 executable (block dims, dynamic shared memory, constant/binding counts —
+// what compiler/plugins/target/CUDA/CUDATarget.cpp:661-691 takes from the export op).
+
+#pragma once
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define B200_HOST_DEVICE __host__ __device__
+#else
+#define B200_HOST_DEVICE
+#endif
+
+namespace b200 {
+
+// MMA kinds.
+enum : int { KIND_F16 = 0, KIND_I8 = 1 };
+
+enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_U8 = 0, FMT_S8 = 1 };
+enum : uint32_t { CFMT_F16 = 0, CFMT_F32 = 1, CFMT_S32 = 2 };
+enum : uint32_t { MAJOR_K = 0, MAJOR_MN = 1 };
+
+// 32-bit instruction descriptor:
+//   [4,6) D format  [7,10) A format  [10,13) B format  [15] A major  [16] B major
+//   [17,23) N>>3    [24,29) M>>4
+B200_HOST_DEVICE constexpr uint32_t make_idesc(uint32_t c_fmt, uint32_t a_fmt, uint32_t b_fmt,
+                                                  uint32_t a_major, uint32_t b_major, uint32_t m,
+                                                  uint32_t n) {
+  return (c_fmt << 4) | (a_fmt << 7) | (b_fmt << 10) | (a_major << 15) | (b_major << 16) |
+         ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+
+template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_>
+struct GemmConfig {
+  static constexpr int kCtaGroup = kCtaGroup_;
+  static constexpr int kKind = kKind_;
+  static constexpr uint32_t kAbFmt = kAbFmt_;
+  static constexpr bool kBMajorK = kBMajorK_;
+  static constexpr int kStages = kStages_;
+
+  static constexpr int kElemSize = (kKind == KIND_I8) ? 1 : 2;
+  static constexpr int kBlockM = 128;                    // rows per CTA
+  static constexpr int kTileM = kBlockM * kCtaGroup;     // rows per cluster tile
+  static constexpr int kTileN = 256;                     // UMMA N
+  static constexpr int kBlockN = kTileN / kCtaGroup;     // B columns loaded per CTA
+  static constexpr int kBlockK = 128 / kElemSize;        // elements per 128-byte row
+  static constexpr int kUmmaK = 32 / kElemSize;
+  static constexpr int kKSteps = kBlockK / kUmmaK;       // 4
+
+  static constexpr int kABytes = kBlockM * 128;                 // 16 KiB
+  static constexpr int kBBytes = kBlockN * kBlockK * kElemSize; // 16 / 32 KiB
+  static constexpr int kStageBytes = kABytes + kBBytes;
+
+  // MN-major B: [kBlockK rows][128 B of N] blocks, one TMA box each.
+  static constexpr int kBBoxN = 128 / kElemSize;               // N elements per box
+  static constexpr int kBBoxBytes = kBlockK * 128;             // bytes per box
+  static constexpr int kBBoxes = kBBytes / kBBoxBytes;
+
+  static constexpr int kAccStages = 2;
+  static constexpr int kTmemCols = kAccStages * kTileN;  // 512
+  static constexpr int kEpiCols = 32;                    // columns per epilogue chunk
+  static constexpr int kEpiBytes = kBlockM * kEpiCols * 4;  // 16 KiB
+  static constexpr int kEpiBufs = 2;
+
+  static constexpr int kSmemTiles = kStages * kStageBytes + kEpiBufs * kEpiBytes;
+  static constexpr int kNumBarriers = 2 * kStages + 2 * kAccStages;
+  static constexpr int kSmemBytes = 1024 /*align slack*/ + kSmemTiles + kNumBarriers * 8 + 16;
+
+  static constexpr int kThreads = 256;
+  static constexpr int kGroupM = 8;  // raster group height in tiles
+
+  static constexpr uint32_t kIdesc =
+      make_idesc(kKind == KIND_I8 ? CFMT_S32 : CFMT_F32, kAbFmt, kAbFmt, MAJOR_K,
+                 kBMajorK ? MAJOR_K : MAJOR_MN, kTileM, kTileN);
+
+  static_assert(kSmemBytes <= 232448, "exceeds 227 KiB of shared memory");
+};
+
+}  // namespace b200

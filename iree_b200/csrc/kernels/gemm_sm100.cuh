@@ -32,55 +32,10 @@
 #pragma once
 
 #include "common.cuh"
+#include "gemm_config.h"
 #include "iree_b200_tma_recipe.h"
 
 namespace b200 {
-
-template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_>
-struct GemmConfig {
-  static constexpr int kCtaGroup = kCtaGroup_;
-  static constexpr int kKind = kKind_;
-  static constexpr uint32_t kAbFmt = kAbFmt_;
-  static constexpr bool kBMajorK = kBMajorK_;
-  static constexpr int kStages = kStages_;
-
-  static constexpr int kElemSize = (kKind == KIND_I8) ? 1 : 2;
-  static constexpr int kBlockM = 128;                    // rows per CTA
-  static constexpr int kTileM = kBlockM * kCtaGroup;     // rows per cluster tile
-  static constexpr int kTileN = 256;                     // UMMA N
-  static constexpr int kBlockN = kTileN / kCtaGroup;     // B columns loaded per CTA
-  static constexpr int kBlockK = 128 / kElemSize;        // elements per 128-byte row
-  static constexpr int kUmmaK = 32 / kElemSize;
-  static constexpr int kKSteps = kBlockK / kUmmaK;       // 4
-
-  static constexpr int kABytes = kBlockM * 128;                 // 16 KiB
-  static constexpr int kBBytes = kBlockN * kBlockK * kElemSize; // 16 / 32 KiB
-  static constexpr int kStageBytes = kABytes + kBBytes;
-
-  // MN-major B: [kBlockK rows][128 B of N] blocks, one TMA box each.
-  static constexpr int kBBoxN = 128 / kElemSize;               // N elements per box
-  static constexpr int kBBoxBytes = kBlockK * 128;             // bytes per box
-  static constexpr int kBBoxes = kBBytes / kBBoxBytes;
-
-  static constexpr int kAccStages = 2;
-  static constexpr int kTmemCols = kAccStages * kTileN;  // 512
-  static constexpr int kEpiCols = 32;                    // columns per epilogue chunk
-  static constexpr int kEpiBytes = kBlockM * kEpiCols * 4;  // 16 KiB
-  static constexpr int kEpiBufs = 2;
-
-  static constexpr int kSmemTiles = kStages * kStageBytes + kEpiBufs * kEpiBytes;
-  static constexpr int kNumBarriers = 2 * kStages + 2 * kAccStages;
-  static constexpr int kSmemBytes = 1024 /*align slack*/ + kSmemTiles + kNumBarriers * 8 + 16;
-
-  static constexpr int kThreads = 256;
-  static constexpr int kGroupM = 8;  // raster group height in tiles
-
-  static constexpr uint32_t kIdesc =
-      make_idesc(kKind == KIND_I8 ? CFMT_S32 : CFMT_F32, kAbFmt, kAbFmt, MAJOR_K,
-                 kBMajorK ? MAJOR_K : MAJOR_MN, kTileM, kTileN);
-
-  static_assert(kSmemBytes <= 232448, "exceeds 227 KiB of shared memory");
-};
 
 struct TileCoord {
   int batch, m_blk, n_blk;
@@ -329,6 +284,10 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     }
     if (epi_leader) tma_store_wait<0>();
   }
+
+  // Warps 0 and 1 ran their loops on one elected lane; reconverge before the .aligned
+  // barrier / dealloc instructions below.
+  __syncwarp();
 
   // Teardown: nobody may free TMEM (or exit while the peer's MMA still reads our smem)
   // until every role of every CTA in the cluster is done.

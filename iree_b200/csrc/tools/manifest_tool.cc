@@ -1,0 +1,43 @@
+// manifest_tool.cc — prints the export table of the builtin executable as JSON.
+//
+// Plays the role of the hal.executable.export ops a compiler would carry: name, ordinal,
+// workgroup_size, workgroup_local_memory, #hal.pipeline.layout (constants, bindings with
+// their ReadOnly flag) — the inputs of CUDATarget.cpp:650-691. Built and run on the host
+// by iree_b200/build.py; the geometry comes from the same constexpr definitions the
+// kernels are compiled from.
+
+#include <cstdio>
+
+#include "../kernels/attention_config.h"
+#include "../kernels/gemm_config.h"
+
+using namespace b200;
+
+static bool first = true;
+
+static void emit(const char* name, const char* module, int threads, int smem, int constants,
+                 const char* binding_flags) {
+  printf("%s\n    {\"name\": \"%s\", \"module\": \"%s\", \"block_dims\": [%d, 1, 1], "
+         "\"shared_memory\": %d, \"constants\": %d, \"binding_flags\": [%s]}",
+         first ? "" : ",", name, module, threads, smem, constants, binding_flags);
+  first = false;
+}
+
+int main() {
+  printf("{\n  \"exports\": [");
+  // READ_ONLY = 1 (cuda_executable_def.fbs:23-26).
+#define X(NAME, CLUSTER, ...)                                                              \
+  emit(#NAME, "gemm_kernels", GemmConfig<__VA_ARGS__>::kThreads,                           \
+       GemmConfig<__VA_ARGS__>::kSmemBytes, 5, "1, 1, 0");
+#include "../kernels/gemm_exports.inc"
+#undef X
+  emit("iree_b200_matmul_generic_bf16_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
+  emit("iree_b200_matmul_generic_f16_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
+  emit("iree_b200_matmul_generic_i8_i32", "generic_kernels", 256, 0, 5, "1, 1, 0");
+#define X(NAME, THREADS, SMEM, CONSTANTS, BINDINGS) \
+  emit(#NAME, "attention_kernels", THREADS, SMEM, CONSTANTS, BINDINGS);
+#include "../kernels/attention_exports.inc"
+#undef X
+  printf("\n  ]\n}\n");
+  return 0;
+}
