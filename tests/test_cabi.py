@@ -1,0 +1,93 @@
+"""CPU-side checks of the drop-in boundary: the library loads without a GPU, exports
+every symbol the headers declare, treats executable blobs as untrusted, and refuses to
+compute without a device (there is no CPU fallback)."""
+
+import ctypes
+import os
+import re
+
+import pytest
+
+from iree_b200 import build, cda1, hal
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    names = set()
+    for header in ("iree_b200_hal.h", "iree_b200_ops.h"):
+        with open(os.path.join(ROOT, "include", header)) as f:
+            text = f.read()
+        text = re.sub(r"//[^\n]*", "", text)
+        for m in re.finditer(r"IREE_B200_API\s[^;{]*?\b(iree_b200_\w+)\s*\(", text, re.S):
+            names.add(m.group(1))
+    return sorted(names)
+
+
+def test_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(build.build())
+    declared = _declared_symbols()
+    assert len(declared) >= 55
+    missing = [n for n in declared if not hasattr(lib, n)]
+    assert not missing, missing
+    # ... and the Python mirror binds exactly that set.
+    assert sorted(hal.ALL_SYMBOLS) == declared
+
+
+def test_status_code_strings_match_reference_names():
+    lib = hal.lib()
+    assert lib.iree_b200_status_code_string(0) == b"OK"
+    assert lib.iree_b200_status_code_string(3) == b"INVALID_ARGUMENT"
+    assert lib.iree_b200_status_code_string(14) == b"UNAVAILABLE"
+
+
+def _have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.mark.skipif(_have_gpu(), reason="checks the no-GPU failure mode")
+def test_no_gpu_fails_loudly_no_cpu_fallback():
+    with pytest.raises(hal.Status) as e:
+        hal.Device(0)
+    assert e.value.name == "UNAVAILABLE"
+
+
+def test_builtin_executable_is_valid_cda1():
+    size = ctypes.c_size_t()
+    ptr = hal.lib().iree_b200_ops_builtin_executable_data(ctypes.byref(size))
+    blob = ctypes.string_at(ptr, size.value)
+    with open(build.cda1_path(), "rb") as f:
+        assert f.read() == blob
+    fmt, inferred = hal.infer_format(blob)
+    assert fmt == "PTXE" and inferred == len(blob)
+    exe = cda1.deserialize(blob)
+    names = [e.kernel_name for e in exe.exports]
+    assert "iree_b200_matmul_bf16_f32" in names and "iree_b200_matmul_generic_i8_i32" in names
+    for e in exe.exports:
+        assert list(e.block_dims) == [256, 1, 1]
+        assert e.block_shared_memory_size <= 227 * 1024
+        assert e.constant_count <= 64 and len(e.binding_flags) <= 16
+    assert all(m[:4] == b"\x7fELF" for m in exe.modules)  # cubins, not PTX (no JIT at load)
+
+
+def test_cda1_roundtrip_and_untrusted_input():
+    exe = cda1.ExecutableDef(
+        exports=[cda1.ExportDef("k0", [128, 1, 1], 1024, 2, [1, 0], 0),
+                 cda1.ExportDef("k1", [32, 2, 1], 0, 0, [0], 1)],
+        modules=[b"// ptx a\n", b"\x7fELFxxxx"])
+    blob = cda1.serialize(exe)
+    back = cda1.deserialize(blob)
+    assert [e.kernel_name for e in back.exports] == ["k0", "k1"]
+    assert back.exports[0].block_shared_memory_size == 1024
+    assert list(back.exports[1].block_dims) == [32, 2, 1]
+    assert back.modules[1] == b"\x7fELFxxxx"
+    assert hal.infer_format(blob) == ("PTXE", len(blob))
+    # Corrupt magic / truncated / garbage: status, never a crash.
+    for bad in (b"XXXX" + blob[4:], blob[:40], b"", os.urandom(256)):
+        with pytest.raises(hal.Status) as e:
+            hal.infer_format(bad)
+        assert e.value.code != 0

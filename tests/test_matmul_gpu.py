@@ -1,0 +1,163 @@
+"""Parity of the CUDA dispatches with the oracle, through the C-ABI (B200 only).
+
+Shape sets are the reference's (tests/e2e/matmul/generate_e2e_matmul_tests.py:33-101,
+generate_e2e_batch_matmul_tests.py:29-31); inputs come from the reference generator
+(seeds lhs=1, rhs=2, acc=3), for which f32 results are exact, so — as in the reference
+runner (--require_exact_results, test_utils.c:287-290) — the bar is bit equality for
+every element type. Random-input cases (PCG, N(0,1) / full-range i8): i8 stays bit-exact;
+bf16 within 1e-2 and f16 within 1e-3 relative (BASELINE.json north_star).
+"""
+
+import numpy as np
+import pytest
+
+import oracle
+from iree_b200 import hal as H
+
+pytestmark = pytest.mark.gpu
+
+SMALL = [(1, 1, 1, True), (1, 1, 1, False), (2, 2, 2, True), (4, 4, 4, True), (8, 8, 8, True),
+         (9, 9, 9, True), (6, 13, 3, True), (15, 37, 7, False), (81, 19, 41, True),
+         (1, 10, 10, True), (1, 10, 10, False), (10, 1, 10, True), (10, 10, 1, True),
+         (10, 10, 1, False)]
+LARGE = [(457, 330, 512, False), (438, 331, 513, False), (540, 332, 516, False),
+         (1000, 4, 512, False), (4, 1000, 512, False), (512, 1000, 4, False),
+         (513, 128, 55, False), (7, 160, 31, False), (512, 330, 33, False),
+         (1, 1000, 1000, True), (1000, 1000, 1, True), (1000, 1000, 1, False)]
+EASY_LARGE_STATIC = [(512, 128, 512, True), (512, 128, 512, False)]
+# TMA-eligible shapes exercising ragged M/N/K tiles, multi-tile rasters, both families.
+TILED = [(128, 64, 256, False), (256, 64, 256, True), (130, 72, 264, False),
+         (1000, 520, 264, True), (384, 1024, 768, False), (2048, 256, 1280, False),
+         (129, 8, 4, False), (8, 16, 2052, True)]
+
+
+def _run(ops, t, batch, M, N, K, flags=0, accumulate=False, nt=False, seeds=(1, 2, 3),
+         lhs=None, rhs=None):
+    if lhs is None:
+        lhs = oracle.generate_random_matrix(t, (batch, M, K), seeds[0])
+        rhs = oracle.generate_random_matrix(t, (batch, N, K) if nt else (batch, K, N), seeds[1])
+    out_t = "i32" if t == "i8" else "f32"
+    acc = oracle.generate_random_matrix(out_t, (batch, M, N), seeds[2]) if accumulate else None
+    out = acc.copy() if accumulate else np.full((batch, M, N), 77, dtype=acc_dtype(t))
+    f = flags | (H.MATMUL_ACCUMULATE if accumulate else 0) | (H.MATMUL_TRANSPOSE_RHS if nt else 0)
+    ops.matmul_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data, f)
+    want = oracle.matmul(t, lhs, rhs, acc=acc, transpose_rhs=nt)
+    return out, want
+
+
+def acc_dtype(t):
+    return np.int32 if t == "i8" else np.float32
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("shape", SMALL + LARGE + EASY_LARGE_STATIC,
+                         ids=lambda s: "%dx%dx%d%s" % (s[0], s[1], s[2], "+acc" if s[3] else ""))
+def test_reference_shape_sets(ops, t, shape):
+    M, K, N, accumulate = shape
+    out, want = _run(ops, t, 1, M, N, K, accumulate=accumulate)
+    assert np.array_equal(out[0], want[0])
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("family", ["1cta", "2cta", "generic"])
+@pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
+@pytest.mark.parametrize("shape", TILED, ids=lambda s: "%dx%dx%d%s" % (s[0], s[1], s[2], "+acc" if s[3] else ""))
+def test_every_kernel_family(ops, t, family, nt, shape):
+    M, K, N, accumulate = shape
+    es = 1 if t == "i8" else 2
+    if family != "generic" and ((K * es) % 16 or (N * 4) % 16 or (not nt and (N * es) % 16)):
+        pytest.skip("shape does not satisfy the TMA guards (goes to the generic kernel)")
+    flag = {"1cta": H.MATMUL_FORCE_1CTA, "2cta": H.MATMUL_FORCE_2CTA,
+            "generic": H.MATMUL_FORCE_GENERIC}[family]
+    out, want = _run(ops, t, 1, M, N, K, flags=flag, accumulate=accumulate, nt=nt)
+    assert np.array_equal(out, want)
+
+
+@pytest.mark.parametrize("t", ["i8", "bf16"])
+@pytest.mark.parametrize("bshape", [(32, 128, 128, 128), (32, 256, 64, 256), (32, 96, 96, 96),
+                                    (3, 300, 136, 520)], ids=str)
+def test_batch_matmul_reference_shapes(ops, t, bshape):
+    batch, M, K, N = bshape
+    out, want = _run(ops, t, batch, M, N, K)
+    assert np.array_equal(out, want)
+
+
+def test_selection_guards(ops):
+    """The matcher guards: unaligned pitches / pointers go to the generic export; big
+    aligned shapes to the 2-CTA family with a persistent, cluster-divisible grid."""
+    exe = ops.executable
+    name = lambda sel: exe.export_info(sel["export_ordinal"])["kernel_name"]
+    s = ops.select_matmul("bf16", 1, 8192, 8192, 8192)
+    assert name(s) == "iree_b200_matmul_bf16_f32"
+    assert s["workgroup_count"][0] % 2 == 0 and s["workgroup_count"][0] <= 148
+    assert name(ops.select_matmul("bf16", 1, 128, 512, 512)).endswith("_1cta")
+    assert "generic" in name(ops.select_matmul("bf16", 1, 457, 330, 512))   # N pitch 660 B
+    assert "generic" in name(ops.select_matmul("bf16", 1, 512, 512, 512, alignment=2))
+    assert name(ops.select_matmul("i8", 1, 512, 512, 512, flags=H.MATMUL_TRANSPOSE_RHS)) \
+        .startswith("iree_b200_matmul_nt_i8")
+    assert ops.select_matmul("bf16", 1, 0, 16, 16)["export_ordinal"] == -1
+    with pytest.raises(H.Status):
+        ops.select_matmul("bf16", 1, 457, 330, 512, flags=H.MATMUL_FORCE_2CTA)
+    with pytest.raises(H.Status):
+        ops.select_matmul(7, 1, 8, 8, 8)
+
+
+def test_empty_and_zero_k(ops):
+    out = np.full((1, 4, 4), 5, np.float32)
+    a = np.zeros((1,), np.uint16)
+    ops.matmul_host("bf16", 1, 4, 4, 0, a.ctypes.data, a.ctypes.data, out.ctypes.data)
+    assert (out == 0).all()                      # linalg.fill 0 seeds the accumulator
+    out[:] = 5
+    ops.matmul_host("bf16", 1, 4, 4, 0, a.ctypes.data, a.ctypes.data, out.ctypes.data,
+                    H.MATMUL_ACCUMULATE)
+    assert (out == 5).all()
+    ops.matmul_host("bf16", 1, 0, 4, 8, a.ctypes.data, a.ctypes.data, out.ctypes.data)
+
+
+def _pcg(seed):
+    return np.random.Generator(np.random.PCG64(seed))
+
+
+def test_i8_full_range_bit_exact(ops):
+    g = _pcg(0xB200)
+    M, N, K = 512, 768, 2048
+    lhs = g.integers(-128, 128, (1, M, K), dtype=np.int8)
+    rhs = g.integers(-128, 128, (1, K, N), dtype=np.int8)
+    for flag in (H.MATMUL_FORCE_1CTA, H.MATMUL_FORCE_2CTA):
+        out, want = _run(ops, "i8", 1, M, N, K, flags=flag, lhs=lhs, rhs=rhs)
+        assert np.array_equal(out, want)
+
+
+@pytest.mark.parametrize("t,rtol", [("bf16", 1e-2), ("f16", 1e-3)])
+def test_random_normal_inputs_within_tolerance(ops, t, rtol):
+    g = _pcg(0xB200 + 1)
+    M, N, K = 384, 512, 4096
+    lhs = oracle.from_f32(t, np.clip(g.standard_normal((1, M, K)), -4, 4).astype(np.float32))
+    rhs = oracle.from_f32(t, np.clip(g.standard_normal((1, K, N)), -4, 4).astype(np.float32))
+    out, want = _run(ops, t, 1, M, N, K, lhs=lhs, rhs=rhs)
+    # Tolerance from BASELINE.json north_star, relative to the result's scale (sqrt(K)).
+    scale = np.abs(want).max()
+    assert np.abs(out - want).max() <= rtol * scale
+    # In practice both sides accumulate exact products in f32: the difference is
+    # summation order only.
+    assert np.abs(out - want).max() <= 1e-5 * scale
+
+
+@pytest.mark.parametrize("t", ["i8", "bf16"])
+def test_full_size_sampled_like_the_reference(ops, t):
+    """BASELINE config sizes: compare the reference checker's sampled index set
+    (iree_test_utils_calculate_check_every, test_utils.c:41-68) at 4096^3."""
+    M = N = K = 4096
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    out = np.empty((M, N), acc_dtype(t))
+    ops.matmul_host(t, 1, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data)
+    idx, every = oracle.sampled_indices(M, N)
+    for i in idx[:: max(1, len(idx) // 2000)]:
+        m, n = divmod(int(i), N)
+        assert out[m, n] == oracle.matmul_element(t, lhs, rhs, m, n)
+    # Size-independent property: row/column checksums (exact in f64 for these inputs).
+    a = lhs.astype(np.float64) if t == "i8" else oracle.to_f32(t, lhs).astype(np.float64)
+    b = rhs.astype(np.float64) if t == "i8" else oracle.to_f32(t, rhs).astype(np.float64)
+    assert np.array_equal(out.astype(np.float64).sum(axis=0), a.sum(axis=0) @ b)
+    assert np.array_equal(out.astype(np.float64).sum(axis=1), a @ b.sum(axis=1))

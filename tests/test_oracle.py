@@ -1,0 +1,120 @@
+"""The CPU oracle against the reference's own fixtures (no GPU).
+
+  * input generator KATs: iree_test_utils_pseudorandom_uint32 (test_utils.c:359-366)
+  * matmul: the reference loops (iree-e2e-matmul-test.cc:28-121) vs exact numpy products
+  * attention: the 13 golden cases extracted from tests/e2e/linalg_ext_ops/attention*.mlir
+"""
+
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "attention_golden.json")
+
+
+def _minstd(state):
+    # uint32 arithmetic: the product wraps mod 2^32 before the modulus (test_utils.c:359-362).
+    return ((state * 48271) & 0xFFFFFFFF) % 2147483647
+
+
+@pytest.mark.parametrize("t,lo,span", [("i8", -2, 5), ("bf16", -2, 5), ("f16", -4, 9)])
+def test_generator_matches_reference_recurrence(t, lo, span):
+    n, seed = 257, 3
+    got = oracle.generate_random_matrix(t, (n,), seed)
+    state, want = seed, []
+    for _ in range(n):
+        state = _minstd(state)
+        want.append(state % span + lo)
+    vals = got.astype(np.float32) if t == "i8" else oracle.to_f32(t, got)
+    assert vals.tolist() == [float(w) for w in want]
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (9, 7, 5), (457, 330, 512), (64, 1, 1000)])
+@pytest.mark.parametrize("nt", [False, True])
+def test_matmul_oracle_exact_on_reference_inputs(t, shape, nt):
+    M, N, K = shape
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (N, K) if nt else (K, N), 2)
+    acc = oracle.generate_random_matrix("i32" if t == "i8" else "f32", (M, N), 3)
+    a = lhs.astype(np.float64) if t == "i8" else oracle.to_f32(t, lhs).astype(np.float64)
+    b = rhs.astype(np.float64) if t == "i8" else oracle.to_f32(t, rhs).astype(np.float64)
+    b = b.T if nt else b
+    want = a @ b
+    got = oracle.matmul(t, lhs, rhs, transpose_rhs=nt)
+    assert np.array_equal(got.astype(np.float64), want)
+    got_acc = oracle.matmul(t, lhs, rhs, acc=acc, transpose_rhs=nt)
+    assert np.array_equal(got_acc.astype(np.float64), want + acc.astype(np.float64))
+    m, n = M // 2, N // 2
+    assert oracle.matmul_element(t, lhs, rhs, m, n, transpose_rhs=nt) == got[m, n]
+
+
+def test_batch_matmul_is_per_batch_matmul():
+    lhs = oracle.generate_random_matrix("bf16", (3, 17, 32), 1)
+    rhs = oracle.generate_random_matrix("bf16", (3, 32, 24), 2)
+    got = oracle.matmul("bf16", lhs, rhs)
+    for b in range(3):
+        assert np.array_equal(got[b], oracle.matmul("bf16", lhs[b], rhs[b]))
+
+
+def test_i8_extremes_wrap_free():
+    lhs = np.full((4, 8192), -128, dtype=np.int8)
+    rhs = np.full((8192, 4), -128, dtype=np.int8)
+    assert (oracle.matmul("i8", lhs, rhs) == 128 * 128 * 8192).all()
+
+
+def test_float_conversions_round_to_nearest_even():
+    x = np.array([1.0, 1.00390625, 1.01171875, -2.5, 3.14159, 65504.0, 1e-8], dtype=np.float32)
+    import torch
+    tb = torch.from_numpy(x).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
+    th = torch.from_numpy(x).to(torch.float16).view(torch.int16).numpy().view(np.uint16)
+    assert np.array_equal(oracle.f32_to_bf16_bits(x), tb)
+    assert np.array_equal(oracle.f32_to_f16_bits(x), th)
+    for v, b, h in zip(x, tb, th):
+        assert oracle.lib().oracle_f32_to_bf16(float(v)) == b
+        assert oracle.lib().oracle_f32_to_f16(float(v)) == h
+
+
+def test_check_every_sampling_rule():
+    # test_utils.c:56-68: smallest stride >= tot/max that does not divide the row length.
+    every = oracle.calculate_check_every(8192 * 8192, 8192)
+    assert every >= 8192 * 8192 // 10000 and 8192 % every != 0
+    assert oracle.calculate_check_every(100, 10) == 1
+
+
+def _tensor(d):
+    a = np.array(d["data"], dtype=np.float64)
+    shape = d["shape"]
+    if a.size == 1 and int(np.prod(shape)) != 1:
+        a = np.full(shape, a.reshape(-1)[0])
+    return a.reshape(shape)
+
+
+def _golden_cases():
+    with open(GOLDEN) as f:
+        return json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("case", _golden_cases(), ids=lambda c: c["source"] + ":" + c["name"])
+@pytest.mark.parametrize("form", ["online", "online_tile2", "oneshot"])
+def test_attention_golden(case, form):
+    t = case["query"]["type"]
+    q, k, v = (_tensor(case[x]).astype(np.float32) for x in ("query", "key", "value"))
+    q, k, v = (oracle.from_f32(t, x) for x in (q, k, v))
+    mask = None
+    if "mask" in case:
+        m = _tensor(case["mask"])
+        mask = m.astype(bool) if case["mask"]["type"] == "i1" else m.astype(np.float32)
+        mask = np.broadcast_to(mask, (q.shape[0], q.shape[1], k.shape[1])).copy()
+    kw = dict(mask=mask, region=case["region"]["kind"], region_param=case["region"]["param"])
+    if form == "oneshot":
+        got = oracle.attention(t, q, k, v, case["scale"], oneshot=True, **kw)
+    else:
+        got = oracle.attention(t, q, k, v, case["scale"], k2_tile=2 if form == "online_tile2" else 0,
+                               **kw)
+    want = _tensor(case["expected"])
+    np.testing.assert_allclose(oracle.to_f32(t, got), want, atol=case["atol"], rtol=0)
