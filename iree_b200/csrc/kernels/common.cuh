@@ -119,9 +119,12 @@ B200_DEVICE void mbar_arrive(uint32_t bar) {
 }
 
 // Arrive on a barrier given by a shared::cluster address (possibly in a peer CTA).
+// Default semantics (.release.cta): an explicit .release.cluster makes ptxas emit
+// MEMBAR.ALL.GPU + ERRBAR in front of every arrive, which costs microseconds inside a
+// pipeline loop. The data these arrives order (TMEM reads, TMA-written smem) is ordered
+// by tcgen05 fences / the async proxy, not by generic-proxy release semantics.
 B200_DEVICE void mbar_arrive_cluster(uint32_t cluster_bar) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar)
-               : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
 }
 
 B200_DEVICE bool mbar_try_wait(uint32_t bar, uint32_t parity) {

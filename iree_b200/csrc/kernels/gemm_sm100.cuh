@@ -92,6 +92,11 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
   const uint32_t tiles_n = (N + Cfg::kTileN - 1) / Cfg::kTileN;
   const uint32_t total_tiles = tiles_m * tiles_n * (uint32_t)batch;
   const uint32_t num_kb = (K + Cfg::kBlockK - 1) / Cfg::kBlockK;
+  // Diagnostic bits (tools/gemm_diag.py; never set by the ops layer): results are
+  // garbage, the pipeline structure is unchanged.
+  const bool diag_no_store = (flags & 0x10) != 0;  // epilogue drains TMEM but stores nothing
+  const bool diag_no_load = (flags & 0x20) != 0;   // no TMA loads; MMA does not wait for data
+  const bool diag_no_mma = (flags & 0x40) != 0;    // MMA warp only recycles the ring
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(tm_a);
@@ -100,7 +105,10 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < Cfg::kStages; ++s) {
-      mbar_init(bar_full + 8 * s, G);  // leader's expect_tx arrive (+ peer's arrive)
+      // One arrival: the pair leader's expect_tx covering BOTH CTAs' loads (the peer's
+      // TMA complete_tx lands on the leader's barrier; no peer arrive is needed since the
+      // peer only refills a slot after the multicast commit freed it in both CTAs).
+      mbar_init(bar_full + 8 * s, 1);
       mbar_init(bar_empty + 8 * s, 1); // one tcgen05.commit
     }
     for (int a = 0; a < Cfg::kAccStages; ++a) {
@@ -125,7 +133,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     //===------------------------------------------------------------------===//
     // TMA producer
     //===------------------------------------------------------------------===//
-    if (elect_one()) {
+    if (!diag_no_load && elect_one()) {
       // All loads of the pair complete on the LEADER's full barrier.
       const uint32_t full0 = (G == 2) ? map_to_cta(bar_full, 0) : bar_full;
       uint32_t stage = 0, phase = 0;
@@ -150,9 +158,6 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
                              n0 + j * Cfg::kBBoxN, k0, tc.batch);
             }
           }
-          if (G == 2 && !is_leader) {
-            mbar_arrive_cluster(full);
-          }
           if (++stage == Cfg::kStages) {
             stage = 0;
             phase ^= 1;
@@ -172,7 +177,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + acc * Cfg::kTileN;
         for (uint32_t kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(bar_full + 8 * stage, phase);
+          if (!diag_no_load) mbar_wait(bar_full + 8 * stage, phase);
           tcgen05_fence_after();
           const uint32_t a_addr = smem_a + stage * Cfg::kABytes;
           const uint32_t b_addr = smem_b + stage * Cfg::kBBytes;
@@ -188,7 +193,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
               // N blocks one TMA box apart; one UMMA consumes kUmmaK rows.
               db = make_smem_desc_sw128(b_addr + k * (Cfg::kUmmaK * 128), Cfg::kBBoxBytes, 1024);
             }
-            umma_ss<G, Cfg::kKind>(tmem_d, da, db, Cfg::kIdesc, (kb | k) != 0);
+            if (!diag_no_mma) umma_ss<G, Cfg::kKind>(tmem_d, da, db, Cfg::kIdesc, (kb | k) != 0);
           }
           umma_commit<G>(bar_empty + 8 * stage);  // smem slot free once these MMAs retire
           if (++stage == Cfg::kStages) {
@@ -270,7 +275,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         }
         fence_proxy_async_smem();
         named_barrier_sync(1, 128);
-        if (epi_leader) {
+        if (epi_leader && !diag_no_store) {
           tma_store_3d(tm_c, smem_epi + buf * Cfg::kEpiBytes, n0 + c * Cfg::kEpiCols, m0,
                        tc.batch);
           tma_store_commit();
