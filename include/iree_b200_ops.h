@@ -34,6 +34,7 @@ enum {
   IREE_B200_ELEMENT_TYPE_I8 = 0,
   IREE_B200_ELEMENT_TYPE_F16 = 1,
   IREE_B200_ELEMENT_TYPE_BF16 = 2,
+  IREE_B200_ELEMENT_TYPE_F32 = 3,  // attention only (generic kernel; the reference's goldens)
 };
 
 enum {
@@ -95,6 +96,64 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops,
                                                            int64_t M, int64_t N, int64_t K,
                                                            uint32_t flags, const void* lhs,
                                                            const void* rhs, void* out);
+
+//===----------------------------------------------------------------------===//
+// iree_linalg_ext.attention
+//===----------------------------------------------------------------------===//
+// Q [B,M,K1], K [B,K2,K1], V [B,K2,N], optional mask [B,M,K2], O [B,M,N]; all operands and
+// the result share |element_type| (f16, bf16, or f32 on the generic kernel), the scale is a scalar of the same type
+// (tests/e2e/attention/generate_e2e_attention_tests.py:271-300). The region is identity.
+
+enum {
+  IREE_B200_ATTENTION_MASK_NONE = 0,
+  IREE_B200_ATTENTION_MASK_BOOL = 1,  // i1 stored one byte per element
+  IREE_B200_ATTENTION_MASK_F32 = 2,   // additive, natural-log domain (scaled by log2e inside)
+};
+
+enum {
+  // Diagnostics: force a kernel family regardless of the shape heuristics.
+  IREE_B200_ATTENTION_FLAG_FORCE_GENERIC = 1u << 8,
+  IREE_B200_ATTENTION_FLAG_FORCE_PREFILL = 1u << 9,
+  IREE_B200_ATTENTION_FLAG_FORCE_DECODE = 1u << 10,
+};
+
+#define IREE_B200_ATTENTION_MAX_DISPATCHES 2
+
+typedef struct iree_b200_attention_dispatch_t {
+  int32_t export_ordinal;
+  uint32_t workgroup_count[3];
+  uint32_t constant_count;
+  uint32_t constants[8];
+} iree_b200_attention_dispatch_t;
+
+typedef struct iree_b200_attention_selection_t {
+  int32_t dispatch_count;  // 0 (empty result), 1, or 2 (split + merge)
+  iree_b200_attention_dispatch_t dispatches[IREE_B200_ATTENTION_MAX_DISPATCHES];
+  uint64_t workspace_bytes;  // transient f32 buffer the two-dispatch form needs (else 0)
+} iree_b200_attention_selection_t;
+
+// Matcher guards + count regions. tcgen05 prefill kernel: K1 == N == 128, no mask, M > 16,
+// 16-byte aligned bindings. Split-KV decode kernels: K1 == N == 128, no mask, M <= 16.
+// Everything else within K1, N <= 512 goes to the generic kernel; beyond that the status is
+// UNIMPLEMENTED (the compiler plugin leaves such ops to IREE's own codegen).
+IREE_B200_API iree_b200_status_t iree_b200_ops_select_attention(
+    const iree_b200_ops_t* ops, int32_t element_type, int64_t B, int64_t M, int64_t K1,
+    int64_t K2, int64_t N, float scale, int32_t mask_kind, uint32_t flags, uint32_t alignment,
+    iree_b200_attention_selection_t* out_selection);
+
+// Records the dispatch(es). |mask| is ignored for MASK_NONE; |workspace| must hold
+// selection.workspace_bytes (ignored when 0).
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_attention(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t B,
+    int64_t M, int64_t K1, int64_t K2, int64_t N, float scale, int32_t mask_kind, uint32_t flags,
+    iree_b200_buffer_ref_t q, iree_b200_buffer_ref_t k, iree_b200_buffer_ref_t v,
+    iree_b200_buffer_ref_t mask, iree_b200_buffer_ref_t workspace, iree_b200_buffer_ref_t out);
+
+// Host-buffer form (H2D of Q/K/V/mask, dispatch, D2H of O), synchronous.
+IREE_B200_API iree_b200_status_t iree_b200_ops_attention_host(
+    iree_b200_ops_t* ops, int32_t element_type, int64_t B, int64_t M, int64_t K1, int64_t K2,
+    int64_t N, float scale, int32_t mask_kind, uint32_t flags, const void* q, const void* k,
+    const void* v, const void* mask, void* out);
 
 #ifdef __cplusplus
 }  // extern "C"

@@ -1,0 +1,366 @@
+// attention_kernels.cu — extern "C" entry points for iree_linalg_ext.attention.
+//
+// ABI (reference: samples/custom_dispatch/cuda/kernels/kernels.cu:7-34): one pointer per
+// binding in layout order, then one 32-bit value per push constant; TMA-fed kernels take
+// their CUtensorMaps after the ABI parameters (iree_b200_tma_recipe.h).
+//
+//   iree_b200_attention_prefill_{f16,bf16}   tcgen05, K1 == N == 128, no mask
+//     bindings  Q [B,M,128] ro, K [B,K2,128] ro, V [B,K2,128] ro, O [B,M,128]
+//     constants B, M, K2, scale (f32 bits), flags      grid [ceil(M/256), B, 1]  block 384
+//   iree_b200_attention_decode_split_{f16,bf16}   HBM-streaming split-KV, K1 == N == 128
+//     bindings  Q ro, K ro, V ro, workspace [B,M,splits,130] f32
+//     constants B, M, K2, scale, splits                grid [splits, M, B]       block 256
+//   iree_b200_attention_decode_merge_{f16,bf16}
+//     bindings  workspace ro, O [B,M,128]
+//     constants B, M, splits                           grid [M, B, 1]            block 128
+//   iree_b200_attention_generic_{f16,bf16,f32}   any shape within the guards, optional mask
+//     bindings  Q ro, K ro, V ro, mask ro (any valid pointer when unused), O
+//     constants B, M, K1, K2, N, scale, mask_kind (0 none, 1 i1-as-u8, 2 f32 additive)
+//                                                      grid [M, B, 1]            block 128
+// Semantics for all of them: the oracle's (oracle/oracle.c), i.e. the llvm-cpu lowering.
+
+#include "attention_sm100.cuh"
+
+using namespace b200;
+
+//===----------------------------------------------------------------------===//
+// Prefill (tcgen05)
+//===----------------------------------------------------------------------===//
+
+using PrefillCfg = AttnPrefillConfig<128>;
+
+#define B200_PREFILL(NAME, BF16)                                                               \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                             \
+      make_attention_prefill_recipe<PrefillCfg, BF16>();                                       \
+  extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \
+      NAME(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, \
+           void* __restrict__ out, int B, int M, int K2, int scale_bits, int flags,            \
+           const __grid_constant__ TensorMap tm_q, const __grid_constant__ TensorMap tm_k,     \
+           const __grid_constant__ TensorMap tm_v) {                                           \
+    (void)q;                                                                                   \
+    (void)k;                                                                                   \
+    (void)v;                                                                                   \
+    attention_prefill_body<PrefillCfg, BF16>(out, B, M, K2, scale_bits, flags, &tm_q, &tm_k,   \
+                                             &tm_v);                                           \
+  }
+
+B200_PREFILL(iree_b200_attention_prefill_f16, false)
+B200_PREFILL(iree_b200_attention_prefill_bf16, true)
+
+//===----------------------------------------------------------------------===//
+// Decode: split-KV streaming kernel + merge. HBM bound: every K and V byte is read once.
+//===----------------------------------------------------------------------===//
+
+namespace {
+
+__device__ __forceinline__ uint4 ld_stream_16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+template <bool kBf16>
+__device__ __forceinline__ void unpack8(const uint4& v, float (&f)[8]) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    f[2 * e] = elem_to_f32<kBf16>((uint16_t)(w[e] & 0xffffu));
+    f[2 * e + 1] = elem_to_f32<kBf16>((uint16_t)(w[e] >> 16));
+  }
+}
+
+template <bool kBf16>
+__device__ __forceinline__ void attention_decode_split_body(const uint16_t* __restrict__ q,
+                                                            const uint16_t* __restrict__ k,
+                                                            const uint16_t* __restrict__ v,
+                                                            float* __restrict__ workspace, int B,
+                                                            int M, int K2, int scale_bits,
+                                                            int splits) {
+  using Cfg = AttnDecodeConfig;
+  constexpr int D = Cfg::kHeadDim;
+  constexpr int R = Cfg::kChunkRows;
+  __shared__ float s_s[R];            // scores, then P (already truncated to the V type)
+  __shared__ float red[8];
+  __shared__ float acc_s[16][D + 4];  // per row-group partial sums
+
+  const int split = blockIdx.x, m = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int sub = tid & 15;   // 16-byte column slab of the 256-byte row
+  const int grp = tid >> 4;   // 16 row groups
+  const int rows_per_split = (K2 + splits - 1) / splits;
+  const int row0 = split * rows_per_split;
+  const int row_end = min(K2, row0 + rows_per_split);
+  (void)B;
+
+  // Q' slab of this thread: round_T(s' * q) (AggregatedOpInterfaceImpl.cpp:355-358).
+  float qf[8];
+  {
+    const float mult = attention_q_multiplier<kBf16>(__int_as_float(scale_bits));
+    const uint4 qv = *reinterpret_cast<const uint4*>(q + ((size_t)b * M + m) * D + sub * 8);
+    unpack8<kBf16>(qv, qf);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) qf[e] = elem_to_f32<kBf16>(f32_to_elem<kBf16>(qf[e] * mult));
+  }
+
+  float run_max = -FLT_MAX, run_sum = 0.f;
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+
+  for (int c0 = row0; c0 < row_end; c0 += R) {
+    const int rows = min(R, row_end - c0);
+    const uint16_t* kbase = k + ((size_t)b * K2 + c0) * D + sub * 8;
+    const uint16_t* vbase = v + ((size_t)b * K2 + c0) * D + sub * 8;
+    // ---- scores: 16 rows per pass, 16 lanes per row ----
+#pragma unroll 4
+    for (int r = grp; r < R; r += 16) {
+      float dot = 0.f;
+      if (r < rows) {
+        float kf[8];
+        unpack8<kBf16>(ld_stream_16(kbase + (size_t)r * D), kf);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dot = fmaf(qf[e], kf[e], dot);
+      }
+      dot += __shfl_xor_sync(0xffffffffu, dot, 8);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 4);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 2);
+      dot += __shfl_xor_sync(0xffffffffu, dot, 1);
+      if (sub == 0) s_s[r] = r < rows ? dot : -INFINITY;
+    }
+    __syncthreads();
+    // ---- block max ----
+    float mx = s_s[tid];  // R == blockDim.x
+    float wmx = mx;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmx = fmaxf(wmx, __shfl_xor_sync(0xffffffffu, wmx, o));
+    if (lane == 0) red[warp] = wmx;
+    __syncthreads();
+    float new_max = run_max;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) new_max = fmaxf(new_max, red[w]);
+    const float norm = exp2f(run_max - new_max);
+    const float p = exp2f(mx - new_max);
+    float psum = p;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) psum += __shfl_xor_sync(0xffffffffu, psum, o);
+    __syncthreads();  // everyone has read red[] and s_s[tid]
+    s_s[tid] = elem_to_f32<kBf16>(f32_to_elem<kBf16>(p));
+    if (lane == 0) red[warp] = psum;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) tot += red[w];
+    run_sum = norm * run_sum + tot;
+    run_max = new_max;
+    // ---- acc = norm*acc + P.V over this thread's row group / column slab ----
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] *= norm;
+#pragma unroll 4
+    for (int r = grp; r < R; r += 16) {
+      if (r < rows) {
+        float vf[8];
+        unpack8<kBf16>(ld_stream_16(vbase + (size_t)r * D), vf);
+        const float pr = s_s[r];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] = fmaf(pr, vf[e], acc[e]);
+      }
+    }
+    __syncthreads();  // s_s / red reused by the next chunk
+  }
+
+  // ---- reduce the 16 row groups and write the partial record ----
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc_s[grp][sub * 8 + e] = acc[e];
+  __syncthreads();
+  float* rec = workspace + (((size_t)b * M + m) * splits + split) * Cfg::kRecordFloats;
+  if (tid < D) {
+    float a = 0.f;
+#pragma unroll
+    for (int g = 0; g < 16; ++g) a += acc_s[g][tid];
+    rec[tid] = a;
+  }
+  if (tid == 0) {
+    rec[D] = run_max;
+    rec[D + 1] = run_sum;
+  }
+}
+
+template <bool kBf16>
+__device__ __forceinline__ void attention_decode_merge_body(const float* __restrict__ workspace,
+                                                            uint16_t* __restrict__ out, int B,
+                                                            int M, int splits) {
+  using Cfg = AttnDecodeConfig;
+  constexpr int D = Cfg::kHeadDim;
+  const int m = blockIdx.x, b = blockIdx.y, n = threadIdx.x;
+  (void)B;
+  const float* rec = workspace + ((size_t)b * M + m) * splits * Cfg::kRecordFloats;
+  float gmax = -FLT_MAX;
+  for (int s = 0; s < splits; ++s) gmax = fmaxf(gmax, rec[s * Cfg::kRecordFloats + D]);
+  float sum = 0.f, acc = 0.f;
+  for (int s = 0; s < splits; ++s) {
+    const float w = exp2f(rec[s * Cfg::kRecordFloats + D] - gmax);
+    sum = fmaf(w, rec[s * Cfg::kRecordFloats + D + 1], sum);
+    acc = fmaf(w, rec[s * Cfg::kRecordFloats + n], acc);
+  }
+  const float rcp = 1.0f / sum;  // TileAttention.cpp:141-146
+  out[((size_t)b * M + m) * D + n] = f32_to_elem<kBf16>(rcp * acc);
+}
+
+}  // namespace
+
+#define B200_DECODE(SUFFIX, BF16)                                                              \
+  extern "C" __global__ void __launch_bounds__(AttnDecodeConfig::kThreads)                     \
+      iree_b200_attention_decode_split_##SUFFIX(                                               \
+          const uint16_t* __restrict__ q, const uint16_t* __restrict__ k,                      \
+          const uint16_t* __restrict__ v, float* __restrict__ workspace, int B, int M, int K2, \
+          int scale_bits, int splits) {                                                        \
+    attention_decode_split_body<BF16>(q, k, v, workspace, B, M, K2, scale_bits, splits);       \
+  }                                                                                            \
+  extern "C" __global__ void __launch_bounds__(128) iree_b200_attention_decode_merge_##SUFFIX( \
+      const float* __restrict__ workspace, uint16_t* __restrict__ out, int B, int M,           \
+      int splits) {                                                                            \
+    attention_decode_merge_body<BF16>(workspace, out, B, M, splits);                           \
+  }
+
+B200_DECODE(f16, false)
+B200_DECODE(bf16, true)
+
+//===----------------------------------------------------------------------===//
+// Generic SIMT kernel: any B/M/K1/K2/N within the guards, optional mask operand, f16 /
+// bf16 / f32 elements. Correctness path (masks, odd head dims, unaligned pointers, the
+// reference's f32 golden vectors): one CTA per (b, m) row, online softmax over K2 tiles of
+// 128 exactly as OnlineAttentionOp::decomposeOperation.
+//===----------------------------------------------------------------------===//
+
+namespace {
+
+enum : int { kElemF16 = 0, kElemBF16 = 1, kElemF32 = 2 };
+
+template <int kType>
+__device__ __forceinline__ float ld_elem(const void* p, size_t i) {
+  if constexpr (kType == kElemF32) {
+    return reinterpret_cast<const float*>(p)[i];
+  } else {
+    return elem_to_f32<kType == kElemBF16>(reinterpret_cast<const uint16_t*>(p)[i]);
+  }
+}
+
+template <int kType>
+__device__ __forceinline__ float round_elem(float v) {
+  if constexpr (kType == kElemF32) {
+    return v;
+  } else {
+    return elem_to_f32<kType == kElemBF16>(f32_to_elem<kType == kElemBF16>(v));
+  }
+}
+
+template <int kType>
+__device__ __forceinline__ void st_elem(void* p, size_t i, float v) {
+  if constexpr (kType == kElemF32) {
+    reinterpret_cast<float*>(p)[i] = v;
+  } else {
+    reinterpret_cast<uint16_t*>(p)[i] = f32_to_elem<kType == kElemBF16>(v);
+  }
+}
+
+template <int kType>
+__device__ __forceinline__ void attention_generic_body(const void* __restrict__ q,
+                                                       const void* __restrict__ k,
+                                                       const void* __restrict__ v,
+                                                       const void* __restrict__ mask,
+                                                       void* __restrict__ out, int B, int M,
+                                                       int K1, int K2, int N, int scale_bits,
+                                                       int mask_kind) {
+  using Cfg = AttnGenericConfig;
+  constexpr int T = Cfg::kThreads;
+  __shared__ float q_s[Cfg::kMaxK1];
+  __shared__ float p_s[T];
+  __shared__ float red[T / 32];
+  const int m = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  (void)B;
+  // s' = scale*log2e in the scale's type, cast to Q's type (:336-358).
+  const float mult = round_elem<kType>(round_elem<kType>(__int_as_float(scale_bits)) *
+                                       round_elem<kType>(1.4426950408889634074f));
+  for (int d = tid; d < K1; d += T) {
+    q_s[d] = round_elem<kType>(mult * ld_elem<kType>(q, ((size_t)b * M + m) * K1 + d));
+  }
+  __syncthreads();
+  float run_max = -FLT_MAX, run_sum = 0.f;
+  float acc[Cfg::kMaxN / T];
+#pragma unroll
+  for (int i = 0; i < Cfg::kMaxN / T; ++i) acc[i] = 0.f;
+  for (int t0 = 0; t0 < K2; t0 += T) {
+    const int j = t0 + tid;
+    float s = -INFINITY;
+    if (j < K2) {
+      const size_t kbase = ((size_t)b * K2 + j) * K1;
+      float a = 0.f;
+      for (int d = 0; d < K1; ++d) a = fmaf(q_s[d], ld_elem<kType>(k, kbase + d), a);
+      const size_t midx = ((size_t)b * M + m) * K2 + j;
+      if (mask_kind == 1) {
+        a = a + (reinterpret_cast<const uint8_t*>(mask)[midx] ? 0.f : -INFINITY);
+      } else if (mask_kind == 2) {
+        a = a + reinterpret_cast<const float*>(mask)[midx] * 1.4426950408889634074f;
+      }
+      s = a;
+    }
+    float wmx = s;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmx = fmaxf(wmx, __shfl_xor_sync(0xffffffffu, wmx, o));
+    if (lane == 0) red[warp] = wmx;
+    __syncthreads();
+    float new_max = run_max;
+#pragma unroll
+    for (int w = 0; w < T / 32; ++w) new_max = fmaxf(new_max, red[w]);
+    const float norm = exp2f(run_max - new_max);
+    const float p = j < K2 ? exp2f(s - new_max) : 0.f;
+    float psum = p;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) psum += __shfl_xor_sync(0xffffffffu, psum, o);
+    __syncthreads();
+    p_s[tid] = round_elem<kType>(p);
+    if (lane == 0) red[warp] = psum;
+    __syncthreads();
+    float tot = 0.f;
+#pragma unroll
+    for (int w = 0; w < T / 32; ++w) tot += red[w];
+    run_sum = norm * run_sum + tot;
+    run_max = new_max;
+    const int tl = min(T, K2 - t0);
+#pragma unroll
+    for (int i = 0; i < Cfg::kMaxN / T; ++i) {
+      const int n = tid + i * T;
+      if (n < N) {
+        float a = norm * acc[i];
+        for (int jj = 0; jj < tl; ++jj) {
+          a = fmaf(p_s[jj], ld_elem<kType>(v, ((size_t)b * K2 + t0 + jj) * N + n), a);
+        }
+        acc[i] = a;
+      }
+    }
+    __syncthreads();
+  }
+  const float rcp = 1.0f / run_sum;
+#pragma unroll
+  for (int i = 0; i < Cfg::kMaxN / T; ++i) {
+    const int n = tid + i * T;
+    if (n < N) st_elem<kType>(out, ((size_t)b * M + m) * N + n, rcp * acc[i]);
+  }
+}
+
+}  // namespace
+
+#define B200_GENERIC(SUFFIX, TYPE)                                                            \
+  extern "C" __global__ void __launch_bounds__(AttnGenericConfig::kThreads)                   \
+      iree_b200_attention_generic_##SUFFIX(                                                   \
+          const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, \
+          const void* __restrict__ mask, void* __restrict__ out, int B, int M, int K1, int K2, \
+          int N, int scale_bits, int mask_kind) {                                             \
+    attention_generic_body<TYPE>(q, k, v, mask, out, B, M, K1, K2, N, scale_bits, mask_kind); \
+  }
+
+B200_GENERIC(f16, kElemF16)
+B200_GENERIC(bf16, kElemBF16)
+B200_GENERIC(f32, kElemF32)

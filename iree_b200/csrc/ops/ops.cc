@@ -4,6 +4,7 @@
 #include <algorithm>
 
 #include "../hal/internal.h"
+#include "../kernels/attention_config.h"
 #include "iree_b200_ops.h"
 
 using namespace b200hal;
@@ -20,6 +21,8 @@ enum MatmulFamily { kFamily2Cta = 0, kFamily1Cta = 1, kFamilyGeneric = 2, kFamil
 
 const char* const kTypeSuffix[3] = {"i8_i32", "f16_f32", "bf16_f32"};
 
+enum AttentionExport { kAttnPrefill = 0, kAttnDecodeSplit = 1, kAttnDecodeMerge = 2, kAttnGeneric = 3 };
+
 }  // namespace
 
 struct iree_b200_ops_t {
@@ -29,7 +32,7 @@ struct iree_b200_ops_t {
   std::atomic<uint64_t> dispatch_count{0};
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[3][2][kFamilyCount];
-  int32_t attention_exports[3][8];
+  int32_t attention_exports[4][8];
 };
 
 namespace {
@@ -84,6 +87,22 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
     }
+  }
+  for (int t = 0; t < 4; ++t) {
+    for (int e = 0; e < 8; ++e) ops->attention_exports[t][e] = -1;
+  }
+  ops->attention_exports[IREE_B200_ELEMENT_TYPE_F32][kAttnGeneric] =
+      lookup(ops->executable, "iree_b200_attention_generic_f32");
+  for (int t = 1; t < 3; ++t) {
+    const std::string suffix = t == IREE_B200_ELEMENT_TYPE_F16 ? "f16" : "bf16";
+    ops->attention_exports[t][kAttnPrefill] =
+        lookup(ops->executable, "iree_b200_attention_prefill_" + suffix);
+    ops->attention_exports[t][kAttnDecodeSplit] =
+        lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
+    ops->attention_exports[t][kAttnDecodeMerge] =
+        lookup(ops->executable, "iree_b200_attention_decode_merge_" + suffix);
+    ops->attention_exports[t][kAttnGeneric] =
+        lookup(ops->executable, "iree_b200_attention_generic_" + suffix);
   }
   *out_ops = ops;
   return IREE_B200_STATUS_OK;
@@ -289,6 +308,284 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
     return iree_b200_device_wait_idle(device);
   };
   status = run();
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
+  iree_b200_command_buffer_release(cb);
+  for (auto* b : buffers) iree_b200_buffer_release(b);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
+
+
+//===----------------------------------------------------------------------===//
+// iree_linalg_ext.attention
+//===----------------------------------------------------------------------===//
+
+static uint32_t float_bits(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+}
+
+iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, int32_t element_type,
+                                                  int64_t B, int64_t M, int64_t K1, int64_t K2,
+                                                  int64_t N, float scale, int32_t mask_kind,
+                                                  uint32_t flags, uint32_t alignment,
+                                                  iree_b200_attention_selection_t* out_selection) {
+  B200_REQUIRE_ARG(ops && out_selection);
+  memset(out_selection, 0, sizeof(*out_selection));
+  if (element_type != IREE_B200_ELEMENT_TYPE_F16 && element_type != IREE_B200_ELEMENT_TYPE_BF16 &&
+      element_type != IREE_B200_ELEMENT_TYPE_F32) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "attention element type %d unsupported (f16 / bf16 / f32)", element_type);
+  }
+  if (mask_kind < 0 || mask_kind > 2) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad attention mask kind %d", mask_kind);
+  }
+  const int64_t dims[5] = {B, M, K1, K2, N};
+  for (int64_t d : dims) {
+    if (d < 0 || d > INT32_MAX) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "attention dimension %lld out of range",
+                         (long long)d);
+    }
+  }
+  if (B == 0 || M == 0 || N == 0) return IREE_B200_STATUS_OK;  // empty result
+  if (K1 == 0 || K2 == 0) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "attention with an empty reduction (K1=%lld, K2=%lld) is undefined",
+                       (long long)K1, (long long)K2);
+  }
+  const bool tc_shape = K1 == 128 && N == 128 && mask_kind == IREE_B200_ATTENTION_MASK_NONE &&
+                        alignment >= 16 && element_type != IREE_B200_ELEMENT_TYPE_F32;
+  enum { kPrefill, kDecode, kGeneric } family;
+  if (flags & IREE_B200_ATTENTION_FLAG_FORCE_GENERIC) {
+    family = kGeneric;
+  } else if (flags & (IREE_B200_ATTENTION_FLAG_FORCE_PREFILL | IREE_B200_ATTENTION_FLAG_FORCE_DECODE)) {
+    if (!tc_shape) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "shape/mask/alignment does not satisfy the guards of the forced kernel");
+    }
+    family = (flags & IREE_B200_ATTENTION_FLAG_FORCE_PREFILL) ? kPrefill : kDecode;
+  } else if (tc_shape) {
+    family = M > 16 ? kPrefill : kDecode;
+  } else {
+    family = kGeneric;
+  }
+  const uint32_t scale_bits = float_bits(scale);
+  iree_b200_attention_dispatch_t* d0 = &out_selection->dispatches[0];
+  iree_b200_attention_dispatch_t* d1 = &out_selection->dispatches[1];
+  switch (family) {
+    case kPrefill: {
+      if (B > 65535) return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention batch too large");
+      d0->export_ordinal = ops->attention_exports[element_type][kAttnPrefill];
+      d0->workgroup_count[0] = (uint32_t)ceil_div(M, 256);
+      d0->workgroup_count[1] = (uint32_t)B;
+      d0->workgroup_count[2] = 1;
+      d0->constant_count = 5;
+      d0->constants[0] = (uint32_t)B;
+      d0->constants[1] = (uint32_t)M;
+      d0->constants[2] = (uint32_t)K2;
+      d0->constants[3] = scale_bits;
+      d0->constants[4] = 0;
+      out_selection->dispatch_count = 1;
+      break;
+    }
+    case kDecode: {
+      if (B > 65535 || M > 65535) {
+        return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention decode grid out of range");
+      }
+      const int64_t chunk = b200::AttnDecodeConfig::kChunkRows;
+      const int64_t want = std::max<int64_t>(1, (int64_t)ops->device->sm_count * 8 / (B * M));
+      const int64_t splits = std::max<int64_t>(1, std::min(ceil_div(K2, chunk), want));
+      d0->export_ordinal = ops->attention_exports[element_type][kAttnDecodeSplit];
+      d0->workgroup_count[0] = (uint32_t)splits;
+      d0->workgroup_count[1] = (uint32_t)M;
+      d0->workgroup_count[2] = (uint32_t)B;
+      d0->constant_count = 5;
+      d0->constants[0] = (uint32_t)B;
+      d0->constants[1] = (uint32_t)M;
+      d0->constants[2] = (uint32_t)K2;
+      d0->constants[3] = scale_bits;
+      d0->constants[4] = (uint32_t)splits;
+      d1->export_ordinal = ops->attention_exports[element_type][kAttnDecodeMerge];
+      d1->workgroup_count[0] = (uint32_t)M;
+      d1->workgroup_count[1] = (uint32_t)B;
+      d1->workgroup_count[2] = 1;
+      d1->constant_count = 3;
+      d1->constants[0] = (uint32_t)B;
+      d1->constants[1] = (uint32_t)M;
+      d1->constants[2] = (uint32_t)splits;
+      out_selection->dispatch_count = 2;
+      out_selection->workspace_bytes =
+          (uint64_t)B * M * splits * b200::AttnDecodeConfig::kRecordFloats * 4;
+      break;
+    }
+    default: {
+      if (K1 > b200::AttnGenericConfig::kMaxK1 || N > b200::AttnGenericConfig::kMaxN) {
+        return make_status(IREE_B200_STATUS_UNIMPLEMENTED,
+                           "attention K1=%lld N=%lld exceeds the generic kernel's limits; such "
+                           "ops stay with the compiler's own codegen",
+                           (long long)K1, (long long)N);
+      }
+      if (B > 65535) return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention batch too large");
+      d0->export_ordinal = ops->attention_exports[element_type][kAttnGeneric];
+      d0->workgroup_count[0] = (uint32_t)M;
+      d0->workgroup_count[1] = (uint32_t)B;
+      d0->workgroup_count[2] = 1;
+      d0->constant_count = 7;
+      d0->constants[0] = (uint32_t)B;
+      d0->constants[1] = (uint32_t)M;
+      d0->constants[2] = (uint32_t)K1;
+      d0->constants[3] = (uint32_t)K2;
+      d0->constants[4] = (uint32_t)N;
+      d0->constants[5] = scale_bits;
+      d0->constants[6] = (uint32_t)mask_kind;
+      out_selection->dispatch_count = 1;
+      break;
+    }
+  }
+  for (int i = 0; i < out_selection->dispatch_count; ++i) {
+    if (out_selection->dispatches[i].export_ordinal < 0) {
+      return make_status(IREE_B200_STATUS_NOT_FOUND,
+                         "the executable lacks an attention export for element type %d",
+                         element_type);
+    }
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+static iree_b200_status_t check_binding(const char* what, iree_b200_buffer_ref_t ref, uint64_t need,
+                                        uint32_t* alignment) {
+  if (!ref.buffer) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "attention binding %s is null", what);
+  }
+  const uint64_t total = ref.buffer->byte_length;
+  if (ref.offset > total) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention binding %s offset out of range",
+                       what);
+  }
+  const uint64_t length = ref.length == UINT64_MAX ? total - ref.offset : ref.length;
+  if (length < need || length > total - ref.offset) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "attention binding %s holds %llu bytes but the shape needs %llu", what,
+                       (unsigned long long)length, (unsigned long long)need);
+  }
+  *alignment = std::min(*alignment, pointer_alignment(ref.buffer->device_ptr + ref.offset));
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_record_attention(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t B,
+    int64_t M, int64_t K1, int64_t K2, int64_t N, float scale, int32_t mask_kind, uint32_t flags,
+    iree_b200_buffer_ref_t q, iree_b200_buffer_ref_t k, iree_b200_buffer_ref_t v,
+    iree_b200_buffer_ref_t mask, iree_b200_buffer_ref_t workspace, iree_b200_buffer_ref_t out) {
+  B200_REQUIRE_ARG(ops && cb);
+  if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "negative attention dimension");
+  }
+  uint32_t alignment = 256;
+  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_F32 ? 4 : 2;
+  B200_RETURN_IF_ERROR(check_binding("Q", q, (uint64_t)B * M * K1 * es, &alignment));
+  B200_RETURN_IF_ERROR(check_binding("K", k, (uint64_t)B * K2 * K1 * es, &alignment));
+  B200_RETURN_IF_ERROR(check_binding("V", v, (uint64_t)B * K2 * N * es, &alignment));
+  B200_RETURN_IF_ERROR(check_binding("O", out, (uint64_t)B * M * N * es, &alignment));
+  if (mask_kind != IREE_B200_ATTENTION_MASK_NONE) {
+    uint32_t ignored = 256;
+    B200_RETURN_IF_ERROR(check_binding(
+        "mask", mask, (uint64_t)B * M * K2 * (mask_kind == IREE_B200_ATTENTION_MASK_F32 ? 4 : 1),
+        &ignored));
+  }
+  iree_b200_attention_selection_t sel;
+  B200_RETURN_IF_ERROR(iree_b200_ops_select_attention(ops, element_type, B, M, K1, K2, N, scale,
+                                                      mask_kind, flags, alignment, &sel));
+  if (sel.dispatch_count == 0) return IREE_B200_STATUS_OK;
+  if (sel.workspace_bytes) {
+    uint32_t ignored = 256;
+    B200_RETURN_IF_ERROR(check_binding("workspace", workspace, sel.workspace_bytes, &ignored));
+  }
+  if (sel.dispatch_count == 2) {
+    const iree_b200_buffer_ref_t split_refs[4] = {q, k, v, workspace};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
+        sel.dispatches[0].constants, sel.dispatches[0].constant_count, split_refs, 4, 0));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
+    const iree_b200_buffer_ref_t merge_refs[2] = {workspace, out};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->executable, sel.dispatches[1].export_ordinal, sel.dispatches[1].workgroup_count,
+        sel.dispatches[1].constants, sel.dispatches[1].constant_count, merge_refs, 2, 0));
+    ops->dispatch_count.fetch_add(2);
+    return IREE_B200_STATUS_OK;
+  }
+  if (sel.dispatches[0].constant_count == 7) {
+    // Generic export: the mask binding must be a valid pointer even when unused.
+    const iree_b200_buffer_ref_t refs[5] = {
+        q, k, v, mask_kind == IREE_B200_ATTENTION_MASK_NONE ? q : mask, out};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
+        sel.dispatches[0].constants, 7, refs, 5, 0));
+  } else {
+    const iree_b200_buffer_ref_t refs[4] = {q, k, v, out};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
+        sel.dispatches[0].constants, 5, refs, 4, 0));
+  }
+  ops->dispatch_count.fetch_add(1);
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t element_type,
+                                                int64_t B, int64_t M, int64_t K1, int64_t K2,
+                                                int64_t N, float scale, int32_t mask_kind,
+                                                uint32_t flags, const void* q, const void* k,
+                                                const void* v, const void* mask, void* out) {
+  B200_REQUIRE_ARG(ops);
+  if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0 || mask_kind < 0 || mask_kind > 2) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad attention shape or mask kind");
+  }
+  iree_b200_attention_selection_t sel;
+  B200_RETURN_IF_ERROR(iree_b200_ops_select_attention(ops, element_type, B, M, K1, K2, N, scale,
+                                                      mask_kind, flags, 256, &sel));
+  if (sel.dispatch_count == 0) return IREE_B200_STATUS_OK;
+  const uint64_t mask_bytes =
+      mask_kind == IREE_B200_ATTENTION_MASK_NONE
+          ? 0
+          : (uint64_t)B * M * K2 * (mask_kind == IREE_B200_ATTENTION_MASK_F32 ? 4 : 1);
+  // 0=Q 1=K 2=V 3=mask 4=workspace 5=O
+  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_F32 ? 4 : 2;
+  const uint64_t bytes[6] = {(uint64_t)B * M * K1 * es, (uint64_t)B * K2 * K1 * es,
+                             (uint64_t)B * K2 * N * es,  mask_bytes,
+                             sel.workspace_bytes,        (uint64_t)B * M * N * es};
+  const void* host_in[4] = {q, k, v, mask};
+  for (int i = 0; i < 4; ++i) B200_REQUIRE_ARG(host_in[i] || !bytes[i]);
+  B200_REQUIRE_ARG(out);
+  iree_b200_device_t* device = ops->device;
+  iree_b200_buffer_t* buffers[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  iree_b200_command_buffer_t* cb = nullptr;
+  auto ref = [&](int i) {
+    return iree_b200_buffer_ref_t{buffers[i], 0, buffers[i] ? bytes[i] : 0};
+  };
+  auto run = [&]() -> iree_b200_status_t {
+    for (int i = 0; i < 6; ++i) {
+      if (!bytes[i]) continue;
+      B200_RETURN_IF_ERROR(iree_b200_allocator_allocate_buffer(
+          device, IREE_B200_MEMORY_TYPE_DEVICE_LOCAL, bytes[i], &buffers[i]));
+    }
+    for (int i = 0; i < 4; ++i) {
+      if (!bytes[i]) continue;
+      B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, host_in[i], buffers[i], 0, bytes[i]));
+    }
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_attention(ops, cb, element_type, B, M, K1, K2, N,
+                                                        scale, mask_kind, flags, ref(0), ref(1),
+                                                        ref(2), ref(3), ref(4), ref(5)));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+    B200_RETURN_IF_ERROR(
+        iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, buffers[5], 0, out, bytes[5]));
+    return iree_b200_device_wait_idle(device);
+  };
+  iree_b200_status_t status = run();
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
   if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
   iree_b200_command_buffer_release(cb);

@@ -18,14 +18,19 @@ from . import build as _build
 
 UINT64_MAX = (1 << 64) - 1
 
-I8, F16, BF16 = 0, 1, 2
-ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16}
+I8, F16, BF16, F32 = 0, 1, 2, 3
+ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32}
 
 MATMUL_ACCUMULATE = 1 << 0
 MATMUL_TRANSPOSE_RHS = 1 << 1
 MATMUL_FORCE_GENERIC = 1 << 8
 MATMUL_FORCE_1CTA = 1 << 9
 MATMUL_FORCE_2CTA = 1 << 10
+
+ATTENTION_MASK_NONE, ATTENTION_MASK_BOOL, ATTENTION_MASK_F32 = 0, 1, 2
+ATTENTION_FORCE_GENERIC = 1 << 8
+ATTENTION_FORCE_PREFILL = 1 << 9
+ATTENTION_FORCE_DECODE = 1 << 10
 
 MODE_GRAPH, MODE_STREAM = 0, 1
 MEMORY_DEVICE_LOCAL, MEMORY_HOST_LOCAL = 1, 2
@@ -80,6 +85,16 @@ class MatmulSelection(Structure):
                 ("constants", c_uint32 * 5)]
 
 
+class AttentionDispatch(Structure):
+    _fields_ = [("export_ordinal", c_int32), ("workgroup_count", c_uint32 * 3),
+                ("constant_count", c_uint32), ("constants", c_uint32 * 8)]
+
+
+class AttentionSelection(Structure):
+    _fields_ = [("dispatch_count", c_int32), ("dispatches", AttentionDispatch * 2),
+                ("workspace_bytes", c_uint64)]
+
+
 _STATUS_FUNCS = {
     # name: argtypes (all return iree_b200_status_t)
     "iree_b200_device_create": [c_int32, POINTER(DeviceParams), POINTER(c_void_p)],
@@ -127,6 +142,16 @@ _STATUS_FUNCS = {
                                     c_int64, c_uint32, BufferRef, BufferRef, BufferRef],
     "iree_b200_ops_matmul_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                   c_uint32, c_void_p, c_void_p, c_void_p],
+    "iree_b200_ops_select_attention": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
+                                       c_int64, ctypes.c_float, c_int32, c_uint32, c_uint32,
+                                       POINTER(AttentionSelection)],
+    "iree_b200_ops_record_attention": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64,
+                                       c_int64, c_int64, ctypes.c_float, c_int32, c_uint32,
+                                       BufferRef, BufferRef, BufferRef, BufferRef, BufferRef,
+                                       BufferRef],
+    "iree_b200_ops_attention_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
+                                     c_int64, ctypes.c_float, c_int32, c_uint32, c_void_p,
+                                     c_void_p, c_void_p, c_void_p, c_void_p],
 }
 
 _OTHER_FUNCS = {
@@ -501,6 +526,31 @@ class Ops:
                     flags=0):
         check(lib().iree_b200_ops_matmul_host(self._h, _etype(element_type), batch, M, N, K, flags,
                                               lhs_ptr, rhs_ptr, out_ptr))
+
+    def select_attention(self, element_type, B, M, K1, K2, N, scale, mask_kind=0, flags=0,
+                         alignment=256) -> dict:
+        sel = AttentionSelection()
+        check(lib().iree_b200_ops_select_attention(self._h, _etype(element_type), B, M, K1, K2, N,
+                                                   scale, mask_kind, flags, alignment, byref(sel)))
+        return {"workspace_bytes": sel.workspace_bytes,
+                "dispatches": [{"export_ordinal": d.export_ordinal,
+                                "workgroup_count": list(d.workgroup_count),
+                                "constants": list(d.constants)[:d.constant_count]}
+                               for d in list(sel.dispatches)[:sel.dispatch_count]]}
+
+    def record_attention(self, cb: CommandBuffer, element_type, B, M, K1, K2, N, scale,
+                         q: BufferRef, k: BufferRef, v: BufferRef, out: BufferRef,
+                         mask: BufferRef = None, workspace: BufferRef = None, mask_kind=0, flags=0):
+        check(lib().iree_b200_ops_record_attention(
+            self._h, cb._h, _etype(element_type), B, M, K1, K2, N, scale, mask_kind, flags, q, k, v,
+            mask if mask is not None else NULL_REF,
+            workspace if workspace is not None else NULL_REF, out))
+
+    def attention_host(self, element_type, B, M, K1, K2, N, scale, q_ptr: int, k_ptr: int,
+                       v_ptr: int, out_ptr: int, mask_ptr: int = 0, mask_kind=0, flags=0):
+        check(lib().iree_b200_ops_attention_host(self._h, _etype(element_type), B, M, K1, K2, N,
+                                                 scale, mask_kind, flags, q_ptr, k_ptr, v_ptr,
+                                                 mask_ptr or None, out_ptr))
 
     def release(self):
         if getattr(self, "_h", None):

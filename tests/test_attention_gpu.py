@@ -1,0 +1,199 @@
+"""Parity of the CUDA attention dispatches with the oracle, through the C-ABI (B200 only).
+
+* the reference's own golden tensors (tests/e2e/linalg_ext_ops/attention*.mlir, atol 1e-4)
+  through the generic kernel (f32, masks);
+* the tcgen05 prefill kernel and the split-KV decode kernels against the oracle's restated
+  llvm-cpu arithmetic on seeded random inputs, tolerance from BASELINE.json north_star
+  (1e-3 relative for f16, 1e-2 for bf16), including ragged M / K2;
+* at the BASELINE Llama-3-8B shapes (32 heads, D=128, seq 4096 prefill / 8192-KV decode):
+  sampled rows against the oracle plus a size-independent property (uniform V => O == V row).
+"""
+
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from iree_b200 import hal as H
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "attention_golden.json")
+RTOL = {"f16": 1e-3, "bf16": 1e-2}
+
+
+def _tensor(d):
+    a = np.array(d["data"], dtype=np.float64)
+    shape = d["shape"]
+    if a.size == 1 and int(np.prod(shape)) != 1:
+        a = np.full(shape, a.reshape(-1)[0])
+    return a.reshape(shape)
+
+
+def _golden_cases():
+    with open(GOLDEN) as f:
+        cases = json.load(f)["cases"]
+    # The region is part of the op's body; the matcher only takes the identity region.
+    return [c for c in cases if c["region"]["kind"] == "identity"]
+
+
+def _gpu_attention(ops, t, q, k, v, scale, mask=None, flags=0):
+    B, M, K1 = q.shape
+    K2, N = k.shape[1], v.shape[2]
+    out = np.zeros((B, M, N), dtype=q.dtype)
+    mask_kind, mask_ptr = H.ATTENTION_MASK_NONE, 0
+    if mask is not None:
+        if mask.dtype == np.bool_:
+            mask = np.ascontiguousarray(mask, dtype=np.uint8)
+            mask_kind = H.ATTENTION_MASK_BOOL
+        else:
+            mask = np.ascontiguousarray(mask, dtype=np.float32)
+            mask_kind = H.ATTENTION_MASK_F32
+        mask_ptr = mask.ctypes.data
+    q, k, v = (np.ascontiguousarray(x) for x in (q, k, v))
+    ops.attention_host(t, B, M, K1, K2, N, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       out.ctypes.data, mask_ptr=mask_ptr, mask_kind=mask_kind, flags=flags)
+    return out
+
+
+@pytest.mark.parametrize("case", _golden_cases(), ids=lambda c: c["source"] + ":" + c["name"])
+def test_reference_golden_vectors(ops, case):
+    q, k, v = (_tensor(case[x]).astype(np.float32) for x in ("query", "key", "value"))
+    mask = None
+    if "mask" in case:
+        m = _tensor(case["mask"])
+        mask = m.astype(bool) if case["mask"]["type"] == "i1" else m.astype(np.float32)
+        mask = np.broadcast_to(mask, (q.shape[0], q.shape[1], k.shape[1])).copy()
+    got = _gpu_attention(ops, "f32", q, k, v, case["scale"], mask=mask)
+    np.testing.assert_allclose(got, _tensor(case["expected"]), atol=case["atol"], rtol=0)
+
+
+def _random_qkv(t, B, M, K2, D, seed, N=None):
+    g = np.random.Generator(np.random.PCG64(0xB200 + seed))
+    N = D if N is None else N
+    q = oracle.from_f32(t, np.clip(g.standard_normal((B, M, D)), -4, 4).astype(np.float32))
+    k = oracle.from_f32(t, np.clip(g.standard_normal((B, K2, D)), -4, 4).astype(np.float32))
+    v = oracle.from_f32(t, np.clip(g.standard_normal((B, K2, N)), -4, 4).astype(np.float32))
+    return q, k, v
+
+
+def _assert_close(t, got, want):
+    g, w = oracle.to_f32(t, got), oracle.to_f32(t, want)
+    assert np.isfinite(g).all()
+    scale = np.abs(w).max()
+    assert np.abs(g - w).max() <= RTOL[t] * max(scale, 1.0), (np.abs(g - w).max(), scale)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("shape", [(1, 128, 128), (2, 256, 256), (3, 384, 640), (2, 200, 300),
+                                   (1, 130, 77), (4, 512, 1024), (1, 17, 129)], ids=str)
+def test_prefill_kernel_vs_oracle(ops, t, shape):
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=M + K2)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_PREFILL)
+    want = oracle.attention(t, q, k, v, scale, k2_tile=128)
+    _assert_close(t, got, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+def test_prefill_kernel_rescale_path(ops, t):
+    """Row maxima that keep growing across K2 blocks force the lazy O correction."""
+    B, M, K2 = 1, 128, 1024
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=7)
+    kf = oracle.to_f32(t, k)
+    kf *= (1.0 + np.arange(K2, dtype=np.float32) / 64.0)[None, :, None]
+    k = oracle.from_f32(t, kf)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_PREFILL)
+    want = oracle.attention(t, q, k, v, scale, k2_tile=128)
+    _assert_close(t, got, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("shape", [(1, 1, 256), (2, 1, 1000), (4, 3, 4096), (32, 1, 8192),
+                                   (1, 16, 77)], ids=str)
+def test_decode_kernels_vs_oracle(ops, t, shape):
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=K2)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_DECODE)
+    want = oracle.attention(t, q, k, v, scale, k2_tile=256)
+    _assert_close(t, got, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("mask_kind", [None, "bool", "f32"])
+@pytest.mark.parametrize("shape", [(2, 5, 16, 40, 24), (1, 33, 64, 300, 64), (1, 4, 130, 129, 200)],
+                         ids=str)
+def test_generic_kernel_vs_oracle(ops, t, mask_kind, shape):
+    B, M, K1, K2, N = shape
+    g = np.random.Generator(np.random.PCG64(0xB200 + K2))
+    q, k, v = _random_qkv(t, B, M, K2, K1, seed=K1, N=N)
+    mask = None
+    if mask_kind == "bool":
+        mask = g.random((B, M, K2)) > 0.3
+        mask[:, :, 0] = True  # no fully masked row (NaN by definition, TileAttention.cpp:141)
+    elif mask_kind == "f32":
+        mask = g.standard_normal((B, M, K2)).astype(np.float32)
+    scale = 1.0 / np.sqrt(float(K1))
+    got = _gpu_attention(ops, t, q, k, v, scale, mask=mask, flags=H.ATTENTION_FORCE_GENERIC)
+    want = oracle.attention(t, q, k, v, scale, mask=mask, k2_tile=128)
+    _assert_close(t, got, want)
+
+
+def test_selection_guards(ops):
+    exe = ops.executable
+    names = lambda sel: [exe.export_info(d["export_ordinal"])["kernel_name"] for d in sel["dispatches"]]
+    s = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088)
+    assert names(s) == ["iree_b200_attention_prefill_f16"]
+    assert s["dispatches"][0]["workgroup_count"] == [16, 32, 1]
+    s = ops.select_attention("f16", 32, 1, 128, 8192, 128, 0.088)
+    assert names(s) == ["iree_b200_attention_decode_split_f16", "iree_b200_attention_decode_merge_f16"]
+    assert s["workspace_bytes"] == 32 * s["dispatches"][0]["workgroup_count"][0] * 130 * 4
+    assert names(ops.select_attention("bf16", 2, 64, 64, 64, 64, 0.125)) == \
+        ["iree_b200_attention_generic_bf16"]
+    assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1,
+                                      mask_kind=H.ATTENTION_MASK_BOOL)) == \
+        ["iree_b200_attention_generic_f16"]
+    assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1, alignment=2)) == \
+        ["iree_b200_attention_generic_f16"]
+    assert ops.select_attention("f16", 0, 4, 8, 8, 8, 1.0)["dispatches"] == []
+    with pytest.raises(H.Status):
+        ops.select_attention("i8", 1, 4, 8, 8, 8, 1.0)
+    with pytest.raises(H.Status):
+        ops.select_attention("f16", 1, 4, 1024, 8, 8, 1.0)
+    with pytest.raises(H.Status):
+        ops.select_attention("f16", 1, 64, 64, 64, 64, 1.0, flags=H.ATTENTION_FORCE_PREFILL)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+def test_llama_prefill_shape_sampled(ops, t):
+    """BASELINE configs[3] prefill: 32 heads, D=128, seq 4096."""
+    B, M, K2 = 32, 4096, 4096
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=99)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale)
+    # Oracle on sampled rows of sampled heads (the full oracle is ~275 GFLOP of scalar code).
+    rows = np.array([0, 1, 127, 128, 255, 256, 1000, 2047, 2048, 4095])
+    for b in (0, 13, 31):
+        want = oracle.attention(t, q[b:b + 1, rows], k[b:b + 1], v[b:b + 1], scale, k2_tile=128)
+        _assert_close(t, got[b:b + 1, rows], want)
+    # Property: softmax weights sum to one, so a V that is constant along K2 comes back.
+    vconst = np.broadcast_to(v[:, :1, :], v.shape).copy()
+    got2 = _gpu_attention(ops, t, q, k, vconst, scale)
+    ref = np.broadcast_to(oracle.to_f32(t, vconst[:, :1, :]), got2.shape)
+    assert np.abs(oracle.to_f32(t, got2) - ref).max() <= RTOL[t] * 4 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+def test_llama_decode_shape(ops, t):
+    """BASELINE configs[3] decode: seq 1 over an 8K KV cache, 32 heads."""
+    B, M, K2 = 32, 1, 8192
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=5)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale)
+    want = oracle.attention(t, q, k, v, scale, k2_tile=256)
+    _assert_close(t, got, want)
