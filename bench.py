@@ -44,6 +44,14 @@ MATMUL_WORKLOADS = {
 }
 
 
+# name -> (op, element type, batch*heads, M, K2, head dim)   [attention]
+ATTENTION_WORKLOADS = {
+    "attention_prefill": ("attention", "f16", 32, 4096, 4096, 128),
+    "attention_prefill_bf16": ("attention", "bf16", 32, 4096, 4096, 128),
+    "attention_decode": ("attention", "f16", 32, 1, 8192, 128),
+}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -162,8 +170,9 @@ def synth_matmul_inputs(torch, et, batch, M, N, K, seed):
 class MatmulStep:
     """One recorded command buffer holding the workload's dispatch; step() replays it."""
 
-    def __init__(self, torch, hal, dev, ops, et, batch, M, N, K, seed):
-        self.shape = (et, batch, M, N, K)
+    def __init__(self, torch, hal, dev, ops, spec, seed):
+        op, et, batch, M, N, K = spec
+        self.spec = spec
         self.tensors = synth_matmul_inputs(torch, et, batch, M, N, K, seed)
         self.buffers = [dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
                         for t in self.tensors]
@@ -178,6 +187,88 @@ class MatmulStep:
     def step(self):
         self.dev.execute(self.cb)
 
+    def host_buffers(self, torch):
+        host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors]
+        host[0].copy_(self.tensors[0])
+        host[1].copy_(self.tensors[1])
+        return host
+
+    def host_call(self, ops, host):
+        op, et, batch, M, N, K = self.spec
+        ops.matmul_host(et, batch, M, N, K, host[0].data_ptr(), host[1].data_ptr(),
+                        host[2].data_ptr())
+
+    def describe(self):
+        op, et, batch, M, N, K = self.spec
+        es = 1 if et == "i8" else 2
+        flop = 2.0 * batch * M * N * K
+        nbytes = float(batch) * (M * K * es + K * N * es + M * N * 4)
+        return {"flop": flop, "bytes": nbytes, "bound": "tensor",
+                "workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU",
+                "dtype": {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
+                          "i8": "i8 (i32 accumulate)"}[et],
+                "h2d": int(batch * (M * K + K * N) * es), "d2h": int(batch * M * N * 4),
+                "api": "iree_b200_ops_matmul_host (pinned host buffers)"}
+
+
+class AttentionStep:
+    """iree_linalg_ext.attention, one recorded command buffer (1 or 2 dispatches)."""
+
+    def __init__(self, torch, hal, dev, ops, spec, seed):
+        op, et, B, M, K2, D = spec
+        self.spec = spec
+        g = torch.Generator(device="cuda")
+        g.manual_seed(0xB200 + seed)
+        dt = torch.bfloat16 if et == "bf16" else torch.float16
+        mk = lambda *shape: torch.randn(shape, device="cuda", generator=g).clamp_(-4, 4).to(dt)
+        self.tensors = [mk(B, M, D), mk(B, K2, D), mk(B, K2, D),
+                        torch.empty((B, M, D), dtype=dt, device="cuda")]
+        self.scale = 1.0 / (D ** 0.5)
+        sel = ops.select_attention(et, B, M, D, K2, D, self.scale)
+        self.workspace = torch.empty((max(sel["workspace_bytes"], 16),), dtype=torch.uint8,
+                                     device="cuda")
+        imp = lambda t: dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
+        self.buffers = [imp(t) for t in self.tensors] + [imp(self.workspace)]
+        before = ops.dispatch_count
+        self.cb = hal.CommandBuffer(dev).begin()
+        ops.record_attention(self.cb, et, B, M, D, K2, D, self.scale, self.buffers[0].ref(),
+                             self.buffers[1].ref(), self.buffers[2].ref(), self.buffers[3].ref(),
+                             workspace=self.buffers[4].ref())
+        self.cb.end()
+        self.launches_per_step = ops.dispatch_count - before
+        self.dev = dev
+
+    def step(self):
+        self.dev.execute(self.cb)
+
+    def host_buffers(self, torch):
+        host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors]
+        for h, t in zip(host[:3], self.tensors[:3]):
+            h.copy_(t)
+        return host
+
+    def host_call(self, ops, host):
+        op, et, B, M, K2, D = self.spec
+        ops.attention_host(et, B, M, D, K2, D, self.scale, host[0].data_ptr(), host[1].data_ptr(),
+                           host[2].data_ptr(), host[3].data_ptr())
+
+    def describe(self):
+        op, et, B, M, K2, D = self.spec
+        flop = 4.0 * B * M * K2 * D
+        nbytes = float(B) * (2 * M * D + 2 * K2 * D) * 2
+        return {"flop": flop, "bytes": nbytes, "bound": "hbm" if M <= 16 else "tensor",
+                "workload": f"iree_linalg_ext.attention {et} batch*heads={B} M={M} K2={K2} "
+                            f"K1=N={D} scale=1/sqrt({D}) no mask, per GPU",
+                "dtype": f"{et} (f32 S/softmax/accumulate)",
+                "h2d": int(B * (M * D + 2 * K2 * D) * 2), "d2h": int(B * M * D * 2),
+                "api": "iree_b200_ops_attention_host (pinned host buffers)"}
+
+
+def make_step(torch, hal, dev, ops, workload, seed):
+    if workload in MATMUL_WORKLOADS:
+        return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed)
+    return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed)
+
 
 def run_ours(args):
     import torch
@@ -190,54 +281,52 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from iree_b200 import hal
 
-    op, et, batch, M, N, K = MATMUL_WORKLOADS[args.workload]
     stream = torch.cuda.Stream()
     dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
     ops = hal.Ops(dev)
-    work = MatmulStep(torch, hal, dev, ops, et, batch, M, N, K, seed=rank)
-    flop, nbytes = algorithmic(op, et, batch, M, N, K)
+    # Rotating input sets: the working set cycled through between timed steps exceeds L2.
+    first = make_step(torch, hal, dev, ops, args.workload, seed=rank)
+    info = first.describe()
+    sets = max(1, min(4, int(-(-2 * 126e6 // info["bytes"]))))
+    works = [first] + [make_step(torch, hal, dev, ops, args.workload, seed=rank + 100 * i)
+                       for i in range(1, sets)]
+    flop, nbytes = info["flop"], info["bytes"]
 
     # ---- device-resident timing (CUDA events on the dispatch stream) ----
     with torch.cuda.stream(stream):
-        for _ in range(args.warmup):
-            work.step()
+        for i in range(args.warmup):
+            works[i % sets].step()
         barrier(world)
         sampler = ClockSampler(local)
         if rank == 0:
             sampler.start()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record(stream)
-        for _ in range(args.steps):
-            work.step()
+        for i in range(args.steps):
+            works[i % sets].step()
         ev1.record(stream)
         barrier(world)
         clocks = sampler.stop() if rank == 0 else None
     ms_total = max_over_ranks(ev0.elapsed_time(ev1), world)
     ms_per_step = ms_total / args.steps
     value = flop * world / (ms_per_step * 1e-3) / 1e12
-    launches = work.launches_per_step * args.steps
+    launches = first.launches_per_step * args.steps
 
     # ---- end to end through the host-buffer C-ABI call ----
-    es = 1 if et == "i8" else 2
-    host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in work.tensors]
-    host[0].copy_(work.tensors[0])
-    host[1].copy_(work.tensors[1])
+    host = first.host_buffers(torch)
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
     for _ in range(2):
-        ops.matmul_host(et, batch, M, N, K, host[0].data_ptr(), host[1].data_ptr(),
-                        host[2].data_ptr())
+        first.host_call(ops, host)
     barrier(world)
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        ops.matmul_host(et, batch, M, N, K, host[0].data_ptr(), host[1].data_ptr(),
-                        host[2].data_ptr())
+        first.host_call(ops, host)
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world) / e2e_steps
     barrier(world)
     e2e = {"value": flop * world / (e2e_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
            "ms_per_step": e2e_ms, "steps": e2e_steps,
-           "h2d_bytes_per_step": int(batch * (M * K + K * N) * es),
-           "d2h_bytes_per_step": int(batch * M * N * 4),
-           "api": "iree_b200_ops_matmul_host (pinned host buffers)"}
+           "h2d_bytes_per_step": info["h2d"], "d2h_bytes_per_step": info["d2h"],
+           "api": info["api"]}
 
     if rank != 0:
         return
@@ -248,79 +337,98 @@ def run_ours(args):
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get(args.workload)
+    if info["bound"] == "tensor":
+        roofline = {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_tflops"],
+                    "unit": "TFLOP/s", "frac": per_gpu / peaks["bf16_tflops"],
+                    "frac_of_sustained": per_gpu / peaks["bf16_tflops_sustained"],
+                    "peak_source": peaks["source"] + " cuBLAS bf16 burst"}
+    else:
+        gbs = nbytes / (ms_per_step * 1e-3) / 1e9
+        roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "frac": gbs / peaks["hbm_gbs"], "peak_source": peaks["source"] + " copy"}
+    roofline.update({"traffic": traffic, "algorithmic_flop_per_launch": flop,
+                     "algorithmic_bytes_per_launch": nbytes})
     line = {
         "metric": METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
-                  "i8": "i8 (i32 accumulate)"}[et],
-        "data": "synthetic",
-        "config": {"workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU"
+        "dtype": info["dtype"], "data": "synthetic",
+        "config": {"workload": info["workload"]
                                + (f", batch-sharded over {world} GPUs (no collective)"
                                   if world > 1 else ""),
-                   "l2": "inputs+output (%.0f MiB) exceed the 126 MB L2; no flush" % (nbytes / 2**20),
-                   "launch": "stream command buffer replay, one dispatch per step"},
-        "roofline": {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_tflops"],
-                     "unit": "TFLOP/s", "frac": per_gpu / peaks["bf16_tflops"],
-                     "frac_of_sustained": per_gpu / peaks["bf16_tflops_sustained"],
-                     "peak_source": peaks["source"] + " cuBLAS bf16 burst", "traffic": traffic,
-                     "algorithmic_flop_per_launch": flop, "algorithmic_bytes_per_launch": nbytes},
-        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+                   "l2": "%d rotating input sets of %.0f MiB each (> 126 MB L2 between reuses); "
+                         "no flush" % (sets, nbytes / 2**20),
+                   "launch": "stream command buffer replay, %d dispatch(es) per step"
+                             % first.launches_per_step},
+        "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(et, threads=os.cpu_count() or 1)
+        line["cpu_baseline"] = cpu_baseline(args.workload, threads=os.cpu_count() or 1)
     print(json.dumps(line), flush=True)
 
 
-def cpu_sample(et, rows, N, K, seed=1):
-    """Rows [0, rows) of the 8192^3 problem: a bounded sample of the same workload."""
+def cpu_work(workload, rows):
+    """A bounded sample of |workload| for the CPU arm: returns (callable, flop, description).
+
+    matmul: the first |rows| rows of the LHS against the full RHS. attention: the first
+    |rows| query rows of one head against that head's full K/V. Inputs come from the
+    reference generator (test_utils.c:359-420) / a seeded PCG as in the parity tests."""
+    import numpy as np
     import oracle
-    lhs = oracle.generate_random_matrix(et, (rows, K), seed)
-    rhs = oracle.generate_random_matrix(et, (K, N), seed + 1)
-    return lhs, rhs
+    if workload in MATMUL_WORKLOADS:
+        op, et, batch, M, N, K = MATMUL_WORKLOADS[workload]
+        rows = min(rows, M)
+        lhs = oracle.generate_random_matrix(et, (rows, K), 1)
+        rhs = oracle.generate_random_matrix(et, (K, N), 2)
+        desc = (f"oracle port of the reference loops (iree-e2e-matmul-test.cc:28-121), OpenMP, "
+                f"{et} M={rows} (of {batch}x{M}) N={N} K={K}")
+        return (lambda: oracle.matmul(et, lhs, rhs)), 2.0 * rows * N * K, desc
+    op, et, B, M, K2, D = ATTENTION_WORKLOADS[workload]
+    rows = min(rows, M)
+    heads = 1 if M > 1 else min(B, 8)
+    g = np.random.Generator(np.random.PCG64(0xB200))
+    mk = lambda *shape: oracle.from_f32(et, np.clip(g.standard_normal(shape), -4, 4).astype(np.float32))
+    q, k, v = mk(heads, rows, D), mk(heads, K2, D), mk(heads, K2, D)
+    scale = 1.0 / (D ** 0.5)
+    desc = (f"oracle port of the llvm-cpu online-attention arithmetic "
+            f"(AggregatedOpInterfaceImpl.cpp:323-632), OpenMP, {et} heads={heads} (of {B}) "
+            f"M={rows} (of {M}) K2={K2} D={D}")
+    return (lambda: oracle.attention(et, q, k, v, scale, k2_tile=128)), 4.0 * heads * rows * K2 * D, desc
 
 
-def cpu_baseline(et, threads):
+def cpu_baseline(workload, threads):
     """The oracle port (oracle/oracle.c, OpenMP) timed on this box's host cores."""
-    import oracle
-    rows, N, K = 1024, 4096, 4096
-    lhs, rhs = cpu_sample(et, rows, N, K)
-    oracle.matmul(et, lhs[:64], rhs)  # warm the thread pool
+    fn, flop, desc = cpu_work(workload, rows=1024)
+    fn()  # warm the thread pool / page in
     t0 = time.perf_counter()
-    oracle.matmul(et, lhs, rhs)
+    fn()
     dt = time.perf_counter() - t0
-    return {"value": 2.0 * rows * N * K / dt / 1e12, "unit": "TFLOP/s", "cores": threads,
-            "kind": "port",
-            "sample": f"oracle matmul {et} M={rows} N={N} K={K} (first {rows} rows of "
-                      f"BASELINE configs[0] 4096^3), 1 run, {dt:.2f} s"}
+    return {"value": flop / dt / 1e12, "unit": "TFLOP/s", "cores": threads, "kind": "port",
+            "sample": f"{desc}, 1 run, {dt:.2f} s"}
 
 
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    import oracle
-    op, et, batch, M, N, K = MATMUL_WORKLOADS[args.workload]
     threads = os.cpu_count() or 1
-    rows = 256
-    lhs, rhs = cpu_sample(et, rows, N, K)
-    for _ in range(args.warmup):
-        oracle.matmul(et, lhs[:32], rhs)
+    fn, flop, desc = cpu_work(args.workload, rows=256)
+    for _ in range(max(1, min(args.warmup, 2))):
+        fn()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        oracle.matmul(et, lhs, rhs)
+        fn()
     dt = (time.perf_counter() - t0) / args.steps
-    value = 2.0 * rows * N * K / dt / 1e12
-    sample = (f"oracle port of the reference loops (iree-e2e-matmul-test.cc:28-121), OpenMP, "
-              f"{et} M={rows} (of {M}) N={N} K={K} per step")
+    value = flop / dt / 1e12
+    spec = MATMUL_WORKLOADS.get(args.workload) or ATTENTION_WORKLOADS[args.workload]
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "TFLOP/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": et, "data": "synthetic",
-            "config": {"workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU",
-                       "sample": sample},
+            "vs_baseline": None, "dtype": spec[1], "data": "synthetic",
+            "config": {"workload": args.workload + " " + "x".join(str(x) for x in spec[2:]),
+                       "sample": desc + " per step"},
             "cpu_baseline": {"value": value, "unit": "TFLOP/s", "cores": threads, "kind": "port",
-                             "sample": sample},
+                             "sample": desc + " per step"},
             "e2e": {"value": value, "unit": "TFLOP/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -334,7 +442,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(MATMUL_WORKLOADS))
+    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)))
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
