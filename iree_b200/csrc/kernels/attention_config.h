@@ -24,7 +24,7 @@ struct AttnPrefillConfig {
   static constexpr int kChunkBytes = 128 * 128;    // [128 rows x 128 B]
   static constexpr int kTileBytes = kChunks * kChunkBytes;  // Q tile == K block == V block
   static constexpr int kSmemTiles = (kTilesPerCta + kKStages + kVStages) * kTileBytes;
-  static constexpr int kNumBarriers = 2 + 2 + 2 * kKStages + 2 * kVStages + 2 + 2 + 1;
+  static constexpr int kNumBarriers = 2 + 2 + 2 * kKStages + 2 * kVStages + 2 + 4 + 1;
   static constexpr int kSmemBytes = 1024 + kSmemTiles + kNumBarriers * 8 + 16;
   static constexpr int kThreads = 384;  // warps 0-3: TMA / MMA / TMEM alloc / spare; 4-11 softmax
   static constexpr int kTmemCols = 512;  // S0 | S1 | O0 | O1, 128 f32 columns each

@@ -64,6 +64,12 @@ B200_DEVICE uint32_t pack2(float lo, float hi) {
   return r;
 }
 
+B200_DEVICE float max3(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
+
 B200_DEVICE float fast_exp2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -108,8 +114,8 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
   const uint32_t bar_v_full = bar_k_empty + 8 * Cfg::kKStages;
   const uint32_t bar_v_empty = bar_v_full + 8 * Cfg::kVStages;
   const uint32_t bar_s_full = bar_v_empty + 8 * Cfg::kVStages;  // [2] MMA -> softmax
-  const uint32_t bar_p_full = bar_s_full + 16;                  // [2] softmax -> MMA
-  const uint32_t bar_o_done = bar_p_full + 16;                  // [1] MMA -> epilogue
+  const uint32_t bar_p_full = bar_s_full + 16;                  // [2 tiles][2 halves] softmax -> MMA
+  const uint32_t bar_o_done = bar_p_full + 32;                  // [1] MMA -> epilogue
   const uint32_t tmem_slot = bar_o_done + 8;
 
   const uint32_t warp = threadIdx.x >> 5;
@@ -128,7 +134,8 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
       mbar_init(bar_q_full + 8 * t, 1);
       mbar_init(bar_q_scaled + 8 * t, 4);  // one arrive per softmax warp
       mbar_init(bar_s_full + 8 * t, 1);
-      mbar_init(bar_p_full + 8 * t, 4);
+      mbar_init(bar_p_full + 16 * t, 4);
+      mbar_init(bar_p_full + 16 * t + 8, 4);
     }
     for (int s = 0; s < Cfg::kKStages; ++s) {
       mbar_init(bar_k_full + 8 * s, 1);
@@ -149,6 +156,9 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
   tcgen05_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
+  // Register reallocation: the softmax warpgroups hold a whole 128-column S row per thread.
+  // (setmaxnreg sits at the top of each role branch so ptxas sees one limit per region.)
+  if (warp < 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 56;");
   if (warp == 0) {
     //===------------------------------------------------------------------===//
     // TMA producer
@@ -193,23 +203,34 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     //===------------------------------------------------------------------===//
     if (elect_one()) {
       // S_t (128 f32 columns) at column t*128; O_t at 256 + t*128; P_t aliases S_t.
+      // Descriptors differ only in the start-address field (low word, 16-byte units), so
+      // each MMA's descriptor is base + immediate: nothing to keep live across the loop.
+      const uint64_t desc_kmajor = make_smem_desc_sw128(0, 16, 1024);
+      // V: 16 K2 rows per step = 16 * 128 B inside each 64-column slab; slabs (N blocks) are
+      // kChunkBytes apart, 8-row groups 1024 B apart.
+      const uint64_t desc_v = make_smem_desc_sw128(0, Cfg::kChunkBytes, 1024);
+      // The empty asm makes the bases opaque per call, so the compiler re-derives the
+      // per-MMA operands with immediate adds instead of hoisting ~60 loop invariants out of
+      // the K2 loop and spilling them (this thread runs with 56 registers: 168*384 allocated at launch = 56*128 + 224*256).
       auto issue_s = [&](int t, uint32_t k_addr) {
-        const uint32_t q_addr = smem_q + t * Cfg::kTileBytes;
+        uint32_t tb = tmem_base, qa = smem_q;
+        asm volatile("" : "+r"(tb), "+r"(qa), "+r"(k_addr));
+        const uint64_t da0 = desc_kmajor + ((qa + t * Cfg::kTileBytes) >> 4);
+        const uint64_t db0 = desc_kmajor + (k_addr >> 4);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
-          const uint32_t off = (kk / 4) * Cfg::kChunkBytes + (kk % 4) * 32;
-          const uint64_t da = make_smem_desc_sw128(q_addr + off, 16, 1024);
-          const uint64_t db = make_smem_desc_sw128(k_addr + off, 16, 1024);
-          umma_ss<1, KIND_F16>(tmem_base + t * BN, da, db, kIdescS, kk != 0);
+          const uint32_t off = ((kk / 4) * Cfg::kChunkBytes + (kk % 4) * 32) >> 4;
+          umma_ss<1, KIND_F16>(tb + t * BN, da0 + off, db0 + off, kIdescS, kk != 0);
         }
       };
-      auto issue_pv = [&](int t, uint32_t v_addr, bool accumulate) {
+      auto issue_pv = [&](int t, uint32_t v_addr, bool accumulate, int half) {
+        uint32_t tb = tmem_base;
+        asm volatile("" : "+r"(tb), "+r"(v_addr));
+        const uint64_t db0 = desc_v + (v_addr >> 4);
 #pragma unroll
-        for (int kk = 0; kk < BN / 16; ++kk) {
-          // 16 K2 rows per step = 16 * 128 B inside each 64-column slab; slabs (N blocks)
-          // are kChunkBytes apart, 8-row groups 1024 B apart.
-          const uint64_t db = make_smem_desc_sw128(v_addr + kk * 2048, Cfg::kChunkBytes, 1024);
-          umma_ts_f16<1>(tmem_base + 256 + t * D, tmem_base + t * BN + kk * 8, db, kIdescPV,
+        for (int kk = half * (BN / 32); kk < (half + 1) * (BN / 32); ++kk) {
+          umma_ts_f16<1>(tb + 256 + t * D, tb + t * BN + kk * 8,
+                         db0 + (uint32_t)(kk * (2048 >> 4)), kIdescPV,
                          (accumulate || kk != 0) ? 1u : 0u);
         }
       };
@@ -231,16 +252,22 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         mbar_wait(bar_v_full + 8 * vs, vphase);
         mbar_wait(bar_p_full, j & 1);
         tcgen05_fence_after();
-        issue_pv(0, v_addr, j != 0);
+        issue_pv(0, v_addr, j != 0, 0);
+        mbar_wait(bar_p_full + 8, j & 1);
+        tcgen05_fence_after();
+        issue_pv(0, v_addr, j != 0, 1);
         if (has_next) {
           mbar_wait(bar_k_full + 8 * ks, kphase);
           tcgen05_fence_after();
           issue_s(0, k_addr);
           umma_commit_1cta(bar_s_full);
         }
-        mbar_wait(bar_p_full + 8, j & 1);
+        mbar_wait(bar_p_full + 16, j & 1);
         tcgen05_fence_after();
-        issue_pv(1, v_addr, j != 0);
+        issue_pv(1, v_addr, j != 0, 0);
+        mbar_wait(bar_p_full + 24, j & 1);
+        tcgen05_fence_after();
+        issue_pv(1, v_addr, j != 0, 1);
         umma_commit_1cta(bar_v_empty + 8 * vs);
         if (has_next) {
           issue_s(1, k_addr);
@@ -262,6 +289,7 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     //===------------------------------------------------------------------===//
     // Softmax warpgroups: tile t = (warp - 4) / 4, one thread per row.
     //===------------------------------------------------------------------===//
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;");
     const int t = (int)(warp - 4) >> 2;
     const uint32_t quarter = warp & 3;                 // TMEM lane quarter of this warp
     const uint32_t wg_tid = (warp - 4 - 4 * t) * 32 + lane;  // 0..127 within the warpgroup
@@ -311,9 +339,22 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
           if (i >= valid) s[i] = 0xff800000u;  // -inf
         }
       }
-      float mx = __uint_as_float(s[0]);
+      // Row max: 8 independent chains of 3-input max (a single chain is 128 dependent ops).
+      float mxs[8];
 #pragma unroll
-      for (int i = 1; i < BN; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+      for (int a = 0; a < 8; ++a) mxs[a] = max3(__uint_as_float(s[a]), __uint_as_float(s[a + 8]),
+                                                __uint_as_float(s[a + 16]));
+#pragma unroll
+      for (int i = 24; i + 16 <= BN; i += 16) {
+#pragma unroll
+        for (int a = 0; a < 8; ++a) {
+          mxs[a] = max3(mxs[a], __uint_as_float(s[i + a]), __uint_as_float(s[i + a + 8]));
+        }
+      }
+#pragma unroll
+      for (int a = 0; a < 8; ++a) mxs[a] = fmaxf(mxs[a], __uint_as_float(s[BN - 8 + a]));
+      const float mx = fmaxf(max3(mxs[0], mxs[1], mxs[2]),
+                             max3(max3(mxs[3], mxs[4], mxs[5]), mxs[6], mxs[7]));
       const float m_new = fmaxf(m_run, mx);
       // Lazy rescale: keep the stale max while it is within 2^8 of the true one.
       const bool grow = (m_new - m_run) > 8.0f;
@@ -331,7 +372,10 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         }
       }
       if (grow) m_run = m_new;
-      float sum = 0.f;
+      // P in two halves of 64 K2 columns: the MMA warp starts P.V on the first half while
+      // the second is still on the MUFU (one barrier per half: a waiter may not fall two
+      // phases behind on one mbarrier).
+      float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
       for (int c = 0; c < BN / 32; ++c) {
         uint32_t p[16];
@@ -339,16 +383,19 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         for (int i = 0; i < 16; ++i) {
           const float p0 = fast_exp2(__uint_as_float(s[c * 32 + 2 * i]) - m_run);
           const float p1 = fast_exp2(__uint_as_float(s[c * 32 + 2 * i + 1]) - m_run);
-          sum += p0 + p1;  // f32 P summed before the truncation (:598-601)
+          sum0 += p0;  // f32 P summed before the truncation (:598-601)
+          sum1 += p1;
           p[i] = pack2<kBf16>(p0, p1);
         }
         tmem_st_32x32b_x16(tmem_s + c * 16, p);
+        if (c & 1) {
+          tmem_wait_st();
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_p_full + 16 * t + 8 * (c >> 1));
+        }
       }
-      l_run += sum;
-      tmem_wait_st();
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_p_full + 8 * t);
+      l_run += sum0 + sum1;
     }
 
     // ---- epilogue: O = cast((1/sum) * acc) ----
