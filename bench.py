@@ -264,6 +264,91 @@ class AttentionStep:
                 "api": "iree_b200_ops_attention_host (pinned host buffers)"}
 
 
+class TpLayerStep:
+    """BASELINE configs[4]: the GEMMs of one Llama-3-8B decoder layer (hidden 4096, 32 q / 8 kv
+    heads x 128, FFN 14336; tokens = 8192), tensor-parallel over the ranks (Megatron split):
+    QKV and gate/up column-parallel, O and down row-parallel followed by an all-reduce(sum) of
+    the [tokens, 4096] bf16 activation through iree_hal_channel (NCCL over NVLink). The
+    row-parallel GEMMs are recorded in token chunks so that, with the device's collective
+    stream, the all-reduce of chunk c overlaps the GEMM of chunk c+1. All GEMMs use the
+    truncating epilogue (bf16 activations)."""
+
+    TOKENS, HIDDEN, QKV, FFN, CHUNKS = 8192, 4096, 6144, 14336, 4
+
+    def __init__(self, torch, hal, dev, ops, world, rank, channel, seed):
+        T, H, QKV, FFN = self.TOKENS, self.HIDDEN, self.QKV, self.FFN
+        assert QKV % world == 0 and H % world == 0 and FFN % world == 0
+        g = torch.Generator(device="cuda")
+        g.manual_seed(0xB200 + seed)
+        mk = lambda *shape: (torch.randn(shape, device="cuda", generator=g) * 0.05).to(torch.bfloat16)
+        out = lambda *shape: torch.empty(shape, dtype=torch.bfloat16, device="cuda")
+        self.t = {
+            "x": mk(T, H), "wqkv": mk(H, QKV // world), "qkv": out(T, QKV // world),
+            "attn": mk(T, H // world), "wo": mk(H // world, H), "o": out(T, H),
+            "wgu": mk(H, 2 * FFN // world), "gu": out(T, 2 * FFN // world),
+            "act": mk(T, FFN // world), "wd": mk(FFN // world, H), "d": out(T, H),
+        }
+        self.b = {k: dev.import_buffer(v.data_ptr(), v.numel() * 2) for k, v in self.t.items()}
+        self.world, self.dev = world, dev
+        self.flop = 2.0 * T * (H * QKV + H * H + H * 2 * FFN + FFN * H) / world
+        trunc = hal.MATMUL_TRUNCATE_RESULT
+        ar = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, "bf16")
+        before = ops.dispatch_count
+        cb = hal.CommandBuffer(dev).begin()
+        b = self.b
+        ops.record_matmul(cb, "bf16", 1, T, QKV // world, H, b["x"].ref(), b["wqkv"].ref(),
+                          b["qkv"].ref(), flags=trunc)
+        self.collectives = 0
+
+        def row_parallel(lhs, k_local, rhs, dst):
+            rows = T // self.CHUNKS
+            for c in range(self.CHUNKS):
+                ops.record_matmul(cb, "bf16", 1, rows, H, k_local,
+                                  b[lhs].ref(c * rows * k_local * 2, rows * k_local * 2),
+                                  b[rhs].ref(), b[dst].ref(c * rows * H * 2, rows * H * 2),
+                                  flags=trunc)
+                if world > 1:
+                    ref = b[dst].ref(c * rows * H * 2, rows * H * 2)
+                    cb.collective(channel, ar, 0, ref, ref, rows * H)
+                    self.collectives += 1
+            cb.barrier()
+
+        row_parallel("attn", H // world, "wo", "o")
+        ops.record_matmul(cb, "bf16", 1, T, 2 * FFN // world, H, b["o"].ref(), b["wgu"].ref(),
+                          b["gu"].ref(), flags=trunc)
+        row_parallel("act", FFN // world, "wd", "d")
+        cb.end()
+        self.cb = cb
+        self.launches_per_step = ops.dispatch_count - before
+
+    def step(self):
+        self.dev.execute(self.cb)
+
+    def host_buffers(self, torch):
+        x = torch.empty(self.t["x"].shape, dtype=torch.bfloat16).pin_memory()
+        x.copy_(self.t["x"])
+        return [x, torch.empty(self.t["d"].shape, dtype=torch.bfloat16).pin_memory()]
+
+    def host_call(self, ops, host):
+        n = host[0].numel() * 2
+        self.dev.h2d(host[0].data_ptr(), self.b["x"], n)
+        self.dev.execute(self.cb)
+        self.dev.d2h(self.b["d"], host[1].data_ptr(), n)
+        self.dev.wait_idle()
+
+    def describe(self):
+        T, H, QKV, FFN, w = self.TOKENS, self.HIDDEN, self.QKV, self.FFN, self.world
+        weights = 2.0 * (H * QKV + H * H + H * 2 * FFN + FFN * H) / w
+        acts = 2.0 * T * (H + QKV / w + H / w + H + H + 2 * FFN / w + FFN / w + H)
+        return {"flop": self.flop, "bytes": weights + acts, "bound": "tensor",
+                "workload": f"Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens={T}, "
+                            f"bf16 -> bf16 (f32 accumulate), tensor-parallel over {w} GPU(s), "
+                            f"{self.collectives} all-reduce(sum, bf16, [{T // self.CHUNKS},{H}]) per "
+                            f"step via iree_hal_channel/NCCL, overlapped on the collective stream",
+                "dtype": "bf16 (f32 accumulate)", "h2d": int(T * H * 2), "d2h": int(T * H * 2),
+                "api": "h2d(x) + iree_b200_device_queue_execute(layer command buffer) + d2h(y)"}
+
+
 def make_step(torch, hal, dev, ops, workload, seed):
     if workload in MATMUL_WORKLOADS:
         return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed)
@@ -282,14 +367,27 @@ def run_ours(args):
     from iree_b200 import hal
 
     stream = torch.cuda.Stream()
-    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
+    tp = args.workload == "tp_decoder_layer"
+    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
+                     overlap_collectives=tp and world > 1)
     ops = hal.Ops(dev)
-    # Rotating input sets: the working set cycled through between timed steps exceeds L2.
-    first = make_step(torch, hal, dev, ops, args.workload, seed=rank)
-    info = first.describe()
-    sets = max(1, min(4, int(-(-2 * 126e6 // info["bytes"]))))
-    works = [first] + [make_step(torch, hal, dev, ops, args.workload, seed=rank + 100 * i)
-                       for i in range(1, sets)]
+    if tp:
+        channel = None
+        if world > 1:
+            import torch.distributed as dist
+            ids = [hal.Channel.create_id() if rank == 0 else None]
+            dist.broadcast_object_list(ids, src=0)
+            channel = hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
+        first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank)
+        info = first.describe()
+        sets, works = 1, [first]
+    else:
+        # Rotating input sets: the working set cycled through between timed steps exceeds L2.
+        first = make_step(torch, hal, dev, ops, args.workload, seed=rank)
+        info = first.describe()
+        sets = max(1, min(4, int(-(-2 * 126e6 // info["bytes"]))))
+        works = [first] + [make_step(torch, hal, dev, ops, args.workload, seed=rank + 100 * i)
+                           for i in range(1, sets)]
     flop, nbytes = info["flop"], info["bytes"]
 
     # ---- device-resident timing (CUDA events on the dispatch stream) ----
@@ -311,6 +409,9 @@ def run_ours(args):
     ms_per_step = ms_total / args.steps
     value = flop * world / (ms_per_step * 1e-3) / 1e12
     launches = first.launches_per_step * args.steps
+    if tp:
+        # Strong scaling: |flop| is this rank's share of the fixed layer.
+        value = flop * world / (ms_per_step * 1e-3) / 1e12
 
     # ---- end to end through the host-buffer C-ABI call ----
     host = first.host_buffers(torch)
@@ -351,11 +452,11 @@ def run_ours(args):
     line = {
         "metric": METRIC, "value": value, "unit": "TFLOP/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "higher_is_better": True, "scaling": "strong" if tp else "weak", "vs_baseline": None,
         "dtype": info["dtype"], "data": "synthetic",
         "config": {"workload": info["workload"]
                                + (f", batch-sharded over {world} GPUs (no collective)"
-                                  if world > 1 else ""),
+                                  if world > 1 and not tp else ""),
                    "l2": "%d rotating input sets of %.0f MiB each (> 126 MB L2 between reuses); "
                          "no flush" % (sets, nbytes / 2**20),
                    "launch": "stream command buffer replay, %d dispatch(es) per step"
@@ -375,8 +476,10 @@ def cpu_work(workload, rows):
     reference generator (test_utils.c:359-420) / a seeded PCG as in the parity tests."""
     import numpy as np
     import oracle
-    if workload in MATMUL_WORKLOADS:
-        op, et, batch, M, N, K = MATMUL_WORKLOADS[workload]
+    if workload in MATMUL_WORKLOADS or workload == "tp_decoder_layer":
+        # The TP layer's CPU sample is its QKV projection (same loops, same dtype).
+        op, et, batch, M, N, K = MATMUL_WORKLOADS.get(
+            workload, ("matmul", "bf16", 1, TpLayerStep.TOKENS, TpLayerStep.QKV, TpLayerStep.HIDDEN))
         rows = min(rows, M)
         lhs = oracle.generate_random_matrix(et, (rows, K), 1)
         rhs = oracle.generate_random_matrix(et, (K, N), 2)
@@ -420,7 +523,8 @@ def run_reference(args):
         fn()
     dt = (time.perf_counter() - t0) / args.steps
     value = flop / dt / 1e12
-    spec = MATMUL_WORKLOADS.get(args.workload) or ATTENTION_WORKLOADS[args.workload]
+    spec = (MATMUL_WORKLOADS.get(args.workload) or ATTENTION_WORKLOADS.get(args.workload) or
+            ("matmul", "bf16", 1, TpLayerStep.TOKENS, TpLayerStep.QKV, TpLayerStep.HIDDEN))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "TFLOP/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
@@ -442,7 +546,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)))
+    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)) + ["tp_decoder_layer"])
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

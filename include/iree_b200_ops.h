@@ -40,6 +40,9 @@ enum {
 enum {
   IREE_B200_MATMUL_FLAG_ACCUMULATE = 1u << 0,     // out = out + lhs·rhs (linalg outs operand)
   IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS = 1u << 1,  // rhs is [N, K] (generate_code.py:172-174)
+  // The dispatch also holds the consumer arith.truncf: out has the operands' element type
+  // (f16 / bf16 only, round to nearest even; not combinable with ACCUMULATE).
+  IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT = 1u << 2,
   // Diagnostics: force a kernel family regardless of the shape heuristics.
   IREE_B200_MATMUL_FLAG_FORCE_GENERIC = 1u << 8,
   IREE_B200_MATMUL_FLAG_FORCE_1CTA = 1u << 9,
@@ -89,8 +92,8 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul(
     int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out);
 
-// Host-buffer form. |out| holds batch*M*N f32 / i32 values; with FLAG_ACCUMULATE it is
-// also the accumulator input.
+// Host-buffer form. |out| holds batch*M*N f32 / i32 values (operand-type values with
+// FLAG_TRUNCATE_RESULT); with FLAG_ACCUMULATE it is also the accumulator input.
 IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops,
                                                            int32_t element_type, int64_t batch,
                                                            int64_t M, int64_t N, int64_t K,

@@ -34,8 +34,12 @@ B200_HOST_DEVICE constexpr uint32_t make_idesc(uint32_t c_fmt, uint32_t a_fmt, u
          ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
-template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_>
+// kOut16: the epilogue truncates the f32 accumulator to the operand type (the fused
+// `linalg.matmul + arith.truncf` dispatch), halving the C traffic.
+template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_,
+          bool kOut16_ = false>
 struct GemmConfig {
+  static constexpr bool kOut16 = kOut16_;
   static constexpr int kCtaGroup = kCtaGroup_;
   static constexpr int kKind = kKind_;
   static constexpr uint32_t kAbFmt = kAbFmt_;
@@ -62,8 +66,8 @@ struct GemmConfig {
 
   static constexpr int kAccStages = 2;
   static constexpr int kTmemCols = kAccStages * kTileN;  // 512
-  static constexpr int kEpiCols = 32;                    // columns per epilogue chunk
-  static constexpr int kEpiBytes = kBlockM * kEpiCols * 4;  // 16 KiB
+  static constexpr int kEpiCols = kOut16 ? 64 : 32;      // columns per epilogue chunk (128 B rows)
+  static constexpr int kEpiBytes = kBlockM * 128;        // 16 KiB
   static constexpr int kEpiBufs = 2;
 
   static constexpr int kSmemTiles = kStages * kStageBytes + kEpiBufs * kEpiBytes;

@@ -37,6 +37,18 @@
 
 namespace b200 {
 
+// Two f32 -> one register of two 16-bit elements (lo = first), round to nearest even.
+template <bool kBf16>
+B200_DEVICE uint32_t pack_pair(float lo, float hi) {
+  uint32_t r;
+  if constexpr (kBf16) {
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  } else {
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  }
+  return r;
+}
+
 struct TileCoord {
   int batch, m_blk, n_blk;
 };
@@ -232,8 +244,26 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         if (epi_leader) tma_store_wait_read<Cfg::kEpiBufs - 1>();
         named_barrier_sync(1, 128);
         uint32_t v[32];
-        tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols, v);
-        tmem_wait_ld();
+        if constexpr (Cfg::kOut16) {
+          // 64 accumulator columns -> 32 packed 16-bit pairs (round to nearest even).
+          uint32_t hi[32];
+          tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols, v);
+          tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols + 32, hi);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[i] = pack_pair<Cfg::kAbFmt == FMT_BF16>(__uint_as_float(v[2 * i]),
+                                                       __uint_as_float(v[2 * i + 1]));
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            v[16 + i] = pack_pair<Cfg::kAbFmt == FMT_BF16>(__uint_as_float(hi[2 * i]),
+                                                            __uint_as_float(hi[2 * i + 1]));
+          }
+        } else {
+          tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols, v);
+          tmem_wait_ld();
+        }
         if (c == Cfg::kTileN / Cfg::kEpiCols - 1) {
           // Whole accumulator stage has been read out: hand it back to the MMA warp.
           tcgen05_fence_before();
@@ -246,7 +276,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
             }
           }
         }
-        if (accumulate) {
+        if (accumulate && !Cfg::kOut16) {
           const int gm = m0 + (int)row;
           const int gn = n0 + c * Cfg::kEpiCols;
           if (gm < M) {
@@ -351,8 +381,9 @@ constexpr iree_b200_tma_recipe_t make_gemm_recipe() {
   r.maps[1].swizzle = IREE_B200_TMA_SWIZZLE_128B;
   // C [batch, M, N] (32-bit elements)
   r.maps[2].binding = 2;
-  r.maps[2].elem_type = Cfg::kKind == KIND_I8 ? IREE_B200_TMA_I32 : IREE_B200_TMA_F32;
-  r.maps[2].elem_size = 4;
+  r.maps[2].elem_type = Cfg::kOut16 ? ab_type
+                                    : (Cfg::kKind == KIND_I8 ? IREE_B200_TMA_I32 : IREE_B200_TMA_F32);
+  r.maps[2].elem_size = Cfg::kOut16 ? 2 : 4;
   r.maps[2].rank = 3;
   r.maps[2].dim[0] = IREE_B200_TMA_DIM_CONST(1);
   r.maps[2].dim[1] = IREE_B200_TMA_DIM_CONST(0);

@@ -12,7 +12,8 @@
 //
 // ABI (kernels.cu:7-34): bindings lhs [batch,M,K], rhs [batch,K,N] (or [batch,N,K] when
 // flags bit 1 is set), out [batch,M,N]; constants M, N, K, batch, flags
-// (bit 0: accumulate into out; bit 1: transpose_rhs). workgroup_size = [256,1,1],
+// (bit 0: accumulate into out; bit 1: transpose_rhs; bit 2: truncate the result to the
+// operand type, f16/bf16 only). workgroup_size = [256,1,1],
 // workgroup count = [ceil(N/64), ceil(M/64), batch].
 
 #include <cuda_bf16.h>
@@ -27,6 +28,11 @@ constexpr int kTileK = 16;
 __device__ __forceinline__ float to_acc(__nv_bfloat16 v) { return __bfloat162float(v); }
 __device__ __forceinline__ float to_acc(__half v) { return __half2float(v); }
 __device__ __forceinline__ int32_t to_acc(int8_t v) { return (int32_t)v; }
+template <typename T> __device__ __forceinline__ T from_acc(float v);
+template <> __device__ __forceinline__ __nv_bfloat16 from_acc<__nv_bfloat16>(float v) {
+  return __float2bfloat16_rn(v);
+}
+template <> __device__ __forceinline__ __half from_acc<__half>(float v) { return __float2half_rn(v); }
 
 template <typename TIn, typename TAcc>
 __device__ __forceinline__ void matmul_generic_body(const TIn* __restrict__ lhs,
@@ -104,6 +110,13 @@ __device__ __forceinline__ void matmul_generic_body(const TIn* __restrict__ lhs,
     for (int j = 0; j < 4; ++j) {
       const int gn = n0 + tx + 16 * j;
       if (gn >= N) continue;
+      if constexpr (sizeof(TIn) == 2) {
+        if (flags & 4) {  // fused arith.truncf: the result buffer holds operand-type elements
+          reinterpret_cast<TIn*>(out - (size_t)b * M * N)[((size_t)b * M + gm) * N + gn] =
+              from_acc<TIn>(acc[i][j]);
+          continue;
+        }
+      }
       out[(size_t)gm * N + gn] = acc[i][j];
     }
   }

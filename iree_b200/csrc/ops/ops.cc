@@ -20,6 +20,7 @@ namespace {
 enum MatmulFamily { kFamily2Cta = 0, kFamily1Cta = 1, kFamilyGeneric = 2, kFamilyCount = 3 };
 
 const char* const kTypeSuffix[3] = {"i8_i32", "f16_f32", "bf16_f32"};
+const char* const kTruncSuffix[3] = {"", "f16_f16", "bf16_bf16"};
 
 enum AttentionExport { kAttnPrefill = 0, kAttnDecodeSplit = 1, kAttnDecodeMerge = 2, kAttnGeneric = 3 };
 
@@ -32,6 +33,7 @@ struct iree_b200_ops_t {
   std::atomic<uint64_t> dispatch_count{0};
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[3][2][kFamilyCount];
+  int32_t matmul_trunc_exports[3][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
   int32_t attention_exports[4][8];
 };
 
@@ -86,6 +88,13 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
       ops->matmul_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta");
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
+      const std::string tbase =
+          std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTruncSuffix[t];
+      ops->matmul_trunc_exports[t][nt][kFamily2Cta] = t ? lookup(ops->executable, tbase) : -1;
+      ops->matmul_trunc_exports[t][nt][kFamily1Cta] =
+          t ? lookup(ops->executable, tbase + "_1cta") : -1;
+      ops->matmul_trunc_exports[t][nt][kFamilyGeneric] =
+          t ? ops->matmul_exports[t][nt][kFamilyGeneric] : -1;
     }
   }
   for (int t = 0; t < 4; ++t) {
@@ -147,7 +156,14 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
                        (long long)M, (long long)N, (long long)K);
   }
   const bool transpose_rhs = (flags & IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS) != 0;
+  const bool truncate = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) != 0;
   const int64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const int64_t out_es = truncate ? 2 : 4;
+  if (truncate && (element_type == IREE_B200_ELEMENT_TYPE_I8 ||
+                   (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE))) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "TRUNCATE_RESULT applies to f16/bf16 without ACCUMULATE only");
+  }
   out_selection->constants[0] = (uint32_t)M;
   out_selection->constants[1] = (uint32_t)N;
   out_selection->constants[2] = (uint32_t)K;
@@ -157,7 +173,7 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
   if (batch == 0 || M == 0 || N == 0) return IREE_B200_STATUS_OK;  // empty result: no dispatch
 
   // Matcher guards of the TMA-fed kernels: 16-byte aligned bases and row pitches.
-  const bool tma_ok = alignment >= 16 && K > 0 && (K * es) % 16 == 0 && (N * 4) % 16 == 0 &&
+  const bool tma_ok = alignment >= 16 && K > 0 && (K * es) % 16 == 0 && (N * out_es) % 16 == 0 &&
                       (transpose_rhs || (N * es) % 16 == 0);
   const int sm_count = ops->device->sm_count;
   const int64_t tiles_2cta = ceil_div(M, 256) * ceil_div(N, 256) * batch;
@@ -180,7 +196,9 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
     // SM pairs only pay off once there are enough 256x256 tiles to occupy them.
     family = (M > 128 && tiles_2cta * 2 >= sm_count) ? kFamily2Cta : kFamily1Cta;
   }
-  const int32_t ordinal = ops->matmul_exports[element_type][transpose_rhs ? 1 : 0][family];
+  const int32_t ordinal =
+      (truncate ? ops->matmul_trunc_exports
+                : ops->matmul_exports)[element_type][transpose_rhs ? 1 : 0][family];
   if (ordinal < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND,
                        "the executable has no export for matmul type %d transpose_rhs %d family %d",
@@ -208,7 +226,7 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
       out_selection->workgroup_count[0] = (uint32_t)ceil_div(N, 64);
       out_selection->workgroup_count[1] = (uint32_t)ceil_div(M, 64);
       out_selection->workgroup_count[2] = (uint32_t)batch;
-      out_selection->constants[4] |= transpose_rhs ? 2u : 0u;
+      out_selection->constants[4] |= (transpose_rhs ? 2u : 0u) | (truncate ? 4u : 0u);
       break;
   }
   return IREE_B200_STATUS_OK;
@@ -231,8 +249,9 @@ iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_c
   const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
   // Binding extents must cover the operands (the HAL validation layer's job,
   // hal/command_buffer_validation.c).
+  const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const uint64_t need[3] = {(uint64_t)batch * M * K * es, (uint64_t)batch * K * N * es,
-                            (uint64_t)batch * M * N * 4};
+                            (uint64_t)batch * M * N * out_es};
   const iree_b200_buffer_ref_t refs[3] = {lhs, rhs, out};
   uint32_t alignment = 256;
   for (int i = 0; i < 3; ++i) {
@@ -270,8 +289,9 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad matmul type or shape");
   }
   const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const uint64_t bytes[3] = {(uint64_t)batch * M * K * es, (uint64_t)batch * K * N * es,
-                             (uint64_t)batch * M * N * 4};
+                             (uint64_t)batch * M * N * out_es};
   B200_REQUIRE_ARG((lhs || !bytes[0]) && (rhs || !bytes[1]) && (out || !bytes[2]));
   iree_b200_device_t* device = ops->device;
   iree_b200_buffer_t* buffers[3] = {nullptr, nullptr, nullptr};
@@ -293,7 +313,7 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
       // Empty reduction: the linalg.fill 0 that seeds the accumulator is the result.
       const uint32_t zero = 0;
       B200_RETURN_IF_ERROR(iree_b200_command_buffer_fill_buffer(
-          cb, iree_b200_buffer_ref_t{buffers[2], 0, bytes[2]}, &zero, 4));
+          cb, iree_b200_buffer_ref_t{buffers[2], 0, bytes[2]}, &zero, out_es == 2 ? 2 : 4));
     } else if (K > 0) {
       B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
           ops, cb, element_type, batch, M, N, K, flags,

@@ -23,6 +23,7 @@ ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32}
 
 MATMUL_ACCUMULATE = 1 << 0
 MATMUL_TRANSPOSE_RHS = 1 << 1
+MATMUL_TRUNCATE_RESULT = 1 << 2
 MATMUL_FORCE_GENERIC = 1 << 8
 MATMUL_FORCE_1CTA = 1 << 9
 MATMUL_FORCE_2CTA = 1 << 10

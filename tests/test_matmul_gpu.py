@@ -161,3 +161,34 @@ def test_full_size_sampled_like_the_reference(ops, t):
     b = rhs.astype(np.float64) if t == "i8" else oracle.to_f32(t, rhs).astype(np.float64)
     assert np.array_equal(out.astype(np.float64).sum(axis=0), a.sum(axis=0) @ b)
     assert np.array_equal(out.astype(np.float64).sum(axis=1), a @ b.sum(axis=1))
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("family", ["1cta", "2cta", "generic"])
+@pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
+@pytest.mark.parametrize("shape", [(256, 64, 256), (130, 72, 264), (1000, 520, 264),
+                                   (384, 1024, 768)], ids=str)
+def test_truncating_epilogue(ops, t, family, nt, shape):
+    """matmul + arith.truncf in one dispatch: out = round_T(f32 accumulate), bit-exact for the
+    reference generator's inputs (the f32 result is exact, so one rounding on both sides)."""
+    M, K, N = shape
+    flag = {"1cta": H.MATMUL_FORCE_1CTA, "2cta": H.MATMUL_FORCE_2CTA,
+            "generic": H.MATMUL_FORCE_GENERIC}[family]
+    lhs = oracle.generate_random_matrix(t, (1, M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (1, N, K) if nt else (1, K, N), 2)
+    out = np.full((1, M, N), 0x7777, dtype=np.uint16)
+    f = flag | H.MATMUL_TRUNCATE_RESULT | (H.MATMUL_TRANSPOSE_RHS if nt else 0)
+    ops.matmul_host(t, 1, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data, f)
+    want = oracle.from_f32(t, oracle.matmul(t, lhs, rhs, transpose_rhs=nt))
+    assert np.array_equal(out, want)
+
+
+def test_truncating_epilogue_guards(ops):
+    with pytest.raises(H.Status):
+        ops.select_matmul("i8", 1, 256, 256, 256, flags=H.MATMUL_TRUNCATE_RESULT)
+    with pytest.raises(H.Status):
+        ops.select_matmul("bf16", 1, 256, 256, 256,
+                          flags=H.MATMUL_TRUNCATE_RESULT | H.MATMUL_ACCUMULATE)
+    exe = ops.executable
+    s = ops.select_matmul("bf16", 1, 8192, 4096, 4096, flags=H.MATMUL_TRUNCATE_RESULT)
+    assert exe.export_info(s["export_ordinal"])["kernel_name"] == "iree_b200_matmul_bf16_bf16"
