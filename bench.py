@@ -378,6 +378,9 @@ def run_ours(args):
             ids = [hal.Channel.create_id() if rank == 0 else None]
             dist.broadcast_object_list(ids, src=0)
             channel = hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
+        if world > 1:
+            ops.set_reserved_sms(args.reserved_sms)
+        TpLayerStep.CHUNKS = args.tp_chunks
         first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank)
         info = first.describe()
         sets, works = 1, [first]
@@ -466,6 +469,10 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.workload, threads=os.cpu_count() or 1)
     print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 def cpu_work(workload, rows):
@@ -549,6 +556,10 @@ def main():
     ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)) + ["tp_decoder_layer"])
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--reserved-sms", type=int, default=16,
+                    help="tp_decoder_layer, N>1: SMs the GEMM grids leave to the NCCL kernels")
+    ap.add_argument("--tp-chunks", type=int, default=4,
+                    help="tp_decoder_layer: token chunks per row-parallel GEMM + all-reduce")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     _, world, _ = dist_env()

@@ -64,6 +64,13 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device
 IREE_B200_API void iree_b200_ops_release(iree_b200_ops_t* ops);
 IREE_B200_API iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* ops);
 
+// Caps the grid of the persistent GEMM kernels at (SM count - |reserved_sms|) so that
+// concurrently running collective kernels (NCCL on the device's collective stream) find
+// free SMs; the persistent kernels otherwise own every SM (1 CTA/SM at 227 KB of shared
+// memory) and the collective could only start when they retire. 0 restores the default.
+IREE_B200_API iree_b200_status_t iree_b200_ops_set_reserved_sms(iree_b200_ops_t* ops,
+                                                                int32_t reserved_sms);
+
 // Number of dispatches recorded through this object since creation (each is one kernel
 // launch when the command buffer executes).
 IREE_B200_API uint64_t iree_b200_ops_dispatch_count(const iree_b200_ops_t* ops);

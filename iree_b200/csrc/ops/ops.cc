@@ -31,6 +31,7 @@ struct iree_b200_ops_t {
   iree_b200_executable_cache_t* cache = nullptr;
   iree_b200_executable_t* executable = nullptr;
   std::atomic<uint64_t> dispatch_count{0};
+  int32_t reserved_sms = 0;
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[3][2][kFamilyCount];
   int32_t matmul_trunc_exports[3][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
@@ -135,6 +136,16 @@ iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* ops) {
   return ops ? ops->executable : nullptr;
 }
 
+iree_b200_status_t iree_b200_ops_set_reserved_sms(iree_b200_ops_t* ops, int32_t reserved_sms) {
+  B200_REQUIRE_ARG(ops);
+  if (reserved_sms < 0 || reserved_sms >= ops->device->sm_count) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "reserved_sms %d out of range [0, %d)",
+                       reserved_sms, ops->device->sm_count);
+  }
+  ops->reserved_sms = reserved_sms;
+  return IREE_B200_STATUS_OK;
+}
+
 uint64_t iree_b200_ops_dispatch_count(const iree_b200_ops_t* ops) {
   return ops ? ops->dispatch_count.load() : 0;
 }
@@ -175,7 +186,7 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
   // Matcher guards of the TMA-fed kernels: 16-byte aligned bases and row pitches.
   const bool tma_ok = alignment >= 16 && K > 0 && (K * es) % 16 == 0 && (N * out_es) % 16 == 0 &&
                       (transpose_rhs || (N * es) % 16 == 0);
-  const int sm_count = ops->device->sm_count;
+  const int sm_count = std::max(2, ops->device->sm_count - ops->reserved_sms);
   const int64_t tiles_2cta = ceil_div(M, 256) * ceil_div(N, 256) * batch;
   const int64_t tiles_1cta = ceil_div(M, 128) * ceil_div(N, 256) * batch;
 

@@ -137,6 +137,7 @@ _STATUS_FUNCS = {
     "iree_b200_channel_split": [c_void_p, c_int32, c_int32, c_uint64, POINTER(c_void_p)],
     "iree_b200_ops_create": [c_void_p, POINTER(c_void_p)],
     "iree_b200_ops_create_from_data": [c_void_p, c_void_p, c_size_t, POINTER(c_void_p)],
+    "iree_b200_ops_set_reserved_sms": [c_void_p, c_int32],
     "iree_b200_ops_select_matmul": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                     c_uint32, c_uint32, POINTER(MatmulSelection)],
     "iree_b200_ops_record_matmul": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64,
@@ -510,6 +511,9 @@ class Ops:
     @property
     def dispatch_count(self) -> int:
         return lib().iree_b200_ops_dispatch_count(self._h)
+
+    def set_reserved_sms(self, reserved_sms: int):
+        check(lib().iree_b200_ops_set_reserved_sms(self._h, reserved_sms))
 
     def select_matmul(self, element_type, batch, M, N, K, flags=0, alignment=256) -> dict:
         sel = MatmulSelection()
