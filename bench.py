@@ -469,10 +469,6 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.workload, threads=os.cpu_count() or 1)
     print(json.dumps(line), flush=True)
-    if world > 1:
-        import torch.distributed as dist
-        dist.barrier()
-        dist.destroy_process_group()
 
 
 def cpu_work(workload, rows):
@@ -571,8 +567,15 @@ def main():
         raise SystemExit(subprocess.call(cmd))
     if args.impl == "reference":
         run_reference(args)
-    else:
+        return
+    try:
         run_ours(args)
+    finally:
+        # Every rank tears the process group down (rank 0 alone prints the line).
+        if world > 1:
+            import torch.distributed as dist
+            if dist.is_initialized():
+                dist.destroy_process_group()
 
 
 if __name__ == "__main__":
