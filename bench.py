@@ -276,8 +276,12 @@ class TpLayerStep:
     TOKENS, HIDDEN, QKV, FFN, CHUNKS = 8192, 4096, 6144, 14336, 4
 
     def __init__(self, torch, hal, dev, ops, world, rank, channel, seed):
+        from iree_b200 import sharding
         T, H, QKV, FFN = self.TOKENS, self.HIDDEN, self.QKV, self.FFN
-        assert QKV % world == 0 and H % world == 0 and FFN % world == 0
+        plan = {g.name: g for g in sharding.decoder_layer_plan(world, rank, tokens=T)}
+        assert (plan["qkv"].N, plan["o"].K, plan["gate_up"].N, plan["down"].K) == \
+            (QKV // world, H // world, 2 * FFN // world, FFN // world)
+        assert len(sharding.token_chunks(T, self.CHUNKS)) == self.CHUNKS and T % self.CHUNKS == 0
         g = torch.Generator(device="cuda")
         g.manual_seed(0xB200 + seed)
         mk = lambda *shape: (torch.randn(shape, device="cuda", generator=g) * 0.05).to(torch.bfloat16)

@@ -491,6 +491,14 @@ def default_rank_and_count():
     return r.value, c.value
 
 
+def exchange_default_id(rank: int, id_bytes: bytes) -> bytes:
+    """iree_hal_channel_provider_exchange_default_id without MPI: rank 0 publishes |id_bytes|
+    (file named by IREE_B200_CHANNEL_ID_FILE), every other rank receives them."""
+    buf = ctypes.create_string_buffer(id_bytes, CHANNEL_ID_SIZE)
+    check(lib().iree_b200_channel_provider_exchange_default_id(rank, buf))
+    return buf.raw
+
+
 class Ops:
     """The dense-contraction dispatches (include/iree_b200_ops.h)."""
 

@@ -1,0 +1,92 @@
+"""World-size-2 CPU (gloo) tests of the N>1 host logic: sharding arithmetic, the channel
+provider's rank discovery / id exchange, and that sharded execution + all-reduce reproduces
+the unsharded op (with the oracle standing in for the device kernels)."""
+
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle
+from iree_b200 import hal, sharding
+
+
+def test_contiguous_shard_covers_exactly():
+    for extent in (0, 1, 7, 64, 4097):
+        for world in (1, 2, 3, 8):
+            spans = [sharding.contiguous_shard(extent, world, r) for r in range(world)]
+            assert spans[0][0] == 0 and sum(l for _, l in spans) == extent
+            for (o0, l0), (o1, _) in zip(spans, spans[1:]):
+                assert o0 + l0 == o1
+    with pytest.raises(ValueError):
+        sharding.contiguous_shard(8, 2, 2)
+
+
+def test_decoder_layer_plan_llama3_8b():
+    total = 0.0
+    for rank in range(8):
+        plan = sharding.decoder_layer_plan(8, rank)
+        assert [(g.name, g.M, g.N, g.K, g.parallel) for g in plan] == [
+            ("qkv", 8192, 768, 4096, "column"), ("o", 8192, 4096, 512, "row"),
+            ("gate_up", 8192, 3584, 4096, "column"), ("down", 8192, 4096, 1792, "row")]
+        total += sum(g.flop for g in plan)
+    assert abs(total - 3573.4e9) / 3573.4e9 < 1e-4       # 3573.4 GFLOP per layer
+    with pytest.raises(ValueError):
+        sharding.decoder_layer_plan(5, 0)
+    assert sharding.token_chunks(8192, 4) == [(0, 2048), (2048, 2048), (4096, 2048), (6144, 2048)]
+
+
+def _worker(rank, world, port, tmp, results):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(world), IREE_B200_CHANNEL_ID_FILE=os.path.join(tmp, "id"))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # 1. default channel provider: rank/count from the launcher's environment.
+        assert hal.default_rank_and_count() == (rank, world)
+        # 2. id exchange without MPI: rank 0 publishes 128 bytes, the others receive them.
+        ident = bytes(range(128)) if rank == 0 else bytes(128)
+        assert hal.exchange_default_id(rank, ident) == bytes(range(128))
+        # 3. row-parallel GEMM + all_reduce(sum) == the full GEMM (oracle as the kernel).
+        M, N, K = 48, 40, 64
+        lhs = oracle.generate_random_matrix("bf16", (M, K), 1)
+        rhs = oracle.generate_random_matrix("bf16", (K, N), 2)
+        ko, kl = sharding.contiguous_shard(K, world, rank)
+        part = oracle.matmul("bf16", np.ascontiguousarray(lhs[:, ko:ko + kl]),
+                             np.ascontiguousarray(rhs[ko:ko + kl]))
+        t = torch.from_numpy(part.copy())
+        dist.all_reduce(t)
+        full = oracle.matmul("bf16", lhs, rhs)
+        assert np.array_equal(t.numpy(), full)            # exact: small-integer inputs
+        gathered = [torch.empty_like(torch.from_numpy(part)) for _ in range(world)]
+        dist.all_gather(gathered, torch.from_numpy(part.copy()))
+        assert np.array_equal(oracle.all_reduce_sum_f32(np.stack([g.numpy() for g in gathered])),
+                              full)
+        # 4. column-parallel GEMM + all_gather == the full GEMM.
+        no, nl = sharding.contiguous_shard(N, world, rank)
+        col = oracle.matmul("bf16", lhs, np.ascontiguousarray(rhs[:, no:no + nl]))
+        cols = [torch.empty((M, sharding.contiguous_shard(N, world, r)[1])) for r in range(world)]
+        dist.all_gather(cols, torch.from_numpy(col.copy()))
+        assert np.array_equal(np.concatenate([c.numpy() for c in cols], axis=1), full)
+        # 5. batch-sharded batch_matmul: slices are independent.
+        B = 5
+        a = oracle.generate_random_matrix("i8", (B, 8, 16), 3)
+        b = oracle.generate_random_matrix("i8", (B, 16, 8), 4)
+        bo, bl = sharding.contiguous_shard(B, world, rank)
+        mine = oracle.matmul("i8", a[bo:bo + bl], b[bo:bo + bl])
+        assert np.array_equal(mine, oracle.matmul("i8", a, b)[bo:bo + bl])
+        results[rank] = "ok"
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_gloo():
+    world = 2
+    with tempfile.TemporaryDirectory() as tmp, mp.Manager() as manager:
+        results = manager.dict()
+        port = 29600 + os.getpid() % 300
+        mp.spawn(_worker, args=(world, port, tmp, results), nprocs=world, join=True)
+        assert dict(results) == {0: "ok", 1: "ok"}
