@@ -219,3 +219,48 @@ def all_reduce_sum_f32(parts: np.ndarray) -> np.ndarray:
     lib().oracle_all_reduce_sum_f32(ctypes.c_int(parts.shape[0]),
                                     ctypes.c_int64(out.size), _ptr(parts), _ptr(out))
     return out
+
+
+# ----------------------------------------------------------------------------
+# oracle/_ref: the reference's own CPU micro-kernels (built by oracle/build_ref.sh)
+# ----------------------------------------------------------------------------
+
+_REF_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libiree_uk_ref.so")
+_ref_lib = None
+
+
+def ref_available() -> bool:
+    return os.path.exists(_REF_PATH)
+
+
+def ref_lib() -> ctypes.CDLL:
+    """oracle/_ref/libiree_uk_ref.so: iree_uk_{query_tile_sizes,pack,mmt4d,unpack} compiled
+    from /root/reference plus oracle/ref_glue.c. Built where /root/reference exists
+    (`make -C oracle ref`); the .so travels to the GPU box."""
+    global _ref_lib
+    if _ref_lib is None:
+        l = ctypes.CDLL(_REF_PATH)
+        l.oracle_ref_matmul.restype = ctypes.c_int
+        l.oracle_ref_matmul.argtypes = [ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
+                                        ctypes.c_int64, ctypes.c_void_p, ctypes.c_void_p,
+                                        ctypes.c_void_p, ctypes.c_int,
+                                        ctypes.POINTER(ctypes.c_int)]
+        l.oracle_ref_cpu_features.restype = ctypes.c_uint64
+        _ref_lib = l
+    return _ref_lib
+
+
+def ref_matmul(t, lhs: np.ndarray, rhs: np.ndarray, force_generic: bool = False,
+               return_tiles: bool = False):
+    """Row-major [M,K] x [K,N] through the reference ukernels (pack -> mmt4d -> unpack)."""
+    tid = type_id(t)
+    M, K = lhs.shape
+    N = rhs.shape[1]
+    lhs, rhs = np.ascontiguousarray(lhs), np.ascontiguousarray(rhs)
+    out = np.empty((M, N), dtype=np.int32 if t == "i8" else np.float32)
+    tiles = (ctypes.c_int * 3)()
+    rc = ref_lib().oracle_ref_matmul(tid, M, N, K, _ptr(lhs), _ptr(rhs), _ptr(out),
+                                     int(force_generic), tiles)
+    if rc != 0:
+        raise RuntimeError(f"oracle_ref_matmul failed for {t} {M}x{N}x{K}")
+    return (out, tuple(tiles)) if return_tiles else out

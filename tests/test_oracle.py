@@ -118,3 +118,35 @@ def test_attention_golden(case, form):
                                **kw)
     want = _tensor(case["expected"])
     np.testing.assert_allclose(oracle.to_f32(t, got), want, atol=case["atol"], rtol=0)
+
+
+# ---- the oracle against the REFERENCE's own CPU kernels (oracle/_ref, built from
+# ---- /root/reference by oracle/build_ref.sh; skipped where the library is absent)
+
+_needs_ref = pytest.mark.skipif(not oracle.ref_available(),
+                                reason="oracle/_ref/libiree_uk_ref.so not built (make -C oracle ref)")
+
+
+@_needs_ref
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("generic", [False, True], ids=["arch", "generic"])
+@pytest.mark.parametrize("shape", [(1, 1, 1), (9, 9, 9), (81, 19, 41), (457, 330, 512),
+                                   (513, 128, 55), (1000, 4, 512)], ids=str)
+def test_oracle_matches_reference_ukernels(t, generic, shape):
+    """iree_uk_pack -> iree_uk_mmt4d -> iree_uk_unpack (what llvm-cpu calls with data tiling +
+    ukernels) on the reference generator's inputs: bit-identical to the restated loops."""
+    M, K, N = shape
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    got = oracle.ref_matmul(t, lhs, rhs, force_generic=generic)
+    assert np.array_equal(got, oracle.matmul(t, lhs, rhs))
+
+
+@_needs_ref
+def test_oracle_matches_reference_ukernels_i8_full_range():
+    g = np.random.Generator(np.random.PCG64(0xB200))
+    lhs = g.integers(-128, 128, (200, 384), dtype=np.int8)
+    rhs = g.integers(-128, 128, (384, 136), dtype=np.int8)
+    for generic in (False, True):
+        assert np.array_equal(oracle.ref_matmul("i8", lhs, rhs, force_generic=generic),
+                              oracle.matmul("i8", lhs, rhs))
