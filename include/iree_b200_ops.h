@@ -71,6 +71,19 @@ IREE_B200_API iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* 
 IREE_B200_API iree_b200_status_t iree_b200_ops_set_reserved_sms(iree_b200_ops_t* ops,
                                                                 int32_t reserved_sms);
 
+// Tuning of the host-buffer calls (iree_b200_ops_matmul_host / _attention_host). Calls that
+// move at least |min_bytes| run as a pipeline: the result is cut into |block_m| x |block_n|
+// blocks (rounded to multiples of 256; batch entries are separate blocks), operand panels go
+// up on an upload stream in the order that enables blocks soonest, each block's dispatch
+// runs on the dispatch stream as soon as its panels have landed, and its result comes back
+// on a download stream while later panels are still going up (PCIe is full duplex). Below
+// |min_bytes|, or when the operands fail the TMA guards, the call is upload / dispatch /
+// download in sequence. Defaults: 16 MiB, 2048 x 2048. Results are identical either way.
+IREE_B200_API iree_b200_status_t iree_b200_ops_set_host_pipeline(iree_b200_ops_t* ops,
+                                                                 uint64_t min_bytes,
+                                                                 int32_t block_m,
+                                                                 int32_t block_n);
+
 // Number of dispatches recorded through this object since creation (each is one kernel
 // launch when the command buffer executes).
 IREE_B200_API uint64_t iree_b200_ops_dispatch_count(const iree_b200_ops_t* ops);

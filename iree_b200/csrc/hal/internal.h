@@ -81,6 +81,7 @@ iree_b200_status_t make_status(iree_b200_status_t code, const char* fmt, ...)
   X(cuMemcpyHtoDAsync)             \
   X(cuMemcpyDtoHAsync)             \
   X(cuMemcpyAsync)                 \
+  X(cuMemcpy2DAsync)               \
   X(cuMemsetD8Async)               \
   X(cuMemsetD16Async)              \
   X(cuMemsetD32Async)              \

@@ -2,6 +2,8 @@
 // the dense-contraction ops. See include/iree_b200_ops.h.
 
 #include <algorithm>
+#include <mutex>
+#include <vector>
 
 #include "../hal/internal.h"
 #include "../kernels/attention_config.h"
@@ -36,6 +38,13 @@ struct iree_b200_ops_t {
   int32_t matmul_exports[3][2][kFamilyCount];
   int32_t matmul_trunc_exports[3][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
   int32_t attention_exports[4][8];
+  // Host-buffer calls: staging arena, transfer streams and events (grow-only, reused).
+  std::mutex host_mutex;
+  uint64_t pipeline_min_bytes = 16ull << 20;
+  int32_t pipeline_block_m = 2048, pipeline_block_n = 2048;
+  iree_b200_buffer_t* arena = nullptr;
+  CUstream upload_stream = nullptr, download_stream = nullptr;
+  std::vector<CUevent> events;
 };
 
 namespace {
@@ -126,6 +135,17 @@ iree_b200_status_t iree_b200_ops_create(iree_b200_device_t* device, iree_b200_op
 
 void iree_b200_ops_release(iree_b200_ops_t* ops) {
   if (!ops) return;
+  if (ops->device && ops->device->cu_context) {
+    const CudaSymbols* cu = ops->device->cu;
+    cu->cuCtxSetCurrent(ops->device->cu_context);
+    for (CUstream s : {ops->upload_stream, ops->download_stream}) {
+      if (!s) continue;
+      cu->cuStreamSynchronize(s);
+      cu->cuStreamDestroy(s);
+    }
+    for (CUevent e : ops->events) cu->cuEventDestroy(e);
+  }
+  iree_b200_buffer_release(ops->arena);
   iree_b200_executable_release(ops->executable);
   iree_b200_executable_cache_release(ops->cache);
   iree_b200_device_release(ops->device);
@@ -143,6 +163,21 @@ iree_b200_status_t iree_b200_ops_set_reserved_sms(iree_b200_ops_t* ops, int32_t 
                        reserved_sms, ops->device->sm_count);
   }
   ops->reserved_sms = reserved_sms;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_set_host_pipeline(iree_b200_ops_t* ops, uint64_t min_bytes,
+                                                   int32_t block_m, int32_t block_n) {
+  B200_REQUIRE_ARG(ops);
+  if (block_m < 256 || block_n < 256 || block_m > (1 << 20) || block_n > (1 << 20)) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "host pipeline blocks must be within [256, 2^20] (got %d x %d)", block_m,
+                       block_n);
+  }
+  std::lock_guard<std::mutex> lock(ops->host_mutex);
+  ops->pipeline_min_bytes = min_bytes;
+  ops->pipeline_block_m = (block_m + 255) / 256 * 256;
+  ops->pipeline_block_n = (block_n + 255) / 256 * 256;
   return IREE_B200_STATUS_OK;
 }
 
@@ -291,6 +326,226 @@ iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_c
   return IREE_B200_STATUS_OK;
 }
 
+namespace {
+
+// Grow-only device staging for the host-buffer calls; caller holds ops->host_mutex.
+iree_b200_status_t reserve_arena(iree_b200_ops_t* ops, uint64_t bytes) {
+  if (ops->arena && ops->arena->byte_length >= bytes) return IREE_B200_STATUS_OK;
+  iree_b200_buffer_release(ops->arena);
+  ops->arena = nullptr;
+  return iree_b200_allocator_allocate_buffer(ops->device, IREE_B200_MEMORY_TYPE_DEVICE_LOCAL,
+                                             (bytes + (1ull << 20) - 1) >> 20 << 20, &ops->arena);
+}
+
+iree_b200_status_t ensure_transfer_streams(iree_b200_ops_t* ops) {
+  const CudaSymbols* cu = ops->device->cu;
+  B200_CU(cu, cuCtxSetCurrent(ops->device->cu_context));
+  if (!ops->upload_stream) B200_CU(cu, cuStreamCreate(&ops->upload_stream, CU_STREAM_NON_BLOCKING));
+  if (!ops->download_stream) {
+    B200_CU(cu, cuStreamCreate(&ops->download_stream, CU_STREAM_NON_BLOCKING));
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t event_at(iree_b200_ops_t* ops, size_t index, CUevent* out_event) {
+  const CudaSymbols* cu = ops->device->cu;
+  while (ops->events.size() <= index) {
+    CUevent e = nullptr;
+    B200_CU(cu, cuEventCreate(&e, CU_EVENT_DISABLE_TIMING));
+    ops->events.push_back(e);
+  }
+  *out_event = ops->events[index];
+  return IREE_B200_STATUS_OK;
+}
+
+// Strided host <-> dense device copy of |rows| x |width| bytes.
+iree_b200_status_t copy_2d(const CudaSymbols* cu, bool to_device, CUdeviceptr device, void* host,
+                           uint64_t host_pitch, uint64_t width, uint64_t rows, CUstream stream) {
+  if (!width || !rows) return IREE_B200_STATUS_OK;
+  if (host_pitch == width) {
+    if (to_device) {
+      B200_CU(cu, cuMemcpyHtoDAsync(device, host, width * rows, stream));
+    } else {
+      B200_CU(cu, cuMemcpyDtoHAsync(host, device, width * rows, stream));
+    }
+    return IREE_B200_STATUS_OK;
+  }
+  CUDA_MEMCPY2D p;
+  memset(&p, 0, sizeof(p));
+  if (to_device) {
+    p.srcMemoryType = CU_MEMORYTYPE_HOST;
+    p.srcHost = host;
+    p.srcPitch = host_pitch;
+    p.dstMemoryType = CU_MEMORYTYPE_DEVICE;
+    p.dstDevice = device;
+    p.dstPitch = width;
+  } else {
+    p.srcMemoryType = CU_MEMORYTYPE_DEVICE;
+    p.srcDevice = device;
+    p.srcPitch = width;
+    p.dstMemoryType = CU_MEMORYTYPE_HOST;
+    p.dstHost = host;
+    p.dstPitch = host_pitch;
+  }
+  p.WidthInBytes = width;
+  p.Height = rows;
+  B200_CU(cu, cuMemcpy2DAsync(&p, stream));
+  return IREE_B200_STATUS_OK;
+}
+
+// Upload / dispatch / download in sequence on the dispatch stream.
+iree_b200_status_t matmul_host_serial(iree_b200_ops_t* ops, int32_t element_type, int64_t batch,
+                                      int64_t M, int64_t N, int64_t K, uint32_t flags,
+                                      const uint64_t bytes[3], const void* lhs, const void* rhs,
+                                      void* out, std::vector<iree_b200_command_buffer_t*>* cbs) {
+  iree_b200_device_t* device = ops->device;
+  const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
+  const uint64_t off[3] = {0, (bytes[0] + 1023) / 1024 * 1024,
+                           (bytes[0] + 1023) / 1024 * 1024 + (bytes[1] + 1023) / 1024 * 1024};
+  B200_RETURN_IF_ERROR(reserve_arena(ops, off[2] + bytes[2] + 1024));
+  iree_b200_buffer_t* arena = ops->arena;
+  B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, lhs, arena, off[0], bytes[0]));
+  B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, rhs, arena, off[1], bytes[1]));
+  if (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) {
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, out, arena, off[2], bytes[2]));
+  }
+  iree_b200_command_buffer_t* cb = nullptr;
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+  cbs->push_back(cb);
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+  if (K == 0 && !(flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) && bytes[2]) {
+    // Empty reduction: the linalg.fill 0 that seeds the accumulator is the result.
+    const uint32_t zero = 0;
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_fill_buffer(
+        cb, iree_b200_buffer_ref_t{arena, off[2], bytes[2]}, &zero, out_es == 2 ? 2 : 4));
+  } else if (K > 0) {
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
+        ops, cb, element_type, batch, M, N, K, flags, iree_b200_buffer_ref_t{arena, off[0], bytes[0]},
+        iree_b200_buffer_ref_t{arena, off[1], bytes[1]},
+        iree_b200_buffer_ref_t{arena, off[2], bytes[2]}));
+  }
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+  B200_RETURN_IF_ERROR(
+      iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+  B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, arena, off[2], out, bytes[2]));
+  return iree_b200_device_wait_idle(device);
+}
+
+// The pipelined form (include/iree_b200_ops.h, iree_b200_ops_set_host_pipeline). Device
+// staging is dense per block so every block is an ordinary dense dispatch:
+//   A   [batch, M, K] as on the host; row panel (b, i) is contiguous
+//   B   per batch, column panels [K, nb_j] packed one after the other (2-D upload);
+//       with TRANSPOSE_RHS a panel is rows of [N, K] and already contiguous
+//   C   per batch and row panel, blocks [mb_i, nb_j] packed one after the other (2-D download)
+iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_type,
+                                         int64_t batch, int64_t M, int64_t N, int64_t K,
+                                         uint32_t flags, const uint64_t bytes[3], const void* lhs,
+                                         const void* rhs, void* out,
+                                         std::vector<iree_b200_command_buffer_t*>* cbs) {
+  iree_b200_device_t* device = ops->device;
+  const CudaSymbols* cu = device->cu;
+  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
+  const bool transpose_rhs = (flags & IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS) != 0;
+  const bool accumulate = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) != 0;
+  const int64_t mb = ops->pipeline_block_m, nb = ops->pipeline_block_n;
+  const int64_t P = ceil_div(M, mb), Q = ceil_div(N, nb);
+  const uint64_t off_a = 0;
+  const uint64_t off_b = (bytes[0] + 1023) / 1024 * 1024;
+  const uint64_t off_c = off_b + (bytes[1] + 1023) / 1024 * 1024;
+  B200_RETURN_IF_ERROR(reserve_arena(ops, off_c + bytes[2] + 1024));
+  B200_RETURN_IF_ERROR(ensure_transfer_streams(ops));
+  iree_b200_buffer_t* arena = ops->arena;
+  const CUdeviceptr base = arena->device_ptr;
+  const uint8_t* host_a = static_cast<const uint8_t*>(lhs);
+  const uint8_t* host_b = static_cast<const uint8_t*>(rhs);
+  uint8_t* host_c = static_cast<uint8_t*>(out);
+  size_t next_event = 0;
+  std::vector<CUevent> a_ready((size_t)P), b_ready((size_t)Q);
+
+  auto wait_on_dispatch_stream = [&](CUevent e) -> iree_b200_status_t {
+    std::lock_guard<std::mutex> lock(device->mutex);
+    B200_CU(cu, cuStreamWaitEvent(device->dispatch_stream, e, 0));
+    return IREE_B200_STATUS_OK;
+  };
+
+  for (int64_t b = 0; b < batch; ++b) {
+    const int64_t steps = std::max(P, Q);
+    for (int64_t s = 0; s < steps; ++s) {
+      if (s < P) {  // row panel s of A
+        const int64_t rows = std::min(mb, M - s * mb);
+        const uint64_t at = ((uint64_t)b * M + (uint64_t)s * mb) * K * es;
+        B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_a + at, const_cast<uint8_t*>(host_a) + at,
+                                     K * es, K * es, rows, ops->upload_stream));
+        B200_RETURN_IF_ERROR(event_at(ops, next_event++, &a_ready[s]));
+        B200_CU(cu, cuEventRecord(a_ready[s], ops->upload_stream));
+      }
+      if (s < Q) {  // column panel s of B
+        const int64_t cols = std::min(nb, N - s * nb);
+        const uint64_t batch_at = (uint64_t)b * K * N * es;
+        if (transpose_rhs) {
+          const uint64_t at = batch_at + (uint64_t)s * nb * K * es;
+          B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_b + at,
+                                       const_cast<uint8_t*>(host_b) + at, K * es, K * es, cols,
+                                       ops->upload_stream));
+        } else {
+          B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_b + batch_at + (uint64_t)K * s * nb * es,
+                                       const_cast<uint8_t*>(host_b) + batch_at + (uint64_t)s * nb * es,
+                                       N * es, cols * es, K, ops->upload_stream));
+        }
+        B200_RETURN_IF_ERROR(event_at(ops, next_event++, &b_ready[s]));
+        B200_CU(cu, cuEventRecord(b_ready[s], ops->upload_stream));
+      }
+      // Blocks enabled by this step: max(i, j) == s.
+      for (int64_t i = 0; i <= std::min(s, P - 1); ++i) {
+        for (int64_t j = 0; j <= std::min(s, Q - 1); ++j) {
+          if (std::max(i, j) != s) continue;
+          const int64_t rows = std::min(mb, M - i * mb), cols = std::min(nb, N - j * nb);
+          const uint64_t a_at = ((uint64_t)b * M + (uint64_t)i * mb) * K * es;
+          const uint64_t b_at = (uint64_t)b * K * N * es + (uint64_t)K * j * nb * es;
+          const uint64_t c_at =
+              ((uint64_t)b * M * N + (uint64_t)i * mb * N + (uint64_t)rows * j * nb) * out_es;
+          uint8_t* c_host = host_c + ((uint64_t)b * M * N + (uint64_t)i * mb * N + (uint64_t)j * nb) * out_es;
+          // The upload stream is in order (A_s, then B_s): the later panel's event covers both.
+          CUevent ready = (j == s) ? b_ready[j] : a_ready[i];
+          if (accumulate) {
+            B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_c + c_at, c_host, N * out_es,
+                                         cols * out_es, rows, ops->upload_stream));
+            B200_RETURN_IF_ERROR(event_at(ops, next_event++, &ready));
+            B200_CU(cu, cuEventRecord(ready, ops->upload_stream));
+          }
+          B200_RETURN_IF_ERROR(wait_on_dispatch_stream(ready));
+          iree_b200_command_buffer_t* cb = nullptr;
+          B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+          cbs->push_back(cb);
+          B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+          B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
+              ops, cb, element_type, 1, rows, cols, K, flags,
+              iree_b200_buffer_ref_t{arena, off_a + a_at, (uint64_t)rows * K * es},
+              iree_b200_buffer_ref_t{arena, off_b + b_at, (uint64_t)cols * K * es},
+              iree_b200_buffer_ref_t{arena, off_c + c_at, (uint64_t)rows * cols * out_es}));
+          B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+          B200_RETURN_IF_ERROR(
+              iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+          CUevent done = nullptr;
+          B200_RETURN_IF_ERROR(event_at(ops, next_event++, &done));
+          {
+            std::lock_guard<std::mutex> lock(device->mutex);
+            B200_CU(cu, cuEventRecord(done, device->dispatch_stream));
+          }
+          B200_CU(cu, cuStreamWaitEvent(ops->download_stream, done, 0));
+          B200_RETURN_IF_ERROR(copy_2d(cu, false, base + off_c + c_at, c_host, N * out_es,
+                                       cols * out_es, rows, ops->download_stream));
+        }
+      }
+    }
+  }
+  B200_CU(cu, cuStreamSynchronize(ops->download_stream));
+  return IREE_B200_STATUS_OK;
+}
+
+}  // namespace
+
 iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t element_type,
                                              int64_t batch, int64_t M, int64_t N, int64_t K,
                                              uint32_t flags, const void* lhs, const void* rhs,
@@ -305,44 +560,31 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
                              (uint64_t)batch * M * N * out_es};
   B200_REQUIRE_ARG((lhs || !bytes[0]) && (rhs || !bytes[1]) && (out || !bytes[2]));
   iree_b200_device_t* device = ops->device;
-  iree_b200_buffer_t* buffers[3] = {nullptr, nullptr, nullptr};
-  iree_b200_command_buffer_t* cb = nullptr;
-  iree_b200_status_t status = IREE_B200_STATUS_OK;
-  auto run = [&]() -> iree_b200_status_t {
-    for (int i = 0; i < 3; ++i) {
-      B200_RETURN_IF_ERROR(iree_b200_allocator_allocate_buffer(
-          device, IREE_B200_MEMORY_TYPE_DEVICE_LOCAL, bytes[i], &buffers[i]));
-    }
-    B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, lhs, buffers[0], 0, bytes[0]));
-    B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, rhs, buffers[1], 0, bytes[1]));
-    if (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) {
-      B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, out, buffers[2], 0, bytes[2]));
-    }
-    B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
-    B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
-    if (K == 0 && !(flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) && bytes[2]) {
-      // Empty reduction: the linalg.fill 0 that seeds the accumulator is the result.
-      const uint32_t zero = 0;
-      B200_RETURN_IF_ERROR(iree_b200_command_buffer_fill_buffer(
-          cb, iree_b200_buffer_ref_t{buffers[2], 0, bytes[2]}, &zero, out_es == 2 ? 2 : 4));
-    } else if (K > 0) {
-      B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
-          ops, cb, element_type, batch, M, N, K, flags,
-          iree_b200_buffer_ref_t{buffers[0], 0, bytes[0]},
-          iree_b200_buffer_ref_t{buffers[1], 0, bytes[1]},
-          iree_b200_buffer_ref_t{buffers[2], 0, bytes[2]}));
-    }
-    B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
-    B200_RETURN_IF_ERROR(
-        iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
-    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, buffers[2], 0, out, bytes[2]));
-    return iree_b200_device_wait_idle(device);
-  };
-  status = run();
+  std::lock_guard<std::mutex> host_lock(ops->host_mutex);
+  // The pipeline needs every block to pass the TMA guards (16-byte pitches) and at least
+  // two blocks to overlap; forced kernel families keep the single whole-problem dispatch.
+  const bool tma_ok = K > 0 && (K * es) % 16 == 0 && (N * out_es) % 16 == 0 && (N * es) % 16 == 0;
+  const int64_t blocks =
+      batch * ceil_div(M, ops->pipeline_block_m) * ceil_div(N, ops->pipeline_block_n);
+  const bool pipelined =
+      tma_ok && blocks >= 2 && bytes[0] + bytes[1] + bytes[2] >= ops->pipeline_min_bytes &&
+      !(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_FORCE_1CTA |
+                 IREE_B200_MATMUL_FLAG_FORCE_2CTA));
+  std::vector<iree_b200_command_buffer_t*> cbs;
+  iree_b200_status_t status =
+      pipelined ? matmul_host_pipelined(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs,
+                                        out, &cbs)
+                : matmul_host_serial(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs, out,
+                                     &cbs);
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
-  if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
-  iree_b200_command_buffer_release(cb);
-  for (auto* b : buffers) iree_b200_buffer_release(b);
+  if (status != IREE_B200_STATUS_OK) {
+    // Drain everything that may still reference the staging arena or the host buffers.
+    const CudaSymbols* cu = device->cu;
+    if (ops->upload_stream) cu->cuStreamSynchronize(ops->upload_stream);
+    iree_b200_device_wait_idle(device);
+    if (ops->download_stream) cu->cuStreamSynchronize(ops->download_stream);
+  }
+  for (auto* cb : cbs) iree_b200_command_buffer_release(cb);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   return IREE_B200_STATUS_OK;
 }
@@ -590,20 +832,23 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
   for (int i = 0; i < 4; ++i) B200_REQUIRE_ARG(host_in[i] || !bytes[i]);
   B200_REQUIRE_ARG(out);
   iree_b200_device_t* device = ops->device;
-  iree_b200_buffer_t* buffers[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  std::lock_guard<std::mutex> host_lock(ops->host_mutex);
+  uint64_t offsets[6], total = 0;
+  for (int i = 0; i < 6; ++i) {
+    offsets[i] = total;
+    total += (bytes[i] + 1023) / 1024 * 1024;
+  }
   iree_b200_command_buffer_t* cb = nullptr;
   auto ref = [&](int i) {
-    return iree_b200_buffer_ref_t{buffers[i], 0, buffers[i] ? bytes[i] : 0};
+    return bytes[i] ? iree_b200_buffer_ref_t{ops->arena, offsets[i], bytes[i]}
+                    : iree_b200_buffer_ref_t{nullptr, 0, 0};
   };
   auto run = [&]() -> iree_b200_status_t {
-    for (int i = 0; i < 6; ++i) {
-      if (!bytes[i]) continue;
-      B200_RETURN_IF_ERROR(iree_b200_allocator_allocate_buffer(
-          device, IREE_B200_MEMORY_TYPE_DEVICE_LOCAL, bytes[i], &buffers[i]));
-    }
+    B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
     for (int i = 0; i < 4; ++i) {
       if (!bytes[i]) continue;
-      B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, host_in[i], buffers[i], 0, bytes[i]));
+      B200_RETURN_IF_ERROR(
+          iree_b200_device_transfer_h2d(device, host_in[i], ops->arena, offsets[i], bytes[i]));
     }
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
@@ -613,14 +858,13 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
     B200_RETURN_IF_ERROR(
         iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
-    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, buffers[5], 0, out, bytes[5]));
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, ops->arena, offsets[5], out, bytes[5]));
     return iree_b200_device_wait_idle(device);
   };
   iree_b200_status_t status = run();
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
   if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
   iree_b200_command_buffer_release(cb);
-  for (auto* b : buffers) iree_b200_buffer_release(b);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   return IREE_B200_STATUS_OK;
 }

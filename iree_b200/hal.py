@@ -138,6 +138,7 @@ _STATUS_FUNCS = {
     "iree_b200_ops_create": [c_void_p, POINTER(c_void_p)],
     "iree_b200_ops_create_from_data": [c_void_p, c_void_p, c_size_t, POINTER(c_void_p)],
     "iree_b200_ops_set_reserved_sms": [c_void_p, c_int32],
+    "iree_b200_ops_set_host_pipeline": [c_void_p, c_uint64, c_int32, c_int32],
     "iree_b200_ops_select_matmul": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                     c_uint32, c_uint32, POINTER(MatmulSelection)],
     "iree_b200_ops_record_matmul": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64,
@@ -522,6 +523,9 @@ class Ops:
 
     def set_reserved_sms(self, reserved_sms: int):
         check(lib().iree_b200_ops_set_reserved_sms(self._h, reserved_sms))
+
+    def set_host_pipeline(self, min_bytes: int, block_m: int = 2048, block_n: int = 2048):
+        check(lib().iree_b200_ops_set_host_pipeline(self._h, min_bytes, block_m, block_n))
 
     def select_matmul(self, element_type, batch, M, N, K, flags=0, alignment=256) -> dict:
         sel = MatmulSelection()

@@ -192,3 +192,39 @@ def test_truncating_epilogue_guards(ops):
     exe = ops.executable
     s = ops.select_matmul("bf16", 1, 8192, 4096, 4096, flags=H.MATMUL_TRUNCATE_RESULT)
     assert exe.export_info(s["export_ordinal"])["kernel_name"] == "iree_b200_matmul_bf16_bf16"
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("case", [
+    # batch, M, K, N, accumulate, nt, truncate
+    (1, 1000, 272, 528, False, False, False),   # 4x3 blocks, ragged last row / column panel
+    (1, 1000, 272, 528, True, False, False),    # accumulator blocks go up too
+    (1, 528, 144, 1008, False, True, False),    # transpose_rhs: panels are rows of [N, K]
+    (3, 300, 528, 272, False, False, False),    # batch entries are separate blocks
+    (2, 513, 64, 768, False, False, True),      # truncating epilogue (2-byte result blocks)
+    (1, 256, 128, 2048, False, False, False),   # one row panel, 8 column panels
+    (1, 2048, 128, 256, True, False, False),    # 8 row panels, one column panel
+], ids=str)
+def test_pipelined_host_call(ops, t, case):
+    """iree_b200_ops_matmul_host as a pipeline (panel uploads, per-block dispatch, block
+    downloads on three streams): same bits as the single-dispatch form and the oracle."""
+    batch, M, K, N, accumulate, nt, truncate = case
+    if truncate and t == "i8":
+        pytest.skip("TRUNCATE_RESULT is f16 / bf16 only")
+    before = ops.dispatch_count
+    ops.set_host_pipeline(0, 256, 256)
+    try:
+        if truncate:
+            lhs = oracle.generate_random_matrix(t, (batch, M, K), 1)
+            rhs = oracle.generate_random_matrix(t, (batch, K, N), 2)
+            out = np.full((batch, M, N), 0x7777, dtype=np.uint16)
+            ops.matmul_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data,
+                            H.MATMUL_TRUNCATE_RESULT)
+            want = oracle.from_f32(t, oracle.matmul(t, lhs, rhs))
+        else:
+            out, want = _run(ops, t, batch, M, N, K, accumulate=accumulate, nt=nt)
+    finally:
+        ops.set_host_pipeline(16 << 20, 2048, 2048)
+    assert np.array_equal(out, want)
+    blocks = batch * -(-M // 256) * -(-N // 256)
+    assert ops.dispatch_count - before == blocks
