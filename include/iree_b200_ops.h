@@ -138,6 +138,10 @@ enum {
   IREE_B200_ATTENTION_FLAG_FORCE_GENERIC = 1u << 8,
   IREE_B200_ATTENTION_FLAG_FORCE_PREFILL = 1u << 9,
   IREE_B200_ATTENTION_FLAG_FORCE_DECODE = 1u << 10,
+  // Within the decode family: the two-dispatch split + merge form / the single-dispatch
+  // cluster form (otherwise chosen by the number of (batch, m) rows and K2).
+  IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT = 1u << 11,
+  IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER = 1u << 12,
 };
 
 #define IREE_B200_ATTENTION_MAX_DISPATCHES 2
@@ -156,7 +160,9 @@ typedef struct iree_b200_attention_selection_t {
 } iree_b200_attention_selection_t;
 
 // Matcher guards + count regions. tcgen05 prefill kernel: K1 == N == 128, no mask, M > 16,
-// 16-byte aligned bindings. Split-KV decode kernels: K1 == N == 128, no mask, M <= 16.
+// 16-byte aligned bindings. Decode kernels: K1 == N == 128, no mask, M <= 16 — one dispatch
+// (a cluster of 8 CTAs per (batch, m) row, merged over distributed shared memory) when
+// there are enough rows to fill the GPU that way, else split-KV + merge (two dispatches).
 // Everything else within K1, N <= 512 goes to the generic kernel; beyond that the status is
 // UNIMPLEMENTED (the compiler plugin leaves such ops to IREE's own codegen).
 IREE_B200_API iree_b200_status_t iree_b200_ops_select_attention(

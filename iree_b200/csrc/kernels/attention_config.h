@@ -41,6 +41,26 @@ struct AttnDecodeConfig {
   static constexpr int kRecordFloats = kHeadDim + 2;
 };
 
+// Decode, single-dispatch form: a cluster of kSplits CTAs owns one (batch, m) row; each CTA
+// streams its share of K and V through a bulk-copy (TMA 1-D) ring in shared memory and
+// the cluster merges the partial softmax states through distributed shared memory.
+struct AttnDecodeClusterConfig {
+  static constexpr int kHeadDim = 128;
+  static constexpr int kSplits = 8;          // == compiled-in cluster size (portable maximum)
+  static constexpr int kStageRows = 32;      // K2 rows per ring stage
+  static constexpr int kStages = 6;
+  static constexpr int kConsumerWarps = 8;   // 16 half-warps, 2 rows of a stage each
+  static constexpr int kThreads = (kConsumerWarps + 1) * 32;  // + 1 producer warp
+  static constexpr int kRowBytes = kHeadDim * 2;
+  static constexpr int kStageBytes = 2 * kStageRows * kRowBytes;  // K rows then V rows
+  static constexpr int kRecordFloats = kHeadDim + 2;              // sums, max, sum
+  static constexpr int kGroups = kConsumerWarps * 2;
+  static constexpr int kSmemBytes = 128 /*alignment slack*/ + kStages * kStageBytes +
+                                    (kGroups + 1) * kRecordFloats * 4 + 2 * kStages * 8 + 64;
+  static constexpr int kMinRowsPerSplit = 32;  // selection guard: K2 >= kSplits * this
+  static_assert(kStageRows == kGroups * 2, "two rows per half-warp and stage");
+};
+
 // Generic SIMT kernel limits (matcher guards).
 struct AttnGenericConfig {
   static constexpr int kThreads = 128;

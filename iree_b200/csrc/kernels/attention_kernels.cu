@@ -13,6 +13,10 @@
 //   iree_b200_attention_decode_merge_{f16,bf16}
 //     bindings  workspace ro, O [B,M,128]
 //     constants B, M, splits                           grid [M, B, 1]            block 128
+//   iree_b200_attention_decode_cluster_{f16,bf16}   single dispatch: cluster of 8 CTAs per
+//     (batch, m) row, bulk-copy ring, merge over distributed shared memory
+//     bindings  Q ro, K ro, V ro, O [B,M,128]
+//     constants B, M, K2, scale, flags                 grid [8, M, B] (cluster 8x1x1)  block 288
 //   iree_b200_attention_generic_{f16,bf16,f32}   any shape within the guards, optional mask
 //     bindings  Q ro, K ro, V ro, mask ro (any valid pointer when unused), O
 //     constants B, M, K1, K2, N, scale, mask_kind (0 none, 1 i1-as-u8, 2 f32 additive)
@@ -226,6 +230,210 @@ __device__ __forceinline__ void attention_decode_merge_body(const float* __restr
 
 B200_DECODE(f16, false)
 B200_DECODE(bf16, true)
+
+//===----------------------------------------------------------------------===//
+// Decode, single dispatch. One cluster of 8 CTAs per (batch, m) row. Inside a CTA a producer
+// warp keeps a 6-stage ring of [32 K rows | 32 V rows] filled with 1-D bulk copies (80 KiB
+// in flight per CTA, independent of what the consumers are doing); 16 half-warps consume
+// two rows per stage each, every half-warp carrying its own online-softmax state (max, sum,
+// 128 sums spread over 16 lanes x 8 columns), so the streaming loop has no block-wide
+// synchronisation at all. The 16 states merge in shared memory, the 8 CTA records merge in
+// CTA 0 through ld.shared::cluster. Same arithmetic as the split + merge pair.
+//===----------------------------------------------------------------------===//
+
+namespace {
+
+template <bool kBf16>
+__device__ __forceinline__ void attention_decode_cluster_body(const uint16_t* __restrict__ q,
+                                                              const uint16_t* __restrict__ k,
+                                                              const uint16_t* __restrict__ v,
+                                                              uint16_t* __restrict__ out, int B,
+                                                              int M, int K2, int scale_bits) {
+  using Cfg = AttnDecodeClusterConfig;
+  constexpr int D = Cfg::kHeadDim;
+  constexpr int S = Cfg::kStages;
+  constexpr int R = Cfg::kStageRows;
+  constexpr int RF = Cfg::kRecordFloats;
+  extern __shared__ uint8_t smem_raw[];
+  (void)B;
+
+  const uint32_t smem_base = (smem_u32(smem_raw) + 127u) & ~127u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  float* group_rec = reinterpret_cast<float*>(smem_gen + S * Cfg::kStageBytes);
+  float* cta_rec = group_rec + Cfg::kGroups * RF;
+  const uint32_t cta_rec_addr = smem_base + S * Cfg::kStageBytes + Cfg::kGroups * RF * 4;
+  const uint32_t bar_full = cta_rec_addr + RF * 4 + 8 - ((cta_rec_addr + RF * 4) & 7u);
+  const uint32_t bar_empty = bar_full + S * 8;
+
+  const int split = (int)cluster_ctarank(), m = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rows_per_split = (K2 + Cfg::kSplits - 1) / Cfg::kSplits;
+  const int row0 = min(K2, split * rows_per_split);
+  const int row_end = min(K2, row0 + rows_per_split);
+  const int num_stages = (row_end - row0 + R - 1) / R;
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, Cfg::kConsumerWarps);
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  if (warp == Cfg::kConsumerWarps) {
+    // ---- producer ----
+    if (lane == 0) {
+      const uint8_t* kb = reinterpret_cast<const uint8_t*>(k) + ((size_t)b * K2 + row0) * Cfg::kRowBytes;
+      const uint8_t* vb = reinterpret_cast<const uint8_t*>(v) + ((size_t)b * K2 + row0) * Cfg::kRowBytes;
+      for (int it = 0; it < num_stages; ++it) {
+        const int s = it % S;
+        if (it >= S) mbar_wait(bar_empty + 8 * s, ((it / S) - 1) & 1);
+        const int rows = min(R, row_end - row0 - it * R);
+        const uint32_t bytes = (uint32_t)rows * Cfg::kRowBytes;
+        const uint32_t dst = smem_base + s * Cfg::kStageBytes;
+        mbar_expect_tx(bar_full + 8 * s, 2 * bytes);
+        bulk_load_1d(dst, kb + (size_t)it * R * Cfg::kRowBytes, bytes, bar_full + 8 * s);
+        bulk_load_1d(dst + R * Cfg::kRowBytes, vb + (size_t)it * R * Cfg::kRowBytes, bytes,
+                     bar_full + 8 * s);
+      }
+    }
+  } else {
+    // ---- consumers ----
+    const int sub = lane & 15;             // 16-byte column slab of the 256-byte row
+    const int grp = warp * 2 + (lane >> 4);  // half-warp id, owns rows 2*grp, 2*grp+1 of a stage
+    float qf[8];
+    {
+      // Q' = round_T(s' * q) (AggregatedOpInterfaceImpl.cpp:355-358).
+      const float mult = attention_q_multiplier<kBf16>(__int_as_float(scale_bits));
+      const uint4 qv = *reinterpret_cast<const uint4*>(q + ((size_t)b * M + m) * D + sub * 8);
+      unpack8<kBf16>(qv, qf);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) qf[e] = elem_to_f32<kBf16>(f32_to_elem<kBf16>(qf[e] * mult));
+    }
+    float run_max = -FLT_MAX, run_sum = 0.f;  // TileAttention.cpp:78-96
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+
+    for (int it = 0; it < num_stages; ++it) {
+      const int s = it % S;
+      mbar_wait(bar_full + 8 * s, (it / S) & 1);
+      const uint8_t* stage = smem_gen + s * Cfg::kStageBytes;
+      const int rows = min(R, row_end - row0 - it * R);
+      const int r0 = grp * 2;
+      const bool ok0 = r0 < rows, ok1 = r0 + 1 < rows;
+      const uint4 k0 = *reinterpret_cast<const uint4*>(stage + r0 * Cfg::kRowBytes + sub * 16);
+      const uint4 k1 = *reinterpret_cast<const uint4*>(stage + (r0 + 1) * Cfg::kRowBytes + sub * 16);
+      const uint4 v0 =
+          *reinterpret_cast<const uint4*>(stage + (R + r0) * Cfg::kRowBytes + sub * 16);
+      const uint4 v1 =
+          *reinterpret_cast<const uint4*>(stage + (R + r0 + 1) * Cfg::kRowBytes + sub * 16);
+      float f0[8], f1[8];
+      unpack8<kBf16>(k0, f0);
+      unpack8<kBf16>(k1, f1);
+      float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        d0 = fmaf(qf[e], f0[e], d0);
+        d1 = fmaf(qf[e], f1[e], d1);
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        d0 += __shfl_xor_sync(0xffffffffu, d0, o);
+        d1 += __shfl_xor_sync(0xffffffffu, d1, o);
+      }
+      // All shared-memory reads of this stage are done: hand it back to the producer.
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + 8 * s);
+      if (ok0) {
+        const float s0 = d0, s1 = ok1 ? d1 : -INFINITY;
+        const float new_max = fmaxf(run_max, fmaxf(s0, s1));
+        const float norm = exp2f(run_max - new_max);
+        const float p0 = exp2f(s0 - new_max), p1 = exp2f(s1 - new_max);
+        run_sum = fmaf(norm, run_sum, p0 + p1);
+        run_max = new_max;
+        // P is truncated to V's element type before P.V (:613-618).
+        const float t0 = elem_to_f32<kBf16>(f32_to_elem<kBf16>(p0));
+        const float t1 = elem_to_f32<kBf16>(f32_to_elem<kBf16>(p1));
+        unpack8<kBf16>(v0, f0);
+        unpack8<kBf16>(v1, f1);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float a = fmaf(t0, f0[e], norm * acc[e]);
+          if (ok1) a = fmaf(t1, f1[e], a);   // a stale row may hold Inf/NaN bits: skip, not x0
+          acc[e] = a;
+        }
+      }
+    }
+    // ---- the 16 half-warp states -> shared memory ----
+    float* rec = group_rec + grp * RF;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) rec[sub * 8 + e] = acc[e];
+    if (sub == 0) {
+      rec[D] = run_max;
+      rec[D + 1] = run_sum;
+    }
+  }
+  __syncthreads();
+  if (tid < D) {
+    float gmax = -FLT_MAX;
+#pragma unroll
+    for (int g = 0; g < Cfg::kGroups; ++g) gmax = fmaxf(gmax, group_rec[g * RF + D]);
+    float sum = 0.f, a = 0.f;
+#pragma unroll
+    for (int g = 0; g < Cfg::kGroups; ++g) {
+      const float w = exp2f(group_rec[g * RF + D] - gmax);
+      sum = fmaf(w, group_rec[g * RF + D + 1], sum);
+      a = fmaf(w, group_rec[g * RF + tid], a);
+    }
+    cta_rec[tid] = a;
+    if (tid == 0) {
+      cta_rec[D] = gmax;
+      cta_rec[D + 1] = sum;
+    }
+  }
+  // Release this CTA's record to the cluster, acquire the others'.
+  cluster_sync();
+  if (split == 0 && tid < D) {
+    float mx[Cfg::kSplits], sm[Cfg::kSplits];
+    float gmax = -FLT_MAX;
+#pragma unroll
+    for (int c = 0; c < Cfg::kSplits; ++c) {
+      const uint32_t remote = map_to_cta(cta_rec_addr, (uint32_t)c);
+      mx[c] = ld_shared_cluster_f32(remote + D * 4);
+      sm[c] = ld_shared_cluster_f32(remote + (D + 1) * 4);
+      gmax = fmaxf(gmax, mx[c]);
+    }
+    float sum = 0.f, a = 0.f;
+#pragma unroll
+    for (int c = 0; c < Cfg::kSplits; ++c) {
+      const float w = exp2f(mx[c] - gmax);
+      sum = fmaf(w, sm[c], sum);
+      a = fmaf(w, ld_shared_cluster_f32(map_to_cta(cta_rec_addr, (uint32_t)c) + tid * 4), a);
+    }
+    const float rcp = 1.0f / sum;  // TileAttention.cpp:141-146
+    out[((size_t)b * M + m) * D + tid] = f32_to_elem<kBf16>(rcp * a);
+  }
+  // No CTA may exit while CTA 0 is still reading its shared memory.
+  cluster_sync();
+}
+
+}  // namespace
+
+#define B200_DECODE_CLUSTER(SUFFIX, BF16)                                                      \
+  extern "C" __global__ void __cluster_dims__(AttnDecodeClusterConfig::kSplits, 1, 1)          \
+      __launch_bounds__(AttnDecodeClusterConfig::kThreads)                                     \
+          iree_b200_attention_decode_cluster_##SUFFIX(                                         \
+              const uint16_t* __restrict__ q, const uint16_t* __restrict__ k,                  \
+              const uint16_t* __restrict__ v, uint16_t* __restrict__ out, int B, int M,        \
+              int K2, int scale_bits, int flags) {                                             \
+    (void)flags;                                                                               \
+    attention_decode_cluster_body<BF16>(q, k, v, out, B, M, K2, scale_bits);                   \
+  }
+
+B200_DECODE_CLUSTER(f16, false)
+B200_DECODE_CLUSTER(bf16, true)
 
 //===----------------------------------------------------------------------===//
 // Generic SIMT kernel: any B/M/K1/K2/N within the guards, optional mask operand, f16 /

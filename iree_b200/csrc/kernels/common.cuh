@@ -181,6 +181,23 @@ B200_DEVICE void tma_load_3d(uint32_t dst_smem, const TensorMap* map, uint32_t b
   }
 }
 
+// 1-D bulk copy global -> this CTA's shared memory (no tensor map: plain pointers, so the
+// kernel stays launchable through the unmodified custom-dispatch ABI). |bytes| and both
+// addresses are multiples of 16; completes |bytes| on |bar|.
+B200_DEVICE void bulk_load_1d(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(dst_smem),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+
+B200_DEVICE float ld_shared_cluster_f32(uint32_t cluster_addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr) : "memory");
+  return v;
+}
+
 B200_DEVICE void tma_store_3d(const TensorMap* map, uint32_t src_smem, int c0, int c1, int c2) {
   asm volatile(
       "cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(

@@ -24,7 +24,13 @@ enum MatmulFamily { kFamily2Cta = 0, kFamily1Cta = 1, kFamilyGeneric = 2, kFamil
 const char* const kTypeSuffix[3] = {"i8_i32", "f16_f32", "bf16_f32"};
 const char* const kTruncSuffix[3] = {"", "f16_f16", "bf16_bf16"};
 
-enum AttentionExport { kAttnPrefill = 0, kAttnDecodeSplit = 1, kAttnDecodeMerge = 2, kAttnGeneric = 3 };
+enum AttentionExport {
+  kAttnPrefill = 0,
+  kAttnDecodeSplit = 1,
+  kAttnDecodeMerge = 2,
+  kAttnGeneric = 3,
+  kAttnDecodeCluster = 4
+};
 
 }  // namespace
 
@@ -120,6 +126,8 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
         lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
     ops->attention_exports[t][kAttnDecodeMerge] =
         lookup(ops->executable, "iree_b200_attention_decode_merge_" + suffix);
+    ops->attention_exports[t][kAttnDecodeCluster] =
+        lookup(ops->executable, "iree_b200_attention_decode_cluster_" + suffix);
     ops->attention_exports[t][kAttnGeneric] =
         lookup(ops->executable, "iree_b200_attention_generic_" + suffix);
   }
@@ -633,7 +641,9 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
   enum { kPrefill, kDecode, kGeneric } family;
   if (flags & IREE_B200_ATTENTION_FLAG_FORCE_GENERIC) {
     family = kGeneric;
-  } else if (flags & (IREE_B200_ATTENTION_FLAG_FORCE_PREFILL | IREE_B200_ATTENTION_FLAG_FORCE_DECODE)) {
+  } else if (flags & (IREE_B200_ATTENTION_FLAG_FORCE_PREFILL | IREE_B200_ATTENTION_FLAG_FORCE_DECODE |
+                      IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT |
+                      IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER)) {
     if (!tc_shape) {
       return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                          "shape/mask/alignment does not satisfy the guards of the forced kernel");
@@ -666,6 +676,27 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
     case kDecode: {
       if (B > 65535 || M > 65535) {
         return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention decode grid out of range");
+      }
+      using Cluster = b200::AttnDecodeClusterConfig;
+      // Single dispatch when 8 CTAs per (batch, m) row already fill the SMs and every CTA
+      // gets a few ring stages of rows; otherwise split-KV sized to the SM count + merge.
+      bool cluster = B * M * Cluster::kSplits >= ops->device->sm_count &&
+                     K2 >= (int64_t)Cluster::kSplits * Cluster::kMinRowsPerSplit;
+      if (flags & IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT) cluster = false;
+      if (flags & IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER) cluster = true;
+      if (cluster) {
+        d0->export_ordinal = ops->attention_exports[element_type][kAttnDecodeCluster];
+        d0->workgroup_count[0] = Cluster::kSplits;
+        d0->workgroup_count[1] = (uint32_t)M;
+        d0->workgroup_count[2] = (uint32_t)B;
+        d0->constant_count = 5;
+        d0->constants[0] = (uint32_t)B;
+        d0->constants[1] = (uint32_t)M;
+        d0->constants[2] = (uint32_t)K2;
+        d0->constants[3] = scale_bits;
+        d0->constants[4] = 0;
+        out_selection->dispatch_count = 1;
+        break;
       }
       const int64_t chunk = b200::AttnDecodeConfig::kChunkRows;
       const int64_t want = std::max<int64_t>(1, (int64_t)ops->device->sm_count * 8 / (B * M));

@@ -32,6 +32,8 @@ ATTENTION_MASK_NONE, ATTENTION_MASK_BOOL, ATTENTION_MASK_F32 = 0, 1, 2
 ATTENTION_FORCE_GENERIC = 1 << 8
 ATTENTION_FORCE_PREFILL = 1 << 9
 ATTENTION_FORCE_DECODE = 1 << 10
+ATTENTION_FORCE_DECODE_SPLIT = 1 << 11
+ATTENTION_FORCE_DECODE_CLUSTER = 1 << 12
 
 MODE_GRAPH, MODE_STREAM = 0, 1
 MEMORY_DEVICE_LOCAL, MEMORY_HOST_LOCAL = 1, 2

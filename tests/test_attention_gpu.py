@@ -113,13 +113,35 @@ def test_prefill_kernel_rescale_path(ops, t):
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("form", ["split", "cluster"])
 @pytest.mark.parametrize("shape", [(1, 1, 256), (2, 1, 1000), (4, 3, 4096), (32, 1, 8192),
-                                   (1, 16, 77)], ids=str)
-def test_decode_kernels_vs_oracle(ops, t, shape):
+                                   (1, 16, 77), (3, 2, 5), (2, 1, 8), (5, 1, 263), (1, 1, 32 * 8 * 7 + 1)],
+                         ids=str)
+def test_decode_kernels_vs_oracle(ops, t, form, shape):
+    """Both decode forms: split-KV + merge (two dispatches) and the single-dispatch cluster
+    kernel (ragged splits, splits with no rows at all, partial ring stages)."""
     B, M, K2 = shape
     q, k, v = _random_qkv(t, B, M, K2, 128, seed=K2)
     scale = 1.0 / np.sqrt(128.0)
-    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_DECODE)
+    before = ops.dispatch_count
+    got = _gpu_attention(ops, t, q, k, v, scale,
+                         flags={"split": H.ATTENTION_FORCE_DECODE_SPLIT,
+                                "cluster": H.ATTENTION_FORCE_DECODE_CLUSTER}[form])
+    assert ops.dispatch_count - before == {"split": 2, "cluster": 1}[form]
+    want = oracle.attention(t, q, k, v, scale, k2_tile=256)
+    _assert_close(t, got, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+def test_decode_cluster_growing_maxima(ops, t):
+    """Scores that keep growing along K2 exercise every rescale of the per-half-warp states
+    and the two merge levels (shared memory, then distributed shared memory)."""
+    B, M, K2 = 20, 1, 2048
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=11)
+    kf = oracle.to_f32(t, k) * (0.25 + np.arange(K2, dtype=np.float32) / 512.0)[None, :, None]
+    k = oracle.from_f32(t, kf)
+    scale = 1.0 / np.sqrt(128.0)
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_DECODE_CLUSTER)
     want = oracle.attention(t, q, k, v, scale, k2_tile=256)
     _assert_close(t, got, want)
 
@@ -151,8 +173,13 @@ def test_selection_guards(ops):
     assert names(s) == ["iree_b200_attention_prefill_f16"]
     assert s["dispatches"][0]["workgroup_count"] == [16, 32, 1]
     s = ops.select_attention("f16", 32, 1, 128, 8192, 128, 0.088)
+    assert names(s) == ["iree_b200_attention_decode_cluster_f16"]
+    assert s["dispatches"][0]["workgroup_count"] == [8, 1, 32] and s["workspace_bytes"] == 0
+    # Few (batch, m) rows: 8 CTAs per row would leave SMs idle -> split-KV + merge.
+    s = ops.select_attention("f16", 4, 1, 128, 8192, 128, 0.088)
     assert names(s) == ["iree_b200_attention_decode_split_f16", "iree_b200_attention_decode_merge_f16"]
-    assert s["workspace_bytes"] == 32 * s["dispatches"][0]["workgroup_count"][0] * 130 * 4
+    assert s["workspace_bytes"] == 4 * s["dispatches"][0]["workgroup_count"][0] * 130 * 4
+    assert names(ops.select_attention("f16", 32, 1, 128, 128, 128, 0.088))[0].endswith("split_f16")
     assert names(ops.select_attention("bf16", 2, 64, 64, 64, 64, 0.125)) == \
         ["iree_b200_attention_generic_bf16"]
     assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1,
