@@ -66,19 +66,55 @@ def load_peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """Samples SM clock, power and throttle reasons WHILE the timed region runs: NVML polled
+    every 5 ms from a thread (nvidia-smi -lms 100 as the fallback when pynvml is missing)."""
 
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index: int):
         self.index = index
-        self.rows = []
+        self.rows = []      # (sm_mhz, power_w, reason names)
+        self.smax = None
         self.proc = None
         self.thread = None
+        self.stop_flag = threading.Event()
+        self.source = None
 
     def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates in PCI order; honour CUDA_VISIBLE_DEVICES when it is a plain list.
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [v for v in vis.split(",") if v.strip().isdigit()]
+            nv_index = int(ids[self.index]) if self.index < len(ids) else self.index
+            h = pynvml.nvmlDeviceGetHandleByIndex(nv_index)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            bits = {"hw_slowdown": pynvml.nvmlClocksEventReasonHwSlowdown,
+                    "hw_thermal_slowdown": pynvml.nvmlClocksEventReasonHwThermalSlowdown,
+                    "sw_thermal_slowdown": pynvml.nvmlClocksEventReasonSwThermalSlowdown,
+                    "sw_power_cap": pynvml.nvmlClocksEventReasonSwPowerCap}
+
+            def poll():
+                while not self.stop_flag.is_set():
+                    try:
+                        sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                        pw = pynvml.nvmlDeviceGetPowerUsage(h) / 1000.0
+                        r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                        self.rows.append((sm, pw, [n for n, b in bits.items() if r & b]))
+                    except Exception:
+                        pass
+                    time.sleep(0.005)
+
+            self.thread = threading.Thread(target=poll, daemon=True)
+            self.thread.start()
+            self.source = "nvml 5 ms"
+            return
+        except Exception:
+            self.thread = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
@@ -86,41 +122,41 @@ class ClockSampler:
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             return
+        self.source = "nvidia-smi 100 ms"
         self.thread = threading.Thread(target=self._read, daemon=True)
         self.thread.start()
 
     def _read(self):
         for line in self.proc.stdout:
             parts = [p.strip() for p in line.split(",")]
-            if len(parts) >= 9:
-                self.rows.append(parts)
-
-    def stop(self) -> dict:
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        sm, smax, power, reasons = [], [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+            if len(parts) < 9:
+                continue
             try:
-                sm.append(float(r[1]))
-                smax.append(float(r[2]))
-                power.append(float(r[3]))
+                sm, smax, pw = float(parts[1]), float(parts[2]), float(parts[3])
             except ValueError:
                 continue
-            for name, v in zip(names, r[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
-                "sm_max_mhz": max(smax) if smax else None,
-                "power_w_max": max(power) if power else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+            self.smax = smax
+            self.rows.append((sm, pw, [n for n, v in zip(self.NAMES, parts[5:9])
+                                       if v.lower().startswith("active")]))
+
+    def stop(self) -> dict:
+        if not self.thread:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock source"]}
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        else:
+            self.stop_flag.set()
+            self.thread.join(timeout=2)
+        sm = sorted(r[0] for r in self.rows)
+        reasons = sorted({n for r in self.rows for n in r[2]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.smax,
+                "power_w_max": max((r[1] for r in self.rows), default=None),
+                "samples": len(sm), "source": self.source, "reasons": reasons}
 
 
 def dist_env():
@@ -564,8 +600,8 @@ def main():
     ap = argparse.ArgumentParser(description=__doc__,
                                  formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)) + ["tp_decoder_layer"])
     ap.add_argument("--e2e-steps", type=int, default=10)

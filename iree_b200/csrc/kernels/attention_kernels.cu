@@ -349,8 +349,8 @@ __device__ __forceinline__ void attention_decode_cluster_body(const uint16_t* __
       if (ok0) {
         const float s0 = d0, s1 = ok1 ? d1 : -INFINITY;
         const float new_max = fmaxf(run_max, fmaxf(s0, s1));
-        const float norm = exp2f(run_max - new_max);
-        const float p0 = exp2f(s0 - new_max), p1 = exp2f(s1 - new_max);
+        const float norm = fast_exp2(run_max - new_max);
+        const float p0 = fast_exp2(s0 - new_max), p1 = fast_exp2(s1 - new_max);
         run_sum = fmaf(norm, run_sum, p0 + p1);
         run_max = new_max;
         // P is truncated to V's element type before P.V (:613-618).

@@ -1,0 +1,28 @@
+#!/bin/bash
+# One GPU-box visit: parity tests, smoke, the bench lines and the ncu evidence, each stage
+# under its own timeout and logged to gpurun_out/<tag>_*.  Usage: tools/gpu_round.sh TAG [stages...]
+TAG=${1:-r1}; shift
+STAGES=${@:-tests smoke bench ncu}
+O=gpurun_out; mkdir -p $O
+run() { name=$1; shift; local t=$1; shift; echo "== $name"; timeout $t "$@" > $O/${TAG}_$name.log 2>&1; echo "   exit $? ($(tail -c 300 $O/${TAG}_$name.log | tr '\n' ' ' | tail -c 200))"; }
+for st in $STAGES; do case $st in
+tests) run pytest 900 python -m pytest tests -m gpu -x -q ;;
+newtests) run pytest_new 600 python -m pytest tests -m gpu -x -q -k "pipelined or decode or selection or full_size" ;;
+smoke) run smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
+bench)
+  run bench_matmul_bf16 400 python bench.py
+  for w in matmul_i8 batch_matmul attention_prefill attention_prefill_bf16 attention_decode; do
+    run bench_$w 300 python bench.py --workload $w --no-cpu-baseline --steps 100
+  done
+  run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
+decode) run bench_attention_decode 300 python bench.py --workload attention_decode --no-cpu-baseline --steps 200 ;;
+ncu)
+  run ncu_launches 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_matmul_bf16.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline
+  run ncu_decode 400 ncu --set full --clock-control none --import-source on -k regex:decode_cluster -c 1 -o $O/${TAG}_attn_decode_cluster -f python bench.py --workload attention_decode --steps 3 --warmup 3 --no-cpu-baseline ;;
+esac; done
+grep -h '^{' $O/${TAG}_bench_*.log 2>/dev/null | python -c "
+import sys, json
+for l in sys.stdin:
+    d = json.loads(l)
+    print(d.get('impl','ours'), d['config'].get('workload','')[:60], '| value %.1f' % d['value'], '| ms %.4f' % d['ms_per_step'], '| frac', d.get('roofline',{}).get('frac'), '| e2e %.2f' % d['e2e']['value'], '| clocks', d.get('clocks'))
+"
