@@ -56,7 +56,7 @@ struct AttnDecodeClusterConfig {
   static constexpr int kRecordFloats = kHeadDim + 2;              // sums, max, sum
   static constexpr int kGroups = kConsumerWarps * 2;
   static constexpr int kSmemBytes = 128 /*alignment slack*/ + kStages * kStageBytes +
-                                    (kGroups + 1) * kRecordFloats * 4 + 2 * kStages * 8 + 64;
+                                    (kGroups + kSplits) * kRecordFloats * 4 + 2 * kStages * 8 + 64;
   static constexpr int kMinRowsPerSplit = 32;  // selection guard: K2 >= kSplits * this
   static_assert(kStageRows == kGroups * 2, "two rows per half-warp and stage");
 };

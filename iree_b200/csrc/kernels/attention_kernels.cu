@@ -237,8 +237,8 @@ B200_DECODE(bf16, true)
 // in flight per CTA, independent of what the consumers are doing); 16 half-warps consume
 // two rows per stage each, every half-warp carrying its own online-softmax state (max, sum,
 // 128 sums spread over 16 lanes x 8 columns), so the streaming loop has no block-wide
-// synchronisation at all. The 16 states merge in shared memory, the 8 CTA records merge in
-// CTA 0 through ld.shared::cluster. Same arithmetic as the split + merge pair.
+// synchronisation at all. The 16 states merge in shared memory, the 8 CTA records are pushed
+// into CTA 0 with st.shared::cluster and merged there. Same arithmetic as the split + merge pair.
 //===----------------------------------------------------------------------===//
 
 namespace {
@@ -262,7 +262,7 @@ __device__ __forceinline__ void attention_decode_cluster_body(const uint16_t* __
   float* group_rec = reinterpret_cast<float*>(smem_gen + S * Cfg::kStageBytes);
   float* cta_rec = group_rec + Cfg::kGroups * RF;
   const uint32_t cta_rec_addr = smem_base + S * Cfg::kStageBytes + Cfg::kGroups * RF * 4;
-  const uint32_t bar_full = cta_rec_addr + RF * 4 + 8 - ((cta_rec_addr + RF * 4) & 7u);
+  const uint32_t bar_full = (cta_rec_addr + Cfg::kSplits * RF * 4 + 7u) & ~7u;
   const uint32_t bar_empty = bar_full + S * 8;
 
   const int split = (int)cluster_ctarank(), m = blockIdx.y, b = blockIdx.z;
@@ -387,36 +387,33 @@ __device__ __forceinline__ void attention_decode_cluster_body(const uint16_t* __
       sum = fmaf(w, group_rec[g * RF + D + 1], sum);
       a = fmaf(w, group_rec[g * RF + tid], a);
     }
-    cta_rec[tid] = a;
+    // Push this CTA's record into CTA 0's shared memory (slot |split|): one cluster barrier
+    // then orders all eight records before CTA 0 reads them locally, and the other CTAs
+    // may retire right after arriving (nobody reads their shared memory).
+    const uint32_t slot = map_to_cta(cta_rec_addr + (uint32_t)split * RF * 4, 0);
+    st_shared_cluster_f32(slot + tid * 4, a);
     if (tid == 0) {
-      cta_rec[D] = gmax;
-      cta_rec[D + 1] = sum;
+      st_shared_cluster_f32(slot + D * 4, gmax);
+      st_shared_cluster_f32(slot + (D + 1) * 4, sum);
     }
   }
-  // Release this CTA's record to the cluster, acquire the others'.
-  cluster_sync();
-  if (split == 0 && tid < D) {
-    float mx[Cfg::kSplits], sm[Cfg::kSplits];
+  cluster_arrive();  // .release: the stores above are visible to whoever acquires
+  if (split != 0) return;
+  cluster_wait();
+  if (tid < D) {
     float gmax = -FLT_MAX;
 #pragma unroll
-    for (int c = 0; c < Cfg::kSplits; ++c) {
-      const uint32_t remote = map_to_cta(cta_rec_addr, (uint32_t)c);
-      mx[c] = ld_shared_cluster_f32(remote + D * 4);
-      sm[c] = ld_shared_cluster_f32(remote + (D + 1) * 4);
-      gmax = fmaxf(gmax, mx[c]);
-    }
+    for (int c = 0; c < Cfg::kSplits; ++c) gmax = fmaxf(gmax, cta_rec[c * RF + D]);
     float sum = 0.f, a = 0.f;
 #pragma unroll
     for (int c = 0; c < Cfg::kSplits; ++c) {
-      const float w = exp2f(mx[c] - gmax);
-      sum = fmaf(w, sm[c], sum);
-      a = fmaf(w, ld_shared_cluster_f32(map_to_cta(cta_rec_addr, (uint32_t)c) + tid * 4), a);
+      const float w = exp2f(cta_rec[c * RF + D] - gmax);
+      sum = fmaf(w, cta_rec[c * RF + D + 1], sum);
+      a = fmaf(w, cta_rec[c * RF + tid], a);
     }
     const float rcp = 1.0f / sum;  // TileAttention.cpp:141-146
     out[((size_t)b * M + m) * D + tid] = f32_to_elem<kBf16>(rcp * a);
   }
-  // No CTA may exit while CTA 0 is still reading its shared memory.
-  cluster_sync();
 }
 
 }  // namespace

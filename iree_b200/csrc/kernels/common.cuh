@@ -192,6 +192,10 @@ B200_DEVICE void bulk_load_1d(uint32_t dst_smem, const void* src, uint32_t bytes
       : "memory");
 }
 
+B200_DEVICE void st_shared_cluster_f32(uint32_t cluster_addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(cluster_addr), "f"(v) : "memory");
+}
+
 B200_DEVICE float ld_shared_cluster_f32(uint32_t cluster_addr) {
   float v;
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(cluster_addr) : "memory");
