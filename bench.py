@@ -311,7 +311,7 @@ class TpLayerStep:
 
     TOKENS, HIDDEN, QKV, FFN, CHUNKS = 8192, 4096, 6144, 14336, 4
 
-    def __init__(self, torch, hal, dev, ops, world, rank, channel, seed):
+    def __init__(self, torch, hal, dev, ops, world, rank, channel, seed, region=None):
         from iree_b200 import sharding
         T, H, QKV, FFN = self.TOKENS, self.HIDDEN, self.QKV, self.FFN
         plan = {g.name: g for g in sharding.decoder_layer_plan(world, rank, tokens=T)}
@@ -328,6 +328,13 @@ class TpLayerStep:
             "wgu": mk(H, 2 * FFN // world), "gu": out(T, 2 * FFN // world),
             "act": mk(T, FFN // world), "wd": mk(FFN // world, H), "d": out(T, H),
         }
+        if region is not None:
+            # The all-reduced activations live in the symmetric region (every rank maps it):
+            # their all-reduces run on the NVLink kernels instead of NCCL.
+            self.t["o"] = region.view(0, (T, H), torch.bfloat16)
+            self.t["d"] = region.view(T * H * 2, (T, H), torch.bfloat16)
+        self.region = region
+        self.channel = channel
         self.b = {k: dev.import_buffer(v.data_ptr(), v.numel() * 2) for k, v in self.t.items()}
         self.world, self.dev = world, dev
         self.flop = 2.0 * T * (H * QKV + H * H + H * 2 * FFN + FFN * H) / world
@@ -376,6 +383,17 @@ class TpLayerStep:
         self.dev.d2h(self.b["d"], host[1].data_ptr(), n)
         self.dev.wait_idle()
 
+    def collective_path(self):
+        if self.world == 1:
+            return "none at N=1"
+        if self.region is None:
+            return "NCCL"
+        counts = self.channel.collective_counts()
+        kind = "NVSwitch multimem.ld_reduce/st kernels" if self.region.multicast_base else \
+            "peer load/store kernels"
+        return (f"symmetric region, {kind}: {counts['symmetric']} issued by our kernels, "
+                f"{counts['nccl']} by NCCL so far")
+
     def describe(self):
         T, H, QKV, FFN, w = self.TOKENS, self.HIDDEN, self.QKV, self.FFN, self.world
         weights = 2.0 * (H * QKV + H * H + H * 2 * FFN + FFN * H) / w
@@ -384,7 +402,8 @@ class TpLayerStep:
                 "workload": f"Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens={T}, "
                             f"bf16 -> bf16 (f32 accumulate), tensor-parallel over {w} GPU(s), "
                             f"{self.collectives} all-reduce(sum, bf16, [{T // self.CHUNKS},{H}]) per "
-                            f"step via iree_hal_channel/NCCL, overlapped on the collective stream",
+                            f"step via iree_hal_channel ({self.collective_path()}), overlapped on "
+                            f"the collective stream",
                 "dtype": "bf16 (f32 accumulate)", "h2d": int(T * H * 2), "d2h": int(T * H * 2),
                 "api": "h2d(x) + iree_b200_device_queue_execute(layer command buffer) + d2h(y)"}
 
@@ -418,10 +437,16 @@ def run_ours(args):
             ids = [hal.Channel.create_id() if rank == 0 else None]
             dist.broadcast_object_list(ids, src=0)
             channel = hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
+        region = None
         if world > 1:
             ops.set_reserved_sms(args.reserved_sms)
+            if args.collective == "symmetric":
+                from iree_b200 import symmetric
+                region = symmetric.SymmetricRegion(
+                    2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
+                region.attach(channel, ops.executable, max_blocks=max(1, min(64, args.reserved_sms)))
         TpLayerStep.CHUNKS = args.tp_chunks
-        first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank)
+        first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank, region=region)
         info = first.describe()
         sets, works = 1, [first]
     else:
@@ -474,6 +499,8 @@ def run_ours(args):
 
     if rank != 0:
         return
+    if tp:
+        info = first.describe()  # refreshed: how many collectives went which way
     peaks = load_peaks()
     per_gpu = value / world
     traffic = None
@@ -608,6 +635,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--reserved-sms", type=int, default=16,
                     help="tp_decoder_layer, N>1: SMs the GEMM grids leave to the NCCL kernels")
+    ap.add_argument("--collective", default="symmetric", choices=["symmetric", "nccl"],
+                    help="tp_decoder_layer, N>1: all-reduce through the symmetric-region NVLink "
+                         "kernels (default) or through NCCL")
     ap.add_argument("--tp-chunks", type=int, default=4,
                     help="tp_decoder_layer: token chunks per row-parallel GEMM + all-reduce")
     args = ap.parse_args()

@@ -399,6 +399,43 @@ IREE_B200_API iree_b200_status_t iree_b200_channel_split(iree_b200_channel_t* ba
 IREE_B200_API void iree_b200_channel_query_rank_and_count(const iree_b200_channel_t* channel,
                                                           int32_t* out_rank, int32_t* out_count);
 
+// Symmetric region: device memory every rank of the channel has mapped at once (CUDA VMM
+// peer mappings + an NVSwitch multicast object; the host side sets those up, e.g. with
+// torch.distributed._symmetric_memory — plumbing). Once attached, an in-place
+// all_reduce(sum) of f16 / bf16 / f32 recorded with iree_b200_command_buffer_collective
+// whose range lies inside the region (16-byte aligned, a multiple of 16 bytes) is executed
+// by the builtin NVLink kernels (kernels/collective_kernels.cu: multimem.ld_reduce +
+// multimem.st through the switch, or peer loads/stores when there is no multicast
+// mapping) instead of ncclAllReduce; every other collective still goes to NCCL. All ranks
+// must attach the same region and record the same collectives in the same order — the
+// contract iree_hal_channel already has (hal/channel.h:33-60).
+#define IREE_B200_SYMMETRIC_MAX_RANKS 8
+#define IREE_B200_SYMMETRIC_FLAG_BYTES 2048  // per rank, zero-initialised, inside or outside the region
+
+typedef struct iree_b200_symmetric_region_params_t {
+  uint64_t byte_length;
+  // This rank's mappings of every rank's copy of the region; peer_bases[rank] is the local one.
+  const uint64_t* peer_bases;
+  // Multicast mapping of the region, or 0: then the peer-load/store kernels are used.
+  uint64_t multicast_base;
+  // This rank's mappings of every rank's flag block (IREE_B200_SYMMETRIC_FLAG_BYTES each).
+  const uint64_t* peer_flag_blocks;
+  // Upper bound on the CTAs one collective uses (<= 64; 0 = default 16). Collectives overlap
+  // with persistent GEMM grids only if that many SMs are left free
+  // (iree_b200_ops_set_reserved_sms).
+  int32_t max_blocks;
+} iree_b200_symmetric_region_params_t;
+
+// |executable| must export the iree_b200_all_reduce_sum_* kernels (the builtin one does:
+// iree_b200_ops_executable).
+IREE_B200_API iree_b200_status_t iree_b200_channel_attach_symmetric_region(
+    iree_b200_channel_t* channel, iree_b200_executable_t* executable,
+    const iree_b200_symmetric_region_params_t* params);
+// Number of collectives this channel has issued through the symmetric kernels / NCCL.
+IREE_B200_API void iree_b200_channel_query_collective_counts(const iree_b200_channel_t* channel,
+                                                             uint64_t* out_symmetric,
+                                                             uint64_t* out_nccl);
+
 #ifdef __cplusplus
 }  // extern "C"
 #endif

@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <thread>
 
+#include "../kernels/collective_config.h"
 #include "internal.h"
 
 using namespace b200hal;
@@ -185,6 +186,8 @@ void iree_b200_channel_release(iree_b200_channel_t* channel) {
   iree_b200_device_t* device = channel->device;
   device->cu->cuCtxSetCurrent(device->cu_context);
   if (channel->comm) channel->nccl->ncclCommDestroy(channel->comm);
+  if (channel->symmetric.table) device->cu->cuMemFree(channel->symmetric.table);
+  iree_b200_executable_release(channel->symmetric.executable);
   delete channel;
   iree_b200_device_release(device);
 }
@@ -217,6 +220,82 @@ iree_b200_status_t iree_b200_channel_split(iree_b200_channel_t* base_channel, in
   iree_b200_device_retain(device);
   *out_split_channel = channel;
   return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_channel_attach_symmetric_region(
+    iree_b200_channel_t* channel, iree_b200_executable_t* executable,
+    const iree_b200_symmetric_region_params_t* params) {
+  B200_REQUIRE_ARG(channel && executable && params);
+  B200_REQUIRE_ARG(params->peer_bases && params->peer_flag_blocks);
+  using Cfg = b200::CollectiveConfig;
+  static_assert(Cfg::kMaxWorld == IREE_B200_SYMMETRIC_MAX_RANKS, "header constant out of date");
+  static_assert(Cfg::kFlagBytes == IREE_B200_SYMMETRIC_FLAG_BYTES, "header constant out of date");
+  if (channel->symmetric.attached) {
+    return make_status(IREE_B200_STATUS_ALREADY_EXISTS,
+                       "the channel already has a symmetric region attached");
+  }
+  if (channel->count > Cfg::kMaxWorld) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "symmetric regions span at most %d ranks (channel has %d)", Cfg::kMaxWorld,
+                       channel->count);
+  }
+  if (params->max_blocks < 0 || params->max_blocks > Cfg::kMaxBlocks) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "max_blocks %d out of range [0, %d]",
+                       params->max_blocks, Cfg::kMaxBlocks);
+  }
+  uint64_t table[2 * Cfg::kMaxWorld] = {0};
+  for (int r = 0; r < channel->count; ++r) {
+    if (!params->peer_bases[r] || !params->peer_flag_blocks[r] || params->peer_bases[r] % 16 ||
+        params->peer_flag_blocks[r] % 4) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "symmetric region: mapping of rank %d is null or misaligned", r);
+    }
+    table[r] = params->peer_bases[r];
+    table[Cfg::kMaxWorld + r] = params->peer_flag_blocks[r];
+  }
+  if (params->multicast_base % 16) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "multicast mapping is misaligned");
+  }
+  const char* const suffix[3] = {"f16", "bf16", "f32"};
+  CUfunction functions[3];
+  for (int t = 0; t < 3; ++t) {
+    const std::string name = std::string("iree_b200_all_reduce_sum_") + suffix[t] +
+                             (params->multicast_base ? "_nvls" : "_p2p");
+    int32_t ordinal = -1;
+    B200_RETURN_IF_ERROR(iree_b200_executable_lookup_export_by_name(executable, name.c_str(), &ordinal));
+    functions[t] = executable->exports[ordinal].function;
+  }
+  iree_b200_device_t* device = channel->device;
+  const CudaSymbols* cu = device->cu;
+  B200_CU(cu, cuCtxSetCurrent(device->cu_context));
+  CUdeviceptr device_table = 0;
+  B200_CU(cu, cuMemAlloc(&device_table, sizeof(table)));
+  {
+    std::lock_guard<std::mutex> lock(device->mutex);
+    CUresult r = cu->cuMemcpyHtoDAsync(device_table, table, sizeof(table), device->dispatch_stream);
+    if (r == CUDA_SUCCESS) r = cu->cuStreamSynchronize(device->dispatch_stream);
+    if (r != CUDA_SUCCESS) {
+      cu->cuMemFree(device_table);
+      return cu_status(cu, r, "upload of the symmetric peer table", __FILE__, __LINE__);
+    }
+  }
+  auto& sym = channel->symmetric;
+  sym.local_base = (CUdeviceptr)params->peer_bases[channel->rank];
+  sym.byte_length = params->byte_length;
+  sym.multicast_base = (CUdeviceptr)params->multicast_base;
+  sym.table = device_table;
+  sym.max_blocks = params->max_blocks ? params->max_blocks : Cfg::kDefaultBlocks;
+  sym.executable = executable;
+  iree_b200_executable_retain(executable);
+  for (int t = 0; t < 3; ++t) sym.all_reduce_sum[t] = functions[t];
+  sym.attached = true;
+  return IREE_B200_STATUS_OK;
+}
+
+void iree_b200_channel_query_collective_counts(const iree_b200_channel_t* channel,
+                                               uint64_t* out_symmetric, uint64_t* out_nccl) {
+  if (out_symmetric) *out_symmetric = channel ? channel->symmetric_collectives.load() : 0;
+  if (out_nccl) *out_nccl = channel ? channel->nccl_collectives.load() : 0;
 }
 
 void iree_b200_channel_query_rank_and_count(const iree_b200_channel_t* channel, int32_t* out_rank,

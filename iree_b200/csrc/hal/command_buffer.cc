@@ -16,9 +16,11 @@
 // For exports that ship a TMA recipe the encoded CUtensorMaps follow as trailing
 // parameters (include/iree_b200_tma_recipe.h).
 
+#include <algorithm>
 #include <cstdlib>
 #include <memory>
 
+#include "../kernels/collective_config.h"
 #include "internal.h"
 
 using namespace b200hal;
@@ -246,6 +248,47 @@ iree_b200_status_t issue_collective(const Command& c, CUstream stream) {
   return IREE_B200_STATUS_OK;
 }
 
+// True when |c| can run on the symmetric-region kernels (kernels/collective_kernels.cu).
+bool symmetric_all_reduce_eligible(const Command& c, int* out_type_index) {
+  const auto& sym = c.channel->symmetric;
+  if (!sym.attached || c.channel->count < 2) return false;
+  const uint32_t kind = c.op & 0xff, reduction = (c.op >> 8) & 0xff, type = (c.op >> 16) & 0xff;
+  if (kind != IREE_B200_COLLECTIVE_KIND_ALL_REDUCE || reduction != IREE_B200_COLLECTIVE_REDUCTION_SUM) {
+    return false;
+  }
+  switch (type) {
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_16: *out_type_index = 0; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_BFLOAT_16: *out_type_index = 1; break;
+    case IREE_B200_COLLECTIVE_ELEMENT_TYPE_FLOAT_32: *out_type_index = 2; break;
+    default: return false;
+  }
+  const uint64_t bytes = c.element_count * collective_element_size(type);
+  if (c.source != c.target || !bytes || bytes % 16 || c.target % 16) return false;
+  return c.target >= sym.local_base && bytes <= sym.byte_length &&
+         c.target - sym.local_base <= sym.byte_length - bytes;
+}
+
+iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index, CUstream stream) {
+  using Cfg = b200::CollectiveConfig;
+  iree_b200_channel_t* channel = c.channel;
+  const auto& sym = channel->symmetric;
+  const CudaSymbols* cu = channel->device->cu;
+  const uint32_t type = (c.op >> 16) & 0xff;
+  uint64_t table = sym.table, multicast = sym.multicast_base;
+  uint64_t byte_offset = c.target - sym.local_base;
+  uint64_t vectors = c.element_count * collective_element_size(type) / 16;
+  int rank = channel->rank, world = channel->count;
+  // Every rank derives the same grid from the same element count (the flag words are per
+  // block index, so the grids must agree across ranks).
+  const uint64_t per_rank = (vectors + world - 1) / world;
+  const uint64_t want = (per_rank + Cfg::kThreads * Cfg::kUnroll - 1) / (Cfg::kThreads * Cfg::kUnroll);
+  const uint32_t blocks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(want, sym.max_blocks));
+  void* params[] = {&table, &multicast, &byte_offset, &vectors, &rank, &world};
+  B200_CU(cu, cuLaunchKernel(sym.all_reduce_sum[type_index], blocks, 1, 1, Cfg::kThreads, 1, 1, 0,
+                             stream, params, nullptr));
+  return IREE_B200_STATUS_OK;
+}
+
 // iree_hal_cuda_nccl_submit_batch (nccl_channel.c:542-588): one group per flushed batch.
 // With a collective stream the batch is ordered after everything already on the dispatch
 // stream and left running; |*pending_join| tells the caller to join before the next
@@ -261,16 +304,33 @@ iree_b200_status_t flush_collectives(iree_b200_device_t* device, std::vector<con
     stream = device->collective_stream;
     *pending_join = true;
   }
-  const NcclSymbols* nccl = batch->front()->channel->nccl;
+  // In-place all_reduce(sum) inside the channel's symmetric region: our own NVLink kernels.
+  std::vector<const Command*> for_nccl;
+  for (const Command* c : *batch) {
+    int type_index = -1;
+    if (symmetric_all_reduce_eligible(*c, &type_index)) {
+      iree_b200_status_t status = launch_symmetric_all_reduce(*c, type_index, stream);
+      if (status != IREE_B200_STATUS_OK) {
+        batch->clear();
+        return status;
+      }
+      c->channel->symmetric_collectives.fetch_add(1);
+    } else {
+      for_nccl.push_back(c);
+    }
+  }
+  batch->clear();
+  if (for_nccl.empty()) return IREE_B200_STATUS_OK;
+  const NcclSymbols* nccl = for_nccl.front()->channel->nccl;
   B200_NCCL(nccl, ncclGroupStart());
   iree_b200_status_t status = IREE_B200_STATUS_OK;
-  for (const Command* c : *batch) {
+  for (const Command* c : for_nccl) {
     status = issue_collective(*c, stream);
     if (status != IREE_B200_STATUS_OK) break;
+    c->channel->nccl_collectives.fetch_add(1);
   }
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
   ncclResult_t end_result = nccl->ncclGroupEnd();
-  batch->clear();
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   if (end_result != ncclSuccess) {
     return nccl_status(nccl, end_result, "ncclGroupEnd()", __FILE__, __LINE__);

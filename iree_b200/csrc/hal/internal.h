@@ -260,6 +260,18 @@ struct iree_b200_channel_t : b200hal::RefCounted {
   ncclComm_t comm = nullptr;
   int32_t rank = 0;
   int32_t count = 1;
+  // Symmetric region (iree_b200_channel_attach_symmetric_region).
+  struct {
+    bool attached = false;
+    CUdeviceptr local_base = 0;
+    uint64_t byte_length = 0;
+    CUdeviceptr multicast_base = 0;
+    CUdeviceptr table = 0;  // device copy of {peer bases[8], peer flag blocks[8]}
+    int32_t max_blocks = 0;
+    iree_b200_executable_t* executable = nullptr;
+    CUfunction all_reduce_sum[3] = {nullptr, nullptr, nullptr};  // f16, bf16, f32
+  } symmetric;
+  std::atomic<uint64_t> symmetric_collectives{0}, nccl_collectives{0};
 };
 
 struct iree_b200_semaphore_t : b200hal::RefCounted {

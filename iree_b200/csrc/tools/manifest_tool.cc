@@ -7,8 +7,10 @@
 // kernels are compiled from.
 
 #include <cstdio>
+#include <initializer_list>
 
 #include "../kernels/attention_config.h"
+#include "../kernels/collective_config.h"
 #include "../kernels/gemm_config.h"
 
 using namespace b200;
@@ -38,6 +40,14 @@ int main() {
   emit(#NAME, "attention_kernels", THREADS, SMEM, CONSTANTS, BINDINGS);
 #include "../kernels/attention_exports.inc"
 #undef X
+  // Channel-launched kernels (not dispatch-ABI exports; see collective_kernels.cu).
+  for (const char* type : {"f16", "bf16", "f32"}) {
+    for (const char* path : {"nvls", "p2p"}) {
+      char name[96];
+      snprintf(name, sizeof(name), "iree_b200_all_reduce_sum_%s_%s", type, path);
+      emit(name, "collective_kernels", CollectiveConfig::kThreads, 0, 0, "1");
+    }
+  }
   printf("\n  ]\n}\n");
   return 0;
 }

@@ -83,6 +83,15 @@ class ChannelParams(Structure):
                 ("rank", c_int32), ("count", c_int32)]
 
 
+class SymmetricRegionParams(Structure):
+    _fields_ = [("byte_length", c_uint64), ("peer_bases", POINTER(c_uint64)),
+                ("multicast_base", c_uint64), ("peer_flag_blocks", POINTER(c_uint64)),
+                ("max_blocks", c_int32)]
+
+
+SYMMETRIC_FLAG_BYTES = 2048
+
+
 class MatmulSelection(Structure):
     _fields_ = [("export_ordinal", c_int32), ("workgroup_count", c_uint32 * 3),
                 ("constants", c_uint32 * 5)]
@@ -137,6 +146,8 @@ _STATUS_FUNCS = {
     "iree_b200_channel_provider_exchange_default_id": [c_int32, c_void_p],
     "iree_b200_channel_create": [c_void_p, POINTER(ChannelParams), POINTER(c_void_p)],
     "iree_b200_channel_split": [c_void_p, c_int32, c_int32, c_uint64, POINTER(c_void_p)],
+    "iree_b200_channel_attach_symmetric_region": [c_void_p, c_void_p,
+                                                  POINTER(SymmetricRegionParams)],
     "iree_b200_ops_create": [c_void_p, POINTER(c_void_p)],
     "iree_b200_ops_create_from_data": [c_void_p, c_void_p, c_size_t, POINTER(c_void_p)],
     "iree_b200_ops_set_reserved_sms": [c_void_p, c_int32],
@@ -182,6 +193,8 @@ _OTHER_FUNCS = {
     "iree_b200_semaphore_release": (None, [c_void_p]),
     "iree_b200_channel_retain": (None, [c_void_p]),
     "iree_b200_channel_release": (None, [c_void_p]),
+    "iree_b200_channel_query_collective_counts": (None, [c_void_p, POINTER(c_uint64),
+                                                         POINTER(c_uint64)]),
     "iree_b200_channel_query_rank_and_count": (None, [c_void_p, POINTER(c_int32),
                                                       POINTER(c_int32)]),
     "iree_b200_ops_builtin_executable_data": (c_void_p, [POINTER(c_size_t)]),
@@ -469,6 +482,20 @@ class Channel:
         buf = ctypes.create_string_buffer(CHANNEL_ID_SIZE)
         check(lib().iree_b200_channel_id_create(buf))
         return buf.raw
+
+    def attach_symmetric_region(self, executable, byte_length: int, peer_bases, peer_flag_blocks,
+                                multicast_base: int = 0, max_blocks: int = 0):
+        """In-place all_reduce(sum) inside the region then runs on the NVLink kernels."""
+        n = len(peer_bases)
+        bases = (c_uint64 * n)(*peer_bases)
+        flags = (c_uint64 * n)(*peer_flag_blocks)
+        p = SymmetricRegionParams(byte_length, bases, multicast_base, flags, max_blocks)
+        check(lib().iree_b200_channel_attach_symmetric_region(self._h, executable._h, byref(p)))
+
+    def collective_counts(self):
+        a, b = c_uint64(), c_uint64()
+        lib().iree_b200_channel_query_collective_counts(self._h, byref(a), byref(b))
+        return {"symmetric": a.value, "nccl": b.value}
 
     def rank_and_count(self):
         r, c = c_int32(), c_int32()

@@ -19,6 +19,14 @@ decode) run bench_attention_decode 300 python bench.py --workload attention_deco
 ncu)
   run ncu_launches 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_matmul_bf16.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline
   run ncu_decode 400 ncu --set full --clock-control none --import-source on -k regex:decode_cluster -c 1 -o $O/${TAG}_attn_decode_cluster -f python bench.py --workload attention_decode --steps 3 --warmup 3 --no-cpu-baseline ;;
+symcheck)
+  N=$(nvidia-smi -L | wc -l)
+  run symcheck 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 tools/symmetric_check.py ;;
+tp)
+  N=$(nvidia-smi -L | wc -l)
+  for c in symmetric nccl; do
+    run bench_tp_${c}_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29542 bench.py --gpus $N --workload tp_decoder_layer --collective $c --steps 50 --warmup 5
+  done ;;
 esac; done
 grep -h '^{' $O/${TAG}_bench_*.log 2>/dev/null | python -c "
 import sys, json

@@ -1,0 +1,162 @@
+"""Multi-GPU check + timing of the symmetric-region all-reduce (run under torchrun):
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+      --master-port 29541 tools/symmetric_check.py [--mib 64]
+
+Parity: in-place all_reduce(sum) recorded through iree_b200_command_buffer_collective on a
+channel with an attached symmetric region (NVLS kernels, then the peer load/store kernels)
+against the exact expected sum (small-integer inputs, so every summation order gives the
+same bits) — f16 / bf16 / f32, ragged sizes, sub-ranges, back-to-back launches (flag reuse).
+Timing: the same collective through NCCL (a channel with no region) and through both kernel
+families, CUDA events, max over ranks. Rank 0 prints one JSON line.
+"""
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--mib", type=int, default=64)
+    ap.add_argument("--iters", type=int, default=20)
+    args = ap.parse_args()
+    import torch
+    import torch.distributed as dist
+    rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from iree_b200 import hal, symmetric
+
+    stream = torch.cuda.Stream()
+    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
+    ops = hal.Ops(dev)
+
+    def make_channel():
+        ids = [hal.Channel.create_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        return hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
+
+    ch_nvls, ch_p2p, ch_nccl = make_channel(), make_channel(), make_channel()
+    data_bytes = args.mib << 20
+    region = symmetric.SymmetricRegion(data_bytes, torch.device("cuda", local), flag_blocks=2)
+    have_mc = region.multicast_base != 0
+    if have_mc:
+        region.attach(ch_nvls, ops.executable, flag_block=0, use_multicast=True)
+    region.attach(ch_p2p, ops.executable, flag_block=1, use_multicast=False)
+    buf = dev.import_buffer(region.local_base, region.data_bytes)
+    plain = torch.empty(data_bytes, dtype=torch.uint8, device="cuda")
+    plain_buf = dev.import_buffer(plain.data_ptr(), data_bytes)
+
+    def all_reduce(channel, buffer, et, byte_offset, count, repeat=1):
+        es = 4 if et == "f32" else 2
+        op = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, et)
+        cb = hal.CommandBuffer(dev).begin()
+        for _ in range(repeat):
+            ref = buffer.ref(byte_offset, count * es)
+            cb.collective(channel, op, 0, ref, ref, count)
+            cb.barrier()
+        cb.end()
+        return cb
+
+    failures = []
+    dtypes = {"f16": torch.float16, "bf16": torch.bfloat16, "f32": torch.float32}
+    families = ([("nvls", ch_nvls)] if have_mc else []) + [("p2p", ch_p2p)]
+    with torch.cuda.stream(stream):
+        for fam, ch in families:
+            for et, dt in dtypes.items():
+                es = dt.itemsize
+                for byte_offset, count in ((0, 8 * 1024), (4096, (1 << 20) + 8 * 3),
+                                           (16, 8), (1 << 20, (3 << 20) // es)):
+                    if byte_offset + count * es > data_bytes:
+                        continue
+                    view = region.view(byte_offset, (count,), dt)
+                    idx = torch.arange(count, device="cuda")
+                    # Values in [-3, 3] * (rank + 1): sums stay small integers -> exact.
+                    mine = (((idx * 7 + 3) % 7) - 3).to(torch.float32) * (rank + 1)
+                    view.copy_(mine.to(dt))
+                    guard_lo = region.view(0, (byte_offset // es,), dt).clone() if byte_offset else None
+                    dist.barrier()
+                    before = ch.collective_counts()["symmetric"]
+                    dev.execute(all_reduce(ch, buf, et, byte_offset, count))
+                    dev.wait_idle()
+                    want = (((idx * 7 + 3) % 7) - 3).to(torch.float32) * (world * (world + 1) // 2)
+                    ok = torch.equal(view.to(torch.float32), want)
+                    ok = ok and ch.collective_counts()["symmetric"] == before + 1
+                    if guard_lo is not None:
+                        ok = ok and torch.equal(region.view(0, (byte_offset // es,), dt), guard_lo)
+                    if not ok:
+                        failures.append(f"{fam} {et} offset {byte_offset} count {count}")
+                    dist.barrier()
+            # Back-to-back launches reuse the flag words: x -> W*x -> W*W*x.
+            view = region.view(0, (1 << 16,), torch.float32)
+            view.fill_(1.0)
+            dist.barrier()
+            dev.execute(all_reduce(ch, buf, "f32", 0, 1 << 16, repeat=3))
+            dev.wait_idle()
+            if not bool((view == float(world ** 3)).all()):
+                failures.append(f"{fam} back-to-back")
+            dist.barrier()
+        # A range outside the region (or an unaligned one) must fall back to NCCL.
+        t = torch.ones(1024, dtype=torch.float32, device="cuda")
+        tb = dev.import_buffer(t.data_ptr(), 4096)
+        before = ch_p2p.collective_counts()
+        dev.execute(all_reduce(ch_p2p, tb, "f32", 0, 1024))
+        dev.wait_idle()
+        after = ch_p2p.collective_counts()
+        if not (bool((t == float(world)).all()) and after["nccl"] == before["nccl"] + 1):
+            failures.append("fallback to NCCL outside the region")
+
+        # ---- timing ----
+        def time_it(channel, buffer):
+            count = data_bytes // 2
+            cb = all_reduce(channel, buffer, "bf16", 0, count)
+            for _ in range(3):
+                dev.execute(cb)
+            dev.wait_idle()
+            dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(args.iters):
+                dev.execute(cb)
+            e1.record(stream)
+            dev.wait_idle()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / args.iters], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        region.tensor.zero_()
+        plain.zero_()
+        times = {"nccl": time_it(ch_nccl, plain_buf)}
+        if have_mc:
+            times["nvls"] = time_it(ch_nvls, buf)
+        times["p2p"] = time_it(ch_p2p, buf)
+    flag_ok = True
+    flags = region.tensor[region.data_bytes:]
+    torch.cuda.synchronize()
+    dist.barrier()
+    flag_ok = bool((flags == 0).all())
+    if not flag_ok:
+        failures.append("flag words not back to zero")
+    bad = torch.tensor([len(failures)], device="cuda")
+    dist.all_reduce(bad)
+    if rank == 0:
+        print(json.dumps({
+            "world": world, "multicast": have_mc, "failures": failures,
+            "failing_ranks_total": int(bad.item()), "all_reduce_mib": args.mib, "dtype": "bf16",
+            "ms": times,
+            "algbw_gbs": {k: data_bytes / (v * 1e-3) / 1e9 for k, v in times.items()}}), flush=True)
+    else:
+        for f in failures:
+            print(f"rank {rank}: FAILED {f}", flush=True)
+    dist.destroy_process_group()
+    sys.exit(1 if failures else 0)
+
+
+if __name__ == "__main__":
+    main()
