@@ -69,7 +69,7 @@ def test_builtin_executable_is_valid_cda1():
     assert "iree_b200_matmul_bf16_f32" in names and "iree_b200_matmul_generic_i8_i32" in names
     assert "iree_b200_attention_prefill_f16" in names and "iree_b200_attention_decode_merge_bf16" in names
     for e in exe.exports:
-        assert list(e.block_dims) in ([256, 1, 1], [384, 1, 1], [128, 1, 1], [288, 1, 1], [512, 1, 1])
+        assert list(e.block_dims) in ([256, 1, 1], [384, 1, 1], [128, 1, 1], [288, 1, 1], [1024, 1, 1])
         assert e.block_shared_memory_size <= 227 * 1024
         assert e.constant_count <= 64 and len(e.binding_flags) <= 16
     assert all(m[:4] == b"\x7fELF" for m in exe.modules)  # cubins, not PTX (no JIT at load)

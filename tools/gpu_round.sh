@@ -22,6 +22,9 @@ ncu)
 symcheck)
   N=$(nvidia-smi -L | wc -l)
   run symcheck 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 tools/symmetric_check.py ;;
+symcheck64)
+  N=$(nvidia-smi -L | wc -l)
+  run symcheck64 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29543 tools/symmetric_check.py --max-blocks 64 ;;
 tp)
   N=$(nvidia-smi -L | wc -l)
   for c in symmetric nccl; do

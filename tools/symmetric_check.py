@@ -24,6 +24,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mib", type=int, default=64)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--max-blocks", type=int, default=0, help="CTAs per collective (0 = default 16)")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -46,8 +47,10 @@ def main():
     region = symmetric.SymmetricRegion(data_bytes, torch.device("cuda", local), flag_blocks=2)
     have_mc = region.multicast_base != 0
     if have_mc:
-        region.attach(ch_nvls, ops.executable, flag_block=0, use_multicast=True)
-    region.attach(ch_p2p, ops.executable, flag_block=1, use_multicast=False)
+        region.attach(ch_nvls, ops.executable, flag_block=0, use_multicast=True,
+                      max_blocks=args.max_blocks)
+    region.attach(ch_p2p, ops.executable, flag_block=1, use_multicast=False,
+                  max_blocks=args.max_blocks)
     buf = dev.import_buffer(region.local_base, region.data_bytes)
     plain = torch.empty(data_bytes, dtype=torch.uint8, device="cuda")
     plain_buf = dev.import_buffer(plain.data_ptr(), data_bytes)
@@ -112,8 +115,8 @@ def main():
             failures.append("fallback to NCCL outside the region")
 
         # ---- timing ----
-        def time_it(channel, buffer):
-            count = data_bytes // 2
+        def time_it(channel, buffer, nbytes=data_bytes):
+            count = nbytes // 2
             cb = all_reduce(channel, buffer, "bf16", 0, count)
             for _ in range(3):
                 dev.execute(cb)
@@ -136,6 +139,12 @@ def main():
         if have_mc:
             times["nvls"] = time_it(ch_nvls, buf)
         times["p2p"] = time_it(ch_p2p, buf)
+        # The tensor-parallel layer's chunk size ([2048, 4096] bf16).
+        chunk = min(16 << 20, data_bytes)
+        times_chunk = {"nccl": time_it(ch_nccl, plain_buf, chunk)}
+        if have_mc:
+            times_chunk["nvls"] = time_it(ch_nvls, buf, chunk)
+        times_chunk["p2p"] = time_it(ch_p2p, buf, chunk)
     flag_ok = True
     flags = region.tensor[region.data_bytes:]
     torch.cuda.synchronize()
@@ -150,7 +159,9 @@ def main():
             "world": world, "multicast": have_mc, "failures": failures,
             "failing_ranks_total": int(bad.item()), "all_reduce_mib": args.mib, "dtype": "bf16",
             "ms": times,
-            "algbw_gbs": {k: data_bytes / (v * 1e-3) / 1e9 for k, v in times.items()}}), flush=True)
+            "algbw_gbs": {k: data_bytes / (v * 1e-3) / 1e9 for k, v in times.items()},
+            "max_blocks": args.max_blocks or 16,
+            "ms_16mib": times_chunk}), flush=True)
     else:
         for f in failures:
             print(f"rank {rank}: FAILED {f}", flush=True)
