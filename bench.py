@@ -428,7 +428,7 @@ def run_ours(args):
     stream = torch.cuda.Stream()
     tp = args.workload == "tp_decoder_layer"
     dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
-                     overlap_collectives=tp and world > 1)
+                     overlap_collectives=(2 if args.no_range_fusion else 1) if tp and world > 1 else 0)
     ops = hal.Ops(dev)
     if tp:
         channel = None
@@ -444,7 +444,8 @@ def run_ours(args):
                 from iree_b200 import symmetric
                 region = symmetric.SymmetricRegion(
                     2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
-                region.attach(channel, ops.executable, max_blocks=max(1, min(64, args.reserved_sms)))
+                blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
+                region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
         TpLayerStep.CHUNKS = args.tp_chunks
         first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank, region=region)
         info = first.describe()
@@ -638,6 +639,11 @@ def main():
     ap.add_argument("--collective", default="symmetric", choices=["symmetric", "nccl"],
                     help="tp_decoder_layer, N>1: all-reduce through the symmetric-region NVLink "
                          "kernels (default) or through NCCL")
+    ap.add_argument("--no-range-fusion", action="store_true",
+                    help="tp_decoder_layer: one all-reduce launch per chunk instead of one "
+                         "persistent launch per row-parallel GEMM")
+    ap.add_argument("--ar-blocks", type=int, default=0,
+                    help="tp_decoder_layer: CTAs per symmetric all-reduce (0 = the reserved SMs)")
     ap.add_argument("--tp-chunks", type=int, default=4,
                     help="tp_decoder_layer: token chunks per row-parallel GEMM + all-reduce")
     args = ap.parse_args()

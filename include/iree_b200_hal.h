@@ -100,7 +100,13 @@ typedef struct iree_b200_device_params_t {
   uint64_t external_dispatch_stream;
   // Collectives are issued on a second, high-priority stream and joined with events so
   // they can overlap independent dispatches (the reference issues NCCL on the single
-  // dispatch stream, nccl_channel.c:542-588). 0 = reference behaviour.
+  // dispatch stream, nccl_channel.c:542-588). 0 = reference behaviour. 1 = overlap; in
+  // addition, symmetric-region all-reduces of equally sized, equally spaced ranges that
+  // alternate with their producer dispatches between two barriers (GEMM chunk, all-reduce,
+  // GEMM chunk, all-reduce, ...) are issued as ONE persistent launch: the kernel starts
+  // behind the first producer and each later range is released by a stream write behind
+  // its producer, so the ranks meet once per range instead of twice per launch and there
+  // are no launch gaps. 2 = overlap without that fusion (diagnostics).
   int32_t overlap_collectives;
   int32_t reserved1;
 } iree_b200_device_params_t;

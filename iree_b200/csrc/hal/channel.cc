@@ -243,7 +243,7 @@ iree_b200_status_t iree_b200_channel_attach_symmetric_region(
     return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "max_blocks %d out of range [0, %d]",
                        params->max_blocks, Cfg::kMaxBlocks);
   }
-  uint64_t table[2 * Cfg::kMaxWorld] = {0};
+  uint64_t table[2 * Cfg::kMaxWorld + 2] = {0};  // + the "range ready" word, zeroed
   for (int r = 0; r < channel->count; ++r) {
     if (!params->peer_bases[r] || !params->peer_flag_blocks[r] || params->peer_bases[r] % 16 ||
         params->peer_flag_blocks[r] % 4) {

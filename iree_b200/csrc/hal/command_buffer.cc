@@ -268,7 +268,11 @@ bool symmetric_all_reduce_eligible(const Command& c, int* out_type_index) {
          c.target - sym.local_base <= sym.byte_length - bytes;
 }
 
-iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index, CUstream stream) {
+// |chunks| > 1: one launch covers |chunks| equally sized ranges |chunk_stride| bytes apart;
+// range c (c >= 1) is released by writing ready_base + c to the channel's ready word.
+iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index, CUstream stream,
+                                               uint32_t chunks = 1, uint64_t chunk_stride = 0,
+                                               uint32_t ready_base = 0) {
   using Cfg = b200::CollectiveConfig;
   iree_b200_channel_t* channel = c.channel;
   const auto& sym = channel->symmetric;
@@ -277,13 +281,15 @@ iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index,
   uint64_t table = sym.table, multicast = sym.multicast_base;
   uint64_t byte_offset = c.target - sym.local_base;
   uint64_t vectors = c.element_count * collective_element_size(type) / 16;
+  uint64_t ready = sym.table + 2 * Cfg::kMaxWorld * sizeof(uint64_t);
   int rank = channel->rank, world = channel->count;
   // Every rank derives the same grid from the same element count (the flag words are per
   // block index, so the grids must agree across ranks).
   const uint64_t per_rank = (vectors + world - 1) / world;
   const uint64_t want = (per_rank + Cfg::kThreads * Cfg::kUnroll - 1) / (Cfg::kThreads * Cfg::kUnroll);
   const uint32_t blocks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(want, sym.max_blocks));
-  void* params[] = {&table, &multicast, &byte_offset, &vectors, &rank, &world};
+  void* params[] = {&table, &multicast, &byte_offset, &vectors, &chunks, &chunk_stride,
+                    &ready,  &ready_base, &rank,       &world};
   B200_CU(cu, cuLaunchKernel(sym.all_reduce_sum[type_index], blocks, 1, 1, Cfg::kThreads, 1, 1, 0,
                              stream, params, nullptr));
   return IREE_B200_STATUS_OK;
@@ -359,9 +365,82 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
     B200_CU(cu, cuEventCreate(&fork_event, CU_EVENT_DISABLE_TIMING));
     B200_CU(cu, cuEventCreate(&join_event, CU_EVENT_DISABLE_TIMING));
   }
+  // Range fusion (include/iree_b200_hal.h, overlap_collectives): chunk_of[i] = 0 for the
+  // leader of a fused group (chunks_of[i] ranges, stride_of[i] bytes apart), c >= 1 for the
+  // collective that releases range c of its group, -1 otherwise.
+  const size_t n = cb->commands.size();
+  std::vector<int32_t> chunk_of(n, -1), type_of(n, -1);
+  std::vector<size_t> leader_of(n, 0);
+  std::vector<uint32_t> base_of(n, 0);
+  std::vector<uint32_t> chunks_of(n, 0);
+  std::vector<uint64_t> stride_of(n, 0);
+  if (device->collective_stream && device->params.overlap_collectives == 1) {
+    auto single_eligible = [&](size_t i, int* type) {
+      const Command& c = cb->commands[i];
+      return c.kind == CommandKind::kCollective &&
+             (i == 0 || cb->commands[i - 1].kind != CommandKind::kCollective) &&
+             (i + 1 == n || cb->commands[i + 1].kind != CommandKind::kCollective) &&
+             symmetric_all_reduce_eligible(c, type);
+    };
+    for (size_t i = 0; i < n; ++i) {
+      int type = -1;
+      if (chunk_of[i] != -1 || !single_eligible(i, &type)) continue;
+      const Command& lead = cb->commands[i];
+      std::vector<size_t> members{i};
+      uint64_t stride = 0;
+      for (size_t j = i + 1; j < n && members.size() < 64; ++j) {
+        const Command& c = cb->commands[j];
+        if (c.kind == CommandKind::kBarrier) break;
+        if (c.kind != CommandKind::kCollective) continue;
+        int type2 = -1;
+        const Command& prev = cb->commands[members.back()];
+        if (!single_eligible(j, &type2) || type2 != type || c.channel != lead.channel ||
+            c.op != lead.op || c.element_count != lead.element_count || c.target <= prev.target) {
+          break;
+        }
+        const uint64_t d = c.target - prev.target;
+        if (members.size() == 1) stride = d;
+        if (d != stride) break;
+        members.push_back(j);
+      }
+      if (members.size() < 2) continue;
+      for (size_t m = 0; m < members.size(); ++m) {
+        chunk_of[members[m]] = (int32_t)m;
+        leader_of[members[m]] = i;
+      }
+      chunks_of[i] = (uint32_t)members.size();
+      stride_of[i] = stride;
+      type_of[i] = type;
+    }
+  }
   iree_b200_status_t status = IREE_B200_STATUS_OK;
   auto run = [&]() -> iree_b200_status_t {
-    for (const Command& c : cb->commands) {
+    for (size_t index = 0; index < n; ++index) {
+      const Command& c = cb->commands[index];
+      if (c.kind == CommandKind::kCollective && chunk_of[index] == 0) {
+        // Leader: fork behind producer 0 and launch the persistent kernel for all ranges.
+        auto& sym = c.channel->symmetric;
+        const uint32_t ready_base = base_of[index] = sym.ready_sequence;
+        sym.ready_sequence += chunks_of[index] - 1;
+        B200_CU(cu, cuEventRecord(fork_event, device->dispatch_stream));
+        B200_CU(cu, cuStreamWaitEvent(device->collective_stream, fork_event, 0));
+        B200_RETURN_IF_ERROR(launch_symmetric_all_reduce(c, type_of[index],
+                                                         device->collective_stream, chunks_of[index],
+                                                         stride_of[index], ready_base));
+        pending_join = true;
+        c.channel->symmetric_collectives.fetch_add(1);
+        continue;
+      }
+      if (c.kind == CommandKind::kCollective && chunk_of[index] > 0) {
+        // Range |chunk_of| is complete on this rank once everything queued so far is.
+        const CUdeviceptr ready = c.channel->symmetric.table +
+                                  2 * b200::CollectiveConfig::kMaxWorld * sizeof(uint64_t);
+        B200_CU(cu, cuStreamWriteValue32(device->dispatch_stream, ready,
+                                         base_of[leader_of[index]] + (uint32_t)chunk_of[index],
+                                         CU_STREAM_WRITE_VALUE_DEFAULT));
+        c.channel->symmetric_collectives.fetch_add(1);
+        continue;
+      }
       if (c.kind == CommandKind::kCollective) {
         batch.push_back(&c);
         continue;

@@ -66,6 +66,7 @@ iree_b200_status_t make_status(iree_b200_status_t code, const char* fmt, ...)
   X(cuStreamDestroy)               \
   X(cuStreamSynchronize)           \
   X(cuStreamWaitEvent)             \
+  X(cuStreamWriteValue32)          \
   X(cuCtxGetStreamPriorityRange)   \
   X(cuEventCreate)                 \
   X(cuEventDestroy)                \
@@ -266,7 +267,9 @@ struct iree_b200_channel_t : b200hal::RefCounted {
     CUdeviceptr local_base = 0;
     uint64_t byte_length = 0;
     CUdeviceptr multicast_base = 0;
-    CUdeviceptr table = 0;  // device copy of {peer bases[8], peer flag blocks[8]}
+    CUdeviceptr table = 0;  // device copy of {peer bases[8], peer flag blocks[8]}, then the
+                            // "range ready" word of fused multi-range launches (offset 128)
+    uint32_t ready_sequence = 0;  // last value written to / expected in that word
     int32_t max_blocks = 0;
     iree_b200_executable_t* executable = nullptr;
     CUfunction all_reduce_sum[3] = {nullptr, nullptr, nullptr};  // f16, bf16, f32

@@ -21,8 +21,15 @@
 //   table       device pointer to {bases[8], flag_blocks[8]} (this rank's mapping of every
 //               rank's region / flag block)
 //   multicast   multicast mapping of the region (nvls only; 0 otherwise)
-//   byte_offset of the range inside the region (multiple of 16)
-//   vectors     number of 16-byte vectors in the range
+//   byte_offset of the (first) range inside the region (multiple of 16)
+//   vectors     number of 16-byte vectors in a range
+//   chunks, chunk_stride   one launch can cover |chunks| equally sized ranges |chunk_stride|
+//               bytes apart whose producers finish one after the other: range 0 is ready at
+//               launch, range c once the word at |ready| has reached ready_base + c (the
+//               launch layer writes it with cuStreamWriteValue32 behind producer c on the
+//               dispatch stream). The ranks meet once per range and once at the very end,
+//               instead of twice per launch, and there is no launch gap between ranges.
+//   ready, ready_base
 //   rank, world
 
 #include <cuda_bf16.h>
@@ -185,11 +192,10 @@ __device__ __forceinline__ uint4 round_result(const float (&acc)[8]) {
 
 // Slice of rank r: vectors [r*per, min(vectors, (r+1)*per)), per = ceil(vectors / world).
 template <int kType, bool kNvls>
-__device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict__ table,
-                                                    uint64_t multicast, uint64_t byte_offset,
-                                                    uint64_t vectors, int rank, int world) {
+__device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table,
+                                             uint64_t multicast, uint64_t byte_offset,
+                                             uint64_t vectors, int rank, int world) {
   constexpr int kUnroll = CollectiveConfig::kUnroll;
-  meet_all_ranks(table, rank, world);
   const uint64_t per = (vectors + world - 1) / world;
   const uint64_t begin = min(vectors, (uint64_t)rank * per);
   const uint64_t end = min(vectors, begin + per);
@@ -229,6 +235,39 @@ __device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict_
       }
     }
   }
+}
+
+__device__ __forceinline__ void wait_ready(const uint32_t* ready, uint32_t value) {
+  if (threadIdx.x == 0) {
+    const long long start = clock64();
+    for (;;) {
+      uint32_t now;
+      asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(now) : "l"(ready) : "memory");
+      if ((int32_t)(now - value) >= 0) break;
+      if (clock64() - start > kWatchdogCycles) {
+        printf("b200 watchdog: all-reduce range never became ready (block %d, want %u, have %u)\n",
+               (int)blockIdx.x, value, now);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+template <int kType, bool kNvls>
+__device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict__ table,
+                                                    uint64_t multicast, uint64_t byte_offset,
+                                                    uint64_t vectors, uint32_t chunks,
+                                                    uint64_t chunk_stride, const uint32_t* ready,
+                                                    uint32_t ready_base, int rank, int world) {
+  for (uint32_t c = 0; c < chunks; ++c) {
+    if (c > 0) wait_ready(ready, ready_base + c);
+    // Every rank's producer of range c has finished.
+    meet_all_ranks(table, rank, world);
+    reduce_slice<kType, kNvls>(table, multicast, byte_offset + c * chunk_stride, vectors, rank,
+                               world);
+  }
+  // Every slice of every range has landed everywhere.
   __threadfence_system();
   meet_all_ranks(table, rank, world);
 }
@@ -237,18 +276,22 @@ __device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict_
 
 #define B200_ALL_REDUCE(SUFFIX, TYPE)                                                           \
   extern "C" __global__ void __launch_bounds__(b200::CollectiveConfig::kThreads)                \
-      iree_b200_all_reduce_sum_##SUFFIX##_nvls(const void* table, uint64_t multicast,           \
-                                               uint64_t byte_offset, uint64_t vectors,          \
-                                               int rank, int world) {                           \
+      iree_b200_all_reduce_sum_##SUFFIX##_nvls(                                                 \
+          const void* table, uint64_t multicast, uint64_t byte_offset, uint64_t vectors,        \
+          uint32_t chunks, uint64_t chunk_stride, const uint32_t* ready, uint32_t ready_base,   \
+          int rank, int world) {                                                                \
     all_reduce_sum_body<TYPE, true>(static_cast<const PeerTable*>(table), multicast,            \
-                                    byte_offset, vectors, rank, world);                         \
+                                    byte_offset, vectors, chunks, chunk_stride, ready,          \
+                                    ready_base, rank, world);                                   \
   }                                                                                             \
   extern "C" __global__ void __launch_bounds__(b200::CollectiveConfig::kThreads)                \
-      iree_b200_all_reduce_sum_##SUFFIX##_p2p(const void* table, uint64_t multicast,            \
-                                              uint64_t byte_offset, uint64_t vectors, int rank, \
-                                              int world) {                                      \
+      iree_b200_all_reduce_sum_##SUFFIX##_p2p(                                                  \
+          const void* table, uint64_t multicast, uint64_t byte_offset, uint64_t vectors,        \
+          uint32_t chunks, uint64_t chunk_stride, const uint32_t* ready, uint32_t ready_base,   \
+          int rank, int world) {                                                                \
     all_reduce_sum_body<TYPE, false>(static_cast<const PeerTable*>(table), multicast,           \
-                                     byte_offset, vectors, rank, world);                        \
+                                     byte_offset, vectors, chunks, chunk_stride, ready,         \
+                                     ready_base, rank, world);                                  \
   }
 
 B200_ALL_REDUCE(f16, kF16)

@@ -28,7 +28,17 @@ symcheck64)
 tp)
   N=$(nvidia-smi -L | wc -l)
   for c in symmetric nccl; do
-    run bench_tp_${c}_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29542 bench.py --gpus $N --workload tp_decoder_layer --collective $c --steps 50 --warmup 5
+    run bench_tp_${c}_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29542 bench.py --gpus $N --workload tp_decoder_layer --collective $c --steps 50 --warmup 5 --e2e-steps 2
+  done ;;
+tpnofuse)
+  N=$(nvidia-smi -L | wc -l)
+  run bench_tp_nofuse_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29544 bench.py --gpus $N --workload tp_decoder_layer --collective symmetric --no-range-fusion --steps 50 --warmup 5 --e2e-steps 2 ;;
+tpsweep)
+  N=$(nvidia-smi -L | wc -l)
+  i=0
+  for cfg in "--tp-chunks 1 --reserved-sms 0" "--tp-chunks 2 --reserved-sms 32" "--tp-chunks 2 --reserved-sms 16" ; do
+    i=$((i+1))
+    run bench_tp_sweep${i}_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2955$i bench.py --gpus $N --workload tp_decoder_layer --collective symmetric --steps 50 --warmup 5 --e2e-steps 2 $cfg
   done ;;
 esac; done
 grep -h '^{' $O/${TAG}_bench_*.log 2>/dev/null | python -c "

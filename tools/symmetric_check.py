@@ -34,7 +34,8 @@ def main():
     from iree_b200 import hal, symmetric
 
     stream = torch.cuda.Stream()
-    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
+    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
+                     overlap_collectives=True)
     ops = hal.Ops(dev)
 
     def make_channel():
@@ -104,6 +105,31 @@ def main():
             if not bool((view == float(world ** 3)).all()):
                 failures.append(f"{fam} back-to-back")
             dist.barrier()
+            # Range fusion: producer (fill), all-reduce, producer, all-reduce, ... between two
+            # barriers becomes one persistent launch; range c is released behind producer c.
+            import struct
+            chunks, chunk_elems = 4, 1 << 20
+            region.tensor[:chunks * chunk_elems * 4].zero_()
+            dist.barrier()
+            op = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, "f32")
+            cb = hal.CommandBuffer(dev).begin()
+            for c in range(chunks):
+                ref = buf.ref(c * chunk_elems * 4, chunk_elems * 4)
+                cb.fill(ref, struct.pack("<f", float((rank + 1) * (c + 1))))
+                cb.collective(ch, op, 0, ref, ref, chunk_elems)
+            cb.barrier()
+            cb.end()
+            for rep in range(2):   # twice: the ready word keeps counting up across replays
+                before = ch.collective_counts()["symmetric"]
+                dev.execute(cb)
+                dev.wait_idle()
+                got = region.view(0, (chunks, chunk_elems), torch.float32)
+                want = torch.arange(1, chunks + 1, device="cuda", dtype=torch.float32) \
+                    * (world * (world + 1) // 2)
+                if not (torch.equal(got, want[:, None].expand(chunks, chunk_elems)) and
+                        ch.collective_counts()["symmetric"] == before + chunks):
+                    failures.append(f"{fam} fused ranges (replay {rep})")
+                dist.barrier()
         # A range outside the region (or an unaligned one) must fall back to NCCL.
         t = torch.ones(1024, dtype=torch.float32, device="cuda")
         tb = dev.import_buffer(t.data_ptr(), 4096)
