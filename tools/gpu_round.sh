@@ -36,7 +36,7 @@ tpnofuse)
 tpsweep)
   N=$(nvidia-smi -L | wc -l)
   i=0
-  for cfg in "--tp-chunks 1 --reserved-sms 0" "--tp-chunks 2 --reserved-sms 32" "--tp-chunks 2 --reserved-sms 16" ; do
+  for cfg in "--tp-chunks 4 --reserved-sms 16" "--tp-chunks 4 --reserved-sms 32" "--tp-chunks 8 --reserved-sms 24" ; do
     i=$((i+1))
     run bench_tp_sweep${i}_n$N 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2955$i bench.py --gpus $N --workload tp_decoder_layer --collective symmetric --steps 50 --warmup 5 --e2e-steps 2 $cfg
   done ;;
