@@ -39,6 +39,7 @@ MATMUL_WORKLOADS = {
     "matmul_bf16": ("matmul", "bf16", 1, 8192, 8192, 8192),
     "matmul_i8": ("matmul", "i8", 1, 8192, 8192, 8192),
     "matmul_f16": ("matmul", "f16", 1, 8192, 8192, 8192),
+    "matmul_f8": ("matmul", "f8e4m3fn", 1, 8192, 8192, 8192),
     "matmul_bf16_4096": ("matmul", "bf16", 1, 4096, 4096, 4096),
     "batch_matmul": ("batch_matmul", "bf16", 64, 2048, 2048, 2048),
 }
@@ -184,7 +185,7 @@ def barrier(world: int):
 
 def algorithmic(op, et, batch, M, N, K):
     """(flop, bytes) per dispatch: SURVEY.md §8(d) — read-once / write-once operands."""
-    es = 1 if et == "i8" else 2
+    es = 2 if et in ("f16", "bf16") else 1
     return 2.0 * batch * M * N * K, float(batch) * (M * K * es + K * N * es + M * N * 4)
 
 
@@ -195,6 +196,11 @@ def synth_matmul_inputs(torch, et, batch, M, N, K, seed):
         a = torch.randint(-128, 128, (batch, M, K), dtype=torch.int8, device="cuda", generator=g)
         b = torch.randint(-128, 128, (batch, K, N), dtype=torch.int8, device="cuda", generator=g)
         c = torch.empty((batch, M, N), dtype=torch.int32, device="cuda")
+    elif et.startswith("f8"):
+        dt = torch.float8_e4m3fn if et == "f8e4m3fn" else torch.float8_e5m2
+        a = torch.randn((batch, M, K), device="cuda", generator=g).clamp_(-4, 4).to(dt)
+        b = torch.randn((batch, K, N), device="cuda", generator=g).clamp_(-4, 4).to(dt)
+        c = torch.empty((batch, M, N), dtype=torch.float32, device="cuda")
     else:
         dt = torch.bfloat16 if et == "bf16" else torch.float16
         a = torch.randn((batch, M, K), device="cuda", generator=g).clamp_(-4, 4).to(dt)
@@ -236,13 +242,14 @@ class MatmulStep:
 
     def describe(self):
         op, et, batch, M, N, K = self.spec
-        es = 1 if et == "i8" else 2
+        es = 2 if et in ("f16", "bf16") else 1
         flop = 2.0 * batch * M * N * K
         nbytes = float(batch) * (M * K * es + K * N * es + M * N * 4)
         return {"flop": flop, "bytes": nbytes, "bound": "tensor",
                 "workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU",
                 "dtype": {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
-                          "i8": "i8 (i32 accumulate)"}[et],
+                          "i8": "i8 (i32 accumulate)", "f8e4m3fn": "f8E4M3FN (f32 accumulate)",
+                          "f8e5m2": "f8E5M2 (f32 accumulate)"}[et],
                 "h2d": int(batch * (M * K + K * N) * es), "d2h": int(batch * M * N * 4),
                 "api": "iree_b200_ops_matmul_host (pinned host buffers)"}
 
@@ -554,7 +561,7 @@ def cpu_work(workload, rows):
         rows = min(rows, M)
         lhs = oracle.generate_random_matrix(et, (rows, K), 1)
         rhs = oracle.generate_random_matrix(et, (K, N), 2)
-        if oracle.ref_available():
+        if oracle.ref_available() and not et.startswith("f8"):
             # The reference's own CPU kernels (oracle/_ref, compiled from /root/reference).
             desc = (f"reference ukernel path iree_uk_pack+mmt4d+unpack (not the full llvm-cpu "
                     f"pipeline), OpenMP over M tiles, {et} M={rows} (of {batch}x{M}) N={N} K={K}")

@@ -30,10 +30,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SM_COUNT = 148  # B200; the count region runs on the host at dispatch time
 
-MLIR_TYPE = {"bf16": "bf16", "f16": "f16", "i8": "i8"}
-ACC_TYPE = {"bf16": "f32", "f16": "f32", "i8": "i32"}
+MLIR_TYPE = {"bf16": "bf16", "f16": "f16", "i8": "i8", "f8e4m3fn": "f8E4M3FN", "f8e5m2": "f8E5M2"}
+ACC_TYPE = {"bf16": "f32", "f16": "f32", "i8": "i32", "f8e4m3fn": "f32", "f8e5m2": "f32"}
 # Elements per 16 bytes: the TMA row-pitch guard.
-PITCH = {"bf16": 8, "f16": 8, "i8": 16}
+PITCH = {"bf16": 8, "f16": 8, "i8": 16, "f8e4m3fn": 16, "f8e5m2": 16}
 
 
 def load_manifest(objects_dir: str) -> dict:
@@ -233,7 +233,7 @@ def attention_rewriter(name: str) -> str:
 def generate(objects_dir: str) -> str:
     man = load_manifest(objects_dir)
     entries, matchers, rewriters, pairs = [], [], [], []
-    for et in ("bf16", "f16", "i8"):
+    for et in ("bf16", "f16", "i8", "f8e4m3fn", "f8e5m2"):
         acc = ACC_TYPE[et]
         for batched in (False, True):
             for big, suffix, g in ((True, "", 2), (False, "_1cta", 1)):

@@ -35,6 +35,10 @@ enum {
   IREE_B200_ELEMENT_TYPE_F16 = 1,
   IREE_B200_ELEMENT_TYPE_BF16 = 2,
   IREE_B200_ELEMENT_TYPE_F32 = 3,  // attention only (generic kernel; the reference's goldens)
+  // OCP 8-bit floats, matmul only, f32 accumulate and result (tcgen05 kind::f8f6f4;
+  // reference loops iree-e2e-matmul-test.cc:123-144, decoding base/internal/math.h:550-560).
+  IREE_B200_ELEMENT_TYPE_F8E4M3FN = 4,
+  IREE_B200_ELEMENT_TYPE_F8E5M2 = 5,
 };
 
 enum {

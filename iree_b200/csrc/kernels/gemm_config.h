@@ -18,9 +18,9 @@
 namespace b200 {
 
 // MMA kinds.
-enum : int { KIND_F16 = 0, KIND_I8 = 1 };
+enum : int { KIND_F16 = 0, KIND_I8 = 1, KIND_F8 = 2 /* tcgen05 kind::f8f6f4, 8-bit operands */ };
 
-enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_U8 = 0, FMT_S8 = 1 };
+enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1, FMT_U8 = 0, FMT_S8 = 1, FMT_E4M3 = 0, FMT_E5M2 = 1 };
 enum : uint32_t { CFMT_F16 = 0, CFMT_F32 = 1, CFMT_S32 = 2 };
 enum : uint32_t { MAJOR_K = 0, MAJOR_MN = 1 };
 
@@ -46,7 +46,7 @@ struct GemmConfig {
   static constexpr bool kBMajorK = kBMajorK_;
   static constexpr int kStages = kStages_;
 
-  static constexpr int kElemSize = (kKind == KIND_I8) ? 1 : 2;
+  static constexpr int kElemSize = (kKind == KIND_F16) ? 2 : 1;
   static constexpr int kBlockM = 128;                    // rows per CTA
   static constexpr int kTileM = kBlockM * kCtaGroup;     // rows per cluster tile
   static constexpr int kTileN = 256;                     // UMMA N

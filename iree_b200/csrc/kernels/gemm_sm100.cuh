@@ -345,7 +345,7 @@ constexpr iree_b200_tma_recipe_t make_gemm_recipe() {
   iree_b200_tma_recipe_t r = {};
   r.magic = IREE_B200_TMA_RECIPE_MAGIC;
   r.map_count = 3;
-  const uint32_t ab_type = Cfg::kKind == KIND_I8
+  const uint32_t ab_type = Cfg::kKind != KIND_F16
                                ? IREE_B200_TMA_U8
                                : (Cfg::kAbFmt == FMT_BF16 ? IREE_B200_TMA_BF16 : IREE_B200_TMA_F16);
   // A [batch, M, K]

@@ -28,6 +28,26 @@ constexpr int kTileK = 16;
 __device__ __forceinline__ float to_acc(__nv_bfloat16 v) { return __bfloat162float(v); }
 __device__ __forceinline__ float to_acc(__half v) { return __half2float(v); }
 __device__ __forceinline__ int32_t to_acc(int8_t v) { return (int32_t)v; }
+
+// OCP 8-bit floats as the reference decodes them (base/internal/math.h:300-362,550-560):
+// f8E5M2 is IEEE-like (it is the top byte of an f16), f8E4M3FN has no infinities and one
+// NaN mantissa (S.1111.111).
+struct F8E4M3FN {
+  uint8_t bits;
+};
+struct F8E5M2 {
+  uint8_t bits;
+};
+__device__ __forceinline__ float to_acc(F8E5M2 v) {
+  return __half2float(__ushort_as_half((unsigned short)((unsigned)v.bits << 8)));
+}
+__device__ __forceinline__ float to_acc(F8E4M3FN v) {
+  const uint32_t sign = (uint32_t)(v.bits & 0x80u) << 24;
+  const uint32_t e = (v.bits >> 3) & 0xfu, m = v.bits & 0x7u;
+  if (e == 0) return __uint_as_float(sign | __float_as_uint((float)m * 0.001953125f));  // m * 2^-9
+  if (e == 15 && m == 7) return __uint_as_float(sign | 0x7fc00000u);
+  return __uint_as_float(sign | ((e + 120u) << 23) | (m << 20));
+}
 template <typename T> __device__ __forceinline__ T from_acc(float v);
 template <> __device__ __forceinline__ __nv_bfloat16 from_acc<__nv_bfloat16>(float v) {
   return __float2bfloat16_rn(v);
@@ -147,4 +167,21 @@ extern "C" __global__ void __launch_bounds__(256)
                                     int flags) {
   (void)batch;
   matmul_generic_body<int8_t, int32_t>(lhs, rhs, out, M, N, K, flags);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_f8e4m3fn_f32(const F8E4M3FN* __restrict__ lhs,
+                                          const F8E4M3FN* __restrict__ rhs,
+                                          float* __restrict__ out, int M, int N, int K, int batch,
+                                          int flags) {
+  (void)batch;
+  matmul_generic_body<F8E4M3FN, float>(lhs, rhs, out, M, N, K, flags);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_f8e5m2_f32(const F8E5M2* __restrict__ lhs,
+                                        const F8E5M2* __restrict__ rhs, float* __restrict__ out,
+                                        int M, int N, int K, int batch, int flags) {
+  (void)batch;
+  matmul_generic_body<F8E5M2, float>(lhs, rhs, out, M, N, K, flags);
 }

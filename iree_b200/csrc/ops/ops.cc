@@ -21,8 +21,17 @@ namespace {
 
 enum MatmulFamily { kFamily2Cta = 0, kFamily1Cta = 1, kFamilyGeneric = 2, kFamilyCount = 3 };
 
-const char* const kTypeSuffix[3] = {"i8_i32", "f16_f32", "bf16_f32"};
-const char* const kTruncSuffix[3] = {"", "f16_f16", "bf16_bf16"};
+// Indexed by IREE_B200_ELEMENT_TYPE_*; f32 operands have no matmul export.
+constexpr int kTypeCount = 6;
+const char* const kTypeSuffix[kTypeCount] = {"i8_i32",  "f16_f32",      "bf16_f32",
+                                             nullptr,   "f8e4m3fn_f32", "f8e5m2_f32"};
+const char* const kTruncSuffix[kTypeCount] = {nullptr, "f16_f16", "bf16_bf16",
+                                              nullptr, nullptr,   nullptr};
+
+bool matmul_type_ok(int32_t t) { return t >= 0 && t < kTypeCount && kTypeSuffix[t]; }
+uint64_t matmul_elem_size(int32_t t) {
+  return (t == IREE_B200_ELEMENT_TYPE_F16 || t == IREE_B200_ELEMENT_TYPE_BF16) ? 2 : 1;
+}
 
 enum AttentionExport {
   kAttnPrefill = 0,
@@ -41,8 +50,8 @@ struct iree_b200_ops_t {
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
-  int32_t matmul_exports[3][2][kFamilyCount];
-  int32_t matmul_trunc_exports[3][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
+  int32_t matmul_exports[6][2][kFamilyCount];
+  int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
   int32_t attention_exports[4][8];
   // Host-buffer calls: staging arena, transfer streams and events (grow-only, reused).
   std::mutex host_mutex;
@@ -97,20 +106,23 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
     iree_b200_ops_release(ops);
     return make_status(status, "%s", message.c_str());
   }
-  for (int t = 0; t < 3; ++t) {
+  for (int t = 0; t < kTypeCount; ++t) {
     for (int nt = 0; nt < 2; ++nt) {
+      for (int f = 0; f < kFamilyCount; ++f) {
+        ops->matmul_exports[t][nt][f] = ops->matmul_trunc_exports[t][nt][f] = -1;
+      }
+      if (!kTypeSuffix[t]) continue;
       const std::string base = std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTypeSuffix[t];
       ops->matmul_exports[t][nt][kFamily2Cta] = lookup(ops->executable, base);
       ops->matmul_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta");
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
+      if (!kTruncSuffix[t]) continue;
       const std::string tbase =
           std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTruncSuffix[t];
-      ops->matmul_trunc_exports[t][nt][kFamily2Cta] = t ? lookup(ops->executable, tbase) : -1;
-      ops->matmul_trunc_exports[t][nt][kFamily1Cta] =
-          t ? lookup(ops->executable, tbase + "_1cta") : -1;
-      ops->matmul_trunc_exports[t][nt][kFamilyGeneric] =
-          t ? ops->matmul_exports[t][nt][kFamilyGeneric] : -1;
+      ops->matmul_trunc_exports[t][nt][kFamily2Cta] = lookup(ops->executable, tbase);
+      ops->matmul_trunc_exports[t][nt][kFamily1Cta] = lookup(ops->executable, tbase + "_1cta");
+      ops->matmul_trunc_exports[t][nt][kFamilyGeneric] = ops->matmul_exports[t][nt][kFamilyGeneric];
     }
   }
   for (int t = 0; t < 4; ++t) {
@@ -199,7 +211,7 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
                                                iree_b200_matmul_selection_t* out_selection) {
   B200_REQUIRE_ARG(ops && out_selection);
   memset(out_selection, 0, sizeof(*out_selection));
-  if (element_type < 0 || element_type > 2) {
+  if (!matmul_type_ok(element_type)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "unsupported matmul element type %d",
                        element_type);
   }
@@ -211,10 +223,9 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
   }
   const bool transpose_rhs = (flags & IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS) != 0;
   const bool truncate = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) != 0;
-  const int64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const int64_t es = (int64_t)matmul_elem_size(element_type);
   const int64_t out_es = truncate ? 2 : 4;
-  if (truncate && (element_type == IREE_B200_ELEMENT_TYPE_I8 ||
-                   (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE))) {
+  if (truncate && (!kTruncSuffix[element_type] || (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE))) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "TRUNCATE_RESULT applies to f16/bf16 without ACCUMULATE only");
   }
@@ -300,7 +311,7 @@ iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_c
                                                iree_b200_buffer_ref_t out) {
   B200_REQUIRE_ARG(ops && cb);
   B200_REQUIRE_ARG(lhs.buffer && rhs.buffer && out.buffer);
-  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const uint64_t es = matmul_elem_size(element_type);
   // Binding extents must cover the operands (the HAL validation layer's job,
   // hal/command_buffer_validation.c).
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
@@ -452,7 +463,7 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
                                          std::vector<iree_b200_command_buffer_t*>* cbs) {
   iree_b200_device_t* device = ops->device;
   const CudaSymbols* cu = device->cu;
-  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const uint64_t es = matmul_elem_size(element_type);
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const bool transpose_rhs = (flags & IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS) != 0;
   const bool accumulate = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) != 0;
@@ -559,10 +570,10 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
                                              uint32_t flags, const void* lhs, const void* rhs,
                                              void* out) {
   B200_REQUIRE_ARG(ops);
-  if (element_type < 0 || element_type > 2 || batch < 0 || M < 0 || N < 0 || K < 0) {
+  if (!matmul_type_ok(element_type) || batch < 0 || M < 0 || N < 0 || K < 0) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad matmul type or shape");
   }
-  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_I8 ? 1 : 2;
+  const uint64_t es = matmul_elem_size(element_type);
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const uint64_t bytes[3] = {(uint64_t)batch * M * K * es, (uint64_t)batch * K * N * es,
                              (uint64_t)batch * M * N * out_es};

@@ -18,8 +18,9 @@ from . import build as _build
 
 UINT64_MAX = (1 << 64) - 1
 
-I8, F16, BF16, F32 = 0, 1, 2, 3
-ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32}
+I8, F16, BF16, F32, F8E4M3FN, F8E5M2 = 0, 1, 2, 3, 4, 5
+ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "f8e4m3fn": F8E4M3FN,
+                 "f8e5m2": F8E5M2}
 
 MATMUL_ACCUMULATE = 1 << 0
 MATMUL_TRANSPOSE_RHS = 1 << 1

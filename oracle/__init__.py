@@ -17,9 +17,11 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
-I8, F16, BF16, F32, I32 = 0, 1, 2, 3, 4
-_TYPE_BY_NAME = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "i32": I32}
-_NP_STORAGE = {I8: np.int8, F16: np.uint16, BF16: np.uint16, F32: np.float32, I32: np.int32}
+I8, F16, BF16, F32, I32, F8E4M3FN, F8E5M2 = 0, 1, 2, 3, 4, 5, 6
+_TYPE_BY_NAME = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "i32": I32,
+                 "f8e4m3fn": F8E4M3FN, "f8e5m2": F8E5M2}
+_NP_STORAGE = {I8: np.int8, F16: np.uint16, BF16: np.uint16, F32: np.float32, I32: np.int32,
+               F8E4M3FN: np.uint8, F8E5M2: np.uint8}
 
 
 def build(force: bool = False) -> str:
@@ -45,6 +47,12 @@ def lib() -> ctypes.CDLL:
         _lib.oracle_f32_to_f16.restype = ctypes.c_uint16
         _lib.oracle_f32_to_bf16.argtypes = [ctypes.c_float]
         _lib.oracle_f32_to_f16.argtypes = [ctypes.c_float]
+        for name in ("oracle_f8e4m3fn_to_f32", "oracle_f8e5m2_to_f32"):
+            getattr(_lib, name).restype = ctypes.c_float
+            getattr(_lib, name).argtypes = [ctypes.c_uint8]
+        for name in ("oracle_f32_to_f8e4m3fn", "oracle_f32_to_f8e5m2"):
+            getattr(_lib, name).restype = ctypes.c_uint8
+            getattr(_lib, name).argtypes = [ctypes.c_float]
         _lib.oracle_matmul_f32acc_element.restype = ctypes.c_float
         _lib.oracle_matmul_i8_i32_element.restype = ctypes.c_int32
         _lib.oracle_calculate_check_every.restype = ctypes.c_int
@@ -86,12 +94,26 @@ def f16_bits_to_f32(b: np.ndarray) -> np.ndarray:
     return b.view(np.float16).astype(np.float32)
 
 
+_F8_NAMES = {F8E4M3FN: "f8e4m3fn", F8E5M2: "f8e5m2"}
+_f8_tables = {}
+
+
+def _f8_decode_table(t) -> np.ndarray:
+    """All 256 codes of an 8-bit float decoded by the C oracle (math.h:300-362 restated)."""
+    if t not in _f8_tables:
+        fn = getattr(lib(), "oracle_%s_to_f32" % _F8_NAMES[t])
+        _f8_tables[t] = np.array([fn(i) for i in range(256)], dtype=np.float32)
+    return _f8_tables[t]
+
+
 def to_f32(t, a: np.ndarray) -> np.ndarray:
     t = type_id(t)
     if t == BF16:
         return bf16_bits_to_f32(a)
     if t == F16:
         return f16_bits_to_f32(a)
+    if t in _F8_NAMES:
+        return _f8_decode_table(t)[a]
     return a.astype(np.float32)
 
 
@@ -101,6 +123,13 @@ def from_f32(t, a: np.ndarray) -> np.ndarray:
         return f32_to_bf16_bits(a)
     if t == F16:
         return f32_to_f16_bits(a)
+    if t in _F8_NAMES:
+        # Round to nearest even through the C encoder, once per distinct value.
+        fn = getattr(lib(), "oracle_f32_to_%s" % _F8_NAMES[t])
+        flat = np.ascontiguousarray(a, dtype=np.float32).reshape(-1)
+        uniq, inverse = np.unique(flat.view(np.uint32), return_inverse=True)
+        codes = np.array([fn(float(u)) for u in uniq.view(np.float32)], dtype=np.uint8)
+        return codes[inverse].reshape(np.shape(a))
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
@@ -131,7 +160,8 @@ def matmul(t, lhs: np.ndarray, rhs: np.ndarray, acc=None, transpose_rhs: bool = 
     """C = acc + A.B with the reference's per-element k-ascending accumulation.
 
     lhs [.., M, K]; rhs [.., K, N] (or [.., N, K] when transpose_rhs). A leading
-    batch dim makes it batch_matmul. t in {"i8","f16","bf16"}; result i32 / f32.
+    batch dim makes it batch_matmul. t in {"i8","f16","bf16","f8e4m3fn","f8e5m2"};
+    result i32 / f32.
     """
     t = type_id(t)
     batched = lhs.ndim == 3
@@ -264,3 +294,24 @@ def ref_matmul(t, lhs: np.ndarray, rhs: np.ndarray, force_generic: bool = False,
     if rc != 0:
         raise RuntimeError(f"oracle_ref_matmul failed for {t} {M}x{N}x{K}")
     return (out, tuple(tiles)) if return_tiles else out
+
+
+_ENCODE_KINDS = {"f8e4m3fn": 0, "f8e5m2": 1, "f16": 2, "bf16": 3}
+
+
+def encode_bulk(t: str, values: np.ndarray, reference: bool = False) -> np.ndarray:
+    """f32 -> narrow float bits for every element: oracle.c's restatement, or — with
+    |reference| — the reference's own iree_math_f32_to_* (math.h, via oracle/_ref)."""
+    v = np.ascontiguousarray(values, dtype=np.float32).reshape(-1)
+    out = np.empty(v.size, dtype=np.uint16)
+    fn = ref_lib().oracle_ref_encode if reference else lib().oracle_encode
+    fn(ctypes.c_int(_ENCODE_KINDS[t]), ctypes.c_int64(v.size), _ptr(v), _ptr(out))
+    return out
+
+
+def decode_reference(t: str, bits: np.ndarray) -> np.ndarray:
+    """narrow float bits -> f32 through the reference's iree_math_*_to_f32 (oracle/_ref)."""
+    fn = getattr(ref_lib(), "oracle_ref_%s_to_f32" % t)
+    fn.restype = ctypes.c_float
+    fn.argtypes = [ctypes.c_uint8 if t.startswith("f8") else ctypes.c_uint16]
+    return np.array([fn(int(b)) for b in np.asarray(bits).reshape(-1)], dtype=np.float32)

@@ -48,5 +48,6 @@ done
 cc "$AVX2 $AVX512 -mavx512vnni" "$A/mmt4d_x86_64_avx512_vnni.c"
 cc "$AVX2 $AVX512 -mavx512bf16" "$A/mmt4d_x86_64_avx512_bf16.c"
 "$CC" $BASE -fopenmp $INC -c "$HERE/ref_glue.c" -o "$OUT/obj/ref_glue.o"
-"$CC" -shared -fopenmp -o "$OUT/libiree_uk_ref.so" $OBJS "$OUT/obj/ref_glue.o" -lm
+"$CC" $BASE $INC -c "$HERE/ref_math_glue.c" -o "$OUT/obj/ref_math_glue.o"
+"$CC" -shared -fopenmp -o "$OUT/libiree_uk_ref.so" $OBJS "$OUT/obj/ref_glue.o" "$OUT/obj/ref_math_glue.o" -lm
 echo "built $OUT/libiree_uk_ref.so"

@@ -34,6 +34,8 @@ enum {
   ORACLE_BF16 = 2,
   ORACLE_F32 = 3,
   ORACLE_I32 = 4,
+  ORACLE_F8E4M3FN = 5,
+  ORACLE_F8E5M2 = 6,
 };
 
 //===----------------------------------------------------------------------===//
@@ -112,6 +114,77 @@ ORACLE_API uint16_t oracle_f32_to_f16(float f) {
   return (uint16_t)(sign | r);
 }
 
+// OCP 8-bit floats. Decoding: math.h:300-362 with the parameters of :550-560 — f8E5M2 is
+// IEEE-like (5 exponent bits, bias 15, infinities; it is the top byte of an f16);
+// f8E4M3FN has bias 7, no infinities, and S.1111.111 as its only NaN. Encoding: the
+// round-to-nearest-even truncation of :376-516 — overflow gives Inf for f8E5M2 and NaN
+// for f8E4M3FN, f32 subnormals flush to zero, results may be subnormal.
+ORACLE_API float oracle_f8e5m2_to_f32(uint8_t b) {
+  return oracle_f16_to_f32((uint16_t)((uint16_t)b << 8));
+}
+
+ORACLE_API float oracle_f8e4m3fn_to_f32(uint8_t b) {
+  uint32_t sign = (uint32_t)(b & 0x80u) << 24;
+  uint32_t exp = (b >> 3) & 0xfu, man = b & 0x7u;
+  if (exp == 0) {
+    float v = ldexpf((float)man, -9);
+    return sign ? -v : v;
+  }
+  if (exp == 15 && man == 7) return bits_f32(sign | 0x7fc00000u);
+  return bits_f32(sign | ((exp + 120u) << 23) | (man << 20));
+}
+
+// Shared RNE encoder for a format with |eb| exponent and |mb| mantissa bits.
+static uint8_t f32_to_f8(float f, int eb, int mb, int have_inf) {
+  uint32_t u = f32_bits(f);
+  uint8_t sign = (uint8_t)((u >> 24) & 0x80u);
+  uint32_t fexp = (u >> 23) & 0xffu, fman = u & 0x7fffffu;
+  const int bias = (1 << (eb - 1)) - 1;
+  const uint8_t exp_mask = (uint8_t)(((1u << eb) - 1u) << mb);
+  const uint8_t man_mask = (uint8_t)((1u << mb) - 1u);
+  const uint8_t nan = (uint8_t)(sign | exp_mask | man_mask);
+  const uint8_t inf = have_inf ? (uint8_t)(sign | exp_mask) : nan;
+  if (fexp == 0xff) return fman ? nan : inf;
+  if (fexp == 0) return sign;  // zero / f32 subnormal
+  int e = (int)fexp - 127;
+  if (e > (1 << (eb - 1)) - have_inf) return inf;
+  uint32_t full = fman | 0x800000u;
+  if (e + bias <= 0) {
+    // Subnormal result: units of 2^(1 - bias - mb).
+    int shift = (23 - mb) + (1 - bias - e);
+    if (shift > 24) return sign;
+    uint32_t lsb = (full >> shift) & 1u;
+    uint32_t r = (full + ((1u << (shift - 1)) - 1u) + lsb) >> shift;
+    return (uint8_t)(sign | r);  // r may carry into the smallest normal: same encoding
+  }
+  int shift = 23 - mb;
+  uint32_t lsb = (fman >> shift) & 1u;
+  uint32_t m = fman + ((1u << (shift - 1)) - 1u) + lsb;
+  if (m & 0x800000u) {
+    m = 0;
+    ++e;
+  }
+  uint32_t de = (uint32_t)(e + bias);
+  if (de > ((1u << eb) - 1u)) return have_inf ? inf : nan;
+  if (have_inf && de == ((1u << eb) - 1u)) return inf;
+  return (uint8_t)(sign | (de << mb) | (m >> shift));
+}
+
+ORACLE_API uint8_t oracle_f32_to_f8e5m2(float f) { return f32_to_f8(f, 5, 2, 1); }
+ORACLE_API uint8_t oracle_f32_to_f8e4m3fn(float f) { return f32_to_f8(f, 4, 3, 0); }
+
+// Bulk encoder, same kind numbering as oracle/ref_math_glue.c (tests sweep bit patterns).
+ORACLE_API void oracle_encode(int kind, int64_t n, const float* in, uint16_t* out) {
+  for (int64_t i = 0; i < n; ++i) {
+    switch (kind) {
+      case 0: out[i] = oracle_f32_to_f8e4m3fn(in[i]); break;
+      case 1: out[i] = oracle_f32_to_f8e5m2(in[i]); break;
+      case 2: out[i] = oracle_f32_to_f16(in[i]); break;
+      default: out[i] = oracle_f32_to_bf16(in[i]); break;
+    }
+  }
+}
+
 static inline float load_elem(int type, const void* p, int64_t i) {
   switch (type) {
     case ORACLE_F16:
@@ -120,6 +193,10 @@ static inline float load_elem(int type, const void* p, int64_t i) {
       return oracle_bf16_to_f32(((const uint16_t*)p)[i]);
     case ORACLE_F32:
       return ((const float*)p)[i];
+    case ORACLE_F8E4M3FN:
+      return oracle_f8e4m3fn_to_f32(((const uint8_t*)p)[i]);
+    case ORACLE_F8E5M2:
+      return oracle_f8e5m2_to_f32(((const uint8_t*)p)[i]);
     default:
       return 0.f;
   }
@@ -150,6 +227,12 @@ static inline void store_elem(int type, void* p, int64_t i, float v) {
     case ORACLE_F32:
       ((float*)p)[i] = v;
       break;
+    case ORACLE_F8E4M3FN:
+      ((uint8_t*)p)[i] = oracle_f32_to_f8e4m3fn(v);
+      break;
+    case ORACLE_F8E5M2:
+      ((uint8_t*)p)[i] = oracle_f32_to_f8e5m2(v);
+      break;
     default:
       break;
   }
@@ -172,6 +255,8 @@ static void min_max_for_type(int type, int32_t* mn, int32_t* mx) {
   switch (type) {
     case ORACLE_I8:
     case ORACLE_BF16:
+    case ORACLE_F8E4M3FN:
+    case ORACLE_F8E5M2:
       *mn = -2, *mx = 2;
       break;
     case ORACLE_F16:

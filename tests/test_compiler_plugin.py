@@ -24,7 +24,7 @@ def test_spec_is_balanced_and_covers_every_tcgen05_family():
     with open(os.path.join(ROOT, "iree_b200", "_build", "exports.json")) as f:
         exports = {e["name"]: e for e in json.load(f)["exports"]}
     dispatched = re.findall(r'hal\.dispatch\.extern "(\w+)"', text)
-    assert len(dispatched) == len(set(dispatched)) + 6  # each matmul kernel: 2-D + batched entry
+    assert len(dispatched) == len(set(dispatched)) + 10  # each matmul kernel: 2-D + batched entry
     for name in set(dispatched):
         e = exports[name]
         block = text[text.index(f'hal.dispatch.extern "{name}"'):]
@@ -35,7 +35,8 @@ def test_spec_is_balanced_and_covers_every_tcgen05_family():
         assert f"workgroup_size = [{e['block_dims'][0]} : index" in block
         assert f"workgroup_local_memory = {e['shared_memory']} : index" in block
         assert f'path = "{e["module"]}.cubin"' in block
-    for et, acc in (("bf16", "f32"), ("f16", "f32"), ("i8", "i32")):
+    for et, acc in (("bf16", "f32"), ("f16", "f32"), ("i8", "i32"), ("f8e4m3fn", "f32"),
+                    ("f8e5m2", "f32")):
         assert f"iree_b200_matmul_{et}_{acc}" in dispatched
         assert f"iree_b200_matmul_{et}_{acc}_1cta" in dispatched
     assert "iree_b200_attention_prefill_f16" in dispatched

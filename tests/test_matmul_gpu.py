@@ -49,7 +49,14 @@ def acc_dtype(t):
     return np.int32 if t == "i8" else np.float32
 
 
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+ALL_TYPES = ["i8", "f16", "bf16", "f8e4m3fn", "f8e5m2"]
+
+
+def elem_size(t):
+    return 2 if t in ("f16", "bf16") else 1
+
+
+@pytest.mark.parametrize("t", ALL_TYPES)
 @pytest.mark.parametrize("shape", SMALL + LARGE + EASY_LARGE_STATIC,
                          ids=lambda s: "%dx%dx%d%s" % (s[0], s[1], s[2], "+acc" if s[3] else ""))
 def test_reference_shape_sets(ops, t, shape):
@@ -58,13 +65,13 @@ def test_reference_shape_sets(ops, t, shape):
     assert np.array_equal(out[0], want[0])
 
 
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ALL_TYPES)
 @pytest.mark.parametrize("family", ["1cta", "2cta", "generic"])
 @pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
 @pytest.mark.parametrize("shape", TILED, ids=lambda s: "%dx%dx%d%s" % (s[0], s[1], s[2], "+acc" if s[3] else ""))
 def test_every_kernel_family(ops, t, family, nt, shape):
     M, K, N, accumulate = shape
-    es = 1 if t == "i8" else 2
+    es = elem_size(t)
     if family != "generic" and ((K * es) % 16 or (N * 4) % 16 or (not nt and (N * es) % 16)):
         pytest.skip("shape does not satisfy the TMA guards (goes to the generic kernel)")
     flag = {"1cta": H.MATMUL_FORCE_1CTA, "2cta": H.MATMUL_FORCE_2CTA,
@@ -73,7 +80,7 @@ def test_every_kernel_family(ops, t, family, nt, shape):
     assert np.array_equal(out, want)
 
 
-@pytest.mark.parametrize("t", ["i8", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "bf16", "f8e4m3fn"])
 @pytest.mark.parametrize("bshape", [(32, 128, 128, 128), (32, 256, 64, 256), (32, 96, 96, 96),
                                     (3, 300, 136, 520)], ids=str)
 def test_batch_matmul_reference_shapes(ops, t, bshape):
@@ -128,6 +135,43 @@ def test_i8_full_range_bit_exact(ops):
         assert np.array_equal(out, want)
 
 
+@pytest.mark.parametrize("t", ["f8e4m3fn", "f8e5m2"])
+def test_f8_random_inputs(ops, t):
+    """N(0,1) inputs rounded to the 8-bit type (so also subnormal and large codes), both
+    tcgen05 families and the generic kernel. Products of two 8-bit floats are exact in f32;
+    what differs from the oracle is the f32 summation order only."""
+    g = _pcg(0xB200 + 8)
+    M, N, K = 384, 512, 4096
+    scale_in = 1.0 if t == "f8e4m3fn" else 16.0
+    lhs = oracle.from_f32(t, (g.standard_normal((1, M, K)) * scale_in).astype(np.float32))
+    rhs = oracle.from_f32(t, (g.standard_normal((1, K, N)) * scale_in).astype(np.float32))
+    for flag in (H.MATMUL_FORCE_1CTA, H.MATMUL_FORCE_2CTA, H.MATMUL_FORCE_GENERIC):
+        out, want = _run(ops, t, 1, M, N, K, flags=flag, lhs=lhs, rhs=rhs)
+        scale = np.abs(want).max()
+        assert np.isfinite(out).all()
+        assert np.abs(out - want).max() <= 1e-3 * scale, (flag, np.abs(out - want).max(), scale)
+
+
+def test_f8_every_code_decodes_like_the_oracle(ops):
+    """A [256, 32] x [32, 256] product with a one-hot RHS reads back every 8-bit code through
+    the tensor core's own decoder (and the generic kernel's): it must equal the oracle's
+    table bit for bit (NaN codes compare as NaN)."""
+    for t in ("f8e4m3fn", "f8e5m2"):
+        codes = np.arange(256, dtype=np.uint8)
+        one = oracle.from_f32(t, np.array([1.0], np.float32))[0]
+        lhs = np.zeros((1, 256, 32), np.uint8)
+        lhs[0, :, 0] = codes
+        rhs = np.zeros((1, 32, 256), np.uint8)
+        rhs[0, 0, :] = one
+        want = oracle.to_f32(t, codes)
+        for flag in (H.MATMUL_FORCE_1CTA, H.MATMUL_FORCE_GENERIC):
+            out, _ = _run(ops, t, 1, 256, 256, 32, flags=flag, lhs=lhs, rhs=rhs)
+            got = out[0, :, 7]
+            fin = np.isfinite(want)
+            assert np.array_equal(got[fin], want[fin]), (t, flag)
+            assert np.isnan(got[np.isnan(want)]).all() and np.array_equal(got[np.isinf(want)], want[np.isinf(want)])
+
+
 @pytest.mark.parametrize("t,rtol", [("bf16", 1e-2), ("f16", 1e-3)])
 def test_random_normal_inputs_within_tolerance(ops, t, rtol):
     g = _pcg(0xB200 + 1)
@@ -143,7 +187,7 @@ def test_random_normal_inputs_within_tolerance(ops, t, rtol):
     assert np.abs(out - want).max() <= 1e-5 * scale
 
 
-@pytest.mark.parametrize("t", ["i8", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "bf16", "f8e4m3fn"])
 def test_full_size_sampled_like_the_reference(ops, t):
     """BASELINE config sizes: compare the reference checker's sampled index set
     (iree_test_utils_calculate_check_every, test_utils.c:41-68) at 4096^3."""
@@ -194,7 +238,7 @@ def test_truncating_epilogue_guards(ops):
     assert exe.export_info(s["export_ordinal"])["kernel_name"] == "iree_b200_matmul_bf16_bf16"
 
 
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ALL_TYPES)
 @pytest.mark.parametrize("case", [
     # batch, M, K, N, accumulate, nt, truncate
     (1, 1000, 272, 528, False, False, False),   # 4x3 blocks, ragged last row / column panel
@@ -209,7 +253,7 @@ def test_pipelined_host_call(ops, t, case):
     """iree_b200_ops_matmul_host as a pipeline (panel uploads, per-block dispatch, block
     downloads on three streams): same bits as the single-dispatch form and the oracle."""
     batch, M, K, N, accumulate, nt, truncate = case
-    if truncate and t == "i8":
+    if truncate and elem_size(t) == 1:
         pytest.skip("TRUNCATE_RESULT is f16 / bf16 only")
     before = ops.dispatch_count
     ops.set_host_pipeline(0, 256, 256)

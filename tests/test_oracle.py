@@ -150,3 +150,72 @@ def test_oracle_matches_reference_ukernels_i8_full_range():
     for generic in (False, True):
         assert np.array_equal(oracle.ref_matmul("i8", lhs, rhs, force_generic=generic),
                               oracle.matmul("i8", lhs, rhs))
+
+
+@pytest.mark.parametrize("t", ["f8e4m3fn", "f8e5m2"])
+def test_f8_decode_known_values(t):
+    """OCP 8-bit floats (math.h:550-560): landmarks of both formats."""
+    tab = oracle.to_f32(t, np.arange(256, dtype=np.uint8))
+    if t == "f8e4m3fn":
+        assert tab[0x38] == 1.0 and tab[0x7E] == 448.0 and np.isnan(tab[0x7F]) and np.isnan(tab[0xFF])
+        assert tab[0x01] == 2.0 ** -9 and tab[0x08] == 2.0 ** -6 and np.isfinite(tab[:0x7F]).all()
+    else:
+        assert tab[0x3C] == 1.0 and tab[0x7B] == 57344.0 and np.isinf(tab[0x7C]) and np.isnan(tab[0x7D])
+        assert tab[0x01] == 2.0 ** -16 and tab[0x04] == 2.0 ** -14
+    assert (tab[128:][np.isfinite(tab[128:])] == -tab[:128][np.isfinite(tab[:128])]).all()
+    # The generator's small integers are exactly representable (test_utils.c:391-397).
+    ints = np.arange(-2, 3, dtype=np.float32)
+    assert (oracle.to_f32(t, oracle.from_f32(t, ints)) == ints).all()
+
+
+@pytest.mark.parametrize("t", ["f8e4m3fn", "f8e5m2"])
+@pytest.mark.parametrize("shape", [(9, 9, 9), (81, 19, 41), (1, 1000, 1000)], ids=str)
+def test_f8_matmul_oracle_exact_on_reference_inputs(t, shape):
+    M, K, N = shape
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    want = oracle.to_f32(t, lhs).astype(np.float64) @ oracle.to_f32(t, rhs).astype(np.float64)
+    assert np.array_equal(oracle.matmul(t, lhs, rhs).astype(np.float64), want)
+    got_nt = oracle.matmul(t, lhs, np.ascontiguousarray(rhs.T), transpose_rhs=True)
+    assert np.array_equal(got_nt.astype(np.float64), want)
+
+
+@_needs_ref
+@pytest.mark.parametrize("t", ["f8e4m3fn", "f8e5m2", "f16", "bf16"])
+def test_float_conversions_match_reference_math_h(t):
+    """oracle.c's narrow-float conversions against the reference's own header-only
+    implementation (base/internal/math.h, compiled into oracle/_ref): every code decodes to
+    the same f32, and ~6M f32 bit patterns (all code values, every midpoint between
+    neighbouring codes and its two f32 neighbours, a bit-pattern sweep, specials) encode
+    to the same bits."""
+    n = 256 if t.startswith("f8") else 65536
+    bits = np.arange(n, dtype=np.uint8 if n == 256 else np.uint16)
+    mine = oracle.to_f32(t, bits)
+    theirs = oracle.decode_reference(t, bits[:: max(1, n // 4096)])
+    sub = mine[:: max(1, n // 4096)]
+    assert np.array_equal(np.isnan(sub), np.isnan(theirs))       # NaN payload / sign may differ
+    assert np.array_equal(sub[~np.isnan(sub)].view(np.uint32), theirs[~np.isnan(theirs)].view(np.uint32))
+    finite = np.sort(mine[np.isfinite(mine)].astype(np.float64))
+    mids = ((finite[1:] + finite[:-1]) / 2).astype(np.float32)
+    probes = np.concatenate([
+        mine[np.isfinite(mine)], mids, np.nextafter(mids, np.float32(np.inf)),
+        np.nextafter(mids, np.float32(-np.inf)),
+        np.arange(0, 2 ** 32, 769, dtype=np.uint64).astype(np.uint32).view(np.float32),
+        np.array([np.inf, -np.inf, np.nan, 0.0, -0.0, 1e-45, 3.4e38, -3.4e38, 464.0, 465.0, 61440.0,
+                  65504.0, 65520.0], dtype=np.float32)])
+    a = oracle.encode_bulk(t, probes)
+    b = oracle.encode_bulk(t, probes, reference=True)
+    nan_in = np.isnan(probes)
+    # One documented difference: math.h:437-441 drops the mantissa when the rounding shift
+    # exceeds 23 bits, so it flushes (minsub/2, minsub) to zero where round-to-nearest-even
+    # (what compiled arith.truncf does, and what oracle.c does) gives the smallest
+    # subnormal. bf16 keeps f32's exponent range and has no such interval.
+    minsub = np.float32(finite[finite > 0][0])
+    quirk = (np.abs(probes) > minsub / 2) & (np.abs(probes) < minsub) & (t != "bf16")
+    same = ~nan_in & ~quirk
+    assert np.array_equal(a[same], b[same])
+    assert ((a[quirk] & 0x7FFF if n > 256 else a[quirk] & 0x7F) == 1).all()
+    assert ((b[quirk] & 0x7FFF if n > 256 else b[quirk] & 0x7F) == 0).all()
+    # NaN inputs: both must produce a NaN encoding (payloads may differ).
+    assert np.isnan(oracle.to_f32(t, a[nan_in].astype(bits.dtype))).all()
+    assert np.isnan(oracle.to_f32(t, b[nan_in].astype(bits.dtype))).all()
