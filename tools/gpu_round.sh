@@ -15,6 +15,7 @@ bench)
     run bench_$w 300 python bench.py --workload $w --no-cpu-baseline --steps 100
   done
   run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
+f8) run bench_matmul_f8 300 python bench.py --workload matmul_f8 --no-cpu-baseline --steps 100 ;;
 decode) run bench_attention_decode 300 python bench.py --workload attention_decode --no-cpu-baseline --steps 200 ;;
 ncu)
   run ncu_launches 400 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches_matmul_bf16.csv python bench.py --steps 20 --warmup 3 --no-cpu-baseline
