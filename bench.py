@@ -256,6 +256,7 @@ class MatmulStep:
 
 class AttentionStep:
     """iree_linalg_ext.attention, one recorded command buffer (1 or 2 dispatches)."""
+    FLAGS = 0  # --attention-flags (diagnostics: kernel family / exp2 split)
 
     def __init__(self, torch, hal, dev, ops, spec, seed):
         op, et, B, M, K2, D = spec
@@ -267,7 +268,7 @@ class AttentionStep:
         self.tensors = [mk(B, M, D), mk(B, K2, D), mk(B, K2, D),
                         torch.empty((B, M, D), dtype=dt, device="cuda")]
         self.scale = 1.0 / (D ** 0.5)
-        sel = ops.select_attention(et, B, M, D, K2, D, self.scale)
+        sel = ops.select_attention(et, B, M, D, K2, D, self.scale, flags=self.FLAGS)
         self.workspace = torch.empty((max(sel["workspace_bytes"], 16),), dtype=torch.uint8,
                                      device="cuda")
         imp = lambda t: dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
@@ -276,7 +277,7 @@ class AttentionStep:
         self.cb = hal.CommandBuffer(dev).begin()
         ops.record_attention(self.cb, et, B, M, D, K2, D, self.scale, self.buffers[0].ref(),
                              self.buffers[1].ref(), self.buffers[2].ref(), self.buffers[3].ref(),
-                             workspace=self.buffers[4].ref())
+                             workspace=self.buffers[4].ref(), flags=self.FLAGS)
         self.cb.end()
         self.launches_per_step = ops.dispatch_count - before
         self.dev = dev
@@ -433,6 +434,7 @@ def run_ours(args):
     from iree_b200 import hal
 
     stream = torch.cuda.Stream()
+    AttentionStep.FLAGS = args.attention_flags
     tp = args.workload == "tp_decoder_layer"
     dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
                      overlap_collectives=(2 if args.no_range_fusion else 1) if tp and world > 1 else 0)
@@ -646,6 +648,8 @@ def main():
     ap.add_argument("--collective", default="symmetric", choices=["symmetric", "nccl"],
                     help="tp_decoder_layer, N>1: all-reduce through the symmetric-region NVLink "
                          "kernels (default) or through NCCL")
+    ap.add_argument("--attention-flags", type=lambda v: int(v, 0), default=0,
+                    help="IREE_B200_ATTENTION_FLAG_* bits for the attention workloads")
     ap.add_argument("--no-range-fusion", action="store_true",
                     help="tp_decoder_layer: one all-reduce launch per chunk instead of one "
                          "persistent launch per row-parallel GEMM")

@@ -146,6 +146,12 @@ enum {
   // cluster form (otherwise chosen by the number of (batch, m) rows and K2).
   IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT = 1u << 11,
   IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER = 1u << 12,
+  // Prefill kernel: how many of every four exp2 run as a polynomial on the FMA pipe instead
+  // of on the MUFU (the prefill kernel's co-limiter): none / 1 of 4 / 2 of 4. Without any of
+  // these the default chosen from the measurements applies.
+  IREE_B200_ATTENTION_FLAG_EXP2_MUFU_ONLY = 1u << 13,
+  IREE_B200_ATTENTION_FLAG_EXP2_POLY_25 = 1u << 14,
+  IREE_B200_ATTENTION_FLAG_EXP2_POLY_50 = 1u << 15,
 };
 
 #define IREE_B200_ATTENTION_MAX_DISPATCHES 2

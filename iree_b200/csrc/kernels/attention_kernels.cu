@@ -33,7 +33,7 @@ using namespace b200;
 
 using PrefillCfg = AttnPrefillConfig<128>;
 
-#define B200_PREFILL(NAME, BF16)                                                               \
+#define B200_PREFILL(NAME, BF16, POLY)                                                         \
   extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                             \
       make_attention_prefill_recipe<PrefillCfg, BF16>();                                       \
   extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \
@@ -44,12 +44,17 @@ using PrefillCfg = AttnPrefillConfig<128>;
     (void)q;                                                                                   \
     (void)k;                                                                                   \
     (void)v;                                                                                   \
-    attention_prefill_body<PrefillCfg, BF16>(out, B, M, K2, scale_bits, flags, &tm_q, &tm_k,   \
-                                             &tm_v);                                           \
+    attention_prefill_body<PrefillCfg, BF16, POLY>(out, B, M, K2, scale_bits, flags, &tm_q,    \
+                                                   &tm_k, &tm_v);                              \
   }
 
-B200_PREFILL(iree_b200_attention_prefill_f16, false)
-B200_PREFILL(iree_b200_attention_prefill_bf16, true)
+B200_PREFILL(iree_b200_attention_prefill_f16, false, 0)
+B200_PREFILL(iree_b200_attention_prefill_bf16, true, 0)
+// Same kernel with 1 / 2 of every 4 exp2 evaluated by poly_exp2 on the FMA pipe.
+B200_PREFILL(iree_b200_attention_prefill_f16_p25, false, 1)
+B200_PREFILL(iree_b200_attention_prefill_bf16_p25, true, 1)
+B200_PREFILL(iree_b200_attention_prefill_f16_p50, false, 2)
+B200_PREFILL(iree_b200_attention_prefill_bf16_p50, true, 2)
 
 //===----------------------------------------------------------------------===//
 // Decode: split-KV streaming kernel + merge. HBM bound: every K and V byte is read once.

@@ -33,12 +33,17 @@ uint64_t matmul_elem_size(int32_t t) {
   return (t == IREE_B200_ELEMENT_TYPE_F16 || t == IREE_B200_ELEMENT_TYPE_BF16) ? 2 : 1;
 }
 
+// The exp2 split the prefill kernel uses unless a flag says otherwise.
+constexpr int kDefaultPrefillVariant = 0;  // kAttnPrefill
+
 enum AttentionExport {
   kAttnPrefill = 0,
   kAttnDecodeSplit = 1,
   kAttnDecodeMerge = 2,
   kAttnGeneric = 3,
-  kAttnDecodeCluster = 4
+  kAttnDecodeCluster = 4,
+  kAttnPrefillPoly25 = 5,
+  kAttnPrefillPoly50 = 6
 };
 
 }  // namespace
@@ -134,6 +139,10 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
     const std::string suffix = t == IREE_B200_ELEMENT_TYPE_F16 ? "f16" : "bf16";
     ops->attention_exports[t][kAttnPrefill] =
         lookup(ops->executable, "iree_b200_attention_prefill_" + suffix);
+    ops->attention_exports[t][kAttnPrefillPoly25] =
+        lookup(ops->executable, "iree_b200_attention_prefill_" + suffix + "_p25");
+    ops->attention_exports[t][kAttnPrefillPoly50] =
+        lookup(ops->executable, "iree_b200_attention_prefill_" + suffix + "_p50");
     ops->attention_exports[t][kAttnDecodeSplit] =
         lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
     ops->attention_exports[t][kAttnDecodeMerge] =
@@ -671,7 +680,11 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
   switch (family) {
     case kPrefill: {
       if (B > 65535) return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention batch too large");
-      d0->export_ordinal = ops->attention_exports[element_type][kAttnPrefill];
+      int variant = kDefaultPrefillVariant;
+      if (flags & IREE_B200_ATTENTION_FLAG_EXP2_MUFU_ONLY) variant = kAttnPrefill;
+      if (flags & IREE_B200_ATTENTION_FLAG_EXP2_POLY_25) variant = kAttnPrefillPoly25;
+      if (flags & IREE_B200_ATTENTION_FLAG_EXP2_POLY_50) variant = kAttnPrefillPoly50;
+      d0->export_ordinal = ops->attention_exports[element_type][variant];
       d0->workgroup_count[0] = (uint32_t)ceil_div(M, 256);
       d0->workgroup_count[1] = (uint32_t)B;
       d0->workgroup_count[2] = 1;

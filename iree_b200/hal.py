@@ -35,6 +35,9 @@ ATTENTION_FORCE_PREFILL = 1 << 9
 ATTENTION_FORCE_DECODE = 1 << 10
 ATTENTION_FORCE_DECODE_SPLIT = 1 << 11
 ATTENTION_FORCE_DECODE_CLUSTER = 1 << 12
+ATTENTION_EXP2_MUFU_ONLY = 1 << 13
+ATTENTION_EXP2_POLY_25 = 1 << 14
+ATTENTION_EXP2_POLY_50 = 1 << 15
 
 MODE_GRAPH, MODE_STREAM = 0, 1
 MEMORY_DEVICE_LOCAL, MEMORY_HOST_LOCAL = 1, 2

@@ -87,13 +87,18 @@ def _assert_close(t, got, want):
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("exp2", ["default", "mufu", "poly25", "poly50"])
 @pytest.mark.parametrize("shape", [(1, 128, 128), (2, 256, 256), (3, 384, 640), (2, 200, 300),
                                    (1, 130, 77), (4, 512, 1024), (1, 17, 129)], ids=str)
-def test_prefill_kernel_vs_oracle(ops, t, shape):
+def test_prefill_kernel_vs_oracle(ops, t, exp2, shape):
+    """Every exp2 split of the prefill kernel (all on the MUFU, 1 or 2 of 4 as a degree-3
+    polynomial on the FMA pipe) against the oracle, same tolerance."""
     B, M, K2 = shape
     q, k, v = _random_qkv(t, B, M, K2, 128, seed=M + K2)
     scale = 1.0 / np.sqrt(128.0)
-    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_PREFILL)
+    flag = {"default": 0, "mufu": H.ATTENTION_EXP2_MUFU_ONLY, "poly25": H.ATTENTION_EXP2_POLY_25,
+            "poly50": H.ATTENTION_EXP2_POLY_50}[exp2]
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_PREFILL | flag)
     want = oracle.attention(t, q, k, v, scale, k2_tile=128)
     _assert_close(t, got, want)
 

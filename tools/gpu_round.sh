@@ -15,6 +15,16 @@ bench)
     run bench_$w 300 python bench.py --workload $w --no-cpu-baseline --steps 100
   done
   run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
+prefillsweep)
+  run pytest_prefill 300 python -m pytest tests/test_attention_gpu.py -m gpu -x -q -k "prefill"
+  for v in 0x2000 0x4000 0x8000; do
+    run bench_prefill_$v 200 python bench.py --workload attention_prefill --no-cpu-baseline --steps 200 --attention-flags $v --e2e-steps 1
+  done
+  run bench_prefill_bf16_0x8000 200 python bench.py --workload attention_prefill_bf16 --no-cpu-baseline --steps 200 --attention-flags 0x8000 --e2e-steps 1 ;;
+ncufinal)
+  run ncu_prefill 300 ncu --set full --clock-control none --import-source on -k regex:attention_prefill -c 1 -o $O/${TAG}_attn_prefill -f python bench.py --workload attention_prefill --steps 3 --warmup 3 --no-cpu-baseline --e2e-steps 1
+  run ncu_f8 300 ncu --set full --clock-control none --import-source on -k regex:matmul_f8e4m3fn_f32 -c 1 -o $O/${TAG}_gemm_f8 -f python bench.py --workload matmul_f8 --steps 3 --warmup 3 --no-cpu-baseline --e2e-steps 1
+  run ncu_i8 300 ncu --set full --clock-control none --import-source on -k regex:matmul_i8_i32 -c 1 -o $O/${TAG}_gemm_i8 -f python bench.py --workload matmul_i8 --steps 3 --warmup 3 --no-cpu-baseline --e2e-steps 1 ;;
 f8) run bench_matmul_f8 300 python bench.py --workload matmul_f8 --no-cpu-baseline --steps 100 ;;
 decode) run bench_attention_decode 300 python bench.py --workload attention_decode --no-cpu-baseline --steps 200 ;;
 ncu)
