@@ -152,6 +152,9 @@ enum {
   IREE_B200_ATTENTION_FLAG_EXP2_MUFU_ONLY = 1u << 13,
   IREE_B200_ATTENTION_FLAG_EXP2_POLY_25 = 1u << 14,
   IREE_B200_ATTENTION_FLAG_EXP2_POLY_50 = 1u << 15,
+  // Prefill kernel: keep the plain [ceil(M/256), B] grid even when the last wave of equal
+  // units would be mostly empty (default: cut that wave's units over K2 and merge).
+  IREE_B200_ATTENTION_FLAG_NO_TAIL_SPLIT = 1u << 16,
 };
 
 #define IREE_B200_ATTENTION_MAX_DISPATCHES 2
@@ -164,7 +167,7 @@ typedef struct iree_b200_attention_dispatch_t {
 } iree_b200_attention_dispatch_t;
 
 typedef struct iree_b200_attention_selection_t {
-  int32_t dispatch_count;  // 0 (empty result), 1, or 2 (split + merge)
+  int32_t dispatch_count;  // 0 (empty result), 1, or 2 (decode split + merge; prefill tail split + merge)
   iree_b200_attention_dispatch_t dispatches[IREE_B200_ATTENTION_MAX_DISPATCHES];
   uint64_t workspace_bytes;  // transient f32 buffer the two-dispatch form needs (else 0)
 } iree_b200_attention_selection_t;

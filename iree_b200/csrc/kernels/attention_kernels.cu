@@ -56,6 +56,87 @@ B200_PREFILL(iree_b200_attention_prefill_bf16_p25, true, 1)
 B200_PREFILL(iree_b200_attention_prefill_f16_p50, false, 2)
 B200_PREFILL(iree_b200_attention_prefill_bf16_p50, true, 2)
 
+// Tail-split form (attention_sm100.cuh, kSplit): 1-D grid over units, the units of the last,
+// partly filled wave cut into |split| CTAs each, plus the merge of their records.
+//   iree_b200_attention_prefill_split_{f16,bf16}
+//     bindings  Q ro, K ro, V ro, O, workspace [tail*split][256*(128+2)] f32
+//     constants B, M, K2, scale, full_units, split     grid [full_units + tail*split, 1, 1]
+//   iree_b200_attention_prefill_merge_{f16,bf16}
+//     bindings  workspace ro, O
+//     constants B, M, full_units, split, tail_units    grid [32, tail_units, 1]  block 256
+#define B200_PREFILL_SPLIT(NAME, BF16)                                                         \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                             \
+      make_attention_prefill_recipe<PrefillCfg, BF16>();                                       \
+  extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \
+      NAME(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, \
+           void* __restrict__ out, float* __restrict__ workspace, int B, int M, int K2,        \
+           int scale_bits, int full_units, int split, const __grid_constant__ TensorMap tm_q,  \
+           const __grid_constant__ TensorMap tm_k, const __grid_constant__ TensorMap tm_v) {   \
+    (void)q;                                                                                   \
+    (void)k;                                                                                   \
+    (void)v;                                                                                   \
+    attention_prefill_body<PrefillCfg, BF16, 0, true>(out, B, M, K2, scale_bits, 0, &tm_q,     \
+                                                      &tm_k, &tm_v, workspace, full_units,     \
+                                                      split);                                  \
+  }
+
+B200_PREFILL_SPLIT(iree_b200_attention_prefill_split_f16, false)
+B200_PREFILL_SPLIT(iree_b200_attention_prefill_split_bf16, true)
+
+namespace {
+
+// One CTA merges 8 rows of one split unit: thread -> (row, 4 columns).
+template <bool kBf16>
+__device__ __forceinline__ void attention_prefill_merge_body(const float* __restrict__ workspace,
+                                                             uint16_t* __restrict__ out, int M,
+                                                             int full_units, int split) {
+  constexpr int D = PrefillCfg::kHeadDim;
+  constexpr int kRows = PrefillCfg::kTilesPerCta * PrefillCfg::kBlockM;
+  constexpr int kRecord = kRows * (D + 2);
+  const int tail_unit = blockIdx.y;
+  const int unit = full_units + tail_unit;
+  const int tiles_m = (M + kRows - 1) / kRows;
+  const int batch = unit / tiles_m;
+  const int r = blockIdx.x * 8 + (int)(threadIdx.x >> 5);
+  const int gm = (unit % tiles_m) * kRows + r;
+  const int col = (int)(threadIdx.x & 31) * 4;
+  if (gm >= M) return;
+  const float* rec0 = workspace + (size_t)tail_unit * split * kRecord;
+  float gmax = -FLT_MAX;
+  for (int p = 0; p < split; ++p) gmax = fmaxf(gmax, rec0[(size_t)p * kRecord + kRows * D + r]);
+  float sum = 0.f;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int p = 0; p < split; ++p) {
+    const float* rec = rec0 + (size_t)p * kRecord;
+    const float w = exp2f(rec[kRows * D + r] - gmax);
+    sum = fmaf(w, rec[kRows * (D + 1) + r], sum);
+    const float4 a = *reinterpret_cast<const float4*>(rec + (size_t)r * D + col);
+    acc.x = fmaf(w, a.x, acc.x);
+    acc.y = fmaf(w, a.y, acc.y);
+    acc.z = fmaf(w, a.z, acc.z);
+    acc.w = fmaf(w, a.w, acc.w);
+  }
+  const float rcp = 1.0f / sum;  // TileAttention.cpp:141-146
+  uint2 o;
+  o.x = pack2<kBf16>(acc.x * rcp, acc.y * rcp);
+  o.y = pack2<kBf16>(acc.z * rcp, acc.w * rcp);
+  *reinterpret_cast<uint2*>(out + ((size_t)batch * M + gm) * D + col) = o;
+}
+
+}  // namespace
+
+#define B200_PREFILL_MERGE(SUFFIX, BF16)                                                       \
+  extern "C" __global__ void __launch_bounds__(256) iree_b200_attention_prefill_merge_##SUFFIX( \
+      const float* __restrict__ workspace, uint16_t* __restrict__ out, int B, int M,           \
+      int full_units, int split, int tail_units) {                                             \
+    (void)B;                                                                                   \
+    (void)tail_units;                                                                          \
+    attention_prefill_merge_body<BF16>(workspace, out, M, full_units, split);                  \
+  }
+
+B200_PREFILL_MERGE(f16, false)
+B200_PREFILL_MERGE(bf16, true)
+
 //===----------------------------------------------------------------------===//
 // Decode: split-KV streaming kernel + merge. HBM bound: every K and V byte is read once.
 //===----------------------------------------------------------------------===//

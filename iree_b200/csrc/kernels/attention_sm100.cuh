@@ -101,11 +101,19 @@ B200_DEVICE float attention_q_multiplier(float scale) {
 
 
 // kPoly: how many of every four exp2 go to poly_exp2 instead of the MUFU (0, 1 or 2).
-template <class Cfg, bool kBf16, int kPoly = 0>
+// kSplit: the tail-split form. The grid is 1-D over work units (a unit = two 128-row Q tiles
+// of one batch slice); units < |full_units| run whole, every later unit is cut into |split|
+// CTAs that each walk 1/split of the K2 blocks and leave an unnormalised record
+// (acc [256,128] f32, max [256], sum [256]) in |workspace| for the merge kernel. With equal
+// units the last wave of a grid is otherwise only partly full (512 units on 148 SMs: 3.46
+// waves); splitting just those units makes the last wave short instead.
+template <class Cfg, bool kBf16, int kPoly = 0, bool kSplit = false>
 __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, int B, int M, int K2,
                                                        int scale_bits, int flags,
                                                        const TensorMap* tm_q, const TensorMap* tm_k,
-                                                       const TensorMap* tm_v) {
+                                                       const TensorMap* tm_v,
+                                                       float* __restrict__ workspace = nullptr,
+                                                       int full_units = 0, int split = 1) {
   constexpr int D = Cfg::kHeadDim;
   constexpr int BM = Cfg::kBlockM;
   constexpr int BN = Cfg::kBlockN;
@@ -135,9 +143,26 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
 
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t lane = threadIdx.x & 31;
-  const int batch = blockIdx.y;
-  const int m_cta = blockIdx.x * (Cfg::kTilesPerCta * BM);
-  const uint32_t num_kv = (uint32_t)((K2 + BN - 1) / BN);
+  int batch = blockIdx.y;
+  int m_cta = blockIdx.x * (Cfg::kTilesPerCta * BM);
+  uint32_t num_kv = (uint32_t)((K2 + BN - 1) / BN);  // K2 blocks this CTA walks
+  uint32_t kv_begin = 0;                              // first of them
+  int record = -1;                                    // workspace record (split CTAs only)
+  if constexpr (kSplit) {
+    const int tiles_m = (M + Cfg::kTilesPerCta * BM - 1) / (Cfg::kTilesPerCta * BM);
+    int unit = blockIdx.x;
+    if (unit >= full_units) {
+      const int r = unit - full_units;
+      unit = full_units + r / split;
+      const uint32_t part = (uint32_t)(r % split);
+      const uint32_t per = (num_kv + split - 1) / split;  // selection guarantees >= 1 each
+      kv_begin = min(num_kv, part * per);
+      num_kv = min(num_kv, kv_begin + per) - kv_begin;
+      record = r;
+    }
+    batch = unit / tiles_m;
+    m_cta = (unit % tiles_m) * (Cfg::kTilesPerCta * BM);
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(tm_q);
@@ -188,7 +213,7 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
       }
       uint32_t ks = 0, kphase = 0, vs = 0, vphase = 0;
       for (uint32_t j = 0; j < num_kv; ++j) {
-        const int row0 = (int)(j * BN);
+        const int row0 = (int)((kv_begin + j) * BN);
         mbar_wait(bar_k_empty + 8 * ks, kphase ^ 1);
         mbar_expect_tx(bar_k_full + 8 * ks, Cfg::kTileBytes);
         for (int c = 0; c < Cfg::kChunks; ++c) {
@@ -347,7 +372,7 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         tmem_ld_32x32b_x32(tmem_s + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
       }
       tmem_wait_ld();
-      const int valid = K2 - (int)(j * BN);  // columns >= valid are TMA zero fill
+      const int valid = K2 - (int)((kv_begin + j) * BN);  // columns >= valid are TMA zero fill
       if (valid < BN) {
 #pragma unroll
         for (int i = 0; i < BN; ++i) {
@@ -417,6 +442,27 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     // ---- epilogue: O = cast((1/sum) * acc) ----
     mbar_wait(bar_o_done, 0);
     tcgen05_fence_after();
+    if (kSplit && record >= 0) {
+      // Split CTA: leave (acc, max, sum) for the merge kernel. m_run may be the stale max of
+      // the lazy rescale; acc and l_run are relative to it, so the record is consistent.
+      constexpr int kRows = Cfg::kTilesPerCta * BM;
+      float* rec = workspace + (size_t)record * (kRows * (D + 2));
+      const int r = t * BM + (int)row;
+      float4* arow = reinterpret_cast<float4*>(rec + (size_t)r * D);
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(tmem_o + c * 32, o);
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          arow[c * 8 + i] = make_float4(__uint_as_float(o[4 * i]), __uint_as_float(o[4 * i + 1]),
+                                        __uint_as_float(o[4 * i + 2]), __uint_as_float(o[4 * i + 3]));
+        }
+      }
+      rec[kRows * D + r] = m_run;
+      rec[kRows * (D + 1) + r] = l_run;
+    } else {
     const float rcp = 1.0f / l_run;
     const int gm = m_cta + t * BM + (int)row;
     uint16_t* orow = reinterpret_cast<uint16_t*>(out) + ((size_t)batch * M + gm) * D;
@@ -437,6 +483,7 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         }
       }
     }
+    }  // !split
   }
 
   __syncwarp();

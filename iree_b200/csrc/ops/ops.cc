@@ -43,7 +43,9 @@ enum AttentionExport {
   kAttnGeneric = 3,
   kAttnDecodeCluster = 4,
   kAttnPrefillPoly25 = 5,
-  kAttnPrefillPoly50 = 6
+  kAttnPrefillPoly50 = 6,
+  kAttnPrefillSplit = 7,
+  kAttnPrefillMerge = 8
 };
 
 }  // namespace
@@ -57,7 +59,7 @@ struct iree_b200_ops_t {
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[6][2][kFamilyCount];
   int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
-  int32_t attention_exports[4][8];
+  int32_t attention_exports[4][12];
   // Host-buffer calls: staging arena, transfer streams and events (grow-only, reused).
   std::mutex host_mutex;
   uint64_t pipeline_min_bytes = 16ull << 20;
@@ -131,7 +133,7 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
     }
   }
   for (int t = 0; t < 4; ++t) {
-    for (int e = 0; e < 8; ++e) ops->attention_exports[t][e] = -1;
+    for (int e = 0; e < 12; ++e) ops->attention_exports[t][e] = -1;
   }
   ops->attention_exports[IREE_B200_ELEMENT_TYPE_F32][kAttnGeneric] =
       lookup(ops->executable, "iree_b200_attention_generic_f32");
@@ -143,6 +145,10 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
         lookup(ops->executable, "iree_b200_attention_prefill_" + suffix + "_p25");
     ops->attention_exports[t][kAttnPrefillPoly50] =
         lookup(ops->executable, "iree_b200_attention_prefill_" + suffix + "_p50");
+    ops->attention_exports[t][kAttnPrefillSplit] =
+        lookup(ops->executable, "iree_b200_attention_prefill_split_" + suffix);
+    ops->attention_exports[t][kAttnPrefillMerge] =
+        lookup(ops->executable, "iree_b200_attention_prefill_merge_" + suffix);
     ops->attention_exports[t][kAttnDecodeSplit] =
         lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
     ops->attention_exports[t][kAttnDecodeMerge] =
@@ -684,6 +690,46 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       if (flags & IREE_B200_ATTENTION_FLAG_EXP2_MUFU_ONLY) variant = kAttnPrefill;
       if (flags & IREE_B200_ATTENTION_FLAG_EXP2_POLY_25) variant = kAttnPrefillPoly25;
       if (flags & IREE_B200_ATTENTION_FLAG_EXP2_POLY_50) variant = kAttnPrefillPoly50;
+      // Tail split: all units (two Q tiles of one batch slice) cost the same, so the last
+      // wave of the grid is only partly full unless the unit count divides by the SM count.
+      // Cut just that wave's units into |split| CTAs over K2 (+ one small merge dispatch)
+      // when that makes the last wave at most half as long.
+      const int64_t tiles_m = ceil_div(M, 256);
+      const int64_t units = tiles_m * B;
+      const int64_t sms = ops->device->sm_count;
+      const int64_t kv_blocks = ceil_div(K2, 128);
+      const int64_t full_units = units / sms * sms;
+      const int64_t tail_units = units - full_units;
+      int64_t split = tail_units ? std::min<int64_t>(4, sms / tail_units) : 1;
+      split = std::min(split, kv_blocks / 4);  // every part keeps >= 4 K2 blocks
+      const bool use_split = !(flags & IREE_B200_ATTENTION_FLAG_NO_TAIL_SPLIT) && split >= 2 &&
+                             variant == kAttnPrefill && full_units + tail_units * split <= 0x7fffffff;
+      if (use_split) {
+        d0->export_ordinal = ops->attention_exports[element_type][kAttnPrefillSplit];
+        d0->workgroup_count[0] = (uint32_t)(full_units + tail_units * split);
+        d0->workgroup_count[1] = 1;
+        d0->workgroup_count[2] = 1;
+        d0->constant_count = 6;
+        d0->constants[0] = (uint32_t)B;
+        d0->constants[1] = (uint32_t)M;
+        d0->constants[2] = (uint32_t)K2;
+        d0->constants[3] = scale_bits;
+        d0->constants[4] = (uint32_t)full_units;
+        d0->constants[5] = (uint32_t)split;
+        d1->export_ordinal = ops->attention_exports[element_type][kAttnPrefillMerge];
+        d1->workgroup_count[0] = 32;  // 256 rows of a unit, 8 per CTA
+        d1->workgroup_count[1] = (uint32_t)tail_units;
+        d1->workgroup_count[2] = 1;
+        d1->constant_count = 5;
+        d1->constants[0] = (uint32_t)B;
+        d1->constants[1] = (uint32_t)M;
+        d1->constants[2] = (uint32_t)full_units;
+        d1->constants[3] = (uint32_t)split;
+        d1->constants[4] = (uint32_t)tail_units;
+        out_selection->dispatch_count = 2;
+        out_selection->workspace_bytes = (uint64_t)tail_units * split * 256 * (128 + 2) * 4;
+        break;
+      }
       d0->export_ordinal = ops->attention_exports[element_type][variant];
       d0->workgroup_count[0] = (uint32_t)ceil_div(M, 256);
       d0->workgroup_count[1] = (uint32_t)B;
@@ -832,10 +878,16 @@ iree_b200_status_t iree_b200_ops_record_attention(
     B200_RETURN_IF_ERROR(check_binding("workspace", workspace, sel.workspace_bytes, &ignored));
   }
   if (sel.dispatch_count == 2) {
-    const iree_b200_buffer_ref_t split_refs[4] = {q, k, v, workspace};
+    // Decode split: (Q, K, V, workspace) then (workspace, O). Prefill tail split:
+    // (Q, K, V, O, workspace) then (workspace, O).
+    const bool prefill_split =
+        sel.dispatches[0].export_ordinal == ops->attention_exports[element_type][kAttnPrefillSplit];
+    const iree_b200_buffer_ref_t decode_refs[4] = {q, k, v, workspace};
+    const iree_b200_buffer_ref_t prefill_refs[5] = {q, k, v, out, workspace};
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
         cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
-        sel.dispatches[0].constants, sel.dispatches[0].constant_count, split_refs, 4, 0));
+        sel.dispatches[0].constants, sel.dispatches[0].constant_count,
+        prefill_split ? prefill_refs : decode_refs, prefill_split ? 5 : 4, 0));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
     const iree_b200_buffer_ref_t merge_refs[2] = {workspace, out};
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(

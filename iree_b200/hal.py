@@ -38,6 +38,7 @@ ATTENTION_FORCE_DECODE_CLUSTER = 1 << 12
 ATTENTION_EXP2_MUFU_ONLY = 1 << 13
 ATTENTION_EXP2_POLY_25 = 1 << 14
 ATTENTION_EXP2_POLY_50 = 1 << 15
+ATTENTION_NO_TAIL_SPLIT = 1 << 16
 
 MODE_GRAPH, MODE_STREAM = 0, 1
 MEMORY_DEVICE_LOCAL, MEMORY_HOST_LOCAL = 1, 2

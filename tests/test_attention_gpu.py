@@ -174,9 +174,14 @@ def test_generic_kernel_vs_oracle(ops, t, mask_kind, shape):
 def test_selection_guards(ops):
     exe = ops.executable
     names = lambda sel: [exe.export_info(d["export_ordinal"])["kernel_name"] for d in sel["dispatches"]]
-    s = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088)
+    s = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088, flags=H.ATTENTION_NO_TAIL_SPLIT)
     assert names(s) == ["iree_b200_attention_prefill_f16"]
     assert s["dispatches"][0]["workgroup_count"] == [16, 32, 1]
+    # 512 equal units on 148 SMs: 444 run whole, the last 68 are cut in two over K2.
+    s = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088)
+    assert names(s) == ["iree_b200_attention_prefill_split_f16", "iree_b200_attention_prefill_merge_f16"]
+    assert s["dispatches"][0]["workgroup_count"] == [444 + 68 * 2, 1, 1]
+    assert s["dispatches"][0]["constants"][4:6] == [444, 2]
     s = ops.select_attention("f16", 32, 1, 128, 8192, 128, 0.088)
     assert names(s) == ["iree_b200_attention_decode_cluster_f16"]
     assert s["dispatches"][0]["workgroup_count"] == [8, 1, 32] and s["workspace_bytes"] == 0
@@ -229,3 +234,27 @@ def test_llama_decode_shape(ops, t):
     got = _gpu_attention(ops, t, q, k, v, scale)
     want = oracle.attention(t, q, k, v, scale, k2_tile=256)
     _assert_close(t, got, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("shape", [(4, 512, 1024), (2, 300, 1100), (5, 700, 2048), (1, 256, 4096),
+                                   (3, 130, 513)], ids=str)
+def test_prefill_tail_split(ops, t, shape):
+    """The tail-split form of the prefill kernel (units of the last, partly filled wave cut
+    over K2 + merge dispatch): selected for these shapes, same tolerance against the oracle,
+    and within rounding of the unsplit kernel. Ragged M and K2, 2- and 4-way splits."""
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=3 * M + K2)
+    scale = 1.0 / np.sqrt(128.0)
+    sel = ops.select_attention(t, B, M, 128, K2, 128, scale, flags=H.ATTENTION_FORCE_PREFILL)
+    exe = ops.executable
+    names = [exe.export_info(d["export_ordinal"])["kernel_name"] for d in sel["dispatches"]]
+    assert names == [f"iree_b200_attention_prefill_split_{t}", f"iree_b200_attention_prefill_merge_{t}"]
+    split = sel["dispatches"][0]["constants"][5]
+    assert split >= 2 and sel["workspace_bytes"] == sel["dispatches"][1]["workgroup_count"][1] * split * 256 * 130 * 4
+    got = _gpu_attention(ops, t, q, k, v, scale, flags=H.ATTENTION_FORCE_PREFILL)
+    want = oracle.attention(t, q, k, v, scale, k2_tile=128)
+    _assert_close(t, got, want)
+    whole = _gpu_attention(ops, t, q, k, v, scale,
+                           flags=H.ATTENTION_FORCE_PREFILL | H.ATTENTION_NO_TAIL_SPLIT)
+    _assert_close(t, got, whole)

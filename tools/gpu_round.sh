@@ -15,6 +15,11 @@ bench)
     run bench_$w 300 python bench.py --workload $w --no-cpu-baseline --steps 100
   done
   run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
+prefillsplit)
+  run pytest_attn 400 python -m pytest tests/test_attention_gpu.py -m gpu -x -q
+  run bench_prefill_split 200 python bench.py --workload attention_prefill --no-cpu-baseline --steps 200 --e2e-steps 1
+  run bench_prefill_nosplit 200 python bench.py --workload attention_prefill --no-cpu-baseline --steps 200 --e2e-steps 1 --attention-flags 0x10000
+  run bench_prefill_bf16_split 200 python bench.py --workload attention_prefill_bf16 --no-cpu-baseline --steps 200 --e2e-steps 1 ;;
 prefillsweep)
   run pytest_prefill 300 python -m pytest tests/test_attention_gpu.py -m gpu -x -q -k "prefill"
   for v in 0x2000 0x4000 0x8000; do
