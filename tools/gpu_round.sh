@@ -15,6 +15,13 @@ bench)
     run bench_$w 300 python bench.py --workload $w --no-cpu-baseline --steps 100
   done
   run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
+final)
+  run pytest 900 python -m pytest tests -m gpu -q
+  run smoke 300 python -c "import __graft_entry__ as g; g.smoke()"
+  run bench_matmul_bf16 400 python bench.py
+  run bench_attention_prefill 300 python bench.py --workload attention_prefill --no-cpu-baseline --steps 200
+  run bench_attention_prefill_bf16 300 python bench.py --workload attention_prefill_bf16 --no-cpu-baseline --steps 200
+  run bench_reference 300 python bench.py --impl reference --steps 2 --warmup 1 ;;
 prefillsplit)
   run pytest_attn 400 python -m pytest tests/test_attention_gpu.py -m gpu -x -q
   run bench_prefill_split 200 python bench.py --workload attention_prefill --no-cpu-baseline --steps 200 --e2e-steps 1
