@@ -54,15 +54,16 @@ struct TileCoord {
 };
 
 template <class Cfg>
-B200_DEVICE TileCoord decode_tile(uint32_t tile, uint32_t tiles_m, uint32_t tiles_n) {
+B200_DEVICE TileCoord decode_tile(uint32_t tile, uint32_t tiles_m, uint32_t tiles_n,
+                                  uint32_t group_rows = Cfg::kGroupM) {
   const uint32_t per_batch = tiles_m * tiles_n;
   TileCoord c;
   c.batch = tile / per_batch;
   const uint32_t t = tile % per_batch;
-  const uint32_t group_span = Cfg::kGroupM * tiles_n;
+  const uint32_t group_span = group_rows * tiles_n;
   const uint32_t group = t / group_span;
-  const uint32_t first_m = group * Cfg::kGroupM;
-  const uint32_t group_m = min(tiles_m - first_m, (uint32_t)Cfg::kGroupM);
+  const uint32_t first_m = group * group_rows;
+  const uint32_t group_m = min(tiles_m - first_m, group_rows);
   const uint32_t in_group = t % group_span;
   c.m_blk = first_m + in_group % group_m;
   c.n_blk = in_group / group_m;
@@ -109,6 +110,9 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
   const bool diag_no_store = (flags & 0x10) != 0;  // epilogue drains TMEM but stores nothing
   const bool diag_no_load = (flags & 0x20) != 0;   // no TMA loads; MMA does not wait for data
   const bool diag_no_mma = (flags & 0x40) != 0;    // MMA warp only recycles the ring
+  const bool diag_l2_hint = (flags & 0x80) != 0;   // A loads evict_last, B loads evict_first
+  // bits 8-15: raster group height override (tile rows walked before the column advances)
+  const uint32_t group_rows = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : Cfg::kGroupM;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(tm_a);
@@ -148,9 +152,10 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     if (!diag_no_load && elect_one()) {
       // All loads of the pair complete on the LEADER's full barrier.
       const uint32_t full0 = (G == 2) ? map_to_cta(bar_full, 0) : bar_full;
+      const uint64_t policy_keep = l2_policy_evict_last(), policy_stream = l2_policy_evict_first();
       uint32_t stage = 0, phase = 0;
       for (uint32_t tile = cluster_idx; tile < total_tiles; tile += cluster_cnt) {
-        const TileCoord tc = decode_tile<Cfg>(tile, tiles_m, tiles_n);
+        const TileCoord tc = decode_tile<Cfg>(tile, tiles_m, tiles_n, group_rows);
         const int m0 = tc.m_blk * Cfg::kTileM + (int)cta_rank * Cfg::kBlockM;
         const int n0 = tc.n_blk * Cfg::kTileN + (int)cta_rank * Cfg::kBlockN;
         for (uint32_t kb = 0; kb < num_kb; ++kb) {
@@ -160,6 +165,20 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
           if (is_leader) {
             mbar_expect_tx(bar_full + 8 * stage, Cfg::kStageBytes * G);
           }
+          if (diag_l2_hint) {
+            tma_load_3d_hint<G>(smem_a + stage * Cfg::kABytes, tm_a, full, k0, m0, tc.batch,
+                                policy_keep);
+            if constexpr (Cfg::kBMajorK) {
+              tma_load_3d_hint<G>(smem_b + stage * Cfg::kBBytes, tm_b, full, k0, n0, tc.batch,
+                                  policy_stream);
+            } else {
+#pragma unroll
+              for (int j = 0; j < Cfg::kBBoxes; ++j) {
+                tma_load_3d_hint<G>(smem_b + stage * Cfg::kBBytes + j * Cfg::kBBoxBytes, tm_b, full,
+                                    n0 + j * Cfg::kBBoxN, k0, tc.batch, policy_stream);
+              }
+            }
+          } else {
           tma_load_3d<G>(smem_a + stage * Cfg::kABytes, tm_a, full, k0, m0, tc.batch);
           if constexpr (Cfg::kBMajorK) {
             tma_load_3d<G>(smem_b + stage * Cfg::kBBytes, tm_b, full, k0, n0, tc.batch);
@@ -169,6 +188,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
               tma_load_3d<G>(smem_b + stage * Cfg::kBBytes + j * Cfg::kBBoxBytes, tm_b, full,
                              n0 + j * Cfg::kBBoxN, k0, tc.batch);
             }
+          }
           }
           if (++stage == Cfg::kStages) {
             stage = 0;
@@ -232,7 +252,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     uint32_t acc = 0, acc_phase = 0;
     uint32_t buf = 0;
     for (uint32_t tile = cluster_idx; tile < total_tiles; tile += cluster_cnt) {
-      const TileCoord tc = decode_tile<Cfg>(tile, tiles_m, tiles_n);
+      const TileCoord tc = decode_tile<Cfg>(tile, tiles_m, tiles_n, group_rows);
       const int m0 = tc.m_blk * Cfg::kTileM + (int)cta_rank * Cfg::kBlockM;
       const int n0 = tc.n_blk * Cfg::kTileN;
       mbar_wait(bar_tfull + 8 * acc, acc_phase);

@@ -471,6 +471,15 @@ iree_b200_status_t matmul_host_serial(iree_b200_ops_t* ops, int32_t element_type
 //   B   per batch, column panels [K, nb_j] packed one after the other (2-D upload);
 //       with TRANSPOSE_RHS a panel is rows of [N, K] and already contiguous
 //   C   per batch and row panel, blocks [mb_i, nb_j] packed one after the other (2-D download)
+// Panel boundaries of one result dimension for the pipelined host call: whole blocks, then
+// the remainder. (A half-height first panel, to shorten the fill, measured 3 % slower at
+// 8192^3 — profiles/host_pipeline_sweep_r1.json — so the panels stay uniform.)
+std::vector<int64_t> panel_edges(int64_t extent, int64_t block) {
+  std::vector<int64_t> edges{0};
+  while (edges.back() < extent) edges.push_back(std::min(extent, edges.back() + block));
+  return edges;
+}
+
 iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_type,
                                          int64_t batch, int64_t M, int64_t N, int64_t K,
                                          uint32_t flags, const uint64_t bytes[3], const void* lhs,
@@ -482,8 +491,12 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const bool transpose_rhs = (flags & IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS) != 0;
   const bool accumulate = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) != 0;
-  const int64_t mb = ops->pipeline_block_m, nb = ops->pipeline_block_n;
-  const int64_t P = ceil_div(M, mb), Q = ceil_div(N, nb);
+  // Uploading a fraction f of both operands enables only f^2 of the result: the download
+  // stream idles early and runs behind late, whatever the panel order (the diagonal order
+  // used here maximises the enabled area at every instant).
+  const std::vector<int64_t> m_edges = panel_edges(M, ops->pipeline_block_m);
+  const std::vector<int64_t> n_edges = panel_edges(N, ops->pipeline_block_n);
+  const int64_t P = (int64_t)m_edges.size() - 1, Q = (int64_t)n_edges.size() - 1;
   const uint64_t off_a = 0;
   const uint64_t off_b = (bytes[0] + 1023) / 1024 * 1024;
   const uint64_t off_c = off_b + (bytes[1] + 1023) / 1024 * 1024;
@@ -507,24 +520,25 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
     const int64_t steps = std::max(P, Q);
     for (int64_t s = 0; s < steps; ++s) {
       if (s < P) {  // row panel s of A
-        const int64_t rows = std::min(mb, M - s * mb);
-        const uint64_t at = ((uint64_t)b * M + (uint64_t)s * mb) * K * es;
+        const int64_t rows = m_edges[s + 1] - m_edges[s];
+        const uint64_t at = ((uint64_t)b * M + (uint64_t)m_edges[s]) * K * es;
         B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_a + at, const_cast<uint8_t*>(host_a) + at,
                                      K * es, K * es, rows, ops->upload_stream));
         B200_RETURN_IF_ERROR(event_at(ops, next_event++, &a_ready[s]));
         B200_CU(cu, cuEventRecord(a_ready[s], ops->upload_stream));
       }
       if (s < Q) {  // column panel s of B
-        const int64_t cols = std::min(nb, N - s * nb);
+        const int64_t cols = n_edges[s + 1] - n_edges[s];
+        const uint64_t col0 = (uint64_t)n_edges[s];
         const uint64_t batch_at = (uint64_t)b * K * N * es;
         if (transpose_rhs) {
-          const uint64_t at = batch_at + (uint64_t)s * nb * K * es;
+          const uint64_t at = batch_at + col0 * K * es;
           B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_b + at,
                                        const_cast<uint8_t*>(host_b) + at, K * es, K * es, cols,
                                        ops->upload_stream));
         } else {
-          B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_b + batch_at + (uint64_t)K * s * nb * es,
-                                       const_cast<uint8_t*>(host_b) + batch_at + (uint64_t)s * nb * es,
+          B200_RETURN_IF_ERROR(copy_2d(cu, true, base + off_b + batch_at + (uint64_t)K * col0 * es,
+                                       const_cast<uint8_t*>(host_b) + batch_at + col0 * es,
                                        N * es, cols * es, K, ops->upload_stream));
         }
         B200_RETURN_IF_ERROR(event_at(ops, next_event++, &b_ready[s]));
@@ -534,12 +548,13 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
       for (int64_t i = 0; i <= std::min(s, P - 1); ++i) {
         for (int64_t j = 0; j <= std::min(s, Q - 1); ++j) {
           if (std::max(i, j) != s) continue;
-          const int64_t rows = std::min(mb, M - i * mb), cols = std::min(nb, N - j * nb);
-          const uint64_t a_at = ((uint64_t)b * M + (uint64_t)i * mb) * K * es;
-          const uint64_t b_at = (uint64_t)b * K * N * es + (uint64_t)K * j * nb * es;
-          const uint64_t c_at =
-              ((uint64_t)b * M * N + (uint64_t)i * mb * N + (uint64_t)rows * j * nb) * out_es;
-          uint8_t* c_host = host_c + ((uint64_t)b * M * N + (uint64_t)i * mb * N + (uint64_t)j * nb) * out_es;
+          const int64_t rows = m_edges[i + 1] - m_edges[i], cols = n_edges[j + 1] - n_edges[j];
+          const uint64_t row0 = (uint64_t)m_edges[i], col0 = (uint64_t)n_edges[j];
+          const uint64_t a_at = ((uint64_t)b * M + row0) * K * es;
+          const uint64_t b_at = (uint64_t)b * K * N * es + (uint64_t)K * col0 * es;
+          // Staged result: row panel i is a run of dense [rows, cols_j] blocks.
+          const uint64_t c_at = ((uint64_t)b * M * N + row0 * N + (uint64_t)rows * col0) * out_es;
+          uint8_t* c_host = host_c + ((uint64_t)b * M * N + row0 * N + col0) * out_es;
           // The upload stream is in order (A_s, then B_s): the later panel's event covers both.
           CUevent ready = (j == s) ? b_ready[j] : a_ready[i];
           if (accumulate) {

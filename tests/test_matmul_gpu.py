@@ -248,15 +248,21 @@ def test_truncating_epilogue_guards(ops):
     (2, 513, 64, 768, False, False, True),      # truncating epilogue (2-byte result blocks)
     (1, 256, 128, 2048, False, False, False),   # one row panel, 8 column panels
     (1, 2048, 128, 256, True, False, False),    # 8 row panels, one column panel
+    # 512-blocks
+    (1, 1536, 144, 1280, False, False, False, 512),
+    (1, 1104, 80, 1040, False, True, False, 512),
+    (2, 1024, 64, 1296, True, False, False, 512),
+    (1, 1280, 64, 784, False, False, True, 512),
 ], ids=str)
 def test_pipelined_host_call(ops, t, case):
     """iree_b200_ops_matmul_host as a pipeline (panel uploads, per-block dispatch, block
     downloads on three streams): same bits as the single-dispatch form and the oracle."""
-    batch, M, K, N, accumulate, nt, truncate = case
+    batch, M, K, N, accumulate, nt, truncate = case[:7]
+    block = case[7] if len(case) > 7 else 256
     if truncate and elem_size(t) == 1:
         pytest.skip("TRUNCATE_RESULT is f16 / bf16 only")
     before = ops.dispatch_count
-    ops.set_host_pipeline(0, 256, 256)
+    ops.set_host_pipeline(0, block, block)
     try:
         if truncate:
             lhs = oracle.generate_random_matrix(t, (batch, M, K), 1)
@@ -270,5 +276,5 @@ def test_pipelined_host_call(ops, t, case):
     finally:
         ops.set_host_pipeline(16 << 20, 2048, 2048)
     assert np.array_equal(out, want)
-    blocks = batch * -(-M // 256) * -(-N // 256)
+    blocks = batch * -(-M // block) * -(-N // block)
     assert ops.dispatch_count - before == blocks

@@ -1,6 +1,6 @@
 """GEMM pipeline diagnostics on a B200: times each tcgen05 matmul export on one shape with
 the kernel's diagnostic flag bits (gemm_sm100.cuh: 0x10 no store, 0x20 no load, 0x40 no
-MMA) so the slowest pipeline leg can be read off directly. Results under a diagnostic bit
+MMA, 0x80 L2 eviction hints on the TMA loads, bits 8-15 raster group height) so the slowest pipeline leg can be read off directly. Results under a diagnostic bit
 are garbage by construction; flag 0 is the real kernel. Also times torch.matmul (cuBLAS)
 on the same operands as the live roofline denominator.
 
@@ -91,6 +91,12 @@ def main():
                     ms = e0.elapsed_time(e1) / args.iters
                     rows.append({"type": et, "kernel": name, "grid": sel["workgroup_count"][0],
                                  "diag": hex(diag), "ms": ms, "tflops": flop / ms / 1e9})
+                    if (diag & 0x70) == 0:
+                        # 0x80 (L2 hints) and bits 8-15 (raster group height) keep the result.
+                        if diag == 0:
+                            want = c.clone()
+                        elif "want" in locals():
+                            rows[-1]["same_result"] = bool(torch.equal(c, want))
                     print(json.dumps(rows[-1]), flush=True)
     if args.out:
         with open(args.out, "w") as f:
