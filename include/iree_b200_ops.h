@@ -47,6 +47,16 @@ enum {
   // The dispatch also holds the consumer arith.truncf: out has the operands' element type
   // (f16 / bf16 only, round to nearest even; not combinable with ACCUMULATE).
   IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT = 1u << 2,
+  // The dispatch also holds the consumer elementwise op (what IREE's
+  // dispatch creation fuses behind a contraction, compiler/src/iree/compiler/DispatchCreation):
+  //   x = (out +) lhs·rhs + bias[n]        BIAS: one more binding, bias [N] in the accumulator
+  //                                        type (f32 / i32), broadcast along batch and M
+  //   x = max(x, 0)                        RELU (needs BIAS): arith.maximumf / arith.maxsi —
+  //                                        NaN propagates, -0 becomes +0
+  // then TRUNCATE_RESULT if set. i8, f16, bf16 (not the f8 types). Selected through
+  // iree_b200_ops_select_matmul with these flags; recorded with ..._record_matmul_bias.
+  IREE_B200_MATMUL_FLAG_BIAS = 1u << 3,
+  IREE_B200_MATMUL_FLAG_RELU = 1u << 4,
   // Diagnostics: force a kernel family regardless of the shape heuristics.
   IREE_B200_MATMUL_FLAG_FORCE_GENERIC = 1u << 8,
   IREE_B200_MATMUL_FLAG_FORCE_1CTA = 1u << 9,
@@ -115,6 +125,18 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul(
     iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t batch,
     int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out);
+
+// As iree_b200_ops_record_matmul for the FLAG_BIAS dispatches (bindings lhs, rhs, bias, out;
+// FLAG_BIAS is implied). |bias| holds N accumulator-type values.
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_bias(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t batch,
+    int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t bias, iree_b200_buffer_ref_t out);
+
+// Host-buffer form of the FLAG_BIAS dispatches (upload, one dispatch, download).
+IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_bias_host(
+    iree_b200_ops_t* ops, int32_t element_type, int64_t batch, int64_t M, int64_t N, int64_t K,
+    uint32_t flags, const void* lhs, const void* rhs, const void* bias, void* out);
 
 // Host-buffer form. |out| holds batch*M*N f32 / i32 values (operand-type values with
 // FLAG_TRUNCATE_RESULT); with FLAG_ACCUMULATE it is also the accumulator input.

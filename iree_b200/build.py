@@ -30,7 +30,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "_build")
 INCLUDE = os.path.join(ROOT, "include")
 
-KERNEL_UNITS = ["gemm_kernels", "generic_kernels", "attention_kernels", "collective_kernels"]
+KERNEL_UNITS = ["gemm_kernels", "gemm_bias_kernels", "generic_kernels", "attention_kernels", "collective_kernels"]
 HOST_SOURCES = ["hal/device.cc", "hal/executable.cc", "hal/command_buffer.cc", "hal/channel.cc",
                 "ops/ops.cc"]
 

@@ -36,10 +36,13 @@ B200_HOST_DEVICE constexpr uint32_t make_idesc(uint32_t c_fmt, uint32_t a_fmt, u
 
 // kOut16: the epilogue truncates the f32 accumulator to the operand type (the fused
 // `linalg.matmul + arith.truncf` dispatch), halving the C traffic.
+// kBias: the dispatch also holds the consumer elementwise op `act(x + bias[n])` (a bias
+// binding between rhs and out; see gemm_bias_kernels.cu).
 template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_,
-          bool kOut16_ = false>
+          bool kOut16_ = false, bool kBias_ = false>
 struct GemmConfig {
   static constexpr bool kOut16 = kOut16_;
+  static constexpr bool kBias = kBias_;
   static constexpr int kCtaGroup = kCtaGroup_;
   static constexpr int kKind = kKind_;
   static constexpr uint32_t kAbFmt = kAbFmt_;

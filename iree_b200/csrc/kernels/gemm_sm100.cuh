@@ -75,7 +75,8 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
                                                 const void* __restrict__ rhs, void* __restrict__ out,
                                                 int M, int N, int K, int batch, int flags,
                                                 const TensorMap* tm_a, const TensorMap* tm_b,
-                                                const TensorMap* tm_c) {
+                                                const TensorMap* tm_c,
+                                                const void* __restrict__ bias = nullptr) {
   constexpr int G = Cfg::kCtaGroup;
   (void)lhs;
   (void)rhs;
@@ -249,6 +250,25 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     const bool epi_leader = (warp == 4) && (lane == 0);
     const uint32_t tempty0 = (G == 2) ? map_to_cta(bar_tempty, 0) : bar_tempty;
     const bool accumulate = (flags & 1) != 0;
+    const bool relu = (flags & 2) != 0;  // kBias exports only
+    (void)relu;
+    // The fused consumer: x + bias[column], then optionally max(x, 0) with arith.maximumf /
+    // arith.maxsi semantics (NaN propagates, -0 -> +0).
+    auto fuse = [&](uint32_t bits, int gn) -> uint32_t {
+      if constexpr (!Cfg::kBias) {
+        return bits;
+      } else if constexpr (Cfg::kKind == KIND_I8) {
+        int32_t x = (int32_t)bits;
+        if (gn < N) x += __ldg(reinterpret_cast<const int32_t*>(bias) + gn);
+        if (relu) x = max(x, 0);
+        return (uint32_t)x;
+      } else {
+        float x = __uint_as_float(bits);
+        if (gn < N) x += __ldg(reinterpret_cast<const float*>(bias) + gn);
+        if (relu) x = (x > 0.f || x != x) ? x : 0.f;
+        return __float_as_uint(x);
+      }
+    };
     uint32_t acc = 0, acc_phase = 0;
     uint32_t buf = 0;
     for (uint32_t tile = cluster_idx; tile < total_tiles; tile += cluster_cnt) {
@@ -270,6 +290,14 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
           tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols, v);
           tmem_ld_32x32b_x32(taddr0 + c * Cfg::kEpiCols + 32, hi);
           tmem_wait_ld();
+          if constexpr (Cfg::kBias) {
+            const int gn = n0 + c * Cfg::kEpiCols;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              v[i] = fuse(v[i], gn + i);
+              hi[i] = fuse(hi[i], gn + 32 + i);
+            }
+          }
 #pragma unroll
           for (int i = 0; i < 16; ++i) {
             v[i] = pack_pair<Cfg::kAbFmt == FMT_BF16>(__uint_as_float(v[2 * i]),
@@ -313,6 +341,11 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
                 if (gn + i < N) v[i] = __float_as_uint(__uint_as_float(v[i]) + cin[i]);
             }
           }
+        }
+        if constexpr (Cfg::kBias && !Cfg::kOut16) {
+          const int gn = n0 + c * Cfg::kEpiCols;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) v[i] = fuse(v[i], gn + i);
         }
         // 128-byte rows, 16-byte chunks XOR-swizzled by (row % 8) == SWIZZLE_128B.
         const uint32_t row_addr = smem_epi + buf * Cfg::kEpiBytes + row * 128;
@@ -359,7 +392,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
 }
 
 // Fills the `<kernel>__tma` recipe for a GEMM config. Push constants: 0=M 1=N 2=K
-// 3=batch 4=flags. Bindings: 0=A 1=B 2=C.
+// 3=batch 4=flags. Bindings: 0=A 1=B 2=C (bias exports: 2=bias 3=C).
 template <class Cfg>
 constexpr iree_b200_tma_recipe_t make_gemm_recipe() {
   iree_b200_tma_recipe_t r = {};
@@ -400,7 +433,7 @@ constexpr iree_b200_tma_recipe_t make_gemm_recipe() {
   r.maps[1].box[2] = 1;
   r.maps[1].swizzle = IREE_B200_TMA_SWIZZLE_128B;
   // C [batch, M, N] (32-bit elements)
-  r.maps[2].binding = 2;
+  r.maps[2].binding = Cfg::kBias ? 3 : 2;
   r.maps[2].elem_type = Cfg::kOut16 ? ab_type
                                     : (Cfg::kKind == KIND_I8 ? IREE_B200_TMA_I32 : IREE_B200_TMA_F32);
   r.maps[2].elem_size = Cfg::kOut16 ? 2 : 4;

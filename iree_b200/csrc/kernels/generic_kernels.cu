@@ -58,7 +58,8 @@ template <typename TIn, typename TAcc>
 __device__ __forceinline__ void matmul_generic_body(const TIn* __restrict__ lhs,
                                                     const TIn* __restrict__ rhs,
                                                     TAcc* __restrict__ out, int M, int N, int K,
-                                                    int flags) {
+                                                    int flags,
+                                                    const TAcc* __restrict__ bias = nullptr) {
   __shared__ TAcc a_tile[kTileK][kTile + 1];
   __shared__ TAcc b_tile[kTileK][kTile + 1];
 
@@ -130,14 +131,19 @@ __device__ __forceinline__ void matmul_generic_body(const TIn* __restrict__ lhs,
     for (int j = 0; j < 4; ++j) {
       const int gn = n0 + tx + 16 * j;
       if (gn >= N) continue;
+      TAcc x = acc[i][j];
+      if (bias) {  // fused consumer: x + bias[n], then (flags & 8) max(x, 0), NaN propagating
+        x += bias[gn];
+        if (flags & 8) x = (x > TAcc(0) || x != x) ? x : TAcc(0);
+      }
       if constexpr (sizeof(TIn) == 2) {
         if (flags & 4) {  // fused arith.truncf: the result buffer holds operand-type elements
           reinterpret_cast<TIn*>(out - (size_t)b * M * N)[((size_t)b * M + gm) * N + gn] =
-              from_acc<TIn>(acc[i][j]);
+              from_acc<TIn>(x);
           continue;
         }
       }
-      out[(size_t)gm * N + gn] = acc[i][j];
+      out[(size_t)gm * N + gn] = x;
     }
   }
 }
@@ -167,6 +173,36 @@ extern "C" __global__ void __launch_bounds__(256)
                                     int flags) {
   (void)batch;
   matmul_generic_body<int8_t, int32_t>(lhs, rhs, out, M, N, K, flags);
+}
+
+// Bias / activation forms (bindings lhs, rhs, bias[N], out; flags bit 3 = relu): the
+// fallback of gemm_bias_kernels.cu for shapes that fail the TMA guards.
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_bias_bf16_f32(const __nv_bfloat16* __restrict__ lhs,
+                                           const __nv_bfloat16* __restrict__ rhs,
+                                           const float* __restrict__ bias, float* __restrict__ out,
+                                           int M, int N, int K, int batch, int flags) {
+  (void)batch;
+  matmul_generic_body<__nv_bfloat16, float>(lhs, rhs, out, M, N, K, flags, bias);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_bias_f16_f32(const __half* __restrict__ lhs,
+                                          const __half* __restrict__ rhs,
+                                          const float* __restrict__ bias, float* __restrict__ out,
+                                          int M, int N, int K, int batch, int flags) {
+  (void)batch;
+  matmul_generic_body<__half, float>(lhs, rhs, out, M, N, K, flags, bias);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_bias_i8_i32(const int8_t* __restrict__ lhs,
+                                         const int8_t* __restrict__ rhs,
+                                         const int32_t* __restrict__ bias,
+                                         int32_t* __restrict__ out, int M, int N, int K, int batch,
+                                         int flags) {
+  (void)batch;
+  matmul_generic_body<int8_t, int32_t>(lhs, rhs, out, M, N, K, flags, bias);
 }
 
 extern "C" __global__ void __launch_bounds__(256)

@@ -59,6 +59,8 @@ struct iree_b200_ops_t {
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[6][2][kFamilyCount];
   int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
+  int32_t matmul_bias_exports[6][2][kFamilyCount];        // bias / activation epilogue
+  int32_t matmul_bias_trunc_exports[6][2][kFamilyCount];  // ... then truncation
   int32_t attention_exports[4][12];
   // Host-buffer calls: staging arena, transfer streams and events (grow-only, reused).
   std::mutex host_mutex;
@@ -117,6 +119,7 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
     for (int nt = 0; nt < 2; ++nt) {
       for (int f = 0; f < kFamilyCount; ++f) {
         ops->matmul_exports[t][nt][f] = ops->matmul_trunc_exports[t][nt][f] = -1;
+        ops->matmul_bias_exports[t][nt][f] = ops->matmul_bias_trunc_exports[t][nt][f] = -1;
       }
       if (!kTypeSuffix[t]) continue;
       const std::string base = std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTypeSuffix[t];
@@ -124,7 +127,22 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
       ops->matmul_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta");
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
+      if (t <= IREE_B200_ELEMENT_TYPE_BF16) {  // i8, f16, bf16
+        const std::string bbase =
+            std::string("iree_b200_matmul_bias_") + (nt ? "nt_" : "") + kTypeSuffix[t];
+        ops->matmul_bias_exports[t][nt][kFamily2Cta] = lookup(ops->executable, bbase);
+        ops->matmul_bias_exports[t][nt][kFamily1Cta] = lookup(ops->executable, bbase + "_1cta");
+        ops->matmul_bias_exports[t][nt][kFamilyGeneric] = lookup(
+            ops->executable, std::string("iree_b200_matmul_generic_bias_") + kTypeSuffix[t]);
+      }
       if (!kTruncSuffix[t]) continue;
+      const std::string btbase =
+          std::string("iree_b200_matmul_bias_") + (nt ? "nt_" : "") + kTruncSuffix[t];
+      ops->matmul_bias_trunc_exports[t][nt][kFamily2Cta] = lookup(ops->executable, btbase);
+      ops->matmul_bias_trunc_exports[t][nt][kFamily1Cta] =
+          lookup(ops->executable, btbase + "_1cta");
+      ops->matmul_bias_trunc_exports[t][nt][kFamilyGeneric] =
+          ops->matmul_bias_exports[t][nt][kFamilyGeneric];
       const std::string tbase =
           std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTruncSuffix[t];
       ops->matmul_trunc_exports[t][nt][kFamily2Cta] = lookup(ops->executable, tbase);
@@ -244,11 +262,20 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "TRUNCATE_RESULT applies to f16/bf16 without ACCUMULATE only");
   }
+  const bool with_bias = (flags & IREE_B200_MATMUL_FLAG_BIAS) != 0;
+  const bool relu = (flags & IREE_B200_MATMUL_FLAG_RELU) != 0;
+  if (relu && !with_bias) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "FLAG_RELU needs FLAG_BIAS");
+  }
+  if (with_bias && element_type > IREE_B200_ELEMENT_TYPE_BF16) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "the bias / activation dispatches exist for i8, f16 and bf16 only");
+  }
   out_selection->constants[0] = (uint32_t)M;
   out_selection->constants[1] = (uint32_t)N;
   out_selection->constants[2] = (uint32_t)K;
   out_selection->constants[3] = (uint32_t)batch;
-  out_selection->constants[4] = flags & IREE_B200_MATMUL_FLAG_ACCUMULATE;
+  out_selection->constants[4] = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) | (relu ? 2u : 0u);
   out_selection->export_ordinal = -1;
   if (batch == 0 || M == 0 || N == 0) return IREE_B200_STATUS_OK;  // empty result: no dispatch
 
@@ -276,9 +303,9 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
     // SM pairs only pay off once there are enough 256x256 tiles to occupy them.
     family = (M > 128 && tiles_2cta * 2 >= sm_count) ? kFamily2Cta : kFamily1Cta;
   }
-  const int32_t ordinal =
-      (truncate ? ops->matmul_trunc_exports
-                : ops->matmul_exports)[element_type][transpose_rhs ? 1 : 0][family];
+  const auto& table = with_bias ? (truncate ? ops->matmul_bias_trunc_exports : ops->matmul_bias_exports)
+                                : (truncate ? ops->matmul_trunc_exports : ops->matmul_exports);
+  const int32_t ordinal = table[element_type][transpose_rhs ? 1 : 0][family];
   if (ordinal < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND,
                        "the executable has no export for matmul type %d transpose_rhs %d family %d",
@@ -306,7 +333,10 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
       out_selection->workgroup_count[0] = (uint32_t)ceil_div(N, 64);
       out_selection->workgroup_count[1] = (uint32_t)ceil_div(M, 64);
       out_selection->workgroup_count[2] = (uint32_t)batch;
-      out_selection->constants[4] |= (transpose_rhs ? 2u : 0u) | (truncate ? 4u : 0u);
+      // The generic kernels' own flag word: 1 accumulate, 2 transpose_rhs, 4 truncate, 8 relu.
+      out_selection->constants[4] = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) |
+                                    (transpose_rhs ? 2u : 0u) | (truncate ? 4u : 0u) |
+                                    (relu ? 8u : 0u);
       break;
   }
   return IREE_B200_STATUS_OK;
@@ -318,23 +348,25 @@ static uint32_t pointer_alignment(uint64_t p) {
   return a;
 }
 
-iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
-                                               int32_t element_type, int64_t batch, int64_t M,
-                                               int64_t N, int64_t K, uint32_t flags,
-                                               iree_b200_buffer_ref_t lhs,
-                                               iree_b200_buffer_ref_t rhs,
-                                               iree_b200_buffer_ref_t out) {
+static iree_b200_status_t record_matmul_impl(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                             int32_t element_type, int64_t batch, int64_t M,
+                                             int64_t N, int64_t K, uint32_t flags,
+                                             const iree_b200_buffer_ref_t* refs, int ref_count) {
   B200_REQUIRE_ARG(ops && cb);
-  B200_REQUIRE_ARG(lhs.buffer && rhs.buffer && out.buffer);
+  for (int i = 0; i < ref_count; ++i) B200_REQUIRE_ARG(refs[i].buffer);
+  const bool with_bias = ref_count == 4;  // lhs, rhs, bias, out
   const uint64_t es = matmul_elem_size(element_type);
   // Binding extents must cover the operands (the HAL validation layer's job,
   // hal/command_buffer_validation.c).
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
-  const uint64_t need[3] = {(uint64_t)batch * M * K * es, (uint64_t)batch * K * N * es,
-                            (uint64_t)batch * M * N * out_es};
-  const iree_b200_buffer_ref_t refs[3] = {lhs, rhs, out};
+  uint64_t need[4] = {(uint64_t)batch * M * K * es, (uint64_t)batch * K * N * es,
+                      (uint64_t)batch * M * N * out_es, 0};
+  if (with_bias) {
+    need[3] = need[2];
+    need[2] = (uint64_t)N * 4;
+  }
   uint32_t alignment = 256;
-  for (int i = 0; i < 3; ++i) {
+  for (int i = 0; i < ref_count; ++i) {
     const uint64_t total = refs[i].buffer->byte_length;
     if (refs[i].offset > total) {
       return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "matmul binding %d offset out of range", i);
@@ -346,8 +378,15 @@ iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_c
                          "matmul binding %d holds %llu bytes but the shape needs %llu", i,
                          (unsigned long long)length, (unsigned long long)need[i]);
     }
-    alignment = std::min(alignment,
-                         pointer_alignment(refs[i].buffer->device_ptr + refs[i].offset));
+    const uint64_t address = refs[i].buffer->device_ptr + refs[i].offset;
+    if (with_bias && i == 2) {
+      // The bias is read with scalar loads: element alignment is all it needs.
+      if (address % 4) {
+        return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "matmul bias must be 4-byte aligned");
+      }
+      continue;
+    }
+    alignment = std::min(alignment, pointer_alignment(address));
   }
   iree_b200_matmul_selection_t sel;
   B200_RETURN_IF_ERROR(
@@ -355,9 +394,32 @@ iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_c
   if (sel.export_ordinal < 0) return IREE_B200_STATUS_OK;  // empty result
   B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(cb, ops->executable, sel.export_ordinal,
                                                          sel.workgroup_count, sel.constants, 5, refs,
-                                                         3, 0));
+                                                         ref_count, 0));
   ops->dispatch_count.fetch_add(1);
   return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_record_matmul(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                               int32_t element_type, int64_t batch, int64_t M,
+                                               int64_t N, int64_t K, uint32_t flags,
+                                               iree_b200_buffer_ref_t lhs,
+                                               iree_b200_buffer_ref_t rhs,
+                                               iree_b200_buffer_ref_t out) {
+  if (flags & (IREE_B200_MATMUL_FLAG_BIAS | IREE_B200_MATMUL_FLAG_RELU)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "FLAG_BIAS dispatches are recorded with iree_b200_ops_record_matmul_bias");
+  }
+  const iree_b200_buffer_ref_t refs[3] = {lhs, rhs, out};
+  return record_matmul_impl(ops, cb, element_type, batch, M, N, K, flags, refs, 3);
+}
+
+iree_b200_status_t iree_b200_ops_record_matmul_bias(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t batch,
+    int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t bias, iree_b200_buffer_ref_t out) {
+  const iree_b200_buffer_ref_t refs[4] = {lhs, rhs, bias, out};
+  return record_matmul_impl(ops, cb, element_type, batch, M, N, K,
+                            flags | IREE_B200_MATMUL_FLAG_BIAS, refs, 4);
 }
 
 namespace {
@@ -431,13 +493,19 @@ iree_b200_status_t copy_2d(const CudaSymbols* cu, bool to_device, CUdeviceptr de
 iree_b200_status_t matmul_host_serial(iree_b200_ops_t* ops, int32_t element_type, int64_t batch,
                                       int64_t M, int64_t N, int64_t K, uint32_t flags,
                                       const uint64_t bytes[3], const void* lhs, const void* rhs,
-                                      void* out, std::vector<iree_b200_command_buffer_t*>* cbs) {
+                                      void* out, std::vector<iree_b200_command_buffer_t*>* cbs,
+                                      const void* bias = nullptr) {
   iree_b200_device_t* device = ops->device;
   const uint64_t out_es = (flags & IREE_B200_MATMUL_FLAG_TRUNCATE_RESULT) ? 2 : 4;
   const uint64_t off[3] = {0, (bytes[0] + 1023) / 1024 * 1024,
                            (bytes[0] + 1023) / 1024 * 1024 + (bytes[1] + 1023) / 1024 * 1024};
-  B200_RETURN_IF_ERROR(reserve_arena(ops, off[2] + bytes[2] + 1024));
+  const uint64_t off_bias = off[2] + (bytes[2] + 1023) / 1024 * 1024;
+  const uint64_t bias_bytes = bias ? (uint64_t)N * 4 : 0;
+  B200_RETURN_IF_ERROR(reserve_arena(ops, off_bias + bias_bytes + 1024));
   iree_b200_buffer_t* arena = ops->arena;
+  if (bias_bytes) {
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, bias, arena, off_bias, bias_bytes));
+  }
   B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, lhs, arena, off[0], bytes[0]));
   B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, rhs, arena, off[1], bytes[1]));
   if (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) {
@@ -447,7 +515,15 @@ iree_b200_status_t matmul_host_serial(iree_b200_ops_t* ops, int32_t element_type
   B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
   cbs->push_back(cb);
   B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
-  if (K == 0 && !(flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) && bytes[2]) {
+  if (bias) {
+    // K == 0 included: the generic kernel then stores act((out +) bias).
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul_bias(
+        ops, cb, element_type, batch, M, N, K, flags,
+        iree_b200_buffer_ref_t{arena, off[0], bytes[0]},
+        iree_b200_buffer_ref_t{arena, off[1], bytes[1]},
+        iree_b200_buffer_ref_t{arena, off_bias, bias_bytes},
+        iree_b200_buffer_ref_t{arena, off[2], bytes[2]}));
+  } else if (K == 0 && !(flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) && bytes[2]) {
     // Empty reduction: the linalg.fill 0 that seeds the accumulator is the result.
     const uint32_t zero = 0;
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_fill_buffer(
@@ -595,10 +671,10 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
 
 }  // namespace
 
-iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t element_type,
-                                             int64_t batch, int64_t M, int64_t N, int64_t K,
-                                             uint32_t flags, const void* lhs, const void* rhs,
-                                             void* out) {
+static iree_b200_status_t matmul_host_impl(iree_b200_ops_t* ops, int32_t element_type,
+                                           int64_t batch, int64_t M, int64_t N, int64_t K,
+                                           uint32_t flags, const void* lhs, const void* rhs,
+                                           const void* bias, void* out) {
   B200_REQUIRE_ARG(ops);
   if (!matmul_type_ok(element_type) || batch < 0 || M < 0 || N < 0 || K < 0) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad matmul type or shape");
@@ -616,7 +692,7 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
   const int64_t blocks =
       batch * ceil_div(M, ops->pipeline_block_m) * ceil_div(N, ops->pipeline_block_n);
   const bool pipelined =
-      tma_ok && blocks >= 2 && bytes[0] + bytes[1] + bytes[2] >= ops->pipeline_min_bytes &&
+      !bias && tma_ok && blocks >= 2 && bytes[0] + bytes[1] + bytes[2] >= ops->pipeline_min_bytes &&
       !(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_FORCE_1CTA |
                  IREE_B200_MATMUL_FLAG_FORCE_2CTA));
   std::vector<iree_b200_command_buffer_t*> cbs;
@@ -624,7 +700,7 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
       pipelined ? matmul_host_pipelined(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs,
                                         out, &cbs)
                 : matmul_host_serial(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs, out,
-                                     &cbs);
+                                     &cbs, bias);
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
   if (status != IREE_B200_STATUS_OK) {
     // Drain everything that may still reference the staging arena or the host buffers.
@@ -636,6 +712,27 @@ iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t eleme
   for (auto* cb : cbs) iree_b200_command_buffer_release(cb);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops, int32_t element_type,
+                                             int64_t batch, int64_t M, int64_t N, int64_t K,
+                                             uint32_t flags, const void* lhs, const void* rhs,
+                                             void* out) {
+  if (flags & (IREE_B200_MATMUL_FLAG_BIAS | IREE_B200_MATMUL_FLAG_RELU)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "FLAG_BIAS calls go through iree_b200_ops_matmul_bias_host");
+  }
+  return matmul_host_impl(ops, element_type, batch, M, N, K, flags, lhs, rhs, nullptr, out);
+}
+
+iree_b200_status_t iree_b200_ops_matmul_bias_host(iree_b200_ops_t* ops, int32_t element_type,
+                                                  int64_t batch, int64_t M, int64_t N, int64_t K,
+                                                  uint32_t flags, const void* lhs, const void* rhs,
+                                                  const void* bias, void* out) {
+  B200_REQUIRE_ARG(bias || !N);
+  if (!bias) return IREE_B200_STATUS_OK;  // N == 0: empty result
+  return matmul_host_impl(ops, element_type, batch, M, N, K,
+                          flags | IREE_B200_MATMUL_FLAG_BIAS, lhs, rhs, bias, out);
 }
 
 

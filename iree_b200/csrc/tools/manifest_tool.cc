@@ -33,11 +33,19 @@ int main() {
        GemmConfig<__VA_ARGS__>::kSmemBytes, 5, "1, 1, 0");
 #include "../kernels/gemm_exports.inc"
 #undef X
+#define X(NAME, CLUSTER, ...)                                                              \
+  emit(#NAME, "gemm_bias_kernels", GemmConfig<__VA_ARGS__>::kThreads,                      \
+       GemmConfig<__VA_ARGS__>::kSmemBytes, 5, "1, 1, 1, 0");
+#include "../kernels/gemm_bias_exports.inc"
+#undef X
   emit("iree_b200_matmul_generic_bf16_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
   emit("iree_b200_matmul_generic_f16_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
   emit("iree_b200_matmul_generic_i8_i32", "generic_kernels", 256, 0, 5, "1, 1, 0");
   emit("iree_b200_matmul_generic_f8e4m3fn_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
   emit("iree_b200_matmul_generic_f8e5m2_f32", "generic_kernels", 256, 0, 5, "1, 1, 0");
+  emit("iree_b200_matmul_generic_bias_bf16_f32", "generic_kernels", 256, 0, 5, "1, 1, 1, 0");
+  emit("iree_b200_matmul_generic_bias_f16_f32", "generic_kernels", 256, 0, 5, "1, 1, 1, 0");
+  emit("iree_b200_matmul_generic_bias_i8_i32", "generic_kernels", 256, 0, 5, "1, 1, 1, 0");
 #define X(NAME, THREADS, SMEM, CONSTANTS, BINDINGS) \
   emit(#NAME, "attention_kernels", THREADS, SMEM, CONSTANTS, BINDINGS);
 #include "../kernels/attention_exports.inc"

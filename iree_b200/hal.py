@@ -25,6 +25,8 @@ ELEMENT_TYPES = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "f8e4m3fn": F8E
 MATMUL_ACCUMULATE = 1 << 0
 MATMUL_TRANSPOSE_RHS = 1 << 1
 MATMUL_TRUNCATE_RESULT = 1 << 2
+MATMUL_BIAS = 1 << 3
+MATMUL_RELU = 1 << 4
 MATMUL_FORCE_GENERIC = 1 << 8
 MATMUL_FORCE_1CTA = 1 << 9
 MATMUL_FORCE_2CTA = 1 << 10
@@ -163,6 +165,11 @@ _STATUS_FUNCS = {
                                     c_int64, c_uint32, BufferRef, BufferRef, BufferRef],
     "iree_b200_ops_matmul_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                   c_uint32, c_void_p, c_void_p, c_void_p],
+    "iree_b200_ops_record_matmul_bias": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64,
+                                         c_int64, c_uint32, BufferRef, BufferRef, BufferRef,
+                                         BufferRef],
+    "iree_b200_ops_matmul_bias_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
+                                       c_uint32, c_void_p, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_select_attention": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                        c_int64, ctypes.c_float, c_int32, c_uint32, c_uint32,
                                        POINTER(AttentionSelection)],
@@ -577,6 +584,18 @@ class Ops:
                     flags=0):
         check(lib().iree_b200_ops_matmul_host(self._h, _etype(element_type), batch, M, N, K, flags,
                                               lhs_ptr, rhs_ptr, out_ptr))
+
+    def record_matmul_bias(self, cb: CommandBuffer, element_type, batch, M, N, K, lhs: BufferRef,
+                           rhs: BufferRef, bias: BufferRef, out: BufferRef, flags=0):
+        """out = act((out +) lhs·rhs + bias[n]) in one dispatch (MATMUL_BIAS implied; MATMUL_RELU,
+        MATMUL_TRUNCATE_RESULT optional)."""
+        check(lib().iree_b200_ops_record_matmul_bias(self._h, cb._h, _etype(element_type), batch,
+                                                     M, N, K, flags, lhs, rhs, bias, out))
+
+    def matmul_bias_host(self, element_type, batch, M, N, K, lhs_ptr: int, rhs_ptr: int,
+                         bias_ptr: int, out_ptr: int, flags=0):
+        check(lib().iree_b200_ops_matmul_bias_host(self._h, _etype(element_type), batch, M, N, K,
+                                                   flags, lhs_ptr, rhs_ptr, bias_ptr, out_ptr))
 
     def select_attention(self, element_type, B, M, K1, K2, N, scale, mask_kind=0, flags=0,
                          alignment=256) -> dict:

@@ -187,6 +187,25 @@ def matmul(t, lhs: np.ndarray, rhs: np.ndarray, acc=None, transpose_rhs: bool = 
     return out
 
 
+def matmul_bias(t, lhs: np.ndarray, rhs: np.ndarray, bias: np.ndarray, acc=None,
+                transpose_rhs: bool = False, relu: bool = False, truncate: bool = False) -> np.ndarray:
+    """The fused matmul + elementwise-consumer dispatch, op by op as the unfused IR evaluates it:
+    linalg.matmul (above), then linalg.generic { arith.addf / addi  %mm, %bias[n] }
+    [ arith.maximumf / maxsi %x, 0 ] [ arith.truncf ]. Each op rounds once in f32 (i32 wraps);
+    maximumf propagates NaN and returns +0 for (-0, +0)."""
+    x = matmul(t, lhs, rhs, acc=acc, transpose_rhs=transpose_rhs)
+    bias = np.asarray(bias, dtype=x.dtype)
+    assert bias.shape == (x.shape[-1],)
+    with np.errstate(over="ignore", invalid="ignore"):
+        x = (x + bias).astype(x.dtype)
+        if relu:
+            keep = x > 0
+            if x.dtype == np.float32:
+                keep |= np.isnan(x)
+            x = np.where(keep, x, x.dtype.type(0))
+    return from_f32(t, x) if truncate else x
+
+
 def matmul_element(t, lhs: np.ndarray, rhs: np.ndarray, m: int, n: int, transpose_rhs: bool = False):
     t = type_id(t)
     M, K = lhs.shape

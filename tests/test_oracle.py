@@ -219,3 +219,28 @@ def test_float_conversions_match_reference_math_h(t):
     # NaN inputs: both must produce a NaN encoding (payloads may differ).
     assert np.isnan(oracle.to_f32(t, a[nan_in].astype(bits.dtype))).all()
     assert np.isnan(oracle.to_f32(t, b[nan_in].astype(bits.dtype))).all()
+
+
+def test_matmul_bias_restates_the_unfused_ops():
+    """oracle.matmul_bias = linalg.matmul, then addf/addi with bias[n], then maximumf/maxsi 0,
+    then truncf — one op (one rounding) at a time."""
+    for t, acc_t in (("i8", "i32"), ("bf16", "f32"), ("f16", "f32")):
+        lhs = oracle.generate_random_matrix(t, (2, 9, 13), 1)
+        rhs = oracle.generate_random_matrix(t, (2, 13, 6), 2)
+        bias = oracle.generate_random_matrix(acc_t, (6,), 4)
+        mm = oracle.matmul(t, lhs, rhs)
+        assert np.array_equal(oracle.matmul_bias(t, lhs, rhs, bias), mm + bias[None, None, :])
+        got = oracle.matmul_bias(t, lhs, rhs, bias, relu=True)
+        assert np.array_equal(got, np.maximum(mm + bias, 0)) and (got == 0).any()
+        if t != "i8":
+            assert np.array_equal(oracle.matmul_bias(t, lhs, rhs, bias, relu=True, truncate=True),
+                                  oracle.from_f32(t, got))
+    # maximumf: NaN propagates, -inf -> 0; K == 0 leaves act(bias); addi wraps.
+    l0 = np.zeros((1, 3, 0), dtype=np.uint16)
+    r0 = np.zeros((1, 0, 4), dtype=np.uint16)
+    b = np.array([1, -2, np.nan, -np.inf], dtype=np.float32)
+    got = oracle.matmul_bias("bf16", l0, r0, b, relu=True)
+    assert np.array_equal(got[0, 1], np.array([1, 0, np.nan, 0], dtype=np.float32), equal_nan=True)
+    one = np.ones((1, 1, 1), dtype=np.int8)
+    wrap = oracle.matmul_bias("i8", one, one, np.array([np.iinfo(np.int32).max], dtype=np.int32))
+    assert wrap[0, 0, 0] == np.iinfo(np.int32).min
