@@ -42,7 +42,10 @@ MATMUL_WORKLOADS = {
     "matmul_f8": ("matmul", "f8e4m3fn", 1, 8192, 8192, 8192),
     "matmul_bf16_4096": ("matmul", "bf16", 1, 4096, 4096, 4096),
     "batch_matmul": ("batch_matmul", "bf16", 64, 2048, 2048, 2048),
+    # The bf16 linear layer as one dispatch: matmul + bias[n] + relu + truncf.
+    "linear_bf16": ("matmul", "bf16", 1, 8192, 8192, 8192),
 }
+FUSED_WORKLOADS = {"linear_bf16"}
 
 
 # name -> (op, element type, batch*heads, M, K2, head dim)   [attention]
@@ -212,16 +215,27 @@ def synth_matmul_inputs(torch, et, batch, M, N, K, seed):
 class MatmulStep:
     """One recorded command buffer holding the workload's dispatch; step() replays it."""
 
-    def __init__(self, torch, hal, dev, ops, spec, seed):
+    def __init__(self, torch, hal, dev, ops, spec, seed, fused=False):
         op, et, batch, M, N, K = spec
         self.spec = spec
+        self.fused = fused
         self.tensors = synth_matmul_inputs(torch, et, batch, M, N, K, seed)
+        if fused:   # result in the operand type, plus the bias vector
+            a, b, _ = self.tensors
+            self.tensors = (a, b, torch.empty((batch, M, N), dtype=a.dtype, device="cuda"),
+                            torch.randn(N, device="cuda"))
+            self.flags = hal.MATMUL_RELU | hal.MATMUL_TRUNCATE_RESULT
         self.buffers = [dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
                         for t in self.tensors]
         before = ops.dispatch_count
         self.cb = hal.CommandBuffer(dev).begin()
-        ops.record_matmul(self.cb, et, batch, M, N, K, self.buffers[0].ref(),
-                          self.buffers[1].ref(), self.buffers[2].ref())
+        if fused:
+            ops.record_matmul_bias(self.cb, et, batch, M, N, K, self.buffers[0].ref(),
+                                   self.buffers[1].ref(), self.buffers[3].ref(),
+                                   self.buffers[2].ref(), flags=self.flags)
+        else:
+            ops.record_matmul(self.cb, et, batch, M, N, K, self.buffers[0].ref(),
+                              self.buffers[1].ref(), self.buffers[2].ref())
         self.cb.end()
         self.launches_per_step = ops.dispatch_count - before
         self.dev = dev
@@ -233,10 +247,16 @@ class MatmulStep:
         host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors]
         host[0].copy_(self.tensors[0])
         host[1].copy_(self.tensors[1])
+        if self.fused:
+            host[3].copy_(self.tensors[3])
         return host
 
     def host_call(self, ops, host):
         op, et, batch, M, N, K = self.spec
+        if self.fused:
+            ops.matmul_bias_host(et, batch, M, N, K, host[0].data_ptr(), host[1].data_ptr(),
+                                 host[3].data_ptr(), host[2].data_ptr(), flags=self.flags)
+            return
         ops.matmul_host(et, batch, M, N, K, host[0].data_ptr(), host[1].data_ptr(),
                         host[2].data_ptr())
 
@@ -244,7 +264,16 @@ class MatmulStep:
         op, et, batch, M, N, K = self.spec
         es = 2 if et in ("f16", "bf16") else 1
         flop = 2.0 * batch * M * N * K
-        nbytes = float(batch) * (M * K * es + K * N * es + M * N * 4)
+        out_es = es if self.fused else 4
+        nbytes = float(batch) * (M * K * es + K * N * es + M * N * out_es)
+        name = f"linalg.{op}" + (" + bias[n] + relu + truncf (one dispatch)" if self.fused else "")
+        if self.fused:
+            return {"flop": flop, "bytes": nbytes + N * 4, "bound": "tensor",
+                    "workload": f"{name} {et} batch={batch} M={M} N={N} K={K} per GPU",
+                    "dtype": f"{et} (f32 accumulate + f32 bias, {et} result)",
+                    "h2d": int(batch * (M * K + K * N) * es + N * 4),
+                    "d2h": int(batch * M * N * out_es),
+                    "api": "iree_b200_ops_matmul_bias_host (pinned host buffers)"}
         return {"flop": flop, "bytes": nbytes, "bound": "tensor",
                 "workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU",
                 "dtype": {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
@@ -418,7 +447,8 @@ class TpLayerStep:
 
 def make_step(torch, hal, dev, ops, workload, seed):
     if workload in MATMUL_WORKLOADS:
-        return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed)
+        return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed,
+                          fused=workload in FUSED_WORKLOADS)
     return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed)
 
 
@@ -563,6 +593,15 @@ def cpu_work(workload, rows):
         rows = min(rows, M)
         lhs = oracle.generate_random_matrix(et, (rows, K), 1)
         rhs = oracle.generate_random_matrix(et, (K, N), 2)
+        if workload in FUSED_WORKLOADS:
+            bias = oracle.generate_random_matrix("f32", (N,), 4)
+            mm = ((lambda: oracle.ref_matmul(et, lhs, rhs)) if oracle.ref_available()
+                  else (lambda: oracle.matmul(et, lhs, rhs)))
+            desc = (("reference ukernel path iree_uk_pack+mmt4d+unpack" if oracle.ref_available()
+                     else "oracle port of the reference loops")
+                    + f", then numpy bias + relu + truncf, {et} M={rows} (of {batch}x{M}) N={N} K={K}")
+            return ((lambda: oracle.from_f32(et, np.maximum(mm() + bias, np.float32(0)))),
+                    2.0 * rows * N * K, desc, "reference" if oracle.ref_available() else "port")
         if oracle.ref_available() and not et.startswith("f8"):
             # The reference's own CPU kernels (oracle/_ref, compiled from /root/reference).
             desc = (f"reference ukernel path iree_uk_pack+mmt4d+unpack (not the full llvm-cpu "
