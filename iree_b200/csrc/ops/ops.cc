@@ -1057,6 +1057,92 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
+  // Batch entries are independent, and every operand is [B, ...] dense: above the pipeline
+  // threshold the call runs in slices of B on the three streams of the matmul pipeline
+  // (slice c+1 goes up while slice c computes and slice c-1 comes down), so the call costs
+  // about the upload alone. Decode-shaped calls (M <= 16) stay whole: their kernel choice
+  // depends on B and there is nothing to overlap but a 28 us dispatch.
+  const uint64_t in_bytes = bytes[0] + bytes[1] + bytes[2] + bytes[3];
+  const uint64_t per_entry_in = in_bytes / (uint64_t)B;
+  // About half the pipeline threshold per slice (8 MiB by default: long enough for PCIe to
+  // run at its full rate).
+  const uint64_t slice_bytes = std::max<uint64_t>(1, ops->pipeline_min_bytes / 2);
+  int64_t slice =
+      (int64_t)std::max<uint64_t>(1, ceil_div(slice_bytes, std::max<uint64_t>(1, per_entry_in)));
+  slice = std::max<int64_t>(slice, ceil_div(B, 64));
+  const bool pipelined = M > 16 && B >= 2 * slice && in_bytes + bytes[5] >= ops->pipeline_min_bytes;
+  std::vector<iree_b200_command_buffer_t*> cbs;
+  if (pipelined) {
+    // Slices share one workspace (they run in order on the dispatch stream); size it for
+    // the largest request (whole slices and the remainder select differently).
+    uint64_t workspace = 0;
+    for (int64_t entries : {slice, B % slice}) {
+      if (!entries) continue;
+      iree_b200_attention_selection_t s;
+      B200_RETURN_IF_ERROR(iree_b200_ops_select_attention(ops, element_type, entries, M, K1, K2, N,
+                                                          scale, mask_kind, flags, 256, &s));
+      workspace = std::max<uint64_t>(workspace, s.workspace_bytes);
+    }
+    total += (workspace + 1023) / 1024 * 1024;  // appended after O; offsets[4] is unused here
+  }
+  auto run_pipelined = [&]() -> iree_b200_status_t {
+    const CudaSymbols* cu = device->cu;
+    B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
+    B200_RETURN_IF_ERROR(ensure_transfer_streams(ops));
+    const CUdeviceptr base = ops->arena->device_ptr;
+    const uint64_t off_workspace = offsets[5] + (bytes[5] + 1023) / 1024 * 1024;
+    const uint64_t workspace_bytes = total - off_workspace;
+    size_t next_event = 0;
+    for (int64_t b0 = 0; b0 < B; b0 += slice) {
+      const int64_t entries = std::min(slice, B - b0);
+      uint64_t at[6], len[6];
+      for (int i = 0; i < 6; ++i) {
+        const uint64_t per_entry = bytes[i] / (uint64_t)B;
+        at[i] = offsets[i] + (uint64_t)b0 * per_entry;
+        len[i] = (uint64_t)entries * per_entry;
+      }
+      for (int i = 0; i < 4; ++i) {
+        if (!len[i]) continue;
+        B200_CU(cu, cuMemcpyHtoDAsync(base + at[i],
+                                      static_cast<const uint8_t*>(host_in[i]) + (at[i] - offsets[i]),
+                                      len[i], ops->upload_stream));
+      }
+      CUevent landed = nullptr, done = nullptr;
+      B200_RETURN_IF_ERROR(event_at(ops, next_event++, &landed));
+      B200_CU(cu, cuEventRecord(landed, ops->upload_stream));
+      {
+        std::lock_guard<std::mutex> lock(device->mutex);
+        B200_CU(cu, cuStreamWaitEvent(device->dispatch_stream, landed, 0));
+      }
+      auto part = [&](int i) {
+        return len[i] ? iree_b200_buffer_ref_t{ops->arena, at[i], len[i]}
+                      : iree_b200_buffer_ref_t{nullptr, 0, 0};
+      };
+      iree_b200_command_buffer_t* cb = nullptr;
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+      cbs.push_back(cb);
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+      B200_RETURN_IF_ERROR(iree_b200_ops_record_attention(
+          ops, cb, element_type, entries, M, K1, K2, N, scale, mask_kind, flags, part(0), part(1),
+          part(2), part(3),
+          workspace_bytes ? iree_b200_buffer_ref_t{ops->arena, off_workspace, workspace_bytes}
+                          : iree_b200_buffer_ref_t{nullptr, 0, 0},
+          part(5)));
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+      B200_RETURN_IF_ERROR(
+          iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+      B200_RETURN_IF_ERROR(event_at(ops, next_event++, &done));
+      {
+        std::lock_guard<std::mutex> lock(device->mutex);
+        B200_CU(cu, cuEventRecord(done, device->dispatch_stream));
+      }
+      B200_CU(cu, cuStreamWaitEvent(ops->download_stream, done, 0));
+      B200_CU(cu, cuMemcpyDtoHAsync(static_cast<uint8_t*>(out) + (at[5] - offsets[5]), base + at[5],
+                                    len[5], ops->download_stream));
+    }
+    B200_CU(cu, cuStreamSynchronize(ops->download_stream));
+    return IREE_B200_STATUS_OK;
+  };
   iree_b200_command_buffer_t* cb = nullptr;
   auto ref = [&](int i) {
     return bytes[i] ? iree_b200_buffer_ref_t{ops->arena, offsets[i], bytes[i]}
@@ -1080,10 +1166,17 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
     B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, ops->arena, offsets[5], out, bytes[5]));
     return iree_b200_device_wait_idle(device);
   };
-  iree_b200_status_t status = run();
+  iree_b200_status_t status = pipelined ? run_pipelined() : run();
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
-  if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
+  if (status != IREE_B200_STATUS_OK) {
+    // Drain everything that may still reference the staging arena or the host buffers.
+    const CudaSymbols* cu = device->cu;
+    if (ops->upload_stream) cu->cuStreamSynchronize(ops->upload_stream);
+    iree_b200_device_wait_idle(device);
+    if (ops->download_stream) cu->cuStreamSynchronize(ops->download_stream);
+  }
   iree_b200_command_buffer_release(cb);
+  for (auto* c : cbs) iree_b200_command_buffer_release(c);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   return IREE_B200_STATUS_OK;
 }

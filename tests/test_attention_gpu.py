@@ -258,3 +258,45 @@ def test_prefill_tail_split(ops, t, shape):
     whole = _gpu_attention(ops, t, q, k, v, scale,
                            flags=H.ATTENTION_FORCE_PREFILL | H.ATTENTION_NO_TAIL_SPLIT)
     _assert_close(t, got, whole)
+
+
+@pytest.mark.parametrize("case", [
+    # type, B, M, K1, K2, N, mask
+    ("f16", 5, 130, 128, 300, 128, None),     # tcgen05 prefill kernel, one entry per slice
+    ("bf16", 3, 512, 128, 1025, 128, None),   # slices small enough for the tail split
+    ("f32", 4, 33, 24, 50, 40, "bool"),       # generic kernel, the mask is sliced too
+    ("f32", 3, 20, 16, 70, 8, "f32"),
+], ids=str)
+def test_pipelined_host_call(ops, case):
+    """iree_b200_ops_attention_host in slices of B on three streams (upload / dispatch /
+    download): same result as the whole-problem call, one selection per slice."""
+    t, B, M, K1, K2, N, mask_kind = case
+    g = np.random.Generator(np.random.PCG64(0xB200 + B + M))
+    if t == "f32":
+        q, k, v = (g.standard_normal(s).astype(np.float32) for s in ((B, M, K1), (B, K2, K1), (B, K2, N)))
+    else:
+        q, k, v = _random_qkv(t, B, M, K2, K1, seed=B * M, N=N)
+    mask = None
+    if mask_kind == "bool":
+        mask = g.random((B, M, K2)) > 0.3
+        mask[:, :, 0] = True
+    elif mask_kind == "f32":
+        mask = g.standard_normal((B, M, K2)).astype(np.float32)
+    scale = 1.0 / np.sqrt(float(K1))
+    whole = _gpu_attention(ops, t, q, k, v, scale, mask=mask)
+    before = ops.dispatch_count
+    ops.set_host_pipeline(0, 2048, 2048)    # threshold 0: one batch entry per slice
+    try:
+        sliced = _gpu_attention(ops, t, q, k, v, scale, mask=mask)
+    finally:
+        ops.set_host_pipeline(16 << 20, 2048, 2048)
+    per_slice = len(ops.select_attention(t, 1, M, K1, K2, N, scale,
+                                         mask_kind={None: 0, "bool": 1, "f32": 2}[mask_kind])["dispatches"])
+    assert ops.dispatch_count - before == B * per_slice
+    want = oracle.attention(t, q, k, v, scale, mask=mask, k2_tile=128)
+    if t == "f32":
+        np.testing.assert_allclose(sliced, want, atol=1e-4, rtol=0)
+        assert np.array_equal(sliced, whole)   # same kernel, per-entry arithmetic
+    else:
+        _assert_close(t, sliced, want)
+        _assert_close(t, sliced, whole)
