@@ -152,6 +152,122 @@ def matmul_rewriter(name: str, entry: str) -> str:
 """
 
 
+def _linear_types(et: str, truncate: bool):
+    t, a = MLIR_TYPE[et], ACC_TYPE[et]
+    return t, a, (t if truncate else a)
+
+
+def linear_entry(e: dict, key: str, et: str, relu: bool, truncate: bool, cta_group: int) -> str:
+    """Entry point of the fused dispatch out = act(A.B + bias[n]) [truncated]: bindings lhs, rhs,
+    bias, out (gemm_bias_kernels.cu); flags bit 1 = relu. %init1 (the matched linalg.fill's
+    destination) only carries the shape."""
+    name = e["name"]
+    t, a, o = _linear_types(et, truncate)
+    lt, bt, at, ot = f"tensor<?x?x{t}>", f"tensor<?x{a}>", f"tensor<?x?x{a}>", f"tensor<?x?x{o}>"
+    tile_m = 128 * cta_group
+    return f"""  func.func private @{key}_entry_point(%lhs: {lt}, %rhs: {lt}, %bias: {bt}, %init1: {at}, %out: {ot}) -> {ot} {{
+    %c0 = arith.constant 0 : index
+    %c1 = arith.constant 1 : index
+    %b = arith.constant 1 : index
+    %m = tensor.dim %lhs, %c0 : {lt}
+    %k = tensor.dim %lhs, %c1 : {lt}
+    %n = tensor.dim %rhs, %c1 : {lt}
+    // i32 push constants: M, N, K, batch, flags (bit 0: accumulate, bit 1: relu after the bias).
+    %m_i32 = arith.index_cast %m : index to i32
+    %n_i32 = arith.index_cast %n : index to i32
+    %k_i32 = arith.index_cast %k : index to i32
+    %b_i32 = arith.index_cast %b : index to i32
+    %flags = arith.constant {2 if relu else 0} : i32
+    %result = hal.dispatch.extern "{name}"[%m, %n, %b](%m_i32, %n_i32, %k_i32, %b_i32, %flags, %lhs, %rhs, %bias, %out)
+        : (i32, i32, i32, i32, i32, {lt}{{%m, %k}}, {lt}{{%k, %n}}, {bt}{{%n}}, {ot}{{%m, %n}}) -> %out{{%m, %n}}
+      count(%device: !hal.device, %wm: index, %wn: index, %wb: index) -> (index, index, index) {{
+        // Persistent grid: min(#tiles * cta_group, #SMs rounded to the cluster size).
+        %tile_m = arith.constant {tile_m} : index
+        %tile_n = arith.constant 256 : index
+        %tm = arith.ceildivui %wm, %tile_m : index
+        %tn = arith.ceildivui %wn, %tile_n : index
+        %t0 = arith.muli %tm, %tn : index
+        %t1 = arith.muli %t0, %wb : index
+        %g = arith.constant {cta_group} : index
+        %ctas = arith.muli %t1, %g : index
+        %sms = arith.constant {SM_COUNT - SM_COUNT % cta_group} : index
+        %x = arith.minui %ctas, %sms : index
+        %one = arith.constant 1 : index
+        hal.return %x, %one, %one : index, index, index
+      }}
+      layout({_layout(e)})
+      {_objects(e)}
+      {_attrs(e)}
+    return %result : {ot}
+  }}
+"""
+
+
+def linear_matcher(key: str, et: str, relu: bool, truncate: bool, big: bool) -> str:
+    """DAG matcher (transform.iree.match.cast_compatible_dag_from_root,
+    PreprocessingExtensionsOps.td:18-59; used like samples/custom_dispatch/cpu/mlp_plugin/
+    mlp_spec.mlir:51-72): linalg.fill 0 -> linalg.matmul -> one elementwise linalg.generic
+    holding add(bias broadcast along rows) [, max 0] [, truncf] - the producer-consumer group
+    dispatch creation puts behind a contraction."""
+    t, a, o = _linear_types(et, truncate)
+    is_int = a == "i32"
+    zero = "0 : i32" if is_int else "0.0 : f32"
+    add, mx = ("arith.addi", "arith.maxsi") if is_int else ("arith.addf", "arith.maximumf")
+    lt, bt, at, ot = f"tensor<?x?x{t}>", f"tensor<?x{a}>", f"tensor<?x?x{a}>", f"tensor<?x?x{o}>"
+    body = [f"            %s = {add} %x, %bv : {a}"]
+    last = "%s"
+    if relu:
+        body.append(f"            %r = {mx} %s, %zero : {a}")
+        last = "%r"
+    if truncate:
+        body.append(f"            %tr = arith.truncf {last} : {a} to {o}")
+        last = "%tr"
+    body.append(f"            linalg.yield {last} : {o}")
+    p = PITCH[et]
+    size_guard = ("transform.iree.match.dim_bounds %lhs[0], umin = 256, none : !transform.any_value"
+                  if big else
+                  "transform.iree.match.dim_bounds %lhs[0], none, umax = 255 : !transform.any_value")
+    return f"""  transform.named_sequence @match_{key}(%root: !transform.any_op {{transform.readonly}}) -> (!transform.any_value, !transform.any_value) {{
+    %ins, %outs = transform.iree.match.cast_compatible_dag_from_root %root {{
+      ^bb0(%a: {lt}, %b: {lt}, %bias: {bt}, %init1: {at}, %init2: {ot}):
+        %zero = arith.constant {zero}
+        %fill = linalg.fill ins(%zero : {a}) outs(%init1 : {at}) -> {at}
+        %mm = linalg.matmul ins(%a, %b : {lt}, {lt}) outs(%fill : {at}) -> {at}
+        %res = linalg.generic {{
+            indexing_maps = [affine_map<(d0, d1) -> (d0, d1)>, affine_map<(d0, d1) -> (d1)>,
+                             affine_map<(d0, d1) -> (d0, d1)>],
+            iterator_types = ["parallel", "parallel"]}}
+            ins(%mm, %bias : {at}, {bt}) outs(%init2 : {ot}) {{
+          ^bb1(%x: {a}, %bv: {a}, %o: {o}):
+{chr(10).join(body)}
+          }} -> {ot}
+      }} : (!transform.any_op) -> (!transform.any_value, !transform.any_value)
+    // Guards on the matmul's operands: kernel family by M, 16-byte row pitches for TMA.
+    %matmul = transform.get_producer_of_operand %root[0] : (!transform.any_op) -> !transform.any_op
+    %lhs = transform.get_operand %matmul[0] : (!transform.any_op) -> !transform.any_value
+    %rhs = transform.get_operand %matmul[1] : (!transform.any_op) -> !transform.any_value
+    {size_guard}
+    transform.iree.match.dim_is_multiple_of %lhs[1], {p} : !transform.any_value
+    transform.iree.match.dim_is_multiple_of %rhs[1], {p} : !transform.any_value
+    transform.yield %ins, %outs : !transform.any_value, !transform.any_value
+  }}
+"""
+
+
+def linear_rewriter(key: str) -> str:
+    return f"""  transform.named_sequence @rewrite_{key}(%ins: !transform.any_value {{transform.readonly}},
+                                      %out: !transform.any_value {{transform.readonly}}) {{
+    %root = transform.get_defining_op %out : (!transform.any_value) -> !transform.any_op
+    %module = transform.util.get_nearest_symbol_table %root : (!transform.any_op) -> !transform.any_op
+    %func = transform.util.import_symbol @{key}_entry_point into %module if undefined : (!transform.any_op) -> !transform.any_op
+    transform.func.cast_and_call %func(%ins) -> %out after %root {{
+        transform.type_conversion.tensor.cast_shape_dynamic_dims
+      }} : (!transform.any_op, !transform.any_value, !transform.any_value, !transform.any_op) -> !transform.any_op
+    transform.yield
+  }}
+"""
+
+
 ATTN_MAPS = """#map_query = affine_map<(b, m, n, k1, k2) -> (b, m, k1)>
 #map_key = affine_map<(b, m, n, k1, k2) -> (b, k2, k1)>
 #map_value = affine_map<(b, m, n, k1, k2) -> (b, k2, n)>
@@ -244,6 +360,21 @@ def generate(objects_dir: str) -> str:
                 rewriters.append(matmul_rewriter(
                     key, f"{kernel}_{'batch_' if batched else ''}entry_point"))
                 pairs.append(f"@match_{key} -> @rewrite_{key}")
+    # Fused consumers first: foreach_match takes the first matcher that succeeds, and the
+    # DAG roots (the elementwise generic) are visited independently of the matmul inside.
+    linear = []
+    for et in ("bf16", "f16", "i8"):
+        for truncate in ((False, True) if et != "i8" else (False,)):
+            out_t = MLIR_TYPE[et] if truncate else ACC_TYPE[et]
+            for relu in (False, True):
+                for big, suffix, g in ((True, "", 2), (False, "_1cta", 1)):
+                    kernel = f"iree_b200_matmul_bias_{et}_{out_t}{suffix}"
+                    key = f"{kernel}{'_relu' if relu else ''}"
+                    entries.append(linear_entry(man[kernel], key, et, relu, truncate, g))
+                    matchers.append(linear_matcher(key, et, relu, truncate, big))
+                    rewriters.append(linear_rewriter(key))
+                    linear.append(f"@match_{key} -> @rewrite_{key}")
+    pairs = linear + pairs
     for et in ("f16", "bf16"):
         kernel = f"iree_b200_attention_prefill_{et}"
         entries.append(attention_entry(man[kernel], et))

@@ -24,7 +24,8 @@ def test_spec_is_balanced_and_covers_every_tcgen05_family():
     with open(os.path.join(ROOT, "iree_b200", "_build", "exports.json")) as f:
         exports = {e["name"]: e for e in json.load(f)["exports"]}
     dispatched = re.findall(r'hal\.dispatch\.extern "(\w+)"', text)
-    assert len(dispatched) == len(set(dispatched)) + 10  # each matmul kernel: 2-D + batched entry
+    # each plain matmul kernel: 2-D + batched entry (10); each bias kernel: with and without relu (10)
+    assert len(dispatched) == len(set(dispatched)) + 20
     for name in set(dispatched):
         e = exports[name]
         block = text[text.index(f'hal.dispatch.extern "{name}"'):]
@@ -40,6 +41,14 @@ def test_spec_is_balanced_and_covers_every_tcgen05_family():
         assert f"iree_b200_matmul_{et}_{acc}" in dispatched
         assert f"iree_b200_matmul_{et}_{acc}_1cta" in dispatched
     assert "iree_b200_attention_prefill_f16" in dispatched
+    for name in ("iree_b200_matmul_bias_bf16_f32", "iree_b200_matmul_bias_bf16_bf16_1cta",
+                 "iree_b200_matmul_bias_i8_i32", "iree_b200_matmul_bias_f16_f16"):
+        assert name in dispatched
+    # relu travels as flags bit 1; the DAG matchers precede the plain contraction matchers
+    relu_entry = text[text.index("@iree_b200_matmul_bias_bf16_bf16_relu_entry_point"):]
+    assert "%flags = arith.constant 2 : i32" in relu_entry[:relu_entry.index("hal.dispatch.extern")]
+    main = text[text.index("@__transform_main"):]
+    assert main.index("@match_iree_b200_matmul_bias_bf16_f32 ") < main.index("@match_iree_b200_matmul_bf16_f32 ")
     # every matcher is wired to a rewriter in @__transform_main
     matchers = re.findall(r"named_sequence @(match_\w+)", text)
     for m in matchers:
