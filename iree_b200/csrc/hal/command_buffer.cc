@@ -493,6 +493,7 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
   B200_CU(cu, cuGraphCreate(&cb->graph, 0));
   std::vector<CUgraphNode> group;   // nodes recorded since the last barrier
   CUgraphNode barrier = nullptr;    // join node of the previous barrier
+  size_t node_count = 0;
   for (const Command& c : cb->commands) {
     const CUgraphNode* deps = barrier ? &barrier : nullptr;
     const size_t dep_count = barrier ? 1 : 0;
@@ -557,9 +558,14 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
                            "collectives are not supported in graph command buffers; create the "
                            "device with IREE_B200_COMMAND_BUFFER_MODE_STREAM");
     }
-    if (node) group.push_back(node);
+    if (node) {
+      group.push_back(node);
+      ++node_count;
+    }
   }
-  B200_CU(cu, cuGraphInstantiateWithFlags(&cb->graph_exec, cb->graph, 0));
+  // A command buffer that recorded nothing launchable stays without an executable graph
+  // (queue_execute then only handles its semaphores).
+  if (node_count) B200_CU(cu, cuGraphInstantiateWithFlags(&cb->graph_exec, cb->graph, 0));
   return IREE_B200_STATUS_OK;
 }
 
@@ -864,8 +870,10 @@ iree_b200_status_t iree_b200_device_queue_execute(
   iree_b200_status_t status = IREE_B200_STATUS_OK;
   if (command_buffer) {
     if (command_buffer->mode == IREE_B200_COMMAND_BUFFER_MODE_GRAPH) {
-      CUresult r = cu->cuGraphLaunch(command_buffer->graph_exec, device->dispatch_stream);
-      if (r != CUDA_SUCCESS) status = cu_status(cu, r, "cuGraphLaunch", __FILE__, __LINE__);
+      if (command_buffer->graph_exec) {
+        CUresult r = cu->cuGraphLaunch(command_buffer->graph_exec, device->dispatch_stream);
+        if (r != CUDA_SUCCESS) status = cu_status(cu, r, "cuGraphLaunch", __FILE__, __LINE__);
+      }
     } else {
       status = replay_on_stream(command_buffer);
     }
