@@ -326,6 +326,10 @@ enum {
 // → nccl_channel.c:327-588). Collectives recorded between two barriers are issued as one
 // ncclGroupStart/End batch. BFLOAT_16 maps to ncclBfloat16 (the reference maps it to
 // ncclFloat64, nccl_channel.c:291-293 — not reproduced).
+// GRAPH mode: each batch is stream-captured at end() and embedded as a child-graph node
+// ordered by the surrounding barriers (the reference returns UNIMPLEMENTED there and
+// sketches this recipe in its TODO, graph_command_buffer.c:291-327). The symmetric-region
+// kernels are a STREAM-mode path; in graphs those all-reduces go through NCCL.
 IREE_B200_API iree_b200_status_t iree_b200_command_buffer_collective(
     iree_b200_command_buffer_t* cb, iree_b200_channel_t* channel, uint32_t packed_op,
     uint32_t param, iree_b200_buffer_ref_t send_binding, iree_b200_buffer_ref_t recv_binding,

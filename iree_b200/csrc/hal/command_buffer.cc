@@ -487,6 +487,62 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
   return IREE_B200_STATUS_OK;
 }
 
+// One batch of collectives (the commands between two barriers, as in stream mode) becomes
+// one child-graph node: the NCCL calls are stream-captured on a scratch stream — the recipe
+// the reference leaves as a TODO (graph_command_buffer.c:291-327) — and the captured graph
+// is embedded with cuGraphAddChildGraphNode (which clones it).
+iree_b200_status_t capture_collectives(iree_b200_command_buffer_t* cb,
+                                       const std::vector<const Command*>& batch,
+                                       const CUgraphNode* deps, size_t dep_count,
+                                       CUgraphNode* out_node) {
+  iree_b200_device_t* device = cb->device;
+  const CudaSymbols* cu = device->cu;
+  const NcclSymbols* nccl = batch.front()->channel->nccl;
+  CUstream scratch = nullptr;
+  B200_CU(cu, cuStreamCreate(&scratch, CU_STREAM_NON_BLOCKING));
+  // RELAXED: NCCL may allocate or set up connections on a communicator's first collective.
+  CUresult r = cu->cuStreamBeginCapture(scratch, CU_STREAM_CAPTURE_MODE_RELAXED);
+  if (r != CUDA_SUCCESS) {
+    cu->cuStreamDestroy(scratch);
+    return cu_status(cu, r, "cuStreamBeginCapture", __FILE__, __LINE__);
+  }
+  iree_b200_status_t status = IREE_B200_STATUS_OK;
+  std::string message;
+  ncclResult_t group = nccl->ncclGroupStart();
+  if (group != ncclSuccess) {
+    status = nccl_status(nccl, group, "ncclGroupStart()", __FILE__, __LINE__);
+  } else {
+    for (const Command* c : batch) {
+      status = issue_collective(*c, scratch);
+      if (status != IREE_B200_STATUS_OK) break;
+    }
+    if (status != IREE_B200_STATUS_OK) message = iree_b200_status_message();
+    group = nccl->ncclGroupEnd();
+    if (status == IREE_B200_STATUS_OK && group != ncclSuccess) {
+      status = nccl_status(nccl, group, "ncclGroupEnd()", __FILE__, __LINE__);
+    }
+  }
+  if (status != IREE_B200_STATUS_OK && message.empty()) message = iree_b200_status_message();
+  CUgraph child = nullptr;
+  r = cu->cuStreamEndCapture(scratch, &child);  // always: it also ends a failed capture
+  cu->cuStreamDestroy(scratch);
+  if (status == IREE_B200_STATUS_OK && (r != CUDA_SUCCESS || !child)) {
+    status = cu_status(cu, r, "cuStreamEndCapture", __FILE__, __LINE__);
+    message = iree_b200_status_message();
+  }
+  if (status == IREE_B200_STATUS_OK) {
+    r = cu->cuGraphAddChildGraphNode(out_node, cb->graph, deps, dep_count, child);
+    if (r != CUDA_SUCCESS) {
+      status = cu_status(cu, r, "cuGraphAddChildGraphNode", __FILE__, __LINE__);
+      message = iree_b200_status_message();
+    }
+  }
+  if (child) cu->cuGraphDestroy(child);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  for (const Command* c : batch) c->channel->nccl_collectives.fetch_add(1);
+  return IREE_B200_STATUS_OK;
+}
+
 iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
   iree_b200_device_t* device = cb->device;
   const CudaSymbols* cu = device->cu;
@@ -494,7 +550,24 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
   std::vector<CUgraphNode> group;   // nodes recorded since the last barrier
   CUgraphNode barrier = nullptr;    // join node of the previous barrier
   size_t node_count = 0;
+  std::vector<const Command*> batch;  // collectives recorded since the last other command
+  auto flush_batch = [&]() -> iree_b200_status_t {
+    if (batch.empty()) return IREE_B200_STATUS_OK;
+    CUgraphNode node = nullptr;
+    iree_b200_status_t status =
+        capture_collectives(cb, batch, barrier ? &barrier : nullptr, barrier ? 1 : 0, &node);
+    batch.clear();
+    if (status != IREE_B200_STATUS_OK) return status;
+    group.push_back(node);
+    ++node_count;
+    return IREE_B200_STATUS_OK;
+  };
   for (const Command& c : cb->commands) {
+    if (c.kind == CommandKind::kCollective) {
+      batch.push_back(&c);
+      continue;
+    }
+    B200_RETURN_IF_ERROR(flush_batch());
     const CUgraphNode* deps = barrier ? &barrier : nullptr;
     const size_t dep_count = barrier ? 1 : 0;
     CUgraphNode node = nullptr;
@@ -552,17 +625,14 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
         break;
       }
       case CommandKind::kCollective:
-        // graph_command_buffer.c:291-327: collectives in graphs are unimplemented in the
-        // reference as well.
-        return make_status(IREE_B200_STATUS_UNIMPLEMENTED,
-                           "collectives are not supported in graph command buffers; create the "
-                           "device with IREE_B200_COMMAND_BUFFER_MODE_STREAM");
+        break;  // batched above
     }
     if (node) {
       group.push_back(node);
       ++node_count;
     }
   }
+  B200_RETURN_IF_ERROR(flush_batch());
   // A command buffer that recorded nothing launchable stays without an executable graph
   // (queue_execute then only handles its semaphores).
   if (node_count) B200_CU(cu, cuGraphInstantiateWithFlags(&cb->graph_exec, cb->graph, 0));

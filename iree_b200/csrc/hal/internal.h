@@ -100,6 +100,9 @@ iree_b200_status_t make_status(iree_b200_status_t code, const char* fmt, ...)
   X(cuGraphAddMemsetNode)          \
   X(cuGraphAddMemcpyNode)          \
   X(cuGraphAddEmptyNode)           \
+  X(cuGraphAddChildGraphNode)      \
+  X(cuStreamBeginCapture)          \
+  X(cuStreamEndCapture)            \
   X(cuGraphInstantiateWithFlags)   \
   X(cuGraphExecDestroy)            \
   X(cuGraphLaunch)

@@ -493,8 +493,9 @@ def test_many_small_submissions(dev, dev_ops):
 
 def test_single_rank_channel_collectives(dev):
     """iree_hal_channel_t over NCCL with count == 1 (what a 1-GPU run of a sharded module
-    sees): every collective degenerates to a copy. Graph command buffers reject collectives
-    like the reference's (graph_command_buffer.c:291-327)."""
+    sees): every collective degenerates to a copy. In graph command buffers each batch of
+    collectives is stream-captured into a child-graph node (the reference leaves this
+    UNIMPLEMENTED, graph_command_buffer.c:291-327)."""
     try:
         ch = H.Channel(dev, rank=0, count=1, id_bytes=H.Channel.create_id())
     except H.Status as e:
@@ -507,20 +508,24 @@ def test_single_rank_channel_collectives(dev):
     cb = H.CommandBuffer(dev).begin()
     op = H.collective_op(H.ALL_REDUCE, H.REDUCTION_SUM, "f32")
     cb.collective(ch, op, 0, src.ref(), dst.ref(), 1024)
-    if dev._mode_name == "graph":
-        with pytest.raises(H.Status) as e:
-            cb.end()
-        assert e.value.name == "UNIMPLEMENTED"
-        return
     cb.barrier()
     gather = _upload(dev, np.zeros(1024, dtype=np.float32))
     cb.collective(ch, H.collective_op(H.ALL_GATHER, H.REDUCTION_NONE, "f32"), 0, dst.ref(),
                   gather.ref(), 1024)
+    cb.barrier()
+    cb.fill(src.ref(), b"\x00")                     # ordered behind both collectives
     cb.end()
-    dev.execute(cb)
-    dev.wait_idle()
-    assert np.array_equal(_download(dev, gather, np.float32, 1024), np.arange(1024, dtype=np.float32))
-    assert ch.collective_counts()["nccl"] == 2
+    ramp = np.arange(1024, dtype=np.float32)
+    for _ in range(2):                               # replayable
+        dev.h2d(ramp.ctypes.data, src, 4096)
+        _run(dev, lambda c2: (c2.fill(dst.ref(), b"\x00"), c2.fill(gather.ref(), b"\x00")))
+        dev.execute(cb)
+        dev.wait_idle()
+        assert np.array_equal(_download(dev, gather, np.float32, 1024),
+                              np.arange(1024, dtype=np.float32))
+        assert (_download(dev, src, np.float32, 1024) == 0).all()
+    # Stream mode issues the batches on every submission; graph mode captured them once.
+    assert ch.collective_counts()["nccl"] == (2 if dev._mode_name == "graph" else 4)
     bad = H.CommandBuffer(dev).begin()
     with pytest.raises(H.Status) as e:   # recv binding too small for count * elements
         bad.collective(ch, op, 0, src.ref(), dst.ref(0, 512), 1024)
