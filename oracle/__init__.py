@@ -17,11 +17,11 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB_PATH = os.path.join(_HERE, "liboracle.so")
 
-I8, F16, BF16, F32, I32, F8E4M3FN, F8E5M2 = 0, 1, 2, 3, 4, 5, 6
+I8, F16, BF16, F32, I32, F8E4M3FN, F8E5M2, U8, F8E8M0FNU = 0, 1, 2, 3, 4, 5, 6, 7, 8
 _TYPE_BY_NAME = {"i8": I8, "f16": F16, "bf16": BF16, "f32": F32, "i32": I32,
-                 "f8e4m3fn": F8E4M3FN, "f8e5m2": F8E5M2}
+                 "f8e4m3fn": F8E4M3FN, "f8e5m2": F8E5M2, "u8": U8, "f8e8m0fnu": F8E8M0FNU}
 _NP_STORAGE = {I8: np.int8, F16: np.uint16, BF16: np.uint16, F32: np.float32, I32: np.int32,
-               F8E4M3FN: np.uint8, F8E5M2: np.uint8}
+               F8E4M3FN: np.uint8, F8E5M2: np.uint8, U8: np.uint8, F8E8M0FNU: np.uint8}
 
 
 def build(force: bool = False) -> str:
@@ -47,10 +47,11 @@ def lib() -> ctypes.CDLL:
         _lib.oracle_f32_to_f16.restype = ctypes.c_uint16
         _lib.oracle_f32_to_bf16.argtypes = [ctypes.c_float]
         _lib.oracle_f32_to_f16.argtypes = [ctypes.c_float]
-        for name in ("oracle_f8e4m3fn_to_f32", "oracle_f8e5m2_to_f32"):
+        for name in ("oracle_f8e4m3fn_to_f32", "oracle_f8e5m2_to_f32", "oracle_f4e2m1fn_to_f32",
+                     "oracle_f8e8m0fnu_to_f32"):
             getattr(_lib, name).restype = ctypes.c_float
             getattr(_lib, name).argtypes = [ctypes.c_uint8]
-        for name in ("oracle_f32_to_f8e4m3fn", "oracle_f32_to_f8e5m2"):
+        for name in ("oracle_f32_to_f8e4m3fn", "oracle_f32_to_f8e5m2", "oracle_f32_to_f8e8m0fnu"):
             getattr(_lib, name).restype = ctypes.c_uint8
             getattr(_lib, name).argtypes = [ctypes.c_float]
         _lib.oracle_matmul_f32acc_element.restype = ctypes.c_float
@@ -206,6 +207,40 @@ def matmul_bias(t, lhs: np.ndarray, rhs: np.ndarray, bias: np.ndarray, acc=None,
     return from_f32(t, x) if truncate else x
 
 
+MX_BLOCK = 32
+
+
+def mx_decode(bytes_: np.ndarray, scales: np.ndarray, block: int = MX_BLOCK) -> np.ndarray:
+    """arith.scaling_extf of packed f4E2M1FN rows [R, K/2] (low nibble first) by their
+    f8E8M0FNU block scales [R, K/block] -> f32 [R, K]."""
+    f4 = np.array([lib().oracle_f4e2m1fn_to_f32(i) for i in range(16)], dtype=np.float32)
+    e8 = np.array([lib().oracle_f8e8m0fnu_to_f32(i) for i in range(256)], dtype=np.float32)
+    b = np.ascontiguousarray(bytes_, dtype=np.uint8)
+    codes = np.stack([b & 0xF, b >> 4], axis=-1).reshape(b.shape[0], -1)
+    with np.errstate(invalid="ignore", over="ignore"):
+        return f4[codes] * np.repeat(e8[scales], block, axis=1)
+
+
+def matmul_mxfp4(lhs: np.ndarray, lhs_scales: np.ndarray, rhs: np.ndarray, rhs_scales: np.ndarray,
+                 acc=None, block: int = MX_BLOCK) -> np.ndarray:
+    """MXFP4 matmul as tests/e2e/matmul/generate_code_mx.py states it (see oracle.c):
+    lhs [M, K/2] / rhs [N, K/2] packed f4E2M1FN bytes, scales [M|N, K/block] f8E8M0FNU,
+    result f32 [M, N]."""
+    lhs, rhs = (np.ascontiguousarray(x, dtype=np.uint8) for x in (lhs, rhs))
+    lhs_scales, rhs_scales = (np.ascontiguousarray(x, dtype=np.uint8)
+                              for x in (lhs_scales, rhs_scales))
+    M, K = lhs.shape[0], lhs.shape[1] * 2
+    N = rhs.shape[0]
+    assert rhs.shape[1] * 2 == K and K % block == 0
+    assert lhs_scales.shape == (M, K // block) and rhs_scales.shape == (N, K // block)
+    out = np.empty((M, N), dtype=np.float32)
+    acc_c = None if acc is None else np.ascontiguousarray(acc, dtype=np.float32)
+    lib().oracle_matmul_mxfp4_f32(ctypes.c_int64(M), ctypes.c_int64(N), ctypes.c_int64(K),
+                                  ctypes.c_int64(block), _ptr(lhs), _ptr(lhs_scales), _ptr(rhs),
+                                  _ptr(rhs_scales), _ptr(acc_c), _ptr(out))
+    return out
+
+
 def matmul_element(t, lhs: np.ndarray, rhs: np.ndarray, m: int, n: int, transpose_rhs: bool = False):
     t = type_id(t)
     M, K = lhs.shape
@@ -315,7 +350,7 @@ def ref_matmul(t, lhs: np.ndarray, rhs: np.ndarray, force_generic: bool = False,
     return (out, tuple(tiles)) if return_tiles else out
 
 
-_ENCODE_KINDS = {"f8e4m3fn": 0, "f8e5m2": 1, "f16": 2, "bf16": 3}
+_ENCODE_KINDS = {"f8e4m3fn": 0, "f8e5m2": 1, "f16": 2, "bf16": 3, "f8e8m0fnu": 4}
 
 
 def encode_bulk(t: str, values: np.ndarray, reference: bool = False) -> np.ndarray:
@@ -332,5 +367,5 @@ def decode_reference(t: str, bits: np.ndarray) -> np.ndarray:
     """narrow float bits -> f32 through the reference's iree_math_*_to_f32 (oracle/_ref)."""
     fn = getattr(ref_lib(), "oracle_ref_%s_to_f32" % t)
     fn.restype = ctypes.c_float
-    fn.argtypes = [ctypes.c_uint8 if t.startswith("f8") else ctypes.c_uint16]
+    fn.argtypes = [ctypes.c_uint8 if t.startswith(("f8", "f4")) else ctypes.c_uint16]
     return np.array([fn(int(b)) for b in np.asarray(bits).reshape(-1)], dtype=np.float32)

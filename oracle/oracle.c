@@ -15,6 +15,10 @@
 //     reference artefact (iree-e2e-attention-test.cc:336-351 never compares), so the pin
 //     there is this restatement + the stated tolerance.
 //
+//   * MXFP4 matmul (f4E2M1FN x f8E8M0FNU block scales): PINNED — element and scale decodes
+//     and the scale encoder against the reference's own math.h (oracle/_ref), the matmul by
+//     exactness on the reference generator's inputs. Oracle only so far: no CUDA path yet.
+//
 // Every function cites the reference file:line (relative to /root/reference) it follows.
 // No reference source is copied; the loops are re-derived from the semantics.
 //
@@ -36,6 +40,8 @@ enum {
   ORACLE_I32 = 4,
   ORACLE_F8E4M3FN = 5,
   ORACLE_F8E5M2 = 6,
+  ORACLE_U8 = 7,         // random bytes: packed sub-byte MX operands (test_utils.c:376-382)
+  ORACLE_F8E8M0FNU = 8,  // MX block scales
 };
 
 //===----------------------------------------------------------------------===//
@@ -173,6 +179,32 @@ static uint8_t f32_to_f8(float f, int eb, int mb, int have_inf) {
 ORACLE_API uint8_t oracle_f32_to_f8e5m2(float f) { return f32_to_f8(f, 5, 2, 1); }
 ORACLE_API uint8_t oracle_f32_to_f8e4m3fn(float f) { return f32_to_f8(f, 4, 3, 0); }
 
+// OCP microscaling (MX) element and scale types.
+// f4E2M1FN (math.h:606-613: 2 exponent bits, 1 mantissa bit, bias 1, no Inf / NaN): the 16
+// codes are +-{0, 0.5, 1, 1.5, 2, 3, 4, 6}. |code| is the low nibble.
+ORACLE_API float oracle_f4e2m1fn_to_f32(uint8_t code) {
+  const uint32_t exp = (code >> 1) & 3u, man = code & 1u;
+  const float mag = exp == 0 ? 0.5f * (float)man : ldexpf(1.0f + 0.5f * (float)man, (int)exp - 1);
+  return (code & 8u) ? -mag : mag;
+}
+
+// f8E8M0FNU (math.h:615-624): a bare biased exponent, 2^(b - 127); 0xFF is NaN; there is
+// no zero and no sign.
+ORACLE_API float oracle_f8e8m0fnu_to_f32(uint8_t b) {
+  return b == 0xFF ? bits_f32(0x7fc00000u) : ldexpf(1.0f, (int)b - 127);
+}
+
+// math.h:625-643: non-finite -> 0xFF, non-positive -> 0, otherwise the nearest power of two
+// with ties (x = 1.5 * 2^e) going up; clamped to [0, 0xFF].
+ORACLE_API uint8_t oracle_f32_to_f8e8m0fnu(float v) {
+  if (!isfinite(v)) return 0xFF;
+  if (v <= 0.f) return 0;
+  int e = 0;
+  const float m = 2.0f * frexpf(v, &e);  // v = m * 2^(e - 1), m in [1, 2)
+  const int biased = (e - 1) + (m >= 1.5f ? 1 : 0) + 127;
+  return (uint8_t)(biased < 0 ? 0 : biased > 0xFF ? 0xFF : biased);
+}
+
 // Bulk encoder, same kind numbering as oracle/ref_math_glue.c (tests sweep bit patterns).
 ORACLE_API void oracle_encode(int kind, int64_t n, const float* in, uint16_t* out) {
   for (int64_t i = 0; i < n; ++i) {
@@ -180,6 +212,7 @@ ORACLE_API void oracle_encode(int kind, int64_t n, const float* in, uint16_t* ou
       case 0: out[i] = oracle_f32_to_f8e4m3fn(in[i]); break;
       case 1: out[i] = oracle_f32_to_f8e5m2(in[i]); break;
       case 2: out[i] = oracle_f32_to_f16(in[i]); break;
+      case 4: out[i] = oracle_f32_to_f8e8m0fnu(in[i]); break;
       default: out[i] = oracle_f32_to_bf16(in[i]); break;
     }
   }
@@ -262,6 +295,12 @@ static void min_max_for_type(int type, int32_t* mn, int32_t* mx) {
     case ORACLE_F16:
       *mn = -4, *mx = 4;
       break;
+    case ORACLE_U8:  // "random bytes" (test_utils.c:376-382)
+      *mn = 0, *mx = 255;
+      break;
+    case ORACLE_F8E8M0FNU:  // scales 1..8 before rounding to a power of two (:421-424)
+      *mn = 1, *mx = 8;
+      break;
     default:  // f32 / i32
       *mn = -8, *mx = 8;
       break;
@@ -282,6 +321,12 @@ ORACLE_API void oracle_generate_random_matrix(int type, int64_t count, int32_t s
         break;
       case ORACLE_I32:
         ((int32_t*)out)[i] = v;
+        break;
+      case ORACLE_U8:
+        ((uint8_t*)out)[i] = (uint8_t)v;
+        break;
+      case ORACLE_F8E8M0FNU:  // test_utils.c:345-346
+        ((uint8_t*)out)[i] = oracle_f32_to_f8e8m0fnu((float)v);
         break;
       default:
         store_elem(type, out, i, (float)v);
@@ -345,6 +390,53 @@ ORACLE_API void oracle_matmul_f32acc(int type, int64_t batch, int64_t M, int64_t
     }
     free(rhs_f32);
   }
+}
+
+// MXFP4 matmul (tests/e2e/matmul/generate_code_mx.py:153-172): operands are f4E2M1FN packed two
+// per byte (element 2i in the low nibble, 2i+1 in the high one: the sub-byte order of
+// builtins/ukernel/mmt4d_tile_generic.c:38-45), K is split in blocks of |block| (32) elements
+// with one f8E8M0FNU scale per (row, block); both operands are [rows, K] (transpose_rhs
+// form). Per element the reference program does, in (block, element) ascending order,
+//   l = arith.scaling_extf(lhs, lhs_scale)   = f32(f4) * 2^(scale - 127)
+//   r = arith.scaling_extf(rhs, rhs_scale)
+//   acc = acc + l * r          (mulf, then addf: two f32 roundings)
+// which is also what the runner's checker computes from the scaled f32 operands with the
+// f32 reference loop (generate_code_mx.py:285-330, iree-e2e-matmul-test.cc:154-160).
+ORACLE_API void oracle_matmul_mxfp4_f32(int64_t M, int64_t N, int64_t K, int64_t block,
+                                        const uint8_t* lhs, const uint8_t* lhs_scales,
+                                        const uint8_t* rhs, const uint8_t* rhs_scales,
+                                        const float* acc, float* out) {
+  const int64_t blocks = K / block;
+  // Scaled operands once, as the checker materialises them.
+  float* l32 = (float*)malloc(sizeof(float) * (size_t)(M * K + 1));
+  float* r32 = (float*)malloc(sizeof(float) * (size_t)(N * K + 1));
+  for (int pass = 0; pass < 2; ++pass) {
+    const int64_t rows = pass ? N : M;
+    const uint8_t* bytes = pass ? rhs : lhs;
+    const uint8_t* scales = pass ? rhs_scales : lhs_scales;
+    float* dst = pass ? r32 : l32;
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < rows; ++r) {
+      for (int64_t k = 0; k < K; ++k) {
+        const uint8_t byte = bytes[(r * K + k) / 2];
+        const uint8_t code = (k & 1) ? (uint8_t)(byte >> 4) : (uint8_t)(byte & 0xF);
+        dst[r * K + k] =
+            oracle_f4e2m1fn_to_f32(code) * oracle_f8e8m0fnu_to_f32(scales[r * blocks + k / block]);
+      }
+    }
+  }
+#pragma omp parallel for schedule(dynamic, 4)
+  for (int64_t m = 0; m < M; ++m) {
+    for (int64_t n = 0; n < N; ++n) {
+      float a = acc ? acc[m * N + n] : 0.0f;
+      const float* lr = l32 + m * K;
+      const float* rr = r32 + n * K;
+      for (int64_t k = 0; k < K; ++k) a += lr[k] * rr[k];
+      out[m * N + n] = a;
+    }
+  }
+  free(l32);
+  free(r32);
 }
 
 ORACLE_API void oracle_matmul_i8_i32(int64_t batch, int64_t M, int64_t N, int64_t K,

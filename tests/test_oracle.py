@@ -244,3 +244,88 @@ def test_matmul_bias_restates_the_unfused_ops():
     one = np.ones((1, 1, 1), dtype=np.int8)
     wrap = oracle.matmul_bias("i8", one, one, np.array([np.iinfo(np.int32).max], dtype=np.int32))
     assert wrap[0, 0, 0] == np.iinfo(np.int32).min
+
+
+# ---- OCP microscaling (MXFP4): the next row of SURVEY §8(f) starts with its oracle ----------
+
+@pytest.mark.skipif(not oracle.ref_available(), reason="oracle/_ref not built")
+def test_mx_element_and_scale_types_match_reference_math_h():
+    """f4E2M1FN and f8E8M0FNU (math.h:606-643): every code decodes like the reference's
+    iree_math_*_to_f32, and the scale encoder agrees on a bit-pattern sweep."""
+    f4 = np.array([oracle.lib().oracle_f4e2m1fn_to_f32(i) for i in range(16)], dtype=np.float32)
+    assert np.array_equal(f4.view(np.uint32),
+                          oracle.decode_reference("f4e2m1fn", np.arange(16)).view(np.uint32))
+    assert sorted(abs(float(x)) for x in f4[:8]) == [0, 0.5, 1, 1.5, 2, 3, 4, 6]
+    e8 = np.array([oracle.lib().oracle_f8e8m0fnu_to_f32(i) for i in range(256)], dtype=np.float32)
+    ref = oracle.decode_reference("f8e8m0fnu", np.arange(256))
+    assert np.array_equal(e8[:255].view(np.uint32), ref[:255].view(np.uint32))
+    assert np.isnan(e8[255]) and np.isnan(ref[255]) and e8[127] == 1.0 and e8[0] == 2.0 ** -127
+    # Encoder: every exponent's first / tie / last mantissa, a random sweep, the specials.
+    exps = (np.arange(256, dtype=np.uint32) << 23)[:, None]
+    mans = np.array([0, 1, 0x3FFFFF, 0x400000, 0x400001, 0x7FFFFF], dtype=np.uint32)[None, :]
+    pos = (exps | mans).reshape(-1)
+    rng = np.random.Generator(np.random.PCG64(8))
+    sweep = np.concatenate([pos, pos | 0x80000000,
+                            rng.integers(0, 1 << 32, 200000, dtype=np.uint64).astype(np.uint32)])
+    values = sweep.view(np.float32)
+    assert np.array_equal(oracle.encode_bulk("f8e8m0fnu", values),
+                          oracle.encode_bulk("f8e8m0fnu", values, reference=True))
+    for v, want in ((1.0, 127), (1.49, 127), (1.5, 128), (3.0, 129), (0.0, 0), (-4.0, 0),
+                    (np.inf, 255), (np.nan, 255), (2.0 ** -127, 0), (3.0e38, 255)):
+        assert oracle.lib().oracle_f32_to_f8e8m0fnu(v) == want, v
+
+
+def test_mx_generator_follows_the_reference_ranges():
+    """test_utils.c:376-382 (UINT_8 = random bytes 0..255) and :421-424 (scales from 1..8,
+    stored through iree_math_f32_to_f8e8m0fnu, :345-346)."""
+    raw = oracle.generate_random_matrix("u8", (64, 64), 1)
+    assert raw.dtype == np.uint8 and raw.min() == 0 and raw.max() == 255
+    state, want = 1, []
+    for _ in range(8):
+        state = (state * 48271) % (1 << 32) % 2147483647
+        want.append(state % 256)
+    assert list(raw.reshape(-1)[:8]) == want
+    scales = oracle.generate_random_matrix("f8e8m0fnu", (64, 8), 2)
+    assert set(np.unique(scales)) == {127, 128, 129, 130}    # 1, 2, 4, 8
+    state = 2
+    state = (state * 48271) % (1 << 32) % 2147483647
+    first = state % 8 + 1
+    assert scales.reshape(-1)[0] == oracle.lib().oracle_f32_to_f8e8m0fnu(float(first))
+
+
+@pytest.mark.parametrize("shape", [(1, 32, 1), (3, 64, 5), (17, 96, 9), (64, 256, 48)], ids=str)
+@pytest.mark.parametrize("accumulate", [False, True], ids=["", "acc"])
+def test_matmul_mxfp4_restates_the_scaled_generic(shape, accumulate):
+    """generate_code_mx.py:153-172: acc += scaling_extf(l, ls) * scaling_extf(r, rs) over
+    (block, element). With the generator's inputs every partial sum is exact in f32, so an
+    independent float64 evaluation of the same formula must agree bit for bit."""
+    M, K, N = shape
+    lhs = oracle.generate_random_matrix("u8", (M, K // 2), 1)
+    ls = oracle.generate_random_matrix("f8e8m0fnu", (M, K // 32), 2)
+    rhs = oracle.generate_random_matrix("u8", (N, K // 2), 3)
+    rs = oracle.generate_random_matrix("f8e8m0fnu", (N, K // 32), 4)
+    acc = oracle.generate_random_matrix("f32", (M, N), 5) if accumulate else None
+    got = oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc)
+    l64 = oracle.mx_decode(lhs, ls).astype(np.float64)
+    r64 = oracle.mx_decode(rhs, rs).astype(np.float64)
+    want = l64 @ r64.T + (acc.astype(np.float64) if accumulate else 0.0)
+    assert got.dtype == np.float32 and np.array_equal(got.astype(np.float64), want)
+
+
+def test_matmul_mxfp4_packing_and_special_scales():
+    # One row, one block: element 0 = 6.0 (low nibble of byte 0), element 1 = -0.5 (high).
+    lhs = np.zeros((1, 16), dtype=np.uint8)
+    lhs[0, 0] = 0x7 | (0x9 << 4)
+    rhs = np.zeros((2, 16), dtype=np.uint8)
+    rhs[0, 0] = 0x2            # picks element 0: 1.0
+    rhs[1, 0] = 0x2 << 4       # picks element 1: 1.0
+    one = np.full((1, 1), 127, dtype=np.uint8)
+    got = oracle.matmul_mxfp4(lhs, one, rhs, np.full((2, 1), 127, dtype=np.uint8))
+    assert got.tolist() == [[6.0, -0.5]]
+    # Scales multiply per (row, block): 2^3 on the lhs row, 2^-2 on rhs row 1.
+    got = oracle.matmul_mxfp4(lhs, np.full((1, 1), 130, dtype=np.uint8), rhs,
+                              np.array([[127], [125]], dtype=np.uint8))
+    assert got.tolist() == [[48.0, -1.0]]
+    # 0xFF is NaN and poisons the rows / columns it scales (arith.scaling_extf).
+    got = oracle.matmul_mxfp4(lhs, one, rhs, np.array([[127], [255]], dtype=np.uint8))
+    assert got[0, 0] == 6.0 and np.isnan(got[0, 1])
