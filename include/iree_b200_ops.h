@@ -147,6 +147,27 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops,
                                                            const void* rhs, void* out);
 
 //===----------------------------------------------------------------------===//
+// MXFP4 matmul — PENDING ITS FIRST GPU RUN (kernels/mx_kernels.cu)
+//===----------------------------------------------------------------------===//
+// out[M,N] f32 = (out +) sum_k f32(lhs[m,k]) * 2^(lhs_scales[m,k/32]-127)
+//                            * f32(rhs[n,k]) * 2^(rhs_scales[n,k/32]-127)
+// as tests/e2e/matmul/generate_code_mx.py:153-172 states it: lhs [M, K/2] and rhs [N, K/2]
+// are f4E2M1FN packed two per byte (low nibble first), the scales are f8E8M0FNU, one per
+// 32-element block; K must be a multiple of 32. FLAG_ACCUMULATE is the only flag. The
+// kernel lives in a second builtin executable that is loaded by the first call; today it is
+// the SIMT form only (the tcgen05 kind::mxf4 block-scaled form is next).
+#define IREE_B200_MX_BLOCK_SIZE 32
+
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
+    uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out);
+
+IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(
+    iree_b200_ops_t* ops, int64_t M, int64_t N, int64_t K, uint32_t flags, const void* lhs,
+    const void* lhs_scales, const void* rhs, const void* rhs_scales, void* out);
+
+//===----------------------------------------------------------------------===//
 // iree_linalg_ext.attention
 //===----------------------------------------------------------------------===//
 // Q [B,M,K1], K [B,K2,K1], V [B,K2,N], optional mask [B,M,K2], O [B,M,N]; all operands and

@@ -31,6 +31,9 @@ OUT = os.path.join(HERE, "_build")
 INCLUDE = os.path.join(ROOT, "include")
 
 KERNEL_UNITS = ["gemm_kernels", "gemm_bias_kernels", "generic_kernels", "attention_kernels", "collective_kernels"]
+# Kernels that have not run on a GPU yet: packed into their own executable, which the ops layer
+# loads only when one of their entry points is called (the validated paths never touch it).
+EXPERIMENTAL_UNITS = ["mx_kernels"]
 HOST_SOURCES = ["hal/device.cc", "hal/executable.cc", "hal/command_buffer.cc", "hal/channel.cc",
                 "ops/ops.cc"]
 
@@ -41,6 +44,7 @@ CXX_FLAGS = ["-O2", "-g", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall",
 
 LIB_NAME = "libiree_b200.so"
 CDA1_NAME = "iree_b200_kernels.cda1"
+EXPERIMENTAL_CDA1_NAME = "iree_b200_mx_kernels.cda1"
 
 
 def _which(*names):
@@ -146,9 +150,11 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
 
     with concurrent.futures.ThreadPoolExecutor(jobs) as pool:
         cubin_futs = [pool.submit(compile_cubin, u) for u in KERNEL_UNITS]
+        experimental_futs = [pool.submit(compile_cubin, u) for u in EXPERIMENTAL_UNITS]
         manifest_fut = pool.submit(manifest)
         host_futs = [pool.submit(compile_host, s) for s in HOST_SOURCES]
         cubins = [f.result() for f in cubin_futs]
+        experimental_cubins = [f.result() for f in experimental_futs]
         exports_json = manifest_fut.result()
         objects = [f.result() for f in host_futs]
 
@@ -157,15 +163,24 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
     for path in cubins:
         with open(path, "rb") as f:
             modules.append(f.read())
-    exports = []
+    exports, experimental_exports = [], []
     for e in exports_json["exports"]:
-        exports.append(cda1.ExportDef(
+        units, into = ((EXPERIMENTAL_UNITS, experimental_exports)
+                       if e["module"] in EXPERIMENTAL_UNITS else (KERNEL_UNITS, exports))
+        into.append(cda1.ExportDef(
             kernel_name=e["name"], block_dims=e["block_dims"],
             block_shared_memory_size=e["shared_memory"], constant_count=e["constants"],
-            binding_flags=e["binding_flags"], module_ordinal=KERNEL_UNITS.index(e["module"])))
+            binding_flags=e["binding_flags"], module_ordinal=units.index(e["module"])))
     blob = cda1.serialize(cda1.ExecutableDef(exports, modules))
     with open(cda1_path(), "wb") as f:
         f.write(blob)
+    experimental_modules = []
+    for path in experimental_cubins:
+        with open(path, "rb") as f:
+            experimental_modules.append(f.read())
+    experimental_path = os.path.join(OUT, EXPERIMENTAL_CDA1_NAME)
+    with open(experimental_path, "wb") as f:
+        f.write(cda1.serialize(cda1.ExecutableDef(experimental_exports, experimental_modules)))
 
     # Embed the blob and link.
     blob_s = os.path.join(OUT, "builtin_blob.S")
@@ -173,7 +188,10 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
         f.write('.section .rodata\n.balign 64\n.global iree_b200_builtin_cda1_start\n'
                 'iree_b200_builtin_cda1_start:\n.incbin "%s"\n'
                 '.global iree_b200_builtin_cda1_end\niree_b200_builtin_cda1_end:\n'
-                '.section .note.GNU-stack,"",@progbits\n' % cda1_path())
+                '.balign 64\n.global iree_b200_builtin_mx_cda1_start\n'
+                'iree_b200_builtin_mx_cda1_start:\n.incbin "%s"\n'
+                '.global iree_b200_builtin_mx_cda1_end\niree_b200_builtin_mx_cda1_end:\n'
+                '.section .note.GNU-stack,"",@progbits\n' % (cda1_path(), experimental_path))
     blob_o = os.path.join(OUT, "builtin_blob.o")
     _run([cxx, "-c", "-o", blob_o, blob_s])
     _run([cxx, "-shared", "-o", lib_path(), *objects, blob_o, "-ldl", "-lpthread"])

@@ -1,0 +1,124 @@
+// mx_kernels.cu — OCP microscaling (MXFP4) matmul, shape-agnostic SIMT form.
+//
+// STATUS: compiled for sm_100a, NOT YET RUN ON A GPU (written after this round's GPU budget
+// was spent). It ships in its own executable (iree_b200_mx_kernels.cda1) that the ops layer
+// loads only when an MX entry point is called, so nothing on the validated paths depends on
+// it; tests/test_zz_mxfp4_gpu.py is skipped unless IREE_B200_PENDING_VALIDATION=1.
+//
+// Semantics (tests/e2e/matmul/generate_code_mx.py:153-172; oracle.c oracle_matmul_mxfp4_f32):
+//   out[m, n] = (out[m, n] +) sum over blocks kb, elements i of
+//               (f32(lhs[m, kb, i]) * 2^(lhs_scale[m, kb] - 127)) *
+//               (f32(rhs[n, kb, i]) * 2^(rhs_scale[n, kb] - 127))
+// lhs / rhs are f4E2M1FN packed two per byte (element 2i in the low nibble,
+// mmt4d_tile_generic.c:38-45), 32 elements per block, one f8E8M0FNU scale per (row, block)
+// (0xFF = NaN); both operands are [rows, K] (the transpose_rhs form, the only one the
+// reference generates). Every scaled operand and every product is exact in f32, so the
+// result is bit-identical to the reference for any input whose partial sums are exact, and
+// within f32 summation error otherwise (same k-ascending order).
+//
+// ABI (samples/custom_dispatch/cuda/kernels/kernels.cu:7-34): bindings lhs [M, K/2] u8,
+// lhs_scales [M, K/32] u8, rhs [N, K/2] u8, rhs_scales [N, K/32] u8, out [M, N] f32;
+// constants M, N, K, batch (must be 1), flags (bit 0: accumulate into out).
+// workgroup_size = [256,1,1], workgroup count = [ceil(N/64), ceil(M/64), 1].
+
+#include <stdint.h>
+
+namespace {
+
+constexpr int kTile = 64;
+constexpr int kBlock = 32;  // MX block size = k elements per step
+
+// f4E2M1FN -> f32 (base/internal/math.h:606-613): S.EE.M, bias 1, no Inf / NaN;
+// exponent 0 is subnormal (0 or 0.5).
+__device__ __forceinline__ float f4e2m1fn_to_f32(uint32_t code) {
+  const uint32_t sign = (code & 8u) << 28;
+  const uint32_t e = (code >> 1) & 3u, m = code & 1u;
+  if (e == 0) return __uint_as_float(sign | (m ? 0x3f000000u : 0u));
+  return __uint_as_float(sign | ((e + 126u) << 23) | (m << 22));
+}
+
+// f8E8M0FNU -> f32 (math.h:615-624): 2^(b - 127); 0xFF is NaN; b == 0 is the f32
+// subnormal 2^-127.
+__device__ __forceinline__ float f8e8m0fnu_to_f32(uint32_t b) {
+  if (b == 0xFFu) return __uint_as_float(0x7fc00000u);
+  if (b == 0u) return __uint_as_float(0x00400000u);
+  return __uint_as_float(b << 23);
+}
+
+// Loads one [64 rows, 32 elements] block of a packed operand, scales it, and stores it
+// k-major into |tile|. Thread t handles row t / 4, elements (t % 4) * 8 .. + 8.
+__device__ __forceinline__ void stage_block(const uint8_t* __restrict__ bytes,
+                                            const uint8_t* __restrict__ scales, int rows, int K,
+                                            int row0, int k0, float (*tile)[kTile + 1]) {
+  const int r = threadIdx.x >> 2, part = threadIdx.x & 3;
+  const int row = row0 + r;
+  float scale = 0.f;
+  uint32_t packed = 0;
+  if (row < rows) {
+    scale = f8e8m0fnu_to_f32(scales[(size_t)row * (K / kBlock) + k0 / kBlock]);
+    const uint8_t* p = bytes + ((size_t)row * K + k0) / 2 + part * 4;
+    // Byte loads: binding pointers are only element-aligned.
+    packed = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float v = f4e2m1fn_to_f32((packed >> (4 * i)) & 0xFu);
+    // Rows past the end contribute exact zeros (scale 0), never NaN.
+    tile[part * 8 + i][r] = row < rows ? v * scale : 0.f;
+  }
+}
+
+}  // namespace
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_generic_mxfp4_f32(const uint8_t* __restrict__ lhs,
+                                       const uint8_t* __restrict__ lhs_scales,
+                                       const uint8_t* __restrict__ rhs,
+                                       const uint8_t* __restrict__ rhs_scales,
+                                       float* __restrict__ out, int M, int N, int K, int batch,
+                                       int flags) {
+  (void)batch;
+  __shared__ float a_tile[kBlock][kTile + 1];
+  __shared__ float b_tile[kBlock][kTile + 1];
+  const bool accumulate = (flags & 1) != 0;
+  const int m0 = blockIdx.y * kTile, n0 = blockIdx.x * kTile;
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gm = m0 + ty + 16 * i, gn = n0 + tx + 16 * j;
+      acc[i][j] = (accumulate && gm < M && gn < N) ? out[(size_t)gm * N + gn] : 0.f;
+    }
+  }
+  for (int k0 = 0; k0 < K; k0 += kBlock) {
+    stage_block(lhs, lhs_scales, M, K, m0, k0, a_tile);
+    stage_block(rhs, rhs_scales, N, K, n0, k0, b_tile);
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < kBlock; ++kk) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = a_tile[kk][ty + 16 * i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = b_tile[kk][tx + 16 * j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = __fadd_rn(acc[i][j], __fmul_rn(a[i], b[j]));
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + ty + 16 * i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gn = n0 + tx + 16 * j;
+      if (gn < N) out[(size_t)gm * N + gn] = acc[i][j];
+    }
+  }
+}

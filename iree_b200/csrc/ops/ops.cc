@@ -15,6 +15,9 @@ extern "C" {
 // Provided by builtin_blob.S (.incbin of the packed CDA1 executable).
 extern const uint8_t iree_b200_builtin_cda1_start[];
 extern const uint8_t iree_b200_builtin_cda1_end[];
+// The executable of kernels that have not run on a GPU yet (build.py EXPERIMENTAL_UNITS).
+extern const uint8_t iree_b200_builtin_mx_cda1_start[];
+extern const uint8_t iree_b200_builtin_mx_cda1_end[];
 }
 
 namespace {
@@ -54,6 +57,10 @@ struct iree_b200_ops_t {
   iree_b200_device_t* device = nullptr;
   iree_b200_executable_cache_t* cache = nullptr;
   iree_b200_executable_t* executable = nullptr;
+  // Loaded by the first MX call only (iree_b200_ops_matmul_mxfp4_*).
+  iree_b200_executable_t* mx_executable = nullptr;
+  int32_t mxfp4_generic_export = -1;
+  std::mutex mx_mutex;
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
@@ -200,6 +207,7 @@ void iree_b200_ops_release(iree_b200_ops_t* ops) {
   }
   iree_b200_buffer_release(ops->arena);
   iree_b200_executable_release(ops->executable);
+  iree_b200_executable_release(ops->mx_executable);
   iree_b200_executable_cache_release(ops->cache);
   iree_b200_device_release(ops->device);
   delete ops;
@@ -735,6 +743,134 @@ iree_b200_status_t iree_b200_ops_matmul_bias_host(iree_b200_ops_t* ops, int32_t 
                           flags | IREE_B200_MATMUL_FLAG_BIAS, lhs, rhs, bias, out);
 }
 
+
+//===----------------------------------------------------------------------===//
+// MXFP4 matmul (pending its first GPU run; see kernels/mx_kernels.cu)
+//===----------------------------------------------------------------------===//
+
+static iree_b200_status_t ensure_mx_executable(iree_b200_ops_t* ops) {
+  std::lock_guard<std::mutex> lock(ops->mx_mutex);  // not host_mutex: the host call holds that
+  if (ops->mx_executable) return IREE_B200_STATUS_OK;
+  B200_RETURN_IF_ERROR(iree_b200_executable_cache_prepare_executable(
+      ops->cache, "PTXE", iree_b200_builtin_mx_cda1_start,
+      (size_t)(iree_b200_builtin_mx_cda1_end - iree_b200_builtin_mx_cda1_start),
+      &ops->mx_executable));
+  ops->mxfp4_generic_export = lookup(ops->mx_executable, "iree_b200_matmul_generic_mxfp4_f32");
+  if (ops->mxfp4_generic_export < 0) {
+    return make_status(IREE_B200_STATUS_NOT_FOUND, "the MX executable has no mxfp4 export");
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
+    uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out) {
+  B200_REQUIRE_ARG(ops && cb);
+  if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "the MXFP4 matmul takes FLAG_ACCUMULATE only (operands are always [rows, K])");
+  }
+  if (M < 0 || N < 0 || K < 0 || M > INT32_MAX || N > INT32_MAX || K > INT32_MAX ||
+      K % IREE_B200_MX_BLOCK_SIZE) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "MXFP4 matmul shape %lldx%lldx%lld: K must be a multiple of the block size %d",
+                       (long long)M, (long long)N, (long long)K, IREE_B200_MX_BLOCK_SIZE);
+  }
+  if (M == 0 || N == 0) return IREE_B200_STATUS_OK;  // empty result
+  if (ceil_div(M, 64) > 65535) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "MXFP4 matmul grid out of range");
+  }
+  const iree_b200_buffer_ref_t refs[5] = {lhs, lhs_scales, rhs, rhs_scales, out};
+  const uint64_t need[5] = {(uint64_t)M * K / 2, (uint64_t)M * (K / IREE_B200_MX_BLOCK_SIZE),
+                            (uint64_t)N * K / 2, (uint64_t)N * (K / IREE_B200_MX_BLOCK_SIZE),
+                            (uint64_t)M * N * 4};
+  for (int i = 0; i < 5; ++i) {
+    // K == 0: the operand bindings are empty and may be NULL; the result is (out +) 0.
+    if (!refs[i].buffer) {
+      if (need[i]) return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 binding %d is NULL", i);
+      continue;
+    }
+    const uint64_t total = refs[i].buffer->byte_length;
+    if (refs[i].offset > total) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "MXFP4 binding %d offset out of range", i);
+    }
+    const uint64_t length = refs[i].length == UINT64_MAX ? total - refs[i].offset : refs[i].length;
+    if (length < need[i] || length > total - refs[i].offset) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                         "MXFP4 binding %d holds %llu bytes but the shape needs %llu", i,
+                         (unsigned long long)length, (unsigned long long)need[i]);
+    }
+  }
+  if ((out.buffer->device_ptr + out.offset) % 4) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 result must be 4-byte aligned");
+  }
+  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  const uint32_t grid[3] = {(uint32_t)ceil_div(N, 64), (uint32_t)ceil_div(M, 64), 1};
+  const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K, 1u,
+                                 flags & IREE_B200_MATMUL_FLAG_ACCUMULATE};
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(cb, ops->mx_executable,
+                                                         ops->mxfp4_generic_export, grid, constants,
+                                                         5, refs, 5, 0));
+  ops->dispatch_count.fetch_add(1);
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t M, int64_t N,
+                                                   int64_t K, uint32_t flags, const void* lhs,
+                                                   const void* lhs_scales, const void* rhs,
+                                                   const void* rhs_scales, void* out) {
+  B200_REQUIRE_ARG(ops);
+  if (M < 0 || N < 0 || K < 0 || K % IREE_B200_MX_BLOCK_SIZE) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad MXFP4 matmul shape");
+  }
+  const uint64_t bytes[5] = {(uint64_t)M * K / 2, (uint64_t)M * (K / IREE_B200_MX_BLOCK_SIZE),
+                             (uint64_t)N * K / 2, (uint64_t)N * (K / IREE_B200_MX_BLOCK_SIZE),
+                             (uint64_t)M * N * 4};
+  const void* host_in[4] = {lhs, lhs_scales, rhs, rhs_scales};
+  for (int i = 0; i < 4; ++i) B200_REQUIRE_ARG(host_in[i] || !bytes[i]);
+  B200_REQUIRE_ARG(out || !bytes[4]);
+  if (!bytes[4]) return IREE_B200_STATUS_OK;
+  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  iree_b200_device_t* device = ops->device;
+  std::lock_guard<std::mutex> host_lock(ops->host_mutex);
+  uint64_t offsets[5], total = 0;
+  for (int i = 0; i < 5; ++i) {
+    offsets[i] = total;
+    total += (bytes[i] + 1023) / 1024 * 1024;
+  }
+  iree_b200_command_buffer_t* cb = nullptr;
+  auto run = [&]() -> iree_b200_status_t {
+    B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
+    auto ref = [&](int i) {
+      return bytes[i] ? iree_b200_buffer_ref_t{ops->arena, offsets[i], bytes[i]}
+                      : iree_b200_buffer_ref_t{nullptr, 0, 0};
+    };
+    for (int i = 0; i < 4; ++i) {
+      if (!bytes[i]) continue;
+      B200_RETURN_IF_ERROR(
+          iree_b200_device_transfer_h2d(device, host_in[i], ops->arena, offsets[i], bytes[i]));
+    }
+    if (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) {
+      B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, out, ops->arena, offsets[4], bytes[4]));
+    }
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul_mxfp4(ops, cb, M, N, K, flags, ref(0), ref(1),
+                                                           ref(2), ref(3), ref(4)));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+    B200_RETURN_IF_ERROR(
+        iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, ops->arena, offsets[4], out, bytes[4]));
+    return iree_b200_device_wait_idle(device);
+  };
+  iree_b200_status_t status = run();
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
+  iree_b200_command_buffer_release(cb);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
 
 //===----------------------------------------------------------------------===//
 // iree_linalg_ext.attention

@@ -50,6 +50,9 @@ int main() {
   emit(#NAME, "attention_kernels", THREADS, SMEM, CONSTANTS, BINDINGS);
 #include "../kernels/attention_exports.inc"
 #undef X
+  // Kernels awaiting their first GPU run ship in a second executable that is loaded on demand
+  // (build.py EXPERIMENTAL_UNITS; mx_kernels.cu): lhs, lhs_scales, rhs, rhs_scales, out.
+  emit("iree_b200_matmul_generic_mxfp4_f32", "mx_kernels", 256, 0, 5, "1, 1, 1, 1, 0");
   // Channel-launched kernels (not dispatch-ABI exports; see collective_kernels.cu).
   for (const char* type : {"f16", "bf16", "f32"}) {
     for (const char* path : {"nvls", "p2p"}) {

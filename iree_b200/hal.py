@@ -170,6 +170,10 @@ _STATUS_FUNCS = {
                                          BufferRef],
     "iree_b200_ops_matmul_bias_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                        c_uint32, c_void_p, c_void_p, c_void_p, c_void_p],
+    "iree_b200_ops_record_matmul_mxfp4": [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_uint32,
+                                          BufferRef, BufferRef, BufferRef, BufferRef, BufferRef],
+    "iree_b200_ops_matmul_mxfp4_host": [c_void_p, c_int64, c_int64, c_int64, c_uint32, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_select_attention": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                        c_int64, ctypes.c_float, c_int32, c_uint32, c_uint32,
                                        POINTER(AttentionSelection)],
@@ -596,6 +600,18 @@ class Ops:
                          bias_ptr: int, out_ptr: int, flags=0):
         check(lib().iree_b200_ops_matmul_bias_host(self._h, _etype(element_type), batch, M, N, K,
                                                    flags, lhs_ptr, rhs_ptr, bias_ptr, out_ptr))
+
+    def record_matmul_mxfp4(self, cb: CommandBuffer, M, N, K, lhs: BufferRef, lhs_scales: BufferRef,
+                            rhs: BufferRef, rhs_scales: BufferRef, out: BufferRef, flags=0):
+        """MXFP4 matmul (pending its first GPU run; include/iree_b200_ops.h)."""
+        check(lib().iree_b200_ops_record_matmul_mxfp4(self._h, cb._h, M, N, K, flags, lhs,
+                                                      lhs_scales, rhs, rhs_scales, out))
+
+    def matmul_mxfp4_host(self, M, N, K, lhs_ptr: int, lhs_scales_ptr: int, rhs_ptr: int,
+                          rhs_scales_ptr: int, out_ptr: int, flags=0):
+        check(lib().iree_b200_ops_matmul_mxfp4_host(self._h, M, N, K, flags, lhs_ptr,
+                                                    lhs_scales_ptr, rhs_ptr, rhs_scales_ptr,
+                                                    out_ptr))
 
     def select_attention(self, element_type, B, M, K1, K2, N, scale, mask_kind=0, flags=0,
                          alignment=256) -> dict:
