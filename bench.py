@@ -574,7 +574,7 @@ def run_ours(args):
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
     if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(args.workload, threads=os.cpu_count() or 1)
+        line["cpu_baseline"] = cpu_baseline(args.workload, threads=use_all_host_threads())
     print(json.dumps(line), flush=True)
 
 
@@ -629,6 +629,25 @@ def oracle_ref() -> bool:
     return oracle.ref_available()
 
 
+def use_all_host_threads() -> int:
+    """Makes the OpenMP runtime behind the CPU arms (oracle/liboracle.so, oracle/_ref) use every
+    core this process may run on, and returns that count. torchrun exports OMP_NUM_THREADS=1
+    to its workers, which would otherwise turn the N>1 reference arm into a 1-thread run."""
+    import ctypes
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    try:
+        gomp = ctypes.CDLL("libgomp.so.1")
+        gomp.omp_set_num_threads(ctypes.c_int(n))
+        n = int(gomp.omp_get_max_threads())
+    except OSError:
+        pass
+    return n
+
+
 def cpu_baseline(workload, threads):
     """The oracle port (oracle/oracle.c, OpenMP) timed on this box's host cores."""
     fn, flop, desc, kind = cpu_work(workload, rows=2048 if workload in MATMUL_WORKLOADS else 1024)
@@ -647,7 +666,7 @@ def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
-    threads = os.cpu_count() or 1
+    threads = use_all_host_threads()
     fn, flop, desc, kind = cpu_work(args.workload, rows=1024 if oracle_ref() else 256)
     for _ in range(max(1, min(args.warmup, 2))):
         fn()
