@@ -75,6 +75,14 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_create(iree_b200_device_t* device
 IREE_B200_API iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device,
                                                                 const void* data, size_t size,
                                                                 iree_b200_ops_t** out_ops);
+// Selection without a GPU: parses |data| (NULL = the builtin executable) for export names and
+// layouts and answers iree_b200_ops_select_* / iree_b200_ops_executable() lookups as a device
+// with |sm_count| SMs would. What a compiler-side tool evaluating the match-and-replace
+// spec's `count` regions needs, and what the CPU test suite uses. Every entry point that would
+// record or run a kernel returns FAILED_PRECONDITION for such an object: there is no CPU path.
+IREE_B200_API iree_b200_status_t iree_b200_ops_create_offline(const void* data, size_t size,
+                                                              int32_t sm_count,
+                                                              iree_b200_ops_t** out_ops);
 IREE_B200_API void iree_b200_ops_release(iree_b200_ops_t* ops);
 IREE_B200_API iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* ops);
 

@@ -503,8 +503,10 @@ void iree_b200_executable_retain(iree_b200_executable_t* executable) {
 void iree_b200_executable_release(iree_b200_executable_t* executable) {
   if (!executable || executable->ref_count.fetch_sub(1) != 1) return;
   iree_b200_device_t* device = executable->device;
-  device->cu->cuCtxSetCurrent(device->cu_context);
-  for (CUmodule module : executable->modules) device->cu->cuModuleUnload(module);
+  if (device) {  // NULL for the module-less executable of an offline ops object
+    device->cu->cuCtxSetCurrent(device->cu_context);
+    for (CUmodule module : executable->modules) device->cu->cuModuleUnload(module);
+  }
   delete executable;
   iree_b200_device_release(device);
 }

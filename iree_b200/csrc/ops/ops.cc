@@ -63,6 +63,7 @@ struct iree_b200_ops_t {
   std::mutex mx_mutex;
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
+  int32_t sm_count = 0;  // device->sm_count, or the caller's for an offline (selection-only) object
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[6][2][kFamilyCount];
   int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
@@ -100,28 +101,8 @@ const void* iree_b200_ops_builtin_executable_data(size_t* out_size) {
   return iree_b200_builtin_cda1_start;
 }
 
-iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, const void* data,
-                                                  size_t size, iree_b200_ops_t** out_ops) {
-  B200_REQUIRE_ARG(device && data && out_ops);
-  *out_ops = nullptr;
-  if (device->cc_major != 10) {
-    return make_status(IREE_B200_STATUS_INCOMPATIBLE,
-                       "the builtin kernels are sm_100a only; device %d is sm_%d%d", device->ordinal,
-                       device->cc_major, device->cc_minor);
-  }
-  auto* ops = new iree_b200_ops_t();
-  ops->device = device;
-  iree_b200_device_retain(device);
-  iree_b200_status_t status = iree_b200_executable_cache_create(device, "iree_b200_ops", &ops->cache);
-  if (status == IREE_B200_STATUS_OK) {
-    status = iree_b200_executable_cache_prepare_executable(ops->cache, "PTXE", data, size,
-                                                           &ops->executable);
-  }
-  if (status != IREE_B200_STATUS_OK) {
-    std::string message = iree_b200_status_message();
-    iree_b200_ops_release(ops);
-    return make_status(status, "%s", message.c_str());
-  }
+// Export ordinals of every kernel family, looked up by name in ops->executable.
+static void populate_export_tables(iree_b200_ops_t* ops) {
   for (int t = 0; t < kTypeCount; ++t) {
     for (int nt = 0; nt < 2; ++nt) {
       for (int f = 0; f < kFamilyCount; ++f) {
@@ -183,7 +164,80 @@ iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, co
     ops->attention_exports[t][kAttnGeneric] =
         lookup(ops->executable, "iree_b200_attention_generic_" + suffix);
   }
+}
+
+iree_b200_status_t iree_b200_ops_create_from_data(iree_b200_device_t* device, const void* data,
+                                                  size_t size, iree_b200_ops_t** out_ops) {
+  B200_REQUIRE_ARG(device && data && out_ops);
+  *out_ops = nullptr;
+  if (device->cc_major != 10) {
+    return make_status(IREE_B200_STATUS_INCOMPATIBLE,
+                       "the builtin kernels are sm_100a only; device %d is sm_%d%d", device->ordinal,
+                       device->cc_major, device->cc_minor);
+  }
+  auto* ops = new iree_b200_ops_t();
+  ops->device = device;
+  iree_b200_device_retain(device);
+  iree_b200_status_t status = iree_b200_executable_cache_create(device, "iree_b200_ops", &ops->cache);
+  if (status == IREE_B200_STATUS_OK) {
+    status = iree_b200_executable_cache_prepare_executable(ops->cache, "PTXE", data, size,
+                                                           &ops->executable);
+  }
+  if (status != IREE_B200_STATUS_OK) {
+    std::string message = iree_b200_status_message();
+    iree_b200_ops_release(ops);
+    return make_status(status, "%s", message.c_str());
+  }
+  ops->sm_count = device->sm_count;
+  populate_export_tables(ops);
   *out_ops = ops;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_create_offline(const void* data, size_t size, int32_t sm_count,
+                                                iree_b200_ops_t** out_ops) {
+  B200_REQUIRE_ARG(out_ops);
+  *out_ops = nullptr;
+  if (sm_count < 2) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "sm_count %d is not a device", sm_count);
+  }
+  if (!data) data = iree_b200_ops_builtin_executable_data(&size);
+  const uint8_t* fb = nullptr;
+  size_t fb_length = 0;
+  B200_RETURN_IF_ERROR(read_executable_header(data, size, /*unsafe_infer_size=*/false, &fb,
+                                              &fb_length));
+  ExecutableDefView view;
+  B200_RETURN_IF_ERROR(parse_executable_def(fb, fb_length, &view));
+  auto* ops = new iree_b200_ops_t();
+  ops->sm_count = sm_count;
+  // An executable with names and layouts but no device, no modules and no functions: good
+  // for lookups and export_info, never dispatchable (there is no command buffer without a
+  // device, and the record / host entry points refuse an offline object).
+  ops->executable = new iree_b200_executable_t();
+  ops->executable->exports.resize(view.exports.size());
+  for (size_t i = 0; i < view.exports.size(); ++i) {
+    const ExportDefView& e = view.exports[i];
+    KernelParams& k = ops->executable->exports[i];
+    k.name = e.kernel_name;
+    for (int d = 0; d < 3; ++d) k.block_dims[d] = e.block_dims[d];
+    k.block_shared_memory_size = e.block_shared_memory_size;
+    k.constant_count = e.constant_count;
+    k.binding_count = (uint32_t)e.binding_flags.size();
+    for (size_t j = 0; j < e.binding_flags.size(); ++j) k.binding_flags[j] = e.binding_flags[j];
+  }
+  populate_export_tables(ops);
+  *out_ops = ops;
+  return IREE_B200_STATUS_OK;
+}
+
+// Every entry point that touches the GPU starts with this.
+static iree_b200_status_t require_device(const iree_b200_ops_t* ops) {
+  if (!ops) return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "ops is NULL");
+  if (!ops->device) {
+    return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
+                       "this ops object was created offline: it selects kernels but cannot "
+                       "record or run them (there is no CPU path)");
+  }
   return IREE_B200_STATUS_OK;
 }
 
@@ -219,9 +273,9 @@ iree_b200_executable_t* iree_b200_ops_executable(iree_b200_ops_t* ops) {
 
 iree_b200_status_t iree_b200_ops_set_reserved_sms(iree_b200_ops_t* ops, int32_t reserved_sms) {
   B200_REQUIRE_ARG(ops);
-  if (reserved_sms < 0 || reserved_sms >= ops->device->sm_count) {
+  if (reserved_sms < 0 || reserved_sms >= ops->sm_count) {
     return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "reserved_sms %d out of range [0, %d)",
-                       reserved_sms, ops->device->sm_count);
+                       reserved_sms, ops->sm_count);
   }
   ops->reserved_sms = reserved_sms;
   return IREE_B200_STATUS_OK;
@@ -290,7 +344,7 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
   // Matcher guards of the TMA-fed kernels: 16-byte aligned bases and row pitches.
   const bool tma_ok = alignment >= 16 && K > 0 && (K * es) % 16 == 0 && (N * out_es) % 16 == 0 &&
                       (transpose_rhs || (N * es) % 16 == 0);
-  const int sm_count = std::max(2, ops->device->sm_count - ops->reserved_sms);
+  const int sm_count = std::max(2, ops->sm_count - ops->reserved_sms);
   const int64_t tiles_2cta = ceil_div(M, 256) * ceil_div(N, 256) * batch;
   const int64_t tiles_1cta = ceil_div(M, 128) * ceil_div(N, 256) * batch;
 
@@ -361,6 +415,7 @@ static iree_b200_status_t record_matmul_impl(iree_b200_ops_t* ops, iree_b200_com
                                              int64_t N, int64_t K, uint32_t flags,
                                              const iree_b200_buffer_ref_t* refs, int ref_count) {
   B200_REQUIRE_ARG(ops && cb);
+  B200_RETURN_IF_ERROR(require_device(ops));
   for (int i = 0; i < ref_count; ++i) B200_REQUIRE_ARG(refs[i].buffer);
   const bool with_bias = ref_count == 4;  // lhs, rhs, bias, out
   const uint64_t es = matmul_elem_size(element_type);
@@ -684,6 +739,7 @@ static iree_b200_status_t matmul_host_impl(iree_b200_ops_t* ops, int32_t element
                                            uint32_t flags, const void* lhs, const void* rhs,
                                            const void* bias, void* out) {
   B200_REQUIRE_ARG(ops);
+  B200_RETURN_IF_ERROR(require_device(ops));
   if (!matmul_type_ok(element_type) || batch < 0 || M < 0 || N < 0 || K < 0) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad matmul type or shape");
   }
@@ -767,6 +823,7 @@ iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
     uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out) {
   B200_REQUIRE_ARG(ops && cb);
+  B200_RETURN_IF_ERROR(require_device(ops));
   if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "the MXFP4 matmul takes FLAG_ACCUMULATE only (operands are always [rows, K])");
@@ -821,6 +878,7 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
                                                    const void* lhs_scales, const void* rhs,
                                                    const void* rhs_scales, void* out) {
   B200_REQUIRE_ARG(ops);
+  B200_RETURN_IF_ERROR(require_device(ops));
   if (M < 0 || N < 0 || K < 0 || K % IREE_B200_MX_BLOCK_SIZE) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad MXFP4 matmul shape");
   }
@@ -944,7 +1002,7 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       // when that makes the last wave at most half as long.
       const int64_t tiles_m = ceil_div(M, 256);
       const int64_t units = tiles_m * B;
-      const int64_t sms = ops->device->sm_count;
+      const int64_t sms = ops->sm_count;
       const int64_t kv_blocks = ceil_div(K2, 128);
       const int64_t full_units = units / sms * sms;
       const int64_t tail_units = units - full_units;
@@ -998,7 +1056,7 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       using Cluster = b200::AttnDecodeClusterConfig;
       // Single dispatch when 8 CTAs per (batch, m) row already fill the SMs and every CTA
       // gets a few ring stages of rows; otherwise split-KV sized to the SM count + merge.
-      bool cluster = B * M * Cluster::kSplits >= ops->device->sm_count &&
+      bool cluster = B * M * Cluster::kSplits >= ops->sm_count &&
                      K2 >= (int64_t)Cluster::kSplits * Cluster::kMinRowsPerSplit;
       if (flags & IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT) cluster = false;
       if (flags & IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER) cluster = true;
@@ -1017,7 +1075,7 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
         break;
       }
       const int64_t chunk = b200::AttnDecodeConfig::kChunkRows;
-      const int64_t want = std::max<int64_t>(1, (int64_t)ops->device->sm_count * 8 / (B * M));
+      const int64_t want = std::max<int64_t>(1, (int64_t)ops->sm_count * 8 / (B * M));
       const int64_t splits = std::max<int64_t>(1, std::min(ceil_div(K2, chunk), want));
       d0->export_ordinal = ops->attention_exports[element_type][kAttnDecodeSplit];
       d0->workgroup_count[0] = (uint32_t)splits;
@@ -1102,6 +1160,7 @@ iree_b200_status_t iree_b200_ops_record_attention(
     iree_b200_buffer_ref_t q, iree_b200_buffer_ref_t k, iree_b200_buffer_ref_t v,
     iree_b200_buffer_ref_t mask, iree_b200_buffer_ref_t workspace, iree_b200_buffer_ref_t out) {
   B200_REQUIRE_ARG(ops && cb);
+  B200_RETURN_IF_ERROR(require_device(ops));
   if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "negative attention dimension");
   }
@@ -1167,6 +1226,7 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
                                                 uint32_t flags, const void* q, const void* k,
                                                 const void* v, const void* mask, void* out) {
   B200_REQUIRE_ARG(ops);
+  B200_RETURN_IF_ERROR(require_device(ops));
   if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0 || mask_kind < 0 || mask_kind > 2) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad attention shape or mask kind");
   }

@@ -157,6 +157,7 @@ _STATUS_FUNCS = {
                                                   POINTER(SymmetricRegionParams)],
     "iree_b200_ops_create": [c_void_p, POINTER(c_void_p)],
     "iree_b200_ops_create_from_data": [c_void_p, c_void_p, c_size_t, POINTER(c_void_p)],
+    "iree_b200_ops_create_offline": [c_void_p, c_size_t, c_int32, POINTER(c_void_p)],
     "iree_b200_ops_set_reserved_sms": [c_void_p, c_int32],
     "iree_b200_ops_set_host_pipeline": [c_void_p, c_uint64, c_int32, c_int32],
     "iree_b200_ops_select_matmul": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
@@ -557,6 +558,21 @@ class Ops:
             check(lib().iree_b200_ops_create_from_data(device._h, buf, len(cda1), byref(h)))
         self._h = h
         self.device = device
+
+    @classmethod
+    def offline(cls, sm_count: int = 148, cda1: bytes = None) -> "Ops":
+        """A selection-only object (no GPU): select_* and executable lookups work, anything
+        that would record or run a kernel raises FAILED_PRECONDITION."""
+        self = cls.__new__(cls)
+        h = c_void_p()
+        if cda1 is None:
+            check(lib().iree_b200_ops_create_offline(None, 0, sm_count, byref(h)))
+        else:
+            buf = ctypes.create_string_buffer(cda1, len(cda1))
+            check(lib().iree_b200_ops_create_offline(buf, len(cda1), sm_count, byref(h)))
+        self._h = h
+        self.device = None
+        return self
 
     @property
     def executable(self) -> Executable:
