@@ -1,0 +1,244 @@
+"""Launch-layer checks that only make sense under the mock driver (tests/mock_cuda/mock_cuda.cc):
+what reaches cuLaunchKernel / cuTensorMapEncodeTiled / the graph API for the ops layer's
+dispatches. Run by tests/test_hal_mock_cpu.py in a subprocess whose libcuda.so.1 is the mock;
+not collected by the normal test run (the file name does not match test_*.py)."""
+
+import ctypes
+
+import numpy as np
+import pytest
+
+from iree_b200 import hal as H
+
+pytestmark = pytest.mark.gpu   # "needs a device": here the device is the mock
+
+MODES = {"stream": H.MODE_STREAM, "graph": H.MODE_GRAPH}
+
+
+def _mock():
+    lib = ctypes.CDLL("libcuda.so.1")
+    assert hasattr(lib, "mock_cuda_take_launches"), "the real driver is loaded, not the mock"
+    for fn in (lib.mock_cuda_take_launches, lib.mock_cuda_take_tensor_maps):
+        fn.restype = ctypes.c_size_t
+        fn.argtypes = [ctypes.c_char_p, ctypes.c_size_t]
+    return lib
+
+
+def _take(fn):
+    buf = ctypes.create_string_buffer(1 << 20)
+    n = fn(buf, len(buf))
+    return [line.split() for line in buf.raw[:n].decode().splitlines()]
+
+
+def launches():
+    return [(l[0], [int(x) for x in l[1:4]], [int(x) for x in l[4:7]], int(l[7]))
+            for l in _take(_mock().mock_cuda_take_launches)]
+
+
+def tensor_maps():
+    out = []
+    for l in _take(_mock().mock_cuda_take_tensor_maps):
+        v = [int(x) for x in l]
+        out.append({"type": v[0], "rank": v[1], "swizzle": v[2], "base": v[3],
+                    "dims": v[4:9], "strides": v[9:14], "box": v[14:19]})
+    return out
+
+
+@pytest.fixture(scope="module", params=list(MODES), ids=list(MODES))
+def dev(request):
+    return H.Device(0, mode=MODES[request.param])
+
+
+@pytest.fixture(scope="module")
+def dev_ops(dev):
+    return H.Ops(dev)
+
+
+def test_mock_device_is_a_b200(dev):
+    assert dev.query_i64("cuda.device", "compute_capability_major") == 10
+    assert dev.query_i64("b200.device", "multiprocessor_count") == 148
+
+
+def test_matmul_dispatch_reaches_the_driver_as_recorded(dev, dev_ops):
+    """One 2-CTA bf16 dispatch: persistent grid, block, opt-in shared memory, and the three
+    tensor maps the `__tma` recipe describes (read from the cubin's ELF symbol table),
+    evaluated from (binding pointers, constants)."""
+    M, N, K = 8192, 4096, 2048
+    a, b, c = dev.allocate(M * K * 2), dev.allocate(K * N * 2), dev.allocate(M * N * 4)
+    launches(), tensor_maps()   # drain
+    cb = H.CommandBuffer(dev).begin()
+    dev_ops.record_matmul(cb, "bf16", 1, M, N, K, a.ref(), b.ref(), c.ref())
+    cb.end()
+    maps = tensor_maps()        # encoded at record time
+    assert launches() == []     # nothing launches before queue_execute
+    for _ in range(2):
+        dev.execute(cb)
+    dev.wait_idle()
+    info = dev_ops.executable.export_info(dev_ops.executable.lookup("iree_b200_matmul_bf16_f32"))
+    want = ("iree_b200_matmul_bf16_f32", [148, 1, 1], [256, 1, 1], info["block_shared_memory_size"])
+    assert launches() == [want, want]
+    assert info["block_shared_memory_size"] > 48 * 1024 and info["tma_map_count"] == 3
+    ta, tb, tc = maps
+    assert ta["base"] == a.device_pointer and tb["base"] == b.device_pointer and tc["base"] == c.device_pointer
+    # A [batch, M, K] bf16: innermost K, 128-byte (64-element) x 128-row boxes, 128B swizzle.
+    assert (ta["type"], ta["rank"], ta["swizzle"]) == (9, 3, 3)
+    assert ta["dims"][:3] == [K, M, 1] and ta["strides"][:2] == [K * 2, M * K * 2]
+    assert ta["box"][:3] == [64, 128, 1]
+    # B [batch, K, N] (MN-major operand): innermost N in 64-element boxes of 64 k rows.
+    assert tb["dims"][:3] == [N, K, 1] and tb["strides"][:2] == [N * 2, K * N * 2]
+    assert tb["box"][:3] == [64, 64, 1]
+    # C [batch, M, N] f32: 32 columns (128 bytes) x 128 rows per store.
+    assert (tc["type"], tc["dims"][:3], tc["box"][:3]) == (7, [N, M, 1], [32, 128, 1])
+    assert tc["strides"][:2] == [N * 4, M * N * 4]
+
+
+def test_sub_range_bindings_move_the_tensor_map_base(dev, dev_ops):
+    M = N = K = 512
+    big = dev.allocate(4 << 20)
+    cb = H.CommandBuffer(dev).begin()
+    tensor_maps()
+    dev_ops.record_matmul(cb, "i8", 1, M, N, K, big.ref(1024, M * K), big.ref(1 << 20, K * N),
+                          big.ref(2 << 20, M * N * 4), flags=H.MATMUL_TRANSPOSE_RHS)
+    ta, tb, tc = tensor_maps()
+    assert [t["base"] - big.device_pointer for t in (ta, tb, tc)] == [1024, 1 << 20, 2 << 20]
+    assert ta["type"] == 0 and ta["box"][:2] == [128, 128]      # bytes: 128 per row
+    assert tb["dims"][:2] == [K, N]                             # [N, K]: K-major rhs
+    assert tc["type"] == 3                                      # i32 result
+
+
+def test_fused_bias_dispatch_binds_the_result_fourth(dev, dev_ops):
+    M, N, K = 1024, 1024, 256
+    a, b, c = dev.allocate(M * K * 2), dev.allocate(K * N * 2), dev.allocate(M * N * 2)
+    bias = dev.allocate(N * 4 + 4)
+    cb = H.CommandBuffer(dev).begin()
+    tensor_maps(), launches()
+    dev_ops.record_matmul_bias(cb, "bf16", 1, M, N, K, a.ref(), b.ref(), bias.ref(4, N * 4), c.ref(),
+                               flags=H.MATMUL_RELU | H.MATMUL_TRUNCATE_RESULT)
+    cb.end()
+    maps = tensor_maps()
+    assert len(maps) == 3 and maps[2]["base"] == c.device_pointer
+    assert maps[2]["type"] == 9 and maps[2]["box"][:2] == [64, 128]   # bf16 result, 64 columns
+    dev.execute(cb)
+    # 16 tiles of 256x256 would leave most SM pairs idle: the 1-CTA family takes it.
+    assert [l[0] for l in launches()] == ["iree_b200_matmul_bias_bf16_bf16_1cta"]
+
+
+def test_attention_chains_keep_their_order(dev, dev_ops):
+    """Prefill with a tail split = split kernel, barrier, merge kernel; decode with few rows =
+    split + merge; decode with many rows = one cluster launch of 8 CTAs per row."""
+    def run(B, M, K2):
+        es = 2
+        q, o = dev.allocate(B * M * 128 * es), dev.allocate(B * M * 128 * es)
+        k, v = dev.allocate(B * K2 * 128 * es), dev.allocate(B * K2 * 128 * es)
+        sel = dev_ops.select_attention("f16", B, M, 128, K2, 128, 0.088)
+        ws = dev.allocate(max(16, sel["workspace_bytes"]))
+        launches()
+        cb = H.CommandBuffer(dev).begin()
+        dev_ops.record_attention(cb, "f16", B, M, 128, K2, 128, 0.088, q.ref(), k.ref(), v.ref(),
+                                 o.ref(), workspace=ws.ref() if sel["workspace_bytes"] else None)
+        cb.end()
+        dev.execute(cb)
+        dev.wait_idle()
+        return launches(), sel
+
+    got, sel = run(32, 4096, 4096)
+    assert [l[0] for l in got] == ["iree_b200_attention_prefill_split_f16",
+                                   "iree_b200_attention_prefill_merge_f16"]
+    assert got[0][1] == [444 + 68 * 2, 1, 1] and got[1][1] == [32, 68, 1]
+    got, _ = run(4, 1, 8192)
+    assert [l[0] for l in got] == ["iree_b200_attention_decode_split_f16",
+                                   "iree_b200_attention_decode_merge_f16"]
+    got, _ = run(32, 1, 8192)
+    assert [(l[0], l[1], l[2]) for l in got] == [("iree_b200_attention_decode_cluster_f16",
+                                                  [8, 1, 32], [288, 1, 1])]
+
+
+def test_pipelined_host_call_issues_one_dispatch_per_block(dev, dev_ops):
+    """iree_b200_ops_matmul_host above the pipeline threshold: panels go up, one dispatch per
+    (row panel, column panel) block, in diagonal order; the mock does not compute, so only
+    the launch sequence is checked here (results: tests/test_matmul_gpu.py on a GPU)."""
+    M, N, K = 1024, 768, 64
+    lhs = np.zeros((M, K), dtype=np.uint16)
+    rhs = np.zeros((K, N), dtype=np.uint16)
+    out = np.zeros((M, N), dtype=np.float32)
+    dev_ops.set_host_pipeline(0, 256, 256)
+    launches()
+    try:
+        dev_ops.matmul_host("bf16", 1, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data)
+    finally:
+        dev_ops.set_host_pipeline(16 << 20, 2048, 2048)
+    got = launches()
+    assert len(got) == (M // 256) * (N // 256)
+    assert {l[0] for l in got} == {"iree_b200_matmul_bf16_f32_1cta"}
+    assert all(l[1] == [2, 1, 1] for l in got)      # 256x256 block = two 128x256 tiles
+
+
+def test_mx_executable_loads_on_first_use_only(dev, dev_ops):
+    M, N, K = 64, 64, 64
+    z = lambda n: np.zeros(n, dtype=np.uint8)
+    lhs, ls, rhs, rs = z(M * K // 2), z(M * K // 32), z(N * K // 2), z(N * K // 32)
+    out = np.zeros((M, N), dtype=np.float32)
+    launches()
+    dev_ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                              rs.ctypes.data, out.ctypes.data)
+    assert launches() == [("iree_b200_matmul_generic_mxfp4_f32", [1, 1, 1], [256, 1, 1], 0)]
+
+
+@pytest.mark.parametrize("case", [
+    # batch, M, K, N, accumulate, nt, truncate, block
+    (1, 1000, 272, 528, True, False, False, 256),
+    (1, 528, 144, 1008, False, True, False, 256),
+    (3, 300, 528, 272, False, False, False, 256),
+    (2, 513, 64, 768, False, False, True, 256),
+    (1, 1536, 144, 1280, False, False, False, 512),
+], ids=str)
+def test_pipelined_matmul_staging_stays_in_bounds(dev, dev_ops, case):
+    """Ragged panels, batches, transpose_rhs, accumulate and truncation through the three-stream
+    host pipeline. The mock's copies are real memcpys between exactly-sized allocations, so
+    under tools/sanitize_host.sh (ASAN) any staging offset error is an abort; here the
+    launch count and the untouched guard bytes around the result are asserted."""
+    batch, M, K, N, accumulate, nt, truncate, block = case
+    lhs = np.zeros((batch, M, K), dtype=np.uint16)
+    rhs = np.zeros((batch, N, K) if nt else (batch, K, N), dtype=np.uint16)
+    guard = 64
+    raw = np.full(batch * M * N * (2 if truncate else 4) + 2 * guard, 0xA5, dtype=np.uint8)
+    out_ptr = raw.ctypes.data + guard
+    flags = ((H.MATMUL_ACCUMULATE if accumulate else 0) | (H.MATMUL_TRANSPOSE_RHS if nt else 0)
+             | (H.MATMUL_TRUNCATE_RESULT if truncate else 0))
+    dev_ops.set_host_pipeline(0, block, block)
+    launches()
+    try:
+        dev_ops.matmul_host("bf16", batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out_ptr, flags)
+    finally:
+        dev_ops.set_host_pipeline(16 << 20, 2048, 2048)
+    assert len(launches()) == batch * -(-M // block) * -(-N // block)
+    assert (raw[:guard] == 0xA5).all() and (raw[-guard:] == 0xA5).all()
+
+
+@pytest.mark.parametrize("case", [("f16", 5, 130, 128, 300, 128, None),
+                                  ("bf16", 3, 512, 128, 1025, 128, None),
+                                  ("f32", 4, 33, 24, 50, 40, "bool"),
+                                  ("f32", 3, 20, 16, 70, 8, "f32")], ids=str)
+def test_sliced_attention_staging_stays_in_bounds(dev, dev_ops, case):
+    t, B, M, K1, K2, N, mask_kind = case
+    es = 4 if t == "f32" else 2
+    q = np.zeros(B * M * K1 * es, dtype=np.uint8)
+    k = np.zeros(B * K2 * K1 * es, dtype=np.uint8)
+    v = np.zeros(B * K2 * N * es, dtype=np.uint8)
+    mask = None if mask_kind is None else np.zeros(B * M * K2 * (1 if mask_kind == "bool" else 4),
+                                                   dtype=np.uint8)
+    guard = 64
+    raw = np.full(B * M * N * es + 2 * guard, 0xA5, dtype=np.uint8)
+    dev_ops.set_host_pipeline(0, 2048, 2048)
+    launches()
+    try:
+        dev_ops.attention_host(t, B, M, K1, K2, N, 0.1, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                               raw.ctypes.data + guard,
+                               mask_ptr=0 if mask is None else mask.ctypes.data,
+                               mask_kind={None: 0, "bool": 1, "f32": 2}[mask_kind])
+    finally:
+        dev_ops.set_host_pipeline(16 << 20, 2048, 2048)
+    per_slice = len(dev_ops.select_attention(t, 1, M, K1, K2, N, 0.1,
+                                             mask_kind={None: 0, "bool": 1, "f32": 2}[mask_kind])["dispatches"])
+    assert len(launches()) == B * per_slice
+    assert (raw[:guard] == 0xA5).all() and (raw[-guard:] == 0xA5).all()

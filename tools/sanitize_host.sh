@@ -1,7 +1,10 @@
 #!/bin/bash
 # Builds the host side of libiree_b200.so with ASAN + UBSAN, then (1) runs tools/sanitize_harness.cc
 # against it with leak detection and (2) runs the CPU-side C-ABI tests (tests/test_cabi.py,
-# tests/test_selection_cpu.py) against it under LD_PRELOADed sanitizer runtimes. No GPU needed.
+# tests/test_selection_cpu.py) against it under LD_PRELOADed sanitizer runtimes and (3) runs the
+# launch layer's host logic (command buffers in both kinds, semaphores, executable loading,
+# the ops layer's dispatch recording) against it on top of the mock CUDA driver
+# (tests/mock_cuda/). No GPU needed.
 set -e
 ROOT=$(cd "$(dirname "$0")/.." && pwd); cd "$ROOT"
 python -m iree_b200.build > /dev/null
@@ -28,4 +31,26 @@ sys.exit(pytest.main(["-x", "-q", "tests/test_selection_cpu.py", "tests/test_cab
 PY
 LD_PRELOAD="$(gcc -print-file-name=libasan.so) $(gcc -print-file-name=libubsan.so)" \
   ASAN_OPTIONS=detect_leaks=0 python $T/run.py
+$CXX -O1 -g -std=c++17 -fPIC -shared -Wl,-soname,libcuda.so.1 -I /usr/local/cuda/include \
+  -o $T/libcuda.so.1 tests/mock_cuda/mock_cuda.cc
+cat > $T/run_mock.py <<PY
+import sys
+sys.path.insert(0, "$ROOT")
+from iree_b200 import build as B
+B.lib_path = lambda: "$T/libiree_b200_asan.so"
+import iree_b200.hal as H
+H._build.lib_path = B.lib_path
+assert H.lib()._name == "$T/libiree_b200_asan.so"
+sys.path.insert(0, "$ROOT/tests")
+from test_hal_mock_cpu import HOST_LOGIC_TESTS
+import pytest
+rc = pytest.main(["-x", "-q", "-m", "gpu", "-p", "no:cacheprovider", "tests/test_hal_gpu.py",
+                  "-k", HOST_LOGIC_TESTS])
+rc = rc or pytest.main(["-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
+                        "tests/mock_cuda/mock_suite.py"])
+sys.exit(rc)
+PY
+LD_LIBRARY_PATH=$T:$LD_LIBRARY_PATH \
+  LD_PRELOAD="$(gcc -print-file-name=libasan.so) $(gcc -print-file-name=libubsan.so)" \
+  ASAN_OPTIONS=detect_leaks=0 python $T/run_mock.py
 rm -rf $T
