@@ -56,3 +56,11 @@ def test_hal_host_logic_under_the_mock_driver(mock_env):
 def test_dispatches_as_seen_by_the_driver(mock_env):
     out = _run(mock_env, "tests/mock_cuda/mock_suite.py")
     assert " passed" in out and "failed" not in out
+
+
+@pytest.mark.skipif(_have_gpu(), reason="a real GPU is present: the GPU suite covers this")
+def test_ops_guards_and_selection_under_the_mock_driver(mock_env):
+    """The GPU suites' guard / selection / empty-shape tests need a device but no kernel."""
+    out = _run(mock_env, "tests/test_matmul_gpu.py", "tests/test_attention_gpu.py",
+               "tests/test_matmul_bias_gpu.py", "-k", "guards or selection or empty_and_zero_k")
+    assert "5 passed" in out, out
