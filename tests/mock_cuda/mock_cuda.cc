@@ -8,14 +8,18 @@
 //   * modules keep a copy of their image; cuModuleGetGlobal finds `__device__ const` globals
 //     (the `<kernel>__tma` recipes) in the cubin's ELF symbol table, so recipe evaluation and
 //     cuTensorMapEncodeTiled's arguments are real;
-//   * cuLaunchKernel does not run anything: it appends (kernel name, grid, block, shared
-//     memory) to a log the tests read back through mock_cuda_take_launches(). Results of
-//     dispatches are therefore NOT checked here — that is what the GPU suite is for;
+//   * cuLaunchKernel appends (kernel name, grid, block, shared memory) to a log the tests read
+//     back through mock_cuda_take_launches(). If the library named by MOCK_CUDA_KERNELS
+//     exports mock_run_<kernel> (mock_kernels_*.cc: the SIMT kernels' own source compiled for
+//     the host, one OS thread per CUDA thread) the launch also RUNS, with the parameter array
+//     exactly as the GPU would get it; the tcgen05 / TMA kernels have no host form and are
+//     only logged — their results are what the GPU suite is for;
 //   * graphs record their nodes and replay them in insertion order (dependencies always point
 //     backwards in the launch layer), so fills / copies / updates in graph mode are checked.
 // Reports one device: compute capability 10.0, 148 SMs, 227 KiB opt-in shared memory.
 
 #include <cuda.h>
+#include <dlfcn.h>
 #include <elf.h>
 
 #include <cstdint>
@@ -55,10 +59,29 @@ struct EncodedMap {
 std::vector<EncodedMap> g_maps;
 int g_dummy_ctx, g_dummy_stream_storage;
 
-void record_launch(const Function* f, unsigned gx, unsigned gy, unsigned gz, unsigned bx,
-                   unsigned by, unsigned bz, unsigned shared) {
-  std::lock_guard<std::mutex> lock(g_mutex);
-  g_launches.push_back({f->name, {gx, gy, gz}, {bx, by, bz}, shared});
+using RunFn = int (*)(const unsigned grid[3], const unsigned block[3], void** params);
+
+void* kernels_library() {
+  static void* lib = [] {
+    const char* path = getenv("MOCK_CUDA_KERNELS");
+    return path ? dlopen(path, RTLD_NOW | RTLD_LOCAL) : nullptr;
+  }();
+  return lib;
+}
+
+CUresult record_launch(const Function* f, unsigned gx, unsigned gy, unsigned gz, unsigned bx,
+                       unsigned by, unsigned bz, unsigned shared, void** params) {
+  {
+    std::lock_guard<std::mutex> lock(g_mutex);
+    g_launches.push_back({f->name, {gx, gy, gz}, {bx, by, bz}, shared});
+  }
+  if (void* lib = kernels_library()) {
+    if (auto run = reinterpret_cast<RunFn>(dlsym(lib, ("mock_run_" + f->name).c_str()))) {
+      const unsigned grid[3] = {gx, gy, gz}, block[3] = {bx, by, bz};
+      if (run(grid, block, params) != 0) return CUDA_ERROR_LAUNCH_FAILED;
+    }
+  }
+  return CUDA_SUCCESS;
 }
 
 void do_memset(CUdeviceptr dst, unsigned value, size_t element_size, size_t count) {
@@ -314,9 +337,9 @@ MOCK_API CUresult cuFuncGetAttribute(int* v, CUfunction_attribute, CUfunction) {
   return CUDA_SUCCESS;
 }
 MOCK_API CUresult cuLaunchKernel(CUfunction f, unsigned gx, unsigned gy, unsigned gz, unsigned bx,
-                                 unsigned by, unsigned bz, unsigned shared, CUstream, void**, void**) {
-  record_launch(reinterpret_cast<Function*>(f), gx, gy, gz, bx, by, bz, shared);
-  return CUDA_SUCCESS;
+                                 unsigned by, unsigned bz, unsigned shared, CUstream, void** params,
+                                 void**) {
+  return record_launch(reinterpret_cast<Function*>(f), gx, gy, gz, bx, by, bz, shared, params);
 }
 MOCK_API CUresult cuTensorMapEncodeTiled(CUtensorMap* map, CUtensorMapDataType type, cuuint32_t rank,
                                          void* base, const cuuint64_t* dims,
@@ -366,8 +389,9 @@ MOCK_API CUresult cuGraphAddKernelNode_v2(CUgraphNode* node, CUgraph g, const CU
                                           const CUDA_KERNEL_NODE_PARAMS* p) {
   const CUDA_KERNEL_NODE_PARAMS k = *p;
   return add_node(node, g, [k] {
+    // The parameter array lives in the command buffer that owns the graph.
     record_launch(reinterpret_cast<Function*>(k.func), k.gridDimX, k.gridDimY, k.gridDimZ,
-                  k.blockDimX, k.blockDimY, k.blockDimZ, k.sharedMemBytes);
+                  k.blockDimX, k.blockDimY, k.blockDimZ, k.sharedMemBytes, k.kernelParams);
   });
 }
 MOCK_API CUresult cuGraphAddMemsetNode(CUgraphNode* node, CUgraph g, const CUgraphNode*, size_t,

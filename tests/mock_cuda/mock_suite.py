@@ -242,3 +242,70 @@ def test_sliced_attention_staging_stays_in_bounds(dev, dev_ops, case):
                                              mask_kind={None: 0, "bool": 1, "f32": 2}[mask_kind])["dispatches"])
     assert len(launches()) == B * per_slice
     assert (raw[:guard] == 0xA5).all() and (raw[-guard:] == 0xA5).all()
+
+
+# ---- with MOCK_CUDA_KERNELS: the SIMT kernels run (their own source compiled for the host) ----
+
+def _kernels_run():
+    import os
+    return bool(os.environ.get("MOCK_CUDA_KERNELS"))
+
+
+needs_kernels = pytest.mark.skipif(not _kernels_run(), reason="MOCK_CUDA_KERNELS not set")
+
+
+@needs_kernels
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16", "f8e4m3fn", "f8e5m2"])
+@pytest.mark.parametrize("case", [(1, 70, 33, 50, False, False), (2, 17, 40, 65, True, True)], ids=str)
+def test_generic_matmul_end_to_end_on_the_host(dev, dev_ops, t, case):
+    """Host call -> staging -> record -> dispatch parameter packing -> (mock) launch -> the
+    generic kernel's own code on OS threads -> download, against the oracle, bit for bit: the
+    whole ABI path of a dispatch without a GPU."""
+    import oracle
+    batch, M, K, N, accumulate, nt = case
+    lhs = oracle.generate_random_matrix(t, (batch, M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (batch, N, K) if nt else (batch, K, N), 2)
+    acc_t = "i32" if t == "i8" else "f32"
+    acc = oracle.generate_random_matrix(acc_t, (batch, M, N), 3) if accumulate else None
+    out = acc.copy() if accumulate else np.full((batch, M, N), 77, dtype=np.int32 if t == "i8" else np.float32)
+    flags = (H.MATMUL_FORCE_GENERIC | (H.MATMUL_ACCUMULATE if accumulate else 0)
+             | (H.MATMUL_TRANSPOSE_RHS if nt else 0))
+    dev_ops.matmul_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data, flags)
+    assert np.array_equal(out, oracle.matmul(t, lhs, rhs, acc=acc, transpose_rhs=nt))
+
+
+@needs_kernels
+@pytest.mark.parametrize("t", ["i8", "bf16"])
+def test_generic_bias_relu_truncate_end_to_end_on_the_host(dev, dev_ops, t):
+    import oracle
+    M, K, N = 37, 24, 70
+    lhs = oracle.generate_random_matrix(t, (1, M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (1, K, N), 2)
+    bias = oracle.generate_random_matrix("i32" if t == "i8" else "f32", (N,), 4)
+    truncate = t != "i8"
+    out = np.zeros((1, M, N), dtype=np.uint16 if truncate else np.int32)
+    dev_ops.matmul_bias_host(t, 1, M, N, K, lhs.ctypes.data, rhs.ctypes.data, bias.ctypes.data,
+                             out.ctypes.data, H.MATMUL_FORCE_GENERIC | H.MATMUL_RELU
+                             | (H.MATMUL_TRUNCATE_RESULT if truncate else 0))
+    assert np.array_equal(out, oracle.matmul_bias(t, lhs, rhs, bias, relu=True, truncate=truncate))
+
+
+@needs_kernels
+@pytest.mark.parametrize("accumulate", [False, True], ids=["", "acc"])
+def test_mxfp4_end_to_end_on_the_host(dev, dev_ops, accumulate):
+    """The MXFP4 entry points (second executable, five bindings) down to the kernel's own code."""
+    import oracle
+    M, K, N = 70, 96, 50
+    lhs = oracle.generate_random_matrix("u8", (M, K // 2), 1)
+    ls = oracle.generate_random_matrix("f8e8m0fnu", (M, K // 32), 2)
+    rhs = oracle.generate_random_matrix("u8", (N, K // 2), 3)
+    rs = oracle.generate_random_matrix("f8e8m0fnu", (N, K // 32), 4)
+    acc = oracle.generate_random_matrix("f32", (M, N), 5) if accumulate else None
+    out = acc.copy() if accumulate else np.full((M, N), 77, dtype=np.float32)
+    dev_ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                              rs.ctypes.data, out.ctypes.data,
+                              flags=H.MATMUL_ACCUMULATE if accumulate else 0)
+    assert np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc))
+    out = np.full((M, N), 5, dtype=np.float32)
+    dev_ops.matmul_mxfp4_host(M, N, 0, 0, 0, 0, 0, out.ctypes.data)      # K == 0
+    assert (out == 0).all()

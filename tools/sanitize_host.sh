@@ -32,7 +32,11 @@ PY
 LD_PRELOAD="$(gcc -print-file-name=libasan.so) $(gcc -print-file-name=libubsan.so)" \
   ASAN_OPTIONS=detect_leaks=0 python $T/run.py
 $CXX -O1 -g -std=c++17 -fPIC -shared -Wl,-soname,libcuda.so.1 -I /usr/local/cuda/include \
-  -o $T/libcuda.so.1 tests/mock_cuda/mock_cuda.cc
+  -o $T/libcuda.so.1 tests/mock_cuda/mock_cuda.cc -ldl
+# The kernels' host builds are instrumented too: an out-of-bounds access by a SIMT kernel's own
+# code (ragged tiles, sub-range bindings, packed nibbles) aborts like under compute-sanitizer.
+$CXX -O1 -g -std=c++17 -ffp-contract=off -fPIC -shared -fsanitize=address,undefined -x c++ \
+  -I /usr/local/cuda/include -o $T/libmock_kernels.so tests/mock_cuda/mock_kernels_generic.cc tests/mock_cuda/mock_kernels_mx.cc -lpthread
 cat > $T/run_mock.py <<PY
 import sys
 sys.path.insert(0, "$ROOT")
@@ -50,7 +54,7 @@ rc = rc or pytest.main(["-x", "-q", "-m", "gpu", "-p", "no:cacheprovider",
                         "tests/mock_cuda/mock_suite.py"])
 sys.exit(rc)
 PY
-LD_LIBRARY_PATH=$T:$LD_LIBRARY_PATH \
+LD_LIBRARY_PATH=$T:$LD_LIBRARY_PATH MOCK_CUDA_KERNELS=$T/libmock_kernels.so \
   LD_PRELOAD="$(gcc -print-file-name=libasan.so) $(gcc -print-file-name=libubsan.so)" \
   ASAN_OPTIONS=detect_leaks=0 python $T/run_mock.py
 rm -rf $T
