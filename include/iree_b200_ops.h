@@ -141,7 +141,9 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_bias(
     int64_t M, int64_t N, int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs,
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t bias, iree_b200_buffer_ref_t out);
 
-// Host-buffer form of the FLAG_BIAS dispatches (upload, one dispatch, download).
+// Host-buffer form of the FLAG_BIAS dispatches: upload, one dispatch, download; above the
+// iree_b200_ops_set_host_pipeline threshold the same panel pipeline as
+// iree_b200_ops_matmul_host, each block dispatched with its columns of |bias|.
 IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_bias_host(
     iree_b200_ops_t* ops, int32_t element_type, int64_t batch, int64_t M, int64_t N, int64_t K,
     uint32_t flags, const void* lhs, const void* rhs, const void* bias, void* out);

@@ -623,7 +623,8 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
                                          int64_t batch, int64_t M, int64_t N, int64_t K,
                                          uint32_t flags, const uint64_t bytes[3], const void* lhs,
                                          const void* rhs, void* out,
-                                         std::vector<iree_b200_command_buffer_t*>* cbs) {
+                                         std::vector<iree_b200_command_buffer_t*>* cbs,
+                                         const void* bias = nullptr) {
   iree_b200_device_t* device = ops->device;
   const CudaSymbols* cu = device->cu;
   const uint64_t es = matmul_elem_size(element_type);
@@ -639,10 +640,16 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
   const uint64_t off_a = 0;
   const uint64_t off_b = (bytes[0] + 1023) / 1024 * 1024;
   const uint64_t off_c = off_b + (bytes[1] + 1023) / 1024 * 1024;
-  B200_RETURN_IF_ERROR(reserve_arena(ops, off_c + bytes[2] + 1024));
+  const uint64_t off_bias = off_c + (bytes[2] + 1023) / 1024 * 1024;
+  const uint64_t bias_bytes = bias ? (uint64_t)N * 4 : 0;
+  B200_RETURN_IF_ERROR(reserve_arena(ops, off_bias + bias_bytes + 1024));
   B200_RETURN_IF_ERROR(ensure_transfer_streams(ops));
   iree_b200_buffer_t* arena = ops->arena;
   const CUdeviceptr base = arena->device_ptr;
+  if (bias) {
+    // First on the upload stream: every panel's "ready" event is recorded behind it.
+    B200_CU(cu, cuMemcpyHtoDAsync(base + off_bias, bias, bias_bytes, ops->upload_stream));
+  }
   const uint8_t* host_a = static_cast<const uint8_t*>(lhs);
   const uint8_t* host_b = static_cast<const uint8_t*>(rhs);
   uint8_t* host_c = static_cast<uint8_t*>(out);
@@ -707,11 +714,17 @@ iree_b200_status_t matmul_host_pipelined(iree_b200_ops_t* ops, int32_t element_t
           B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
           cbs->push_back(cb);
           B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
-          B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
-              ops, cb, element_type, 1, rows, cols, K, flags,
-              iree_b200_buffer_ref_t{arena, off_a + a_at, (uint64_t)rows * K * es},
-              iree_b200_buffer_ref_t{arena, off_b + b_at, (uint64_t)cols * K * es},
-              iree_b200_buffer_ref_t{arena, off_c + c_at, (uint64_t)rows * cols * out_es}));
+          const iree_b200_buffer_ref_t a_ref{arena, off_a + a_at, (uint64_t)rows * K * es};
+          const iree_b200_buffer_ref_t b_ref{arena, off_b + b_at, (uint64_t)cols * K * es};
+          const iree_b200_buffer_ref_t c_ref{arena, off_c + c_at, (uint64_t)rows * cols * out_es};
+          if (bias) {  // this block's columns of the bias vector
+            B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul_bias(
+                ops, cb, element_type, 1, rows, cols, K, flags, a_ref, b_ref,
+                iree_b200_buffer_ref_t{arena, off_bias + col0 * 4, (uint64_t)cols * 4}, c_ref));
+          } else {
+            B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(ops, cb, element_type, 1, rows, cols, K,
+                                                             flags, a_ref, b_ref, c_ref));
+          }
           B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
           B200_RETURN_IF_ERROR(
               iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
@@ -755,14 +768,18 @@ static iree_b200_status_t matmul_host_impl(iree_b200_ops_t* ops, int32_t element
   const bool tma_ok = K > 0 && (K * es) % 16 == 0 && (N * out_es) % 16 == 0 && (N * es) % 16 == 0;
   const int64_t blocks =
       batch * ceil_div(M, ops->pipeline_block_m) * ceil_div(N, ops->pipeline_block_n);
-  const bool pipelined =
-      !bias && tma_ok && blocks >= 2 && bytes[0] + bytes[1] + bytes[2] >= ops->pipeline_min_bytes &&
-      !(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_FORCE_1CTA |
-                 IREE_B200_MATMUL_FLAG_FORCE_2CTA));
+  // (With the threshold set to 0 — a test setting — a forced generic family is pipelined as
+  // well: the mock-driver suite runs the SIMT kernels on the host and so checks the whole
+  // panel / block data path without a GPU.)
+  const bool family_forced =
+      (flags & (IREE_B200_MATMUL_FLAG_FORCE_1CTA | IREE_B200_MATMUL_FLAG_FORCE_2CTA)) ||
+      ((flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC) && ops->pipeline_min_bytes != 0);
+  const bool pipelined = tma_ok && blocks >= 2 && !family_forced &&
+                         bytes[0] + bytes[1] + bytes[2] >= ops->pipeline_min_bytes;
   std::vector<iree_b200_command_buffer_t*> cbs;
   iree_b200_status_t status =
       pipelined ? matmul_host_pipelined(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs,
-                                        out, &cbs)
+                                        out, &cbs, bias)
                 : matmul_host_serial(ops, element_type, batch, M, N, K, flags, bytes, lhs, rhs, out,
                                      &cbs, bias);
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";

@@ -47,6 +47,7 @@ struct Graph {
 struct Launch {
   std::string name;
   unsigned grid[3], block[3], shared;
+  uint64_t args[4];  // first four parameter slots (matmul dispatches only, else 0)
 };
 
 std::mutex g_mutex;
@@ -72,8 +73,14 @@ void* kernels_library() {
 CUresult record_launch(const Function* f, unsigned gx, unsigned gy, unsigned gz, unsigned bx,
                        unsigned by, unsigned bz, unsigned shared, void** params) {
   {
+    Launch l = {f->name, {gx, gy, gz}, {bx, by, bz}, shared, {0, 0, 0, 0}};
+    // Dispatch parameters are 8-byte slots (command_buffer.cc record_dispatch); every matmul
+    // export has at least four (three bindings + M).
+    if (f->name.rfind("iree_b200_matmul", 0) == 0) {
+      for (int i = 0; i < 4; ++i) memcpy(&l.args[i], params[i], sizeof(uint64_t));
+    }
     std::lock_guard<std::mutex> lock(g_mutex);
-    g_launches.push_back({f->name, {gx, gy, gz}, {bx, by, bz}, shared});
+    g_launches.push_back(l);
   }
   if (void* lib = kernels_library()) {
     if (auto run = reinterpret_cast<RunFn>(dlsym(lib, ("mock_run_" + f->name).c_str()))) {
@@ -121,14 +128,17 @@ bool find_symbol(std::vector<uint8_t>& image, const char* name, uint8_t** out, s
 
 // ---- test-side accessors -------------------------------------------------------------------
 
-// Writes up to |capacity| bytes of "name gx gy gz bx by bz shared\n" lines and clears the log.
+// Writes up to |capacity| bytes of "name gx gy gz bx by bz shared a0 a1 a2 a3\n" lines and
+// clears the log.
 MOCK_API size_t mock_cuda_take_launches(char* out, size_t capacity) {
   std::lock_guard<std::mutex> lock(g_mutex);
   std::string text;
   for (const Launch& l : g_launches) {
-    char line[256];
-    snprintf(line, sizeof(line), "%s %u %u %u %u %u %u %u\n", l.name.c_str(), l.grid[0], l.grid[1],
-             l.grid[2], l.block[0], l.block[1], l.block[2], l.shared);
+    char line[384];
+    snprintf(line, sizeof(line), "%s %u %u %u %u %u %u %u %llu %llu %llu %llu\n", l.name.c_str(),
+             l.grid[0], l.grid[1], l.grid[2], l.block[0], l.block[1], l.block[2], l.shared,
+             (unsigned long long)l.args[0], (unsigned long long)l.args[1],
+             (unsigned long long)l.args[2], (unsigned long long)l.args[3]);
     text += line;
   }
   g_launches.clear();

@@ -35,6 +35,11 @@ def launches():
             for l in _take(_mock().mock_cuda_take_launches)]
 
 
+def launch_args():
+    """(kernel name, [first four parameter slots]) per launch (matmul dispatches only)."""
+    return [(l[0], [int(x) for x in l[8:12]]) for l in _take(_mock().mock_cuda_take_launches)]
+
+
 def tensor_maps():
     out = []
     for l in _take(_mock().mock_cuda_take_tensor_maps):
@@ -173,6 +178,56 @@ def test_pipelined_host_call_issues_one_dispatch_per_block(dev, dev_ops):
     assert all(l[1] == [2, 1, 1] for l in got)      # 256x256 block = two 128x256 tiles
 
 
+@pytest.mark.parametrize("case", [(1, 1000, 272, 528, False, False), (2, 513, 64, 784, True, True)],
+                         ids=str)
+def test_pipelined_bias_call_hands_each_block_its_bias_columns(dev, dev_ops, case):
+    """iree_b200_ops_matmul_bias_host through the pipeline: the bias goes up once (the mock's
+    device memory is host memory, so the staged copy is read back here), each block's
+    dispatch is the fused export with binding 2 at bias + 4 * (first column of the block),
+    and lhs / result bindings follow the row panel / packed-block layout."""
+    batch, M, K, N, nt, truncate = case
+    block, out_es = 256, 2 if truncate else 4
+    lhs = np.zeros((batch, M, K), dtype=np.uint16)
+    rhs = np.zeros((batch, N, K) if nt else (batch, K, N), dtype=np.uint16)
+    bias = np.arange(N, dtype=np.float32) + 0.5
+    guard = 64
+    raw = np.full(batch * M * N * out_es + 2 * guard, 0xA5, dtype=np.uint8)
+    flags = (H.MATMUL_RELU | (H.MATMUL_TRANSPOSE_RHS if nt else 0)
+             | (H.MATMUL_TRUNCATE_RESULT if truncate else 0))
+    dev_ops.set_host_pipeline(0, block, block)
+    launches()
+    try:
+        dev_ops.matmul_bias_host("bf16", batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data,
+                                 bias.ctypes.data, raw.ctypes.data + guard, flags)
+    finally:
+        dev_ops.set_host_pipeline(16 << 20, 2048, 2048)
+    got = launch_args()
+    rows, cols = -(-M // block), -(-N // block)
+    assert len(got) == batch * rows * cols
+    suffix = ("_nt" if nt else "") + ("_bf16_bf16" if truncate else "_bf16_f32")
+    assert {g[0].replace("_1cta", "") for g in got} == {"iree_b200_matmul_bias" + suffix}
+    assert (raw[:guard] == 0xA5).all() and (raw[-guard:] == 0xA5).all()
+
+    lhs0 = min(g[1][0] for g in got)
+    bias0 = min(g[1][2] for g in got)
+    out0 = min(g[1][3] for g in got)
+    staged = np.ctypeslib.as_array(ctypes.cast(bias0, ctypes.POINTER(ctypes.c_float)), (N,))
+    assert np.array_equal(staged, bias)
+    # The bias sits behind the (1 KiB-rounded) result staging.
+    assert bias0 == out0 + -(-batch * M * N * out_es // 1024) * 1024
+    seen = set()
+    for _, (a, _, bptr, c) in got:
+        j = (bptr - bias0) // (4 * block)
+        assert bptr == bias0 + 4 * block * j and 0 <= j < cols
+        b, rem = divmod(a - lhs0, M * K * 2)
+        i = rem // (block * K * 2)
+        assert rem == i * block * K * 2 and 0 <= b < batch and 0 <= i < rows
+        mb = min(block, M - i * block)
+        assert c == out0 + ((b * M + i * block) * N + mb * j * block) * out_es
+        seen.add((b, i, j))
+    assert len(seen) == len(got)                       # every block exactly once
+
+
 def test_mx_executable_loads_on_first_use_only(dev, dev_ops):
     M, N, K = 64, 64, 64
     z = lambda n: np.zeros(n, dtype=np.uint8)
@@ -309,3 +364,58 @@ def test_mxfp4_end_to_end_on_the_host(dev, dev_ops, accumulate):
     out = np.full((M, N), 5, dtype=np.float32)
     dev_ops.matmul_mxfp4_host(M, N, 0, 0, 0, 0, 0, out.ctypes.data)      # K == 0
     assert (out == 0).all()
+
+
+@needs_kernels
+@pytest.mark.parametrize("t", ["bf16", "i8"])
+@pytest.mark.parametrize("case", [
+    # batch, M, K, N, accumulate, nt, truncate, bias, relu
+    (1, 300, 16, 528, False, False, False, False, False),
+    (2, 260, 32, 272, True, True, False, False, False),
+    (1, 520, 16, 272, False, False, True, False, False),
+    (1, 300, 16, 528, False, False, False, True, True),
+    (2, 260, 32, 272, True, True, False, True, False),
+    (1, 264, 16, 528, False, True, True, True, True),
+], ids=str)
+def test_pipelined_host_call_end_to_end_on_the_host(dev, dev_ops, t, case):
+    """The three-stream pipeline's whole data path (row / column panel uploads, accumulator
+    and bias staging, packed result blocks, 2-D downloads) with the generic kernel standing
+    in for the tcgen05 one (threshold 0 lets the forced family through), bit for bit
+    against the oracle."""
+    import oracle
+    batch, M, K, N, accumulate, nt, truncate, with_bias, relu = case
+    if truncate and t == "i8":
+        pytest.skip("TRUNCATE_RESULT is f16 / bf16 only")
+    acc_t = "i32" if t == "i8" else "f32"
+    lhs = oracle.generate_random_matrix(t, (batch, M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (batch, N, K) if nt else (batch, K, N), 2)
+    acc = oracle.generate_random_matrix(acc_t, (batch, M, N), 3) if accumulate else None
+    bias = oracle.generate_random_matrix(acc_t, (N,), 4) if with_bias else None
+    if truncate:
+        out = np.full((batch, M, N), 0x7777, dtype=np.uint16)
+    else:
+        out = acc.copy() if accumulate else np.full((batch, M, N), 77, dtype=np.dtype(
+            np.int32 if t == "i8" else np.float32))
+    flags = (H.MATMUL_FORCE_GENERIC | (H.MATMUL_ACCUMULATE if accumulate else 0)
+             | (H.MATMUL_TRANSPOSE_RHS if nt else 0) | (H.MATMUL_TRUNCATE_RESULT if truncate else 0)
+             | (H.MATMUL_RELU if relu else 0))
+    dev_ops.set_host_pipeline(0, 256, 256)
+    launches()
+    try:
+        if with_bias:
+            dev_ops.matmul_bias_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data,
+                                     bias.ctypes.data, out.ctypes.data, flags)
+        else:
+            dev_ops.matmul_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data,
+                                out.ctypes.data, flags)
+    finally:
+        dev_ops.set_host_pipeline(16 << 20, 2048, 2048)
+    assert len(launches()) == batch * -(-M // 256) * -(-N // 256)     # it was the pipeline
+    if with_bias:
+        want = oracle.matmul_bias(t, lhs, rhs, bias, acc=acc, transpose_rhs=nt, relu=relu,
+                                  truncate=truncate)
+    else:
+        want = oracle.matmul(t, lhs, rhs, acc=acc, transpose_rhs=nt)
+        if truncate:
+            want = oracle.from_f32(t, want)
+    assert np.array_equal(out, want)
