@@ -178,6 +178,30 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(
     const void* lhs_scales, const void* rhs, const void* rhs_scales, void* out);
 
 //===----------------------------------------------------------------------===//
+// linalg.mmt4d — the contraction on data-tiled (pre-packed) operands (SURVEY §8(f) rank 3;
+// PENDING its first GPU run — see kernels/mmt4d_kernels.cu)
+//===----------------------------------------------------------------------===//
+//
+// What IREE's encoding path turns a matmul into once the operands carry a tiled layout;
+// the CPU backends lower it to the iree_uk_mmt4d micro-kernel
+// (runtime/src/iree/builtins/ukernel/mmt4d.h:14-22), whose argument meaning this mirrors:
+//   lhs [M1, K1, M0, K0], rhs [N1, K1, N0, K0], out [M1, N1, M0, N0], all dense;
+//   out = (FLAG_ACCUMULATE ? out : 0) + sum_{k1,k0} lhs[m1,k1,m0,k0] * rhs[n1,k1,n0,k0]
+// in f32 (F16 / BF16 operands) or wrapping i32 (I8). Tile sizes are run-time values in
+// [1, 32767] (the micro-kernel's int16 range, mmt4d.c:12-52). No other flag applies. An
+// empty result (M1 == 0 or N1 == 0) records nothing; K1 == 0 stores zeros (or leaves out
+// unchanged with FLAG_ACCUMULATE), as iree_uk_mmt4d_early does (mmt4d.c:106-114).
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_mmt4d(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* command_buffer, int32_t element_type,
+    int64_t M1, int64_t N1, int64_t K1, int32_t M0, int32_t N0, int32_t K0, uint32_t flags,
+    iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out);
+
+// Host-buffer form (upload, one dispatch, download).
+IREE_B200_API iree_b200_status_t iree_b200_ops_mmt4d_host(
+    iree_b200_ops_t* ops, int32_t element_type, int64_t M1, int64_t N1, int64_t K1, int32_t M0,
+    int32_t N0, int32_t K0, uint32_t flags, const void* lhs, const void* rhs, void* out);
+
+//===----------------------------------------------------------------------===//
 // iree_linalg_ext.attention
 //===----------------------------------------------------------------------===//
 // Q [B,M,K1], K [B,K2,K1], V [B,K2,N], optional mask [B,M,K2], O [B,M,N]; all operands and

@@ -1,0 +1,131 @@
+// mmt4d_kernels.cu — linalg.mmt4d on data-tiled operands, SIMT form.
+//
+// PENDING VALIDATION: written after this round's GPU budget was spent. The device code below
+// has run only on host threads (tests/mock_cuda/mock_kernels_mmt4d.cc under the mock driver:
+// bit-exact against the oracle and against the reference's own iree_uk_mmt4d, also under
+// ASAN). Ships in the on-demand second executable (build.py EXPERIMENTAL_UNITS).
+//
+// IREE's encoding path pre-packs matmul operands into tiles ("data tiling"); the contraction
+// on packed operands is linalg.mmt4d, whose CPU lowering is the iree_uk_mmt4d micro-kernel
+// (runtime/src/iree/builtins/ukernel/mmt4d.h:14-22 parameters, mmt4d.c:55-103 outer loops,
+// mmt4d_tile_generic.c:54-79,199-227,289-317 tiles; element-wise statement
+// tools/mmt4d_test.c:17-31):
+//   lhs [M1, K1, M0, K0], rhs [N1, K1, N0, K0] (the "t": rhs tiles are N-major),
+//   out [M1, N1, M0, N0];
+//   out[m1,n1,m0,n0] = (accumulate ? out[m1,n1,m0,n0] : 0)
+//                      + sum over k1 ascending, k0 ascending of lhs[m1,k1,m0,k0] * rhs[n1,k1,n0,k0]
+// in f32 (f16 / bf16 operands) or wrapping i32 (i8 operands). Tile sizes are run-time values:
+// the compiler picks them per target (16x16x2 for AVX-512-BF16, 8x8x1, 16x16x16 for a GPU MMA
+// intrinsic, …), so a module packed for any of them runs unchanged.
+//
+// ABI: bindings lhs, rhs (read-only), out; constants M1, N1, K1, M0, N0, K0, flags (bit 0:
+// accumulate into out). workgroup_size = [256,1,1]; workgroup count =
+// [ceil(N1*N0/64), ceil(M1*M0/64), 1]: a block owns a 64x64 region of the logical
+// [M1*M0, N1*N0] result, k accumulated in ascending order exactly as the reference loops do,
+// so results are bit-identical for any input whose f32 products are exact (all f16 / bf16
+// products are) and for every i8 input.
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+namespace {
+
+constexpr int kMmt4dTile = 64;
+constexpr int kMmt4dTileK = 16;
+
+__device__ __forceinline__ float mmt4d_to_acc(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float mmt4d_to_acc(__half v) { return __half2float(v); }
+__device__ __forceinline__ int32_t mmt4d_to_acc(int8_t v) { return (int32_t)v; }
+
+// Element (r, k) of a packed [R1, K1, R0, K0] operand.
+__device__ __forceinline__ size_t packed_at(int r, int k, int K1, int R0, int K0) {
+  return ((size_t)(r / R0) * K1 + k / K0) * ((size_t)R0 * K0) + (size_t)(r % R0) * K0 + k % K0;
+}
+
+template <typename TIn, typename TAcc>
+__device__ __forceinline__ void mmt4d_generic_body(const TIn* __restrict__ lhs,
+                                                   const TIn* __restrict__ rhs,
+                                                   TAcc* __restrict__ out, int M1, int N1, int K1,
+                                                   int M0, int N0, int K0, int flags) {
+  __shared__ TAcc a_tile[kMmt4dTileK][kMmt4dTile + 1];
+  __shared__ TAcc b_tile[kMmt4dTileK][kMmt4dTile + 1];
+
+  const bool accumulate = (flags & 1) != 0;
+  const int M = M1 * M0, N = N1 * N0, K = K1 * K0;  // logical (padded) extents
+  const int m0 = blockIdx.y * kMmt4dTile;
+  const int n0 = blockIdx.x * kMmt4dTile;
+  const int tx = threadIdx.x % 16;
+  const int ty = threadIdx.x / 16;
+
+  TAcc acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gm = m0 + ty + 16 * i, gn = n0 + tx + 16 * j;
+      acc[i][j] = (accumulate && gm < M && gn < N) ? out[packed_at(gm, gn, N1, M0, N0)] : TAcc(0);
+    }
+  }
+
+  for (int k0 = 0; k0 < K; k0 += kMmt4dTileK) {
+    // Consecutive threads walk k: contiguous within a tile row when K0 > 1.
+    for (int idx = threadIdx.x; idx < kMmt4dTile * kMmt4dTileK; idx += 256) {
+      const int kk = idx % kMmt4dTileK, rr = idx / kMmt4dTileK;
+      const int gk = k0 + kk, gm = m0 + rr, gn = n0 + rr;
+      a_tile[kk][rr] =
+          (gm < M && gk < K) ? mmt4d_to_acc(lhs[packed_at(gm, gk, K1, M0, K0)]) : TAcc(0);
+      b_tile[kk][rr] =
+          (gn < N && gk < K) ? mmt4d_to_acc(rhs[packed_at(gn, gk, K1, N0, K0)]) : TAcc(0);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < kMmt4dTileK; ++kk) {
+      TAcc a[4], bb[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = a_tile[kk][ty + 16 * i];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bb[j] = b_tile[kk][tx + 16 * j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] += a[i] * bb[j];
+    }
+    __syncthreads();
+  }
+
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int gm = m0 + ty + 16 * i;
+    if (gm >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int gn = n0 + tx + 16 * j;
+      if (gn >= N) continue;
+      out[packed_at(gm, gn, N1, M0, N0)] = acc[i][j];
+    }
+  }
+}
+
+}  // namespace
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_generic_bf16_f32(const __nv_bfloat16* __restrict__ lhs,
+                                     const __nv_bfloat16* __restrict__ rhs, float* __restrict__ out,
+                                     int M1, int N1, int K1, int M0, int N0, int K0, int flags) {
+  mmt4d_generic_body<__nv_bfloat16, float>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_generic_f16_f32(const __half* __restrict__ lhs, const __half* __restrict__ rhs,
+                                    float* __restrict__ out, int M1, int N1, int K1, int M0, int N0,
+                                    int K0, int flags) {
+  mmt4d_generic_body<__half, float>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_generic_i8_i32(const int8_t* __restrict__ lhs, const int8_t* __restrict__ rhs,
+                                   int32_t* __restrict__ out, int M1, int N1, int K1, int M0, int N0,
+                                   int K0, int flags) {
+  mmt4d_generic_body<int8_t, int32_t>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
+}

@@ -60,6 +60,7 @@ struct iree_b200_ops_t {
   // Loaded by the first MX call only (iree_b200_ops_matmul_mxfp4_*).
   iree_b200_executable_t* mx_executable = nullptr;
   int32_t mxfp4_generic_export = -1;
+  int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
   std::mutex mx_mutex;
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
@@ -832,6 +833,16 @@ static iree_b200_status_t ensure_mx_executable(iree_b200_ops_t* ops) {
   if (ops->mxfp4_generic_export < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND, "the MX executable has no mxfp4 export");
   }
+  static const char* const kMmt4dNames[3] = {"iree_b200_mmt4d_generic_i8_i32",
+                                             "iree_b200_mmt4d_generic_f16_f32",
+                                             "iree_b200_mmt4d_generic_bf16_f32"};
+  for (int i = 0; i < 3; ++i) {
+    ops->mmt4d_generic_exports[i] = lookup(ops->mx_executable, kMmt4dNames[i]);
+    if (ops->mmt4d_generic_exports[i] < 0) {
+      return make_status(IREE_B200_STATUS_NOT_FOUND, "the second executable has no %s export",
+                         kMmt4dNames[i]);
+    }
+  }
   return IREE_B200_STATUS_OK;
 }
 
@@ -937,6 +948,148 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     B200_RETURN_IF_ERROR(
         iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
     B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, ops->arena, offsets[4], out, bytes[4]));
+    return iree_b200_device_wait_idle(device);
+  };
+  iree_b200_status_t status = run();
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (status != IREE_B200_STATUS_OK) iree_b200_device_wait_idle(device);
+  iree_b200_command_buffer_release(cb);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
+
+//===----------------------------------------------------------------------===//
+// linalg.mmt4d on data-tiled operands (pending its first GPU run; kernels/mmt4d_kernels.cu)
+//===----------------------------------------------------------------------===//
+
+namespace {
+
+struct Mmt4dShape {
+  int slot;             // index into mmt4d_generic_exports
+  uint64_t bytes[3];    // lhs, rhs, out
+};
+
+iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int64_t K1, int32_t M0,
+                               int32_t N0, int32_t K0, uint32_t flags, Mmt4dShape* shape) {
+  switch (element_type) {
+    case IREE_B200_ELEMENT_TYPE_I8: shape->slot = 0; break;
+    case IREE_B200_ELEMENT_TYPE_F16: shape->slot = 1; break;
+    case IREE_B200_ELEMENT_TYPE_BF16: shape->slot = 2; break;
+    default:
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "mmt4d takes i8, f16 or bf16 operands (got element type %d)", element_type);
+  }
+  if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "mmt4d takes FLAG_ACCUMULATE only");
+  }
+  if (M0 < 1 || N0 < 1 || K0 < 1 || M0 > 32767 || N0 > 32767 || K0 > 32767) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "mmt4d tile sizes %dx%dx%d must be within [1, 32767]", M0, N0, K0);
+  }
+  // The logical extents index with 32-bit ints in the kernel; rows are grid.y blocks of 64.
+  if (M1 < 0 || N1 < 0 || K1 < 0 || M1 > INT32_MAX / M0 || N1 > INT32_MAX / N0 ||
+      K1 > INT32_MAX / K0 || ceil_div(M1 * M0, 64) > 65535) {
+    return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                       "mmt4d shape [%lld,%lld,%lld] x tiles %dx%dx%d out of range", (long long)M1,
+                       (long long)N1, (long long)K1, M0, N0, K0);
+  }
+  const uint64_t es = matmul_elem_size(element_type);
+  shape->bytes[0] = (uint64_t)M1 * K1 * M0 * K0 * es;
+  shape->bytes[1] = (uint64_t)N1 * K1 * N0 * K0 * es;
+  shape->bytes[2] = (uint64_t)M1 * N1 * M0 * N0 * 4;
+  return IREE_B200_STATUS_OK;
+}
+
+}  // namespace
+
+iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                              int32_t element_type, int64_t M1, int64_t N1,
+                                              int64_t K1, int32_t M0, int32_t N0, int32_t K0,
+                                              uint32_t flags, iree_b200_buffer_ref_t lhs,
+                                              iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out) {
+  B200_REQUIRE_ARG(ops && cb);
+  B200_RETURN_IF_ERROR(require_device(ops));
+  Mmt4dShape shape;
+  B200_RETURN_IF_ERROR(check_mmt4d(element_type, M1, N1, K1, M0, N0, K0, flags, &shape));
+  if (M1 == 0 || N1 == 0) return IREE_B200_STATUS_OK;  // empty result
+  // K1 == 0 with ACCUMULATE leaves the result as it is (iree_uk_mmt4d_early, mmt4d.c:106-114).
+  if (K1 == 0 && (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE)) return IREE_B200_STATUS_OK;
+  const iree_b200_buffer_ref_t refs[3] = {lhs, rhs, out};
+  const uint64_t align[3] = {matmul_elem_size(element_type), matmul_elem_size(element_type), 4};
+  for (int i = 0; i < 3; ++i) {
+    if (!refs[i].buffer) {  // K1 == 0: the operand bindings are empty and may be NULL
+      if (shape.bytes[i]) return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "mmt4d binding %d is NULL", i);
+      continue;
+    }
+    const uint64_t total = refs[i].buffer->byte_length;
+    if (refs[i].offset > total) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "mmt4d binding %d offset out of range", i);
+    }
+    const uint64_t length = refs[i].length == UINT64_MAX ? total - refs[i].offset : refs[i].length;
+    if (length < shape.bytes[i] || length > total - refs[i].offset) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE,
+                         "mmt4d binding %d holds %llu bytes but the shape needs %llu", i,
+                         (unsigned long long)length, (unsigned long long)shape.bytes[i]);
+    }
+    if ((refs[i].buffer->device_ptr + refs[i].offset) % align[i]) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "mmt4d binding %d is not aligned to its element size", i);
+    }
+  }
+  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  const uint32_t grid[3] = {(uint32_t)ceil_div(N1 * N0, 64), (uint32_t)ceil_div(M1 * M0, 64), 1};
+  const uint32_t constants[7] = {(uint32_t)M1, (uint32_t)N1, (uint32_t)K1, (uint32_t)M0,
+                                 (uint32_t)N0, (uint32_t)K0,
+                                 flags & IREE_B200_MATMUL_FLAG_ACCUMULATE};
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+      cb, ops->mx_executable, ops->mmt4d_generic_exports[shape.slot], grid, constants, 7, refs, 3, 0));
+  ops->dispatch_count.fetch_add(1);
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t element_type, int64_t M1,
+                                            int64_t N1, int64_t K1, int32_t M0, int32_t N0,
+                                            int32_t K0, uint32_t flags, const void* lhs,
+                                            const void* rhs, void* out) {
+  B200_REQUIRE_ARG(ops);
+  B200_RETURN_IF_ERROR(require_device(ops));
+  Mmt4dShape shape;
+  B200_RETURN_IF_ERROR(check_mmt4d(element_type, M1, N1, K1, M0, N0, K0, flags, &shape));
+  const uint64_t* bytes = shape.bytes;
+  B200_REQUIRE_ARG((lhs || !bytes[0]) && (rhs || !bytes[1]) && (out || !bytes[2]));
+  const bool accumulate = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) != 0;
+  if (!bytes[2] || (K1 == 0 && accumulate)) return IREE_B200_STATUS_OK;
+  iree_b200_device_t* device = ops->device;
+  std::lock_guard<std::mutex> host_lock(ops->host_mutex);
+  uint64_t offsets[3], total = 0;
+  for (int i = 0; i < 3; ++i) {
+    offsets[i] = total;
+    total += (bytes[i] + 1023) / 1024 * 1024;
+  }
+  iree_b200_command_buffer_t* cb = nullptr;
+  auto run = [&]() -> iree_b200_status_t {
+    B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
+    auto ref = [&](int i) {
+      return bytes[i] ? iree_b200_buffer_ref_t{ops->arena, offsets[i], bytes[i]}
+                      : iree_b200_buffer_ref_t{nullptr, 0, 0};
+    };
+    const void* host_in[2] = {lhs, rhs};
+    for (int i = 0; i < 2; ++i) {
+      if (!bytes[i]) continue;
+      B200_RETURN_IF_ERROR(
+          iree_b200_device_transfer_h2d(device, host_in[i], ops->arena, offsets[i], bytes[i]));
+    }
+    if (accumulate) {
+      B200_RETURN_IF_ERROR(iree_b200_device_transfer_h2d(device, out, ops->arena, offsets[2], bytes[2]));
+    }
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_mmt4d(ops, cb, element_type, M1, N1, K1, M0, N0, K0,
+                                                    flags, ref(0), ref(1), ref(2)));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
+    B200_RETURN_IF_ERROR(
+        iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));
+    B200_RETURN_IF_ERROR(iree_b200_device_transfer_d2h(device, ops->arena, offsets[2], out, bytes[2]));
     return iree_b200_device_wait_idle(device);
   };
   iree_b200_status_t status = run();

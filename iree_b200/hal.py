@@ -175,6 +175,10 @@ _STATUS_FUNCS = {
                                           BufferRef, BufferRef, BufferRef, BufferRef, BufferRef],
     "iree_b200_ops_matmul_mxfp4_host": [c_void_p, c_int64, c_int64, c_int64, c_uint32, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p],
+    "iree_b200_ops_record_mmt4d": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64, c_int32,
+                                   c_int32, c_int32, c_uint32, BufferRef, BufferRef, BufferRef],
+    "iree_b200_ops_mmt4d_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32,
+                                 c_int32, c_uint32, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_select_attention": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                        c_int64, ctypes.c_float, c_int32, c_uint32, c_uint32,
                                        POINTER(AttentionSelection)],
@@ -628,6 +632,17 @@ class Ops:
         check(lib().iree_b200_ops_matmul_mxfp4_host(self._h, M, N, K, flags, lhs_ptr,
                                                     lhs_scales_ptr, rhs_ptr, rhs_scales_ptr,
                                                     out_ptr))
+
+    def record_mmt4d(self, cb: CommandBuffer, element_type, M1, N1, K1, M0, N0, K0,
+                     lhs: BufferRef, rhs: BufferRef, out: BufferRef, flags=0):
+        """linalg.mmt4d: lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0] -> out [M1,N1,M0,N0]."""
+        check(lib().iree_b200_ops_record_mmt4d(self._h, cb._h, _etype(element_type), M1, N1, K1,
+                                               M0, N0, K0, flags, lhs, rhs, out))
+
+    def mmt4d_host(self, element_type, M1, N1, K1, M0, N0, K0, lhs_ptr: int, rhs_ptr: int,
+                   out_ptr: int, flags=0):
+        check(lib().iree_b200_ops_mmt4d_host(self._h, _etype(element_type), M1, N1, K1, M0, N0, K0,
+                                             flags, lhs_ptr, rhs_ptr, out_ptr))
 
     def select_attention(self, element_type, B, M, K1, K2, N, scale, mask_kind=0, flags=0,
                          alignment=256) -> dict:

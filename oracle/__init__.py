@@ -241,6 +241,60 @@ def matmul_mxfp4(lhs: np.ndarray, lhs_scales: np.ndarray, rhs: np.ndarray, rhs_s
     return out
 
 
+def pack(a: np.ndarray, tile0: int, tile1: int) -> np.ndarray:
+    """[R, C] -> [ceil(R/tile0), ceil(C/tile1), tile0, tile1], zero padded: linalg.pack with
+    inner_dims_pos = [0, 1] (what iree_uk_pack produces for the LHS; the RHS of a mmt4d is
+    pack(rhs.T, N0, K0))."""
+    R, C = a.shape
+    R1, C1 = -(-R // tile0), -(-C // tile1)
+    padded = np.zeros((R1 * tile0, C1 * tile1), dtype=a.dtype)
+    padded[:R, :C] = a
+    return np.ascontiguousarray(padded.reshape(R1, tile0, C1, tile1).transpose(0, 2, 1, 3))
+
+
+def unpack(a4: np.ndarray, rows: int, cols: int) -> np.ndarray:
+    """Inverse of pack(): [R1, C1, tile0, tile1] -> [rows, cols]."""
+    R1, C1, t0, t1 = a4.shape
+    return np.ascontiguousarray(a4.transpose(0, 2, 1, 3).reshape(R1 * t0, C1 * t1)[:rows, :cols])
+
+
+def mmt4d(t, lhs: np.ndarray, rhs: np.ndarray, acc=None) -> np.ndarray:
+    """linalg.mmt4d (see oracle.c): lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0] -> [M1,N1,M0,N0]."""
+    tid = type_id(t)
+    lhs, rhs = np.ascontiguousarray(lhs), np.ascontiguousarray(rhs)
+    M1, K1, M0, K0 = lhs.shape
+    N1, K1r, N0, K0r = rhs.shape
+    assert (K1, K0) == (K1r, K0r)
+    out_t = np.int32 if t == "i8" else np.float32
+    out = np.empty((M1, N1, M0, N0), dtype=out_t)
+    acc_c = None if acc is None else np.ascontiguousarray(acc, dtype=out_t)
+    assert acc_c is None or acc_c.shape == out.shape
+    rc = lib().oracle_mmt4d(ctypes.c_int(tid), *(ctypes.c_int64(v) for v in (M1, N1, K1, M0, N0, K0)),
+                            _ptr(lhs), _ptr(rhs), _ptr(acc_c), _ptr(out))
+    if rc != 0:
+        raise ValueError(f"mmt4d: unsupported element type {t}")
+    return out
+
+
+def ref_mmt4d(t, lhs: np.ndarray, rhs: np.ndarray, acc=None, force_generic: bool = False) -> np.ndarray:
+    """The same contraction through the reference's own iree_uk_mmt4d (oracle/_ref)."""
+    tid = type_id(t)
+    lhs, rhs = np.ascontiguousarray(lhs), np.ascontiguousarray(rhs)
+    M1, K1, M0, K0 = lhs.shape
+    N1, _, N0, _ = rhs.shape
+    out_t = np.int32 if t == "i8" else np.float32
+    out = (np.zeros((M1, N1, M0, N0), dtype=out_t) if acc is None
+           else np.ascontiguousarray(acc, dtype=out_t).copy())
+    fn = ref_lib().oracle_ref_mmt4d
+    fn.restype = ctypes.c_int
+    rc = fn(ctypes.c_int(tid), ctypes.c_int64(M1), ctypes.c_int64(N1), ctypes.c_int64(K1),
+            ctypes.c_int(M0), ctypes.c_int(N0), ctypes.c_int(K0), _ptr(lhs), _ptr(rhs), _ptr(out),
+            ctypes.c_int(int(acc is not None)), ctypes.c_int(int(force_generic)))
+    if rc != 0:
+        raise RuntimeError("oracle_ref_mmt4d failed")
+    return out
+
+
 def matmul_element(t, lhs: np.ndarray, rhs: np.ndarray, m: int, n: int, transpose_rhs: bool = False):
     t = type_id(t)
     M, K = lhs.shape

@@ -439,6 +439,56 @@ ORACLE_API void oracle_matmul_mxfp4_f32(int64_t M, int64_t N, int64_t K, int64_t
   free(r32);
 }
 
+// linalg.mmt4d on data-tiled operands, as the reference's own test states it one result
+// element at a time (runtime/src/iree/builtins/ukernel/tools/mmt4d_test.c:31-45 f16,
+// :94-108 bf16, :157-169 s8; the tile loops around them :249-367):
+//   lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0], out [M1,N1,M0,N0];
+//   acc = accumulate ? out : 0;  for k1, for k0: acc += lhs[m1,k1,m0,k0] * rhs[n1,k1,n0,k0]
+// |type| uses this file's ids (I8 -> i32 result, F16 / BF16 -> f32 result). |acc| NULL = zero
+// init. Mirrors iree_uk_mmt4d_early (mmt4d.c:106-114): nothing is read or written for an
+// empty result; with K1*K0 == 0 the result is acc (or zeros).
+ORACLE_API int oracle_mmt4d(int type, int64_t M1, int64_t N1, int64_t K1, int64_t M0, int64_t N0,
+                            int64_t K0, const void* lhs, const void* rhs, const void* acc,
+                            void* out) {
+  if (type != ORACLE_I8 && type != ORACLE_F16 && type != ORACLE_BF16) return -1;
+#pragma omp parallel for collapse(2) schedule(static)
+  for (int64_t m1 = 0; m1 < M1; ++m1) {
+    for (int64_t n1 = 0; n1 < N1; ++n1) {
+      for (int64_t m0 = 0; m0 < M0; ++m0) {
+        for (int64_t n0 = 0; n0 < N0; ++n0) {
+          const int64_t o = ((m1 * N1 + n1) * M0 + m0) * N0 + n0;
+          const int64_t l = (m1 * K1 * M0 + m0) * K0, r = (n1 * K1 * N0 + n0) * K0;
+          if (type == ORACLE_I8) {
+            // Wrapping i32 accumulate (unsigned arithmetic: no UB on overflow).
+            uint32_t a = acc ? (uint32_t)((const int32_t*)acc)[o] : 0u;
+            for (int64_t k1 = 0; k1 < K1; ++k1) {
+              for (int64_t k0 = 0; k0 < K0; ++k0) {
+                const int32_t x = ((const int8_t*)lhs)[l + k1 * M0 * K0 + k0];
+                const int32_t y = ((const int8_t*)rhs)[r + k1 * N0 * K0 + k0];
+                a += (uint32_t)(x * y);
+              }
+            }
+            ((int32_t*)out)[o] = (int32_t)a;
+          } else {
+            float a = acc ? ((const float*)acc)[o] : 0.0f;
+            for (int64_t k1 = 0; k1 < K1; ++k1) {
+              for (int64_t k0 = 0; k0 < K0; ++k0) {
+                const uint16_t x = ((const uint16_t*)lhs)[l + k1 * M0 * K0 + k0];
+                const uint16_t y = ((const uint16_t*)rhs)[r + k1 * N0 * K0 + k0];
+                const float xf = type == ORACLE_F16 ? oracle_f16_to_f32(x) : oracle_bf16_to_f32(x);
+                const float yf = type == ORACLE_F16 ? oracle_f16_to_f32(y) : oracle_bf16_to_f32(y);
+                a += xf * yf;
+              }
+            }
+            ((float*)out)[o] = a;
+          }
+        }
+      }
+    }
+  }
+  return 0;
+}
+
 ORACLE_API void oracle_matmul_i8_i32(int64_t batch, int64_t M, int64_t N, int64_t K,
                                      int transpose_rhs, const int8_t* lhs,
                                      const int8_t* rhs, const int32_t* acc,

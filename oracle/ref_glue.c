@@ -163,3 +163,27 @@ ORACLE_REF_API int oracle_ref_matmul(int type, int64_t M, int64_t N, int64_t K, 
   free(pout);
   return 0;
 }
+
+// linalg.mmt4d straight through the reference micro-kernel on already-packed operands:
+// lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0], out [M1,N1,M0,N0] (out is also the accumulator input
+// when |accumulate|). |type| as in oracle_ref_matmul. Returns 0 or -1.
+ORACLE_REF_API int oracle_ref_mmt4d(int type, int64_t M1, int64_t N1, int64_t K1, int M0, int N0,
+                                    int K0, const void* lhs, const void* rhs, void* out,
+                                    int accumulate, int force_generic) {
+  uint32_t mm;
+  switch (type) {
+    case 0: mm = IREE_UK_FLAG_MMT4D_TYPE_S8S8S32; break;
+    case 1: mm = IREE_UK_FLAG_MMT4D_TYPE_F16F16F32; break;
+    case 2: mm = IREE_UK_FLAG_MMT4D_TYPE_BF16BF16F32; break;
+    default: return -1;
+  }
+  if (M1 < 0 || N1 < 0 || K1 < 0 || M0 <= 0 || N0 <= 0 || K0 <= 0) return -1;
+  uint64_t cpu_data[IREE_CPU_DATA_FIELD_COUNT];
+  fill_cpu_data(cpu_data);
+  if (force_generic) cpu_data[0] = 0;
+  mm |= IREE_UK_FLAG_MMT4D_ALLOW_GENERIC_FALLBACK_TILE_FUNCTION;
+  if (accumulate) mm |= IREE_UK_FLAG_MMT4D_ACCUMULATE;
+  iree_uk_mmt4d(lhs, 0, K1 * M0 * K0, rhs, 0, K1 * N0 * K0, out, 0, N1 * M0 * N0, M1, N1, K1, M0, N0,
+                K0, mm, cpu_data);
+  return 0;
+}

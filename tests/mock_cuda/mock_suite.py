@@ -419,3 +419,86 @@ def test_pipelined_host_call_end_to_end_on_the_host(dev, dev_ops, t, case):
         if truncate:
             want = oracle.from_f32(t, want)
     assert np.array_equal(out, want)
+
+
+@needs_kernels
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("case", [
+    # M, K, N (logical, before packing), M0, N0, K0, accumulate
+    (37, 50, 29, 16, 16, 2, False),      # the AVX-512-BF16 / VNNI tile shape
+    (70, 33, 130, 8, 8, 1, True),
+    (64, 64, 64, 16, 16, 16, False),     # an MMA-intrinsic-shaped tile
+    (100, 40, 33, 8, 32, 4, True),
+    (33, 17, 40, 1, 1, 1, False),        # degenerate tiles: plain [M,K] x [N,K]
+    (20, 24, 90, 7, 5, 3, True),         # tiles that divide nothing
+], ids=str)
+def test_mmt4d_end_to_end_on_the_host(dev, dev_ops, t, case):
+    """linalg.mmt4d through the host call on packed operands, bit for bit against the oracle's
+    restatement and — when oracle/_ref is built — the reference's own iree_uk_mmt4d; unpacking
+    the result gives the plain matmul of the unpacked operands."""
+    import oracle
+    M, K, N, M0, N0, K0, accumulate = case
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    l4 = oracle.pack(lhs, M0, K0)
+    r4 = oracle.pack(np.ascontiguousarray(rhs.T), N0, K0)
+    M1, K1, N1 = l4.shape[0], l4.shape[1], r4.shape[0]
+    acc_t = "i32" if t == "i8" else "f32"
+    acc = oracle.generate_random_matrix(acc_t, (M1, N1, M0, N0), 3) if accumulate else None
+    out = acc.copy() if accumulate else np.full((M1, N1, M0, N0), 77, dtype=np.dtype(
+        np.int32 if t == "i8" else np.float32))
+    launches()
+    dev_ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, out.ctypes.data,
+                       flags=H.MATMUL_ACCUMULATE if accumulate else 0)
+    got = launches()
+    assert [(g[0], g[1]) for g in got] == [
+        ("iree_b200_mmt4d_generic_%s_%s" % (t, acc_t), [-(-N1 * N0 // 64), -(-M1 * M0 // 64), 1])]
+    assert np.array_equal(out, oracle.mmt4d(t, l4, r4, acc=acc))
+    if oracle.ref_available():
+        assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
+    if not accumulate:
+        assert np.array_equal(oracle.unpack(out, M, N), oracle.matmul(t, lhs[None], rhs[None])[0])
+
+
+@needs_kernels
+def test_mmt4d_edge_cases_and_guards(dev, dev_ops):
+    import oracle
+    t, M0, N0, K0 = "bf16", 16, 16, 2
+    l4 = oracle.pack(oracle.generate_random_matrix(t, (32, 8), 1), M0, K0)
+    r4 = oracle.pack(oracle.generate_random_matrix(t, (16, 8), 2), N0, K0)
+    out = np.full((2, 1, M0, N0), 5, dtype=np.float32)
+    # K1 == 0: zeros without ACCUMULATE, untouched (and nothing launched) with it.
+    dev_ops.mmt4d_host(t, 2, 1, 0, M0, N0, K0, 0, 0, out.ctypes.data)
+    assert (out == 0).all()
+    out[:] = 5
+    launches()
+    dev_ops.mmt4d_host(t, 2, 1, 0, M0, N0, K0, 0, 0, out.ctypes.data, flags=H.MATMUL_ACCUMULATE)
+    dev_ops.mmt4d_host(t, 0, 1, 4, M0, N0, K0, 0, r4.ctypes.data, 0)      # empty result
+    assert launches() == [] and (out == 5).all()
+    for bad in (dict(M0=0), dict(K0=40000), dict(flags=H.MATMUL_TRANSPOSE_RHS), dict(t="f32"),
+                dict(M1=-1)):
+        a = dict(t=t, M1=2, N1=1, K1=4, M0=M0, N0=N0, K0=K0, flags=0)
+        a.update(bad)
+        with pytest.raises(H.Status):
+            dev_ops.mmt4d_host(a["t"], a["M1"], a["N1"], a["K1"], a["M0"], a["N0"], a["K0"],
+                               l4.ctypes.data, r4.ctypes.data, out.ctypes.data, flags=a["flags"])
+    # Recorded form: operands at sub-ranges of their buffers.
+    lhs_b, rhs_b = dev.allocate(l4.nbytes + 64), dev.allocate(r4.nbytes)
+    dev.h2d(l4.ctypes.data, lhs_b, l4.nbytes, 64)
+    dev.h2d(r4.ctypes.data, rhs_b, r4.nbytes)
+    out_b = dev.allocate(out.nbytes)
+    cb = H.CommandBuffer(dev).begin()
+    dev_ops.record_mmt4d(cb, t, 2, 1, 4, M0, N0, K0, lhs_b.ref(64, l4.nbytes), rhs_b.ref(),
+                         out_b.ref())
+    cb.end()
+    dev.execute(cb)
+    dev.wait_idle()
+    dev.d2h(out_b, out.ctypes.data, out.nbytes)
+    assert np.array_equal(out, oracle.mmt4d(t, l4, r4))
+    cb = H.CommandBuffer(dev).begin()
+    with pytest.raises(H.Status):       # result binding too short
+        dev_ops.record_mmt4d(cb, t, 2, 1, 4, M0, N0, K0, lhs_b.ref(64, l4.nbytes), rhs_b.ref(),
+                             out_b.ref(0, out.nbytes - 4))
+    with pytest.raises(H.Status):       # lhs at an odd byte: not a bf16 element boundary
+        dev_ops.record_mmt4d(cb, t, 2, 1, 4, M0, N0, K0, lhs_b.ref(63, l4.nbytes), rhs_b.ref(),
+                             out_b.ref())

@@ -40,7 +40,8 @@ def mock_env(tmp_path_factory):
     subprocess.run([cxx, "-O1", "-std=c++17", "-ffp-contract=off", "-fPIC", "-shared", "-x", "c++",
                     "-I", "/usr/local/cuda/include", "-o", str(out / "libmock_kernels.so"),
                     os.path.join(mock, "mock_kernels_generic.cc"),
-                    os.path.join(mock, "mock_kernels_mx.cc"), "-lpthread"], check=True)
+                    os.path.join(mock, "mock_kernels_mx.cc"),
+                    os.path.join(mock, "mock_kernels_mmt4d.cc"), "-lpthread"], check=True)
     env = dict(os.environ)
     env["LD_LIBRARY_PATH"] = str(out) + os.pathsep + env.get("LD_LIBRARY_PATH", "")
     env["MOCK_CUDA_KERNELS"] = str(out / "libmock_kernels.so")

@@ -329,3 +329,74 @@ def test_matmul_mxfp4_packing_and_special_scales():
     # 0xFF is NaN and poisons the rows / columns it scales (arith.scaling_extf).
     got = oracle.matmul_mxfp4(lhs, one, rhs, np.array([[127], [255]], dtype=np.uint8))
     assert got[0, 0] == 6.0 and np.isnan(got[0, 1])
+
+
+# ---- linalg.mmt4d on data-tiled operands ---------------------------------
+
+MMT4D_CASES = [
+    # M, K, N (logical), M0, N0, K0
+    (37, 50, 29, 16, 16, 2), (64, 64, 64, 8, 8, 1), (5, 3, 7, 16, 16, 1), (100, 40, 33, 8, 32, 2),
+    (33, 17, 40, 1, 1, 1), (20, 24, 90, 7, 5, 3), (48, 64, 48, 16, 16, 16),
+]
+
+
+def _mmt4d_inputs(t, case):
+    M, K, N, M0, N0, K0 = case
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    l4 = oracle.pack(lhs, M0, K0)
+    r4 = oracle.pack(np.ascontiguousarray(rhs.T), N0, K0)
+    acc = oracle.generate_random_matrix("i32" if t == "i8" else "f32",
+                                        (l4.shape[0], r4.shape[0], M0, N0), 3)
+    return lhs, rhs, l4, r4, acc
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("case", MMT4D_CASES, ids=str)
+def test_mmt4d_is_the_matmul_of_the_unpacked_operands(t, case):
+    """pack -> mmt4d -> unpack == matmul (the identity the reference's e2e_matmul_benchmark.c
+    relies on), and the accumulate form adds the packed accumulator."""
+    M, K, N = case[:3]
+    lhs, rhs, l4, r4, acc = _mmt4d_inputs(t, case)
+    out = oracle.mmt4d(t, l4, r4)
+    assert out.shape == (l4.shape[0], r4.shape[0], case[3], case[4])
+    assert np.array_equal(oracle.unpack(out, M, N), oracle.matmul(t, lhs[None], rhs[None])[0])
+    # Padding rows / columns of the tiles hold exact zeros.
+    full = oracle.unpack(out, out.shape[0] * case[3], out.shape[1] * case[4])
+    assert (full[M:] == 0).all() and (full[:, N:] == 0).all()
+    with_acc = oracle.mmt4d(t, l4, r4, acc=acc)
+    assert np.array_equal(with_acc, out + acc)      # exact: small integers in f32 / i32
+
+
+@_needs_ref
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("generic", [False, True], ids=["arch", "generic"])
+@pytest.mark.parametrize("case", MMT4D_CASES, ids=str)
+def test_mmt4d_matches_the_reference_microkernel(t, generic, case):
+    """Pins oracle.mmt4d on the reference's own iree_uk_mmt4d (oracle/_ref), arch-specific
+    tile functions where the tile shape has one (16x16x2, 8x8x1, …) and the generic C tiles
+    (mmt4d_tile_generic.c) everywhere."""
+    _, _, l4, r4, acc = _mmt4d_inputs(t, case)
+    for a in (None, acc):
+        assert np.array_equal(oracle.mmt4d(t, l4, r4, acc=a),
+                              oracle.ref_mmt4d(t, l4, r4, acc=a, force_generic=generic))
+
+
+def test_mmt4d_i8_full_range_wraps_like_the_reference():
+    rng = np.random.Generator(np.random.PCG64(5))
+    l4 = rng.integers(-128, 128, (3, 40, 16, 2), dtype=np.int8)
+    r4 = rng.integers(-128, 128, (2, 40, 16, 2), dtype=np.int8)
+    acc = np.full((3, 2, 16, 16), np.iinfo(np.int32).max, dtype=np.int32)
+    out = oracle.mmt4d("i8", l4, r4, acc=acc)
+    want = (np.einsum("akmc,bknc->abmn", l4.astype(np.int64), r4.astype(np.int64)) + acc)
+    assert np.array_equal(out, want.astype(np.uint64).astype(np.uint32).view(np.int32).reshape(out.shape))
+    if oracle.ref_available():
+        assert np.array_equal(out, oracle.ref_mmt4d("i8", l4, r4, acc=acc))
+
+
+def test_mmt4d_empty_reduction():
+    l4 = np.zeros((2, 0, 8, 4), dtype=np.uint16)
+    r4 = np.zeros((3, 0, 8, 4), dtype=np.uint16)
+    assert (oracle.mmt4d("bf16", l4, r4) == 0).all()
+    acc = np.full((2, 3, 8, 8), 2.5, dtype=np.float32)
+    assert np.array_equal(oracle.mmt4d("bf16", l4, r4, acc=acc), acc)

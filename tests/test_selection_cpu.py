@@ -27,7 +27,8 @@ def test_offline_object_selects_but_never_computes(ops):
     for call in (lambda: ops.matmul_host("bf16", 1, 8, 8, 8, 1, 1, 1),
                  lambda: ops.attention_host("f16", 1, 1, 8, 8, 8, 1.0, 1, 1, 1, 1),
                  lambda: ops.matmul_bias_host("bf16", 1, 8, 8, 8, 1, 1, 1, 1),
-                 lambda: ops.matmul_mxfp4_host(8, 8, 32, 1, 1, 1, 1, 1)):
+                 lambda: ops.matmul_mxfp4_host(8, 8, 32, 1, 1, 1, 1, 1),
+                 lambda: ops.mmt4d_host("bf16", 1, 1, 1, 8, 8, 1, 1, 1, 1)):
         with pytest.raises(H.Status) as e:
             call()
         assert e.value.name == "FAILED_PRECONDITION"

@@ -36,7 +36,7 @@ $CXX -O1 -g -std=c++17 -fPIC -shared -Wl,-soname,libcuda.so.1 -I /usr/local/cuda
 # The kernels' host builds are instrumented too: an out-of-bounds access by a SIMT kernel's own
 # code (ragged tiles, sub-range bindings, packed nibbles) aborts like under compute-sanitizer.
 $CXX -O1 -g -std=c++17 -ffp-contract=off -fPIC -shared -fsanitize=address,undefined -x c++ \
-  -I /usr/local/cuda/include -o $T/libmock_kernels.so tests/mock_cuda/mock_kernels_generic.cc tests/mock_cuda/mock_kernels_mx.cc -lpthread
+  -I /usr/local/cuda/include -o $T/libmock_kernels.so tests/mock_cuda/mock_kernels_generic.cc tests/mock_cuda/mock_kernels_mx.cc tests/mock_cuda/mock_kernels_mmt4d.cc -lpthread
 cat > $T/run_mock.py <<PY
 import sys
 sys.path.insert(0, "$ROOT")
