@@ -346,6 +346,19 @@ IREE_B200_API iree_b200_status_t iree_b200_semaphore_create(iree_b200_device_t* 
 IREE_B200_API void iree_b200_semaphore_release(iree_b200_semaphore_t* semaphore);
 IREE_B200_API iree_b200_status_t iree_b200_semaphore_query(iree_b200_semaphore_t* semaphore,
                                                            uint64_t* out_value);
+// Host-side signal (iree_hal_semaphore_signal -> event_semaphore.c:108-131): advances the
+// timeline to |value|. Values only grow: INVALID_ARGUMENT if the timeline is already at or
+// past |value| (async/semaphore.c:577-599). Submissions and waits issued AFTER the signal see
+// it; this thin layer has no deferred work queue, so a submission that waits on a value
+// nothing queued or signalled reaches is refused rather than parked (see queue_execute).
+IREE_B200_API iree_b200_status_t iree_b200_semaphore_signal(iree_b200_semaphore_t* semaphore,
+                                                            uint64_t value);
+// Marks the semaphore failed (iree_hal_semaphore_fail; async/semaphore.c:185-204): the first
+// failure wins, and every later query / wait / signal / submission that involves the
+// semaphore returns |code| with |message| (NULL = a default text). |code| must not be OK.
+IREE_B200_API iree_b200_status_t iree_b200_semaphore_fail(iree_b200_semaphore_t* semaphore,
+                                                          iree_b200_status_t code,
+                                                          const char* message);
 // Blocks the host until the timeline reaches |value| (cuEventSynchronize,
 // cuda_device.c:184-191). |timeout_ns| < 0 = infinite.
 IREE_B200_API iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore,

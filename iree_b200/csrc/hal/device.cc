@@ -500,6 +500,38 @@ iree_b200_status_t iree_b200_semaphore_query(iree_b200_semaphore_t* semaphore, u
   return IREE_B200_STATUS_OK;
 }
 
+iree_b200_status_t iree_b200_semaphore_signal(iree_b200_semaphore_t* semaphore, uint64_t value) {
+  B200_REQUIRE_ARG(semaphore);
+  std::lock_guard<std::mutex> lock(semaphore->mutex);
+  semaphore->device->cu->cuCtxSetCurrent(semaphore->device->cu_context);
+  semaphore_poll(semaphore);
+  if (semaphore->failure != IREE_B200_STATUS_OK) {
+    return make_status(semaphore->failure, "%s", semaphore->failure_message.c_str());
+  }
+  // Each timeline value is signalled once and values only grow (async/semaphore.c:577-599).
+  if (value <= semaphore->host_value) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "semaphore already signaled past %llu (timeline is at %llu)",
+                       (unsigned long long)value, (unsigned long long)semaphore->host_value);
+  }
+  semaphore->host_value = value;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_semaphore_fail(iree_b200_semaphore_t* semaphore,
+                                            iree_b200_status_t code, const char* message) {
+  B200_REQUIRE_ARG(semaphore);
+  if (code == IREE_B200_STATUS_OK) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "a semaphore cannot fail with OK");
+  }
+  std::lock_guard<std::mutex> lock(semaphore->mutex);
+  if (semaphore->failure == IREE_B200_STATUS_OK) {  // the first failure wins
+    semaphore->failure = code;
+    semaphore->failure_message = message ? message : "semaphore failed by the host";
+  }
+  return IREE_B200_STATUS_OK;
+}
+
 iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore, uint64_t value,
                                             int64_t timeout_ns) {
   B200_REQUIRE_ARG(semaphore);

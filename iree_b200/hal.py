@@ -145,6 +145,8 @@ _STATUS_FUNCS = {
     "iree_b200_semaphore_create": [c_void_p, c_uint64, POINTER(c_void_p)],
     "iree_b200_semaphore_query": [c_void_p, POINTER(c_uint64)],
     "iree_b200_semaphore_wait": [c_void_p, c_uint64, c_int64],
+    "iree_b200_semaphore_signal": [c_void_p, c_uint64],
+    "iree_b200_semaphore_fail": [c_void_p, ctypes.c_int, ctypes.c_char_p],
     "iree_b200_device_queue_execute": [c_void_p, c_size_t, POINTER(c_void_p), POINTER(c_uint64),
                                        c_size_t, POINTER(c_void_p), POINTER(c_uint64), c_void_p],
     "iree_b200_channel_id_create": [c_void_p],
@@ -355,6 +357,13 @@ class Semaphore:
 
     def wait(self, value: int, timeout_ns=-1):
         check(lib().iree_b200_semaphore_wait(self._h, value, timeout_ns))
+
+    def signal(self, value: int):
+        check(lib().iree_b200_semaphore_signal(self._h, value))
+
+    def fail(self, code: int, message: str = None):
+        check(lib().iree_b200_semaphore_fail(self._h, code,
+                                             None if message is None else message.encode()))
 
     def release(self):
         if getattr(self, "_h", None):

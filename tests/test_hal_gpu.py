@@ -468,6 +468,57 @@ def test_semaphores_and_queue_ordering(dev):
     assert e.value.name == "FAILED_PRECONDITION"
 
 
+def test_semaphore_host_signal_and_failure(dev):
+    """The host side of the timeline (reference CTS core/semaphore_test.cc: NoOp, NormalSignaling,
+    Failure, WaitThenFail / FailThenWait; semaphore_thread_test.cc for the cross-thread wait)."""
+    import threading
+    sem = H.Semaphore(dev, 2)
+    sem.signal(3)
+    sem.signal(40)                                   # values may skip
+    assert sem.query() == 40
+    sem.wait(40)
+    for stale in (40, 7, 0):                         # each value once, values only grow
+        with pytest.raises(H.Status) as e:
+            sem.signal(stale)
+        assert e.value.name == "INVALID_ARGUMENT"
+    assert sem.query() == 40
+    # A submission issued after the host signal sees it; device signals continue from there.
+    buf = _upload(dev, np.zeros(4096, dtype=np.uint8))
+    cb = H.CommandBuffer(dev).begin()
+    cb.fill(buf.ref(), b"\x5a")
+    cb.end()
+    dev.execute(cb, waits=[(sem, 40)], signals=[(sem, 41)])
+    sem.wait(41)
+    assert (_download(dev, buf, np.uint8, 4096) == 0x5A).all()
+    # Another thread's bounded wait is released by a host signal.
+    result = []
+
+    def waiter():
+        try:
+            sem.wait(50, timeout_ns=5_000_000_000)
+            result.append("ok")
+        except H.Status as err:          # pragma: no cover - reported through the assert below
+            result.append(err.name)
+
+    th = threading.Thread(target=waiter)
+    th.start()
+    sem.signal(50)
+    th.join(10)
+    assert result == ["ok"]
+    # Failure: the first one wins and poisons query / wait / signal / submissions.
+    ABORTED, DATA_LOSS = 10, 15
+    sem.fail(ABORTED, "upstream producer died")
+    sem.fail(DATA_LOSS, "second failure is ignored")
+    for call in (sem.query, lambda: sem.wait(50), lambda: sem.wait(60, timeout_ns=1_000_000),
+                 lambda: sem.signal(60), lambda: dev.execute(None, waits=[(sem, 60)])):
+        with pytest.raises(H.Status) as e:
+            call()
+        assert e.value.name == "ABORTED" and "upstream producer died" in e.value.message
+    with pytest.raises(H.Status):
+        H.Semaphore(dev, 0).fail(0)                  # OK is not a failure
+    dev.wait_idle()
+
+
 def test_many_small_submissions(dev, dev_ops):
     """command_buffer/stress_test.cc in miniature: 200 submissions of a two-command buffer,
     each ordered behind the previous one through one timeline."""
