@@ -374,6 +374,23 @@ IREE_B200_API iree_b200_status_t iree_b200_device_queue_execute(
     iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
     iree_b200_command_buffer_t* command_buffer);
 
+// iree_hal_device_queue_alloca / _dealloca (cuda_device.c:1034-1140), the form the reference
+// takes on devices without memory pools: the HOST waits for the wait list, the buffer comes
+// from the ordinary allocator, and the signal list is then signalled from the host — or
+// failed with the allocation's error, so that downstream waiters see it instead of hanging.
+// dealloca is a point on the timeline only: the memory goes back when the last reference to
+// |buffer| is released (the caller keeps its own).
+IREE_B200_API iree_b200_status_t iree_b200_device_queue_alloca(
+    iree_b200_device_t* device, size_t wait_count, iree_b200_semaphore_t* const* wait_semaphores,
+    const uint64_t* wait_values, size_t signal_count,
+    iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
+    int32_t memory_type, uint64_t byte_length, iree_b200_buffer_t** out_buffer);
+IREE_B200_API iree_b200_status_t iree_b200_device_queue_dealloca(
+    iree_b200_device_t* device, size_t wait_count, iree_b200_semaphore_t* const* wait_semaphores,
+    const uint64_t* wait_values, size_t signal_count,
+    iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
+    iree_b200_buffer_t* buffer);
+
 //===----------------------------------------------------------------------===//
 // Channels (hal/channel.h:33-129, channel_provider.h:29-66; drivers/cuda/nccl_channel.c,
 // cuda_device.c:845-927)

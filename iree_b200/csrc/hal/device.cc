@@ -577,4 +577,67 @@ iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore, ui
   }
 }
 
+// Transient allocations in queue order. Like the reference without memory pools
+// (cuda_device.c:1034-1091): the host waits for the wait list, allocates from the ordinary
+// allocator, then host-signals the signal list — or fails it, so downstream waiters see the
+// error instead of hanging.
+static iree_b200_status_t wait_all(size_t count, iree_b200_semaphore_t* const* semaphores,
+                                   const uint64_t* values) {
+  for (size_t i = 0; i < count; ++i) {
+    B200_RETURN_IF_ERROR(iree_b200_semaphore_wait(semaphores[i], values[i], /*timeout_ns=*/-1));
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+static iree_b200_status_t signal_all(size_t count, iree_b200_semaphore_t* const* semaphores,
+                                     const uint64_t* values) {
+  for (size_t i = 0; i < count; ++i) {
+    B200_RETURN_IF_ERROR(iree_b200_semaphore_signal(semaphores[i], values[i]));
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_device_queue_alloca(
+    iree_b200_device_t* device, size_t wait_count, iree_b200_semaphore_t* const* wait_semaphores,
+    const uint64_t* wait_values, size_t signal_count,
+    iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
+    int32_t memory_type, uint64_t byte_length, iree_b200_buffer_t** out_buffer) {
+  B200_REQUIRE_ARG(device && out_buffer);
+  B200_REQUIRE_ARG(!wait_count || (wait_semaphores && wait_values));
+  B200_REQUIRE_ARG(!signal_count || (signal_semaphores && signal_values));
+  *out_buffer = nullptr;
+  B200_RETURN_IF_ERROR(wait_all(wait_count, wait_semaphores, wait_values));
+  iree_b200_status_t status =
+      iree_b200_allocator_allocate_buffer(device, memory_type, byte_length, out_buffer);
+  if (status != IREE_B200_STATUS_OK) {
+    const std::string message = iree_b200_status_message();
+    for (size_t i = 0; i < signal_count; ++i) {
+      iree_b200_semaphore_fail(signal_semaphores[i], status, message.c_str());
+    }
+    return make_status(status, "%s", message.c_str());
+  }
+  status = signal_all(signal_count, signal_semaphores, signal_values);
+  if (status != IREE_B200_STATUS_OK) {
+    const std::string message = iree_b200_status_message();
+    iree_b200_buffer_release(*out_buffer);
+    *out_buffer = nullptr;
+    return make_status(status, "%s", message.c_str());
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_device_queue_dealloca(
+    iree_b200_device_t* device, size_t wait_count, iree_b200_semaphore_t* const* wait_semaphores,
+    const uint64_t* wait_values, size_t signal_count,
+    iree_b200_semaphore_t* const* signal_semaphores, const uint64_t* signal_values,
+    iree_b200_buffer_t* buffer) {
+  B200_REQUIRE_ARG(device && buffer);
+  B200_REQUIRE_ARG(!wait_count || (wait_semaphores && wait_values));
+  B200_REQUIRE_ARG(!signal_count || (signal_semaphores && signal_values));
+  // The memory itself goes back when the last reference is released (cuda_device.c:1093-1140:
+  // without pools dealloca is only a point on the timeline); the caller keeps its reference.
+  B200_RETURN_IF_ERROR(wait_all(wait_count, wait_semaphores, wait_values));
+  return signal_all(signal_count, signal_semaphores, signal_values);
+}
+
 }  // extern "C"

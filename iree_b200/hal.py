@@ -149,6 +149,11 @@ _STATUS_FUNCS = {
     "iree_b200_semaphore_fail": [c_void_p, ctypes.c_int, ctypes.c_char_p],
     "iree_b200_device_queue_execute": [c_void_p, c_size_t, POINTER(c_void_p), POINTER(c_uint64),
                                        c_size_t, POINTER(c_void_p), POINTER(c_uint64), c_void_p],
+    "iree_b200_device_queue_alloca": [c_void_p, c_size_t, POINTER(c_void_p), POINTER(c_uint64),
+                                      c_size_t, POINTER(c_void_p), POINTER(c_uint64), c_int32,
+                                      c_uint64, POINTER(c_void_p)],
+    "iree_b200_device_queue_dealloca": [c_void_p, c_size_t, POINTER(c_void_p), POINTER(c_uint64),
+                                        c_size_t, POINTER(c_void_p), POINTER(c_uint64), c_void_p],
     "iree_b200_channel_id_create": [c_void_p],
     "iree_b200_channel_provider_query_default_rank_and_count": [POINTER(c_int32),
                                                                 POINTER(c_int32)],
@@ -328,13 +333,29 @@ class Device:
     def d2h(self, source: Buffer, host_ptr: int, nbytes: int, offset=0):
         check(lib().iree_b200_device_transfer_d2h(self._h, source._h, offset, host_ptr, nbytes))
 
-    def execute(self, cb, waits=(), signals=()):
+    @staticmethod
+    def _semaphore_lists(waits, signals):
         nw, ns = len(waits), len(signals)
         ws = (c_void_p * max(nw, 1))(*[s._h for s, _ in waits])
         wv = (c_uint64 * max(nw, 1))(*[v for _, v in waits])
         ss = (c_void_p * max(ns, 1))(*[s._h for s, _ in signals])
         sv = (c_uint64 * max(ns, 1))(*[v for _, v in signals])
-        check(lib().iree_b200_device_queue_execute(self._h, nw, ws, wv, ns, ss, sv, _ptr(cb)))
+        return nw, ws, wv, ns, ss, sv
+
+    def execute(self, cb, waits=(), signals=()):
+        check(lib().iree_b200_device_queue_execute(self._h, *self._semaphore_lists(waits, signals),
+                                                   _ptr(cb)))
+
+    def queue_alloca(self, nbytes: int, waits=(), signals=(),
+                     memory_type=MEMORY_DEVICE_LOCAL) -> "Buffer":
+        h = c_void_p()
+        check(lib().iree_b200_device_queue_alloca(self._h, *self._semaphore_lists(waits, signals),
+                                                  memory_type, nbytes, byref(h)))
+        return Buffer(h, self)
+
+    def queue_dealloca(self, buffer: "Buffer", waits=(), signals=()):
+        check(lib().iree_b200_device_queue_dealloca(
+            self._h, *self._semaphore_lists(waits, signals), buffer._h))
 
     def release(self):
         if getattr(self, "_h", None):

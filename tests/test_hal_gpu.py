@@ -468,6 +468,42 @@ def test_semaphores_and_queue_ordering(dev):
     assert e.value.name == "FAILED_PRECONDITION"
 
 
+def test_queue_alloca_and_dealloca_follow_the_timeline(dev):
+    """Reference CTS queue/queue_alloca_test.cc: a transient is allocated after its waits,
+    usable by the submission that waits on its signal, and released on the timeline."""
+    sem = H.Semaphore(dev, 0)
+    src = _upload(dev, np.arange(4096, dtype=np.uint8))
+    prep = H.CommandBuffer(dev).begin()
+    prep.fill(src.ref(0, 1024), b"\x11")
+    prep.end()
+    dev.execute(prep, signals=[(sem, 1)])
+    tmp = dev.queue_alloca(4096, waits=[(sem, 1)], signals=[(sem, 2)])
+    assert tmp.byte_length == 4096 and sem.query() == 2
+    cb = H.CommandBuffer(dev).begin()
+    cb.copy(src.ref(), tmp.ref())
+    cb.end()
+    dev.execute(cb, waits=[(sem, 2)], signals=[(sem, 3)])
+    dev.queue_dealloca(tmp, waits=[(sem, 3)], signals=[(sem, 4)])
+    assert sem.query() == 4
+    got = _download(dev, tmp, np.uint8, 4096)        # our reference keeps the memory alive
+    want = np.arange(4096, dtype=np.uint8)
+    want[:1024] = 0x11
+    assert np.array_equal(got, want)
+    # A failed allocation fails the signal list instead of leaving waiters hanging.
+    bad = H.Semaphore(dev, 0)
+    with pytest.raises(H.Status):
+        dev.queue_alloca(1 << 60, signals=[(bad, 1)])
+    with pytest.raises(H.Status):
+        bad.wait(1, timeout_ns=1_000_000)
+    with pytest.raises(H.Status) as e:
+        bad.query()
+    assert e.value.name != "DEADLINE_EXCEEDED"
+    # Waiting on a failed semaphore refuses the allocation.
+    with pytest.raises(H.Status):
+        dev.queue_alloca(64, waits=[(bad, 1)])
+    dev.wait_idle()
+
+
 def test_semaphore_host_signal_and_failure(dev):
     """The host side of the timeline (reference CTS core/semaphore_test.cc: NoOp, NormalSignaling,
     Failure, WaitThenFail / FailThenWait; semaphore_thread_test.cc for the cross-thread wait)."""

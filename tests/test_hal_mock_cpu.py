@@ -20,7 +20,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HOST_LOGIC_TESTS = ("allocator_and_transfers or host_local or imported_buffers or fill_buffer or "
                     "update_buffer or copy_buffer or execution_barriers or argument_checks or "
                     "recording_state_machine or keeps_its_resources or device_queries or "
-                    "semaphores_and_queue_ordering or semaphore_host_signal or "
+                    "semaphores_and_queue_ordering or semaphore_host_signal or queue_alloca or "
                     "dispatch_constants_and_binding or "
                     "dispatch_reuse or executable_cache")
 
@@ -61,7 +61,7 @@ def _run(env, *args):
 def test_hal_host_logic_under_the_mock_driver(mock_env):
     out = _run(mock_env, "tests/test_hal_gpu.py", "-k", HOST_LOGIC_TESTS)
     passed = int(out.strip().splitlines()[-1].split(" passed")[0].split()[-1])
-    assert passed >= 38, out      # 19 tests x {stream, graph}
+    assert passed >= 40, out      # 20 tests x {stream, graph}
 
 
 @pytest.mark.skipif(_have_gpu(), reason="a real GPU is present: the GPU suite covers this")
