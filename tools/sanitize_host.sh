@@ -56,5 +56,5 @@ sys.exit(rc)
 PY
 LD_LIBRARY_PATH=$T:$LD_LIBRARY_PATH MOCK_CUDA_KERNELS=$T/libmock_kernels.so \
   LD_PRELOAD="$(gcc -print-file-name=libasan.so) $(gcc -print-file-name=libubsan.so)" \
-  ASAN_OPTIONS=detect_leaks=0 python $T/run_mock.py
+  ASAN_OPTIONS=detect_leaks=0:allocator_may_return_null=1 python $T/run_mock.py
 rm -rf $T
