@@ -44,7 +44,7 @@ CXX_FLAGS = ["-O2", "-g", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall",
 
 LIB_NAME = "libiree_b200.so"
 CDA1_NAME = "iree_b200_kernels.cda1"
-EXPERIMENTAL_CDA1_NAME = "iree_b200_mx_kernels.cda1"
+EXPERIMENTAL_CDA1_NAME = "iree_b200_pending_kernels.cda1"
 
 
 def _which(*names):
@@ -188,9 +188,9 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
         f.write('.section .rodata\n.balign 64\n.global iree_b200_builtin_cda1_start\n'
                 'iree_b200_builtin_cda1_start:\n.incbin "%s"\n'
                 '.global iree_b200_builtin_cda1_end\niree_b200_builtin_cda1_end:\n'
-                '.balign 64\n.global iree_b200_builtin_mx_cda1_start\n'
-                'iree_b200_builtin_mx_cda1_start:\n.incbin "%s"\n'
-                '.global iree_b200_builtin_mx_cda1_end\niree_b200_builtin_mx_cda1_end:\n'
+                '.balign 64\n.global iree_b200_builtin_pending_cda1_start\n'
+                'iree_b200_builtin_pending_cda1_start:\n.incbin "%s"\n'
+                '.global iree_b200_builtin_pending_cda1_end\niree_b200_builtin_pending_cda1_end:\n'
                 '.section .note.GNU-stack,"",@progbits\n' % (cda1_path(), experimental_path))
     blob_o = os.path.join(OUT, "builtin_blob.o")
     _run([cxx, "-c", "-o", blob_o, blob_s])

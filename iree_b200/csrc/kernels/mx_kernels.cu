@@ -1,7 +1,7 @@
 // mx_kernels.cu — OCP microscaling (MXFP4) matmul, shape-agnostic SIMT form.
 //
 // STATUS: compiled for sm_100a, NOT YET RUN ON A GPU (written after this round's GPU budget
-// was spent). It ships in its own executable (iree_b200_mx_kernels.cda1) that the ops layer
+// was spent). It ships in its own executable (iree_b200_pending_kernels.cda1) that the ops layer
 // loads only when an MX entry point is called, so nothing on the validated paths depends on
 // it; tests/test_zz_mxfp4_gpu.py is skipped unless IREE_B200_PENDING_VALIDATION=1.
 //

@@ -16,8 +16,8 @@ extern "C" {
 extern const uint8_t iree_b200_builtin_cda1_start[];
 extern const uint8_t iree_b200_builtin_cda1_end[];
 // The executable of kernels that have not run on a GPU yet (build.py EXPERIMENTAL_UNITS).
-extern const uint8_t iree_b200_builtin_mx_cda1_start[];
-extern const uint8_t iree_b200_builtin_mx_cda1_end[];
+extern const uint8_t iree_b200_builtin_pending_cda1_start[];
+extern const uint8_t iree_b200_builtin_pending_cda1_end[];
 }
 
 namespace {
@@ -58,10 +58,10 @@ struct iree_b200_ops_t {
   iree_b200_executable_cache_t* cache = nullptr;
   iree_b200_executable_t* executable = nullptr;
   // Loaded by the first MX call only (iree_b200_ops_matmul_mxfp4_*).
-  iree_b200_executable_t* mx_executable = nullptr;
+  iree_b200_executable_t* pending_executable = nullptr;
   int32_t mxfp4_generic_export = -1;
   int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
-  std::mutex mx_mutex;
+  std::mutex pending_mutex;
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
   int32_t sm_count = 0;  // device->sm_count, or the caller's for an offline (selection-only) object
@@ -262,7 +262,7 @@ void iree_b200_ops_release(iree_b200_ops_t* ops) {
   }
   iree_b200_buffer_release(ops->arena);
   iree_b200_executable_release(ops->executable);
-  iree_b200_executable_release(ops->mx_executable);
+  iree_b200_executable_release(ops->pending_executable);
   iree_b200_executable_cache_release(ops->cache);
   iree_b200_device_release(ops->device);
   delete ops;
@@ -819,17 +819,19 @@ iree_b200_status_t iree_b200_ops_matmul_bias_host(iree_b200_ops_t* ops, int32_t 
 
 
 //===----------------------------------------------------------------------===//
-// MXFP4 matmul (pending its first GPU run; see kernels/mx_kernels.cu)
+// The second builtin executable: kernels that have not had a GPU run yet (build.py
+// EXPERIMENTAL_UNITS), loaded on first use so nothing validated depends on it.
+// MXFP4 matmul (see kernels/mx_kernels.cu)
 //===----------------------------------------------------------------------===//
 
-static iree_b200_status_t ensure_mx_executable(iree_b200_ops_t* ops) {
-  std::lock_guard<std::mutex> lock(ops->mx_mutex);  // not host_mutex: the host call holds that
-  if (ops->mx_executable) return IREE_B200_STATUS_OK;
+static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
+  std::lock_guard<std::mutex> lock(ops->pending_mutex);  // not host_mutex: the host call holds that
+  if (ops->pending_executable) return IREE_B200_STATUS_OK;
   B200_RETURN_IF_ERROR(iree_b200_executable_cache_prepare_executable(
-      ops->cache, "PTXE", iree_b200_builtin_mx_cda1_start,
-      (size_t)(iree_b200_builtin_mx_cda1_end - iree_b200_builtin_mx_cda1_start),
-      &ops->mx_executable));
-  ops->mxfp4_generic_export = lookup(ops->mx_executable, "iree_b200_matmul_generic_mxfp4_f32");
+      ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
+      (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
+      &ops->pending_executable));
+  ops->mxfp4_generic_export = lookup(ops->pending_executable, "iree_b200_matmul_generic_mxfp4_f32");
   if (ops->mxfp4_generic_export < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND, "the MX executable has no mxfp4 export");
   }
@@ -837,7 +839,7 @@ static iree_b200_status_t ensure_mx_executable(iree_b200_ops_t* ops) {
                                              "iree_b200_mmt4d_generic_f16_f32",
                                              "iree_b200_mmt4d_generic_bf16_f32"};
   for (int i = 0; i < 3; ++i) {
-    ops->mmt4d_generic_exports[i] = lookup(ops->mx_executable, kMmt4dNames[i]);
+    ops->mmt4d_generic_exports[i] = lookup(ops->pending_executable, kMmt4dNames[i]);
     if (ops->mmt4d_generic_exports[i] < 0) {
       return make_status(IREE_B200_STATUS_NOT_FOUND, "the second executable has no %s export",
                          kMmt4dNames[i]);
@@ -890,11 +892,11 @@ iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
   if ((out.buffer->device_ptr + out.offset) % 4) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 result must be 4-byte aligned");
   }
-  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
   const uint32_t grid[3] = {(uint32_t)ceil_div(N, 64), (uint32_t)ceil_div(M, 64), 1};
   const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K, 1u,
                                  flags & IREE_B200_MATMUL_FLAG_ACCUMULATE};
-  B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(cb, ops->mx_executable,
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(cb, ops->pending_executable,
                                                          ops->mxfp4_generic_export, grid, constants,
                                                          5, refs, 5, 0));
   ops->dispatch_count.fetch_add(1);
@@ -917,7 +919,7 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
   for (int i = 0; i < 4; ++i) B200_REQUIRE_ARG(host_in[i] || !bytes[i]);
   B200_REQUIRE_ARG(out || !bytes[4]);
   if (!bytes[4]) return IREE_B200_STATUS_OK;
-  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
   iree_b200_device_t* device = ops->device;
   std::lock_guard<std::mutex> host_lock(ops->host_mutex);
   uint64_t offsets[5], total = 0;
@@ -1036,13 +1038,13 @@ iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_co
                          "mmt4d binding %d is not aligned to its element size", i);
     }
   }
-  B200_RETURN_IF_ERROR(ensure_mx_executable(ops));
+  B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
   const uint32_t grid[3] = {(uint32_t)ceil_div(N1 * N0, 64), (uint32_t)ceil_div(M1 * M0, 64), 1};
   const uint32_t constants[7] = {(uint32_t)M1, (uint32_t)N1, (uint32_t)K1, (uint32_t)M0,
                                  (uint32_t)N0, (uint32_t)K0,
                                  flags & IREE_B200_MATMUL_FLAG_ACCUMULATE};
   B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
-      cb, ops->mx_executable, ops->mmt4d_generic_exports[shape.slot], grid, constants, 7, refs, 3, 0));
+      cb, ops->pending_executable, ops->mmt4d_generic_exports[shape.slot], grid, constants, 7, refs, 3, 0));
   ops->dispatch_count.fetch_add(1);
   return IREE_B200_STATUS_OK;
 }

@@ -228,7 +228,7 @@ def test_pipelined_bias_call_hands_each_block_its_bias_columns(dev, dev_ops, cas
     assert len(seen) == len(got)                       # every block exactly once
 
 
-def test_mx_executable_loads_on_first_use_only(dev, dev_ops):
+def test_pending_executable_loads_on_first_use_only(dev, dev_ops):
     M, N, K = 64, 64, 64
     z = lambda n: np.zeros(n, dtype=np.uint8)
     lhs, ls, rhs, rs = z(M * K // 2), z(M * K // 32), z(N * K // 2), z(N * K // 32)
