@@ -9,7 +9,9 @@ for st in $STAGES; do case $st in
 tests) run pytest 900 python -m pytest tests -m gpu -x -q ;;
 newtests) run pytest_new 600 python -m pytest tests -m gpu -x -q -k "pipelined or decode or selection or full_size" ;;
 pending)  # code written without GPU time: first thing to run next round
-  IREE_B200_PENDING_VALIDATION=1 run pytest_pending 300 python -m pytest tests/test_zz_mxfp4_gpu.py tests/test_zz_pipelined_bias_gpu.py tests/test_zz_mmt4d_gpu.py -m gpu -q ;;
+  IREE_B200_PENDING_VALIDATION=1 run pytest_pending 300 python -m pytest tests/test_zz_mxfp4_gpu.py tests/test_zz_pipelined_bias_gpu.py tests/test_zz_mmt4d_gpu.py -m gpu -q
+  run pending_bench 300 python tools/pending_bench.py --out $O/${TAG}_pending_bench.json
+  run bench_linear_bf16 300 python bench.py --workload linear_bf16 --no-cpu-baseline --steps 100 ;;
 smoke) run smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
 bench)
   run bench_matmul_bf16 400 python bench.py
