@@ -164,14 +164,32 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_host(iree_b200_ops_t* ops,
 // as tests/e2e/matmul/generate_code_mx.py:153-172 states it: lhs [M, K/2] and rhs [N, K/2]
 // are f4E2M1FN packed two per byte (low nibble first), the scales are f8E8M0FNU, one per
 // 32-element block; K must be a multiple of 32. FLAG_ACCUMULATE is the only flag. The
-// kernel lives in a second builtin executable that is loaded by the first call; today it is
-// the SIMT form only (the tcgen05 kind::mxf4 block-scaled form is next).
+// kernels live in a second builtin executable that is loaded by the first call: a SIMT form
+// (this entry point) and a bf16-expansion + tcgen05 form (the _tensor entry point below); the
+// tcgen05 kind::mxf4 block-scaled form is next.
 #define IREE_B200_MX_BLOCK_SIZE 32
 
 IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
     iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
     uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out);
+
+// Tensor-core route of the same op: both operands are expanded to bf16 in |workspace| (two
+// dispatches of iree_b200_matmul_mxfp4_dequant_bf16 — exact for every f4E2M1FN x f8E8M0FNU
+// pair, kernels/mx_kernels.cu), then the bf16 tcgen05 NT GEMM runs on them with the f32
+// accumulate of the plain matmul: bit-identical to the reference whenever the partial sums
+// are exact (they are on the reference generator's inputs), f32 summation error otherwise.
+// Taken when iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K) is non-zero (M, N, K >= 128
+// and the result pitch passes the TMA guard) and |workspace| (256-byte aligned) holds that
+// many bytes; with a NULL workspace or a shape off the route this records the single SIMT
+// dispatch of iree_b200_ops_record_matmul_mxfp4. The host-buffer form below makes the same
+// choice with a workspace of its own.
+IREE_B200_API uint64_t iree_b200_ops_matmul_mxfp4_workspace_size(int64_t M, int64_t N, int64_t K);
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_mxfp4_tensor(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* command_buffer, int64_t M, int64_t N,
+    int64_t K, uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales,
+    iree_b200_buffer_ref_t workspace, iree_b200_buffer_ref_t out);
 
 IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(
     iree_b200_ops_t* ops, int64_t M, int64_t N, int64_t K, uint32_t flags, const void* lhs,

@@ -122,3 +122,48 @@ extern "C" __global__ void __launch_bounds__(256)
     }
   }
 }
+
+// ---- MXFP4 -> bf16 operand expansion (first dispatch of the tensor-core MX path) ------------
+//
+// out[r, k] = bf16(f32(f4[r, k]) * 2^(scale[r, k / 32] - 127)). The conversion is EXACT for
+// every (code, scale) pair: an f4E2M1FN value has at most two significand bits and bf16 has
+// the exponent range of f32, including its subnormals (the smallest product, 0.5 * 2^-127 =
+// 2^-128, is f32 bit 21), so the low 16 bits of the f32 product are always zero and the
+// truncation below is the identity; overflow (>= 2^128) is +-inf and a 0xFF scale is NaN in
+// both formats. The ops layer then runs the validated bf16 tcgen05 NT GEMM on the expanded
+// operands (f32 accumulate): bit-identical to the reference whenever the partial sums are
+// exact — which they are on the reference generator's inputs (values <= 6 * 8, granularity
+// 0.25) — and within f32 summation error otherwise, the bf16 GEMM's own bar.
+//
+// HBM-bound: reads 17/32 byte and writes 2 bytes per element. One thread expands 8 elements
+// (4 packed bytes -> one 16-byte store).
+//
+// ABI: bindings packed [rows, K/2] u8, scales [rows, K/32] u8 (read-only), out [rows, K] bf16
+// (16-byte aligned: the ops layer owns this buffer); constants rows, K (K % 32 == 0).
+// workgroup_size = [256,1,1], workgroup count = [ceil(rows * K / 8 / 256), 1, 1].
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_matmul_mxfp4_dequant_bf16(const uint8_t* __restrict__ packed,
+                                        const uint8_t* __restrict__ scales,
+                                        uint16_t* __restrict__ out, int rows, int K) {
+  const int parts = K / 8;
+  const long long gid = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (gid >= (long long)rows * parts) return;
+  const int row = (int)(gid / parts), k = (int)(gid % parts) * 8;
+  const float scale = f8e8m0fnu_to_f32(scales[(size_t)row * (K / kBlock) + k / kBlock]);
+  const uint8_t* p = packed + ((size_t)row * K + k) / 2;
+  const uint32_t word =
+      (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+  uint32_t pairs[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t lo = __float_as_uint(__fmul_rn(f4e2m1fn_to_f32((word >> (8 * i)) & 0xFu), scale));
+    const uint32_t hi =
+        __float_as_uint(__fmul_rn(f4e2m1fn_to_f32((word >> (8 * i + 4)) & 0xFu), scale));
+    pairs[i] = (lo >> 16) | (hi & 0xFFFF0000u);
+  }
+  uint32_t* dst = reinterpret_cast<uint32_t*>(out + (size_t)row * K + k);
+  dst[0] = pairs[0];
+  dst[1] = pairs[1];
+  dst[2] = pairs[2];
+  dst[3] = pairs[3];
+}

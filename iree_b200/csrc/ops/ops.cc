@@ -60,6 +60,7 @@ struct iree_b200_ops_t {
   // Loaded by the first MX call only (iree_b200_ops_matmul_mxfp4_*).
   iree_b200_executable_t* pending_executable = nullptr;
   int32_t mxfp4_generic_export = -1;
+  int32_t mxfp4_dequant_export = -1;
   int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
   std::mutex pending_mutex;
   std::atomic<uint64_t> dispatch_count{0};
@@ -832,7 +833,9 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
       &ops->pending_executable));
   ops->mxfp4_generic_export = lookup(ops->pending_executable, "iree_b200_matmul_generic_mxfp4_f32");
-  if (ops->mxfp4_generic_export < 0) {
+  ops->mxfp4_dequant_export =
+      lookup(ops->pending_executable, "iree_b200_matmul_mxfp4_dequant_bf16");
+  if (ops->mxfp4_generic_export < 0 || ops->mxfp4_dequant_export < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND, "the MX executable has no mxfp4 export");
   }
   static const char* const kMmt4dNames[3] = {"iree_b200_mmt4d_generic_i8_i32",
@@ -848,10 +851,23 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   return IREE_B200_STATUS_OK;
 }
 
-iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
+// The tensor-core route (expand both operands to bf16, then the bf16 tcgen05 NT GEMM) pays
+// for shapes that fill at least one 128x128 tile and pass the GEMM's TMA guards; smaller or
+// ragged shapes stay on the single SIMT dispatch.
+static bool mxfp4_tensor_route(int64_t M, int64_t N, int64_t K) {
+  return M >= 128 && N >= 128 && K >= 128 && (N * 4) % 16 == 0;
+}
+
+uint64_t iree_b200_ops_matmul_mxfp4_workspace_size(int64_t M, int64_t N, int64_t K) {
+  if (M < 0 || N < 0 || K < 0 || !mxfp4_tensor_route(M, N, K)) return 0;
+  return ((uint64_t)M * K * 2 + 255) / 256 * 256 + (uint64_t)N * K * 2;
+}
+
+static iree_b200_status_t record_matmul_mxfp4_impl(
     iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
     uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
-    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out) {
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out,
+    const iree_b200_buffer_ref_t* workspace) {
   B200_REQUIRE_ARG(ops && cb);
   B200_RETURN_IF_ERROR(require_device(ops));
   if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
@@ -893,6 +909,48 @@ iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 result must be 4-byte aligned");
   }
   B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
+  const uint64_t ws_need = iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
+  if (workspace && workspace->buffer && ws_need) {
+    const uint64_t total = workspace->buffer->byte_length;
+    if (workspace->offset > total) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "MXFP4 workspace offset out of range");
+    }
+    const uint64_t length =
+        workspace->length == UINT64_MAX ? total - workspace->offset : workspace->length;
+    if (length < ws_need || length > total - workspace->offset ||
+        (workspace->buffer->device_ptr + workspace->offset) % 256) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "MXFP4 workspace must be 256-byte aligned and hold %llu bytes "
+                         "(iree_b200_ops_matmul_mxfp4_workspace_size)",
+                         (unsigned long long)ws_need);
+    }
+    // Expand lhs and rhs to bf16 (exact, kernels/mx_kernels.cu), then the bf16 tcgen05 GEMM.
+    const uint64_t a_bytes = (uint64_t)M * K * 2, b_bytes = (uint64_t)N * K * 2;
+    const iree_b200_buffer_ref_t a_ws{workspace->buffer, workspace->offset, a_bytes};
+    const iree_b200_buffer_ref_t b_ws{workspace->buffer,
+                                      workspace->offset + (a_bytes + 255) / 256 * 256, b_bytes};
+    const struct {
+      iree_b200_buffer_ref_t packed, scales, expanded;
+      int64_t rows;
+    } sides[2] = {{lhs, lhs_scales, a_ws, M}, {rhs, rhs_scales, b_ws, N}};
+    for (const auto& side : sides) {
+      const int64_t blocks = ceil_div(side.rows * (K / 8), 256);
+      if (blocks > INT32_MAX) {
+        return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "MXFP4 expansion grid out of range");
+      }
+      const uint32_t grid[3] = {(uint32_t)blocks, 1, 1};
+      const uint32_t constants[2] = {(uint32_t)side.rows, (uint32_t)K};
+      const iree_b200_buffer_ref_t bindings[3] = {side.packed, side.scales, side.expanded};
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+          cb, ops->pending_executable, ops->mxfp4_dequant_export, grid, constants, 2, bindings, 3, 0));
+      ops->dispatch_count.fetch_add(1);
+    }
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
+    return iree_b200_ops_record_matmul(
+        ops, cb, IREE_B200_ELEMENT_TYPE_BF16, 1, M, N, K,
+        IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS | (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE), a_ws, b_ws,
+        out);
+  }
   const uint32_t grid[3] = {(uint32_t)ceil_div(N, 64), (uint32_t)ceil_div(M, 64), 1};
   const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K, 1u,
                                  flags & IREE_B200_MATMUL_FLAG_ACCUMULATE};
@@ -901,6 +959,23 @@ iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
                                                          5, refs, 5, 0));
   ops->dispatch_count.fetch_add(1);
   return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_record_matmul_mxfp4(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
+    uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t out) {
+  return record_matmul_mxfp4_impl(ops, cb, M, N, K, flags, lhs, lhs_scales, rhs, rhs_scales, out,
+                                  nullptr);
+}
+
+iree_b200_status_t iree_b200_ops_record_matmul_mxfp4_tensor(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int64_t M, int64_t N, int64_t K,
+    uint32_t flags, iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t lhs_scales,
+    iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales, iree_b200_buffer_ref_t workspace,
+    iree_b200_buffer_ref_t out) {
+  return record_matmul_mxfp4_impl(ops, cb, M, N, K, flags, lhs, lhs_scales, rhs, rhs_scales, out,
+                                  &workspace);
 }
 
 iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t M, int64_t N,
@@ -927,6 +1002,8 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
+  const uint64_t ws_offset = total, ws_bytes = iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
+  total += ws_bytes;
   iree_b200_command_buffer_t* cb = nullptr;
   auto run = [&]() -> iree_b200_status_t {
     B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
@@ -934,6 +1011,9 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
       return bytes[i] ? iree_b200_buffer_ref_t{ops->arena, offsets[i], bytes[i]}
                       : iree_b200_buffer_ref_t{nullptr, 0, 0};
     };
+    const iree_b200_buffer_ref_t workspace =
+        ws_bytes ? iree_b200_buffer_ref_t{ops->arena, ws_offset, ws_bytes}
+                 : iree_b200_buffer_ref_t{nullptr, 0, 0};
     for (int i = 0; i < 4; ++i) {
       if (!bytes[i]) continue;
       B200_RETURN_IF_ERROR(
@@ -944,8 +1024,8 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     }
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
-    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul_mxfp4(ops, cb, M, N, K, flags, ref(0), ref(1),
-                                                           ref(2), ref(3), ref(4)));
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul_mxfp4_tensor(
+        ops, cb, M, N, K, flags, ref(0), ref(1), ref(2), ref(3), workspace, ref(4)));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
     B200_RETURN_IF_ERROR(
         iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));

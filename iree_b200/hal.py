@@ -180,6 +180,9 @@ _STATUS_FUNCS = {
                                        c_uint32, c_void_p, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_record_matmul_mxfp4": [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_uint32,
                                           BufferRef, BufferRef, BufferRef, BufferRef, BufferRef],
+    "iree_b200_ops_record_matmul_mxfp4_tensor": [c_void_p, c_void_p, c_int64, c_int64, c_int64,
+                                                 c_uint32, BufferRef, BufferRef, BufferRef,
+                                                 BufferRef, BufferRef, BufferRef],
     "iree_b200_ops_matmul_mxfp4_host": [c_void_p, c_int64, c_int64, c_int64, c_uint32, c_void_p,
                                         c_void_p, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_record_mmt4d": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64, c_int32,
@@ -227,6 +230,7 @@ _OTHER_FUNCS = {
                                                       POINTER(c_int32)]),
     "iree_b200_ops_builtin_executable_data": (c_void_p, [POINTER(c_size_t)]),
     "iree_b200_ops_release": (None, [c_void_p]),
+    "iree_b200_ops_matmul_mxfp4_workspace_size": (c_uint64, [c_int64, c_int64, c_int64]),
     "iree_b200_ops_executable": (c_void_p, [c_void_p]),
     "iree_b200_ops_dispatch_count": (c_uint64, [c_void_p]),
 }
@@ -656,6 +660,18 @@ class Ops:
         """MXFP4 matmul (pending its first GPU run; include/iree_b200_ops.h)."""
         check(lib().iree_b200_ops_record_matmul_mxfp4(self._h, cb._h, M, N, K, flags, lhs,
                                                       lhs_scales, rhs, rhs_scales, out))
+
+    @staticmethod
+    def matmul_mxfp4_workspace_size(M, N, K) -> int:
+        return lib().iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K)
+
+    def record_matmul_mxfp4_tensor(self, cb: CommandBuffer, M, N, K, lhs: BufferRef,
+                                   lhs_scales: BufferRef, rhs: BufferRef, rhs_scales: BufferRef,
+                                   workspace: BufferRef, out: BufferRef, flags=0):
+        """MXFP4 via bf16 expansion + the tcgen05 GEMM (include/iree_b200_ops.h)."""
+        check(lib().iree_b200_ops_record_matmul_mxfp4_tensor(
+            self._h, cb._h, M, N, K, flags, lhs, lhs_scales, rhs, rhs_scales,
+            workspace if workspace is not None else NULL_REF, out))
 
     def matmul_mxfp4_host(self, M, N, K, lhs_ptr: int, lhs_scales_ptr: int, rhs_ptr: int,
                           rhs_scales_ptr: int, out_ptr: int, flags=0):

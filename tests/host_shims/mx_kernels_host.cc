@@ -30,6 +30,11 @@ static inline float __uint_as_float(uint32_t u) {
 // -ffp-contract=off on the command line keeps these two roundings apart, like the PTX.
 static inline float __fadd_rn(float a, float b) { return a + b; }
 static inline float __fmul_rn(float a, float b) { return a * b; }
+static inline uint32_t __float_as_uint(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  return u;
+}
 #define __syncthreads() pthread_barrier_wait(&block_barrier)
 
 #include "../../iree_b200/csrc/kernels/mx_kernels.cu"

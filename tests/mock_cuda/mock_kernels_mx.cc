@@ -14,3 +14,13 @@ extern "C" __attribute__((visibility("default"))) int mock_run_iree_b200_matmul_
   });
   return 0;
 }
+
+extern "C" __attribute__((visibility("default"))) int mock_run_iree_b200_matmul_mxfp4_dequant_bf16(
+    const unsigned grid[3], const unsigned block[3], void** p) {
+  if (block[0] != 256) return 1;
+  run_grid(grid, [&] {
+    iree_b200_matmul_mxfp4_dequant_bf16(arg<const uint8_t*>(p, 0), arg<const uint8_t*>(p, 1),
+                                        arg<uint16_t*>(p, 2), arg<int>(p, 3), arg<int>(p, 4));
+  });
+  return 0;
+}

@@ -502,3 +502,72 @@ def test_mmt4d_edge_cases_and_guards(dev, dev_ops):
     with pytest.raises(H.Status):       # lhs at an odd byte: not a bf16 element boundary
         dev_ops.record_mmt4d(cb, t, 2, 1, 4, M0, N0, K0, lhs_b.ref(63, l4.nbytes), rhs_b.ref(),
                              out_b.ref())
+
+
+@needs_kernels
+def test_mxfp4_expansion_is_exact_for_every_code_and_scale(dev, dev_ops):
+    """The tensor-core MX route, first half: iree_b200_matmul_mxfp4_dequant_bf16 run on the
+    host. One row per scale byte (all 256), every f4 code in every block: the bf16 it writes
+    equals the oracle's f32 decode exactly (NaN for scale 0xFF), and the host call's launch
+    sequence is expand(lhs), expand(rhs), bf16 tcgen05 NT GEMM (logged only: no host form)."""
+    import oracle
+    M, N, K = 256, 128, 128
+    rng = np.random.Generator(np.random.PCG64(11))
+    lhs = rng.integers(0, 256, (M, K // 2), dtype=np.uint8)
+    lhs[:, :8] = np.arange(8, dtype=np.uint8) * 0x22 + 0x10     # codes 0..15 in the first block
+    ls = np.repeat(np.arange(256, dtype=np.uint8)[:, None], K // 32, axis=1)
+    rhs = rng.integers(0, 256, (N, K // 2), dtype=np.uint8)
+    rs = rng.integers(120, 135, (N, K // 32), dtype=np.uint8)
+    out = np.zeros((M, N), dtype=np.float32)
+    assert dev_ops.matmul_mxfp4_workspace_size(M, N, K) == M * K * 2 + N * K * 2
+    assert dev_ops.matmul_mxfp4_workspace_size(127, N, K) == 0      # below one tile: SIMT
+    assert dev_ops.matmul_mxfp4_workspace_size(M, 130, K) == 0      # result pitch 520 B
+    launches()
+    before = dev_ops.dispatch_count
+    dev_ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                              rs.ctypes.data, out.ctypes.data)
+    assert dev_ops.dispatch_count - before == 3
+    got = launch_args()
+    assert [g[0] for g in got] == ["iree_b200_matmul_mxfp4_dequant_bf16"] * 2 + \
+        ["iree_b200_matmul_nt_bf16_f32_1cta"]
+    (_, (_, _, a_ws, rows_a)), (_, (_, _, b_ws, rows_b)), (_, (a_gemm, b_gemm, _, m_gemm)) = got
+    assert (rows_a, rows_b, m_gemm) == (M, N, M) and (a_gemm, b_gemm) == (a_ws, b_ws)
+    assert b_ws == a_ws + M * K * 2 and a_ws % 256 == 0
+    for ptr, packed, scales, rows in ((a_ws, lhs, ls, M), (b_ws, rhs, rs, N)):
+        bits = np.ctypeslib.as_array(ctypes.cast(ptr, ctypes.POINTER(ctypes.c_uint16)), (rows, K))
+        want = oracle.mx_decode(packed, scales)                  # f32 [rows, K]
+        have = oracle.to_f32("bf16", bits.copy())
+        assert np.array_equal(have, want, equal_nan=True)
+        assert np.isnan(have[scales[:, 0] == 0xFF]).all() if (scales == 0xFF).any() else True
+    # Signed zeros and the subnormal end survive: row 0 has scale 2^-127.
+    row0 = np.ctypeslib.as_array(ctypes.cast(a_ws, ctypes.POINTER(ctypes.c_uint16)), (M, K))[0]
+    assert set(np.unique(row0[:16])) >= {0x0000, 0x8000, 0x0020}     # +0, -0, 0.5 * 2^-127
+
+
+@needs_kernels
+def test_mxfp4_tensor_route_recorded_form_and_guards(dev, dev_ops):
+    M, N, K = 128, 128, 128
+    z = lambda n: dev.allocate(n)
+    lhs, ls, rhs, rs = z(M * K // 2), z(M * K // 32), z(N * K // 2), z(N * K // 32)
+    out = z(M * N * 4)
+    need = dev_ops.matmul_mxfp4_workspace_size(M, N, K)
+    ws = z(need + 256)
+    launches()
+    cb = H.CommandBuffer(dev).begin()
+    dev_ops.record_matmul_mxfp4_tensor(cb, M, N, K, lhs.ref(), ls.ref(), rhs.ref(), rs.ref(),
+                                       ws.ref(256, need), out.ref(), flags=H.MATMUL_ACCUMULATE)
+    # No workspace: the single SIMT dispatch.
+    dev_ops.record_matmul_mxfp4_tensor(cb, M, N, K, lhs.ref(), ls.ref(), rhs.ref(), rs.ref(),
+                                       None, out.ref())
+    with pytest.raises(H.Status):       # workspace too small
+        dev_ops.record_matmul_mxfp4_tensor(cb, M, N, K, lhs.ref(), ls.ref(), rhs.ref(), rs.ref(),
+                                           ws.ref(0, need - 2), out.ref())
+    with pytest.raises(H.Status):       # workspace not 256-byte aligned
+        dev_ops.record_matmul_mxfp4_tensor(cb, M, N, K, lhs.ref(), ls.ref(), rhs.ref(), rs.ref(),
+                                           ws.ref(16, need), out.ref())
+    cb.end()
+    dev.execute(cb)
+    dev.wait_idle()
+    names = [l[0] for l in launches()]
+    assert names == ["iree_b200_matmul_mxfp4_dequant_bf16"] * 2 + \
+        ["iree_b200_matmul_nt_bf16_f32_1cta", "iree_b200_matmul_generic_mxfp4_f32"]

@@ -29,7 +29,9 @@ def _inputs(M, K, N, accumulate):
 
 
 @pytest.mark.parametrize("shape", [(1, 32, 1), (3, 64, 5), (70, 96, 50), (64, 256, 130),
-                                   (512, 1024, 384), (1000, 32, 8)], ids=str)
+                                   (512, 1024, 384), (1000, 32, 8),
+                                   # tensor-core route (bf16 expansion + tcgen05 GEMM)
+                                   (128, 128, 128), (1000, 512, 264), (2048, 2048, 2048)], ids=str)
 @pytest.mark.parametrize("accumulate", [False, True], ids=["", "acc"])
 def test_mxfp4_matmul_vs_oracle(ops, shape, accumulate):
     M, K, N = shape
@@ -39,7 +41,8 @@ def test_mxfp4_matmul_vs_oracle(ops, shape, accumulate):
     ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
                           rs.ctypes.data, out.ctypes.data,
                           flags=H.MATMUL_ACCUMULATE if accumulate else 0)
-    assert ops.dispatch_count - before == 1
+    # Shapes on the tensor-core route expand both operands to bf16 first (3 dispatches).
+    assert ops.dispatch_count - before == (3 if ops.matmul_mxfp4_workspace_size(M, N, K) else 1)
     assert np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc))
 
 
@@ -63,3 +66,20 @@ def test_mxfp4_special_scales_and_guards(ops):
     out = np.full((M, N), 5, dtype=np.float32)
     ops.matmul_mxfp4_host(M, N, 0, 0, 0, 0, 0, out.ctypes.data)
     assert (out == 0).all()
+
+
+def test_mxfp4_tensor_route_handles_special_scales(ops):
+    """NaN scales, the subnormal end (2^-127) and overflow through the bf16 expansion and the
+    tcgen05 GEMM: same values as the oracle (NaN where the oracle has NaN)."""
+    M, K, N = 128, 128, 128
+    lhs, ls, rhs, rs, _ = _inputs(M, K, N, False)
+    ls[2, 1] = 0xFF
+    rs[5, 0] = 0
+    ls[7, :] = 1          # 2^-126: products with rs[5] land deep in the f32 subnormals
+    out = np.zeros((M, N), dtype=np.float32)
+    ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                          rs.ctypes.data, out.ctypes.data)
+    want = oracle.matmul_mxfp4(lhs, ls, rhs, rs)
+    assert np.isnan(out[2]).all() and np.array_equal(np.isnan(out), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.allclose(out[ok], want[ok], rtol=1e-6, atol=1e-30)

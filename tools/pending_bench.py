@@ -1,5 +1,6 @@
 """Times the kernels that have not had a GPU run yet (the on-demand second executable: the
-MXFP4 and mmt4d SIMT kernels) after checking each result against the oracle, so the first GPU
+mmt4d SIMT kernels, the MXFP4 SIMT kernel and the MXFP4 bf16-expansion + tcgen05 route) after
+checking each result against the oracle, so the first GPU
 call of the next round yields parity AND a number. CUDA events on the dispatch stream, after
 warm-up; one JSON line per kernel. Not part of bench.py: nothing here is a headline metric.
 
@@ -79,7 +80,21 @@ def main():
                              "ms": ms, "tflops": 2.0 * size ** 3 / ms / 1e9})
             print(json.dumps(rows[-1]), flush=True)
 
-    # ---- MXFP4 ------------------------------------------------------------------------------
+    # ---- MXFP4: the SIMT dispatch and the bf16-expansion + tcgen05 route -----------------------
+    def _mx_row(route, size, check, cb, bufs, out, lhs, ls, rhs, rs):
+        name = "matmul_mxfp4_" + route
+        if check:
+            dev.execute(cb)
+            dev.wait_idle()
+            dev.d2h(bufs[4], out.ctypes.data, out.nbytes)
+            ok = bool(np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs)))
+            rows.append({"kernel": name, "size": size, "bit_exact_vs_oracle": ok})
+        else:
+            ms = _time(torch, stream, dev, cb, args.iters)
+            rows.append({"kernel": name, "size": size, "ms": ms,
+                         "tflops": 2.0 * size ** 3 / ms / 1e9})
+        print(json.dumps(rows[-1]), flush=True)
+
     for size, check in ((args.check_size, True), (args.size, False)):
         lhs = oracle.generate_random_matrix("u8", (size, size // 2), 1)
         ls = oracle.generate_random_matrix("f8e8m0fnu", (size, size // 32), 2)
@@ -87,21 +102,21 @@ def main():
         rs = oracle.generate_random_matrix("f8e8m0fnu", (size, size // 32), 4)
         out = np.zeros((size, size), dtype=np.float32)
         bufs = [upload(a) for a in (lhs, ls, rhs, rs, out)]
-        cb = hal.CommandBuffer(dev).begin()
-        ops.record_matmul_mxfp4(cb, size, size, size, *[b.ref() for b in bufs])
-        cb.end()
-        if check:
-            dev.execute(cb)
-            dev.wait_idle()
-            dev.d2h(bufs[4], out.ctypes.data, out.nbytes)
-            ok = bool(np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs)))
-            rows.append({"kernel": "matmul_generic_mxfp4_f32", "size": size,
-                         "bit_exact_vs_oracle": ok})
-        else:
-            ms = _time(torch, stream, dev, cb, args.iters)
-            rows.append({"kernel": "matmul_generic_mxfp4_f32", "size": size, "ms": ms,
-                         "tflops": 2.0 * size ** 3 / ms / 1e9})
-        print(json.dumps(rows[-1]), flush=True)
+        for route in ("simt", "tensor"):
+            need = ops.matmul_mxfp4_workspace_size(size, size, size)
+            if route == "tensor" and not need:
+                continue
+            if route == "simt" and not check and size > 4096:
+                continue                        # the SIMT kernel is a correctness path
+            cb = hal.CommandBuffer(dev).begin()
+            refs = [b.ref() for b in bufs]
+            if route == "tensor":
+                ws = dev.allocate(need)
+                ops.record_matmul_mxfp4_tensor(cb, size, size, size, *refs[:4], ws.ref(), refs[4])
+            else:
+                ops.record_matmul_mxfp4(cb, size, size, size, *refs)
+            cb.end()
+            _mx_row(route, size, check, cb, bufs, out, lhs, ls, rhs, rs)
 
     if args.out:
         with open(args.out, "w") as f:
