@@ -214,7 +214,23 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_record_mmt4d(
     int64_t M1, int64_t N1, int64_t K1, int32_t M0, int32_t N0, int32_t K0, uint32_t flags,
     iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out);
 
-// Host-buffer form (upload, one dispatch, download).
+// Tensor-core route: lhs, rhs (and with FLAG_ACCUMULATE the accumulator) are unpacked to
+// row-major in |workspace| (iree_b200_mmt4d_relayout_b{8,16,32}: pure data movement), the
+// tcgen05 NT GEMM runs on them, and the result is packed back into [M1, N1, M0, N0] tiles —
+// 4 or 5 dispatches. Taken when iree_b200_ops_mmt4d_workspace_size(...) is non-zero (logical
+// M, N, K >= 128 and the GEMM's TMA guards hold) and |workspace| (256-byte aligned) holds
+// that many bytes; otherwise the single SIMT dispatch of iree_b200_ops_record_mmt4d. Same
+// result bits as the plain matmul of the unpacked operands.
+IREE_B200_API uint64_t iree_b200_ops_mmt4d_workspace_size(int32_t element_type, int64_t M1,
+                                                          int64_t N1, int64_t K1, int32_t M0,
+                                                          int32_t N0, int32_t K0);
+IREE_B200_API iree_b200_status_t iree_b200_ops_record_mmt4d_tensor(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* command_buffer, int32_t element_type,
+    int64_t M1, int64_t N1, int64_t K1, int32_t M0, int32_t N0, int32_t K0, uint32_t flags,
+    iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t workspace,
+    iree_b200_buffer_ref_t out);
+
+// Host-buffer form (upload, dispatch(es) — tensor-core route when the shape allows —, download).
 IREE_B200_API iree_b200_status_t iree_b200_ops_mmt4d_host(
     iree_b200_ops_t* ops, int32_t element_type, int64_t M1, int64_t N1, int64_t K1, int32_t M0,
     int32_t N0, int32_t K0, uint32_t flags, const void* lhs, const void* rhs, void* out);

@@ -129,3 +129,50 @@ extern "C" __global__ void __launch_bounds__(256)
                                    int K0, int flags) {
   mmt4d_generic_body<int8_t, int32_t>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
 }
+
+// ---- tiled <-> row-major relayout (the dispatches around the tensor-core mmt4d route) -------
+//
+// The tcgen05 GEMM consumes dense row-major operands; until a kernel reads tiles directly
+//  the ops layer unpacks lhs / rhs (and the accumulator) into a workspace,
+// runs the validated NT GEMM, and packs the result back. Pure data movement, so exact.
+//   tiled [R1, C1, R0, C0]  <->  row-major [R1*R0, C1*C0]
+// One thread per element, consecutive threads along the row-major row (coalesced on that
+// side; the tiled side is coalesced within a tile row of C0 elements). HBM-bound: one read and
+// one write per element.
+//
+// ABI: bindings src (read-only), dst; constants R1, C1, R0, C0, to_tiled (0: tiled ->
+// row-major, 1: row-major -> tiled). workgroup_size = [256,1,1], workgroup count =
+// [ceil(C1*C0/256), min(R1*R0, 65535), 1] (rows are strided over grid.y).
+template <typename T>
+__device__ __forceinline__ void mmt4d_relayout_body(const T* __restrict__ src, T* __restrict__ dst,
+                                                    int R1, int C1, int R0, int C0, int to_tiled) {
+  const int rows = R1 * R0, cols = C1 * C0;
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= cols) return;
+  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+    const size_t tiled = packed_at(r, c, C1, R0, C0), flat = (size_t)r * cols + c;
+    if (to_tiled) {
+      dst[tiled] = src[flat];
+    } else {
+      dst[flat] = src[tiled];
+    }
+  }
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_relayout_b8(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int R1,
+                                int C1, int R0, int C0, int to_tiled) {
+  mmt4d_relayout_body<uint8_t>(src, dst, R1, C1, R0, C0, to_tiled);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_relayout_b16(const uint16_t* __restrict__ src, uint16_t* __restrict__ dst,
+                                 int R1, int C1, int R0, int C0, int to_tiled) {
+  mmt4d_relayout_body<uint16_t>(src, dst, R1, C1, R0, C0, to_tiled);
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_relayout_b32(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst,
+                                 int R1, int C1, int R0, int C0, int to_tiled) {
+  mmt4d_relayout_body<uint32_t>(src, dst, R1, C1, R0, C0, to_tiled);
+}

@@ -62,6 +62,7 @@ struct iree_b200_ops_t {
   int32_t mxfp4_generic_export = -1;
   int32_t mxfp4_dequant_export = -1;
   int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
+  int32_t mmt4d_relayout_exports[3] = {-1, -1, -1};  // 1-, 2-, 4-byte elements
   std::mutex pending_mutex;
   std::atomic<uint64_t> dispatch_count{0};
   int32_t reserved_sms = 0;
@@ -848,6 +849,16 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
                          kMmt4dNames[i]);
     }
   }
+  static const char* const kRelayoutNames[3] = {"iree_b200_mmt4d_relayout_b8",
+                                                "iree_b200_mmt4d_relayout_b16",
+                                                "iree_b200_mmt4d_relayout_b32"};
+  for (int i = 0; i < 3; ++i) {
+    ops->mmt4d_relayout_exports[i] = lookup(ops->pending_executable, kRelayoutNames[i]);
+    if (ops->mmt4d_relayout_exports[i] < 0) {
+      return make_status(IREE_B200_STATUS_NOT_FOUND, "the second executable has no %s export",
+                         kRelayoutNames[i]);
+    }
+  }
   return IREE_B200_STATUS_OK;
 }
 
@@ -1084,11 +1095,45 @@ iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int
 
 }  // namespace
 
-iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
-                                              int32_t element_type, int64_t M1, int64_t N1,
-                                              int64_t K1, int32_t M0, int32_t N0, int32_t K0,
-                                              uint32_t flags, iree_b200_buffer_ref_t lhs,
-                                              iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out) {
+// The tensor-core route: unpack lhs / rhs (and the accumulator) to row-major in a workspace,
+// run the tcgen05 NT GEMM, pack the result back into tiles. Worth it once the logical shape
+// fills a 128x128 tile and passes the GEMM's TMA guards.
+static uint64_t round256(uint64_t v) { return (v + 255) / 256 * 256; }
+
+uint64_t iree_b200_ops_mmt4d_workspace_size(int32_t element_type, int64_t M1, int64_t N1, int64_t K1,
+                                            int32_t M0, int32_t N0, int32_t K0) {
+  Mmt4dShape shape;
+  if (check_mmt4d(element_type, M1, N1, K1, M0, N0, K0, 0, &shape) != IREE_B200_STATUS_OK) return 0;
+  const int64_t M = M1 * M0, N = N1 * N0, K = K1 * K0;
+  const int64_t es = (int64_t)matmul_elem_size(element_type);
+  if (M < 128 || N < 128 || K < 128 || (K * es) % 16 || (N * 4) % 16) return 0;
+  return round256(shape.bytes[0]) + round256(shape.bytes[1]) + shape.bytes[2];
+}
+
+static iree_b200_status_t record_mmt4d_relayout(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                                uint64_t elem_size, int64_t R1, int64_t C1,
+                                                int32_t R0, int32_t C0, bool to_tiled,
+                                                iree_b200_buffer_ref_t src,
+                                                iree_b200_buffer_ref_t dst) {
+  const int64_t rows = R1 * R0, cols = C1 * C0;
+  const uint32_t grid[3] = {(uint32_t)ceil_div(cols, 256), (uint32_t)std::min<int64_t>(rows, 592), 1};
+  const uint32_t constants[5] = {(uint32_t)R1, (uint32_t)C1, (uint32_t)R0, (uint32_t)C0,
+                                 to_tiled ? 1u : 0u};
+  const iree_b200_buffer_ref_t bindings[2] = {src, dst};
+  const int slot = elem_size == 1 ? 0 : elem_size == 2 ? 1 : 2;
+  B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+      cb, ops->pending_executable, ops->mmt4d_relayout_exports[slot], grid, constants, 5, bindings, 2,
+      0));
+  ops->dispatch_count.fetch_add(1);
+  return IREE_B200_STATUS_OK;
+}
+
+static iree_b200_status_t record_mmt4d_impl(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                            int32_t element_type, int64_t M1, int64_t N1,
+                                            int64_t K1, int32_t M0, int32_t N0, int32_t K0,
+                                            uint32_t flags, iree_b200_buffer_ref_t lhs,
+                                            iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out,
+                                            const iree_b200_buffer_ref_t* workspace) {
   B200_REQUIRE_ARG(ops && cb);
   B200_RETURN_IF_ERROR(require_device(ops));
   Mmt4dShape shape;
@@ -1119,6 +1164,42 @@ iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_co
     }
   }
   B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
+  const uint64_t ws_need =
+      iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
+  if (workspace && workspace->buffer && ws_need) {
+    const uint64_t total = workspace->buffer->byte_length;
+    if (workspace->offset > total) {
+      return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "mmt4d workspace offset out of range");
+    }
+    const uint64_t length =
+        workspace->length == UINT64_MAX ? total - workspace->offset : workspace->length;
+    if (length < ws_need || length > total - workspace->offset ||
+        (workspace->buffer->device_ptr + workspace->offset) % 256) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "mmt4d workspace must be 256-byte aligned and hold %llu bytes "
+                         "(iree_b200_ops_mmt4d_workspace_size)",
+                         (unsigned long long)ws_need);
+    }
+    const uint64_t es = matmul_elem_size(element_type);
+    const uint64_t a_at = workspace->offset, b_at = a_at + round256(shape.bytes[0]),
+                   c_at = b_at + round256(shape.bytes[1]);
+    const iree_b200_buffer_ref_t a_rm{workspace->buffer, a_at, shape.bytes[0]};
+    const iree_b200_buffer_ref_t b_rm{workspace->buffer, b_at, shape.bytes[1]};
+    const iree_b200_buffer_ref_t c_rm{workspace->buffer, c_at, shape.bytes[2]};
+    const bool accumulate = (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) != 0;
+    B200_RETURN_IF_ERROR(record_mmt4d_relayout(ops, cb, es, M1, K1, M0, K0, false, lhs, a_rm));
+    B200_RETURN_IF_ERROR(record_mmt4d_relayout(ops, cb, es, N1, K1, N0, K0, false, rhs, b_rm));
+    if (accumulate) {
+      B200_RETURN_IF_ERROR(record_mmt4d_relayout(ops, cb, 4, M1, N1, M0, N0, false, out, c_rm));
+    }
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_matmul(
+        ops, cb, element_type, 1, M1 * M0, N1 * N0, K1 * K0,
+        IREE_B200_MATMUL_FLAG_TRANSPOSE_RHS | (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE), a_rm, b_rm,
+        c_rm));
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
+    return record_mmt4d_relayout(ops, cb, 4, M1, N1, M0, N0, true, c_rm, out);
+  }
   const uint32_t grid[3] = {(uint32_t)ceil_div(N1 * N0, 64), (uint32_t)ceil_div(M1 * M0, 64), 1};
   const uint32_t constants[7] = {(uint32_t)M1, (uint32_t)N1, (uint32_t)K1, (uint32_t)M0,
                                  (uint32_t)N0, (uint32_t)K0,
@@ -1127,6 +1208,24 @@ iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_co
       cb, ops->pending_executable, ops->mmt4d_generic_exports[shape.slot], grid, constants, 7, refs, 3, 0));
   ops->dispatch_count.fetch_add(1);
   return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_ops_record_mmt4d(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
+                                              int32_t element_type, int64_t M1, int64_t N1,
+                                              int64_t K1, int32_t M0, int32_t N0, int32_t K0,
+                                              uint32_t flags, iree_b200_buffer_ref_t lhs,
+                                              iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t out) {
+  return record_mmt4d_impl(ops, cb, element_type, M1, N1, K1, M0, N0, K0, flags, lhs, rhs, out,
+                           nullptr);
+}
+
+iree_b200_status_t iree_b200_ops_record_mmt4d_tensor(
+    iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb, int32_t element_type, int64_t M1,
+    int64_t N1, int64_t K1, int32_t M0, int32_t N0, int32_t K0, uint32_t flags,
+    iree_b200_buffer_ref_t lhs, iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t workspace,
+    iree_b200_buffer_ref_t out) {
+  return record_mmt4d_impl(ops, cb, element_type, M1, N1, K1, M0, N0, K0, flags, lhs, rhs, out,
+                           &workspace);
 }
 
 iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t element_type, int64_t M1,
@@ -1148,6 +1247,9 @@ iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t elemen
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
+  const uint64_t ws_offset = total,
+                 ws_bytes = iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
+  total += ws_bytes;
   iree_b200_command_buffer_t* cb = nullptr;
   auto run = [&]() -> iree_b200_status_t {
     B200_RETURN_IF_ERROR(reserve_arena(ops, total + 1024));
@@ -1166,8 +1268,11 @@ iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t elemen
     }
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_create(device, &cb));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_begin(cb));
-    B200_RETURN_IF_ERROR(iree_b200_ops_record_mmt4d(ops, cb, element_type, M1, N1, K1, M0, N0, K0,
-                                                    flags, ref(0), ref(1), ref(2)));
+    const iree_b200_buffer_ref_t workspace =
+        ws_bytes ? iree_b200_buffer_ref_t{ops->arena, ws_offset, ws_bytes}
+                 : iree_b200_buffer_ref_t{nullptr, 0, 0};
+    B200_RETURN_IF_ERROR(iree_b200_ops_record_mmt4d_tensor(
+        ops, cb, element_type, M1, N1, K1, M0, N0, K0, flags, ref(0), ref(1), workspace, ref(2)));
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_end(cb));
     B200_RETURN_IF_ERROR(
         iree_b200_device_queue_execute(device, 0, nullptr, nullptr, 0, nullptr, nullptr, cb));

@@ -59,6 +59,10 @@ int main() {
   emit("iree_b200_mmt4d_generic_bf16_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_f16_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_i8_i32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
+  // tiled <-> row-major relayout: src, dst; constants R1 C1 R0 C0 to_tiled.
+  emit("iree_b200_mmt4d_relayout_b8", "mmt4d_kernels", 256, 0, 5, "1, 0");
+  emit("iree_b200_mmt4d_relayout_b16", "mmt4d_kernels", 256, 0, 5, "1, 0");
+  emit("iree_b200_mmt4d_relayout_b32", "mmt4d_kernels", 256, 0, 5, "1, 0");
   // Channel-launched kernels (not dispatch-ABI exports; see collective_kernels.cu).
   for (const char* type : {"f16", "bf16", "f32"}) {
     for (const char* path : {"nvls", "p2p"}) {

@@ -187,6 +187,9 @@ _STATUS_FUNCS = {
                                         c_void_p, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_record_mmt4d": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64, c_int32,
                                    c_int32, c_int32, c_uint32, BufferRef, BufferRef, BufferRef],
+    "iree_b200_ops_record_mmt4d_tensor": [c_void_p, c_void_p, c_int32, c_int64, c_int64, c_int64,
+                                          c_int32, c_int32, c_int32, c_uint32, BufferRef,
+                                          BufferRef, BufferRef, BufferRef],
     "iree_b200_ops_mmt4d_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int32, c_int32,
                                  c_int32, c_uint32, c_void_p, c_void_p, c_void_p],
     "iree_b200_ops_select_attention": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
@@ -231,6 +234,8 @@ _OTHER_FUNCS = {
     "iree_b200_ops_builtin_executable_data": (c_void_p, [POINTER(c_size_t)]),
     "iree_b200_ops_release": (None, [c_void_p]),
     "iree_b200_ops_matmul_mxfp4_workspace_size": (c_uint64, [c_int64, c_int64, c_int64]),
+    "iree_b200_ops_mmt4d_workspace_size": (c_uint64, [c_int32, c_int64, c_int64, c_int64, c_int32,
+                                                      c_int32, c_int32]),
     "iree_b200_ops_executable": (c_void_p, [c_void_p]),
     "iree_b200_ops_dispatch_count": (c_uint64, [c_void_p]),
 }
@@ -684,6 +689,17 @@ class Ops:
         """linalg.mmt4d: lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0] -> out [M1,N1,M0,N0]."""
         check(lib().iree_b200_ops_record_mmt4d(self._h, cb._h, _etype(element_type), M1, N1, K1,
                                                M0, N0, K0, flags, lhs, rhs, out))
+
+    @staticmethod
+    def mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0) -> int:
+        return lib().iree_b200_ops_mmt4d_workspace_size(_etype(element_type), M1, N1, K1, M0, N0, K0)
+
+    def record_mmt4d_tensor(self, cb: CommandBuffer, element_type, M1, N1, K1, M0, N0, K0,
+                            lhs: BufferRef, rhs: BufferRef, workspace: BufferRef, out: BufferRef,
+                            flags=0):
+        check(lib().iree_b200_ops_record_mmt4d_tensor(
+            self._h, cb._h, _etype(element_type), M1, N1, K1, M0, N0, K0, flags, lhs, rhs,
+            workspace if workspace is not None else NULL_REF, out))
 
     def mmt4d_host(self, element_type, M1, N1, K1, M0, N0, K0, lhs_ptr: int, rhs_ptr: int,
                    out_ptr: int, flags=0):

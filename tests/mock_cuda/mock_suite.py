@@ -571,3 +571,51 @@ def test_mxfp4_tensor_route_recorded_form_and_guards(dev, dev_ops):
     names = [l[0] for l in launches()]
     assert names == ["iree_b200_matmul_mxfp4_dequant_bf16"] * 2 + \
         ["iree_b200_matmul_nt_bf16_f32_1cta", "iree_b200_matmul_generic_mxfp4_f32"]
+
+
+@needs_kernels
+@pytest.mark.parametrize("t,tiles", [("bf16", (16, 16, 2)), ("i8", (8, 32, 4)), ("f16", (16, 16, 16))],
+                         ids=str)
+def test_mmt4d_tensor_route_relayouts(dev, dev_ops, t, tiles):
+    """The tensor-core mmt4d route under the mock: the relayout kernels run on the host, the
+    tcgen05 GEMM in the middle is only logged. Checked: the dispatch sequence, that the GEMM's
+    operand bindings hold exactly the unpacked (row-major) lhs / rhs, and — with ACCUMULATE —
+    that accumulator -> row-major -> tiles is the identity (the GEMM being a no-op here)."""
+    import oracle
+    M0, N0, K0 = tiles
+    M, K, N = 128, 128, 256
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    l4 = oracle.pack(lhs, M0, K0)
+    r4 = oracle.pack(np.ascontiguousarray(rhs.T), N0, K0)
+    M1, K1, N1 = l4.shape[0], l4.shape[1], r4.shape[0]
+    acc_t = "i32" if t == "i8" else "f32"
+    acc = oracle.generate_random_matrix(acc_t, (M1, N1, M0, N0), 3)
+    es = l4.dtype.itemsize
+    need = dev_ops.mmt4d_workspace_size(t, M1, N1, K1, M0, N0, K0)
+    assert need == M * K * es + N * K * es + M * N * 4
+    assert dev_ops.mmt4d_workspace_size(t, M1 - 1, N1, K1, M0, N0, K0) == 0    # < 128 rows
+    out = acc.copy()
+    launches()
+    before = dev_ops.dispatch_count
+    dev_ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, out.ctypes.data,
+                       flags=H.MATMUL_ACCUMULATE)
+    assert dev_ops.dispatch_count - before == 5
+    got = launch_args()
+    relayout = {1: "iree_b200_mmt4d_relayout_b8", 2: "iree_b200_mmt4d_relayout_b16"}[es]
+    names = [g[0] for g in got]
+    assert names[:3] == [relayout, relayout, "iree_b200_mmt4d_relayout_b32"]
+    assert names[3].startswith("iree_b200_matmul_nt_%s_%s" % (t, acc_t))
+    assert names[4] == "iree_b200_mmt4d_relayout_b32"
+    a_rm, b_rm = got[3][1][0], got[3][1][1]
+    ct = {1: ctypes.c_int8, 2: ctypes.c_uint16}[es]
+    a_have = np.ctypeslib.as_array(ctypes.cast(a_rm, ctypes.POINTER(ct)), (M, K))
+    b_have = np.ctypeslib.as_array(ctypes.cast(b_rm, ctypes.POINTER(ct)), (N, K))
+    assert np.array_equal(a_have.view(lhs.dtype), lhs)
+    assert np.array_equal(b_have.view(rhs.dtype), np.ascontiguousarray(rhs.T))
+    assert np.array_equal(out, acc)
+    # Without ACCUMULATE the accumulator is not unpacked: 4 dispatches.
+    before = dev_ops.dispatch_count
+    dev_ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, out.ctypes.data)
+    assert dev_ops.dispatch_count - before == 4
+    launches()

@@ -28,7 +28,7 @@
 namespace {
 struct Dim3 { unsigned x = 0, y = 0, z = 0; };
 thread_local Dim3 threadIdx;
-Dim3 blockIdx;
+Dim3 blockIdx, gridDim;
 pthread_barrier_t block_barrier;
 inline float __uint_as_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 inline uint32_t __float_as_uint(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
@@ -42,6 +42,9 @@ namespace {
 template <class F>
 void run_grid(const unsigned grid[3], F body) {
   pthread_barrier_init(&block_barrier, nullptr, 256);
+  gridDim.x = grid[0];
+  gridDim.y = grid[1];
+  gridDim.z = grid[2];
   for (unsigned z = 0; z < grid[2]; ++z) {
     for (unsigned y = 0; y < grid[1]; ++y) {
       for (unsigned x = 0; x < grid[0]; ++x) {

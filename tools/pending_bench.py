@@ -63,22 +63,30 @@ def main():
             M1, K1, N1 = l4.shape[0], l4.shape[1], r4.shape[0]
             out = np.zeros((M1, N1, M0, N0), dtype=np.int32 if t == "i8" else np.float32)
             bufs = [upload(l4), upload(r4), upload(out)]
-            cb = hal.CommandBuffer(dev).begin()
-            ops.record_mmt4d(cb, t, M1, N1, K1, M0, N0, K0, bufs[0].ref(), bufs[1].ref(),
-                             bufs[2].ref())
-            cb.end()
-            if check:
-                dev.execute(cb)
-                dev.wait_idle()
-                dev.d2h(bufs[2], out.ctypes.data, out.nbytes)
-                ok = bool(np.array_equal(out, oracle.mmt4d(t, l4, r4)))
-                rows.append({"kernel": f"mmt4d_generic_{t}", "tiles": [M0, N0, K0], "size": size,
-                             "bit_exact_vs_oracle": ok})
-            else:
-                ms = _time(torch, stream, dev, cb, args.iters)
-                rows.append({"kernel": f"mmt4d_generic_{t}", "tiles": [M0, N0, K0], "size": size,
-                             "ms": ms, "tflops": 2.0 * size ** 3 / ms / 1e9})
-            print(json.dumps(rows[-1]), flush=True)
+            need = ops.mmt4d_workspace_size(t, M1, N1, K1, M0, N0, K0)
+            for route in ("simt", "tensor"):
+                if route == "tensor" and not need:
+                    continue
+                cb = hal.CommandBuffer(dev).begin()
+                if route == "tensor":
+                    ws = dev.allocate(need)
+                    ops.record_mmt4d_tensor(cb, t, M1, N1, K1, M0, N0, K0, bufs[0].ref(),
+                                            bufs[1].ref(), ws.ref(), bufs[2].ref())
+                else:
+                    ops.record_mmt4d(cb, t, M1, N1, K1, M0, N0, K0, bufs[0].ref(), bufs[1].ref(),
+                                     bufs[2].ref())
+                cb.end()
+                row = {"kernel": f"mmt4d_{route}_{t}", "tiles": [M0, N0, K0], "size": size}
+                if check:
+                    dev.execute(cb)
+                    dev.wait_idle()
+                    dev.d2h(bufs[2], out.ctypes.data, out.nbytes)
+                    row["bit_exact_vs_oracle"] = bool(np.array_equal(out, oracle.mmt4d(t, l4, r4)))
+                else:
+                    ms = _time(torch, stream, dev, cb, args.iters)
+                    row.update(ms=ms, tflops=2.0 * size ** 3 / ms / 1e9)
+                rows.append(row)
+                print(json.dumps(row), flush=True)
 
     # ---- MXFP4: the SIMT dispatch and the bf16-expansion + tcgen05 route -----------------------
     def _mx_row(route, size, check, cb, bufs, out, lhs, ls, rhs, rs):
