@@ -161,9 +161,9 @@ extern "C" __global__ void __launch_bounds__(256)
         __float_as_uint(__fmul_rn(f4e2m1fn_to_f32((word >> (8 * i + 4)) & 0xFu), scale));
     pairs[i] = (lo >> 16) | (hi & 0xFFFF0000u);
   }
-  uint32_t* dst = reinterpret_cast<uint32_t*>(out + (size_t)row * K + k);
-  dst[0] = pairs[0];
-  dst[1] = pairs[1];
-  dst[2] = pairs[2];
-  dst[3] = pairs[3];
+  // One 16-byte store: the ops layer guarantees a 16-byte aligned |out| and K % 32 == 0.
+  struct alignas(16) Quad {
+    uint32_t x, y, z, w;
+  };
+  *reinterpret_cast<Quad*>(out + (size_t)row * K + k) = Quad{pairs[0], pairs[1], pairs[2], pairs[3]};
 }
