@@ -21,7 +21,6 @@ from iree_b200 import hal as H
 pytestmark = pytest.mark.gpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "attention_golden.json")
-RTOL = {"f16": 1e-3, "bf16": 1e-2}
 
 
 def _tensor(d):
@@ -79,11 +78,39 @@ def _random_qkv(t, B, M, K2, D, seed, N=None):
     return q, k, v
 
 
-def _assert_close(t, got, want):
-    g, w = oracle.to_f32(t, got), oracle.to_f32(t, want)
+# Bound on max|got - want| as a fraction of max|want| ITSELF (no absolute floor): the f32
+# accumulate is compared after one rounding to the element type (half an ulp = 2^-9 of the
+# value for bf16, 2^-12 for f16) on top of the P -> V-type truncation both sides perform in a
+# different K2 tile order. north_star's 1e-2 (bf16) / 1e-3 (f16) are relative to the *element*
+# for a well-conditioned sum; softmax outputs are averages of ~K2 values of either sign, so
+# the bound is stated against the largest output: 2e-2 * max|want| for bf16, 2e-3 for f16
+# (CheckOps.td:139 isclose rule with atol = rtol * max|want|), plus a per-row cosine floor.
+RTOL_MAX = {"f16": 2e-3, "bf16": 2e-2}
+COS_MIN = {"f16": 1.0 - 1e-5, "bf16": 1.0 - 2e-4}
+ERRLOG = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out",
+                      "attention_parity_errors.jsonl")
+
+
+def _assert_close(t, got, want, label=None):
+    g, w = oracle.to_f32(t, got).astype(np.float64), oracle.to_f32(t, want).astype(np.float64)
     assert np.isfinite(g).all()
     scale = np.abs(w).max()
-    assert np.abs(g - w).max() <= RTOL[t] * max(scale, 1.0), (np.abs(g - w).max(), scale)
+    err = np.abs(g - w).max()
+    g2, w2 = g.reshape(-1, g.shape[-1]), w.reshape(-1, w.shape[-1])
+    den = np.linalg.norm(g2, axis=1) * np.linalg.norm(w2, axis=1)
+    cos = np.where(den > 0, (g2 * w2).sum(axis=1) / np.where(den > 0, den, 1), 1.0).min()
+    if label is not None:
+        try:
+            os.makedirs(os.path.dirname(ERRLOG), exist_ok=True)
+            with open(ERRLOG, "a") as f:
+                f.write(json.dumps({"case": label, "type": t, "max_abs_err": float(err),
+                                    "max_abs_want": float(scale), "rel_to_max": float(err / scale),
+                                    "rms_want": float(np.sqrt((w * w).mean())),
+                                    "min_row_cosine": float(cos)}) + "\n")
+        except OSError:
+            pass
+    assert err <= RTOL_MAX[t] * scale, (err, scale, err / scale)
+    assert cos >= COS_MIN[t], cos
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16"])
@@ -217,12 +244,13 @@ def test_llama_prefill_shape_sampled(ops, t):
     rows = np.array([0, 1, 127, 128, 255, 256, 1000, 2047, 2048, 4095])
     for b in (0, 13, 31):
         want = oracle.attention(t, q[b:b + 1, rows], k[b:b + 1], v[b:b + 1], scale, k2_tile=128)
-        _assert_close(t, got[b:b + 1, rows], want)
+        _assert_close(t, got[b:b + 1, rows], want, label=f"llama_prefill_32x4096x4096x128 head {b}")
     # Property: softmax weights sum to one, so a V that is constant along K2 comes back.
     vconst = np.broadcast_to(v[:, :1, :], v.shape).copy()
     got2 = _gpu_attention(ops, t, q, k, vconst, scale)
     ref = np.broadcast_to(oracle.to_f32(t, vconst[:, :1, :]), got2.shape)
-    assert np.abs(oracle.to_f32(t, got2) - ref).max() <= RTOL[t] * 4 * np.abs(ref).max()
+    # every output row is V's row rounded once more: within one ulp of the element type
+    assert np.abs(oracle.to_f32(t, got2) - ref).max() <= {"f16": 2.0 ** -10, "bf16": 2.0 ** -7}[t] * np.abs(ref).max()
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16"])
@@ -233,7 +261,7 @@ def test_llama_decode_shape(ops, t):
     scale = 1.0 / np.sqrt(128.0)
     got = _gpu_attention(ops, t, q, k, v, scale)
     want = oracle.attention(t, q, k, v, scale, k2_tile=256)
-    _assert_close(t, got, want)
+    _assert_close(t, got, want, label="llama_decode_32x1x8192x128")
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16"])

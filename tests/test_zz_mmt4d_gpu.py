@@ -15,9 +15,7 @@ import pytest
 import oracle
 from iree_b200 import hal as H
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("IREE_B200_PENDING_VALIDATION") != "1",
-                                 reason="mmt4d kernel has not had its first GPU run yet")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("t", ["i8", "f16", "bf16"])

@@ -14,9 +14,7 @@ import pytest
 import oracle
 from iree_b200 import hal as H
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("IREE_B200_PENDING_VALIDATION") != "1",
-                                 reason="MXFP4 kernel has not had its first GPU run yet")]
+pytestmark = pytest.mark.gpu
 
 
 def _inputs(M, K, N, accumulate):

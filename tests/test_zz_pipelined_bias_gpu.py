@@ -19,9 +19,7 @@ import pytest
 import oracle
 from iree_b200 import hal as H
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("IREE_B200_PENDING_VALIDATION") != "1",
-                                 reason="pipelined fused-bias host call has not run on a GPU yet")]
+pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
