@@ -278,3 +278,136 @@ def test_pipelined_host_call(ops, t, case):
     assert np.array_equal(out, want)
     blocks = batch * -(-M // block) * -(-N // block)
     assert ops.dispatch_count - before == blocks
+
+
+# ---------------------------------------------------------------------------------------
+# BASELINE.json configuration sizes, as such (configs[1] and configs[2]).
+# ---------------------------------------------------------------------------------------
+
+def _checksums_exact(out, a64, b64):
+    """Row / column checksum identity, exact: sum_m C[m,:] = (sum_m A[m,:]) . B and
+    sum_n C[:,n] = A . (sum_n B[:,n]). Every intermediate is an integer (or a multiple of a
+    small power of two) far below 2^53, so f64 is exact."""
+    assert np.array_equal(out.sum(axis=0, dtype=np.float64), a64.sum(axis=0) @ b64)
+    assert np.array_equal(out.sum(axis=1, dtype=np.float64), a64 @ b64.sum(axis=1))
+
+
+@pytest.mark.parametrize("inputs", ["reference_generator", "full_range"])
+def test_config_i8_8192_cubed_bit_exact(device, ops, inputs):
+    """BASELINE configs[1]: linalg.matmul i8 x i8 -> i32 8192^3, ONE device-resident dispatch
+    (the form bench.py times), bit-exact: the reference checker's sampled index set
+    (test_utils.c:41-68) against the oracle's element loop + exact row / column checksums of
+    the whole result. `full_range` draws i8 over [-128, 127] (|C| < 2^27, no i32 wrap)."""
+    M = N = K = 8192
+    if inputs == "reference_generator":
+        lhs = oracle.generate_random_matrix("i8", (M, K), 1)
+        rhs = oracle.generate_random_matrix("i8", (K, N), 2)
+    else:
+        g = np.random.Generator(np.random.PCG64(0xB200))
+        lhs = g.integers(-128, 128, (M, K), dtype=np.int8)
+        rhs = g.integers(-128, 128, (K, N), dtype=np.int8)
+    out = np.empty((M, N), np.int32)
+    bl, br, bo = device.allocate(lhs.nbytes), device.allocate(rhs.nbytes), device.allocate(out.nbytes)
+    try:
+        device.h2d(lhs.ctypes.data, bl, lhs.nbytes)
+        device.h2d(rhs.ctypes.data, br, rhs.nbytes)
+        sel = ops.select_matmul("i8", 1, M, N, K)
+        assert ops.executable.export_info(sel["export_ordinal"])["kernel_name"] == "iree_b200_matmul_i8_i32"
+        cb = H.CommandBuffer(device).begin()
+        ops.record_matmul(cb, "i8", 1, M, N, K, bl.ref(), br.ref(), bo.ref())
+        cb.end()
+        device.execute(cb)
+        device.d2h(bo, out.ctypes.data, out.nbytes)
+        device.wait_idle()
+        cb.release()
+    finally:
+        for b in (bl, br, bo):
+            b.release()
+    idx, _ = oracle.sampled_indices(M, N)
+    assert len(idx) >= 8000
+    for i in idx:
+        m, n = divmod(int(i), N)
+        assert out[m, n] == oracle.matmul_element("i8", lhs, rhs, m, n), (m, n)
+    _checksums_exact(out, lhs.astype(np.float64), rhs.astype(np.float64))
+
+
+def test_config_bf16_8192_cubed_exact(device, ops):
+    """BASELINE configs[1], bf16 half: 8192^3 in one dispatch on the reference generator's
+    inputs (f32 result exact => bit equality), sampled like the reference + checksums."""
+    M = N = K = 8192
+    lhs = oracle.generate_random_matrix("bf16", (M, K), 1)
+    rhs = oracle.generate_random_matrix("bf16", (K, N), 2)
+    out = np.empty((M, N), np.float32)
+    bl, br, bo = device.allocate(lhs.nbytes), device.allocate(rhs.nbytes), device.allocate(out.nbytes)
+    try:
+        device.h2d(lhs.ctypes.data, bl, lhs.nbytes)
+        device.h2d(rhs.ctypes.data, br, rhs.nbytes)
+        cb = H.CommandBuffer(device).begin()
+        ops.record_matmul(cb, "bf16", 1, M, N, K, bl.ref(), br.ref(), bo.ref())
+        cb.end()
+        device.execute(cb)
+        device.d2h(bo, out.ctypes.data, out.nbytes)
+        device.wait_idle()
+        cb.release()
+    finally:
+        for b in (bl, br, bo):
+            b.release()
+    idx, _ = oracle.sampled_indices(M, N)
+    for i in idx:
+        m, n = divmod(int(i), N)
+        assert out[m, n] == oracle.matmul_element("bf16", lhs, rhs, m, n), (m, n)
+    _checksums_exact(out, oracle.to_f32("bf16", lhs).astype(np.float64),
+                     oracle.to_f32("bf16", rhs).astype(np.float64))
+
+
+def test_config_batch_matmul_64x2048_cubed_exact(device, ops):
+    """BASELINE configs[2]: linalg.batch_matmul bf16 batch=64 M=N=K=2048 as ONE dispatch
+    (batch is a tile coordinate of the persistent grid), every batch entry sampled like the
+    reference's per-batch check (iree-e2e-matmul-test.cc:882-911) + exact checksums of each
+    entry. The same buffers are then run as the 8-way shard (8 dispatches of batch=8 on
+    sub-ranges, what each rank of the batch-sharded config executes): identical bits."""
+    B, M, N, K = 64, 2048, 2048, 2048
+    lhs = oracle.generate_random_matrix("bf16", (B, M, K), 1)
+    rhs = oracle.generate_random_matrix("bf16", (B, K, N), 2)
+    out = np.empty((B, M, N), np.float32)
+    bl, br, bo = device.allocate(lhs.nbytes), device.allocate(rhs.nbytes), device.allocate(out.nbytes)
+    try:
+        device.h2d(lhs.ctypes.data, bl, lhs.nbytes)
+        device.h2d(rhs.ctypes.data, br, rhs.nbytes)
+        cb = H.CommandBuffer(device).begin()
+        ops.record_matmul(cb, "bf16", B, M, N, K, bl.ref(), br.ref(), bo.ref())
+        cb.end()
+        device.execute(cb)
+        device.d2h(bo, out.ctypes.data, out.nbytes)
+        device.wait_idle()
+        cb.release()
+        idx, _ = oracle.sampled_indices(M, N, max_elements=400)
+        for b in range(B):
+            for i in idx:
+                m, n = divmod(int(i), N)
+                assert out[b, m, n] == oracle.matmul_element("bf16", lhs[b], rhs[b], m, n), (b, m, n)
+            _checksums_exact(out[b], oracle.to_f32("bf16", lhs[b]).astype(np.float64),
+                             oracle.to_f32("bf16", rhs[b]).astype(np.float64))
+        # The sharded form: rank r of 8 owns entries [8r, 8r+8).
+        shard = np.empty_like(out)
+        fill = H.CommandBuffer(device).begin()
+        fill.fill(bo.ref(), b"\xff\xff\xff\xff")
+        fill.end()
+        device.execute(fill)
+        cb = H.CommandBuffer(device).begin()
+        per = B // 8
+        for r in range(8):
+            ops.record_matmul(cb, "bf16", per, M, N, K,
+                              bl.ref(r * per * M * K * 2, per * M * K * 2),
+                              br.ref(r * per * K * N * 2, per * K * N * 2),
+                              bo.ref(r * per * M * N * 4, per * M * N * 4))
+        cb.end()
+        device.execute(cb)
+        device.d2h(bo, shard.ctypes.data, shard.nbytes)
+        device.wait_idle()
+        cb.release()
+        fill.release()
+        assert np.array_equal(shard, out)
+    finally:
+        for b in (bl, br, bo):
+            b.release()
