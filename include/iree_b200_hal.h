@@ -416,8 +416,12 @@ IREE_B200_API iree_b200_status_t iree_b200_channel_id_create(
 // Default channel provider (channel_provider.h:57-66) without MPI: rank/count from
 // IREE_B200_RANK / IREE_B200_WORLD_SIZE, else RANK / WORLD_SIZE (torchrun), else
 // OMPI_COMM_WORLD_RANK / _SIZE (mpi_channel_provider.c:164-173); the id is exchanged
-// through the file named by IREE_B200_CHANNEL_ID_FILE (rank 0 writes, others poll),
-// standing in for MPI_Bcast (mpi_channel_provider.c:185-190).
+// through files next to the path named by IREE_B200_CHANNEL_ID_FILE, standing in for
+// MPI_Bcast (mpi_channel_provider.c:185-190): every rank publishes a fresh random token,
+// rank 0 publishes {sequence number, tokens, id}, a rank accepts only the id file that
+// carries its own token and acknowledges it, rank 0 returns when all have and removes the
+// files — so a file left by an earlier run or an earlier channel is never taken for the id.
+// Like MPI_Bcast it is collective: all ranks call it, in the same order per channel.
 IREE_B200_API iree_b200_status_t iree_b200_channel_provider_query_default_rank_and_count(
     int32_t* out_rank, int32_t* out_count);
 IREE_B200_API iree_b200_status_t iree_b200_channel_provider_exchange_default_id(

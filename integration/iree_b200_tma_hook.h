@@ -69,6 +69,7 @@ static inline CUresult iree_b200_tma_hook_encode(iree_b200_pfn_cuTensorMapEncode
                                                  uint32_t binding_count, const uint32_t* constants,
                                                  uint32_t constant_count, CUtensorMap* out_map) {
   const iree_b200_tma_map_t* map = &recipe->maps[i];
+  if (!encode_tiled) return CUDA_ERROR_NOT_SUPPORTED;  // driver older than CUDA 12
   if (map->rank < 1 || map->rank > IREE_B200_TMA_MAX_RANK || map->binding >= binding_count) {
     return CUDA_ERROR_INVALID_VALUE;
   }

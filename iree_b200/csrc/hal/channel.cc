@@ -10,9 +10,12 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <chrono>
 #include <cstdlib>
+#include <string>
 #include <thread>
+#include <vector>
 
 #include "../kernels/collective_config.h"
 #include "internal.h"
@@ -76,46 +79,174 @@ iree_b200_status_t iree_b200_channel_provider_query_default_rank_and_count(int32
   return IREE_B200_STATUS_OK;
 }
 
-iree_b200_status_t iree_b200_channel_provider_exchange_default_id(
-    int32_t rank, uint8_t inout_id[IREE_B200_CHANNEL_ID_SIZE]) {
-  B200_REQUIRE_ARG(inout_id);
+// The id exchange (stands in for MPI_Bcast, mpi_channel_provider.c:185-190) is a handshake
+// through small files next to IREE_B200_CHANNEL_ID_FILE, keyed by a per-process exchange
+// sequence number (ranks create their default-id channels in the same order, the assumption
+// MPI_Bcast makes too) and by a FRESH random token per rank and exchange:
+//   rank r>0  publishes  <path>.<seq>.hello.<r> = token_r            (write + rename)
+//   rank 0    waits for every hello, publishes <path>.<seq>.id = {magic, seq, count,
+//             token_1..token_{count-1}, id[128]}
+//   rank r    accepts the id file only if it carries ITS token, then publishes
+//             <path>.<seq>.ack.<r> = token_r
+//   rank 0    returns once every ack carries the token it published for that rank — and
+//             republishes if a hello changes meanwhile (it had read a stale one) — then
+//             removes every file of the exchange.
+// A file left behind by an earlier run or an earlier channel can therefore never be taken
+// for the current id: it does not carry a token drawn after this exchange started.
+namespace {
+
+constexpr uint32_t kIdFileMagic = 0x31444942u;  // "BID1"
+
+bool write_file_atomically(const std::string& path, const void* data, size_t size) {
+  const std::string tmp = path + ".tmp." + std::to_string((long)getpid());
+  FILE* f = fopen(tmp.c_str(), "wb");
+  if (!f) return false;
+  const size_t written = fwrite(data, 1, size, f);
+  fclose(f);
+  if (written != size || rename(tmp.c_str(), path.c_str()) != 0) {
+    unlink(tmp.c_str());
+    return false;
+  }
+  return true;
+}
+
+bool read_file_exactly(const std::string& path, void* data, size_t size) {
+  struct stat st;
+  if (stat(path.c_str(), &st) != 0 || (size_t)st.st_size != size) return false;
+  FILE* f = fopen(path.c_str(), "rb");
+  if (!f) return false;
+  const size_t got = fread(data, 1, size, f);
+  fclose(f);
+  return got == size;
+}
+
+uint64_t fresh_token() {
+  uint64_t token = 0;
+  FILE* f = fopen("/dev/urandom", "rb");
+  if (f) {
+    if (fread(&token, 1, sizeof(token), f) != sizeof(token)) token = 0;
+    fclose(f);
+  }
+  if (!token) {
+    token = (uint64_t)std::chrono::steady_clock::now().time_since_epoch().count() ^
+            ((uint64_t)getpid() << 32) ^ (uint64_t)(uintptr_t)&token;
+  }
+  return token | 1;  // never 0
+}
+
+std::atomic<uint32_t> g_exchange_sequence{0};
+
+iree_b200_status_t exchange_id(int32_t rank, int32_t count, uint8_t inout_id[IREE_B200_CHANNEL_ID_SIZE]) {
   const char* path = getenv("IREE_B200_CHANNEL_ID_FILE");
   if (!path || !*path) {
     return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
                        "no channel id given and IREE_B200_CHANNEL_ID_FILE is not set; cannot "
                        "exchange the default id between ranks");
   }
-  if (rank == 0) {
-    // Write-then-rename so readers never observe a partial id.
-    std::string tmp = std::string(path) + ".tmp." + std::to_string((long)getpid());
-    FILE* f = fopen(tmp.c_str(), "wb");
-    if (!f) return make_status(IREE_B200_STATUS_PERMISSION_DENIED, "cannot write %s", tmp.c_str());
-    const size_t written = fwrite(inout_id, 1, IREE_B200_CHANNEL_ID_SIZE, f);
-    fclose(f);
-    if (written != IREE_B200_CHANNEL_ID_SIZE || rename(tmp.c_str(), path) != 0) {
-      return make_status(IREE_B200_STATUS_DATA_LOSS, "cannot publish channel id at %s", path);
-    }
-    return IREE_B200_STATUS_OK;
+  if (count < 2 || rank < 0 || rank >= count) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "id exchange: rank %d of %d", rank, count);
   }
+  const uint32_t seq = g_exchange_sequence.fetch_add(1);
+  const std::string base = std::string(path) + "." + std::to_string(seq);
+  const std::string id_path = base + ".id";
+  auto hello_path = [&](int r) { return base + ".hello." + std::to_string(r); };
+  auto ack_path = [&](int r) { return base + ".ack." + std::to_string(r); };
   int32_t timeout_s = 120;
   env_int("IREE_B200_CHANNEL_ID_TIMEOUT_S", &timeout_s);
   const auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(timeout_s);
+  auto expired = [&] { return std::chrono::steady_clock::now() >= deadline; };
+  auto nap = [] { std::this_thread::sleep_for(std::chrono::milliseconds(2)); };
+  // {magic, seq, count, reserved} + tokens[count] + id.
+  const size_t payload_size = 16 + 8 * (size_t)count + IREE_B200_CHANNEL_ID_SIZE;
+  std::vector<uint8_t> payload(payload_size);
+
+  if (rank != 0) {
+    const uint64_t token = fresh_token();
+    unlink(ack_path(rank).c_str());
+    if (!write_file_atomically(hello_path(rank), &token, sizeof(token))) {
+      return make_status(IREE_B200_STATUS_PERMISSION_DENIED, "cannot write %s",
+                         hello_path(rank).c_str());
+    }
+    for (;;) {
+      if (read_file_exactly(id_path, payload.data(), payload_size)) {
+        uint32_t head[4];
+        uint64_t published = 0;
+        memcpy(head, payload.data(), sizeof(head));
+        memcpy(&published, payload.data() + 16 + 8 * (size_t)rank, sizeof(published));
+        if (head[0] == kIdFileMagic && head[1] == seq && head[2] == (uint32_t)count &&
+            published == token) {
+          memcpy(inout_id, payload.data() + 16 + 8 * (size_t)count, IREE_B200_CHANNEL_ID_SIZE);
+          if (!write_file_atomically(ack_path(rank), &token, sizeof(token))) {
+            return make_status(IREE_B200_STATUS_PERMISSION_DENIED, "cannot write %s",
+                               ack_path(rank).c_str());
+          }
+          return IREE_B200_STATUS_OK;
+        }
+      }
+      if (expired()) {
+        return make_status(IREE_B200_STATUS_DEADLINE_EXCEEDED,
+                           "rank %d timed out waiting for channel id #%u at %s", rank, seq,
+                           id_path.c_str());
+      }
+      nap();
+    }
+  }
+
+  // Rank 0.
+  unlink(id_path.c_str());
+  std::vector<uint64_t> tokens(count, 0), published(count, 0);
   for (;;) {
-    struct stat st;
-    if (stat(path, &st) == 0 && st.st_size == IREE_B200_CHANNEL_ID_SIZE) {
-      FILE* f = fopen(path, "rb");
-      if (f) {
-        const size_t got = fread(inout_id, 1, IREE_B200_CHANNEL_ID_SIZE, f);
-        fclose(f);
-        if (got == IREE_B200_CHANNEL_ID_SIZE) return IREE_B200_STATUS_OK;
+    bool all_hello = true, all_acked = true, changed = false;
+    for (int r = 1; r < count; ++r) {
+      uint64_t t = 0;
+      if (read_file_exactly(hello_path(r), &t, sizeof(t)) && t) {
+        if (t != tokens[r]) changed = true;
+        tokens[r] = t;
+      }
+      if (!tokens[r]) all_hello = false;
+    }
+    if (all_hello && (changed || !published[1])) {
+      const uint32_t head[4] = {kIdFileMagic, seq, (uint32_t)count, 0};
+      memcpy(payload.data(), head, sizeof(head));
+      memcpy(payload.data() + 16, tokens.data(), 8 * (size_t)count);
+      memcpy(payload.data() + 16 + 8 * (size_t)count, inout_id, IREE_B200_CHANNEL_ID_SIZE);
+      if (!write_file_atomically(id_path, payload.data(), payload_size)) {
+        return make_status(IREE_B200_STATUS_DATA_LOSS, "cannot publish channel id at %s",
+                           id_path.c_str());
+      }
+      published = tokens;
+    }
+    for (int r = 1; r < count; ++r) {
+      uint64_t t = 0;
+      if (!published[r] || !read_file_exactly(ack_path(r), &t, sizeof(t)) || t != published[r]) {
+        all_acked = false;
       }
     }
-    if (std::chrono::steady_clock::now() >= deadline) {
+    if (all_hello && all_acked) break;
+    if (expired()) {
       return make_status(IREE_B200_STATUS_DEADLINE_EXCEEDED,
-                         "rank %d timed out waiting for the channel id at %s", rank, path);
+                         "rank 0 timed out exchanging channel id #%u through %s (%s)", seq,
+                         base.c_str(), all_hello ? "acknowledgements missing" : "ranks missing");
     }
-    std::this_thread::sleep_for(std::chrono::milliseconds(5));
+    nap();
   }
+  unlink(id_path.c_str());
+  for (int r = 1; r < count; ++r) {
+    unlink(hello_path(r).c_str());
+    unlink(ack_path(r).c_str());
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+}  // namespace
+
+iree_b200_status_t iree_b200_channel_provider_exchange_default_id(
+    int32_t rank, uint8_t inout_id[IREE_B200_CHANNEL_ID_SIZE]) {
+  B200_REQUIRE_ARG(inout_id);
+  int32_t default_rank = 0, count = 1;
+  B200_RETURN_IF_ERROR(
+      iree_b200_channel_provider_query_default_rank_and_count(&default_rank, &count));
+  return exchange_id(rank, count, inout_id);
 }
 
 iree_b200_status_t iree_b200_channel_create(iree_b200_device_t* device,
@@ -155,8 +286,7 @@ iree_b200_status_t iree_b200_channel_create(iree_b200_device_t* device,
   } else {
     if (rank == 0) B200_NCCL(nccl, ncclGetUniqueId(&id));
     if (count > 1) {
-      B200_RETURN_IF_ERROR(iree_b200_channel_provider_exchange_default_id(
-          rank, reinterpret_cast<uint8_t*>(&id)));
+      B200_RETURN_IF_ERROR(exchange_id(rank, count, reinterpret_cast<uint8_t*>(&id)));
     }
   }
 

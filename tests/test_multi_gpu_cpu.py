@@ -50,6 +50,15 @@ def _worker(rank, world, port, tmp, results):
         # 2. id exchange without MPI: rank 0 publishes 128 bytes, the others receive them.
         ident = bytes(range(128)) if rank == 0 else bytes(128)
         assert hal.exchange_default_id(rank, ident) == bytes(range(128))
+        # ... a second channel in the same run gets ITS id (per-process sequence number), and
+        # neither exchange is fooled by the stale files the test planted (a leftover
+        # id file must never be taken for the current id).
+        ident2 = bytes(reversed(range(128))) if rank == 0 else bytes(128)
+        assert hal.exchange_default_id(rank, ident2) == bytes(reversed(range(128)))
+        if rank == 0:
+            left = [f for f in os.listdir(tmp) if f.startswith("id.") and ".tmp." not in f
+                    and not f.startswith("id.7.")]
+            assert left == [], left   # rank 0 removes the files of a finished exchange
         # 3. row-parallel GEMM + all_reduce(sum) == the full GEMM (oracle as the kernel).
         M, N, K = 48, 40, 64
         lhs = oracle.generate_random_matrix("bf16", (M, K), 1)
@@ -88,5 +97,16 @@ def test_world_size_2_gloo():
     with tempfile.TemporaryDirectory() as tmp, mp.Manager() as manager:
         results = manager.dict()
         port = 29600 + os.getpid() % 300
+        # Leftovers of an "earlier run": a well-formed id file for exchanges #0 and #1 with
+        # someone else's id and tokens, a stale hello and a stale ack of rank 1.
+        import struct
+        for seq in (0, 1, 7):
+            stale = struct.pack("<4I", 0x31444942, seq, world, 0) + struct.pack("<2Q", 0, 0x1234567) \
+                + bytes([0xEE]) * 128
+            with open(os.path.join(tmp, f"id.{seq}.id"), "wb") as f:
+                f.write(stale)
+            for kind in ("hello", "ack"):
+                with open(os.path.join(tmp, f"id.{seq}.{kind}.1"), "wb") as f:
+                    f.write(struct.pack("<Q", 0x1234567))
         mp.spawn(_worker, args=(world, port, tmp, results), nprocs=world, join=True)
         assert dict(results) == {0: "ok", 1: "ok"}

@@ -160,7 +160,7 @@ def test_stock_reference_driver_runs_the_decode_cluster_attention(ops, hal, tmp_
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("t,shape", [("bf16", (512, 512, 512)), ("i8", (1000, 264, 520)),
+@pytest.mark.parametrize("t,shape", [("bf16", (512, 512, 512)), ("i8", (1000, 272, 528)),
                                      ("f16", (384, 768, 1024)), ("bf16", (2048, 1280, 256))])
 def test_patched_reference_driver_runs_the_tcgen05_matmul(ops, hal, tmp_path, t, shape):
     """The TMA-fed tcgen05 exports through the reference driver + the 60-line hook of
