@@ -12,6 +12,13 @@ own batch slice (batch-sharded linalg.batch_matmul, batch = N, no data-path coll
 weak scaling. `value` = aggregate TFLOP/s over all ranks from CUDA-event time (max over
 ranks); `e2e` = the same metric through iree_b200_ops_matmul_host with pinned HOST
 buffers (H2D of both operands and D2H of the result inside the timed region).
+The default workload's line also carries, device-timed in the same invocation:
+  N = 1: "also"    — i8 8192^3, batch_matmul 64 x 2048^3, prefill and decode attention, the
+                     decoder-layer GEMMs on one GPU (the other single-GPU BASELINE configs);
+  N > 1: "sharded" — the configs BASELINE.json shards, STRONG scaling with their own N=1
+                     figure and efficiency: batch_matmul 64 x 2048^3 split 64/N (no
+                     collective) and the tensor-parallel decoder layer with its all-reduces
+                     through iree_b200_channel_t (+ GEMMs alone, collectives alone, overlap).
 
 Reference arm (`--impl reference`): the reference's CPU path for the same op on the box's
 host cores — the oracle port (oracle/oracle.c; kind "port") — on a bounded sample.
@@ -71,7 +78,7 @@ def load_peaks():
 
 class ClockSampler:
     """Samples SM clock, power and throttle reasons WHILE the timed region runs: NVML polled
-    every 5 ms from a thread (nvidia-smi -lms 100 as the fallback when pynvml is missing)."""
+    every 1 ms from a thread (nvidia-smi -lms 100 as the fallback when pynvml is missing)."""
 
     FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
               "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -111,11 +118,11 @@ class ClockSampler:
                         self.rows.append((sm, pw, [n for n, b in bits.items() if r & b]))
                     except Exception:
                         pass
-                    time.sleep(0.005)
+                    time.sleep(0.001)
 
             self.thread = threading.Thread(target=poll, daemon=True)
             self.thread.start()
-            self.source = "nvml 5 ms"
+            self.source = "nvml 1 ms"
             return
         except Exception:
             self.thread = None
@@ -341,69 +348,26 @@ class TpLayerStep:
     """BASELINE configs[4]: the GEMMs of one Llama-3-8B decoder layer (hidden 4096, 32 q / 8 kv
     heads x 128, FFN 14336; tokens = 8192), tensor-parallel over the ranks (Megatron split):
     QKV and gate/up column-parallel, O and down row-parallel followed by an all-reduce(sum) of
-    the [tokens, 4096] bf16 activation through iree_hal_channel (NCCL over NVLink). The
-    row-parallel GEMMs are recorded in token chunks so that, with the device's collective
-    stream, the all-reduce of chunk c overlaps the GEMM of chunk c+1. All GEMMs use the
+    the [tokens, 4096] bf16 activation through iree_hal_channel. Recording and schedule live in
+    iree_b200/tp_layer.py (row-parallel GEMMs and gate/up in token chunks, staged so that the
+    all-reduce of a chunk runs beside the GEMMs of its neighbours). All GEMMs use the
     truncating epilogue (bf16 activations)."""
 
     TOKENS, HIDDEN, QKV, FFN, CHUNKS = 8192, 4096, 6144, 14336, 4
+    STAGED = True
 
     def __init__(self, torch, hal, dev, ops, world, rank, channel, seed, region=None):
-        from iree_b200 import sharding
-        T, H, QKV, FFN = self.TOKENS, self.HIDDEN, self.QKV, self.FFN
-        plan = {g.name: g for g in sharding.decoder_layer_plan(world, rank, tokens=T)}
-        assert (plan["qkv"].N, plan["o"].K, plan["gate_up"].N, plan["down"].K) == \
-            (QKV // world, H // world, 2 * FFN // world, FFN // world)
-        assert len(sharding.token_chunks(T, self.CHUNKS)) == self.CHUNKS and T % self.CHUNKS == 0
-        g = torch.Generator(device="cuda")
-        g.manual_seed(0xB200 + seed)
-        mk = lambda *shape: (torch.randn(shape, device="cuda", generator=g) * 0.05).to(torch.bfloat16)
-        out = lambda *shape: torch.empty(shape, dtype=torch.bfloat16, device="cuda")
-        self.t = {
-            "x": mk(T, H), "wqkv": mk(H, QKV // world), "qkv": out(T, QKV // world),
-            "attn": mk(T, H // world), "wo": mk(H // world, H), "o": out(T, H),
-            "wgu": mk(H, 2 * FFN // world), "gu": out(T, 2 * FFN // world),
-            "act": mk(T, FFN // world), "wd": mk(FFN // world, H), "d": out(T, H),
-        }
-        if region is not None:
-            # The all-reduced activations live in the symmetric region (every rank maps it):
-            # their all-reduces run on the NVLink kernels instead of NCCL.
-            self.t["o"] = region.view(0, (T, H), torch.bfloat16)
-            self.t["d"] = region.view(T * H * 2, (T, H), torch.bfloat16)
-        self.region = region
-        self.channel = channel
-        self.b = {k: dev.import_buffer(v.data_ptr(), v.numel() * 2) for k, v in self.t.items()}
-        self.world, self.dev = world, dev
-        self.flop = 2.0 * T * (H * QKV + H * H + H * 2 * FFN + FFN * H) / world
-        trunc = hal.MATMUL_TRUNCATE_RESULT
-        ar = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, "bf16")
-        before = ops.dispatch_count
-        cb = hal.CommandBuffer(dev).begin()
-        b = self.b
-        ops.record_matmul(cb, "bf16", 1, T, QKV // world, H, b["x"].ref(), b["wqkv"].ref(),
-                          b["qkv"].ref(), flags=trunc)
-        self.collectives = 0
-
-        def row_parallel(lhs, k_local, rhs, dst):
-            rows = T // self.CHUNKS
-            for c in range(self.CHUNKS):
-                ops.record_matmul(cb, "bf16", 1, rows, H, k_local,
-                                  b[lhs].ref(c * rows * k_local * 2, rows * k_local * 2),
-                                  b[rhs].ref(), b[dst].ref(c * rows * H * 2, rows * H * 2),
-                                  flags=trunc)
-                if world > 1:
-                    ref = b[dst].ref(c * rows * H * 2, rows * H * 2)
-                    cb.collective(channel, ar, 0, ref, ref, rows * H)
-                    self.collectives += 1
-            cb.barrier()
-
-        row_parallel("attn", H // world, "wo", "o")
-        ops.record_matmul(cb, "bf16", 1, T, 2 * FFN // world, H, b["o"].ref(), b["wgu"].ref(),
-                          b["gu"].ref(), flags=trunc)
-        row_parallel("act", FFN // world, "wd", "d")
-        cb.end()
-        self.cb = cb
-        self.launches_per_step = ops.dispatch_count - before
+        from iree_b200 import tp_layer
+        self.layer = tp_layer.DecoderLayerGemms(
+            torch, hal, dev, ops, world, rank, channel, tokens=self.TOKENS, hidden=self.HIDDEN,
+            ffn=self.FFN, chunks=self.CHUNKS, region=region, seed=seed,
+            chunk_consumers=self.STAGED)
+        assert self.layer.dims["qkv"] == self.QKV
+        self.t, self.b, self.cb = self.layer.t, self.layer.b, self.layer.cb
+        self.world, self.dev, self.channel, self.region = world, dev, channel, region
+        self.flop = self.layer.flop
+        self.collectives = self.layer.collectives
+        self.launches_per_step = self.layer.launches_per_step
 
     def step(self):
         self.dev.execute(self.cb)
@@ -420,17 +384,6 @@ class TpLayerStep:
         self.dev.d2h(self.b["d"], host[1].data_ptr(), n)
         self.dev.wait_idle()
 
-    def collective_path(self):
-        if self.world == 1:
-            return "none at N=1"
-        if self.region is None:
-            return "NCCL"
-        counts = self.channel.collective_counts()
-        kind = "NVSwitch multimem.ld_reduce/st kernels" if self.region.multicast_base else \
-            "peer load/store kernels"
-        return (f"symmetric region, {kind}: {counts['symmetric']} issued by our kernels, "
-                f"{counts['nccl']} by NCCL so far")
-
     def describe(self):
         T, H, QKV, FFN, w = self.TOKENS, self.HIDDEN, self.QKV, self.FFN, self.world
         weights = 2.0 * (H * QKV + H * H + H * 2 * FFN + FFN * H) / w
@@ -439,8 +392,9 @@ class TpLayerStep:
                 "workload": f"Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens={T}, "
                             f"bf16 -> bf16 (f32 accumulate), tensor-parallel over {w} GPU(s), "
                             f"{self.collectives} all-reduce(sum, bf16, [{T // self.CHUNKS},{H}]) per "
-                            f"step via iree_hal_channel ({self.collective_path()}), overlapped on "
-                            f"the collective stream",
+                            f"step via iree_hal_channel ({self.layer.collective_path()}), "
+                            f"{len(self.layer.stages)} barrier-separated stages, collectives on "
+                            f"the collective stream beside the stage's GEMMs",
                 "dtype": "bf16 (f32 accumulate)", "h2d": int(T * H * 2), "d2h": int(T * H * 2),
                 "api": "h2d(x) + iree_b200_device_queue_execute(layer command buffer) + d2h(y)"}
 
@@ -450,6 +404,178 @@ def make_step(torch, hal, dev, ops, workload, seed):
         return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed,
                           fused=workload in FUSED_WORKLOADS)
     return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed)
+
+
+def time_steps(torch, works, steps, warmup, stream, world, sampler=None):
+    """|warmup| untimed steps, then exactly |steps| between two CUDA events on |stream|,
+    bracketed by barrier + synchronize; returns ms per step, max over ranks."""
+    sets = len(works)
+    with torch.cuda.stream(stream):
+        for i in range(warmup):
+            works[i % sets].step()
+        barrier(world)
+        if sampler is not None:
+            sampler.start()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for i in range(steps):
+            works[i % sets].step()
+        ev1.record(stream)
+        barrier(world)
+    return max_over_ranks(ev0.elapsed_time(ev1), world) / steps
+
+
+def rotating_sets(make, info_bytes):
+    """Input sets cycled through between timed steps so that the working set exceeds L2."""
+    first = make(0)
+    sets = max(1, min(4, int(-(-2 * 126e6 // info_bytes(first)))))
+    return [first] + [make(i) for i in range(1, sets)]
+
+
+def roofline_of(info, per_gpu_tflops, ms_per_step, peaks):
+    if info["bound"] == "tensor":
+        return {"bound": "tensor", "achieved": per_gpu_tflops, "peak": peaks["bf16_tflops"],
+                "unit": "TFLOP/s", "frac": per_gpu_tflops / peaks["bf16_tflops"],
+                "frac_of_sustained": per_gpu_tflops / peaks["bf16_tflops_sustained"],
+                "frac_of_nominal_2250": per_gpu_tflops / 2250.0,
+                "peak_source": peaks["source"] + " cuBLAS bf16 burst"}
+    gbs = info["bytes"] / (ms_per_step * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "frac": gbs / peaks["hbm_gbs"], "frac_of_nominal_8000": gbs / 8000.0,
+            "peak_source": peaks["source"] + " copy"}
+
+
+def make_tp_device(torch, hal, args, world, rank, local):
+    """Device + ops + channel (+ symmetric region) for the tensor-parallel layer: two streams
+    (overlap_collectives), a few SMs kept free of persistent GEMM CTAs for the collective
+    kernels, the channel created by iree_b200_channel_create through the DEFAULT provider
+    (rank / count from the launcher's environment, id through IREE_B200_CHANNEL_ID_FILE)."""
+    stream = torch.cuda.Stream()
+    overlap = 0
+    if world > 1:
+        overlap = 1 if args.range_fusion else 2
+    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
+                     overlap_collectives=overlap)
+    ops = hal.Ops(dev)
+    channel = region = None
+    if world > 1:
+        import tempfile
+        os.environ.setdefault("IREE_B200_CHANNEL_ID_FILE", os.path.join(
+            tempfile.gettempdir(), "iree_b200_bench_id." + os.environ.get("MASTER_PORT", "0")))
+        channel = hal.Channel(dev)
+        assert channel.rank_and_count() == (rank, world)
+        ops.set_reserved_sms(args.reserved_sms)
+        if args.collective == "symmetric":
+            from iree_b200 import symmetric
+            region = symmetric.SymmetricRegion(
+                2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
+            blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
+            region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
+    TpLayerStep.CHUNKS = args.tp_chunks
+    TpLayerStep.STAGED = not args.range_fusion
+    return stream, dev, ops, channel, region
+
+
+def sharded_lines(torch, hal, args, world, rank, local, peaks):
+    """N > 1: the two configurations BASELINE.json shards, STRONG scaling, each
+    with its own N=1 figure measured in this same invocation (every rank runs the unsharded
+    workload on its own GPU at the same time; the slowest rank counts) so that the efficiency
+    is T(1) / (N * T(N)) on one box, one run:
+      batch_matmul       configs[2]: 64 x 2048^3 bf16, batch split 64/N, no collective
+      tp_decoder_layer   configs[4]: Llama-3-8B layer GEMMs, Megatron split, all-reduce through
+                         iree_b200_channel_t, + the step's GEMMs alone and collectives alone"""
+    out = {}
+    steps, warmup = max(10, min(args.steps, 50)), max(3, min(args.warmup, 5))
+    stream = torch.cuda.Stream()
+    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
+    ops = hal.Ops(dev)
+    # ---- configs[2]
+    op, et, B, M, N, K = MATMUL_WORKLOADS["batch_matmul"]
+    if B % world == 0:
+        full = [MatmulStep(torch, hal, dev, ops, (op, et, B, M, N, K), seed=rank)]
+        t1 = time_steps(torch, full, steps, warmup, stream, world)
+        del full
+        torch.cuda.empty_cache()
+        part = rotating_sets(lambda i: MatmulStep(torch, hal, dev, ops, (op, et, B // world, M, N, K),
+                                                  seed=rank + 100 * i),
+                             lambda w: w.describe()["bytes"])
+        tn = time_steps(torch, part, steps, warmup, stream, world)
+        flop = 2.0 * B * M * N * K
+        out["batch_matmul"] = {
+            "workload": f"linalg.batch_matmul bf16 batch={B} M=N=K={M}, batch split {B // world} per GPU "
+                        f"over {world} GPUs, no collective", "scaling": "strong",
+            "value": flop / (tn * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": tn,
+            "n1_ms_per_step": t1, "n1_value": flop / (t1 * 1e-3) / 1e12,
+            "efficiency": t1 / (world * tn), "steps": steps,
+            "roofline_frac": flop / world / (tn * 1e-3) / 1e12 / peaks["bf16_tflops"]}
+        del part
+        torch.cuda.empty_cache()
+    # ---- configs[4]
+    solo = TpLayerStep(torch, hal, dev, ops, 1, 0, None, seed=rank)
+    t1 = time_steps(torch, [solo], steps, warmup, stream, world)
+    layer_flop = solo.flop
+    del solo
+    torch.cuda.empty_cache()
+    tstream, tdev, tops, channel, region = make_tp_device(torch, hal, args, world, rank, local)
+    step = TpLayerStep(torch, hal, tdev, tops, world, rank, channel, seed=rank, region=region)
+    tn = time_steps(torch, [step], steps, warmup, tstream, world)
+    info = step.describe()
+    # The step's two halves alone: GEMMs without collectives, collectives without GEMMs.
+    from iree_b200 import tp_layer
+    kw = dict(tokens=TpLayerStep.TOKENS, hidden=TpLayerStep.HIDDEN, ffn=TpLayerStep.FFN,
+              chunks=TpLayerStep.CHUNKS, region=region, seed=rank, chunk_consumers=TpLayerStep.STAGED)
+    gemms = tp_layer.DecoderLayerGemms(torch, hal, tdev, tops, world, rank, channel,
+                                       only="gemms", **kw)
+    t_gemm = time_steps(torch, [gemms], steps, warmup, tstream, world)
+    colls = tp_layer.DecoderLayerGemms(torch, hal, tdev, tops, world, rank, channel,
+                                       only="collectives", **kw)
+    t_coll = time_steps(torch, [colls], steps, warmup, tstream, world)
+    payload = 2.0 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2   # two [tokens, hidden] bf16
+    out["tp_decoder_layer"] = {
+        "workload": info["workload"], "scaling": "strong",
+        "value": layer_flop / (tn * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": tn,
+        "n1_ms_per_step": t1, "n1_value": layer_flop / (t1 * 1e-3) / 1e12,
+        "efficiency": t1 / (world * tn), "steps": steps,
+        "gemm_ms": t_gemm, "collective_ms": t_coll,
+        "overlap_frac": max(0.0, (t_gemm + t_coll - tn) / max(1e-9, min(t_gemm, t_coll))),
+        "collective": {"what": f"{step.collectives} x all_reduce(sum, bf16) = {payload / 2**20:.0f} MiB "
+                               f"per step, {args.collective}",
+                       "algbw_gbs": payload / (t_coll * 1e-3) / 1e9,
+                       "nvlink_bound_ms": payload * (1.0 + 1.0 / world) / 900e9 * 1e3,
+                       "frac_of_nvlink_bound": payload * (1.0 + 1.0 / world) / 900e9 * 1e3 / t_coll},
+        "limiter": "collective" if t_coll > t_gemm else "gemm",
+        "launches_per_step": step.launches_per_step}
+    return out
+
+
+ALSO_WORKLOADS = ["matmul_i8", "batch_matmul", "attention_prefill", "attention_decode"]
+
+
+def also_lines(torch, hal, dev, ops, stream, args, peaks):
+    """N = 1: the other single-GPU configurations of BASELINE.json, driver-runnable, as short
+    device-timed runs under the "also" key (value + roofline fraction each)."""
+    out = {}
+    steps, warmup = max(10, min(args.steps, 50)), max(3, min(args.warmup, 5))
+    for name in ALSO_WORKLOADS:
+        works = rotating_sets(lambda i: make_step(torch, hal, dev, ops, name, seed=100 * i),
+                              lambda w: w.describe()["bytes"])
+        ms = time_steps(torch, works, steps, warmup, stream, 1)
+        info = works[0].describe()
+        tflops = info["flop"] / (ms * 1e-3) / 1e12
+        roof = roofline_of(info, tflops, ms, peaks)
+        out[name] = {"workload": info["workload"], "value": tflops, "unit": "TFLOP/s",
+                     "ms_per_step": ms, "steps": steps, "dtype": info["dtype"],
+                     "launches_per_step": works[0].launches_per_step,
+                     "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "unit", "frac")}}
+        del works
+        torch.cuda.empty_cache()
+    solo = TpLayerStep(torch, hal, dev, ops, 1, 0, None, seed=0)
+    ms = time_steps(torch, [solo], steps, warmup, stream, 1)
+    tflops = solo.flop / (ms * 1e-3) / 1e12
+    out["tp_decoder_layer_n1"] = {"workload": solo.describe()["workload"], "value": tflops,
+                                  "unit": "TFLOP/s", "ms_per_step": ms, "steps": steps,
+                                  "roofline": {"bound": "tensor", "frac": tflops / peaks["bf16_tflops"]}}
+    return out
 
 
 def run_ours(args):
@@ -463,63 +589,33 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from iree_b200 import hal
 
-    stream = torch.cuda.Stream()
+    peaks = load_peaks()
     AttentionStep.FLAGS = args.attention_flags
     tp = args.workload == "tp_decoder_layer"
-    dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
-                     overlap_collectives=(2 if args.no_range_fusion else 1) if tp and world > 1 else 0)
-    ops = hal.Ops(dev)
     if tp:
-        channel = None
-        if world > 1:
-            import torch.distributed as dist
-            ids = [hal.Channel.create_id() if rank == 0 else None]
-            dist.broadcast_object_list(ids, src=0)
-            channel = hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
-        region = None
-        if world > 1:
-            ops.set_reserved_sms(args.reserved_sms)
-            if args.collective == "symmetric":
-                from iree_b200 import symmetric
-                region = symmetric.SymmetricRegion(
-                    2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
-                blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
-                region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
-        TpLayerStep.CHUNKS = args.tp_chunks
+        stream, dev, ops, channel, region = make_tp_device(torch, hal, args, world, rank, local)
         first = TpLayerStep(torch, hal, dev, ops, world, rank, channel, seed=rank, region=region)
-        info = first.describe()
-        sets, works = 1, [first]
+        works = [first]
     else:
+        stream = torch.cuda.Stream()
+        dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
+        ops = hal.Ops(dev)
         # Rotating input sets: the working set cycled through between timed steps exceeds L2.
-        first = make_step(torch, hal, dev, ops, args.workload, seed=rank)
-        info = first.describe()
-        sets = max(1, min(4, int(-(-2 * 126e6 // info["bytes"]))))
-        works = [first] + [make_step(torch, hal, dev, ops, args.workload, seed=rank + 100 * i)
-                           for i in range(1, sets)]
+        works = rotating_sets(lambda i: make_step(torch, hal, dev, ops, args.workload,
+                                                  seed=rank + 100 * i),
+                              lambda w: w.describe()["bytes"])
+        first = works[0]
+    info = first.describe()
+    sets = len(works)
     flop, nbytes = info["flop"], info["bytes"]
 
     # ---- device-resident timing (CUDA events on the dispatch stream) ----
-    with torch.cuda.stream(stream):
-        for i in range(args.warmup):
-            works[i % sets].step()
-        barrier(world)
-        sampler = ClockSampler(local)
-        if rank == 0:
-            sampler.start()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record(stream)
-        for i in range(args.steps):
-            works[i % sets].step()
-        ev1.record(stream)
-        barrier(world)
-        clocks = sampler.stop() if rank == 0 else None
-    ms_total = max_over_ranks(ev0.elapsed_time(ev1), world)
-    ms_per_step = ms_total / args.steps
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms_per_step = time_steps(torch, works, args.steps, args.warmup, stream, world, sampler)
+    clocks = sampler.stop() if rank == 0 else None
+    # Weak scaling: every rank's |flop|; the TP layer: |flop| is this rank's share (strong).
     value = flop * world / (ms_per_step * 1e-3) / 1e12
     launches = first.launches_per_step * args.steps
-    if tp:
-        # Strong scaling: |flop| is this rank's share of the fixed layer.
-        value = flop * world / (ms_per_step * 1e-3) / 1e12
 
     # ---- end to end through the host-buffer C-ABI call ----
     host = first.host_buffers(torch)
@@ -536,27 +632,28 @@ def run_ours(args):
            "ms_per_step": e2e_ms, "steps": e2e_steps,
            "h2d_bytes_per_step": info["h2d"], "d2h_bytes_per_step": info["d2h"],
            "api": info["api"]}
+    del host
+
+    extra = {}
+    if args.workload == "matmul_bf16" and not args.no_extra:
+        if world > 1:
+            del works
+            torch.cuda.empty_cache()
+            extra["sharded"] = sharded_lines(torch, hal, args, world, rank, local, peaks)
+        else:
+            extra["also"] = also_lines(torch, hal, dev, ops, stream, args, peaks)
 
     if rank != 0:
         return
     if tp:
         info = first.describe()  # refreshed: how many collectives went which way
-    peaks = load_peaks()
     per_gpu = value / world
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get(args.workload)
-    if info["bound"] == "tensor":
-        roofline = {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_tflops"],
-                    "unit": "TFLOP/s", "frac": per_gpu / peaks["bf16_tflops"],
-                    "frac_of_sustained": per_gpu / peaks["bf16_tflops_sustained"],
-                    "peak_source": peaks["source"] + " cuBLAS bf16 burst"}
-    else:
-        gbs = nbytes / (ms_per_step * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": gbs / peaks["hbm_gbs"], "peak_source": peaks["source"] + " copy"}
+    roofline = roofline_of(info, per_gpu, ms_per_step, peaks)
     roofline.update({"traffic": traffic, "algorithmic_flop_per_launch": flop,
                      "algorithmic_bytes_per_launch": nbytes})
     line = {
@@ -564,18 +661,39 @@ def run_ours(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "strong" if tp else "weak", "vs_baseline": None,
         "dtype": info["dtype"], "data": "synthetic",
-        "config": {"workload": info["workload"]
-                               + (f", batch-sharded over {world} GPUs (no collective)"
-                                  if world > 1 and not tp else ""),
+        "config": {"workload": workload_string(args.workload, world, info),
                    "l2": "%d rotating input sets of %.0f MiB each (> 126 MB L2 between reuses); "
                          "no flush" % (sets, nbytes / 2**20),
                    "launch": "stream command buffer replay, %d dispatch(es) per step"
                              % first.launches_per_step},
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
     }
+    line.update(extra)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.workload, threads=use_all_host_threads())
     print(json.dumps(line), flush=True)
+
+
+def workload_string(workload, world, info=None):
+    """config.workload — identical in both arms (the reference arm times a bounded sample of
+    this same workload; its own `sample` key says which)."""
+    if info is None:
+        if workload in MATMUL_WORKLOADS:
+            op, et, batch, M, N, K = MATMUL_WORKLOADS[workload]
+            name = f"linalg.{op}" + (" + bias[n] + relu + truncf (one dispatch)"
+                                     if workload in FUSED_WORKLOADS else "")
+            text = f"{name} {et} batch={batch} M={M} N={N} K={K} per GPU"
+        elif workload in ATTENTION_WORKLOADS:
+            op, et, B, M, K2, D = ATTENTION_WORKLOADS[workload]
+            text = (f"iree_linalg_ext.attention {et} batch*heads={B} M={M} K2={K2} "
+                    f"K1=N={D} scale=1/sqrt({D}) no mask, per GPU")
+        else:
+            text = "Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens=8192"
+    else:
+        text = info["workload"]
+    if world > 1 and workload != "tp_decoder_layer":
+        text += f", batch-sharded over {world} GPUs (no collective)"
+    return text
 
 
 def cpu_work(workload, rows):
@@ -648,9 +766,16 @@ def use_all_host_threads() -> int:
     return n
 
 
+# Both CPU arms (cpu_baseline in the own arm's line, and --impl reference) time the SAME
+# bounded sample: the first CPU_SAMPLE_ROWS rows of the LHS / of one head's queries against
+# the full RHS / K,V. Each call includes the reference path's packing of both operands
+# (oracle/ref_glue.c: pack -> mmt4d -> unpack, as tools/e2e_matmul_benchmark.c does).
+CPU_SAMPLE_ROWS = 2048
+
+
 def cpu_baseline(workload, threads):
     """The oracle port (oracle/oracle.c, OpenMP) timed on this box's host cores."""
-    fn, flop, desc, kind = cpu_work(workload, rows=2048 if workload in MATMUL_WORKLOADS else 1024)
+    fn, flop, desc, kind = cpu_work(workload, rows=CPU_SAMPLE_ROWS)
     fn()  # warm the thread pool / page in
     t0 = time.perf_counter()
     runs = 0
@@ -662,12 +787,17 @@ def cpu_baseline(workload, threads):
             "sample": f"{desc}, {runs} run(s), {dt:.2f} s each"}
 
 
+CPU_DTYPES = {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
+              "i8": "i8 (i32 accumulate)", "f8e4m3fn": "f8E4M3FN (f32 accumulate)",
+              "f8e5m2": "f8E5M2 (f32 accumulate)"}
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return
     threads = use_all_host_threads()
-    fn, flop, desc, kind = cpu_work(args.workload, rows=1024 if oracle_ref() else 256)
+    fn, flop, desc, kind = cpu_work(args.workload, rows=CPU_SAMPLE_ROWS)
     for _ in range(max(1, min(args.warmup, 2))):
         fn()
     t0 = time.perf_counter()
@@ -679,9 +809,10 @@ def run_reference(args):
             ("matmul", "bf16", 1, TpLayerStep.TOKENS, TpLayerStep.QKV, TpLayerStep.HIDDEN))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "TFLOP/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": spec[1], "data": "synthetic",
-            "config": {"workload": args.workload + " " + "x".join(str(x) for x in spec[2:]),
+            "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "strong" if args.workload == "tp_decoder_layer" else "weak",
+            "vs_baseline": None, "dtype": CPU_DTYPES.get(spec[1], spec[1]), "data": "synthetic",
+            "config": {"workload": workload_string(args.workload, world),
                        "sample": desc + " per step"},
             "cpu_baseline": {"value": value, "unit": "TFLOP/s", "cores": threads, "kind": kind,
                              "sample": desc + " per step"},
@@ -708,9 +839,12 @@ def main():
                          "kernels (default) or through NCCL")
     ap.add_argument("--attention-flags", type=lambda v: int(v, 0), default=0,
                     help="IREE_B200_ATTENTION_FLAG_* bits for the attention workloads")
-    ap.add_argument("--no-range-fusion", action="store_true",
-                    help="tp_decoder_layer: one all-reduce launch per chunk instead of one "
-                         "persistent launch per row-parallel GEMM")
+    ap.add_argument("--range-fusion", action="store_true",
+                    help="tp_decoder_layer: the unstaged recording (GEMM chunk, all-reduce, ...) "
+                         "with one persistent all-reduce launch per row-parallel GEMM, instead "
+                         "of the staged schedule")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the `also` (N=1) / `sharded` (N>1) lines of the default workload")
     ap.add_argument("--ar-blocks", type=int, default=0,
                     help="tp_decoder_layer: CTAs per symmetric all-reduce (0 = the reserved SMs)")
     ap.add_argument("--tp-chunks", type=int, default=4,

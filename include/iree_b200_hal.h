@@ -475,10 +475,27 @@ typedef struct iree_b200_symmetric_region_params_t {
 IREE_B200_API iree_b200_status_t iree_b200_channel_attach_symmetric_region(
     iree_b200_channel_t* channel, iree_b200_executable_t* executable,
     const iree_b200_symmetric_region_params_t* params);
+// Tuning and watchdog of the symmetric kernels are read from the environment at attach
+// time (every rank must see the same values):
+//   IREE_B200_ALL_REDUCE_TUNING="threads,unroll,pipelined"   block size (multiple of 32,
+//       <= 1024), 16-byte multimem requests in flight per thread (1 / 2 / 4 / 8) and whether
+//       the loads of step i+1 are issued before the stores of step i; default "1024,4,0".
+//   IREE_B200_COLLECTIVE_WATCHDOG_MS=<n>   a wait on a peer (or on a producer in a fused
+//       range launch) that lasts longer makes the launch record the reason and retire (no
+//       trap: the context stays usable; the channel must then be considered failed), readable
+//       with iree_b200_channel_query_collective_status. Default 0: wait indefinitely, as a
+//       NCCL collective does (ranks may legitimately be seconds apart: first-launch module
+//       load, a profiler replay, a long producer).
 // Number of collectives this channel has issued through the symmetric kernels / NCCL.
 IREE_B200_API void iree_b200_channel_query_collective_counts(const iree_b200_channel_t* channel,
                                                              uint64_t* out_symmetric,
                                                              uint64_t* out_nccl);
+
+// 0 while no symmetric kernel of this channel has timed out; otherwise reason (1 = a put to
+// a peer's flag word never succeeded, 2 = a peer never arrived, 3 = a fused range was never
+// released by its producer) | block index << 8. Reads device memory (synchronous, tiny).
+IREE_B200_API iree_b200_status_t iree_b200_channel_query_collective_status(
+    iree_b200_channel_t* channel, uint32_t* out_status);
 
 #ifdef __cplusplus
 }  // extern "C"

@@ -373,7 +373,27 @@ iree_b200_status_t iree_b200_channel_attach_symmetric_region(
     return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "max_blocks %d out of range [0, %d]",
                        params->max_blocks, Cfg::kMaxBlocks);
   }
-  uint64_t table[2 * Cfg::kMaxWorld + 2] = {0};  // + the "range ready" word, zeroed
+  // bases, flag blocks, then {ready word, status word} (zeroed) and the watchdog limit.
+  static_assert(Cfg::kTableBytes % 8 == 0 && Cfg::kWatchdogOffset % 8 == 0, "table layout");
+  uint64_t table[Cfg::kTableBytes / 8] = {0};
+  int32_t watchdog_ms = 0;
+  env_int("IREE_B200_COLLECTIVE_WATCHDOG_MS", &watchdog_ms);
+  if (watchdog_ms > 0) {
+    int clock_khz = 0;
+    const CudaSymbols* cu0 = channel->device->cu;
+    cu0->cuDeviceGetAttribute(&clock_khz, CU_DEVICE_ATTRIBUTE_CLOCK_RATE, channel->device->cu_device);
+    if (clock_khz <= 0) clock_khz = 2000000;
+    table[Cfg::kWatchdogOffset / 8] = (uint64_t)watchdog_ms * (uint64_t)clock_khz;
+  }
+  int32_t threads = Cfg::kThreads, unroll = Cfg::kUnroll, pipelined = 0;
+  if (const char* tuning = getenv("IREE_B200_ALL_REDUCE_TUNING")) {
+    if (sscanf(tuning, "%d,%d,%d", &threads, &unroll, &pipelined) < 1 || threads < 32 ||
+        threads > Cfg::kThreads || threads % 32 ||
+        !(unroll == 1 || unroll == 2 || unroll == 4 || unroll == 8) || (pipelined && unroll == 8)) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "IREE_B200_ALL_REDUCE_TUNING=\"%s\": want threads,unroll,pipelined", tuning);
+    }
+  }
   for (int r = 0; r < channel->count; ++r) {
     if (!params->peer_bases[r] || !params->peer_flag_blocks[r] || params->peer_bases[r] % 16 ||
         params->peer_flag_blocks[r] % 4) {
@@ -415,10 +435,31 @@ iree_b200_status_t iree_b200_channel_attach_symmetric_region(
   sym.multicast_base = (CUdeviceptr)params->multicast_base;
   sym.table = device_table;
   sym.max_blocks = params->max_blocks ? params->max_blocks : Cfg::kDefaultBlocks;
+  sym.threads = threads;
+  sym.tuning = (uint32_t)unroll | (pipelined ? 0x100u : 0u);
   sym.executable = executable;
   iree_b200_executable_retain(executable);
   for (int t = 0; t < 3; ++t) sym.all_reduce_sum[t] = functions[t];
   sym.attached = true;
+  return IREE_B200_STATUS_OK;
+}
+
+iree_b200_status_t iree_b200_channel_query_collective_status(iree_b200_channel_t* channel,
+                                                             uint32_t* out_status) {
+  B200_REQUIRE_ARG(channel && out_status);
+  *out_status = 0;
+  if (!channel->symmetric.attached) return IREE_B200_STATUS_OK;
+  const CudaSymbols* cu = channel->device->cu;
+  B200_CU(cu, cuCtxSetCurrent(channel->device->cu_context));
+  // On a stream of its own: the dispatch stream may be busy behind the very kernel asked about.
+  CUstream stream = nullptr;
+  B200_CU(cu, cuStreamCreate(&stream, CU_STREAM_NON_BLOCKING));
+  CUresult r = cu->cuMemcpyDtoHAsync(
+      out_status, channel->symmetric.table + b200::CollectiveConfig::kStatusOffset, sizeof(uint32_t),
+      stream);
+  if (r == CUDA_SUCCESS) r = cu->cuStreamSynchronize(stream);
+  cu->cuStreamDestroy(stream);
+  if (r != CUDA_SUCCESS) return cu_status(cu, r, "read of the collective status word", __FILE__, __LINE__);
   return IREE_B200_STATUS_OK;
 }
 

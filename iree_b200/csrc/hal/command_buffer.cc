@@ -272,7 +272,11 @@ bool symmetric_all_reduce_eligible(const Command& c, int* out_type_index) {
 // range c (c >= 1) is released by writing ready_base + c to the channel's ready word.
 iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index, CUstream stream,
                                                uint32_t chunks = 1, uint64_t chunk_stride = 0,
-                                               uint32_t ready_base = 0) {
+                                               uint32_t ready_base = 0,
+                                               CUDA_KERNEL_NODE_PARAMS* out_node_params = nullptr,
+                                               CUgraph graph = nullptr,
+                                               const CUgraphNode* deps = nullptr,
+                                               size_t dep_count = 0, CUgraphNode* out_node = nullptr) {
   using Cfg = b200::CollectiveConfig;
   iree_b200_channel_t* channel = c.channel;
   const auto& sym = channel->symmetric;
@@ -281,16 +285,31 @@ iree_b200_status_t launch_symmetric_all_reduce(const Command& c, int type_index,
   uint64_t table = sym.table, multicast = sym.multicast_base;
   uint64_t byte_offset = c.target - sym.local_base;
   uint64_t vectors = c.element_count * collective_element_size(type) / 16;
-  uint64_t ready = sym.table + 2 * Cfg::kMaxWorld * sizeof(uint64_t);
+  uint64_t ready = sym.table + Cfg::kReadyOffset;
   int rank = channel->rank, world = channel->count;
+  uint32_t tuning = sym.tuning;
+  const uint32_t threads = (uint32_t)sym.threads, unroll = std::max<uint32_t>(1, tuning & 0xff);
   // Every rank derives the same grid from the same element count (the flag words are per
   // block index, so the grids must agree across ranks).
   const uint64_t per_rank = (vectors + world - 1) / world;
-  const uint64_t want = (per_rank + Cfg::kThreads * Cfg::kUnroll - 1) / (Cfg::kThreads * Cfg::kUnroll);
+  const uint64_t want = (per_rank + threads * unroll - 1) / (threads * unroll);
   const uint32_t blocks = (uint32_t)std::max<uint64_t>(1, std::min<uint64_t>(want, sym.max_blocks));
-  void* params[] = {&table, &multicast, &byte_offset, &vectors, &chunks, &chunk_stride,
-                    &ready,  &ready_base, &rank,       &world};
-  B200_CU(cu, cuLaunchKernel(sym.all_reduce_sum[type_index], blocks, 1, 1, Cfg::kThreads, 1, 1, 0,
+  void* params[] = {&table, &multicast,  &byte_offset, &vectors, &chunks, &chunk_stride,
+                    &ready, &ready_base, &rank,        &world,   &tuning};
+  if (out_node_params) {
+    // Graph command buffers: the same launch as a kernel node (cuGraphAddKernelNode copies
+    // the parameter values, so stack storage is enough).
+    memset(out_node_params, 0, sizeof(*out_node_params));
+    out_node_params->func = sym.all_reduce_sum[type_index];
+    out_node_params->gridDimX = blocks;
+    out_node_params->gridDimY = out_node_params->gridDimZ = 1;
+    out_node_params->blockDimX = threads;
+    out_node_params->blockDimY = out_node_params->blockDimZ = 1;
+    out_node_params->kernelParams = params;
+    B200_CU(cu, cuGraphAddKernelNode(out_node, graph, deps, dep_count, out_node_params));
+    return IREE_B200_STATUS_OK;
+  }
+  B200_CU(cu, cuLaunchKernel(sym.all_reduce_sum[type_index], blocks, 1, 1, threads, 1, 1, 0,
                              stream, params, nullptr));
   return IREE_B200_STATUS_OK;
 }
@@ -414,6 +433,8 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
     }
   }
   iree_b200_status_t status = IREE_B200_STATUS_OK;
+  // Fused launches whose ranges have not all been released yet: (leader index, released).
+  std::vector<std::pair<size_t, uint32_t>> open_groups;
   auto run = [&]() -> iree_b200_status_t {
     for (size_t index = 0; index < n; ++index) {
       const Command& c = cb->commands[index];
@@ -428,16 +449,19 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
                                                          device->collective_stream, chunks_of[index],
                                                          stride_of[index], ready_base));
         pending_join = true;
+        open_groups.emplace_back(index, 0u);
         c.channel->symmetric_collectives.fetch_add(1);
         continue;
       }
       if (c.kind == CommandKind::kCollective && chunk_of[index] > 0) {
         // Range |chunk_of| is complete on this rank once everything queued so far is.
-        const CUdeviceptr ready = c.channel->symmetric.table +
-                                  2 * b200::CollectiveConfig::kMaxWorld * sizeof(uint64_t);
+        const CUdeviceptr ready = c.channel->symmetric.table + b200::CollectiveConfig::kReadyOffset;
         B200_CU(cu, cuStreamWriteValue32(device->dispatch_stream, ready,
                                          base_of[leader_of[index]] + (uint32_t)chunk_of[index],
                                          CU_STREAM_WRITE_VALUE_DEFAULT));
+        for (auto& g : open_groups) {
+          if (g.first == leader_of[index]) g.second = (uint32_t)chunk_of[index];
+        }
         c.channel->symmetric_collectives.fetch_add(1);
         continue;
       }
@@ -481,6 +505,19 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
   };
   status = run();
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (status != IREE_B200_STATUS_OK) {
+    // A persistent all-reduce launched above may still be waiting for ranges whose release
+    // was never queued: release them now (the data is garbage, the status says so) so that
+    // the kernel retires instead of spinning under the caller's wait_idle.
+    for (const auto& g : open_groups) {
+      const Command& lead = cb->commands[g.first];
+      const uint32_t last = chunks_of[g.first] - 1;
+      if (g.second >= last) continue;
+      cu->cuStreamWriteValue32(device->dispatch_stream,
+                               lead.channel->symmetric.table + b200::CollectiveConfig::kReadyOffset,
+                               base_of[g.first] + last, CU_STREAM_WRITE_VALUE_DEFAULT);
+    }
+  }
   if (fork_event) cu->cuEventDestroy(fork_event);
   if (join_event) cu->cuEventDestroy(join_event);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
@@ -553,10 +590,34 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
   std::vector<const Command*> batch;  // collectives recorded since the last other command
   auto flush_batch = [&]() -> iree_b200_status_t {
     if (batch.empty()) return IREE_B200_STATUS_OK;
+    // In-place all_reduce(sum) inside an attached symmetric region: a plain kernel node of
+    // our NVLink kernel (where the reference has UNIMPLEMENTED, graph_command_buffer.c:
+    // 291-327); everything else is captured from NCCL into one child graph.
+    std::vector<const Command*> for_nccl;
+    for (const Command* c : batch) {
+      int type_index = -1;
+      if (!symmetric_all_reduce_eligible(*c, &type_index)) {
+        for_nccl.push_back(c);
+        continue;
+      }
+      CUDA_KERNEL_NODE_PARAMS p;
+      CUgraphNode node = nullptr;
+      iree_b200_status_t status = launch_symmetric_all_reduce(
+          *c, type_index, nullptr, 1, 0, 0, &p, cb->graph, barrier ? &barrier : nullptr,
+          barrier ? 1 : 0, &node);
+      if (status != IREE_B200_STATUS_OK) {
+        batch.clear();
+        return status;
+      }
+      c->channel->symmetric_collectives.fetch_add(1);
+      group.push_back(node);
+      ++node_count;
+    }
+    batch.clear();
+    if (for_nccl.empty()) return IREE_B200_STATUS_OK;
     CUgraphNode node = nullptr;
     iree_b200_status_t status =
-        capture_collectives(cb, batch, barrier ? &barrier : nullptr, barrier ? 1 : 0, &node);
-    batch.clear();
+        capture_collectives(cb, for_nccl, barrier ? &barrier : nullptr, barrier ? 1 : 0, &node);
     if (status != IREE_B200_STATUS_OK) return status;
     group.push_back(node);
     ++node_count;

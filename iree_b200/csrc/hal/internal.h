@@ -274,6 +274,8 @@ struct iree_b200_channel_t : b200hal::RefCounted {
                             // "range ready" word of fused multi-range launches (offset 128)
     uint32_t ready_sequence = 0;  // last value written to / expected in that word
     int32_t max_blocks = 0;
+    int32_t threads = 0;   // block size of the all-reduce launches
+    uint32_t tuning = 0;   // kernel |tuning| parameter (unroll | pipelined << 8)
     iree_b200_executable_t* executable = nullptr;
     CUfunction all_reduce_sum[3] = {nullptr, nullptr, nullptr};  // f16, bf16, f32
   } symmetric;

@@ -14,6 +14,14 @@ struct CollectiveConfig {
   static constexpr int kUnroll = 4;      // 16-byte multimem requests in flight per thread
   static constexpr int kFlagBytes = kMaxBlocks * kMaxWorld * 4;
   static constexpr int kDefaultBlocks = 16;
+  // Device table: bases[kMaxWorld], flag_blocks[kMaxWorld] (u64 each), then
+  // {u32 ready, u32 status, u64 watchdog_cycles}.
+  static constexpr int kTableBytes = 2 * kMaxWorld * 8 + 16;
+  static constexpr int kReadyOffset = 2 * kMaxWorld * 8;
+  static constexpr int kStatusOffset = kReadyOffset + 4;
+  static constexpr int kWatchdogOffset = kReadyOffset + 8;
+  // Status word values (low byte) left by a watchdog expiry.
+  static constexpr uint32_t kStatusPutStuck = 1, kStatusWaitStuck = 2, kStatusNeverReady = 3;
 };
 
 }  // namespace b200

@@ -31,6 +31,17 @@
 //               instead of twice per launch, and there is no launch gap between ranges.
 //   ready, ready_base
 //   rank, world
+//   tuning      bits 0-7: 16-byte multimem requests in flight per thread (1, 2, 4 or 8;
+//               0 = CollectiveConfig::kUnroll); bit 8: software-pipelined (the loads of
+//               step i+1 are issued before the stores of step i, so the switch's reduce
+//               traffic and its broadcast traffic overlap on the two link directions).
+//               The block size is the launch's blockDim.x. Every rank passes the same values.
+// Watchdog: off unless the table's |watchdog_cycles| is non-zero (set at attach from
+// IREE_B200_COLLECTIVE_WATCHDOG_MS). A spin that exceeds it records why in the table's
+// status word (host-readable: iree_b200_channel_query_collective_status) and the launch
+// retires without touching more data — no trap, the context stays usable; the channel is
+// then failed (its flag words are in an unknown state). Without a limit a missing peer is
+// waited for indefinitely, as NCCL does.
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -46,58 +57,71 @@ using b200::CollectiveConfig;
 struct PeerTable {
   uint64_t bases[CollectiveConfig::kMaxWorld];
   uint64_t flag_blocks[CollectiveConfig::kMaxWorld];
+  uint32_t ready;             // "range c is ready" word of fused launches
+  uint32_t status;            // 0, or CollectiveConfig::kStatus* | block << 8 after a timeout
+  uint64_t watchdog_cycles;   // 0 = wait forever
 };
+static_assert(sizeof(PeerTable) == CollectiveConfig::kTableBytes, "table layout");
 
 enum : int { kF16 = 0, kBF16 = 1, kF32 = 2 };
 
-constexpr long long kWatchdogCycles = 6000000000ll;  // ~3 s: trap instead of hanging the box
+// A spin outlived the watchdog: leave the reason where the host can read it; the caller
+// then winds the block down.
+__device__ __noinline__ void watchdog_expired(const PeerTable* table, uint32_t what) {
+  atomicCAS(const_cast<uint32_t*>(&table->status), 0u, what | ((uint32_t)blockIdx.x << 8));
+  __threadfence_system();
+}
 
-__device__ __forceinline__ void put_flag(uint32_t* addr) {
+// Both return false when the watchdog ended the spin.
+__device__ __forceinline__ bool put_flag(const PeerTable* table, uint32_t* addr) {
   uint32_t old;
   const long long start = clock64();
+  const long long limit = (long long)table->watchdog_cycles;
   do {
     asm volatile("atom.global.release.sys.cas.b32 %0, [%1], 0, 1;"
                  : "=r"(old)
                  : "l"(addr)
                  : "memory");
-    if (old != 0 && clock64() - start > kWatchdogCycles) {
-      printf("b200 watchdog: symmetric all-reduce put stuck (block %d thread %d)\n",
-             (int)blockIdx.x, (int)threadIdx.x);
-      __trap();
+    if (old != 0 && limit && clock64() - start > limit) {
+      watchdog_expired(table, CollectiveConfig::kStatusPutStuck);
+      return false;
     }
   } while (old != 0);
+  return true;
 }
 
-__device__ __forceinline__ void wait_flag(uint32_t* addr) {
+__device__ __forceinline__ bool wait_flag(const PeerTable* table, uint32_t* addr) {
   uint32_t old;
   const long long start = clock64();
+  const long long limit = (long long)table->watchdog_cycles;
   do {
     asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], 1, 0;"
                  : "=r"(old)
                  : "l"(addr)
                  : "memory");
-    if (old != 1 && clock64() - start > kWatchdogCycles) {
-      printf("b200 watchdog: symmetric all-reduce wait stuck (block %d thread %d)\n",
-             (int)blockIdx.x, (int)threadIdx.x);
-      __trap();
+    if (old != 1 && limit && clock64() - start > limit) {
+      watchdog_expired(table, CollectiveConfig::kStatusWaitStuck);
+      return false;
     }
   } while (old != 1);
+  return true;
 }
 
 // Block |blockIdx.x| of every rank meets here. Callers fence (system scope) their own
 // writes before, so that the release of the put covers the whole block's traffic.
-__device__ __forceinline__ void meet_all_ranks(const PeerTable* table, int rank, int world) {
+// Returns false (to every thread of the block) when the watchdog gave up on a peer.
+__device__ __forceinline__ bool meet_all_ranks(const PeerTable* table, int rank, int world) {
   __syncthreads();
+  bool ok = true;
   if ((int)threadIdx.x < world) {
     const int peer = threadIdx.x;
     uint32_t* theirs = reinterpret_cast<uint32_t*>(table->flag_blocks[peer]) +
                        blockIdx.x * CollectiveConfig::kMaxWorld + rank;
     uint32_t* mine = reinterpret_cast<uint32_t*>(table->flag_blocks[rank]) +
                      blockIdx.x * CollectiveConfig::kMaxWorld + peer;
-    put_flag(theirs);
-    wait_flag(mine);
+    ok = put_flag(table, theirs) && wait_flag(table, mine);
   }
-  __syncthreads();
+  return __syncthreads_and(ok) != 0;
 }
 
 template <int kType>
@@ -191,19 +215,13 @@ __device__ __forceinline__ uint4 round_result(const float (&acc)[8]) {
 }
 
 // Slice of rank r: vectors [r*per, min(vectors, (r+1)*per)), per = ceil(vectors / world).
-template <int kType, bool kNvls>
-__device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table,
-                                             uint64_t multicast, uint64_t byte_offset,
-                                             uint64_t vectors, int rank, int world) {
-  constexpr int kUnroll = CollectiveConfig::kUnroll;
-  const uint64_t per = (vectors + world - 1) / world;
-  const uint64_t begin = min(vectors, (uint64_t)rank * per);
-  const uint64_t end = min(vectors, begin + per);
+template <int kType, int kUnroll, bool kPipelined>
+__device__ __forceinline__ void reduce_slice_nvls(uint64_t base, uint64_t begin, uint64_t end) {
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-  const uint64_t first = begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if constexpr (kNvls) {
-    const uint64_t base = multicast + byte_offset;
-    for (uint64_t i = first; i < end; i += stride * kUnroll) {
+  const uint64_t step = stride * kUnroll;
+  uint64_t i = begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if constexpr (!kPipelined) {
+    for (; i < end; i += step) {
       uint4 v[kUnroll];
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
@@ -215,6 +233,60 @@ __device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table
       }
     }
   } else {
+    if (i >= end) return;
+    uint4 cur[kUnroll], next[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (i + u * stride < end) cur[u] = multimem_ld_reduce<kType>(base + (i + u * stride) * 16);
+    }
+    for (;;) {
+      const uint64_t n = i + step;
+      if (n < end) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          if (n + u * stride < end) next[u] = multimem_ld_reduce<kType>(base + (n + u * stride) * 16);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (i + u * stride < end) multimem_st(base + (i + u * stride) * 16, cur[u]);
+      }
+      if (n >= end) break;
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) cur[u] = next[u];
+      i = n;
+    }
+  }
+}
+
+template <int kType, bool kNvls>
+__device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table,
+                                             uint64_t multicast, uint64_t byte_offset,
+                                             uint64_t vectors, int rank, int world,
+                                             uint32_t tuning) {
+  const uint64_t per = (vectors + world - 1) / world;
+  const uint64_t begin = min(vectors, (uint64_t)rank * per);
+  const uint64_t end = min(vectors, begin + per);
+  if constexpr (kNvls) {
+    const uint64_t base = multicast + byte_offset;
+    const uint32_t unroll = tuning & 0xff;
+    if (tuning & 0x100) {
+      switch (unroll) {
+        case 1: reduce_slice_nvls<kType, 1, true>(base, begin, end); break;
+        case 2: reduce_slice_nvls<kType, 2, true>(base, begin, end); break;
+        default: reduce_slice_nvls<kType, 4, true>(base, begin, end); break;
+      }
+    } else {
+      switch (unroll) {
+        case 1: reduce_slice_nvls<kType, 1, false>(base, begin, end); break;
+        case 2: reduce_slice_nvls<kType, 2, false>(base, begin, end); break;
+        case 8: reduce_slice_nvls<kType, 8, false>(base, begin, end); break;
+        default: reduce_slice_nvls<kType, CollectiveConfig::kUnroll, false>(base, begin, end); break;
+      }
+    }
+  } else {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t first = begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     for (uint64_t i = first; i < end; i += stride) {
       float acc[8];
 #pragma unroll
@@ -237,21 +309,24 @@ __device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table
   }
 }
 
-__device__ __forceinline__ void wait_ready(const uint32_t* ready, uint32_t value) {
+__device__ __forceinline__ bool wait_ready(const PeerTable* table, const uint32_t* ready,
+                                           uint32_t value) {
+  bool ok = true;
   if (threadIdx.x == 0) {
     const long long start = clock64();
+    const long long limit = (long long)table->watchdog_cycles;
     for (;;) {
       uint32_t now;
       asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(now) : "l"(ready) : "memory");
       if ((int32_t)(now - value) >= 0) break;
-      if (clock64() - start > kWatchdogCycles) {
-        printf("b200 watchdog: all-reduce range never became ready (block %d, want %u, have %u)\n",
-               (int)blockIdx.x, value, now);
-        __trap();
+      if (limit && clock64() - start > limit) {
+        watchdog_expired(table, CollectiveConfig::kStatusNeverReady);
+        ok = false;
+        break;
       }
     }
   }
-  __syncthreads();
+  return __syncthreads_and(ok) != 0;
 }
 
 template <int kType, bool kNvls>
@@ -259,13 +334,14 @@ __device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict_
                                                     uint64_t multicast, uint64_t byte_offset,
                                                     uint64_t vectors, uint32_t chunks,
                                                     uint64_t chunk_stride, const uint32_t* ready,
-                                                    uint32_t ready_base, int rank, int world) {
+                                                    uint32_t ready_base, int rank, int world,
+                                                    uint32_t tuning) {
   for (uint32_t c = 0; c < chunks; ++c) {
-    if (c > 0) wait_ready(ready, ready_base + c);
+    if (c > 0 && !wait_ready(table, ready, ready_base + c)) return;
     // Every rank's producer of range c has finished.
-    meet_all_ranks(table, rank, world);
+    if (!meet_all_ranks(table, rank, world)) return;
     reduce_slice<kType, kNvls>(table, multicast, byte_offset + c * chunk_stride, vectors, rank,
-                               world);
+                               world, tuning);
   }
   // Every slice of every range has landed everywhere.
   __threadfence_system();
@@ -279,19 +355,19 @@ __device__ __forceinline__ void all_reduce_sum_body(const PeerTable* __restrict_
       iree_b200_all_reduce_sum_##SUFFIX##_nvls(                                                 \
           const void* table, uint64_t multicast, uint64_t byte_offset, uint64_t vectors,        \
           uint32_t chunks, uint64_t chunk_stride, const uint32_t* ready, uint32_t ready_base,   \
-          int rank, int world) {                                                                \
+          int rank, int world, uint32_t tuning) {                                               \
     all_reduce_sum_body<TYPE, true>(static_cast<const PeerTable*>(table), multicast,            \
                                     byte_offset, vectors, chunks, chunk_stride, ready,          \
-                                    ready_base, rank, world);                                   \
+                                    ready_base, rank, world, tuning);                           \
   }                                                                                             \
   extern "C" __global__ void __launch_bounds__(b200::CollectiveConfig::kThreads)                \
       iree_b200_all_reduce_sum_##SUFFIX##_p2p(                                                  \
           const void* table, uint64_t multicast, uint64_t byte_offset, uint64_t vectors,        \
           uint32_t chunks, uint64_t chunk_stride, const uint32_t* ready, uint32_t ready_base,   \
-          int rank, int world) {                                                                \
+          int rank, int world, uint32_t tuning) {                                               \
     all_reduce_sum_body<TYPE, false>(static_cast<const PeerTable*>(table), multicast,           \
                                      byte_offset, vectors, chunks, chunk_stride, ready,         \
-                                     ready_base, rank, world);                                  \
+                                     ready_base, rank, world, tuning);                          \
   }
 
 B200_ALL_REDUCE(f16, kF16)

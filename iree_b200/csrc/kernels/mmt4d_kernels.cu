@@ -22,8 +22,14 @@
 // accumulate into out). workgroup_size = [256,1,1]; workgroup count =
 // [ceil(N1*N0/64), ceil(M1*M0/64), 1]: a block owns a 64x64 region of the logical
 // [M1*M0, N1*N0] result, k accumulated in ascending order exactly as the reference loops do,
-// so results are bit-identical for any input whose f32 products are exact (all f16 / bf16
-// products are) and for every i8 input.
+// so THIS kernel's results are bit-identical to iree_uk_mmt4d's generic tiles for any input
+// whose f32 products are exact (all f16 / bf16 products are) and for every i8 input.
+// The tensor-core route the ops layer takes for tile-filling shapes (relayout -> tcgen05 GEMM
+// -> relayout, ops.cc) accumulates in f32 in the tensor core's order instead: bit-identical
+// for i8 and for inputs whose partial sums are exact (the reference generator's), within
+// f32 summation-order error (<= 1e-5 of the result's scale; tests/test_zz_mmt4d_gpu.py::
+// test_tensor_route_vs_simt_on_random_data) otherwise. IREE_B200_MATMUL_FLAG_FORCE_GENERIC
+// keeps a call on this kernel.
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>

@@ -829,36 +829,36 @@ iree_b200_status_t iree_b200_ops_matmul_bias_host(iree_b200_ops_t* ops, int32_t 
 static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   std::lock_guard<std::mutex> lock(ops->pending_mutex);  // not host_mutex: the host call holds that
   if (ops->pending_executable) return IREE_B200_STATUS_OK;
+  // Everything is looked up into locals first; the executable and its ordinals are published
+  // together only when all of them resolved, so a failed load can never leave a half
+  // initialised table behind a non-null |pending_executable| (later calls would dispatch
+  // ordinal -1).
+  iree_b200_executable_t* executable = nullptr;
   B200_RETURN_IF_ERROR(iree_b200_executable_cache_prepare_executable(
       ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
-      &ops->pending_executable));
-  ops->mxfp4_generic_export = lookup(ops->pending_executable, "iree_b200_matmul_generic_mxfp4_f32");
-  ops->mxfp4_dequant_export =
-      lookup(ops->pending_executable, "iree_b200_matmul_mxfp4_dequant_bf16");
-  if (ops->mxfp4_generic_export < 0 || ops->mxfp4_dequant_export < 0) {
-    return make_status(IREE_B200_STATUS_NOT_FOUND, "the MX executable has no mxfp4 export");
-  }
-  static const char* const kMmt4dNames[3] = {"iree_b200_mmt4d_generic_i8_i32",
-                                             "iree_b200_mmt4d_generic_f16_f32",
-                                             "iree_b200_mmt4d_generic_bf16_f32"};
-  for (int i = 0; i < 3; ++i) {
-    ops->mmt4d_generic_exports[i] = lookup(ops->pending_executable, kMmt4dNames[i]);
-    if (ops->mmt4d_generic_exports[i] < 0) {
+      &executable));
+  static const char* const kNames[8] = {
+      "iree_b200_matmul_generic_mxfp4_f32", "iree_b200_matmul_mxfp4_dequant_bf16",
+      "iree_b200_mmt4d_generic_i8_i32",     "iree_b200_mmt4d_generic_f16_f32",
+      "iree_b200_mmt4d_generic_bf16_f32",   "iree_b200_mmt4d_relayout_b8",
+      "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32"};
+  int32_t ordinals[8];
+  for (int i = 0; i < 8; ++i) {
+    ordinals[i] = lookup(executable, kNames[i]);
+    if (ordinals[i] < 0) {
+      iree_b200_executable_release(executable);
       return make_status(IREE_B200_STATUS_NOT_FOUND, "the second executable has no %s export",
-                         kMmt4dNames[i]);
+                         kNames[i]);
     }
   }
-  static const char* const kRelayoutNames[3] = {"iree_b200_mmt4d_relayout_b8",
-                                                "iree_b200_mmt4d_relayout_b16",
-                                                "iree_b200_mmt4d_relayout_b32"};
+  ops->mxfp4_generic_export = ordinals[0];
+  ops->mxfp4_dequant_export = ordinals[1];
   for (int i = 0; i < 3; ++i) {
-    ops->mmt4d_relayout_exports[i] = lookup(ops->pending_executable, kRelayoutNames[i]);
-    if (ops->mmt4d_relayout_exports[i] < 0) {
-      return make_status(IREE_B200_STATUS_NOT_FOUND, "the second executable has no %s export",
-                         kRelayoutNames[i]);
-    }
+    ops->mmt4d_generic_exports[i] = ordinals[2 + i];
+    ops->mmt4d_relayout_exports[i] = ordinals[5 + i];
   }
+  ops->pending_executable = executable;
   return IREE_B200_STATUS_OK;
 }
 
@@ -881,9 +881,10 @@ static iree_b200_status_t record_matmul_mxfp4_impl(
     const iree_b200_buffer_ref_t* workspace) {
   B200_REQUIRE_ARG(ops && cb);
   B200_RETURN_IF_ERROR(require_device(ops));
-  if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
+  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
-                       "the MXFP4 matmul takes FLAG_ACCUMULATE only (operands are always [rows, K])");
+                       "the MXFP4 matmul takes FLAG_ACCUMULATE and FLAG_FORCE_GENERIC only "
+                       "(operands are always [rows, K])");
   }
   if (M < 0 || N < 0 || K < 0 || M > INT32_MAX || N > INT32_MAX || K > INT32_MAX ||
       K % IREE_B200_MX_BLOCK_SIZE) {
@@ -1013,7 +1014,10 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
-  const uint64_t ws_offset = total, ws_bytes = iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
+  const uint64_t ws_offset = total,
+                 ws_bytes = (flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC)
+                                ? 0
+                                : iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
   total += ws_bytes;
   iree_b200_command_buffer_t* cb = nullptr;
   auto run = [&]() -> iree_b200_status_t {
@@ -1072,8 +1076,9 @@ iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int
       return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                          "mmt4d takes i8, f16 or bf16 operands (got element type %d)", element_type);
   }
-  if (flags & ~(uint32_t)IREE_B200_MATMUL_FLAG_ACCUMULATE) {
-    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "mmt4d takes FLAG_ACCUMULATE only");
+  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "mmt4d takes FLAG_ACCUMULATE and FLAG_FORCE_GENERIC only");
   }
   if (M0 < 1 || N0 < 1 || K0 < 1 || M0 > 32767 || N0 > 32767 || K0 > 32767) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
@@ -1247,8 +1252,11 @@ iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t elemen
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
+  // FORCE_GENERIC keeps the call on the single SIMT dispatch (k-ascending accumulation).
   const uint64_t ws_offset = total,
-                 ws_bytes = iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
+                 ws_bytes = (flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC)
+                                ? 0
+                                : iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
   total += ws_bytes;
   iree_b200_command_buffer_t* cb = nullptr;
   auto run = [&]() -> iree_b200_status_t {

@@ -158,6 +158,7 @@ _STATUS_FUNCS = {
     "iree_b200_channel_provider_query_default_rank_and_count": [POINTER(c_int32),
                                                                 POINTER(c_int32)],
     "iree_b200_channel_provider_exchange_default_id": [c_int32, c_void_p],
+    "iree_b200_channel_query_collective_status": [c_void_p, POINTER(ctypes.c_uint32)],
     "iree_b200_channel_create": [c_void_p, POINTER(ChannelParams), POINTER(c_void_p)],
     "iree_b200_channel_split": [c_void_p, c_int32, c_int32, c_uint64, POINTER(c_void_p)],
     "iree_b200_channel_attach_symmetric_region": [c_void_p, c_void_p,
@@ -551,6 +552,12 @@ class Channel:
         flags = (c_uint64 * n)(*peer_flag_blocks)
         p = SymmetricRegionParams(byte_length, bases, multicast_base, flags, max_blocks)
         check(lib().iree_b200_channel_attach_symmetric_region(self._h, executable._h, byref(p)))
+
+    def collective_status(self) -> int:
+        """0, or why a symmetric kernel of this channel gave up (watchdog; see the header)."""
+        v = ctypes.c_uint32()
+        check(lib().iree_b200_channel_query_collective_status(self._h, byref(v)))
+        return v.value
 
     def collective_counts(self):
         a, b = c_uint64(), c_uint64()

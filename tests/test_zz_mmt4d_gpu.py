@@ -1,10 +1,7 @@
 """linalg.mmt4d on data-tiled operands, on the GPU, against the oracle (bit-exact) and the
 reference's own iree_uk_mmt4d when oracle/_ref travelled.
 
-PENDING VALIDATION: kernels/mmt4d_kernels.cu was written after this round's GPU budget was
-spent; its device code has run only on host threads under the mock driver
-(tests/mock_cuda/mock_suite.py::test_mmt4d_end_to_end_on_the_host, also under ASAN). Skipped
-unless IREE_B200_PENDING_VALIDATION=1; first thing next round: run, then drop the gate.
+First GPU run: round 2 (profiles/mmt4d_mxfp4_first_gpu_run_r2.json), bit-exact; ungated since.
 """
 
 import os
@@ -47,6 +44,40 @@ def test_mmt4d_vs_oracle(ops, t, case):
         assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
     if not accumulate:
         assert np.array_equal(oracle.unpack(out, M, N), oracle.matmul(t, lhs[None], rhs[None])[0])
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16", "i8"])
+def test_tensor_route_vs_simt_on_random_data(ops, t):
+    """Non-integer operands (N(0,1), where f32 partial sums round): the routed result (relayout
+    -> tcgen05 GEMM -> relayout) against the SIMT kernel's k-ascending result. i8 stays
+    bit-exact; f16 / bf16 differ by f32 summation order only: <= 1e-5 of the result's scale."""
+    M, K, N, M0, N0, K0 = 512, 1024, 384, 16, 16, 2
+    g = np.random.Generator(np.random.PCG64(0xB200))
+    if t == "i8":
+        lhs = g.integers(-128, 128, (M, K), dtype=np.int8)
+        rhs = g.integers(-128, 128, (K, N), dtype=np.int8)
+    else:
+        lhs = oracle.from_f32(t, g.standard_normal((M, K)).astype(np.float32))
+        rhs = oracle.from_f32(t, g.standard_normal((K, N)).astype(np.float32))
+    l4 = oracle.pack(lhs, M0, K0)
+    r4 = oracle.pack(np.ascontiguousarray(rhs.T), N0, K0)
+    M1, K1, N1 = l4.shape[0], l4.shape[1], r4.shape[0]
+    assert ops.mmt4d_workspace_size(t, M1, N1, K1, M0, N0, K0) != 0
+    dt = np.int32 if t == "i8" else np.float32
+    routed, simt = np.empty((M1, N1, M0, N0), dt), np.empty((M1, N1, M0, N0), dt)
+    before = ops.dispatch_count
+    ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, routed.ctypes.data)
+    assert ops.dispatch_count - before == 4
+    ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, simt.ctypes.data,
+                   flags=H.MATMUL_FORCE_GENERIC)
+    assert ops.dispatch_count - before == 5
+    want = oracle.mmt4d(t, l4, r4)
+    assert np.array_equal(simt, want)              # the SIMT kernel IS the reference order
+    if t == "i8":
+        assert np.array_equal(routed, want)
+    else:
+        scale = np.abs(want).max()
+        assert np.abs(routed - want).max() <= 1e-5 * scale
 
 
 def test_mmt4d_edge_cases(ops):

@@ -25,7 +25,11 @@ def main():
     ap.add_argument("--mib", type=int, default=64)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--max-blocks", type=int, default=0, help="CTAs per collective (0 = default 16)")
+    ap.add_argument("--sweep", default="",
+                    help="timing only: ';'-separated 'blocks,threads,unroll,pipelined' variants of "
+                         "the NVLS kernel (IREE_B200_ALL_REDUCE_TUNING per channel)")
     args = ap.parse_args()
+    os.environ.setdefault("IREE_B200_COLLECTIVE_WATCHDOG_MS", "30000")
     import torch
     import torch.distributed as dist
     rank, world, local = (int(os.environ[k]) for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
@@ -43,8 +47,11 @@ def main():
         dist.broadcast_object_list(ids, src=0)
         return hal.Channel(dev, rank=rank, count=world, id_bytes=ids[0])
 
-    ch_nvls, ch_p2p, ch_nccl = make_channel(), make_channel(), make_channel()
     data_bytes = args.mib << 20
+    if args.sweep:
+        return sweep(args, torch, dist, hal, symmetric, dev, ops, stream, make_channel, rank, world,
+                     local, data_bytes)
+    ch_nvls, ch_p2p, ch_nccl = make_channel(), make_channel(), make_channel()
     region = symmetric.SymmetricRegion(data_bytes, torch.device("cuda", local), flag_blocks=2)
     have_mc = region.multicast_base != 0
     if have_mc:
@@ -193,6 +200,64 @@ def main():
             print(f"rank {rank}: FAILED {f}", flush=True)
     dist.destroy_process_group()
     sys.exit(1 if failures else 0)
+
+
+def sweep(args, torch, dist, hal, symmetric, dev, ops, stream, make_channel, rank, world, local,
+          data_bytes):
+    variants = [tuple(int(x) for x in v.split(",")) for v in args.sweep.split(";") if v]
+    region = symmetric.SymmetricRegion(data_bytes, torch.device("cuda", local),
+                                       flag_blocks=len(variants))
+    assert region.multicast_base, "the sweep is of the NVLS kernel"
+    buf = dev.import_buffer(region.local_base, region.data_bytes)
+    region.tensor[:data_bytes].zero_()
+    op = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, "bf16")
+    results = []
+    with torch.cuda.stream(stream):
+        for i, (blocks, threads, unroll, pipelined) in enumerate(variants):
+            os.environ["IREE_B200_ALL_REDUCE_TUNING"] = f"{threads},{unroll},{pipelined}"
+            ch = make_channel()
+            region.attach(ch, ops.executable, flag_block=i, use_multicast=True, max_blocks=blocks)
+            row = {"blocks": blocks, "threads": threads, "unroll": unroll, "pipelined": pipelined}
+            # Parity first: x -> W*x on a ragged size.
+            count = (1 << 20) + 8 * 3
+            view = region.view(0, (count,), torch.bfloat16)
+            view.fill_(1.0)
+            dist.barrier()
+            cb = hal.CommandBuffer(dev).begin()
+            cb.collective(ch, op, 0, buf.ref(0, count * 2), buf.ref(0, count * 2), count)
+            cb.barrier()
+            cb.end()
+            dev.execute(cb)
+            dev.wait_idle()
+            row["exact"] = bool((view == float(world)).all()) and ch.collective_status() == 0
+            region.tensor[:data_bytes].zero_()
+            for nbytes, key in ((data_bytes, "ms"), (min(16 << 20, data_bytes), "ms_16mib")):
+                count = nbytes // 2
+                cb = hal.CommandBuffer(dev).begin()
+                cb.collective(ch, op, 0, buf.ref(0, nbytes), buf.ref(0, nbytes), count)
+                cb.barrier()
+                cb.end()
+                for _ in range(3):
+                    dev.execute(cb)
+                dev.wait_idle()
+                dist.barrier()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                for _ in range(args.iters):
+                    dev.execute(cb)
+                e1.record(stream)
+                dev.wait_idle()
+                torch.cuda.synchronize()
+                t = torch.tensor([e0.elapsed_time(e1) / args.iters], device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                row[key] = float(t.item())
+            row["algbw_gbs"] = data_bytes / (row["ms"] * 1e-3) / 1e9
+            results.append(row)
+    if rank == 0:
+        print(json.dumps({"world": world, "all_reduce_mib": args.mib, "dtype": "bf16",
+                          "sweep": results}), flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if all(r["exact"] for r in results) else 1)
 
 
 if __name__ == "__main__":
