@@ -406,13 +406,26 @@ def make_step(torch, hal, dev, ops, workload, seed):
     return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed)
 
 
-def time_steps(torch, works, steps, warmup, stream, world, sampler=None):
+def time_steps(torch, works, steps, warmup, stream, world, sampler=None, min_ms=0.0):
     """|warmup| untimed steps, then exactly |steps| between two CUDA events on |stream|,
-    bracketed by barrier + synchronize; returns ms per step, max over ranks."""
+    bracketed by barrier + synchronize; returns ms per step, max over ranks. |min_ms| > 0
+    (the extra lines only, never the headline): |steps| is raised so that the timed region
+    lasts at least that long — a 20 ms burst runs at 1965 MHz, before the power limiter has
+    settled, and reads 30-40 % above what the same kernel sustains."""
     sets = len(works)
     with torch.cuda.stream(stream):
         for i in range(warmup):
             works[i % sets].step()
+        if min_ms > 0:
+            barrier(world)
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record(stream)
+            for i in range(5):
+                works[i % sets].step()
+            p1.record(stream)
+            barrier(world)
+            pilot = max_over_ranks(p0.elapsed_time(p1), world) / 5
+            steps = int(max(steps, min(5000, -(-min_ms // max(pilot, 1e-3)))))
         barrier(world)
         if sampler is not None:
             sampler.start()
@@ -422,7 +435,8 @@ def time_steps(torch, works, steps, warmup, stream, world, sampler=None):
             works[i % sets].step()
         ev1.record(stream)
         barrier(world)
-    return max_over_ranks(ev0.elapsed_time(ev1), world) / steps
+    ms = max_over_ranks(ev0.elapsed_time(ev1), world) / steps
+    return (ms, steps) if min_ms > 0 else ms
 
 
 def rotating_sets(make, info_bytes):
@@ -486,6 +500,7 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
                          iree_b200_channel_t, + the step's GEMMs alone and collectives alone"""
     out = {}
     steps, warmup = max(10, min(args.steps, 50)), max(3, min(args.warmup, 5))
+    MIN = max(args.extra_min_ms, 1.0)   # every extra line is timed over at least this long (sustained)
     stream = torch.cuda.Stream()
     dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream)
     ops = hal.Ops(dev)
@@ -493,32 +508,33 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
     op, et, B, M, N, K = MATMUL_WORKLOADS["batch_matmul"]
     if B % world == 0:
         full = [MatmulStep(torch, hal, dev, ops, (op, et, B, M, N, K), seed=rank)]
-        t1 = time_steps(torch, full, steps, warmup, stream, world)
+        t1, _ = time_steps(torch, full, steps, warmup, stream, world, min_ms=MIN)
         del full
         torch.cuda.empty_cache()
         part = rotating_sets(lambda i: MatmulStep(torch, hal, dev, ops, (op, et, B // world, M, N, K),
                                                   seed=rank + 100 * i),
                              lambda w: w.describe()["bytes"])
-        tn = time_steps(torch, part, steps, warmup, stream, world)
+        tn, steps_n = time_steps(torch, part, steps, warmup, stream, world, min_ms=MIN)
         flop = 2.0 * B * M * N * K
         out["batch_matmul"] = {
             "workload": f"linalg.batch_matmul bf16 batch={B} M=N=K={M}, batch split {B // world} per GPU "
                         f"over {world} GPUs, no collective", "scaling": "strong",
             "value": flop / (tn * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": tn,
             "n1_ms_per_step": t1, "n1_value": flop / (t1 * 1e-3) / 1e12,
-            "efficiency": t1 / (world * tn), "steps": steps,
-            "roofline_frac": flop / world / (tn * 1e-3) / 1e12 / peaks["bf16_tflops"]}
+            "efficiency": t1 / (world * tn), "steps": steps_n, "timed_region_ms": tn * steps_n,
+            "roofline_frac": flop / world / (tn * 1e-3) / 1e12 / peaks["bf16_tflops"],
+            "roofline_frac_of_sustained": flop / world / (tn * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]}
         del part
         torch.cuda.empty_cache()
     # ---- configs[4]
     solo = TpLayerStep(torch, hal, dev, ops, 1, 0, None, seed=rank)
-    t1 = time_steps(torch, [solo], steps, warmup, stream, world)
+    t1, _ = time_steps(torch, [solo], steps, warmup, stream, world, min_ms=MIN)
     layer_flop = solo.flop
     del solo
     torch.cuda.empty_cache()
     tstream, tdev, tops, channel, region = make_tp_device(torch, hal, args, world, rank, local)
     step = TpLayerStep(torch, hal, tdev, tops, world, rank, channel, seed=rank, region=region)
-    tn = time_steps(torch, [step], steps, warmup, tstream, world)
+    tn, steps_n = time_steps(torch, [step], steps, warmup, tstream, world, min_ms=MIN)
     info = step.describe()
     # The step's two halves alone: GEMMs without collectives, collectives without GEMMs.
     from iree_b200 import tp_layer
@@ -526,16 +542,16 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
               chunks=TpLayerStep.CHUNKS, region=region, seed=rank, chunk_consumers=TpLayerStep.STAGED)
     gemms = tp_layer.DecoderLayerGemms(torch, hal, tdev, tops, world, rank, channel,
                                        only="gemms", **kw)
-    t_gemm = time_steps(torch, [gemms], steps, warmup, tstream, world)
+    t_gemm, _ = time_steps(torch, [gemms], steps, warmup, tstream, world, min_ms=MIN)
     colls = tp_layer.DecoderLayerGemms(torch, hal, tdev, tops, world, rank, channel,
                                        only="collectives", **kw)
-    t_coll = time_steps(torch, [colls], steps, warmup, tstream, world)
+    t_coll, _ = time_steps(torch, [colls], steps, warmup, tstream, world, min_ms=MIN / 2)
     payload = 2.0 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2   # two [tokens, hidden] bf16
     out["tp_decoder_layer"] = {
         "workload": info["workload"], "scaling": "strong",
         "value": layer_flop / (tn * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": tn,
         "n1_ms_per_step": t1, "n1_value": layer_flop / (t1 * 1e-3) / 1e12,
-        "efficiency": t1 / (world * tn), "steps": steps,
+        "efficiency": t1 / (world * tn), "steps": steps_n, "timed_region_ms": tn * steps_n,
         "gemm_ms": t_gemm, "collective_ms": t_coll,
         "overlap_frac": max(0.0, (t_gemm + t_coll - tn) / max(1e-9, min(t_gemm, t_coll))),
         "collective": {"what": f"{step.collectives} x all_reduce(sum, bf16) = {payload / 2**20:.0f} MiB "
@@ -559,21 +575,22 @@ def also_lines(torch, hal, dev, ops, stream, args, peaks):
     for name in ALSO_WORKLOADS:
         works = rotating_sets(lambda i: make_step(torch, hal, dev, ops, name, seed=100 * i),
                               lambda w: w.describe()["bytes"])
-        ms = time_steps(torch, works, steps, warmup, stream, 1)
+        ms, steps_n = time_steps(torch, works, steps, warmup, stream, 1, min_ms=max(args.extra_min_ms, 1.0))
         info = works[0].describe()
         tflops = info["flop"] / (ms * 1e-3) / 1e12
         roof = roofline_of(info, tflops, ms, peaks)
         out[name] = {"workload": info["workload"], "value": tflops, "unit": "TFLOP/s",
-                     "ms_per_step": ms, "steps": steps, "dtype": info["dtype"],
+                     "ms_per_step": ms, "steps": steps_n, "timed_region_ms": ms * steps_n,
+                     "dtype": info["dtype"],
                      "launches_per_step": works[0].launches_per_step,
                      "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "unit", "frac")}}
         del works
         torch.cuda.empty_cache()
     solo = TpLayerStep(torch, hal, dev, ops, 1, 0, None, seed=0)
-    ms = time_steps(torch, [solo], steps, warmup, stream, 1)
+    ms, steps_n = time_steps(torch, [solo], steps, warmup, stream, 1, min_ms=max(args.extra_min_ms, 1.0))
     tflops = solo.flop / (ms * 1e-3) / 1e12
     out["tp_decoder_layer_n1"] = {"workload": solo.describe()["workload"], "value": tflops,
-                                  "unit": "TFLOP/s", "ms_per_step": ms, "steps": steps,
+                                  "unit": "TFLOP/s", "ms_per_step": ms, "steps": steps_n,
                                   "roofline": {"bound": "tensor", "frac": tflops / peaks["bf16_tflops"]}}
     return out
 
@@ -843,6 +860,8 @@ def main():
                     help="tp_decoder_layer: the unstaged recording (GEMM chunk, all-reduce, ...) "
                          "with one persistent all-reduce launch per row-parallel GEMM, instead "
                          "of the staged schedule")
+    ap.add_argument("--extra-min-ms", type=float, default=200.0,
+                    help="minimum timed region of each `also` / `sharded` line")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the `also` (N=1) / `sharded` (N>1) lines of the default workload")
     ap.add_argument("--ar-blocks", type=int, default=0,
