@@ -60,7 +60,13 @@ ATTENTION_WORKLOADS = {
     "attention_prefill": ("attention", "f16", 32, 4096, 4096, 128),
     "attention_prefill_bf16": ("attention", "bf16", 32, 4096, 4096, 128),
     "attention_decode": ("attention", "f16", 32, 1, 8192, 128),
+    # The same prefill with the mask real Llama prefill carries: causal, computed in the kernel
+    # (IREE_B200_ATTENTION_MASK_CAUSAL), masked K2 blocks skipped. Algorithmic FLOP count only
+    # the unmasked (m, k2) pairs ("no causal discount unless a mask is present").
+    "attention_prefill_causal": ("attention", "f16", 32, 4096, 4096, 128),
+    "attention_prefill_causal_bf16": ("attention", "bf16", 32, 4096, 4096, 128),
 }
+CAUSAL_WORKLOADS = {"attention_prefill_causal", "attention_prefill_causal_bf16"}
 
 
 def load_peaks():
@@ -294,9 +300,11 @@ class AttentionStep:
     """iree_linalg_ext.attention, one recorded command buffer (1 or 2 dispatches)."""
     FLAGS = 0  # --attention-flags (diagnostics: kernel family / exp2 split)
 
-    def __init__(self, torch, hal, dev, ops, spec, seed):
+    def __init__(self, torch, hal, dev, ops, spec, seed, causal=False):
         op, et, B, M, K2, D = spec
         self.spec = spec
+        self.causal = causal
+        self.mask_kind = hal.ATTENTION_MASK_CAUSAL if causal else hal.ATTENTION_MASK_NONE
         g = torch.Generator(device="cuda")
         g.manual_seed(0xB200 + seed)
         dt = torch.bfloat16 if et == "bf16" else torch.float16
@@ -304,7 +312,8 @@ class AttentionStep:
         self.tensors = [mk(B, M, D), mk(B, K2, D), mk(B, K2, D),
                         torch.empty((B, M, D), dtype=dt, device="cuda")]
         self.scale = 1.0 / (D ** 0.5)
-        sel = ops.select_attention(et, B, M, D, K2, D, self.scale, flags=self.FLAGS)
+        sel = ops.select_attention(et, B, M, D, K2, D, self.scale, mask_kind=self.mask_kind,
+                                   flags=self.FLAGS)
         self.workspace = torch.empty((max(sel["workspace_bytes"], 16),), dtype=torch.uint8,
                                      device="cuda")
         imp = lambda t: dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
@@ -313,7 +322,8 @@ class AttentionStep:
         self.cb = hal.CommandBuffer(dev).begin()
         ops.record_attention(self.cb, et, B, M, D, K2, D, self.scale, self.buffers[0].ref(),
                              self.buffers[1].ref(), self.buffers[2].ref(), self.buffers[3].ref(),
-                             workspace=self.buffers[4].ref(), flags=self.FLAGS)
+                             workspace=self.buffers[4].ref(), mask_kind=self.mask_kind,
+                             flags=self.FLAGS)
         self.cb.end()
         self.launches_per_step = ops.dispatch_count - before
         self.dev = dev
@@ -330,15 +340,18 @@ class AttentionStep:
     def host_call(self, ops, host):
         op, et, B, M, K2, D = self.spec
         ops.attention_host(et, B, M, D, K2, D, self.scale, host[0].data_ptr(), host[1].data_ptr(),
-                           host[2].data_ptr(), host[3].data_ptr())
+                           host[2].data_ptr(), host[3].data_ptr(), mask_kind=self.mask_kind)
 
     def describe(self):
         op, et, B, M, K2, D = self.spec
         flop = 4.0 * B * M * K2 * D
+        if self.causal:   # only the unmasked pairs: row m sees m + (K2 - M) + 1 keys
+            flop = 4.0 * B * D * (M * (M + 1) / 2.0 + float(M) * (K2 - M))
         nbytes = float(B) * (2 * M * D + 2 * K2 * D) * 2
+        mask = "causal mask (k2 <= m + K2 - M) computed in the kernel" if self.causal else "no mask"
         return {"flop": flop, "bytes": nbytes, "bound": "hbm" if M <= 16 else "tensor",
                 "workload": f"iree_linalg_ext.attention {et} batch*heads={B} M={M} K2={K2} "
-                            f"K1=N={D} scale=1/sqrt({D}) no mask, per GPU",
+                            f"K1=N={D} scale=1/sqrt({D}) {mask}, per GPU",
                 "dtype": f"{et} (f32 S/softmax/accumulate)",
                 "h2d": int(B * (M * D + 2 * K2 * D) * 2), "d2h": int(B * M * D * 2),
                 "api": "iree_b200_ops_attention_host (pinned host buffers)"}
@@ -355,13 +368,14 @@ class TpLayerStep:
 
     TOKENS, HIDDEN, QKV, FFN, CHUNKS = 8192, 4096, 6144, 14336, 4
     STAGED = True
+    SCHEDULE = "dataflow"
 
     def __init__(self, torch, hal, dev, ops, world, rank, channel, seed, region=None):
         from iree_b200 import tp_layer
         self.layer = tp_layer.DecoderLayerGemms(
             torch, hal, dev, ops, world, rank, channel, tokens=self.TOKENS, hidden=self.HIDDEN,
             ffn=self.FFN, chunks=self.CHUNKS, region=region, seed=seed,
-            chunk_consumers=self.STAGED)
+            chunk_consumers=self.STAGED, schedule=self.SCHEDULE)
         assert self.layer.dims["qkv"] == self.QKV
         self.t, self.b, self.cb = self.layer.t, self.layer.b, self.layer.cb
         self.world, self.dev, self.channel, self.region = world, dev, channel, region
@@ -393,8 +407,8 @@ class TpLayerStep:
                             f"bf16 -> bf16 (f32 accumulate), tensor-parallel over {w} GPU(s), "
                             f"{self.collectives} all-reduce(sum, bf16, [{T // self.CHUNKS},{H}]) per "
                             f"step via iree_hal_channel ({self.layer.collective_path()}), "
-                            f"{len(self.layer.stages)} barrier-separated stages, collectives on "
-                            f"the collective stream beside the stage's GEMMs",
+                            f"schedule {self.SCHEDULE if w > 1 else 'sequence'}: collectives on "
+                            f"the collective stream beside the GEMMs that do not consume them",
                 "dtype": "bf16 (f32 accumulate)", "h2d": int(T * H * 2), "d2h": int(T * H * 2),
                 "api": "h2d(x) + iree_b200_device_queue_execute(layer command buffer) + d2h(y)"}
 
@@ -403,7 +417,8 @@ def make_step(torch, hal, dev, ops, workload, seed):
     if workload in MATMUL_WORKLOADS:
         return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed,
                           fused=workload in FUSED_WORKLOADS)
-    return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed)
+    return AttentionStep(torch, hal, dev, ops, ATTENTION_WORKLOADS[workload], seed,
+                         causal=workload in CAUSAL_WORKLOADS)
 
 
 def time_steps(torch, works, steps, warmup, stream, world, sampler=None, min_ms=0.0):
@@ -459,6 +474,56 @@ def roofline_of(info, per_gpu_tflops, ms_per_step, peaks):
             "peak_source": peaks["source"] + " copy"}
 
 
+def host_link_line(torch, world):
+    """The PCIe floor under `e2e`: H2D alone, D2H alone and both at once, 256 MiB pinned
+    buffers, every rank at the same time (aggregate = sum over ranks of bytes / slowest
+    rank's time). `e2e` moves its operands over this link inside the timed region, so its
+    scaling with N is bounded by how the aggregate scales — a property of the box (how many
+    GPUs share a host bridge / NUMA node), not of the kernels."""
+    n = 256 << 20
+    host_a = torch.empty(n, dtype=torch.uint8).pin_memory()
+    host_b = torch.empty(n, dtype=torch.uint8).pin_memory()
+    dev_a = torch.empty(n, dtype=torch.uint8, device="cuda")
+    dev_b = torch.empty(n, dtype=torch.uint8, device="cuda")
+    up, down = torch.cuda.Stream(), torch.cuda.Stream()
+    out = {}
+
+    def timed(fn, bytes_moved, reps=4):
+        fn()
+        barrier(world)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        torch.cuda.synchronize()
+        ms = max_over_ranks((time.perf_counter() - t0) * 1e3, world) / reps
+        return bytes_moved * world / (ms * 1e-3) / 1e9
+
+    def h2d():
+        with torch.cuda.stream(up):
+            dev_a.copy_(host_a, non_blocking=True)
+
+    def d2h():
+        with torch.cuda.stream(down):
+            host_b.copy_(dev_b, non_blocking=True)
+
+    def both():
+        h2d()
+        d2h()
+
+    def sync(fn):
+        def run():
+            fn()
+            torch.cuda.synchronize()
+        return run
+
+    out["h2d_gbs_aggregate"] = timed(sync(h2d), n)
+    out["d2h_gbs_aggregate"] = timed(sync(d2h), n)
+    out["duplex_gbs_aggregate_each_way"] = timed(sync(both), n)
+    out["ranks"] = world
+    out["what"] = "256 MiB pinned copies, all ranks concurrently; GB/s summed over ranks"
+    return out
+
+
 def make_tp_device(torch, hal, args, world, rank, local):
     """Device + ops + channel (+ symmetric region) for the tensor-parallel layer: two streams
     (overlap_collectives), a few SMs kept free of persistent GEMM CTAs for the collective
@@ -467,7 +532,7 @@ def make_tp_device(torch, hal, args, world, rank, local):
     stream = torch.cuda.Stream()
     overlap = 0
     if world > 1:
-        overlap = 1 if args.range_fusion else 2
+        overlap = {"fused": 1, "staged": 2, "dataflow": 3}[args.tp_schedule]
     dev = hal.Device(local, mode=hal.MODE_STREAM, external_stream=stream.cuda_stream,
                      overlap_collectives=overlap)
     ops = hal.Ops(dev)
@@ -486,7 +551,8 @@ def make_tp_device(torch, hal, args, world, rank, local):
             blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
             region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
     TpLayerStep.CHUNKS = args.tp_chunks
-    TpLayerStep.STAGED = not args.range_fusion
+    TpLayerStep.STAGED = args.tp_schedule != "fused"
+    TpLayerStep.SCHEDULE = args.tp_schedule
     return stream, dev, ops, channel, region
 
 
@@ -498,7 +564,7 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
       batch_matmul       configs[2]: 64 x 2048^3 bf16, batch split 64/N, no collective
       tp_decoder_layer   configs[4]: Llama-3-8B layer GEMMs, Megatron split, all-reduce through
                          iree_b200_channel_t, + the step's GEMMs alone and collectives alone"""
-    out = {}
+    out = {"host_link": host_link_line(torch, world)}
     steps, warmup = max(10, min(args.steps, 50)), max(3, min(args.warmup, 5))
     MIN = max(args.extra_min_ms, 1.0)   # every extra line is timed over at least this long (sustained)
     stream = torch.cuda.Stream()
@@ -539,7 +605,8 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
     # The step's two halves alone: GEMMs without collectives, collectives without GEMMs.
     from iree_b200 import tp_layer
     kw = dict(tokens=TpLayerStep.TOKENS, hidden=TpLayerStep.HIDDEN, ffn=TpLayerStep.FFN,
-              chunks=TpLayerStep.CHUNKS, region=region, seed=rank, chunk_consumers=TpLayerStep.STAGED)
+              chunks=TpLayerStep.CHUNKS, region=region, seed=rank, chunk_consumers=TpLayerStep.STAGED,
+              schedule=TpLayerStep.SCHEDULE)
     gemms = tp_layer.DecoderLayerGemms(torch, hal, tdev, tops, world, rank, channel,
                                        only="gemms", **kw)
     t_gemm, _ = time_steps(torch, [gemms], steps, warmup, tstream, world, min_ms=MIN)
@@ -564,13 +631,14 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
     return out
 
 
-ALSO_WORKLOADS = ["matmul_i8", "batch_matmul", "attention_prefill", "attention_decode"]
+ALSO_WORKLOADS = ["matmul_i8", "batch_matmul", "attention_prefill", "attention_prefill_causal",
+                  "attention_decode"]
 
 
 def also_lines(torch, hal, dev, ops, stream, args, peaks):
     """N = 1: the other single-GPU configurations of BASELINE.json, driver-runnable, as short
     device-timed runs under the "also" key (value + roofline fraction each)."""
-    out = {}
+    out = {"host_link": host_link_line(torch, 1)}
     steps, warmup = max(10, min(args.steps, 50)), max(3, min(args.warmup, 5))
     for name in ALSO_WORKLOADS:
         works = rotating_sets(lambda i: make_step(torch, hal, dev, ops, name, seed=100 * i),
@@ -702,8 +770,10 @@ def workload_string(workload, world, info=None):
             text = f"{name} {et} batch={batch} M={M} N={N} K={K} per GPU"
         elif workload in ATTENTION_WORKLOADS:
             op, et, B, M, K2, D = ATTENTION_WORKLOADS[workload]
+            mask = ("causal mask (k2 <= m + K2 - M) computed in the kernel"
+                    if workload in CAUSAL_WORKLOADS else "no mask")
             text = (f"iree_linalg_ext.attention {et} batch*heads={B} M={M} K2={K2} "
-                    f"K1=N={D} scale=1/sqrt({D}) no mask, per GPU")
+                    f"K1=N={D} scale=1/sqrt({D}) {mask}, per GPU")
         else:
             text = "Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens=8192"
     else:
@@ -755,6 +825,16 @@ def cpu_work(workload, rows):
     desc = (f"oracle port of the llvm-cpu online-attention arithmetic "
             f"(AggregatedOpInterfaceImpl.cpp:323-632), OpenMP, {et} heads={heads} (of {B}) "
             f"M={rows} (of {M}) K2={K2} D={D}")
+    if workload in CAUSAL_WORKLOADS:
+        # The LAST |rows| query rows (the ones with the most unmasked keys), explicit i1 mask:
+        # the oracle, like the reference's decomposition, evaluates masked entries too, so its
+        # FLOP are counted like the GPU's (unmasked pairs) to keep the two arms comparable.
+        first = M - rows
+        mask = (np.arange(K2)[None, :] <= (first + np.arange(rows))[:, None] + (K2 - M))[None]
+        mask = np.broadcast_to(mask, (heads, rows, K2)).copy()
+        return ((lambda: oracle.attention(et, q, k, v, scale, mask=mask, k2_tile=128)),
+                4.0 * heads * D * float(mask[0].sum()), desc + ", last rows, explicit causal i1 mask",
+                "port")
     return ((lambda: oracle.attention(et, q, k, v, scale, k2_tile=128)),
             4.0 * heads * rows * K2 * D, desc, "port")
 
@@ -856,10 +936,11 @@ def main():
                          "kernels (default) or through NCCL")
     ap.add_argument("--attention-flags", type=lambda v: int(v, 0), default=0,
                     help="IREE_B200_ATTENTION_FLAG_* bits for the attention workloads")
-    ap.add_argument("--range-fusion", action="store_true",
-                    help="tp_decoder_layer: the unstaged recording (GEMM chunk, all-reduce, ...) "
-                         "with one persistent all-reduce launch per row-parallel GEMM, instead "
-                         "of the staged schedule")
+    ap.add_argument("--tp-schedule", default="dataflow", choices=["dataflow", "staged", "fused"],
+                    help="tp_decoder_layer, N>1: dataflow = dependencies derived from binding ranges "
+                         "(overlap_collectives 3); staged = barrier-separated stages, barriers join "
+                         "the streams (2); fused = GEMM chunk, all-reduce, ... with one persistent "
+                         "all-reduce launch per row-parallel GEMM (1)")
     ap.add_argument("--extra-min-ms", type=float, default=200.0,
                     help="minimum timed region of each `also` / `sharded` line")
     ap.add_argument("--no-extra", action="store_true",

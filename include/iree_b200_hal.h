@@ -107,6 +107,13 @@ typedef struct iree_b200_device_params_t {
   // behind the first producer and each later range is released by a stream write behind
   // its producer, so the ranks meet once per range instead of twice per launch and there
   // are no launch gaps. 2 = overlap without that fusion (diagnostics).
+  // 3 = DATAFLOW: as 2, but an execution barrier no longer joins the two streams wholesale:
+  // every command waits only for the latest command on the other stream, recorded before
+  // the last barrier preceding it, with which it has a read/write hazard on its binding
+  // ranges (read-only bindings, cuda_executable_def.fbs BindingBits, count as reads).
+  // Kernels reach device memory through their bindings only, so the result is that of the
+  // serialised execution; collectives then run under every dispatch that does not consume
+  // them. The streams join at the end of the command buffer.
   int32_t overlap_collectives;
   int32_t reserved1;
 } iree_b200_device_params_t;

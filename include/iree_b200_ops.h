@@ -246,6 +246,11 @@ enum {
   IREE_B200_ATTENTION_MASK_NONE = 0,
   IREE_B200_ATTENTION_MASK_BOOL = 1,  // i1 stored one byte per element
   IREE_B200_ATTENTION_MASK_F32 = 2,   // additive, natural-log domain (scaled by log2e inside)
+  // The causal i1 mask, mask[m, k2] = k2 <= m + (K2 - M) (K2 >= M), WITHOUT a mask operand:
+  // what a matcher emits when the op's mask is the iota-compare pattern. The kernels compute
+  // it in registers and skip K2 blocks that are masked for a whole tile (tcgen05 prefill:
+  // half the work at M == K2). Same result as passing that mask as MASK_BOOL.
+  IREE_B200_ATTENTION_MASK_CAUSAL = 3,
 };
 
 enum {

@@ -53,6 +53,15 @@ struct Command {
   uint32_t op = 0;
   uint32_t param = 0;
   uint64_t element_count = 0;
+  // Device memory the command reads / writes: [begin, end) byte ranges from its bindings
+  // (hazard tracking of the dataflow replay, replay_dataflow).
+  struct Range {
+    uint64_t begin, end;
+  };
+  std::vector<Range> reads, writes;
+  void touch(bool write, uint64_t ptr, uint64_t length) {
+    if (ptr && length) (write ? writes : reads).push_back(Range{ptr, ptr + length});
+  }
 };
 
 enum class State { kInitial, kRecording, kExecutable };
@@ -373,9 +382,14 @@ iree_b200_status_t join_collectives(iree_b200_device_t* device, bool* pending_jo
   return IREE_B200_STATUS_OK;
 }
 
+iree_b200_status_t replay_dataflow(iree_b200_command_buffer_t* cb);
+
 iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
   iree_b200_device_t* device = cb->device;
   const CudaSymbols* cu = device->cu;
+  if (device->collective_stream && device->params.overlap_collectives == 3) {
+    return replay_dataflow(cb);
+  }
   CUstream stream = device->dispatch_stream;
   std::vector<const Command*> batch;
   bool pending_join = false;
@@ -520,6 +534,153 @@ iree_b200_status_t replay_on_stream(iree_b200_command_buffer_t* cb) {
   }
   if (fork_event) cu->cuEventDestroy(fork_event);
   if (join_event) cu->cuEventDestroy(join_event);
+  if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+  return IREE_B200_STATUS_OK;
+}
+
+// Launches one non-collective, non-barrier command on |stream|.
+iree_b200_status_t launch_command(const CudaSymbols* cu, const Command& c, CUstream stream) {
+  switch (c.kind) {
+    case CommandKind::kDispatch:
+      B200_CU(cu, cuLaunchKernel(c.function, c.grid[0], c.grid[1], c.grid[2], c.block[0], c.block[1],
+                                 c.block[2], c.shared_memory, stream, c.params, nullptr));
+      break;
+    case CommandKind::kFill:
+      if (c.pattern_length == 4) {
+        B200_CU(cu, cuMemsetD32Async(c.target, c.pattern, c.length / 4, stream));
+      } else if (c.pattern_length == 2) {
+        B200_CU(cu, cuMemsetD16Async(c.target, (uint16_t)c.pattern, c.length / 2, stream));
+      } else {
+        B200_CU(cu, cuMemsetD8Async(c.target, (uint8_t)c.pattern, c.length, stream));
+      }
+      break;
+    case CommandKind::kUpdate:
+      B200_CU(cu, cuMemcpyHtoDAsync(c.target, c.storage.get(), c.length, stream));
+      break;
+    case CommandKind::kCopy:
+      B200_CU(cu, cuMemcpyAsync(c.target, c.source, c.length, stream));
+      break;
+    default:
+      break;
+  }
+  return IREE_B200_STATUS_OK;
+}
+
+bool ranges_overlap(const std::vector<Command::Range>& a, const std::vector<Command::Range>& b) {
+  for (const auto& x : a) {
+    for (const auto& y : b) {
+      if (x.begin < y.end && y.begin < x.end) return true;
+    }
+  }
+  return false;
+}
+
+// A hazard orders |later| behind |earlier|: read-after-write, write-after-read or
+// write-after-write on overlapping device memory.
+bool has_hazard(const Command& earlier, const Command& later) {
+  return ranges_overlap(earlier.writes, later.reads) || ranges_overlap(earlier.writes, later.writes) ||
+         ranges_overlap(earlier.reads, later.writes);
+}
+
+// overlap_collectives == 3: DATAFLOW replay on two in-order streams. Dispatches, fills and
+// copies go to the dispatch stream and collectives to the collective stream, each in
+// recording order; an execution barrier does not join the streams wholesale — a command
+// waits (cuStreamWaitEvent) only for the latest command on the OTHER stream, recorded before
+// the last barrier that precedes it, with which it has a data hazard on its binding ranges.
+// Commands of one barrier-delimited group are unordered by contract; same-stream order is
+// implicit. Kernels touch device memory through their bindings only (the dispatch ABI), so
+// the recorded ranges are the complete access set and the result equals the fully
+// serialised execution. The streams join at the end of the command buffer. This is what
+// lets the all-reduce of chunk c of a row-parallel GEMM run under the GEMMs of other
+// chunks while only its true consumer waits for it (iree_b200/tp_layer.py).
+iree_b200_status_t replay_dataflow(iree_b200_command_buffer_t* cb) {
+  iree_b200_device_t* device = cb->device;
+  const CudaSymbols* cu = device->cu;
+  const size_t n = cb->commands.size();
+  CUstream streams[2] = {device->dispatch_stream, device->collective_stream};
+  std::vector<int> stream_of(n, -1), group_of(n, 0);
+  int group = 0;
+  for (size_t i = 0; i < n; ++i) {
+    const Command& c = cb->commands[i];
+    if (c.kind == CommandKind::kBarrier) {
+      ++group;
+      continue;
+    }
+    group_of[i] = group;
+    stream_of[i] = c.kind == CommandKind::kCollective ? 1 : 0;
+  }
+  // wait_for[j] = the command on the other stream j must wait for (or -1).
+  std::vector<int64_t> wait_for(n, -1);
+  std::vector<bool> signals(n, false);
+  for (size_t j = 0; j < n; ++j) {
+    if (stream_of[j] < 0) continue;
+    for (size_t i = j; i-- > 0;) {
+      if (stream_of[i] < 0 || stream_of[i] == stream_of[j] || group_of[i] == group_of[j]) continue;
+      if (has_hazard(cb->commands[i], cb->commands[j])) {
+        wait_for[j] = (int64_t)i;
+        signals[i] = true;
+        break;  // stream order covers every earlier command of that stream
+      }
+    }
+  }
+  std::vector<CUevent> events(n, nullptr);
+  CUevent fork = nullptr, join = nullptr;
+  int64_t last_waited[2] = {-1, -1};  // per stream: latest command of the other one already waited for
+  auto run = [&]() -> iree_b200_status_t {
+    // Everything already queued on the dispatch stream precedes the command buffer.
+    B200_CU(cu, cuEventCreate(&fork, CU_EVENT_DISABLE_TIMING));
+    B200_CU(cu, cuEventRecord(fork, streams[0]));
+    B200_CU(cu, cuStreamWaitEvent(streams[1], fork, 0));
+    bool used_collective_stream = false;
+    for (size_t j = 0; j < n; ++j) {
+      const Command& c = cb->commands[j];
+      const int sj = stream_of[j];
+      if (sj < 0) continue;
+      if (wait_for[j] > last_waited[sj]) {
+        B200_CU(cu, cuStreamWaitEvent(streams[sj], events[(size_t)wait_for[j]], 0));
+        last_waited[sj] = wait_for[j];
+      }
+      if (c.kind == CommandKind::kCollective) {
+        used_collective_stream = true;
+        int type_index = -1;
+        if (symmetric_all_reduce_eligible(c, &type_index)) {
+          B200_RETURN_IF_ERROR(launch_symmetric_all_reduce(c, type_index, streams[1]));
+          c.channel->symmetric_collectives.fetch_add(1);
+        } else {
+          const NcclSymbols* nccl = c.channel->nccl;
+          B200_NCCL(nccl, ncclGroupStart());
+          iree_b200_status_t status = issue_collective(c, streams[1]);
+          std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+          ncclResult_t end_result = nccl->ncclGroupEnd();
+          if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
+          if (end_result != ncclSuccess) {
+            return nccl_status(nccl, end_result, "ncclGroupEnd()", __FILE__, __LINE__);
+          }
+          c.channel->nccl_collectives.fetch_add(1);
+        }
+      } else {
+        B200_RETURN_IF_ERROR(launch_command(cu, c, streams[0]));
+      }
+      if (signals[j]) {
+        B200_CU(cu, cuEventCreate(&events[j], CU_EVENT_DISABLE_TIMING));
+        B200_CU(cu, cuEventRecord(events[j], streams[sj]));
+      }
+    }
+    if (used_collective_stream) {
+      B200_CU(cu, cuEventCreate(&join, CU_EVENT_DISABLE_TIMING));
+      B200_CU(cu, cuEventRecord(join, streams[1]));
+      B200_CU(cu, cuStreamWaitEvent(streams[0], join, 0));
+    }
+    return IREE_B200_STATUS_OK;
+  };
+  iree_b200_status_t status = run();
+  std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  // Destroying an event that is still pending only defers the release of its resources.
+  for (CUevent e : events) {
+    if (e) cu->cuEventDestroy(e);
+  }
+  if (fork) cu->cuEventDestroy(fork);
+  if (join) cu->cuEventDestroy(join);
   if (status != IREE_B200_STATUS_OK) return make_status(status, "%s", message.c_str());
   return IREE_B200_STATUS_OK;
 }
@@ -779,6 +940,7 @@ iree_b200_status_t iree_b200_command_buffer_fill_buffer(iree_b200_command_buffer
   }
   memcpy(&c.pattern, pattern, pattern_length);
   c.pattern_length = (uint32_t)pattern_length;
+  c.touch(true, c.target, c.length);
   if (c.length) cb->commands.push_back(std::move(c));
   return IREE_B200_STATUS_OK;
 }
@@ -797,6 +959,7 @@ iree_b200_status_t iree_b200_command_buffer_update_buffer(iree_b200_command_buff
   c.storage.reset(static_cast<uint8_t*>(aligned_alloc(64, (c.length + 63) / 64 * 64)));
   if (!c.storage) return make_status(IREE_B200_STATUS_RESOURCE_EXHAUSTED, "out of host memory");
   memcpy(c.storage.get(), static_cast<const uint8_t*>(source) + source_offset, c.length);
+  c.touch(true, c.target, c.length);
   cb->commands.push_back(std::move(c));
   return IREE_B200_STATUS_OK;
 }
@@ -815,6 +978,8 @@ iree_b200_status_t iree_b200_command_buffer_copy_buffer(iree_b200_command_buffer
                        "copy source (%llu bytes) and target (%llu bytes) lengths differ",
                        (unsigned long long)source_length, (unsigned long long)c.length);
   }
+  c.touch(false, c.source, c.length);
+  c.touch(true, c.target, c.length);
   if (c.length) cb->commands.push_back(std::move(c));
   return IREE_B200_STATUS_OK;
 }
@@ -882,6 +1047,8 @@ iree_b200_status_t iree_b200_command_buffer_dispatch(
     binding_ptrs[i] = ptr;
     slots[i] = ptr;
     c.params[i] = &slots[i];
+    // cuda_executable_def.fbs BindingBits: 1 = READ_ONLY; anything else may be written.
+    c.touch((k.binding_flags[i] & 1) == 0, ptr, length);
   }
   for (size_t i = 0; i < constant_count; ++i) {
     slots[binding_count + i] = constants[i];  // low 32 bits are the value
@@ -953,6 +1120,8 @@ iree_b200_status_t iree_b200_command_buffer_collective(
                        (unsigned long long)recv_length,
                        (unsigned long long)(recv_elements * element_size));
   }
+  c.touch(false, c.source, send_elements * element_size);
+  c.touch(true, c.target, recv_elements * element_size);
   iree_b200_channel_retain(channel);
   cb->channels.push_back(channel);
   cb->commands.push_back(std::move(c));

@@ -4,9 +4,14 @@
 // binding in layout order, then one 32-bit value per push constant; TMA-fed kernels take
 // their CUtensorMaps after the ABI parameters (iree_b200_tma_recipe.h).
 //
-//   iree_b200_attention_prefill_{f16,bf16}   tcgen05, K1 == N == 128, no mask
+//   iree_b200_attention_prefill_{f16,bf16}   tcgen05, K1 == N == 128, no mask operand
 //     bindings  Q [B,M,128] ro, K [B,K2,128] ro, V [B,K2,128] ro, O [B,M,128]
 //     constants B, M, K2, scale (f32 bits), flags      grid [ceil(M/256), B, 1]  block 384
+//     flags bit 0: causal mask computed in the kernel (k2 <= m + K2 - M), fully masked K2
+//     blocks skipped; the grid is then [ceil(M/256) * B, 1, 1]
+//   iree_b200_attention_prefill_mask_{f16,bf16}   the same with an i1 mask operand
+//     bindings  Q ro, K ro, V ro, mask [B,M,K2] u8 ro, O
+//     constants B, M, K2, scale, flags                 grid [ceil(M/256), B, 1]  block 384
 //   iree_b200_attention_decode_split_{f16,bf16}   HBM-streaming split-KV, K1 == N == 128
 //     bindings  Q ro, K ro, V ro, workspace [B,M,splits,130] f32
 //     constants B, M, K2, scale, splits                grid [splits, M, B]       block 256
@@ -19,7 +24,8 @@
 //     constants B, M, K2, scale, flags                 grid [8, M, B] (cluster 8x1x1)  block 288
 //   iree_b200_attention_generic_{f16,bf16,f32}   any shape within the guards, optional mask
 //     bindings  Q ro, K ro, V ro, mask ro (any valid pointer when unused), O
-//     constants B, M, K1, K2, N, scale, mask_kind (0 none, 1 i1-as-u8, 2 f32 additive)
+//     constants B, M, K1, K2, N, scale, mask_kind (0 none, 1 i1-as-u8, 2 f32 additive,
+//               3 causal computed in the kernel: no operand)
 //                                                      grid [M, B, 1]            block 128
 // Semantics for all of them: the oracle's (oracle/oracle.c), i.e. the llvm-cpu lowering.
 
@@ -55,6 +61,25 @@ B200_PREFILL(iree_b200_attention_prefill_f16_p25, false, 1)
 B200_PREFILL(iree_b200_attention_prefill_bf16_p25, true, 1)
 B200_PREFILL(iree_b200_attention_prefill_f16_p50, false, 2)
 B200_PREFILL(iree_b200_attention_prefill_bf16_p50, true, 2)
+
+#define B200_PREFILL_MASK(NAME, BF16)                                                          \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                             \
+      make_attention_prefill_recipe<PrefillCfg, BF16>();                                       \
+  extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \
+      NAME(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, \
+           const void* __restrict__ mask, void* __restrict__ out, int B, int M, int K2,        \
+           int scale_bits, int flags, const __grid_constant__ TensorMap tm_q,                  \
+           const __grid_constant__ TensorMap tm_k, const __grid_constant__ TensorMap tm_v) {   \
+    (void)q;                                                                                   \
+    (void)k;                                                                                   \
+    (void)v;                                                                                   \
+    attention_prefill_body<PrefillCfg, BF16, 0, false, true>(                                  \
+        out, B, M, K2, scale_bits, flags, &tm_q, &tm_k, &tm_v, nullptr, 0, 1,                  \
+        static_cast<const uint8_t*>(mask));                                                    \
+  }
+
+B200_PREFILL_MASK(iree_b200_attention_prefill_mask_f16, false)
+B200_PREFILL_MASK(iree_b200_attention_prefill_mask_bf16, true)
 
 // Tail-split form (attention_sm100.cuh, kSplit): 1-D grid over units, the units of the last,
 // partly filled wave cut into |split| CTAs each, plus the merge of their records.
@@ -594,6 +619,8 @@ __device__ __forceinline__ void attention_generic_body(const void* __restrict__ 
         a = a + (reinterpret_cast<const uint8_t*>(mask)[midx] ? 0.f : -INFINITY);
       } else if (mask_kind == 2) {
         a = a + reinterpret_cast<const float*>(mask)[midx] * 1.4426950408889634074f;
+      } else if (mask_kind == 3) {  // causal, computed: k2 <= m + (K2 - M)
+        a = a + (j <= m + (K2 - M) ? 0.f : -INFINITY);
       }
       s = a;
     }

@@ -10,6 +10,18 @@
 // accumulator is applied lazily (only when a row's max grew by more than 2^8), which is
 // algebraically the same result; parity is therefore by tolerance (1e-3 f16 / 1e-2 bf16).
 //
+// Masks (the op's optional mask operand, LinalgExtOps.td:967-1071; applied to S before the
+// row max as `S + select(mask, 0, -inf)`, AggregatedOpInterfaceImpl.cpp:239-291):
+//   * flags bit 0 (kAttnFlagCausal): the mask is the causal one, mask[m, k2] = k2 <= m +
+//     (K2 - M), and is never materialised: the softmax thread of row m turns the columns
+//     beyond its limit into -inf, and K2 blocks that are masked for every row of the CTA are
+//     not loaded or multiplied at all (half the work at M == K2). The grid is then 1-D over
+//     units with the heaviest units (largest m) first, so the light ones fill the tail.
+//   * kMask: an i1 mask tensor [B, M, K2] (one byte per element, as IREE stores i1) is a
+//     fourth read-only binding; each softmax thread reads the 128 bytes of its row and block
+//     (issued before it waits for S, so the latency hides behind the MMA) and turns masked
+//     columns into -inf.
+//
 // Layouts (row-major): Q [B,M,D], K [B,K2,D], V [B,K2,D], O [B,M,D], D = 128.
 //
 // One CTA (384 threads) owns two 128-row Q tiles of one batch slice:
@@ -64,6 +76,15 @@ B200_DEVICE uint32_t pack2(float lo, float hi) {
   return r;
 }
 
+// 16 read-only bytes that are touched once (the mask): no L1 allocation.
+B200_DEVICE uint4 ld_nc_na_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
 B200_DEVICE float max3(float a, float b, float c) {
   float r;
   asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
@@ -107,21 +128,24 @@ B200_DEVICE float attention_q_multiplier(float scale) {
 // (acc [256,128] f32, max [256], sum [256]) in |workspace| for the merge kernel. With equal
 // units the last wave of a grid is otherwise only partly full (512 units on 148 SMs: 3.46
 // waves); splitting just those units makes the last wave short instead.
-template <class Cfg, bool kBf16, int kPoly = 0, bool kSplit = false>
+constexpr int kAttnFlagCausal = 1;
+
+template <class Cfg, bool kBf16, int kPoly = 0, bool kSplit = false, bool kMask = false>
 __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, int B, int M, int K2,
                                                        int scale_bits, int flags,
                                                        const TensorMap* tm_q, const TensorMap* tm_k,
                                                        const TensorMap* tm_v,
                                                        float* __restrict__ workspace = nullptr,
-                                                       int full_units = 0, int split = 1) {
+                                                       int full_units = 0, int split = 1,
+                                                       const uint8_t* __restrict__ mask = nullptr) {
   constexpr int D = Cfg::kHeadDim;
   constexpr int BM = Cfg::kBlockM;
   constexpr int BN = Cfg::kBlockN;
   constexpr uint32_t kFmt = kBf16 ? FMT_BF16 : FMT_F16;
   constexpr uint32_t kIdescS = make_idesc(CFMT_F32, kFmt, kFmt, MAJOR_K, MAJOR_K, BM, BN);
   constexpr uint32_t kIdescPV = make_idesc(CFMT_F32, kFmt, kFmt, MAJOR_K, MAJOR_MN, BM, D);
-  (void)B;
-  (void)flags;
+  const bool causal = !kSplit && (flags & kAttnFlagCausal) != 0;
+  const int causal_shift = K2 - M;  // >= 0 (selection guard): row m sees columns <= m + shift
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -162,6 +186,14 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     }
     batch = unit / tiles_m;
     m_cta = (unit % tiles_m) * (Cfg::kTilesPerCta * BM);
+  } else if (causal) {
+    // 1-D grid, heaviest units first: unit u = (m tile counted from the bottom, batch).
+    const int tiles_m = (M + Cfg::kTilesPerCta * BM - 1) / (Cfg::kTilesPerCta * BM);
+    batch = (int)blockIdx.x % B;
+    m_cta = (tiles_m - 1 - (int)blockIdx.x / B) * (Cfg::kTilesPerCta * BM);
+    // Blocks whose first column lies beyond the last row's limit are masked for every row.
+    const int last_row = min(M, m_cta + Cfg::kTilesPerCta * BM) - 1;
+    num_kv = min(num_kv, (uint32_t)((last_row + causal_shift + BN) / BN));
   }
 
   if (warp == 0 && lane == 0) {
@@ -363,7 +395,24 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
 
     float m_run = -FLT_MAX;  // TileAttention.cpp:82-84 (useOnlyFiniteValue)
     float l_run = 0.f;
+    const int gm_row = m_cta + t * BM + (int)row;
+    const uint8_t* mask_row = nullptr;
+    if constexpr (kMask) {
+      mask_row = mask + ((size_t)batch * M + (size_t)min(gm_row, M - 1)) * (size_t)K2;
+    }
     for (uint32_t j = 0; j < num_kv; ++j) {
+      const int col0 = (int)((kv_begin + j) * BN);
+      // The row's 128 mask bytes of this block, requested before the wait for S.
+      uint4 mbytes[kMask ? BN / 16 : 1];
+      if constexpr (kMask) {
+#pragma unroll
+        for (int c = 0; c < BN / 16; ++c) {
+          mbytes[c] = make_uint4(0x01010101u, 0x01010101u, 0x01010101u, 0x01010101u);
+          if (col0 + c * 16 < K2) {  // K2 % 16 == 0 (selection guard)
+            mbytes[c] = ld_nc_na_v4(mask_row + col0 + c * 16);
+          }
+        }
+      }
       mbar_wait(bar_s_full + 8 * t, j & 1);
       tcgen05_fence_after();
       uint32_t s[BN];
@@ -372,11 +421,24 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
         tmem_ld_32x32b_x32(tmem_s + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
       }
       tmem_wait_ld();
-      const int valid = K2 - (int)((kv_begin + j) * BN);  // columns >= valid are TMA zero fill
+      // Columns >= valid are TMA zero fill (K2 tail) or beyond the row's causal limit.
+      int valid = K2 - col0;
+      if (causal) valid = min(valid, gm_row + causal_shift + 1 - col0);
       if (valid < BN) {
 #pragma unroll
         for (int i = 0; i < BN; ++i) {
           if (i >= valid) s[i] = 0xff800000u;  // -inf
+        }
+      }
+      if constexpr (kMask) {
+#pragma unroll
+        for (int c = 0; c < BN / 16; ++c) {
+          const uint32_t w[4] = {mbytes[c].x, mbytes[c].y, mbytes[c].z, mbytes[c].w};
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            // i1 is stored one byte per element; any non-zero byte is "true".
+            if (((w[i >> 2] >> (8 * (i & 3))) & 0xffu) == 0) s[c * 16 + i] = 0xff800000u;
+          }
         }
       }
       // Row max: 8 independent chains of 3-input max (a single chain is 128 dependent ops).
@@ -464,7 +526,7 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
       rec[kRows * (D + 1) + r] = l_run;
     } else {
     const float rcp = 1.0f / l_run;
-    const int gm = m_cta + t * BM + (int)row;
+    const int gm = gm_row;
     uint16_t* orow = reinterpret_cast<uint16_t*>(out) + ((size_t)batch * M + gm) * D;
 #pragma unroll
     for (int c = 0; c < D / 32; ++c) {

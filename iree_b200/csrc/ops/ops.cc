@@ -48,7 +48,8 @@ enum AttentionExport {
   kAttnPrefillPoly25 = 5,
   kAttnPrefillPoly50 = 6,
   kAttnPrefillSplit = 7,
-  kAttnPrefillMerge = 8
+  kAttnPrefillMerge = 8,
+  kAttnPrefillMask = 9
 };
 
 }  // namespace
@@ -158,6 +159,8 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
         lookup(ops->executable, "iree_b200_attention_prefill_split_" + suffix);
     ops->attention_exports[t][kAttnPrefillMerge] =
         lookup(ops->executable, "iree_b200_attention_prefill_merge_" + suffix);
+    ops->attention_exports[t][kAttnPrefillMask] =
+        lookup(ops->executable, "iree_b200_attention_prefill_mask_" + suffix);
     ops->attention_exports[t][kAttnDecodeSplit] =
         lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
     ops->attention_exports[t][kAttnDecodeMerge] =
@@ -1317,8 +1320,17 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "attention element type %d unsupported (f16 / bf16 / f32)", element_type);
   }
-  if (mask_kind < 0 || mask_kind > 2) {
+  if (mask_kind < 0 || mask_kind > IREE_B200_ATTENTION_MASK_CAUSAL) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad attention mask kind %d", mask_kind);
+  }
+  if (mask_kind == IREE_B200_ATTENTION_MASK_CAUSAL) {
+    if (K2 < M) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "causal attention needs K2 >= M (row m sees keys <= m + K2 - M); got "
+                         "M=%lld K2=%lld", (long long)M, (long long)K2);
+    }
+    // A single query row sees every key: the mask is all-true.
+    if (M == 1) mask_kind = IREE_B200_ATTENTION_MASK_NONE;
   }
   const int64_t dims[5] = {B, M, K1, K2, N};
   for (int64_t d : dims) {
@@ -1333,19 +1345,27 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
                        "attention with an empty reduction (K1=%lld, K2=%lld) is undefined",
                        (long long)K1, (long long)K2);
   }
-  const bool tc_shape = K1 == 128 && N == 128 && mask_kind == IREE_B200_ATTENTION_MASK_NONE &&
-                        alignment >= 16 && element_type != IREE_B200_ELEMENT_TYPE_F32;
+  // The tcgen05 prefill kernel takes no mask, the causal mask (computed in the kernel) or an
+  // i1 mask operand whose rows can be read 16 bytes at a time; the decode kernels take none.
+  const bool tc_operands = K1 == 128 && N == 128 && alignment >= 16 &&
+                           element_type != IREE_B200_ELEMENT_TYPE_F32;
+  const bool prefill_mask_ok =
+      mask_kind == IREE_B200_ATTENTION_MASK_NONE || mask_kind == IREE_B200_ATTENTION_MASK_CAUSAL ||
+      (mask_kind == IREE_B200_ATTENTION_MASK_BOOL && K2 % 16 == 0);
+  const bool tc_shape = tc_operands && (M > 16 ? prefill_mask_ok
+                                               : mask_kind == IREE_B200_ATTENTION_MASK_NONE);
   enum { kPrefill, kDecode, kGeneric } family;
   if (flags & IREE_B200_ATTENTION_FLAG_FORCE_GENERIC) {
     family = kGeneric;
   } else if (flags & (IREE_B200_ATTENTION_FLAG_FORCE_PREFILL | IREE_B200_ATTENTION_FLAG_FORCE_DECODE |
                       IREE_B200_ATTENTION_FLAG_FORCE_DECODE_SPLIT |
                       IREE_B200_ATTENTION_FLAG_FORCE_DECODE_CLUSTER)) {
-    if (!tc_shape) {
+    family = (flags & IREE_B200_ATTENTION_FLAG_FORCE_PREFILL) ? kPrefill : kDecode;
+    if (!tc_operands || (family == kPrefill ? !prefill_mask_ok
+                                            : mask_kind != IREE_B200_ATTENTION_MASK_NONE)) {
       return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                          "shape/mask/alignment does not satisfy the guards of the forced kernel");
     }
-    family = (flags & IREE_B200_ATTENTION_FLAG_FORCE_PREFILL) ? kPrefill : kDecode;
   } else if (tc_shape) {
     family = M > 16 ? kPrefill : kDecode;
   } else {
@@ -1374,7 +1394,8 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       int64_t split = tail_units ? std::min<int64_t>(4, sms / tail_units) : 1;
       split = std::min(split, kv_blocks / 4);  // every part keeps >= 4 K2 blocks
       const bool use_split = !(flags & IREE_B200_ATTENTION_FLAG_NO_TAIL_SPLIT) && split >= 2 &&
-                             variant == kAttnPrefill && full_units + tail_units * split <= 0x7fffffff;
+                             variant == kAttnPrefill && mask_kind == IREE_B200_ATTENTION_MASK_NONE &&
+                             full_units + tail_units * split <= 0x7fffffff;
       if (use_split) {
         d0->export_ordinal = ops->attention_exports[element_type][kAttnPrefillSplit];
         d0->workgroup_count[0] = (uint32_t)(full_units + tail_units * split);
@@ -1401,6 +1422,7 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
         out_selection->workspace_bytes = (uint64_t)tail_units * split * 256 * (128 + 2) * 4;
         break;
       }
+      if (mask_kind == IREE_B200_ATTENTION_MASK_BOOL) variant = kAttnPrefillMask;
       d0->export_ordinal = ops->attention_exports[element_type][variant];
       d0->workgroup_count[0] = (uint32_t)ceil_div(M, 256);
       d0->workgroup_count[1] = (uint32_t)B;
@@ -1411,6 +1433,15 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       d0->constants[2] = (uint32_t)K2;
       d0->constants[3] = scale_bits;
       d0->constants[4] = 0;
+      if (mask_kind == IREE_B200_ATTENTION_MASK_CAUSAL) {
+        // Units differ in work (row m walks K2 blocks up to its limit only): a 1-D grid that
+        // the kernel reads heaviest-first, so the hardware's in-order block dispatch is
+        // longest-processing-time-first scheduling.
+        if (units > 0x7fffffff) return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "attention grid too large");
+        d0->workgroup_count[0] = (uint32_t)units;
+        d0->workgroup_count[1] = 1;
+        d0->constants[4] = 1;  // kAttnFlagCausal
+      }
       out_selection->dispatch_count = 1;
       break;
     }
@@ -1535,11 +1566,14 @@ iree_b200_status_t iree_b200_ops_record_attention(
   B200_RETURN_IF_ERROR(check_binding("K", k, (uint64_t)B * K2 * K1 * es, &alignment));
   B200_RETURN_IF_ERROR(check_binding("V", v, (uint64_t)B * K2 * N * es, &alignment));
   B200_RETURN_IF_ERROR(check_binding("O", out, (uint64_t)B * M * N * es, &alignment));
-  if (mask_kind != IREE_B200_ATTENTION_MASK_NONE) {
-    uint32_t ignored = 256;
+  if (mask_kind == IREE_B200_ATTENTION_MASK_BOOL || mask_kind == IREE_B200_ATTENTION_MASK_F32) {
+    // The i1 mask of the tcgen05 prefill kernel is read 16 bytes at a time: its alignment
+    // counts like the operands'; the generic kernel reads it element by element.
+    uint32_t mask_alignment = 256;
     B200_RETURN_IF_ERROR(check_binding(
         "mask", mask, (uint64_t)B * M * K2 * (mask_kind == IREE_B200_ATTENTION_MASK_F32 ? 4 : 1),
-        &ignored));
+        &mask_alignment));
+    if (mask_kind == IREE_B200_ATTENTION_MASK_BOOL) alignment = std::min(alignment, mask_alignment);
   }
   iree_b200_attention_selection_t sel;
   B200_RETURN_IF_ERROR(iree_b200_ops_select_attention(ops, element_type, B, M, K1, K2, N, scale,
@@ -1568,10 +1602,17 @@ iree_b200_status_t iree_b200_ops_record_attention(
     ops->dispatch_count.fetch_add(2);
     return IREE_B200_STATUS_OK;
   }
-  if (sel.dispatches[0].constant_count == 7) {
+  if (element_type != IREE_B200_ELEMENT_TYPE_F32 &&
+      sel.dispatches[0].export_ordinal == ops->attention_exports[element_type][kAttnPrefillMask]) {
+    const iree_b200_buffer_ref_t refs[5] = {q, k, v, mask, out};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
+        sel.dispatches[0].constants, 5, refs, 5, 0));
+  } else if (sel.dispatches[0].constant_count == 7) {
     // Generic export: the mask binding must be a valid pointer even when unused.
-    const iree_b200_buffer_ref_t refs[5] = {
-        q, k, v, mask_kind == IREE_B200_ATTENTION_MASK_NONE ? q : mask, out};
+    const bool has_operand = mask_kind == IREE_B200_ATTENTION_MASK_BOOL ||
+                             mask_kind == IREE_B200_ATTENTION_MASK_F32;
+    const iree_b200_buffer_ref_t refs[5] = {q, k, v, has_operand ? mask : q, out};
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
         cb, ops->executable, sel.dispatches[0].export_ordinal, sel.dispatches[0].workgroup_count,
         sel.dispatches[0].constants, 7, refs, 5, 0));
@@ -1592,7 +1633,8 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
                                                 const void* v, const void* mask, void* out) {
   B200_REQUIRE_ARG(ops);
   B200_RETURN_IF_ERROR(require_device(ops));
-  if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0 || mask_kind < 0 || mask_kind > 2) {
+  if (B < 0 || M < 0 || K1 < 0 || K2 < 0 || N < 0 || mask_kind < 0 ||
+      mask_kind > IREE_B200_ATTENTION_MASK_CAUSAL) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "bad attention shape or mask kind");
   }
   iree_b200_attention_selection_t sel;
@@ -1600,9 +1642,9 @@ iree_b200_status_t iree_b200_ops_attention_host(iree_b200_ops_t* ops, int32_t el
                                                       mask_kind, flags, 256, &sel));
   if (sel.dispatch_count == 0) return IREE_B200_STATUS_OK;
   const uint64_t mask_bytes =
-      mask_kind == IREE_B200_ATTENTION_MASK_NONE
-          ? 0
-          : (uint64_t)B * M * K2 * (mask_kind == IREE_B200_ATTENTION_MASK_F32 ? 4 : 1);
+      (mask_kind == IREE_B200_ATTENTION_MASK_BOOL || mask_kind == IREE_B200_ATTENTION_MASK_F32)
+          ? (uint64_t)B * M * K2 * (mask_kind == IREE_B200_ATTENTION_MASK_F32 ? 4 : 1)
+          : 0;  // none, or the causal mask the kernels compute themselves
   // 0=Q 1=K 2=V 3=mask 4=workspace 5=O
   const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_F32 ? 4 : 2;
   const uint64_t bytes[6] = {(uint64_t)B * M * K1 * es, (uint64_t)B * K2 * K1 * es,

@@ -28,12 +28,17 @@ from . import sharding
 class DecoderLayerGemms:
     def __init__(self, torch, hal, dev, ops, world, rank, channel, *, tokens=8192, hidden=4096,
                  q_heads=32, kv_heads=8, head_dim=128, ffn=14336, chunks=4, region=None,
-                 init=None, seed=0, chunk_consumers=True, only=None):
+                 init=None, seed=0, chunk_consumers=True, only=None, schedule="staged"):
         """|init(name, shape) -> torch tensor (bf16, on the device)| fills an operand with the
         FULL (unsharded) shape; the rank's slice is taken here. Default: N(0, 0.05) noise.
         All GEMMs use the truncating epilogue: bf16 activations, bf16 all-reduce (f32
         accumulate), as a bf16 model's module does. |only| = "gemms" / "collectives" records
-        the same schedule with the other kind left out (the bench's breakdown of a step)."""
+        the same schedule with the other kind left out (the bench's breakdown of a step).
+        |schedule| (with chunk_consumers): "staged" = barrier-separated stages balanced by
+        list scheduling (for a launch layer whose barrier joins its streams:
+        overlap_collectives 2); "dataflow" = every command its own barrier group, in the order
+        each in-order stream should see them (for overlap_collectives 3, where the launch
+        layer derives the true dependencies from the binding ranges)."""
         T, H, FFN = tokens, hidden, ffn
         QKV = (q_heads + 2 * kv_heads) * head_dim
         plan = {g.name: g for g in sharding.decoder_layer_plan(
@@ -116,7 +121,20 @@ class DecoderLayerGemms:
             o_all = [(f"ar_o{c}" if world > 1 else f"o{c}") for c in range(chunks)]
             tasks["gu"] = ("gemm", chunks * H * 2 * fn / (H * hn), o_all,
                            gemm("o", "wgu", "gu", 2 * fn, H))
-        self.stages = self.schedule(tasks, software_pipeline=chunk_consumers and world > 1)
+        if schedule == "dataflow" and chunk_consumers and world > 1:
+            # GEMM stream: the producers of the first reduce, then chunk by chunk what each
+            # finished reduce unblocks; collective stream: the reduces in the order their
+            # consumers need them. One command per barrier group: the launch layer orders
+            # exactly the pairs that share memory.
+            order = [f"o{c}" for c in range(chunks)] + ["qkv"]
+            for c in range(chunks):
+                order += [f"ar_o{c}"]
+            for c in range(chunks):
+                order += [f"gu{c}", f"d{c}", f"ar_d{c}"]
+            assert sorted(order) == sorted(tasks)
+            self.stages = [[n] for n in order]
+        else:
+            self.stages = self.schedule(tasks, software_pipeline=chunk_consumers and world > 1)
         cb = hal.CommandBuffer(dev).begin()
         for stage in self.stages:
             # The collective first: the launch layer issues it on the collective stream behind

@@ -220,7 +220,7 @@ def test_selection_guards(ops):
     assert names(ops.select_attention("bf16", 2, 64, 64, 64, 64, 0.125)) == \
         ["iree_b200_attention_generic_bf16"]
     assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1,
-                                      mask_kind=H.ATTENTION_MASK_BOOL)) == \
+                                      mask_kind=H.ATTENTION_MASK_F32)) == \
         ["iree_b200_attention_generic_f16"]
     assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1, alignment=2)) == \
         ["iree_b200_attention_generic_f16"]
@@ -328,3 +328,101 @@ def test_pipelined_host_call(ops, case):
     else:
         _assert_close(t, sliced, want)
         _assert_close(t, sliced, whole)
+
+
+# ---------------------------------------------------------------------------------------
+# Masks on the tcgen05 prefill kernel (the op's mask operand, LinalgExtOps.td:967-1071;
+# AggregatedOpInterfaceImpl.cpp:239-291): causal computed in the kernel, i1 operand.
+# ---------------------------------------------------------------------------------------
+
+def _causal(B, M, K2):
+    m = np.arange(M)[:, None]
+    k2 = np.arange(K2)[None, :]
+    return np.broadcast_to(k2 <= m + (K2 - M), (B, M, K2)).copy()
+
+
+def _kernel_of(ops, t, B, M, K2, mask_kind, flags=0):
+    sel = ops.select_attention(t, B, M, 128, K2, 128, 0.088, mask_kind=mask_kind, flags=flags)
+    return [ops.executable.export_info(d["export_ordinal"])["kernel_name"] for d in sel["dispatches"]]
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("shape", [(1, 256, 256), (2, 512, 512), (3, 384, 640), (2, 200, 300),
+                                   (1, 130, 130), (2, 1024, 1024), (1, 17, 129), (5, 768, 768)],
+                         ids=str)
+def test_prefill_causal_vs_oracle_with_the_same_mask(ops, t, shape):
+    """MASK_CAUSAL (no operand; masked K2 blocks skipped, heaviest units first) must equal the
+    oracle run with the explicit i1 mask k2 <= m + (K2 - M)."""
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=3 * M + K2)
+    scale = 1.0 / np.sqrt(128.0)
+    assert _kernel_of(ops, t, B, M, K2, H.ATTENTION_MASK_CAUSAL) == [f"iree_b200_attention_prefill_{t}"]
+    out = np.zeros((B, M, 128), dtype=q.dtype)
+    ops.attention_host(t, B, M, 128, K2, 128, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       out.ctypes.data, mask_kind=H.ATTENTION_MASK_CAUSAL)
+    want = oracle.attention(t, q, k, v, scale, mask=_causal(B, M, K2), k2_tile=128)
+    _assert_close(t, out, want, label=f"causal prefill {shape}")
+    # ... and the generic kernel computes the same mask (mask_kind 3).
+    gen = np.zeros_like(out)
+    ops.attention_host(t, B, M, 128, K2, 128, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       gen.ctypes.data, mask_kind=H.ATTENTION_MASK_CAUSAL,
+                       flags=H.ATTENTION_FORCE_GENERIC)
+    _assert_close(t, gen, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("shape", [(1, 256, 256), (2, 384, 640), (2, 200, 304), (1, 130, 144),
+                                   (3, 512, 1024)], ids=str)
+@pytest.mark.parametrize("pattern", ["causal", "random", "banded"])
+def test_prefill_i1_mask_operand_vs_oracle(ops, t, shape, pattern):
+    """An i1 mask operand on the tcgen05 kernel (iree_b200_attention_prefill_mask_*)."""
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=M + 5 * K2)
+    scale = 1.0 / np.sqrt(128.0)
+    g = np.random.Generator(np.random.PCG64(0xB200 + M))
+    if pattern == "causal":
+        mask = _causal(B, M, K2)
+    elif pattern == "random":
+        mask = g.random((B, M, K2)) < 0.7
+        mask[:, :, 0] = True                       # every row keeps at least one key
+    else:
+        m, k2 = np.arange(M)[:, None], np.arange(K2)[None, :]
+        mask = np.broadcast_to(np.abs(k2 - m * K2 // M) <= 96, (B, M, K2)).copy()
+    assert _kernel_of(ops, t, B, M, K2, H.ATTENTION_MASK_BOOL) == [f"iree_b200_attention_prefill_mask_{t}"]
+    got = _gpu_attention(ops, t, q, k, v, scale, mask=mask)
+    want = oracle.attention(t, q, k, v, scale, mask=mask, k2_tile=128)
+    _assert_close(t, got, want, label=f"i1-mask prefill {pattern} {shape}")
+
+
+def test_mask_selection_guards(ops):
+    # K2 not a multiple of 16: the mask rows cannot be read 16 bytes at a time -> generic.
+    assert _kernel_of(ops, "f16", 2, 256, 300, H.ATTENTION_MASK_BOOL) == ["iree_b200_attention_generic_f16"]
+    # additive f32 masks stay on the generic kernel.
+    assert _kernel_of(ops, "f16", 2, 256, 256, H.ATTENTION_MASK_F32) == ["iree_b200_attention_generic_f16"]
+    # causal with one query row is no mask at all (decode kernels); with a few rows: generic.
+    assert _kernel_of(ops, "f16", 32, 1, 8192, H.ATTENTION_MASK_CAUSAL) == ["iree_b200_attention_decode_cluster_f16"]
+    assert _kernel_of(ops, "f16", 2, 8, 512, H.ATTENTION_MASK_CAUSAL) == ["iree_b200_attention_generic_f16"]
+    with pytest.raises(H.Status):
+        ops.select_attention("f16", 1, 512, 128, 256, 128, 0.088, mask_kind=H.ATTENTION_MASK_CAUSAL)
+    # causal: 1-D grid over units, no tail split.
+    sel = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088, mask_kind=H.ATTENTION_MASK_CAUSAL)
+    assert len(sel["dispatches"]) == 1 and sel["dispatches"][0]["workgroup_count"] == [512, 1, 1]
+    assert sel["dispatches"][0]["constants"][4] == 1
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+def test_llama_prefill_shape_causal_sampled(ops, t):
+    """BASELINE configs[3] with the mask real Llama prefill uses: 32 heads x 4096 x 4096,
+    sampled rows against the oracle with the explicit causal mask."""
+    B, M, K2 = 32, 4096, 4096
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=11)
+    scale = 1.0 / np.sqrt(128.0)
+    out = np.zeros((B, M, 128), dtype=q.dtype)
+    ops.attention_host(t, B, M, 128, K2, 128, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       out.ctypes.data, mask_kind=H.ATTENTION_MASK_CAUSAL)
+    rows = np.array([0, 1, 127, 128, 255, 256, 1000, 2047, 2048, 3000, 4095])
+    for b in (0, 13, 31):
+        mask = (np.arange(K2)[None, :] <= rows[:, None])[None]
+        want = oracle.attention(t, q[b:b + 1, rows], k[b:b + 1], v[b:b + 1], scale, mask=mask,
+                                k2_tile=128)
+        _assert_close(t, out[b:b + 1, rows], want, label=f"llama causal prefill head {b}")

@@ -54,4 +54,4 @@ def test_tensor_parallel_decoder_layer_matches_the_oracle(world):
     r, lines = torchrun(world, "tools/tp_layer_check.py", port=29570 + world)
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
     assert lines and lines[-1]["world"] == world and lines[-1]["failures"] == []
-    assert len(lines[-1]["paths"]) == 12
+    assert len(lines[-1]["paths"]) == 16

@@ -92,9 +92,22 @@ def test_attention_selection(ops):
     assert names(s) == ["iree_b200_attention_decode_split_f16", "iree_b200_attention_decode_merge_f16"]
     assert names(ops.select_attention("bf16", 2, 64, 64, 64, 64, 0.125)) == \
         ["iree_b200_attention_generic_bf16"]
-    assert names(ops.select_attention("f16", 2, 256, 128, 256, 128, 0.1,
-                                      mask_kind=H.ATTENTION_MASK_BOOL)) == \
-        ["iree_b200_attention_generic_f16"]
+    # Masks: an i1 operand with 16-byte readable rows and the computed causal mask run on the
+    # tcgen05 prefill kernel; everything else (f32 additive, ragged K2, few rows) is generic.
+    mk = lambda kind, B=2, M=256, K2=256: names(ops.select_attention(
+        "f16", B, M, 128, K2, 128, 0.1, mask_kind=kind))
+    assert mk(H.ATTENTION_MASK_BOOL) == ["iree_b200_attention_prefill_mask_f16"]
+    assert mk(H.ATTENTION_MASK_BOOL, K2=300) == ["iree_b200_attention_generic_f16"]
+    assert mk(H.ATTENTION_MASK_F32) == ["iree_b200_attention_generic_f16"]
+    assert mk(H.ATTENTION_MASK_CAUSAL) == ["iree_b200_attention_prefill_f16"]
+    assert mk(H.ATTENTION_MASK_CAUSAL, B=32, M=1, K2=8192) == ["iree_b200_attention_decode_cluster_f16"]
+    assert mk(H.ATTENTION_MASK_CAUSAL, M=8, K2=512) == ["iree_b200_attention_generic_f16"]
+    s = ops.select_attention("f16", 32, 4096, 128, 4096, 128, 0.088, mask_kind=H.ATTENTION_MASK_CAUSAL)
+    assert names(s) == ["iree_b200_attention_prefill_f16"]      # no tail split: units differ
+    assert s["dispatches"][0]["workgroup_count"] == [512, 1, 1]  # 1-D, heaviest first
+    assert s["dispatches"][0]["constants"][4] == 1               # kAttnFlagCausal
+    with pytest.raises(H.Status):                                # K2 < M
+        ops.select_attention("f16", 1, 512, 128, 256, 128, 0.1, mask_kind=H.ATTENTION_MASK_CAUSAL)
     assert ops.select_attention("f16", 0, 4, 8, 8, 8, 1.0)["dispatches"] == []
     with pytest.raises(H.Status):
         ops.select_attention("i8", 1, 4, 8, 8, 8, 1.0)

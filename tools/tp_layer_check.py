@@ -15,6 +15,8 @@ script asserts; the sharded result must then EQUAL the oracle's unsharded
 
   nccl/stream        ncclAllReduce on the dispatch stream (the reference's arrangement)
   nccl/overlap       ncclAllReduce on the collective stream, staged schedule
+  */dataflow         one command per barrier group; the launch layer orders only commands that
+                     share memory (overlap_collectives 3), NCCL and symmetric kernels
   nccl/graph         CUgraph command buffer, NCCL captured into child graphs (2+ ranks: the
                      reference has UNIMPLEMENTED here, graph_command_buffer.c:291-327)
   symmetric/overlap  our NVLink all-reduce kernels (multimem when the box has NVLS, else
@@ -107,8 +109,10 @@ def main():
 
     configs = [("nccl/stream", hal.MODE_STREAM, 0, False, True),
                ("nccl/overlap", hal.MODE_STREAM, 2, False, True),
+               ("nccl/dataflow", hal.MODE_STREAM, 3, False, "dataflow"),
                ("nccl/graph", hal.MODE_GRAPH, 0, False, True),
                ("symmetric/overlap", hal.MODE_STREAM, 2, True, True),
+               ("symmetric/dataflow", hal.MODE_STREAM, 3, True, "dataflow"),
                ("symmetric/fused", hal.MODE_STREAM, 1, True, False),
                ("symmetric/graph", hal.MODE_GRAPH, 0, True, True)]
     have_mc = None
@@ -125,9 +129,10 @@ def main():
                 have_mc = region.multicast_base != 0
                 region.attach(channel, ops.executable, max_blocks=16)
             for rep in range(2):   # twice: flag words / ready sequence / graph replay
-                layer = tp_layer.DecoderLayerGemms(torch, hal, dev, ops, world, rank, channel,
-                                                   region=region, init=init, chunk_consumers=staged,
-                                                   **dims) if rep == 0 else layer
+                layer = tp_layer.DecoderLayerGemms(
+                    torch, hal, dev, ops, world, rank, channel, region=region, init=init,
+                    chunk_consumers=bool(staged), schedule="dataflow" if staged == "dataflow" else "staged",
+                    **dims) if rep == 0 else layer
                 for k in ("qkv", "o", "gu", "d"):
                     layer.t[k].fill_(float("nan"))
                 dist.barrier()

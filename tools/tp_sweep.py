@@ -66,7 +66,8 @@ def main():
         seen.add(key)
         port += 1
         env = {"IREE_B200_ALL_REDUCE_TUNING": tuning} if tuning else {}
-        for extra in ([], ["--range-fusion"]) if collective == "symmetric" and tuning is None else ([],):
+        for extra in ([], ["--tp-schedule", "staged"], ["--tp-schedule", "fused"]) \
+                if collective == "symmetric" and tuning is None else ([],):
             port += 1
             lines = torchrun(n, port, "bench.py", "--gpus", str(n), "--workload", "tp_decoder_layer",
                              "--collective", collective, "--reserved-sms", str(reserved),
@@ -74,7 +75,7 @@ def main():
                              "--e2e-steps", "2", *extra, env=env)
             for l in lines:
                 emit({"tp_bench": {"collective": collective, "reserved_sms": reserved, "ar_blocks": blocks,
-                                   "tuning": tuning, "range_fusion": bool(extra), "value": l["value"],
+                                   "tuning": tuning, "schedule": extra[-1] if extra else "dataflow", "value": l["value"],
                                    "ms_per_step": l["ms_per_step"], "e2e": l["e2e"]["value"],
                                    "workload": l["config"]["workload"][-260:]}, "world": n})
 
