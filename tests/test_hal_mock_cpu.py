@@ -75,4 +75,4 @@ def test_ops_guards_and_selection_under_the_mock_driver(mock_env):
     """The GPU suites' guard / selection / empty-shape tests need a device but no kernel."""
     out = _run(mock_env, "tests/test_matmul_gpu.py", "tests/test_attention_gpu.py",
                "tests/test_matmul_bias_gpu.py", "-k", "guards or selection or empty_and_zero_k")
-    assert "5 passed" in out, out
+    assert "6 passed" in out, out
