@@ -296,6 +296,56 @@ class MatmulStep:
                 "api": "iree_b200_ops_matmul_host (pinned host buffers)"}
 
 
+class MxStep:
+    """MXFP4 matmul (f4E2M1FN x f4E2M1FN, f8E8M0FNU scale per 32 elements, f32 result; SURVEY
+    §8(f) rank 3, tests/e2e/matmul/generate_code_mx.py) as one dispatch of the block-scaled
+    tcgen05 kernel."""
+
+    def __init__(self, torch, hal, dev, ops, spec, seed):
+        _, _, _, M, N, K = spec
+        self.spec = spec
+        g = torch.Generator(device="cuda")
+        g.manual_seed(0xB200 + seed)
+        rnd = lambda shape, lo, hi: torch.randint(lo, hi, shape, dtype=torch.uint8, device="cuda",
+                                                  generator=g)
+        self.tensors = [rnd((M, K // 2), 0, 256), rnd((M, K // 32), 120, 135),
+                        rnd((N, K // 2), 0, 256), rnd((N, K // 32), 120, 135),
+                        torch.empty((M, N), dtype=torch.float32, device="cuda")]
+        self.buffers = [dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
+                        for t in self.tensors]
+        before = ops.dispatch_count
+        self.cb = hal.CommandBuffer(dev).begin()
+        b = self.buffers
+        ops.record_matmul_mxfp4(self.cb, M, N, K, b[0].ref(), b[1].ref(), b[2].ref(), b[3].ref(),
+                                b[4].ref())
+        self.cb.end()
+        self.launches_per_step = ops.dispatch_count - before
+        self.dev = dev
+
+    def step(self):
+        self.dev.execute(self.cb)
+
+    def host_buffers(self, torch):
+        host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors]
+        for h, t in zip(host[:4], self.tensors[:4]):
+            h.copy_(t)
+        return host
+
+    def host_call(self, ops, host):
+        _, _, _, M, N, K = self.spec
+        ops.matmul_mxfp4_host(M, N, K, *(h.data_ptr() for h in host))
+
+    def describe(self):
+        _, _, _, M, N, K = self.spec
+        operand = (M + N) * (K // 2 + K // 32)
+        return {"flop": 2.0 * M * N * K, "bytes": float(operand + M * N * 4), "bound": "tensor",
+                "workload": f"MXFP4 matmul (f4E2M1FN, f8E8M0FNU scale / 32 elements) M={M} N={N} K={K} "
+                            f"-> f32, tcgen05.mma.kind::mxf4.block_scale, per GPU",
+                "dtype": "f4E2M1FN x f8E8M0FNU block scale (f32 accumulate)",
+                "h2d": int(operand), "d2h": int(M * N * 4),
+                "api": "iree_b200_ops_matmul_mxfp4_host (pinned host buffers)"}
+
+
 class AttentionStep:
     """iree_linalg_ext.attention, one recorded command buffer (1 or 2 dispatches)."""
     FLAGS = 0  # --attention-flags (diagnostics: kernel family / exp2 split)
@@ -413,7 +463,12 @@ class TpLayerStep:
                 "api": "h2d(x) + iree_b200_device_queue_execute(layer command buffer) + d2h(y)"}
 
 
+MX_WORKLOADS = {"matmul_mxfp4": ("matmul", "mxfp4", 1, 8192, 8192, 8192)}
+
+
 def make_step(torch, hal, dev, ops, workload, seed):
+    if workload in MX_WORKLOADS:
+        return MxStep(torch, hal, dev, ops, MX_WORKLOADS[workload], seed)
     if workload in MATMUL_WORKLOADS:
         return MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS[workload], seed,
                           fused=workload in FUSED_WORKLOADS)
@@ -763,7 +818,11 @@ def workload_string(workload, world, info=None):
     """config.workload — identical in both arms (the reference arm times a bounded sample of
     this same workload; its own `sample` key says which)."""
     if info is None:
-        if workload in MATMUL_WORKLOADS:
+        if workload in MX_WORKLOADS:
+            _, _, _, M, N, K = MX_WORKLOADS[workload]
+            text = (f"MXFP4 matmul (f4E2M1FN, f8E8M0FNU scale / 32 elements) M={M} N={N} K={K} "
+                    f"-> f32, tcgen05.mma.kind::mxf4.block_scale, per GPU")
+        elif workload in MATMUL_WORKLOADS:
             op, et, batch, M, N, K = MATMUL_WORKLOADS[workload]
             name = f"linalg.{op}" + (" + bias[n] + relu + truncf (one dispatch)"
                                      if workload in FUSED_WORKLOADS else "")
@@ -791,6 +850,16 @@ def cpu_work(workload, rows):
     reference generator (test_utils.c:359-420) / a seeded PCG as in the parity tests."""
     import numpy as np
     import oracle
+    if workload in MX_WORKLOADS:
+        _, _, _, M, N, K = MX_WORKLOADS[workload]
+        rows = min(rows // 16, M)     # the scalar port decodes every element: a small slab
+        lhs = oracle.generate_random_matrix("u8", (rows, K // 2), 1)
+        ls = oracle.generate_random_matrix("f8e8m0fnu", (rows, K // 32), 2)
+        rhs = oracle.generate_random_matrix("u8", (N, K // 2), 3)
+        rs = oracle.generate_random_matrix("f8e8m0fnu", (N, K // 32), 4)
+        desc = (f"oracle port of the MX reference (generate_code_mx.py:153-172), OpenMP, "
+                f"M={rows} (of {M}) N={N} K={K}")
+        return (lambda: oracle.matmul_mxfp4(lhs, ls, rhs, rs)), 2.0 * rows * N * K, desc, "port"
     if workload in MATMUL_WORKLOADS or workload == "tp_decoder_layer":
         # The TP layer's CPU sample is its QKV projection (same loops, same dtype).
         op, et, batch, M, N, K = MATMUL_WORKLOADS.get(
@@ -903,6 +972,7 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / args.steps
     value = flop / dt / 1e12
     spec = (MATMUL_WORKLOADS.get(args.workload) or ATTENTION_WORKLOADS.get(args.workload) or
+            MX_WORKLOADS.get(args.workload) or
             ("matmul", "bf16", 1, TpLayerStep.TOKENS, TpLayerStep.QKV, TpLayerStep.HIDDEN))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "TFLOP/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -926,7 +996,7 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS)) + ["tp_decoder_layer"])
+    ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS) + list(MX_WORKLOADS)) + ["tp_decoder_layer"])
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--reserved-sms", type=int, default=16,

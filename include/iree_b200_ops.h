@@ -61,6 +61,8 @@ enum {
   IREE_B200_MATMUL_FLAG_FORCE_GENERIC = 1u << 8,
   IREE_B200_MATMUL_FLAG_FORCE_1CTA = 1u << 9,
   IREE_B200_MATMUL_FLAG_FORCE_2CTA = 1u << 10,
+  // MXFP4 only: take the expand-to-bf16 + bf16 GEMM route instead of the block-scaled kernel.
+  IREE_B200_MATMUL_FLAG_MX_EXPAND = 1u << 11,
 };
 
 // The builtin executable ("CDA1" blob linked into this library: one cubin per kernel

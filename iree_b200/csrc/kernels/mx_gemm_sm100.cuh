@@ -43,38 +43,6 @@
 
 namespace b200 {
 
-struct MxGemmConfig {
-  static constexpr int kTileM = 128, kTileN = 256;
-  static constexpr int kBlockKBytes = 128;             // packed bytes of K per row and stage
-  static constexpr int kBlockK = 2 * kBlockKBytes;     // 256 elements
-  static constexpr int kUmmaK = 64;                    // elements per MMA
-  static constexpr int kKSteps = kBlockK / kUmmaK;     // 4
-  static constexpr int kStages = 3;
-  static constexpr int kABytes = kTileM * kBlockKBytes;   // 16 KiB
-  static constexpr int kBBytes = kTileN * kBlockKBytes;   // 32 KiB
-  static constexpr int kAtomBytes = 512;                  // 128 rows x 4 scales
-  static constexpr int kSfaBytes = 2 * kAtomBytes;        // 2 K atoms
-  static constexpr int kSfbBytes = 4 * kAtomBytes;        // 2 K atoms x 2 N halves
-  static constexpr int kStageBytes = kABytes + kBBytes + kSfaBytes + kSfbBytes;  // 51 KiB
-  static constexpr int kEpiCols = 32, kEpiBytes = kTileM * 128, kEpiBufs = 2;
-  static constexpr int kSmemTiles = kStages * kStageBytes + kEpiBufs * kEpiBytes;
-  static constexpr int kNumBarriers = 2 * kStages + 2;
-  static constexpr int kSmemBytes = 1024 + kSmemTiles + kNumBarriers * 8 + 16;
-  static constexpr int kThreads = 256;
-  static constexpr int kTmemCols = 512;
-  static constexpr int kSfCol0 = kTileN;               // first scale column
-  static constexpr int kSfColsPerStage = 8 + 16;
-  static constexpr int kGroupM = 8;
-  // Block-scaled instruction descriptor (cute/arch/mma_sm100_desc.hpp
-  // InstrDescriptorBlockScaled): [7,10) A format, [10,13) B format (E2M1 = 5), [15]/[16]
-  // majors (K), [17,23) N >> 3, [23] scale format (1 = UE8M0), [24,29) M >> 4; the scale
-  // ids ([4,6) B, [29,31) A) are OR-ed in per MMA.
-  static constexpr uint32_t kIdesc = (5u << 7) | (5u << 10) | ((kTileN >> 3) << 17) | (1u << 23) |
-                                     ((kTileM >> 4) << 24);
-  static_assert(kSmemBytes <= 232448, "exceeds 227 KiB of shared memory");
-  static_assert(kSfCol0 + kStages * kSfColsPerStage <= kTmemCols, "TMEM columns");
-};
-
 // No-swizzle shared-memory matrix descriptor of one scale atom: 32 rows of 16 bytes, 8-row
 // core matrices 128 bytes apart.
 B200_DEVICE uint64_t make_smem_desc_sf_atom(uint32_t smem_addr) {

@@ -23,6 +23,31 @@
 
 #include <stdint.h>
 
+#include "mx_gemm_sm100.cuh"
+
+// ---- tcgen05 block-scaled form ---------------------------------------------------------------
+// iree_b200_matmul_mxfp4_f32: bindings lhs [M, K/2] u8, lhs_scales [M, K/32] u8, rhs [N, K/2]
+// u8, rhs_scales [N, K/32] u8 (read-only), out [M, N] f32; constants M, N, K, flags (bit 0:
+// accumulate), K / 2; then the three tensor maps of the recipe (lhs bytes, rhs bytes, out).
+// workgroup_size = [256,1,1]; workgroup count = [min(tiles, #SMs), 1, 1] (persistent).
+// Guards (iree_b200_ops_select side): K % 256 == 0, N % 4 == 0, 16-byte aligned bindings.
+extern "C" __device__ const iree_b200_tma_recipe_t iree_b200_matmul_mxfp4_f32__tma =
+    b200::make_mx_gemm_recipe();
+extern "C" __global__ void __launch_bounds__(b200::MxGemmConfig::kThreads, 1)
+    iree_b200_matmul_mxfp4_f32(const void* __restrict__ lhs, const void* __restrict__ lhs_scales,
+                               const void* __restrict__ rhs, const void* __restrict__ rhs_scales,
+                               void* __restrict__ out, int M, int N, int K, int flags, int k_bytes,
+                               const __grid_constant__ b200::TensorMap tm_a,
+                               const __grid_constant__ b200::TensorMap tm_b,
+                               const __grid_constant__ b200::TensorMap tm_c) {
+  (void)lhs;
+  (void)rhs;
+  (void)k_bytes;
+  b200::mx_gemm_sm100_body(static_cast<const uint8_t*>(lhs_scales),
+                           static_cast<const uint8_t*>(rhs_scales), out, M, N, K, flags, &tm_a,
+                           &tm_b, &tm_c);
+}
+
 namespace {
 
 constexpr int kTile = 64;

@@ -7,6 +7,7 @@
 
 #include "../hal/internal.h"
 #include "../kernels/attention_config.h"
+#include "../kernels/gemm_config.h"
 #include "iree_b200_ops.h"
 
 using namespace b200hal;
@@ -62,6 +63,7 @@ struct iree_b200_ops_t {
   iree_b200_executable_t* pending_executable = nullptr;
   int32_t mxfp4_generic_export = -1;
   int32_t mxfp4_dequant_export = -1;
+  int32_t mxfp4_block_scaled_export = -1;
   int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
   int32_t mmt4d_relayout_exports[3] = {-1, -1, -1};  // 1-, 2-, 4-byte elements
   std::mutex pending_mutex;
@@ -841,13 +843,14 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
       ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
       &executable));
-  static const char* const kNames[8] = {
+  static const char* const kNames[9] = {
       "iree_b200_matmul_generic_mxfp4_f32", "iree_b200_matmul_mxfp4_dequant_bf16",
       "iree_b200_mmt4d_generic_i8_i32",     "iree_b200_mmt4d_generic_f16_f32",
       "iree_b200_mmt4d_generic_bf16_f32",   "iree_b200_mmt4d_relayout_b8",
-      "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32"};
-  int32_t ordinals[8];
-  for (int i = 0; i < 8; ++i) {
+      "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32",
+      "iree_b200_matmul_mxfp4_f32"};
+  int32_t ordinals[9];
+  for (int i = 0; i < 9; ++i) {
     ordinals[i] = lookup(executable, kNames[i]);
     if (ordinals[i] < 0) {
       iree_b200_executable_release(executable);
@@ -857,6 +860,7 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   }
   ops->mxfp4_generic_export = ordinals[0];
   ops->mxfp4_dequant_export = ordinals[1];
+  ops->mxfp4_block_scaled_export = ordinals[8];
   for (int i = 0; i < 3; ++i) {
     ops->mmt4d_generic_exports[i] = ordinals[2 + i];
     ops->mmt4d_relayout_exports[i] = ordinals[5 + i];
@@ -884,10 +888,11 @@ static iree_b200_status_t record_matmul_mxfp4_impl(
     const iree_b200_buffer_ref_t* workspace) {
   B200_REQUIRE_ARG(ops && cb);
   B200_RETURN_IF_ERROR(require_device(ops));
-  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC)) {
+  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC |
+                          IREE_B200_MATMUL_FLAG_MX_EXPAND)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
-                       "the MXFP4 matmul takes FLAG_ACCUMULATE and FLAG_FORCE_GENERIC only "
-                       "(operands are always [rows, K])");
+                       "the MXFP4 matmul takes FLAG_ACCUMULATE, FLAG_FORCE_GENERIC and "
+                       "FLAG_MX_EXPAND only (operands are always [rows, K])");
   }
   if (M < 0 || N < 0 || K < 0 || M > INT32_MAX || N > INT32_MAX || K > INT32_MAX ||
       K % IREE_B200_MX_BLOCK_SIZE) {
@@ -924,6 +929,25 @@ static iree_b200_status_t record_matmul_mxfp4_impl(
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 result must be 4-byte aligned");
   }
   B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
+  // The block-scaled tensor-core kernel (tcgen05.mma.kind::mxf4.block_scale, one dispatch, no
+  // workspace): K in whole 256-element stages, TMA-legal operand / result pitches and bases,
+  // 4-byte readable scale rows.
+  auto aligned = [](const iree_b200_buffer_ref_t& r, uint64_t a) {
+    return r.buffer && (r.buffer->device_ptr + r.offset) % a == 0;
+  };
+  if (!(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_MX_EXPAND)) && K >= 256 &&
+      K % 256 == 0 && N % 4 == 0 && aligned(lhs, 16) && aligned(rhs, 16) && aligned(out, 16) &&
+      aligned(lhs_scales, 4) && aligned(rhs_scales, 4)) {
+    const int64_t tiles = ceil_div(M, b200::MxGemmConfig::kTileM) * ceil_div(N, b200::MxGemmConfig::kTileN);
+    const int64_t sms = std::max<int64_t>(1, ops->sm_count - ops->reserved_sms);
+    const uint32_t grid[3] = {(uint32_t)std::min<int64_t>(tiles, sms), 1, 1};
+    const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K,
+                                   flags & IREE_B200_MATMUL_FLAG_ACCUMULATE, (uint32_t)(K / 2)};
+    B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+        cb, ops->pending_executable, ops->mxfp4_block_scaled_export, grid, constants, 5, refs, 5, 0));
+    ops->dispatch_count.fetch_add(1);
+    return IREE_B200_STATUS_OK;
+  }
   const uint64_t ws_need = iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
   if (workspace && workspace->buffer && ws_need) {
     const uint64_t total = workspace->buffer->byte_length;
@@ -1017,8 +1041,11 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     offsets[i] = total;
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
+  // The expansion workspace is only needed when the bf16-expansion route can be taken.
+  const bool block_scaled = !(flags & IREE_B200_MATMUL_FLAG_MX_EXPAND) && K >= 256 && K % 256 == 0 &&
+                            N % 4 == 0;
   const uint64_t ws_offset = total,
-                 ws_bytes = (flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC)
+                 ws_bytes = ((flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC) || block_scaled)
                                 ? 0
                                 : iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
   total += ws_bytes;

@@ -1,9 +1,10 @@
 """MXFP4 matmul on the GPU against the oracle (bit-exact on the reference generator's inputs).
 
-PENDING VALIDATION: kernels/mx_kernels.cu was written after this round's GPU budget was
-spent; its device code has only been executed on host threads (tests/test_mx_host_shim.py).
-These tests are skipped unless IREE_B200_PENDING_VALIDATION=1, so the round-end GPU run stays
-a statement about validated code. First thing next round: run them, then drop the gate.
+Three routes (iree_b200_ops_matmul_mxfp4_host picks; flags force): the block-scaled tcgen05
+kernel (kind::mxf4.block_scale; K % 256 == 0, N % 4 == 0), the exact bf16 expansion + bf16
+tcgen05 GEMM (FLAG_MX_EXPAND; tile-filling shapes), the SIMT kernel (FLAG_FORCE_GENERIC; any
+shape). First GPU run of the SIMT / expansion routes: round 2
+(profiles/mmt4d_mxfp4_first_gpu_run_r2.json).
 """
 
 import os
@@ -39,9 +40,70 @@ def test_mxfp4_matmul_vs_oracle(ops, shape, accumulate):
     ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
                           rs.ctypes.data, out.ctypes.data,
                           flags=H.MATMUL_ACCUMULATE if accumulate else 0)
-    # Shapes on the tensor-core route expand both operands to bf16 first (3 dispatches).
-    assert ops.dispatch_count - before == (3 if ops.matmul_mxfp4_workspace_size(M, N, K) else 1)
+    # Block-scaled kernel: one dispatch; bf16-expansion route: 3; SIMT: 1.
+    block_scaled = K >= 256 and K % 256 == 0 and N % 4 == 0
+    expected = 1 if block_scaled else (3 if ops.matmul_mxfp4_workspace_size(M, N, K) else 1)
+    assert ops.dispatch_count - before == expected
     assert np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc))
+
+
+@pytest.mark.parametrize("shape", [(128, 256, 256), (129, 256, 4), (1000, 512, 264), (300, 768, 520),
+                                   (128, 2048, 256), (257, 1024, 1028), (2048, 2048, 2048)], ids=str)
+@pytest.mark.parametrize("accumulate", [False, True], ids=["", "acc"])
+def test_block_scaled_kernel_and_the_other_routes_agree_with_the_oracle(ops, shape, accumulate):
+    """tcgen05.mma.kind::mxf4.block_scale (iree_b200_matmul_mxfp4_f32) against the oracle, bit
+    for bit on the reference generator's inputs, ragged M / N tiles, many K stages; and the
+    same call forced onto the expansion route and the SIMT kernel."""
+    M, K, N = shape
+    lhs, ls, rhs, rs, acc = _inputs(M, K, N, accumulate)
+    want = oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc)
+    base = H.MATMUL_ACCUMULATE if accumulate else 0
+    for route, flag, dispatches in (("block_scaled", 0, 1), ("expand", H.MATMUL_MX_EXPAND, None),
+                                    ("simt", H.MATMUL_FORCE_GENERIC, 1)):
+        if route == "simt" and M * N * K > 1 << 28:
+            continue
+        out = acc.copy() if accumulate else np.full((M, N), 77, dtype=np.float32)
+        before = ops.dispatch_count
+        ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                              rs.ctypes.data, out.ctypes.data, flags=base | flag)
+        if dispatches is not None:
+            assert ops.dispatch_count - before == dispatches, route
+        assert np.array_equal(out, want), route
+
+
+def test_block_scaled_kernel_random_scales_and_values(ops):
+    """Full-range f4 codes and scales spread over 2^-10 .. 2^10 (PCG): sums are no longer exact,
+    so the bar is the f32 summation-order tolerance against the oracle (k-ascending)."""
+    M, K, N = 384, 1024, 512
+    g = np.random.Generator(np.random.PCG64(0xB200))
+    lhs = g.integers(0, 256, (M, K // 2), dtype=np.uint8)
+    rhs = g.integers(0, 256, (N, K // 2), dtype=np.uint8)
+    ls = g.integers(117, 138, (M, K // 32), dtype=np.uint8)
+    rs = g.integers(117, 138, (N, K // 32), dtype=np.uint8)
+    out = np.zeros((M, N), dtype=np.float32)
+    ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                          rs.ctypes.data, out.ctypes.data)
+    want = oracle.matmul_mxfp4(lhs, ls, rhs, rs)
+    assert np.abs(out - want).max() <= 1e-5 * np.abs(want).max()
+
+
+def test_block_scaled_kernel_special_scales(ops):
+    """NaN scale (0xFF) poisons exactly the rows / columns it scales; the smallest scale
+    (2^-127) gives products deep in the f32 subnormals (the tensor core may flush those)."""
+    M, K, N = 128, 256, 256
+    lhs, ls, rhs, rs, _ = _inputs(M, K, N, False)
+    ls[2, 1] = 0xFF
+    rs[5, 0] = 0
+    ls[7, :] = 1
+    out = np.zeros((M, N), dtype=np.float32)
+    before = ops.dispatch_count
+    ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
+                          rs.ctypes.data, out.ctypes.data)
+    assert ops.dispatch_count - before == 1
+    want = oracle.matmul_mxfp4(lhs, ls, rhs, rs)
+    assert np.isnan(out[2]).all() and np.array_equal(np.isnan(out), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.allclose(out[ok], want[ok], rtol=1e-6, atol=1e-30)
 
 
 def test_mxfp4_special_scales_and_guards(ops):

@@ -38,12 +38,9 @@ def main():
         out.flush()
 
     variants = []
-    for blocks in (16, 32, 64):
-        for threads in (512, 1024):
-            for unroll, pipe in ((4, 0), (8, 0), (2, 1), (4, 1)):
-                if blocks == 16 and threads == 512:
-                    continue
-                variants.append((blocks, threads, unroll, pipe))
+    for blocks in (8, 16, 24, 32, 64):
+        for threads, unroll, pipe in ((1024, 4, 0), (1024, 2, 1), (512, 4, 0)):
+            variants.append((blocks, threads, unroll, pipe))
     lines = torchrun(n, 29581, "tools/symmetric_check.py", "--mib", "64", "--iters", "20", "--sweep",
                      ";".join(",".join(map(str, v)) for v in variants), timeout=900)
     rows = lines[-1]["sweep"] if lines else []
@@ -52,7 +49,7 @@ def main():
     port = 29590
     configs = [("nccl", 16, 16, None), ("symmetric", 16, 16, None)]
     ok = [r for r in rows if r["exact"]]
-    for cap in (16, 32):
+    for cap in (8, 24, 32):
         fit = sorted((r for r in ok if r["blocks"] <= cap), key=lambda r: r["ms_16mib"])
         if fit:
             b = fit[0]
