@@ -311,13 +311,17 @@ class MxStep:
         self.tensors = [rnd((M, K // 2), 0, 256), rnd((M, K // 32), 120, 135),
                         rnd((N, K // 2), 0, 256), rnd((N, K // 32), 120, 135),
                         torch.empty((M, N), dtype=torch.float32, device="cuda")]
+        # Workspace for the scales in the instruction's atom order (two small repack dispatches
+        # ahead of the GEMM, every step: the scales of activations change per call).
+        self.tensors.append(torch.empty(max(16, ops.matmul_mxfp4_scale_workspace_size(M, N, K)),
+                                        dtype=torch.uint8, device="cuda"))
         self.buffers = [dev.import_buffer(t.data_ptr(), t.numel() * t.element_size())
                         for t in self.tensors]
         before = ops.dispatch_count
         self.cb = hal.CommandBuffer(dev).begin()
         b = self.buffers
-        ops.record_matmul_mxfp4(self.cb, M, N, K, b[0].ref(), b[1].ref(), b[2].ref(), b[3].ref(),
-                                b[4].ref())
+        ops.record_matmul_mxfp4_tensor(self.cb, M, N, K, b[0].ref(), b[1].ref(), b[2].ref(),
+                                       b[3].ref(), b[5].ref(), b[4].ref())
         self.cb.end()
         self.launches_per_step = ops.dispatch_count - before
         self.dev = dev
@@ -326,7 +330,7 @@ class MxStep:
         self.dev.execute(self.cb)
 
     def host_buffers(self, torch):
-        host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors]
+        host = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in self.tensors[:5]]
         for h, t in zip(host[:4], self.tensors[:4]):
             h.copy_(t)
         return host
@@ -340,7 +344,7 @@ class MxStep:
         operand = (M + N) * (K // 2 + K // 32)
         return {"flop": 2.0 * M * N * K, "bytes": float(operand + M * N * 4), "bound": "tensor",
                 "workload": f"MXFP4 matmul (f4E2M1FN, f8E8M0FNU scale / 32 elements) M={M} N={N} K={K} "
-                            f"-> f32, tcgen05.mma.kind::mxf4.block_scale, per GPU",
+                            f"-> f32, tcgen05.mma.kind::mxf4.block_scale (scale repack x2 + GEMM), per GPU",
                 "dtype": "f4E2M1FN x f8E8M0FNU block scale (f32 accumulate)",
                 "h2d": int(operand), "d2h": int(M * N * 4),
                 "api": "iree_b200_ops_matmul_mxfp4_host (pinned host buffers)"}
@@ -821,7 +825,7 @@ def workload_string(workload, world, info=None):
         if workload in MX_WORKLOADS:
             _, _, _, M, N, K = MX_WORKLOADS[workload]
             text = (f"MXFP4 matmul (f4E2M1FN, f8E8M0FNU scale / 32 elements) M={M} N={N} K={K} "
-                    f"-> f32, tcgen05.mma.kind::mxf4.block_scale, per GPU")
+                    f"-> f32, tcgen05.mma.kind::mxf4.block_scale (scale repack x2 + GEMM), per GPU")
         elif workload in MATMUL_WORKLOADS:
             op, et, batch, M, N, K = MATMUL_WORKLOADS[workload]
             name = f"linalg.{op}" + (" + bias[n] + relu + truncf (one dispatch)"

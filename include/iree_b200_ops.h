@@ -193,6 +193,14 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_record_matmul_mxfp4_tensor(
     iree_b200_buffer_ref_t rhs, iree_b200_buffer_ref_t rhs_scales,
     iree_b200_buffer_ref_t workspace, iree_b200_buffer_ref_t out);
 
+// Bytes of workspace with which iree_b200_ops_record_matmul_mxfp4_tensor takes the fast form
+// of the block-scaled tcgen05 kernel (scales repacked into the instruction's atom order by
+// two small dispatches, then moved by TMA); 0 when the shape does not qualify (K % 256,
+// N % 4). A workspace of max(this, iree_b200_ops_matmul_mxfp4_workspace_size) serves every
+// route.
+IREE_B200_API uint64_t iree_b200_ops_matmul_mxfp4_scale_workspace_size(int64_t M, int64_t N,
+                                                                       int64_t K);
+
 IREE_B200_API iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(
     iree_b200_ops_t* ops, int64_t M, int64_t N, int64_t K, uint32_t flags, const void* lhs,
     const void* lhs_scales, const void* rhs, const void* rhs_scales, void* out);

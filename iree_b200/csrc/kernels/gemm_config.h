@@ -88,36 +88,46 @@ struct GemmConfig {
 };
 
 // MXFP4 block-scaled GEMM (mx_gemm_sm100.cuh): tcgen05.mma.kind::mxf4.block_scale.
+// kCtaGroup 2 pairs two CTAs of a cluster on a 256 x 256 tile (each CTA: 128 rows of A and
+// 128 of the 256 columns of B in its shared memory, all 256 columns' scales in its TMEM).
+template <int kCtaGroup_>
 struct MxGemmConfig {
-  static constexpr int kTileM = 128, kTileN = 256;
-  static constexpr int kBlockKBytes = 128;             // packed bytes of K per row and stage
-  static constexpr int kBlockK = 2 * kBlockKBytes;     // 256 elements
-  static constexpr int kUmmaK = 64;                    // elements per MMA
-  static constexpr int kKSteps = kBlockK / kUmmaK;     // 4
-  static constexpr int kStages = 3;
-  static constexpr int kABytes = kTileM * kBlockKBytes;   // 16 KiB
-  static constexpr int kBBytes = kTileN * kBlockKBytes;   // 32 KiB
+  static constexpr int kCtaGroup = kCtaGroup_;
+  static constexpr int kBlockM = 128;                     // A rows per CTA
+  static constexpr int kTileM = kBlockM * kCtaGroup, kTileN = 256;
+  static constexpr int kBlockN = kTileN / kCtaGroup;      // B rows (result columns) loaded per CTA
+  static constexpr int kBlockKBytes = 128;                // packed bytes of K per row and stage
+  static constexpr int kBlockK = 2 * kBlockKBytes;        // 256 elements
+  static constexpr int kUmmaK = 64;                       // elements per MMA
+  static constexpr int kKSteps = kBlockK / kUmmaK;        // 4
+  static constexpr int kStages = kCtaGroup == 2 ? 5 : 3;
+  static constexpr int kABytes = kBlockM * kBlockKBytes;  // 16 KiB
+  static constexpr int kBBytes = kBlockN * kBlockKBytes;  // 16 / 32 KiB
   static constexpr int kAtomBytes = 512;                  // 128 rows x 4 scales
-  static constexpr int kSfaBytes = 2 * kAtomBytes;        // 2 K atoms
-  static constexpr int kSfbBytes = 4 * kAtomBytes;        // 2 K atoms x 2 N halves
-  static constexpr int kStageBytes = kABytes + kBBytes + kSfaBytes + kSfbBytes;  // 51 KiB
-  static constexpr int kEpiCols = 32, kEpiBytes = kTileM * 128, kEpiBufs = 2;
-  static constexpr int kSmemTiles = kStages * kStageBytes + kEpiBufs * kEpiBytes;
-  static constexpr int kNumBarriers = 2 * kStages + 2;
+  static constexpr int kSfaBytes = 2 * kAtomBytes;        // 2 K atoms of this CTA's 128 rows
+  static constexpr int kSfbBytes = 4 * kAtomBytes;        // 2 K atoms x 2 halves of the 256 columns
+  static constexpr int kStageBytes = kABytes + kBBytes + kSfaBytes + kSfbBytes;
+  // Epilogue: two warpgroups (column halves), one 16 KiB staging buffer each.
+  static constexpr int kEpiCols = 32, kEpiBytes = kBlockM * 128, kEpiGroups = 2;
+  static constexpr int kSmemTiles = kStages * kStageBytes + kEpiGroups * kEpiBytes;
+  static constexpr int kNumBarriers = 3 * kStages + 2;    // full, empty, scales-landed; tfull, tempty
   static constexpr int kSmemBytes = 1024 + kSmemTiles + kNumBarriers * 8 + 16;
-  static constexpr int kThreads = 256;
+  static constexpr int kThreads = 384;                    // warps 0-3 control, 4-11 epilogue
   static constexpr int kTmemCols = 512;
-  static constexpr int kSfCol0 = kTileN;               // first scale column
+  static constexpr int kSfCol0 = kTileN;                  // first scale column
   static constexpr int kSfColsPerStage = 8 + 16;
   static constexpr int kGroupM = 8;
+  static constexpr int kScaleLookahead = 2;               // stages the scale loader runs ahead
   // Block-scaled instruction descriptor (cute/arch/mma_sm100_desc.hpp
-  // InstrDescriptorBlockScaled): [7,10) A format, [10,13) B format (E2M1 = 5), [15]/[16]
+  // InstrDescriptorBlockScaled): [7,10) A format, [10,13) B format (kind::mxf4: E2M1 = 1;
+  // the value 5 belongs to kind::mxf8f6f4's unpacked form and is illegal here), [15]/[16]
   // majors (K), [17,23) N >> 3, [23] scale format (1 = UE8M0), [24,29) M >> 4; the scale
   // ids ([4,6) B, [29,31) A) are OR-ed in per MMA.
-  static constexpr uint32_t kIdesc = (5u << 7) | (5u << 10) | ((kTileN >> 3) << 17) | (1u << 23) |
+  static constexpr uint32_t kIdesc = (1u << 7) | (1u << 10) | ((kTileN >> 3) << 17) | (1u << 23) |
                                      ((kTileM >> 4) << 24);
   static_assert(kSmemBytes <= 232448, "exceeds 227 KiB of shared memory");
   static_assert(kSfCol0 + kStages * kSfColsPerStage <= kTmemCols, "TMEM columns");
+  static_assert(kScaleLookahead < kStages, "lookahead");
 };
 
 }  // namespace b200

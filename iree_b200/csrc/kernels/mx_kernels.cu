@@ -26,26 +26,87 @@
 #include "mx_gemm_sm100.cuh"
 
 // ---- tcgen05 block-scaled form ---------------------------------------------------------------
-// iree_b200_matmul_mxfp4_f32: bindings lhs [M, K/2] u8, lhs_scales [M, K/32] u8, rhs [N, K/2]
-// u8, rhs_scales [N, K/32] u8 (read-only), out [M, N] f32; constants M, N, K, flags (bit 0:
-// accumulate), K / 2; then the three tensor maps of the recipe (lhs bytes, rhs bytes, out).
-// workgroup_size = [256,1,1]; workgroup count = [min(tiles, #SMs), 1, 1] (persistent).
-// Guards (iree_b200_ops_select side): K % 256 == 0, N % 4 == 0, 16-byte aligned bindings.
-extern "C" __device__ const iree_b200_tma_recipe_t iree_b200_matmul_mxfp4_f32__tma =
-    b200::make_mx_gemm_recipe();
-extern "C" __global__ void __launch_bounds__(b200::MxGemmConfig::kThreads, 1)
-    iree_b200_matmul_mxfp4_f32(const void* __restrict__ lhs, const void* __restrict__ lhs_scales,
-                               const void* __restrict__ rhs, const void* __restrict__ rhs_scales,
-                               void* __restrict__ out, int M, int N, int K, int flags, int k_bytes,
-                               const __grid_constant__ b200::TensorMap tm_a,
-                               const __grid_constant__ b200::TensorMap tm_b,
-                               const __grid_constant__ b200::TensorMap tm_c) {
-  (void)lhs;
-  (void)rhs;
-  (void)k_bytes;
-  b200::mx_gemm_sm100_body(static_cast<const uint8_t*>(lhs_scales),
-                           static_cast<const uint8_t*>(rhs_scales), out, M, N, K, flags, &tm_a,
-                           &tm_b, &tm_c);
+// iree_b200_matmul_mxfp4_f32 (SM pairs, 256 x 256 tiles) / _1cta (128 x 256): bindings lhs
+// [M, K/2] u8, lhs_scales [M, K/32] u8, rhs [N, K/2] u8, rhs_scales [N, K/32] u8 (read-only),
+// out [M, N] f32; constants M, N, K, flags (bit 0: accumulate), K / 2; then the three tensor
+// maps of the recipe (lhs bytes, rhs bytes, out). workgroup_size = [384,1,1]; workgroup count
+// = [min(tiles x CTAs per tile, #SMs), 1, 1] (persistent). Guards (ops layer): K % 256 == 0,
+// N % 4 == 0, 16-byte aligned operand / result bindings, 4-byte aligned scale bindings.
+#define B200_MXFP4(NAME, G, CLUSTER)                                                            \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                              \
+      b200::make_mx_gemm_recipe(false);                                                         \
+  extern "C" __global__ void CLUSTER __launch_bounds__(b200::MxGemmConfig<G>::kThreads, 1)      \
+      NAME(const void* __restrict__ lhs, const void* __restrict__ lhs_scales,                   \
+           const void* __restrict__ rhs, const void* __restrict__ rhs_scales,                   \
+           void* __restrict__ out, int M, int N, int K, int flags, int k_bytes,                 \
+           const __grid_constant__ b200::TensorMap tm_a,                                        \
+           const __grid_constant__ b200::TensorMap tm_b,                                        \
+           const __grid_constant__ b200::TensorMap tm_c) {                                      \
+    (void)lhs;                                                                                  \
+    (void)rhs;                                                                                  \
+    (void)k_bytes;                                                                              \
+    b200::mx_gemm_sm100_body<b200::MxGemmConfig<G>, false>(                                     \
+        static_cast<const uint8_t*>(lhs_scales), static_cast<const uint8_t*>(rhs_scales), out,  \
+        M, N, K, flags, &tm_a, &tm_b, &tm_c);                                                   \
+  }
+
+B200_MXFP4(iree_b200_matmul_mxfp4_f32, 2, __cluster_dims__(2, 1, 1))
+B200_MXFP4(iree_b200_matmul_mxfp4_f32_1cta, 1, )
+
+// iree_b200_matmul_mxfp4_packed_f32[_1cta]: the same with the scale bindings already in atom
+// order ([ceil(rows / 128)][K / 128][512 bytes], 16-byte aligned); constants M, N, K, flags,
+// K / 2, K / 128, ceil(M / 128), ceil(N / 128); five tensor maps (lhs, rhs, out, lhs scale
+// atoms, rhs scale atoms).
+#define B200_MXFP4_PACKED(NAME, G, CLUSTER)                                                     \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                              \
+      b200::make_mx_gemm_recipe(true);                                                          \
+  extern "C" __global__ void CLUSTER __launch_bounds__(b200::MxGemmConfig<G>::kThreads, 1)      \
+      NAME(const void* __restrict__ lhs, const void* __restrict__ lhs_scales,                   \
+           const void* __restrict__ rhs, const void* __restrict__ rhs_scales,                   \
+           void* __restrict__ out, int M, int N, int K, int flags, int k_bytes, int k_atoms,    \
+           int m_tiles, int n_tiles, const __grid_constant__ b200::TensorMap tm_a,              \
+           const __grid_constant__ b200::TensorMap tm_b,                                        \
+           const __grid_constant__ b200::TensorMap tm_c,                                        \
+           const __grid_constant__ b200::TensorMap tm_sfa,                                      \
+           const __grid_constant__ b200::TensorMap tm_sfb) {                                    \
+    (void)lhs;                                                                                  \
+    (void)rhs;                                                                                  \
+    (void)k_bytes;                                                                              \
+    (void)k_atoms;                                                                              \
+    (void)m_tiles;                                                                              \
+    (void)n_tiles;                                                                              \
+    b200::mx_gemm_sm100_body<b200::MxGemmConfig<G>, true>(                                      \
+        static_cast<const uint8_t*>(lhs_scales), static_cast<const uint8_t*>(rhs_scales), out,  \
+        M, N, K, flags, &tm_a, &tm_b, &tm_c, &tm_sfa, &tm_sfb);                                 \
+  }
+
+B200_MXFP4_PACKED(iree_b200_matmul_mxfp4_packed_f32, 2, __cluster_dims__(2, 1, 1))
+B200_MXFP4_PACKED(iree_b200_matmul_mxfp4_packed_f32_1cta, 1, )
+
+// iree_b200_mxfp4_pack_scales: row-major scales [rows, K / 32] -> the atoms the block-scaled
+// instruction reads: out[(rt * (K / 128) + ka) * 512 + (r % 32) * 16 + ((r % 128) / 32) * 4 + c]
+// = in[r, 4 ka + c], r = 128 rt + ..., rows padded to a multiple of 128 with the scale 1.0
+// (0x7F; padded rows only reach result rows / columns the TMA store clips). One thread per
+// output word (coalesced 4-byte stores; the reads are 4 aligned bytes of one row).
+// bindings: scales (read-only), atoms; constants rows, K. workgroup_size [256,1,1],
+// workgroup count [ceil(ceil(rows / 128) * (K / 128) * 128 / 256), 1, 1]. K % 128 == 0.
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mxfp4_pack_scales(const uint8_t* __restrict__ scales, uint32_t* __restrict__ atoms,
+                                int rows, int K) {
+  const int k_atoms = K / 128;
+  const long long word = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long total = (long long)((rows + 127) / 128) * k_atoms * 128;
+  if (word >= total) return;
+  const int j = (int)(word % 128);
+  const long long atom = word / 128;
+  const int ka = (int)(atom % k_atoms), rt = (int)(atom / k_atoms);
+  const int r = rt * 128 + (j % 4) * 32 + j / 4;
+  uint32_t v = 0x7F7F7F7Fu;
+  if (r < rows) {
+    const uint8_t* p = scales + (size_t)r * (K / 32) + ka * 4;
+    v = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
+  }
+  atoms[word] = v;
 }
 
 namespace {

@@ -64,6 +64,8 @@ struct iree_b200_ops_t {
   int32_t mxfp4_generic_export = -1;
   int32_t mxfp4_dequant_export = -1;
   int32_t mxfp4_block_scaled_export = -1;
+  int32_t mxfp4_block_scaled_1cta_export = -1;
+  int32_t mxfp4_packed_export = -1, mxfp4_packed_1cta_export = -1, mxfp4_pack_scales_export = -1;
   int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
   int32_t mmt4d_relayout_exports[3] = {-1, -1, -1};  // 1-, 2-, 4-byte elements
   std::mutex pending_mutex;
@@ -843,14 +845,16 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
       ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
       &executable));
-  static const char* const kNames[9] = {
+  static const char* const kNames[13] = {
       "iree_b200_matmul_generic_mxfp4_f32", "iree_b200_matmul_mxfp4_dequant_bf16",
       "iree_b200_mmt4d_generic_i8_i32",     "iree_b200_mmt4d_generic_f16_f32",
       "iree_b200_mmt4d_generic_bf16_f32",   "iree_b200_mmt4d_relayout_b8",
       "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32",
-      "iree_b200_matmul_mxfp4_f32"};
-  int32_t ordinals[9];
-  for (int i = 0; i < 9; ++i) {
+      "iree_b200_matmul_mxfp4_f32",         "iree_b200_matmul_mxfp4_f32_1cta",
+      "iree_b200_matmul_mxfp4_packed_f32",  "iree_b200_matmul_mxfp4_packed_f32_1cta",
+      "iree_b200_mxfp4_pack_scales"};
+  int32_t ordinals[13];
+  for (int i = 0; i < 13; ++i) {
     ordinals[i] = lookup(executable, kNames[i]);
     if (ordinals[i] < 0) {
       iree_b200_executable_release(executable);
@@ -861,6 +865,10 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   ops->mxfp4_generic_export = ordinals[0];
   ops->mxfp4_dequant_export = ordinals[1];
   ops->mxfp4_block_scaled_export = ordinals[8];
+  ops->mxfp4_block_scaled_1cta_export = ordinals[9];
+  ops->mxfp4_packed_export = ordinals[10];
+  ops->mxfp4_packed_1cta_export = ordinals[11];
+  ops->mxfp4_pack_scales_export = ordinals[12];
   for (int i = 0; i < 3; ++i) {
     ops->mmt4d_generic_exports[i] = ordinals[2 + i];
     ops->mmt4d_relayout_exports[i] = ordinals[5 + i];
@@ -876,6 +884,21 @@ static bool mxfp4_tensor_route(int64_t M, int64_t N, int64_t K) {
   return M >= 128 && N >= 128 && K >= 128 && (N * 4) % 16 == 0;
 }
 
+// Shapes the block-scaled tcgen05 kernel takes (K in whole 256-element stages, TMA-legal
+// operand and result pitches).
+static bool mxfp4_block_scaled_shape(int64_t M, int64_t N, int64_t K) {
+  return M > 0 && N > 0 && K >= 256 && K % 256 == 0 && N % 4 == 0;
+}
+
+static uint64_t mxfp4_scale_atoms_bytes(int64_t rows, int64_t K) {
+  return (uint64_t)ceil_div(rows, 128) * (uint64_t)(K / 128) * 512;
+}
+
+uint64_t iree_b200_ops_matmul_mxfp4_scale_workspace_size(int64_t M, int64_t N, int64_t K) {
+  if (M < 0 || N < 0 || K < 0 || !mxfp4_block_scaled_shape(M, N, K)) return 0;
+  return mxfp4_scale_atoms_bytes(M, K) + mxfp4_scale_atoms_bytes(N, K);  // multiples of 512
+}
+
 uint64_t iree_b200_ops_matmul_mxfp4_workspace_size(int64_t M, int64_t N, int64_t K) {
   if (M < 0 || N < 0 || K < 0 || !mxfp4_tensor_route(M, N, K)) return 0;
   return ((uint64_t)M * K * 2 + 255) / 256 * 256 + (uint64_t)N * K * 2;
@@ -889,7 +912,8 @@ static iree_b200_status_t record_matmul_mxfp4_impl(
   B200_REQUIRE_ARG(ops && cb);
   B200_RETURN_IF_ERROR(require_device(ops));
   if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC |
-                          IREE_B200_MATMUL_FLAG_MX_EXPAND)) {
+                          IREE_B200_MATMUL_FLAG_MX_EXPAND | IREE_B200_MATMUL_FLAG_FORCE_1CTA |
+                          IREE_B200_MATMUL_FLAG_FORCE_2CTA)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "the MXFP4 matmul takes FLAG_ACCUMULATE, FLAG_FORCE_GENERIC and "
                        "FLAG_MX_EXPAND only (operands are always [rows, K])");
@@ -929,22 +953,77 @@ static iree_b200_status_t record_matmul_mxfp4_impl(
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "MXFP4 result must be 4-byte aligned");
   }
   B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
-  // The block-scaled tensor-core kernel (tcgen05.mma.kind::mxf4.block_scale, one dispatch, no
-  // workspace): K in whole 256-element stages, TMA-legal operand / result pitches and bases,
-  // 4-byte readable scale rows.
+  // The block-scaled tensor-core kernel (tcgen05.mma.kind::mxf4.block_scale): K in whole
+  // 256-element stages, TMA-legal operand / result pitches and bases, 4-byte readable scale
+  // rows. With a workspace the scales are first repacked into the instruction's atom order
+  // (two small dispatches) and the kernel moves them by TMA (5.6 PFLOP/s at 8192^3); without,
+  // one dispatch gathers them itself at about half that rate.
   auto aligned = [](const iree_b200_buffer_ref_t& r, uint64_t a) {
     return r.buffer && (r.buffer->device_ptr + r.offset) % a == 0;
   };
-  if (!(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_MX_EXPAND)) && K >= 256 &&
-      K % 256 == 0 && N % 4 == 0 && aligned(lhs, 16) && aligned(rhs, 16) && aligned(out, 16) &&
+  if (!(flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_MX_EXPAND)) &&
+      mxfp4_block_scaled_shape(M, N, K) && aligned(lhs, 16) && aligned(rhs, 16) && aligned(out, 16) &&
       aligned(lhs_scales, 4) && aligned(rhs_scales, 4)) {
-    const int64_t tiles = ceil_div(M, b200::MxGemmConfig::kTileM) * ceil_div(N, b200::MxGemmConfig::kTileN);
-    const int64_t sms = std::max<int64_t>(1, ops->sm_count - ops->reserved_sms);
-    const uint32_t grid[3] = {(uint32_t)std::min<int64_t>(tiles, sms), 1, 1};
-    const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K,
-                                   flags & IREE_B200_MATMUL_FLAG_ACCUMULATE, (uint32_t)(K / 2)};
+    // Same family rule as the other tcgen05 GEMMs: SM pairs once there are enough 256 x 256
+    // tiles to occupy them (FORCE_1CTA / FORCE_2CTA override).
+    const int64_t sms = std::max<int64_t>(2, ops->sm_count - ops->reserved_sms);
+    const int64_t tiles_2cta = ceil_div(M, 256) * ceil_div(N, 256);
+    const int64_t tiles_1cta = ceil_div(M, 128) * ceil_div(N, 256);
+    bool pair = M > 128 && tiles_2cta * 2 >= sms;
+    if (flags & IREE_B200_MATMUL_FLAG_FORCE_1CTA) pair = false;
+    if (flags & IREE_B200_MATMUL_FLAG_FORCE_2CTA) pair = true;
+    const uint32_t grid[3] = {
+        (uint32_t)(pair ? std::min<int64_t>(tiles_2cta * 2, sms & ~1) : std::min<int64_t>(tiles_1cta, sms)),
+        1, 1};
+    uint32_t kernel_flags = flags & IREE_B200_MATMUL_FLAG_ACCUMULATE;
+    if (const char* diag = getenv("IREE_B200_MX_DIAG")) kernel_flags |= (uint32_t)strtoul(diag, nullptr, 0);
+    const uint64_t sf_need = iree_b200_ops_matmul_mxfp4_scale_workspace_size(M, N, K);
+    bool packed = false;
+    if (workspace && workspace->buffer) {
+      const uint64_t total = workspace->buffer->byte_length;
+      if (workspace->offset > total) {
+        return make_status(IREE_B200_STATUS_OUT_OF_RANGE, "MXFP4 workspace offset out of range");
+      }
+      const uint64_t length =
+          workspace->length == UINT64_MAX ? total - workspace->offset : workspace->length;
+      packed = length >= sf_need && length <= total - workspace->offset &&
+               (workspace->buffer->device_ptr + workspace->offset) % 256 == 0;
+    }
+    if (packed) {
+      const uint64_t a_atoms = mxfp4_scale_atoms_bytes(M, K), b_atoms = mxfp4_scale_atoms_bytes(N, K);
+      const iree_b200_buffer_ref_t sfa{workspace->buffer, workspace->offset, a_atoms};
+      const iree_b200_buffer_ref_t sfb{workspace->buffer, workspace->offset + a_atoms, b_atoms};
+      const struct {
+        iree_b200_buffer_ref_t scales, atoms;
+        int64_t rows;
+        uint64_t bytes;
+      } sides[2] = {{lhs_scales, sfa, M, a_atoms}, {rhs_scales, sfb, N, b_atoms}};
+      for (const auto& side : sides) {
+        const uint32_t pgrid[3] = {(uint32_t)ceil_div((int64_t)(side.bytes / 4), 256), 1, 1};
+        const uint32_t pconst[2] = {(uint32_t)side.rows, (uint32_t)K};
+        const iree_b200_buffer_ref_t pbind[2] = {side.scales, side.atoms};
+        B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+            cb, ops->pending_executable, ops->mxfp4_pack_scales_export, pgrid, pconst, 2, pbind, 2, 0));
+        ops->dispatch_count.fetch_add(1);
+      }
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_execution_barrier(cb));
+      const uint32_t constants[8] = {(uint32_t)M,       (uint32_t)N,
+                                     (uint32_t)K,       kernel_flags,
+                                     (uint32_t)(K / 2), (uint32_t)(K / 128),
+                                     (uint32_t)ceil_div(M, 128), (uint32_t)ceil_div(N, 128)};
+      const iree_b200_buffer_ref_t packed_refs[5] = {lhs, sfa, rhs, sfb, out};
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+          cb, ops->pending_executable, pair ? ops->mxfp4_packed_export : ops->mxfp4_packed_1cta_export,
+          grid, constants, 8, packed_refs, 5, 0));
+      ops->dispatch_count.fetch_add(1);
+      return IREE_B200_STATUS_OK;
+    }
+    const uint32_t constants[5] = {(uint32_t)M, (uint32_t)N, (uint32_t)K, kernel_flags,
+                                   (uint32_t)(K / 2)};
     B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
-        cb, ops->pending_executable, ops->mxfp4_block_scaled_export, grid, constants, 5, refs, 5, 0));
+        cb, ops->pending_executable,
+        pair ? ops->mxfp4_block_scaled_export : ops->mxfp4_block_scaled_1cta_export, grid, constants,
+        5, refs, 5, 0));
     ops->dispatch_count.fetch_add(1);
     return IREE_B200_STATUS_OK;
   }
@@ -1042,12 +1121,13 @@ iree_b200_status_t iree_b200_ops_matmul_mxfp4_host(iree_b200_ops_t* ops, int64_t
     total += (bytes[i] + 1023) / 1024 * 1024;
   }
   // The expansion workspace is only needed when the bf16-expansion route can be taken.
-  const bool block_scaled = !(flags & IREE_B200_MATMUL_FLAG_MX_EXPAND) && K >= 256 && K % 256 == 0 &&
-                            N % 4 == 0;
+  // Workspace of the route the call will take: packed scale atoms for the block-scaled
+  // kernel, the bf16 expansion of both operands for the expansion route, none for SIMT.
+  const bool block_scaled = !(flags & IREE_B200_MATMUL_FLAG_MX_EXPAND) && mxfp4_block_scaled_shape(M, N, K);
   const uint64_t ws_offset = total,
-                 ws_bytes = ((flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC) || block_scaled)
-                                ? 0
-                                : iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
+                 ws_bytes = (flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC) ? 0
+                            : block_scaled ? iree_b200_ops_matmul_mxfp4_scale_workspace_size(M, N, K)
+                                           : iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K);
   total += ws_bytes;
   iree_b200_command_buffer_t* cb = nullptr;
   auto run = [&]() -> iree_b200_status_t {

@@ -54,8 +54,17 @@ int main() {
   // (build.py EXPERIMENTAL_UNITS; mx_kernels.cu): lhs, lhs_scales, rhs, rhs_scales, out.
   emit("iree_b200_matmul_generic_mxfp4_f32", "mx_kernels", 256, 0, 5, "1, 1, 1, 1, 0");
   // The block-scaled tcgen05 form: constants M, N, K, flags, K / 2.
-  emit("iree_b200_matmul_mxfp4_f32", "mx_kernels", MxGemmConfig::kThreads, MxGemmConfig::kSmemBytes, 5,
-       "1, 1, 1, 1, 0");
+  emit("iree_b200_matmul_mxfp4_f32", "mx_kernels", MxGemmConfig<2>::kThreads,
+       MxGemmConfig<2>::kSmemBytes, 5, "1, 1, 1, 1, 0");
+  emit("iree_b200_matmul_mxfp4_f32_1cta", "mx_kernels", MxGemmConfig<1>::kThreads,
+       MxGemmConfig<1>::kSmemBytes, 5, "1, 1, 1, 1, 0");
+  // ... with the scales already in the instruction's atom order: + K/128, ceil(M/128), ceil(N/128).
+  emit("iree_b200_matmul_mxfp4_packed_f32", "mx_kernels", MxGemmConfig<2>::kThreads,
+       MxGemmConfig<2>::kSmemBytes, 8, "1, 1, 1, 1, 0");
+  emit("iree_b200_matmul_mxfp4_packed_f32_1cta", "mx_kernels", MxGemmConfig<1>::kThreads,
+       MxGemmConfig<1>::kSmemBytes, 8, "1, 1, 1, 1, 0");
+  // row-major scales -> atoms: scales, atoms; constants rows, K.
+  emit("iree_b200_mxfp4_pack_scales", "mx_kernels", 256, 0, 2, "1, 0");
   // MXFP4 -> bf16 operand expansion: packed, scales, out; constants rows, K.
   emit("iree_b200_matmul_mxfp4_dequant_bf16", "mx_kernels", 256, 0, 2, "1, 1, 0");
   // linalg.mmt4d on data-tiled operands (mmt4d_kernels.cu): constants M1 N1 K1 M0 N0 K0 flags.

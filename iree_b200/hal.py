@@ -237,6 +237,7 @@ _OTHER_FUNCS = {
     "iree_b200_ops_builtin_executable_data": (c_void_p, [POINTER(c_size_t)]),
     "iree_b200_ops_release": (None, [c_void_p]),
     "iree_b200_ops_matmul_mxfp4_workspace_size": (c_uint64, [c_int64, c_int64, c_int64]),
+    "iree_b200_ops_matmul_mxfp4_scale_workspace_size": (c_uint64, [c_int64, c_int64, c_int64]),
     "iree_b200_ops_mmt4d_workspace_size": (c_uint64, [c_int32, c_int64, c_int64, c_int64, c_int32,
                                                       c_int32, c_int32]),
     "iree_b200_ops_executable": (c_void_p, [c_void_p]),
@@ -678,6 +679,10 @@ class Ops:
     @staticmethod
     def matmul_mxfp4_workspace_size(M, N, K) -> int:
         return lib().iree_b200_ops_matmul_mxfp4_workspace_size(M, N, K)
+
+    @staticmethod
+    def matmul_mxfp4_scale_workspace_size(M, N, K) -> int:
+        return lib().iree_b200_ops_matmul_mxfp4_scale_workspace_size(M, N, K)
 
     def record_matmul_mxfp4_tensor(self, cb: CommandBuffer, M, N, K, lhs: BufferRef,
                                    lhs_scales: BufferRef, rhs: BufferRef, rhs_scales: BufferRef,

@@ -40,15 +40,16 @@ def test_mxfp4_matmul_vs_oracle(ops, shape, accumulate):
     ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
                           rs.ctypes.data, out.ctypes.data,
                           flags=H.MATMUL_ACCUMULATE if accumulate else 0)
-    # Block-scaled kernel: one dispatch; bf16-expansion route: 3; SIMT: 1.
-    block_scaled = K >= 256 and K % 256 == 0 and N % 4 == 0
-    expected = 1 if block_scaled else (3 if ops.matmul_mxfp4_workspace_size(M, N, K) else 1)
+    # Block-scaled kernel: two scale repacks + the GEMM; bf16-expansion route: 3; SIMT: 1.
+    block_scaled = ops.matmul_mxfp4_scale_workspace_size(M, N, K) != 0
+    expected = 3 if block_scaled else (3 if ops.matmul_mxfp4_workspace_size(M, N, K) else 1)
     assert ops.dispatch_count - before == expected
     assert np.array_equal(out, oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc))
 
 
 @pytest.mark.parametrize("shape", [(128, 256, 256), (129, 256, 4), (1000, 512, 264), (300, 768, 520),
-                                   (128, 2048, 256), (257, 1024, 1028), (2048, 2048, 2048)], ids=str)
+                                   (128, 2048, 256), (257, 1024, 1028), (2048, 2048, 2048),
+                                   (4096, 4096, 1536)], ids=str)
 @pytest.mark.parametrize("accumulate", [False, True], ids=["", "acc"])
 def test_block_scaled_kernel_and_the_other_routes_agree_with_the_oracle(ops, shape, accumulate):
     """tcgen05.mma.kind::mxf4.block_scale (iree_b200_matmul_mxfp4_f32) against the oracle, bit
@@ -58,9 +59,14 @@ def test_block_scaled_kernel_and_the_other_routes_agree_with_the_oracle(ops, sha
     lhs, ls, rhs, rs, acc = _inputs(M, K, N, accumulate)
     want = oracle.matmul_mxfp4(lhs, ls, rhs, rs, acc=acc)
     base = H.MATMUL_ACCUMULATE if accumulate else 0
-    for route, flag, dispatches in (("block_scaled", 0, 1), ("expand", H.MATMUL_MX_EXPAND, None),
+    for route, flag, dispatches in (("block_scaled", 0, 3),
+                                    ("block_scaled_1cta", H.MATMUL_FORCE_1CTA, 3),
+                                    ("block_scaled_2cta", H.MATMUL_FORCE_2CTA, 3),
+                                    ("expand", H.MATMUL_MX_EXPAND, None),
                                     ("simt", H.MATMUL_FORCE_GENERIC, 1)):
         if route == "simt" and M * N * K > 1 << 28:
+            continue
+        if route == "expand" and M * N * K > 1 << 33:
             continue
         out = acc.copy() if accumulate else np.full((M, N), 77, dtype=np.float32)
         before = ops.dispatch_count
@@ -69,6 +75,39 @@ def test_block_scaled_kernel_and_the_other_routes_agree_with_the_oracle(ops, sha
         if dispatches is not None:
             assert ops.dispatch_count - before == dispatches, route
         assert np.array_equal(out, want), route
+    # The workspace-free recorded form (scales gathered inside the kernel): one dispatch.
+    for family in (0, H.MATMUL_FORCE_1CTA, H.MATMUL_FORCE_2CTA):
+        out = _recorded_without_workspace(ops, M, N, K, lhs, ls, rhs, rs, acc, base | family)
+        assert np.array_equal(out, want), ("gather", family)
+
+
+def _recorded_without_workspace(ops, M, N, K, lhs, ls, rhs, rs, acc, flags):
+    from iree_b200 import hal
+    dev = _device(ops)
+    host = [lhs, ls, rhs, rs]
+    out = acc.copy() if acc is not None else np.full((M, N), 77, dtype=np.float32)
+    bufs = [dev.allocate(max(x.nbytes, 16)) for x in host] + [dev.allocate(out.nbytes)]
+    try:
+        for b, x in zip(bufs, host):
+            dev.h2d(x.ctypes.data, b, x.nbytes)
+        dev.h2d(out.ctypes.data, bufs[4], out.nbytes)
+        before = ops.dispatch_count
+        cb = hal.CommandBuffer(dev).begin()
+        ops.record_matmul_mxfp4(cb, M, N, K, *(b.ref() for b in bufs), flags=flags)
+        cb.end()
+        assert ops.dispatch_count - before == 1
+        dev.execute(cb)
+        dev.d2h(bufs[4], out.ctypes.data, out.nbytes)
+        dev.wait_idle()
+        cb.release()
+    finally:
+        for b in bufs:
+            b.release()
+    return out
+
+
+def _device(ops):
+    return ops.device   # the session fixture's device (tests/conftest.py)
 
 
 def test_block_scaled_kernel_random_scales_and_values(ops):
@@ -99,7 +138,7 @@ def test_block_scaled_kernel_special_scales(ops):
     before = ops.dispatch_count
     ops.matmul_mxfp4_host(M, N, K, lhs.ctypes.data, ls.ctypes.data, rhs.ctypes.data,
                           rs.ctypes.data, out.ctypes.data)
-    assert ops.dispatch_count - before == 1
+    assert ops.dispatch_count - before == 3
     want = oracle.matmul_mxfp4(lhs, ls, rhs, rs)
     assert np.isnan(out[2]).all() and np.array_equal(np.isnan(out), np.isnan(want))
     ok = ~np.isnan(want)
