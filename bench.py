@@ -459,7 +459,7 @@ class TpLayerStep:
         return {"flop": self.flop, "bytes": weights + acts, "bound": "tensor",
                 "workload": f"Llama-3-8B decoder-layer GEMMs (QKV/O/gate+up/down), tokens={T}, "
                             f"bf16 -> bf16 (f32 accumulate), tensor-parallel over {w} GPU(s), "
-                            f"{self.collectives} all-reduce(sum, bf16, [{T // self.CHUNKS},{H}]) per "
+                            f"{self.collectives} all-reduce(sum, bf16, chunks of {self.CHUNKS} x [.,{H}]) per "
                             f"step via iree_hal_channel ({self.layer.collective_path()}), "
                             f"schedule {self.SCHEDULE if w > 1 else 'sequence'}: collectives on "
                             f"the collective stream beside the GEMMs that do not consume them",
@@ -609,7 +609,8 @@ def make_tp_device(torch, hal, args, world, rank, local):
                 2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
             blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
             region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
-    TpLayerStep.CHUNKS = args.tp_chunks
+    TpLayerStep.CHUNKS = ([int(r) for r in args.tp_chunk_rows.split(",")] if args.tp_chunk_rows
+                          else args.tp_chunks)
     TpLayerStep.STAGED = args.tp_schedule != "fused"
     TpLayerStep.SCHEDULE = args.tp_schedule
     return stream, dev, ops, channel, region
@@ -1003,7 +1004,7 @@ def main():
     ap.add_argument("--workload", default="matmul_bf16", choices=sorted(list(MATMUL_WORKLOADS) + list(ATTENTION_WORKLOADS) + list(MX_WORKLOADS)) + ["tp_decoder_layer"])
     ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--reserved-sms", type=int, default=16,
+    ap.add_argument("--reserved-sms", type=int, default=8,
                     help="tp_decoder_layer, N>1: SMs the GEMM grids leave to the NCCL kernels")
     ap.add_argument("--collective", default="symmetric", choices=["symmetric", "nccl"],
                     help="tp_decoder_layer, N>1: all-reduce through the symmetric-region NVLink "
@@ -1021,6 +1022,8 @@ def main():
                     help="skip the `also` (N=1) / `sharded` (N>1) lines of the default workload")
     ap.add_argument("--ar-blocks", type=int, default=0,
                     help="tp_decoder_layer: CTAs per symmetric all-reduce (0 = the reserved SMs)")
+    ap.add_argument("--tp-chunk-rows", default="",
+                    help="tp_decoder_layer: explicit token rows per chunk, e.g. 1024,3584,3584")
     ap.add_argument("--tp-chunks", type=int, default=4,
                     help="tp_decoder_layer: token chunks per row-parallel GEMM + all-reduce")
     args = ap.parse_args()

@@ -486,7 +486,7 @@ IREE_B200_API iree_b200_status_t iree_b200_channel_attach_symmetric_region(
 // time (every rank must see the same values):
 //   IREE_B200_ALL_REDUCE_TUNING="threads,unroll,pipelined"   block size (multiple of 32,
 //       <= 1024), 16-byte multimem requests in flight per thread (1 / 2 / 4 / 8) and whether
-//       the loads of step i+1 are issued before the stores of step i; default "1024,4,0".
+//       the loads of step i+1 are issued before the stores of step i; default "1024,2,1".
 //   IREE_B200_COLLECTIVE_WATCHDOG_MS=<n>   a wait on a peer (or on a producer in a fused
 //       range launch) that lasts longer makes the launch record the reason and retire (no
 //       trap: the context stays usable; the channel must then be considered failed), readable

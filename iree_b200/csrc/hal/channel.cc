@@ -385,7 +385,7 @@ iree_b200_status_t iree_b200_channel_attach_symmetric_region(
     if (clock_khz <= 0) clock_khz = 2000000;
     table[Cfg::kWatchdogOffset / 8] = (uint64_t)watchdog_ms * (uint64_t)clock_khz;
   }
-  int32_t threads = Cfg::kThreads, unroll = Cfg::kUnroll, pipelined = 0;
+  int32_t threads = Cfg::kThreads, unroll = Cfg::kUnroll, pipelined = Cfg::kPipelined;
   if (const char* tuning = getenv("IREE_B200_ALL_REDUCE_TUNING")) {
     if (sscanf(tuning, "%d,%d,%d", &threads, &unroll, &pipelined) < 1 || threads < 32 ||
         threads > Cfg::kThreads || threads % 32 ||

@@ -11,7 +11,10 @@ struct CollectiveConfig {
   static constexpr int kMaxWorld = 8;    // one NVSwitch domain of B200s
   static constexpr int kMaxBlocks = 64;  // flag words: [kMaxBlocks][kMaxWorld] u32 per rank
   static constexpr int kThreads = 1024;
-  static constexpr int kUnroll = 4;      // 16-byte multimem requests in flight per thread
+  // Defaults of IREE_B200_ALL_REDUCE_TUNING (profiles/tp_sweep_n8_r2.jsonl: with <= 24 CTAs the
+  // software-pipelined form with 2 requests per thread is the fastest or level with it).
+  static constexpr int kUnroll = 2;      // 16-byte multimem requests in flight per thread
+  static constexpr int kPipelined = 1;   // loads of step i+1 issued before the stores of step i
   static constexpr int kFlagBytes = kMaxBlocks * kMaxWorld * 4;
   static constexpr int kDefaultBlocks = 16;
   // Device table: bases[kMaxWorld], flag_blocks[kMaxWorld] (u64 each), then

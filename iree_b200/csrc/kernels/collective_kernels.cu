@@ -31,8 +31,8 @@
 //               instead of twice per launch, and there is no launch gap between ranges.
 //   ready, ready_base
 //   rank, world
-//   tuning      bits 0-7: 16-byte multimem requests in flight per thread (1, 2, 4 or 8;
-//               0 = CollectiveConfig::kUnroll); bit 8: software-pipelined (the loads of
+//   tuning      bits 0-7: 16-byte multimem requests in flight per thread (1, 2, 4 or 8);
+//               bit 8: software-pipelined (the loads of
 //               step i+1 are issued before the stores of step i, so the switch's reduce
 //               traffic and its broadcast traffic overlap on the two link directions).
 //               The block size is the launch's blockDim.x. Every rank passes the same values.
@@ -281,7 +281,7 @@ __device__ __forceinline__ void reduce_slice(const PeerTable* __restrict__ table
         case 1: reduce_slice_nvls<kType, 1, false>(base, begin, end); break;
         case 2: reduce_slice_nvls<kType, 2, false>(base, begin, end); break;
         case 8: reduce_slice_nvls<kType, 8, false>(base, begin, end); break;
-        default: reduce_slice_nvls<kType, CollectiveConfig::kUnroll, false>(base, begin, end); break;
+        default: reduce_slice_nvls<kType, 4, false>(base, begin, end); break;
       }
     }
   } else {

@@ -58,6 +58,17 @@ def decoder_layer_plan(world: int, rank: int, tokens=8192, hidden=4096, q_heads=
     ]
 
 
-def token_chunks(tokens: int, chunks: int):
-    """Row chunks of a row-parallel GEMM; chunk c's all-reduce overlaps chunk c+1's GEMM."""
-    return [contiguous_shard(tokens, chunks, c) for c in range(chunks)]
+def token_chunks(tokens: int, chunks):
+    """Row chunks of a row-parallel GEMM; chunk c's all-reduce overlaps chunk c+1's GEMM.
+    |chunks|: a count (equal chunks) or a list of row counts summing to |tokens| (a short
+    first chunk starts the link early; few, larger chunks keep the per-collective cost low)."""
+    if isinstance(chunks, int):
+        return [contiguous_shard(tokens, chunks, c) for c in range(chunks)]
+    rows = [int(r) for r in chunks]
+    if sum(rows) != tokens or any(r <= 0 for r in rows):
+        raise ValueError(f"chunk rows {rows} do not partition {tokens} tokens")
+    out, at = [], 0
+    for r in rows:
+        out.append((at, r))
+        at += r
+    return out

@@ -79,6 +79,8 @@ class DecoderLayerGemms:
         flags = hal.MATMUL_TRUNCATE_RESULT
         ar = hal.collective_op(hal.ALL_REDUCE, hal.REDUCTION_SUM, "bf16")
         rows_of = sharding.token_chunks(T, chunks)
+        chunks = len(rows_of)
+        self.chunks = chunks
         before = ops.dispatch_count
         b = self.b
         self.collectives = 0
