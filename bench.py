@@ -609,8 +609,18 @@ def make_tp_device(torch, hal, args, world, rank, local):
                 2 * TpLayerStep.TOKENS * TpLayerStep.HIDDEN * 2, torch.device("cuda", local))
             blocks = args.ar_blocks or (args.reserved_sms if args.reserved_sms > 0 else 64)
             region.attach(channel, ops.executable, max_blocks=max(1, min(64, blocks)))
-    TpLayerStep.CHUNKS = ([int(r) for r in args.tp_chunk_rows.split(",")] if args.tp_chunk_rows
-                          else args.tp_chunks)
+    if args.tp_chunk_rows:
+        TpLayerStep.CHUNKS = [int(r) for r in args.tp_chunk_rows.split(",")]
+    elif args.tp_chunks:
+        TpLayerStep.CHUNKS = args.tp_chunks
+    elif world >= 4:
+        # All-reduce-bound: a short first chunk starts the link early, two large ones keep the
+        # per-collective cost (two rank meetings + ramp, ~20 us) low
+        # (profiles/tp_chunk_experiments_n8_r2.jsonl: 0.559 ms vs 0.586 for 4 equal chunks).
+        T = TpLayerStep.TOKENS
+        TpLayerStep.CHUNKS = [T // 8, 7 * T // 16, T - T // 8 - 7 * T // 16]
+    else:
+        TpLayerStep.CHUNKS = 4
     TpLayerStep.STAGED = args.tp_schedule != "fused"
     TpLayerStep.SCHEDULE = args.tp_schedule
     return stream, dev, ops, channel, region
@@ -1024,8 +1034,8 @@ def main():
                     help="tp_decoder_layer: CTAs per symmetric all-reduce (0 = the reserved SMs)")
     ap.add_argument("--tp-chunk-rows", default="",
                     help="tp_decoder_layer: explicit token rows per chunk, e.g. 1024,3584,3584")
-    ap.add_argument("--tp-chunks", type=int, default=4,
-                    help="tp_decoder_layer: token chunks per row-parallel GEMM + all-reduce")
+    ap.add_argument("--tp-chunks", type=int, default=0,
+                    help="tp_decoder_layer: equal token chunks per row-parallel GEMM (0 = auto)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     _, world, _ = dist_env()

@@ -23,6 +23,9 @@
 
 #include <stdint.h>
 
+// The tcgen05 forms are device-only; the SIMT kernels below (and the scale repack) are also
+// compiled for the host by the mock-driver tests (tests/mock_cuda/mock_kernels_mx.cc).
+#if defined(__CUDACC__)
 #include "mx_gemm_sm100.cuh"
 
 // ---- tcgen05 block-scaled form ---------------------------------------------------------------
@@ -82,6 +85,7 @@ B200_MXFP4(iree_b200_matmul_mxfp4_f32_1cta, 1, )
 
 B200_MXFP4_PACKED(iree_b200_matmul_mxfp4_packed_f32, 2, __cluster_dims__(2, 1, 1))
 B200_MXFP4_PACKED(iree_b200_matmul_mxfp4_packed_f32_1cta, 1, )
+#endif  // __CUDACC__
 
 // iree_b200_mxfp4_pack_scales: row-major scales [rows, K / 32] -> the atoms the block-scaled
 // instruction reads: out[(rt * (K / 128) + ka) * 512 + (r % 32) * 16 + ((r % 128) / 32) * 4 + c]

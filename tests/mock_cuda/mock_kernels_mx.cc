@@ -24,3 +24,13 @@ extern "C" __attribute__((visibility("default"))) int mock_run_iree_b200_matmul_
   });
   return 0;
 }
+
+extern "C" __attribute__((visibility("default"))) int mock_run_iree_b200_mxfp4_pack_scales(
+    const unsigned grid[3], const unsigned block[3], void** p) {
+  if (block[0] != 256) return 1;
+  run_grid(grid, [&] {
+    iree_b200_mxfp4_pack_scales(arg<const uint8_t*>(p, 0), arg<uint32_t*>(p, 1), arg<int>(p, 2),
+                                arg<int>(p, 3));
+  });
+  return 0;
+}

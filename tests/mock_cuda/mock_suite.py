@@ -574,6 +574,65 @@ def test_mxfp4_tensor_route_recorded_form_and_guards(dev, dev_ops):
 
 
 @needs_kernels
+def test_mxfp4_block_scaled_route_packs_the_scales_into_atoms(dev, dev_ops):
+    """The block-scaled tcgen05 route under the mock: the two scale repack dispatches run on
+    host threads — their output must be the instruction's atom order, byte (r % 32) * 16 +
+    (r % 128 / 32) * 4 + c of atom [r / 128][kb / 4], padding rows = scale 1.0 — and the GEMM
+    dispatch reaches the driver with 8 constants, 5 bindings and 5 tensor maps (operands as
+    bytes with the 128-byte swizzle, scale atoms as 128 x 2 boxes of u32, no swizzle)."""
+    M, N, K = 300, 264, 512          # ragged row tiles on both sides
+    g = np.random.Generator(np.random.PCG64(7))
+    host = {"lhs": g.integers(0, 256, (M, K // 2), dtype=np.uint8),
+            "ls": g.integers(100, 150, (M, K // 32), dtype=np.uint8),
+            "rhs": g.integers(0, 256, (N, K // 2), dtype=np.uint8),
+            "rs": g.integers(100, 150, (N, K // 32), dtype=np.uint8)}
+    bufs = {k: dev.allocate(v.nbytes) for k, v in host.items()}
+    for k, v in host.items():
+        dev.h2d(v.ctypes.data, bufs[k], v.nbytes)
+    out = dev.allocate(M * N * 4)
+    need = dev_ops.matmul_mxfp4_scale_workspace_size(M, N, K)
+    tiles = lambda rows: -(-rows // 128)
+    assert need == (tiles(M) + tiles(N)) * (K // 128) * 512
+    assert dev_ops.matmul_mxfp4_scale_workspace_size(M, N, 384) == 0     # K % 256
+    assert dev_ops.matmul_mxfp4_scale_workspace_size(M, 266, K) == 0     # N % 4
+    ws = dev.allocate(need + 256)
+    launches(), tensor_maps()
+    cb = H.CommandBuffer(dev).begin()
+    dev_ops.record_matmul_mxfp4_tensor(cb, M, N, K, bufs["lhs"].ref(), bufs["ls"].ref(),
+                                       bufs["rhs"].ref(), bufs["rs"].ref(), ws.ref(256, need), out.ref())
+    # Without a workspace: ONE dispatch of the form that gathers the scales itself.
+    dev_ops.record_matmul_mxfp4(cb, M, N, K, bufs["lhs"].ref(), bufs["ls"].ref(), bufs["rhs"].ref(),
+                                bufs["rs"].ref(), out.ref())
+    cb.end()
+    dev.execute(cb)
+    dev.wait_idle()
+    names = [l[0] for l in launches()]
+    # (a 3 x 2-tile problem is far below one tile pair per SM: the 1-CTA family)
+    assert names == ["iree_b200_mxfp4_pack_scales"] * 2 + ["iree_b200_matmul_mxfp4_packed_f32_1cta",
+                                                            "iree_b200_matmul_mxfp4_f32_1cta"]
+    maps = tensor_maps()
+    assert len(maps) == 5 + 3
+    packed = maps[:5]
+    assert [m["type"] for m in packed] == [0, 0, 7, 2, 2]            # u8, u8, f32, u32, u32
+    assert packed[0]["dims"][:2] == [K // 2, M] and packed[1]["dims"][:2] == [K // 2, N]
+    assert packed[3]["dims"][:3] == [128, K // 128, tiles(M)] and packed[3]["box"][:3] == [128, 2, 1]
+    assert packed[4]["dims"][:3] == [128, K // 128, tiles(N)] and packed[3]["swizzle"] == 0
+    atoms = np.zeros(need, dtype=np.uint8)
+    dev.d2h(ws, atoms.ctypes.data, need, offset=256)
+    dev.wait_idle()
+
+    def want_atoms(scales, rows):
+        a = np.full((tiles(rows), K // 128, 32, 4, 4), 0x7F, dtype=np.uint8)   # [rt][ka][r%32][r%128/32][c]
+        for r in range(rows):
+            a[r // 128, :, r % 32, (r % 128) // 32, :] = scales[r].reshape(K // 128, 4)
+        return a.reshape(-1)
+
+    split = tiles(M) * (K // 128) * 512
+    assert np.array_equal(atoms[:split], want_atoms(host["ls"], M))
+    assert np.array_equal(atoms[split:], want_atoms(host["rs"], N))
+
+
+@needs_kernels
 @pytest.mark.parametrize("t,tiles", [("bf16", (16, 16, 2)), ("i8", (8, 32, 4)), ("f16", (16, 16, 16))],
                          ids=str)
 def test_mmt4d_tensor_route_relayouts(dev, dev_ops, t, tiles):
