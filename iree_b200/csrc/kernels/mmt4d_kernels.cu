@@ -43,6 +43,7 @@ constexpr int kMmt4dTileK = 16;
 __device__ __forceinline__ float mmt4d_to_acc(__nv_bfloat16 v) { return __bfloat162float(v); }
 __device__ __forceinline__ float mmt4d_to_acc(__half v) { return __half2float(v); }
 __device__ __forceinline__ int32_t mmt4d_to_acc(int8_t v) { return (int32_t)v; }
+__device__ __forceinline__ float mmt4d_to_acc(float v) { return v; }
 
 // Element (r, k) of a packed [R1, K1, R0, K0] operand.
 __device__ __forceinline__ size_t packed_at(int r, int k, int K1, int R0, int K0) {
@@ -129,6 +130,16 @@ extern "C" __global__ void __launch_bounds__(256)
   mmt4d_generic_body<__half, float>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
 }
 
+// f32f32f32 (mmt4d_tile_generic.c's most common data-tiled case): `acc += a * b` contracts to
+// an FMA here as in the reference's AVX tiles (_mm256_fmadd_ps); the generic C tile rounds the
+// product first. Identical on inputs whose products are exact; <= 1 ulp per step otherwise.
+extern "C" __global__ void __launch_bounds__(256)
+    iree_b200_mmt4d_generic_f32_f32(const float* __restrict__ lhs, const float* __restrict__ rhs,
+                                    float* __restrict__ out, int M1, int N1, int K1, int M0, int N0,
+                                    int K0, int flags) {
+  mmt4d_generic_body<float, float>(lhs, rhs, out, M1, N1, K1, M0, N0, K0, flags);
+}
+
 extern "C" __global__ void __launch_bounds__(256)
     iree_b200_mmt4d_generic_i8_i32(const int8_t* __restrict__ lhs, const int8_t* __restrict__ rhs,
                                    int32_t* __restrict__ out, int M1, int N1, int K1, int M0, int N0,
@@ -142,26 +153,67 @@ extern "C" __global__ void __launch_bounds__(256)
 //  the ops layer unpacks lhs / rhs (and the accumulator) into a workspace,
 // runs the validated NT GEMM, and packs the result back. Pure data movement, so exact.
 //   tiled [R1, C1, R0, C0]  <->  row-major [R1*R0, C1*C0]
-// One thread per element, consecutive threads along the row-major row (coalesced on that
-// side; the tiled side is coalesced within a tile row of C0 elements). HBM-bound: one read and
-// one write per element.
+// HBM-bound: one read and one write per element, BOTH sides coalesced. For a fixed r1 a run of
+// tiles [c1, c1 + t) is contiguous in the tiled buffer (t * R0 * C0 elements) and covers R0
+// row segments of t * C0 contiguous elements in the row-major buffer. A block moves one such
+// panel through shared memory: linear on the tiled side, row by row on the other (the
+// round-1 kernel moved one element per thread straight through and touched the tiled side in
+// runs of C0 elements: 1/8 sector efficiency for a 16x16x2 bf16 tile). Tiles too large for
+// the staging buffer (R0 * C0 > kPanelElems) fall back to the element-wise path.
 //
 // ABI: bindings src (read-only), dst; constants R1, C1, R0, C0, to_tiled (0: tiled ->
-// row-major, 1: row-major -> tiled). workgroup_size = [256,1,1], workgroup count =
-// [ceil(C1*C0/256), min(R1*R0, 65535), 1] (rows are strided over grid.y).
+// row-major, 1: row-major -> tiled). workgroup_size = [256,1,1]; any 1-D workgroup count
+// (work items are strided over the grid; the ops layer launches min(items, 8 per SM)).
+constexpr int kPanelBytes = 16384;
+
 template <typename T>
 __device__ __forceinline__ void mmt4d_relayout_body(const T* __restrict__ src, T* __restrict__ dst,
                                                     int R1, int C1, int R0, int C0, int to_tiled) {
-  const int rows = R1 * R0, cols = C1 * C0;
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c >= cols) return;
-  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
-    const size_t tiled = packed_at(r, c, C1, R0, C0), flat = (size_t)r * cols + c;
-    if (to_tiled) {
-      dst[tiled] = src[flat];
-    } else {
-      dst[flat] = src[tiled];
+  constexpr int kPanelElems = kPanelBytes / (int)sizeof(T);
+  __shared__ T panel[kPanelElems];
+  const int tile = R0 * C0;
+  const size_t cols = (size_t)C1 * C0;
+  if (tile > kPanelElems) {
+    // Element-wise fallback (huge tiles): consecutive threads along the row-major row.
+    const size_t total = (size_t)R1 * R0 * cols;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
+      const int r = (int)(i / cols), c = (int)(i % cols);
+      const size_t tiled = packed_at(r, c, C1, R0, C0);
+      if (to_tiled) {
+        dst[tiled] = src[i];
+      } else {
+        dst[i] = src[tiled];
+      }
     }
+    return;
+  }
+  const int tiles_per_panel = kPanelElems / tile;                     // >= 1
+  const int panels_per_row = (C1 + tiles_per_panel - 1) / tiles_per_panel;
+  const long long items = (long long)R1 * panels_per_row;
+  for (long long w = blockIdx.x; w < items; w += gridDim.x) {
+    const int r1 = (int)(w / panels_per_row);
+    const int t0 = (int)(w % panels_per_row) * tiles_per_panel;
+    const int t = tiles_per_panel < C1 - t0 ? tiles_per_panel : C1 - t0;
+    const int n = t * tile;               // elements of the panel
+    const int seg = t * C0;               // contiguous row-major elements per row
+    const size_t tiled_base = ((size_t)r1 * C1 + t0) * tile;
+    const size_t flat_base = (size_t)r1 * R0 * cols + (size_t)t0 * C0;
+    if (to_tiled) {
+      for (int j = threadIdx.x; j < n; j += 256) {
+        const int r0 = j / seg, x = j % seg;
+        panel[(x / C0) * tile + r0 * C0 + (x % C0)] = src[flat_base + (size_t)r0 * cols + x];
+      }
+      __syncthreads();
+      for (int j = threadIdx.x; j < n; j += 256) dst[tiled_base + j] = panel[j];
+    } else {
+      for (int j = threadIdx.x; j < n; j += 256) panel[j] = src[tiled_base + j];
+      __syncthreads();
+      for (int j = threadIdx.x; j < n; j += 256) {
+        const int r0 = j / seg, x = j % seg;
+        dst[flat_base + (size_t)r0 * cols + x] = panel[(x / C0) * tile + r0 * C0 + (x % C0)];
+      }
+    }
+    __syncthreads();
   }
 }
 

@@ -66,7 +66,7 @@ struct iree_b200_ops_t {
   int32_t mxfp4_block_scaled_export = -1;
   int32_t mxfp4_block_scaled_1cta_export = -1;
   int32_t mxfp4_packed_export = -1, mxfp4_packed_1cta_export = -1, mxfp4_pack_scales_export = -1;
-  int32_t mmt4d_generic_exports[3] = {-1, -1, -1};  // I8, F16, BF16
+  int32_t mmt4d_generic_exports[4] = {-1, -1, -1, -1};  // I8, F16, BF16, F32
   int32_t mmt4d_relayout_exports[3] = {-1, -1, -1};  // 1-, 2-, 4-byte elements
   std::mutex pending_mutex;
   std::atomic<uint64_t> dispatch_count{0};
@@ -845,16 +845,16 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
       ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
       &executable));
-  static const char* const kNames[13] = {
+  static const char* const kNames[14] = {
       "iree_b200_matmul_generic_mxfp4_f32", "iree_b200_matmul_mxfp4_dequant_bf16",
       "iree_b200_mmt4d_generic_i8_i32",     "iree_b200_mmt4d_generic_f16_f32",
       "iree_b200_mmt4d_generic_bf16_f32",   "iree_b200_mmt4d_relayout_b8",
       "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32",
       "iree_b200_matmul_mxfp4_f32",         "iree_b200_matmul_mxfp4_f32_1cta",
       "iree_b200_matmul_mxfp4_packed_f32",  "iree_b200_matmul_mxfp4_packed_f32_1cta",
-      "iree_b200_mxfp4_pack_scales"};
-  int32_t ordinals[13];
-  for (int i = 0; i < 13; ++i) {
+      "iree_b200_mxfp4_pack_scales",        "iree_b200_mmt4d_generic_f32_f32"};
+  int32_t ordinals[14];
+  for (int i = 0; i < 14; ++i) {
     ordinals[i] = lookup(executable, kNames[i]);
     if (ordinals[i] < 0) {
       iree_b200_executable_release(executable);
@@ -869,6 +869,7 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   ops->mxfp4_packed_export = ordinals[10];
   ops->mxfp4_packed_1cta_export = ordinals[11];
   ops->mxfp4_pack_scales_export = ordinals[12];
+  ops->mmt4d_generic_exports[3] = ordinals[13];
   for (int i = 0; i < 3; ++i) {
     ops->mmt4d_generic_exports[i] = ordinals[2 + i];
     ops->mmt4d_relayout_exports[i] = ordinals[5 + i];
@@ -1182,9 +1183,10 @@ iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int
     case IREE_B200_ELEMENT_TYPE_I8: shape->slot = 0; break;
     case IREE_B200_ELEMENT_TYPE_F16: shape->slot = 1; break;
     case IREE_B200_ELEMENT_TYPE_BF16: shape->slot = 2; break;
+    case IREE_B200_ELEMENT_TYPE_F32: shape->slot = 3; break;  // SIMT only (no exact f32 tensor-core form)
     default:
       return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
-                         "mmt4d takes i8, f16 or bf16 operands (got element type %d)", element_type);
+                         "mmt4d takes i8, f16, bf16 or f32 operands (got element type %d)", element_type);
   }
   if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
@@ -1201,7 +1203,7 @@ iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int
                        "mmt4d shape [%lld,%lld,%lld] x tiles %dx%dx%d out of range", (long long)M1,
                        (long long)N1, (long long)K1, M0, N0, K0);
   }
-  const uint64_t es = matmul_elem_size(element_type);
+  const uint64_t es = element_type == IREE_B200_ELEMENT_TYPE_F32 ? 4 : matmul_elem_size(element_type);
   shape->bytes[0] = (uint64_t)M1 * K1 * M0 * K0 * es;
   shape->bytes[1] = (uint64_t)N1 * K1 * N0 * K0 * es;
   shape->bytes[2] = (uint64_t)M1 * N1 * M0 * N0 * 4;
@@ -1219,6 +1221,7 @@ uint64_t iree_b200_ops_mmt4d_workspace_size(int32_t element_type, int64_t M1, in
                                             int32_t M0, int32_t N0, int32_t K0) {
   Mmt4dShape shape;
   if (check_mmt4d(element_type, M1, N1, K1, M0, N0, K0, 0, &shape) != IREE_B200_STATUS_OK) return 0;
+  if (element_type == IREE_B200_ELEMENT_TYPE_F32) return 0;  // SIMT only
   const int64_t M = M1 * M0, N = N1 * N0, K = K1 * K0;
   const int64_t es = (int64_t)matmul_elem_size(element_type);
   if (M < 128 || N < 128 || K < 128 || (K * es) % 16 || (N * 4) % 16) return 0;
@@ -1230,8 +1233,12 @@ static iree_b200_status_t record_mmt4d_relayout(iree_b200_ops_t* ops, iree_b200_
                                                 int32_t R0, int32_t C0, bool to_tiled,
                                                 iree_b200_buffer_ref_t src,
                                                 iree_b200_buffer_ref_t dst) {
-  const int64_t rows = R1 * R0, cols = C1 * C0;
-  const uint32_t grid[3] = {(uint32_t)ceil_div(cols, 256), (uint32_t)std::min<int64_t>(rows, 592), 1};
+  // One work item per (tile row, panel of tiles that fits the kernel's 16 KiB staging buffer),
+  // strided over a 1-D grid of at most 8 blocks per SM (mmt4d_kernels.cu).
+  const int64_t tile = (int64_t)R0 * C0, panel_elems = 16384 / (int64_t)elem_size;
+  const int64_t items = tile > panel_elems ? ceil_div(R1 * R0 * C1 * C0, 256)
+                                           : R1 * ceil_div(C1, std::max<int64_t>(1, panel_elems / tile));
+  const uint32_t grid[3] = {(uint32_t)std::max<int64_t>(1, std::min<int64_t>(items, 8 * (int64_t)ops->sm_count)), 1, 1};
   const uint32_t constants[5] = {(uint32_t)R1, (uint32_t)C1, (uint32_t)R0, (uint32_t)C0,
                                  to_tiled ? 1u : 0u};
   const iree_b200_buffer_ref_t bindings[2] = {src, dst};
@@ -1257,7 +1264,8 @@ static iree_b200_status_t record_mmt4d_impl(iree_b200_ops_t* ops, iree_b200_comm
   // K1 == 0 with ACCUMULATE leaves the result as it is (iree_uk_mmt4d_early, mmt4d.c:106-114).
   if (K1 == 0 && (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE)) return IREE_B200_STATUS_OK;
   const iree_b200_buffer_ref_t refs[3] = {lhs, rhs, out};
-  const uint64_t align[3] = {matmul_elem_size(element_type), matmul_elem_size(element_type), 4};
+  const uint64_t in_align = element_type == IREE_B200_ELEMENT_TYPE_F32 ? 4 : matmul_elem_size(element_type);
+  const uint64_t align[3] = {in_align, in_align, 4};
   for (int i = 0; i < 3; ++i) {
     if (!refs[i].buffer) {  // K1 == 0: the operand bindings are empty and may be NULL
       if (shape.bytes[i]) return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "mmt4d binding %d is NULL", i);

@@ -71,6 +71,7 @@ int main() {
   emit("iree_b200_mmt4d_generic_bf16_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_f16_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_i8_i32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
+  emit("iree_b200_mmt4d_generic_f32_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   // tiled <-> row-major relayout: src, dst; constants R1 C1 R0 C0 to_tiled.
   emit("iree_b200_mmt4d_relayout_b8", "mmt4d_kernels", 256, 0, 5, "1, 0");
   emit("iree_b200_mmt4d_relayout_b16", "mmt4d_kernels", 256, 0, 5, "1, 0");

@@ -444,13 +444,15 @@ ORACLE_API void oracle_matmul_mxfp4_f32(int64_t M, int64_t N, int64_t K, int64_t
 // :94-108 bf16, :157-169 s8; the tile loops around them :249-367):
 //   lhs [M1,K1,M0,K0], rhs [N1,K1,N0,K0], out [M1,N1,M0,N0];
 //   acc = accumulate ? out : 0;  for k1, for k0: acc += lhs[m1,k1,m0,k0] * rhs[n1,k1,n0,k0]
-// |type| uses this file's ids (I8 -> i32 result, F16 / BF16 -> f32 result). |acc| NULL = zero
+// |type| uses this file's ids (I8 -> i32 result, F16 / BF16 / F32 -> f32 result; f32 as
+// mmt4d_tile_generic.c's f32f32f32 loop states it: acc += lhs * rhs, one product and one add
+// per step). |acc| NULL = zero
 // init. Mirrors iree_uk_mmt4d_early (mmt4d.c:106-114): nothing is read or written for an
 // empty result; with K1*K0 == 0 the result is acc (or zeros).
 ORACLE_API int oracle_mmt4d(int type, int64_t M1, int64_t N1, int64_t K1, int64_t M0, int64_t N0,
                             int64_t K0, const void* lhs, const void* rhs, const void* acc,
                             void* out) {
-  if (type != ORACLE_I8 && type != ORACLE_F16 && type != ORACLE_BF16) return -1;
+  if (type != ORACLE_I8 && type != ORACLE_F16 && type != ORACLE_BF16 && type != ORACLE_F32) return -1;
 #pragma omp parallel for collapse(2) schedule(static)
   for (int64_t m1 = 0; m1 < M1; ++m1) {
     for (int64_t n1 = 0; n1 < N1; ++n1) {
@@ -469,6 +471,15 @@ ORACLE_API int oracle_mmt4d(int type, int64_t M1, int64_t N1, int64_t K1, int64_
               }
             }
             ((int32_t*)out)[o] = (int32_t)a;
+          } else if (type == ORACLE_F32) {
+            float a = acc ? ((const float*)acc)[o] : 0.0f;
+            for (int64_t k1 = 0; k1 < K1; ++k1) {
+              for (int64_t k0 = 0; k0 < K0; ++k0) {
+                a += ((const float*)lhs)[l + k1 * M0 * K0 + k0] *
+                     ((const float*)rhs)[r + k1 * N0 * K0 + k0];
+              }
+            }
+            ((float*)out)[o] = a;
           } else {
             float a = acc ? ((const float*)acc)[o] : 0.0f;
             for (int64_t k1 = 0; k1 < K1; ++k1) {

@@ -175,6 +175,7 @@ ORACLE_REF_API int oracle_ref_mmt4d(int type, int64_t M1, int64_t N1, int64_t K1
     case 0: mm = IREE_UK_FLAG_MMT4D_TYPE_S8S8S32; break;
     case 1: mm = IREE_UK_FLAG_MMT4D_TYPE_F16F16F32; break;
     case 2: mm = IREE_UK_FLAG_MMT4D_TYPE_BF16BF16F32; break;
+    case 3: mm = IREE_UK_FLAG_MMT4D_TYPE_F32F32F32; break;
     default: return -1;
   }
   if (M1 < 0 || N1 < 0 || K1 < 0 || M0 <= 0 || N0 <= 0 || K0 <= 0) return -1;

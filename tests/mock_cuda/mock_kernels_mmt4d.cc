@@ -17,6 +17,7 @@
 MOCK_RUN_MMT4D(iree_b200_mmt4d_generic_bf16_f32, __nv_bfloat16, float)
 MOCK_RUN_MMT4D(iree_b200_mmt4d_generic_f16_f32, __half, float)
 MOCK_RUN_MMT4D(iree_b200_mmt4d_generic_i8_i32, int8_t, int32_t)
+MOCK_RUN_MMT4D(iree_b200_mmt4d_generic_f32_f32, float, float)
 
 #define MOCK_RUN_RELAYOUT(NAME, T)                                                              \
   extern "C" __attribute__((visibility("default"))) int mock_run_##NAME(                         \

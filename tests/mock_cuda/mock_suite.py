@@ -422,7 +422,7 @@ def test_pipelined_host_call_end_to_end_on_the_host(dev, dev_ops, t, case):
 
 
 @needs_kernels
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16", "f32"])
 @pytest.mark.parametrize("case", [
     # M, K, N (logical, before packing), M0, N0, K0, accumulate
     (37, 50, 29, 16, 16, 2, False),      # the AVX-512-BF16 / VNNI tile shape
@@ -457,7 +457,9 @@ def test_mmt4d_end_to_end_on_the_host(dev, dev_ops, t, case):
     if oracle.ref_available():
         assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
     if not accumulate:
-        assert np.array_equal(oracle.unpack(out, M, N), oracle.matmul(t, lhs[None], rhs[None])[0])
+        want_mm = (lhs.astype(np.float64) @ rhs.astype(np.float64)).astype(np.float32) if t == "f32" \
+            else oracle.matmul(t, lhs[None], rhs[None])[0]
+        assert np.array_equal(oracle.unpack(out, M, N), want_mm)
 
 
 @needs_kernels
@@ -475,7 +477,7 @@ def test_mmt4d_edge_cases_and_guards(dev, dev_ops):
     dev_ops.mmt4d_host(t, 2, 1, 0, M0, N0, K0, 0, 0, out.ctypes.data, flags=H.MATMUL_ACCUMULATE)
     dev_ops.mmt4d_host(t, 0, 1, 4, M0, N0, K0, 0, r4.ctypes.data, 0)      # empty result
     assert launches() == [] and (out == 5).all()
-    for bad in (dict(M0=0), dict(K0=40000), dict(flags=H.MATMUL_TRANSPOSE_RHS), dict(t="f32"),
+    for bad in (dict(M0=0), dict(K0=40000), dict(flags=H.MATMUL_TRANSPOSE_RHS), dict(t="f8e4m3fn"),
                 dict(M1=-1)):
         a = dict(t=t, M1=2, N1=1, K1=4, M0=M0, N0=N0, K0=K0, flags=0)
         a.update(bad)

@@ -5,6 +5,8 @@ reference's tests/e2e/collectives/collectives_test.py:46-93.
 * tools/symmetric_check.py — all_reduce(sum) through iree_b200_command_buffer_collective on
   our NVLink kernels (NVLS + peer load/store), f16/bf16/f32, ragged sizes, sub-ranges,
   back-to-back launches, fused ranges, NCCL fallback: exact sums.
+* tools/collectives_check.py — every collective kind through NCCL on real ranks, stream and
+  graph-captured, exact.
 * tools/tp_layer_check.py — the tensor-parallel decoder-layer GEMMs against the oracle's
   unsharded layer, bit for bit, through NCCL (stream / overlapped / graph-captured) and
   through the symmetric kernels (staged / fused / graph kernel nodes).
@@ -45,6 +47,19 @@ def test_symmetric_all_reduce_ranks(world):
     assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
     assert lines and lines[-1]["world"] == world and lines[-1]["failures"] == []
     assert lines[-1]["failing_ranks_total"] == 0
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_every_collective_kind_on_real_ranks(world):
+    """tools/collectives_check.py: all_reduce (sum / max), all_gather, reduce_scatter, broadcast,
+    reduce, all_to_all, send_recv, send / recv through iree_b200_command_buffer_collective, f32 /
+    bf16 / i32, in stream mode and captured into a CUgraph (collectives_test.py:46-93)."""
+    if device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    r, lines = torchrun(world, "tools/collectives_check.py", port=29580 + world)
+    assert r.returncode == 0, (r.stdout[-1500:], r.stderr[-1500:])
+    assert lines and lines[-1]["world"] == world and lines[-1]["failures"] == []
+    assert lines[-1]["cases"] >= 2 * (3 * 7 + 1)
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])

@@ -369,7 +369,7 @@ def test_mmt4d_is_the_matmul_of_the_unpacked_operands(t, case):
 
 
 @_needs_ref
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16", "f32"])
 @pytest.mark.parametrize("generic", [False, True], ids=["arch", "generic"])
 @pytest.mark.parametrize("case", MMT4D_CASES, ids=str)
 def test_mmt4d_matches_the_reference_microkernel(t, generic, case):

@@ -15,7 +15,7 @@ from iree_b200 import hal as H
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16", "f32"])
 @pytest.mark.parametrize("case", [
     (37, 50, 29, 16, 16, 2, False), (70, 33, 130, 8, 8, 1, True), (64, 64, 64, 16, 16, 16, False),
     (100, 40, 33, 8, 32, 4, True), (33, 17, 40, 1, 1, 1, False), (20, 24, 90, 7, 5, 3, True),
@@ -43,7 +43,9 @@ def test_mmt4d_vs_oracle(ops, t, case):
     if oracle.ref_available():
         assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
     if not accumulate:
-        assert np.array_equal(oracle.unpack(out, M, N), oracle.matmul(t, lhs[None], rhs[None])[0])
+        want_mm = (lhs.astype(np.float64) @ rhs.astype(np.float64)).astype(np.float32) if t == "f32" \
+            else oracle.matmul(t, lhs[None], rhs[None])[0]
+        assert np.array_equal(oracle.unpack(out, M, N), want_mm)
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16", "i8"])
@@ -92,4 +94,4 @@ def test_mmt4d_edge_cases(ops):
     with pytest.raises(H.Status):
         ops.mmt4d_host(t, 2, 1, 4, 0, N0, K0, 1, 1, out.ctypes.data)
     with pytest.raises(H.Status):
-        ops.mmt4d_host("f32", 2, 1, 4, M0, N0, K0, 1, 1, out.ctypes.data)
+        ops.mmt4d_host("f8e4m3fn", 2, 1, 4, M0, N0, K0, 1, 1, out.ctypes.data)
