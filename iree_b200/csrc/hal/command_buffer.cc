@@ -863,6 +863,35 @@ iree_b200_status_t build_graph(iree_b200_command_buffer_t* cb) {
 
 }  // namespace
 
+namespace b200hal {
+
+void reap_in_flight(iree_b200_device_t* device, bool everything) {
+  std::vector<iree_b200_device_t::InFlight> done;
+  {
+    std::lock_guard<std::mutex> lock(device->mutex);
+    auto& list = device->in_flight;
+    size_t kept = 0;
+    for (size_t i = 0; i < list.size(); ++i) {
+      // Submission order: once one is still running, so are the later ones.
+      const bool finished =
+          everything || (kept == 0 && device->cu->cuEventQuery(list[i].done) == CUDA_SUCCESS);
+      if (finished) {
+        done.push_back(list[i]);
+      } else {
+        list[kept++] = list[i];
+      }
+    }
+    list.resize(kept);
+  }
+  // Outside the lock: releasing a command buffer may release the device.
+  for (auto& e : done) {
+    device->cu->cuEventDestroy(e.done);
+    iree_b200_command_buffer_release(e.command_buffer);
+  }
+}
+
+}  // namespace b200hal
+
 extern "C" {
 
 iree_b200_status_t iree_b200_command_buffer_create(iree_b200_device_t* device,
@@ -1141,15 +1170,33 @@ iree_b200_status_t iree_b200_device_queue_execute(
                        "command buffer has not been ended (state is not executable)");
   }
   const CudaSymbols* cu = device->cu;
+  b200hal::reap_in_flight(device, /*everything=*/false);
   std::lock_guard<std::mutex> lock(device->mutex);
   B200_CU(cu, cuCtxSetCurrent(device->cu_context));
+
+  // An operation that cannot be queued fails its signal semaphores, so that waiters
+  // downstream see the failure instead of hanging (cuda_device.c:1187-1191).
+  auto fail_signals = [&](iree_b200_status_t code, const std::string& message) {
+    for (size_t i = 0; i < signal_count; ++i) {
+      iree_b200_semaphore_t* s = signal_semaphores[i];
+      std::lock_guard<std::mutex> sem_lock(s->mutex);
+      if (s->failure == IREE_B200_STATUS_OK) {
+        s->failure = code;
+        s->failure_message = message;
+      }
+    }
+  };
 
   // Device-side waits (cuda_device.c:148-158,229-240).
   for (size_t i = 0; i < wait_count; ++i) {
     iree_b200_semaphore_t* s = wait_semaphores[i];
-    std::lock_guard<std::mutex> sem_lock(s->mutex);
+    std::unique_lock<std::mutex> sem_lock(s->mutex);
     if (s->failure != IREE_B200_STATUS_OK) {
-      return make_status(s->failure, "wait semaphore has failed: %s", s->failure_message.c_str());
+      const iree_b200_status_t code = s->failure;
+      const std::string message = "wait semaphore has failed: " + s->failure_message;
+      sem_lock.unlock();
+      fail_signals(code, message);
+      return make_status(code, "%s", message.c_str());
     }
     if (s->host_value >= wait_values[i]) continue;
     CUevent event = nullptr;
@@ -1160,9 +1207,15 @@ iree_b200_status_t iree_b200_device_queue_execute(
       }
     }
     if (!event) {
-      return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,
-                         "wait on semaphore value %llu that no queued operation signals",
-                         (unsigned long long)wait_values[i]);
+      // No deferred work queue here (the reference's supports wait-before-signal,
+      // hal/utils/deferred_work_queue.c): submissions must be queued in dependency order.
+      char message[128];
+      snprintf(message, sizeof(message),
+               "wait on semaphore value %llu that no queued operation signals",
+               (unsigned long long)wait_values[i]);
+      sem_lock.unlock();
+      fail_signals(IREE_B200_STATUS_FAILED_PRECONDITION, message);
+      return make_status(IREE_B200_STATUS_FAILED_PRECONDITION, "%s", message);
     }
     B200_CU(cu, cuStreamWaitEvent(device->dispatch_stream, event, 0));
   }
@@ -1179,6 +1232,19 @@ iree_b200_status_t iree_b200_device_queue_execute(
     }
   }
   std::string message = status != IREE_B200_STATUS_OK ? iree_b200_status_message() : "";
+  if (command_buffer && status == IREE_B200_STATUS_OK) {
+    // Keep the command buffer (and through it its buffers, executables, captured update
+    // bytes and graph) alive until the GPU is done with this submission.
+    CUevent done = nullptr;
+    if (cu->cuEventCreate(&done, CU_EVENT_DISABLE_TIMING) == CUDA_SUCCESS) {
+      if (cu->cuEventRecord(done, device->dispatch_stream) == CUDA_SUCCESS) {
+        iree_b200_command_buffer_retain(command_buffer);
+        device->in_flight.push_back({command_buffer, done});
+      } else {
+        cu->cuEventDestroy(done);
+      }
+    }
+  }
 
   for (size_t i = 0; i < signal_count; ++i) {
     iree_b200_semaphore_t* s = signal_semaphores[i];

@@ -318,6 +318,7 @@ iree_b200_status_t iree_b200_device_wait_idle(iree_b200_device_t* device) {
   B200_CU(cu, cuCtxSetCurrent(device->cu_context));
   B200_CU(cu, cuStreamSynchronize(device->dispatch_stream));
   if (device->collective_stream) B200_CU(cu, cuStreamSynchronize(device->collective_stream));
+  b200hal::reap_in_flight(device, /*everything=*/true);
   return IREE_B200_STATUS_OK;
 }
 
@@ -539,6 +540,7 @@ iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore, ui
   const auto deadline = std::chrono::steady_clock::now() + std::chrono::nanoseconds(timeout_ns);
   for (;;) {
     CUevent event = nullptr;
+    bool reached = false;
     {
       std::lock_guard<std::mutex> lock(semaphore->mutex);
       cu->cuCtxSetCurrent(semaphore->device->cu_context);
@@ -546,8 +548,9 @@ iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore, ui
       if (semaphore->failure != IREE_B200_STATUS_OK) {
         return make_status(semaphore->failure, "%s", semaphore->failure_message.c_str());
       }
-      if (semaphore->host_value >= value) return IREE_B200_STATUS_OK;
+      reached = semaphore->host_value >= value;
       for (auto& tp : semaphore->timepoints) {
+        if (reached) break;
         if (tp.value >= value) {
           event = tp.event;
           break;
@@ -564,6 +567,12 @@ iree_b200_status_t iree_b200_semaphore_wait(iree_b200_semaphore_t* semaphore, ui
         }
         continue;
       }
+    }
+    if (reached) {
+      // Outside the semaphore's mutex (queue_execute takes device then semaphore): command
+      // buffers whose submissions have completed are released here too.
+      b200hal::reap_in_flight(semaphore->device, /*everything=*/false);
+      return IREE_B200_STATUS_OK;
     }
     if (!event && timeout_ns < 0) {
       return make_status(IREE_B200_STATUS_FAILED_PRECONDITION,

@@ -190,7 +190,22 @@ struct iree_b200_device_t : b200hal::RefCounted {
   int32_t max_block_dims[3] = {0, 0, 0};
   int32_t max_threads_per_block = 0;
   std::mutex mutex;  // guards stream submission order
+  // Command buffers the GPU may still be executing: retained by queue_execute until the
+  // event recorded behind them has fired (the reference keeps them until the signal
+  // timepoint, cuda_device.c:1168-1196). Guarded by |mutex|; reaped by queue_execute,
+  // wait_idle and host semaphore waits.
+  struct InFlight {
+    iree_b200_command_buffer_t* command_buffer;
+    CUevent done;
+  };
+  std::vector<InFlight> in_flight;
 };
+
+namespace b200hal {
+// Releases the in-flight command buffers whose work has completed (all of them when
+// |everything|: the caller has just synchronised the streams). Takes the device mutex.
+void reap_in_flight(iree_b200_device_t* device, bool everything);
+}  // namespace b200hal
 
 struct iree_b200_buffer_t : b200hal::RefCounted {
   iree_b200_device_t* device = nullptr;

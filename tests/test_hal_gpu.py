@@ -375,6 +375,47 @@ def test_command_buffer_keeps_its_resources_alive(dev):
     assert np.array_equal(_download(dev, sink, np.uint8, 4096), np.arange(4096, dtype=np.uint8) % 251)
 
 
+def test_queue_execute_retains_the_command_buffer_until_the_gpu_is_done(dev):
+    """The reference keeps a submitted command buffer alive until its signal timepoint
+    (cuda_device.c:1168-1196). Here: queue_execute retains it behind an event; the caller may
+    release it right after submitting — also in GRAPH mode, where an update_buffer node reads
+    the command buffer's captured bytes when the graph runs."""
+    n = 1 << 20
+    payload = (np.arange(n, dtype=np.uint32) * 2654435761 & 0xFF).astype(np.uint8)
+    sink, mid = dev.allocate(n), dev.allocate(n)
+    sem = H.Semaphore(dev, 0)
+    for round_ in range(3):
+        cb = H.CommandBuffer(dev).begin()
+        cb.update(bytes(payload ^ round_), mid.ref())
+        cb.barrier()
+        cb.copy(mid.ref(), sink.ref())
+        cb.end()
+        dev.execute(cb, signals=[(sem, round_ + 1)])
+        cb.release()                                 # the queue holds the only reference now
+        del cb
+    sem.wait(3)
+    assert np.array_equal(_download(dev, sink, np.uint8, n), payload ^ 2)
+    dev.wait_idle()
+
+
+def test_a_submission_that_cannot_be_queued_fails_its_signal_semaphores(dev):
+    """A wait on a failed semaphore, or on a value nothing queued will ever signal (no
+    wait-before-signal here), is refused AND poisons the signal list, so downstream waiters
+    see the failure instead of hanging (cuda_device.c:1187-1191)."""
+    bad, never, out1, out2 = (H.Semaphore(dev, 0) for _ in range(4))
+    bad.fail(10, "upstream died")                    # ABORTED
+    with pytest.raises(H.Status):
+        dev.execute(None, waits=[(bad, 1)], signals=[(out1, 1)])
+    with pytest.raises(H.Status):
+        out1.wait(1, timeout_ns=1_000_000)
+    with pytest.raises(H.Status) as e:
+        dev.execute(None, waits=[(never, 7)], signals=[(out2, 1)])
+    assert e.value.name == "FAILED_PRECONDITION"
+    with pytest.raises(H.Status) as e:
+        out2.query()
+    assert e.value.name == "FAILED_PRECONDITION"
+
+
 # ---- core/executable_cache_test.cc, executable_test.cc -----------------------------------
 
 def test_executable_cache(dev, dev_ops):
