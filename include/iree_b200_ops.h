@@ -63,6 +63,9 @@ enum {
   IREE_B200_MATMUL_FLAG_FORCE_2CTA = 1u << 10,
   // MXFP4 only: take the expand-to-bf16 + bf16 GEMM route instead of the block-scaled kernel.
   IREE_B200_MATMUL_FLAG_MX_EXPAND = 1u << 11,
+  // mmt4d only: take the relayout + row-major GEMM route (needs the workspace) even where the
+  // tile-direct tcgen05 export applies (comparison runs, tools/mmt4d_bench.py).
+  IREE_B200_MATMUL_FLAG_MMT4D_RELAYOUT = 1u << 12,
 };
 
 // The builtin executable ("CDA1" blob linked into this library: one cubin per kernel

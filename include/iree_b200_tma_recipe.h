@@ -46,17 +46,26 @@ enum {
 #define IREE_B200_TMA_DIM_CONST(i) (0x80000000u | (uint32_t)(i))
 #define IREE_B200_TMA_DIM_LITERAL(v) ((uint32_t)(v))
 
+// Dense position of map dimension d (0 = innermost), 4 bits per dimension.
+#define IREE_B200_TMA_ORDER(o0, o1, o2, o3) \
+  ((uint32_t)(o0) | ((uint32_t)(o1) << 4) | ((uint32_t)(o2) << 8) | ((uint32_t)(o3) << 12))
+
 typedef struct iree_b200_tma_map_t {
   uint32_t binding;    // index of the binding whose device pointer is the base
   uint32_t elem_type;  // IREE_B200_TMA_*
   uint32_t elem_size;  // bytes
   uint32_t rank;       // 1..4
-  // Extents, innermost (contiguous) first. The tensor is dense row-major, so
-  // stride[d] = elem_size * prod(dim[0..d)).
+  // Extents of the MAP's dimensions (a literal or "push constant #i"). The tensor is dense;
+  // with |order| == 0 its layout is the map's own dimension order, innermost first:
+  // stride[d] = elem_size * prod(dim[0..d)). A non-zero |order| (IREE_B200_TMA_ORDER) gives,
+  // per map dimension, its position in the dense layout, so a map can walk a tiled tensor in
+  // another order than it is stored: stride[d] = elem_size * prod(dim[e] : order[e] < order[d]).
+  // Dimension 0 must be the dense-innermost one (order[0] == 0).
   uint32_t dim[IREE_B200_TMA_MAX_RANK];
-  uint32_t box[IREE_B200_TMA_MAX_RANK];  // tile extents, innermost first
-  uint32_t swizzle;                      // IREE_B200_TMA_SWIZZLE_*
-  uint32_t reserved;
+  // Tile extents per map dimension (a literal or "push constant #i").
+  uint32_t box[IREE_B200_TMA_MAX_RANK];
+  uint32_t swizzle;                      // IREE_B200_TMA_SWIZZLE_* (a literal or "push constant #i")
+  uint32_t order;                        // 0 = identity
 } iree_b200_tma_map_t;
 
 typedef struct iree_b200_tma_recipe_t {

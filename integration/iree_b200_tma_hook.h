@@ -77,29 +77,51 @@ static inline CUresult iree_b200_tma_hook_encode(iree_b200_pfn_cuTensorMapEncode
   cuuint64_t strides[IREE_B200_TMA_MAX_RANK];
   cuuint32_t box[IREE_B200_TMA_MAX_RANK];
   cuuint32_t elem_strides[IREE_B200_TMA_MAX_RANK];
-  uint64_t stride = map->elem_size;
+  uint32_t order[IREE_B200_TMA_MAX_RANK];
   for (uint32_t d = 0; d < map->rank; ++d) {
-    uint64_t extent = map->dim[d];
+    // Extents and box sizes are literals or "push constant #i".
+    uint64_t extent = map->dim[d], tile = map->box[d];
     if (extent & 0x80000000u) {
       const uint32_t index = (uint32_t)(extent & 0x7fffffffu);
       if (index >= constant_count) return CUDA_ERROR_INVALID_VALUE;
       extent = constants[index];
     }
-    if (extent == 0) return CUDA_ERROR_INVALID_VALUE;
-    dims[d] = extent;
-    if (d > 0) {
-      if (stride % 16 != 0) return CUDA_ERROR_INVALID_VALUE;
-      strides[d - 1] = stride;  // globalStrides[j] = byte stride of dim j + 1
+    if (tile & 0x80000000u) {
+      const uint32_t index = (uint32_t)(tile & 0x7fffffffu);
+      if (index >= constant_count) return CUDA_ERROR_INVALID_VALUE;
+      tile = constants[index];
     }
-    stride *= extent;
-    box[d] = map->box[d];
+    if (extent == 0 || tile == 0 || tile > 256) return CUDA_ERROR_INVALID_VALUE;
+    dims[d] = extent;
+    box[d] = (cuuint32_t)tile;
     elem_strides[d] = 1;
+    order[d] = map->order ? (map->order >> (4 * d)) & 0xfu : d;
+  }
+  if (order[0] != 0) return CUDA_ERROR_INVALID_VALUE;
+  for (uint32_t d = 1; d < map->rank; ++d) {
+    // Dense tensor walked in the map's dimension order: the stride of a dimension is the
+    // product of the extents stored inside it.
+    uint64_t stride = map->elem_size;
+    for (uint32_t e = 0; e < map->rank; ++e) {
+      if (order[e] < order[d]) stride *= dims[e];
+    }
+    if (stride % 16 != 0) return CUDA_ERROR_INVALID_VALUE;
+    strides[d - 1] = stride;  // globalStrides[j] = byte stride of dim j + 1
   }
   const CUdeviceptr base = binding_ptrs[map->binding];
   if (base % 16 != 0) return CUDA_ERROR_INVALID_VALUE;
+  uint32_t swizzle = map->swizzle;
+  if (swizzle & 0x80000000u) {
+    const uint32_t index = swizzle & 0x7fffffffu;
+    if (index >= constant_count) return CUDA_ERROR_INVALID_VALUE;
+    swizzle = constants[index];
+  }
+  if (swizzle > IREE_B200_TMA_SWIZZLE_128B) return CUDA_ERROR_INVALID_VALUE;
+  // The hardware faults on a swizzled box whose inner row is narrower than the swizzle span.
+  if (swizzle && box[0] * map->elem_size < (16u << swizzle)) return CUDA_ERROR_INVALID_VALUE;
   return encode_tiled(out_map, (CUtensorMapDataType)map->elem_type, map->rank, (void*)base, dims,
                       strides, box, elem_strides, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                      (CUtensorMapSwizzle)map->swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      (CUtensorMapSwizzle)swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
 }
 

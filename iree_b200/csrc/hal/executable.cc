@@ -272,29 +272,45 @@ iree_b200_status_t encode_tensor_map(const CudaSymbols* cu, const iree_b200_tma_
                        map.rank);
   }
   cuuint64_t dims[IREE_B200_TMA_MAX_RANK];
-  cuuint64_t strides[IREE_B200_TMA_MAX_RANK];
+  cuuint64_t strides[IREE_B200_TMA_MAX_RANK];       // globalStrides[i] = stride of dim i + 1
   cuuint32_t box[IREE_B200_TMA_MAX_RANK];
   cuuint32_t elem_strides[IREE_B200_TMA_MAX_RANK];
-  uint64_t stride = map.elem_size;
-  for (uint32_t d = 0; d < map.rank; ++d) {
-    uint64_t extent = map.dim[d];
-    if (extent & 0x80000000u) {
-      const uint32_t index = (uint32_t)(extent & 0x7fffffffu);
-      if (index >= constant_count) {
-        return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
-                           "TMA recipe refers to push constant %u but only %zu were provided", index,
-                           constant_count);
-      }
-      extent = constants[index];
+  auto resolve = [&](uint32_t v, uint64_t* out) -> bool {
+    if (v & 0x80000000u) {
+      const uint32_t index = v & 0x7fffffffu;
+      if (index >= constant_count) return false;
+      v = constants[index];
     }
-    if (extent == 0) {
-      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "TMA tensor extent %u is zero", d);
+    *out = v;
+    return true;
+  };
+  uint32_t order[IREE_B200_TMA_MAX_RANK];
+  for (uint32_t d = 0; d < map.rank; ++d) {
+    order[d] = map.order ? (map.order >> (4 * d)) & 0xfu : d;
+    uint64_t extent = 0, tile = 0;
+    if (!resolve(map.dim[d], &extent) || !resolve(map.box[d], &tile)) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "TMA recipe refers to a push constant beyond the %zu provided",
+                         constant_count);
+    }
+    if (extent == 0 || tile == 0 || tile > 256) {
+      return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                         "TMA tensor extent / box of dim %u is zero or too large", d);
     }
     dims[d] = extent;
-    if (d > 0) strides[d - 1] = stride;  // globalStrides[i] = byte stride of dim i+1
-    stride *= extent;
-    box[d] = map.box[d];
+    box[d] = (cuuint32_t)tile;
     elem_strides[d] = 1;
+  }
+  if (order[0] != 0) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "TMA recipe: map dimension 0 must be the dense-innermost one");
+  }
+  for (uint32_t d = 0; d < map.rank; ++d) {
+    uint64_t stride = map.elem_size;
+    for (uint32_t e = 0; e < map.rank; ++e) {
+      if (order[e] < order[d]) stride *= dims[e];
+    }
+    if (d > 0) strides[d - 1] = stride;
   }
   if (base_pointer % 16 != 0) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
@@ -308,10 +324,21 @@ iree_b200_status_t encode_tensor_map(const CudaSymbols* cu, const iree_b200_tma_
                          map.binding, (unsigned long long)strides[d], d + 1);
     }
   }
+  uint64_t swizzle = 0;
+  if (!resolve(map.swizzle, &swizzle) || swizzle > IREE_B200_TMA_SWIZZLE_128B) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT, "TMA recipe: bad swizzle mode");
+  }
+  // Measured on the B200 (tools/tma4d_probe.cu): a swizzled box whose inner row is narrower
+  // than the swizzle span faults with an illegal address; refuse it here instead.
+  if (swizzle && (uint64_t)box[0] * map.elem_size < (16ull << swizzle)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "TMA recipe: inner box of %llu bytes is narrower than the %llu-byte swizzle",
+                       (unsigned long long)box[0] * map.elem_size, 16ull << swizzle);
+  }
   B200_CU(cu, cuTensorMapEncodeTiled(
                   out_map, (CUtensorMapDataType)map.elem_type, map.rank,
                   reinterpret_cast<void*>(base_pointer), dims, strides, box, elem_strides,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)map.swizzle,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, (CUtensorMapSwizzle)swizzle,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE));
   return IREE_B200_STATUS_OK;
 }

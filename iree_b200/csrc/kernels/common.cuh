@@ -181,6 +181,34 @@ B200_DEVICE void tma_load_3d(uint32_t dst_smem, const TensorMap* map, uint32_t b
   }
 }
 
+// 4-D form of tma_load_3d (tiled operands: linalg.mmt4d).
+template <int kCtaGroup>
+B200_DEVICE void tma_load_4d(uint32_t dst_smem, const TensorMap* map, uint32_t bar, int c0, int c1,
+                             int c2, int c3) {
+  if constexpr (kCtaGroup == 1) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst_smem),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst_smem),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+  }
+}
+
+B200_DEVICE void tma_store_4d(const TensorMap* map, uint32_t src_smem, int c0, int c1, int c2,
+                              int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(map)),
+      "r"(src_smem), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 // 1-D bulk copy global -> this CTA's shared memory (no tensor map: plain pointers, so the
 // kernel stays launchable through the unmodified custom-dispatch ABI). |bytes| and both
 // addresses are multiples of 16; completes |bytes| on |bar|.
@@ -448,6 +476,19 @@ B200_DEVICE uint64_t make_smem_desc_sw128(uint32_t smem_addr, uint32_t lbo_bytes
   d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= 1ull << 46;
   d |= 2ull << 61;
+  return d;
+}
+
+// Unswizzled K-major operand: core matrices of 8 rows x 16 bytes stored contiguously
+// (128 bytes); |lbo_bytes| between core matrices adjacent in K, |sbo_bytes| between 8-row
+// groups (layout type 0).
+B200_DEVICE uint64_t make_smem_desc_interleaved(uint32_t smem_addr, uint32_t lbo_bytes,
+                                                uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
   return d;
 }
 

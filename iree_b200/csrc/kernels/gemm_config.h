@@ -38,11 +38,15 @@ B200_HOST_DEVICE constexpr uint32_t make_idesc(uint32_t c_fmt, uint32_t a_fmt, u
 // `linalg.matmul + arith.truncf` dispatch), halving the C traffic.
 // kBias: the dispatch also holds the consumer elementwise op `act(x + bias[n])` (a bias
 // binding between rhs and out; see gemm_bias_kernels.cu).
+// kTiled: linalg.mmt4d — operands and result are data-tiled ([R1, K1, R0, K0] with K0 * size =
+// 16 bytes; result [M1, N1, M0, N0]) and reach the same shared-memory tiles through rank-4
+// tensor maps that walk the tiled tensor in (k0, k1, r0, r1) order (gemm_sm100.cuh).
 template <int kCtaGroup_, int kKind_, uint32_t kAbFmt_, bool kBMajorK_, int kStages_,
-          bool kOut16_ = false, bool kBias_ = false>
+          bool kOut16_ = false, bool kBias_ = false, bool kTiled_ = false>
 struct GemmConfig {
   static constexpr bool kOut16 = kOut16_;
   static constexpr bool kBias = kBias_;
+  static constexpr bool kTiled = kTiled_;
   static constexpr int kCtaGroup = kCtaGroup_;
   static constexpr int kKind = kKind_;
   static constexpr uint32_t kAbFmt = kAbFmt_;

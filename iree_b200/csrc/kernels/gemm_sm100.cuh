@@ -76,8 +76,18 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
                                                 int M, int N, int K, int batch, int flags,
                                                 const TensorMap* tm_a, const TensorMap* tm_b,
                                                 const TensorMap* tm_c,
-                                                const void* __restrict__ bias = nullptr) {
+                                                const void* __restrict__ bias = nullptr,
+                                                int tile_m0 = 1, int tile_n0 = 1,
+                                                uint32_t epi_swizzle = 7) {
+  // kTiled (linalg.mmt4d): M = M1 * M0, N = N1 * N0, K = K1 * K0 are the logical extents,
+  // |tile_m0| / |tile_n0| the tile rows of lhs / rhs (= result tile shape), multiples of 8;
+  // K0 rows are 16 bytes. 8 tile rows x 16 bytes are contiguous in memory = one UMMA core
+  // matrix, so the operands sit in shared memory UNSWIZZLED as [8-row group][8 K tiles]
+  // [8 rows][16 B] (make_gemm_tiled_recipe). |epi_swizzle| = the XOR mask of the result
+  // map's swizzle (7 / 3 / 1 for 128 / 64 / 32-byte result-tile rows).
   constexpr int G = Cfg::kCtaGroup;
+  static_assert(!Cfg::kTiled || (Cfg::kBMajorK && !Cfg::kOut16 && !Cfg::kBias),
+                "the tiled form is the NT f32 / i32 GEMM");
   (void)lhs;
   (void)rhs;
 
@@ -180,6 +190,11 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
               }
             }
           } else {
+          if constexpr (Cfg::kTiled) {
+            // Coordinates (8 rows x k0, k1, r0 / 8, r1): K tile kb * 8, row tile (row / R0).
+            tma_load_4d<G>(smem_a + stage * Cfg::kABytes, tm_a, full, 0, (int)kb * 8, 0, m0 / tile_m0);
+            tma_load_4d<G>(smem_b + stage * Cfg::kBBytes, tm_b, full, 0, (int)kb * 8, 0, n0 / tile_n0);
+          } else {
           tma_load_3d<G>(smem_a + stage * Cfg::kABytes, tm_a, full, k0, m0, tc.batch);
           if constexpr (Cfg::kBMajorK) {
             tma_load_3d<G>(smem_b + stage * Cfg::kBBytes, tm_b, full, k0, n0, tc.batch);
@@ -189,6 +204,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
               tma_load_3d<G>(smem_b + stage * Cfg::kBBytes + j * Cfg::kBBoxBytes, tm_b, full,
                              n0 + j * Cfg::kBBoxN, k0, tc.batch);
             }
+          }
           }
           }
           if (++stage == Cfg::kStages) {
@@ -217,14 +233,20 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
 #pragma unroll
           for (int k = 0; k < Cfg::kKSteps; ++k) {
             // A: K-major SW128 atom rows of 128 B; 8-row groups 1024 B apart.
-            const uint64_t da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
-            uint64_t db;
+            uint64_t da, db;
+            if constexpr (Cfg::kTiled) {
+              // Core matrices 128 B apart along K (one UMMA = 2 of them), 8-row groups 1024 B.
+              da = make_smem_desc_interleaved(a_addr + k * 256, 128, 1024);
+              db = make_smem_desc_interleaved(b_addr + k * 256, 128, 1024);
+            } else {
+            da = make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
             if constexpr (Cfg::kBMajorK) {
               db = make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
             } else {
               // MN-major: 128 B (of N) x 8 (K rows) atoms; K groups 1024 B apart,
               // N blocks one TMA box apart; one UMMA consumes kUmmaK rows.
               db = make_smem_desc_sw128(b_addr + k * (Cfg::kUmmaK * 128), Cfg::kBBoxBytes, 1024);
+            }
             }
             if (!diag_no_mma) umma_ss<G, Cfg::kKind>(tmem_d, da, db, Cfg::kIdesc, (kb | k) != 0);
           }
@@ -327,7 +349,22 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         if (accumulate && !Cfg::kOut16) {
           const int gm = m0 + (int)row;
           const int gn = n0 + c * Cfg::kEpiCols;
-          if (gm < M) {
+          if (Cfg::kTiled && gm < M) {
+            // Result tiles [M1, N1, M0, N0]: element (gm, gn + i).
+            const size_t row_base =
+                (size_t)(gm / tile_m0) * ((size_t)N * tile_m0) + (size_t)(gm % tile_m0) * tile_n0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              const int n = gn + i;
+              if (n >= N) continue;
+              const size_t at = row_base + (size_t)(n / tile_n0) * ((size_t)tile_m0 * tile_n0) + n % tile_n0;
+              if constexpr (Cfg::kKind == KIND_I8) {
+                v[i] = (uint32_t)((int32_t)v[i] + reinterpret_cast<const int32_t*>(out)[at]);
+              } else {
+                v[i] = __float_as_uint(__uint_as_float(v[i]) + reinterpret_cast<const float*>(out)[at]);
+              }
+            }
+          } else if (gm < M) {
             const size_t base = ((size_t)tc.batch * M + gm) * (size_t)N + gn;
             if constexpr (Cfg::kKind == KIND_I8) {
               const int32_t* cin = reinterpret_cast<const int32_t*>(out) + base;
@@ -351,7 +388,7 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         const uint32_t row_addr = smem_epi + buf * Cfg::kEpiBytes + row * 128;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const uint32_t dst = row_addr + ((i ^ (row & 7)) << 4);
+          const uint32_t dst = row_addr + ((i ^ (row & (Cfg::kTiled ? epi_swizzle : 7u))) << 4);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(v[4 * i]),
                        "r"(v[4 * i + 1]), "r"(v[4 * i + 2]), "r"(v[4 * i + 3])
                        : "memory");
@@ -359,8 +396,15 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
         fence_proxy_async_smem();
         named_barrier_sync(1, 128);
         if (epi_leader && !diag_no_store) {
-          tma_store_3d(tm_c, smem_epi + buf * Cfg::kEpiBytes, n0 + c * Cfg::kEpiCols, m0,
-                       tc.batch);
+          if constexpr (Cfg::kTiled) {
+            // Coordinates (n0, n1, m0, m1) of the result tiles.
+            const int col = n0 + c * Cfg::kEpiCols;
+            tma_store_4d(tm_c, smem_epi + buf * Cfg::kEpiBytes, col % tile_n0, col / tile_n0, 0,
+                         m0 / tile_m0);
+          } else {
+            tma_store_3d(tm_c, smem_epi + buf * Cfg::kEpiBytes, n0 + c * Cfg::kEpiCols, m0,
+                         tc.batch);
+          }
           tma_store_commit();
         }
         buf ^= 1;
@@ -445,6 +489,60 @@ constexpr iree_b200_tma_recipe_t make_gemm_recipe() {
   r.maps[2].box[1] = Cfg::kBlockM;
   r.maps[2].box[2] = 1;
   r.maps[2].swizzle = IREE_B200_TMA_SWIZZLE_128B;
+  return r;
+}
+
+// `<kernel>__tma` of the tiled (linalg.mmt4d) exports. Bindings 0 lhs [M1,K1,M0,K0], 1 rhs
+// [N1,K1,N0,K0], 2 out [M1,N1,M0,N0]. Push constants: 0 M1, 1 N1, 2 K1, 3 M0, 4 N0, 5 K0,
+// 6 flags, 7 M0 / 8, 8 = 128 / M0, 9 N0 / 8, 10 = kBlockN / N0, 11 = min(N0, 32),
+// 12 = 32 / min(N0, 32), 13 = swizzle mode of the result map (min(N0, 32) * 4 bytes wide).
+//
+// Operands: K0 rows are 16 bytes and tile rows are multiples of 8, so 8 tile rows x K0 are
+// 128 contiguous bytes = one UMMA core matrix. The map sees the tiled tensor [R1][K1][R0/8]
+// [8 x K0] as (8 x K0, K1, R0 / 8, R1) — its dense order is (8 x K0, R0 / 8, K1, R1) — and a
+// box of (8 x K0, 8, R0 / 8, rows / R0) lands UNSWIZZLED as [8-row group][8 K tiles][128 B]:
+// the interleaved K-major UMMA layout with core matrices 128 B apart along K and 1024 B
+// apart along the rows. (A 16-byte inner box under SWIZZLE_128B, the other way to reach the
+// row-major GEMM's tile, faults on the hardware: tools/tma4d_probe.cu.)
+// Result: (n0, n1, m0, m1) with boxes of 32 columns; the swizzle span equals the box row.
+template <class Cfg>
+constexpr iree_b200_tma_recipe_t make_gemm_tiled_recipe() {
+  iree_b200_tma_recipe_t r = {};
+  r.magic = IREE_B200_TMA_RECIPE_MAGIC;
+  r.map_count = 3;
+  const uint32_t ab_type = Cfg::kKind != KIND_F16
+                               ? IREE_B200_TMA_U8
+                               : (Cfg::kAbFmt == FMT_BF16 ? IREE_B200_TMA_BF16 : IREE_B200_TMA_F16);
+  for (int i = 0; i < 2; ++i) {
+    r.maps[i].binding = i;
+    r.maps[i].elem_type = ab_type;
+    r.maps[i].elem_size = Cfg::kElemSize;
+    r.maps[i].rank = 4;
+    r.maps[i].dim[0] = 128 / Cfg::kElemSize;                     // 8 rows x k0
+    r.maps[i].dim[1] = IREE_B200_TMA_DIM_CONST(2);               // k1
+    r.maps[i].dim[2] = IREE_B200_TMA_DIM_CONST(i == 0 ? 7 : 9);  // r0 / 8
+    r.maps[i].dim[3] = IREE_B200_TMA_DIM_CONST(i == 0 ? 0 : 1);  // r1
+    r.maps[i].box[0] = 128 / Cfg::kElemSize;
+    r.maps[i].box[1] = 8;
+    r.maps[i].box[2] = IREE_B200_TMA_DIM_CONST(i == 0 ? 7 : 9);
+    r.maps[i].box[3] = IREE_B200_TMA_DIM_CONST(i == 0 ? 8 : 10);
+    r.maps[i].swizzle = IREE_B200_TMA_SWIZZLE_NONE;
+    r.maps[i].order = IREE_B200_TMA_ORDER(0, 2, 1, 3);
+  }
+  r.maps[2].binding = 2;
+  r.maps[2].elem_type = Cfg::kKind == KIND_I8 ? IREE_B200_TMA_I32 : IREE_B200_TMA_F32;
+  r.maps[2].elem_size = 4;
+  r.maps[2].rank = 4;
+  r.maps[2].dim[0] = IREE_B200_TMA_DIM_CONST(4);  // n0
+  r.maps[2].dim[1] = IREE_B200_TMA_DIM_CONST(1);  // n1
+  r.maps[2].dim[2] = IREE_B200_TMA_DIM_CONST(3);  // m0
+  r.maps[2].dim[3] = IREE_B200_TMA_DIM_CONST(0);  // m1
+  r.maps[2].box[0] = IREE_B200_TMA_DIM_CONST(11);
+  r.maps[2].box[1] = IREE_B200_TMA_DIM_CONST(12);
+  r.maps[2].box[2] = IREE_B200_TMA_DIM_CONST(3);
+  r.maps[2].box[3] = IREE_B200_TMA_DIM_CONST(8);
+  r.maps[2].swizzle = IREE_B200_TMA_DIM_CONST(13);
+  r.maps[2].order = IREE_B200_TMA_ORDER(0, 2, 1, 3);
   return r;
 }
 

@@ -35,6 +35,43 @@
 #include <cuda_fp16.h>
 #include <stdint.h>
 
+// ---- tcgen05 form: tiles read and written directly -----------------------------------------
+// iree_b200_mmt4d_{bf16,f16}_f32 / _i8_i32 [_1cta]: for tiles whose K0 row is 16 bytes (K0 = 8
+// for f16 / bf16, 16 for i8) and M0, N0 in {8, 16, 32, 64, 128}, the operand tiles reach shared
+// memory as UMMA core matrices through rank-4 tensor maps (gemm_sm100.cuh, kTiled) and the
+// result goes back as tiles the same way: ONE dispatch, no workspace, the tcgen05 GEMM's rate.
+// Bindings lhs, rhs (read-only), out; constants M1, N1, K1, M0, N0, K0, flags (bit 0
+// accumulate), then the map extents make_gemm_tiled_recipe lists (M0 / 8, 128 / M0, N0 / 8,
+// (256 or 128) / N0, min(N0, 32), 32 / min(N0, 32), result swizzle mode); then the three
+// tensor maps. Device-only (the SIMT kernels below also compile for the host shims).
+#if defined(__CUDACC__)
+#include "gemm_sm100.cuh"
+
+#define B200_MMT4D(NAME, CLUSTER, G, KIND, FMT, STAGES)                                          \
+  using NAME##_cfg = b200::GemmConfig<G, b200::KIND, b200::FMT, true, STAGES, false, false, true>; \
+  extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                              \
+      b200::make_gemm_tiled_recipe<NAME##_cfg>();                                               \
+  extern "C" __global__ void CLUSTER __launch_bounds__(256, 1)                                  \
+      NAME(const void* __restrict__ lhs, const void* __restrict__ rhs, void* __restrict__ out,  \
+           int M1, int N1, int K1, int M0, int N0, int K0, int flags, int m0_groups,            \
+           int box_m1, int n0_groups, int box_n1, int box_c0, int box_c1, int c_swizzle,        \
+           const __grid_constant__ b200::TensorMap tm_a,                                        \
+           const __grid_constant__ b200::TensorMap tm_b,                                        \
+           const __grid_constant__ b200::TensorMap tm_c) {                                      \
+    (void)m0_groups, (void)box_m1, (void)n0_groups, (void)box_n1, (void)box_c0, (void)box_c1;   \
+    b200::gemm_sm100_body<NAME##_cfg>(lhs, rhs, out, M1 * M0, N1 * N0, K1 * K0, 1, flags & 0xf1, \
+                                      &tm_a, &tm_b, &tm_c, nullptr, M0, N0,                     \
+                                      (1u << c_swizzle) - 1u);                                  \
+  }
+
+B200_MMT4D(iree_b200_mmt4d_bf16_f32, __cluster_dims__(2, 1, 1), 2, KIND_F16, FMT_BF16, 6)
+B200_MMT4D(iree_b200_mmt4d_f16_f32, __cluster_dims__(2, 1, 1), 2, KIND_F16, FMT_F16, 6)
+B200_MMT4D(iree_b200_mmt4d_i8_i32, __cluster_dims__(2, 1, 1), 2, KIND_I8, FMT_S8, 6)
+B200_MMT4D(iree_b200_mmt4d_bf16_f32_1cta, , 1, KIND_F16, FMT_BF16, 4)
+B200_MMT4D(iree_b200_mmt4d_f16_f32_1cta, , 1, KIND_F16, FMT_F16, 4)
+B200_MMT4D(iree_b200_mmt4d_i8_i32_1cta, , 1, KIND_I8, FMT_S8, 4)
+#endif  // __CUDACC__
+
 namespace {
 
 constexpr int kMmt4dTile = 64;

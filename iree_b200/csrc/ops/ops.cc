@@ -67,6 +67,7 @@ struct iree_b200_ops_t {
   int32_t mxfp4_block_scaled_1cta_export = -1;
   int32_t mxfp4_packed_export = -1, mxfp4_packed_1cta_export = -1, mxfp4_pack_scales_export = -1;
   int32_t mmt4d_generic_exports[4] = {-1, -1, -1, -1};  // I8, F16, BF16, F32
+  int32_t mmt4d_direct_exports[3][2] = {{-1, -1}, {-1, -1}, {-1, -1}};  // [I8, F16, BF16][2-CTA, 1-CTA]
   int32_t mmt4d_relayout_exports[3] = {-1, -1, -1};  // 1-, 2-, 4-byte elements
   std::mutex pending_mutex;
   std::atomic<uint64_t> dispatch_count{0};
@@ -845,16 +846,20 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
       ops->cache, "PTXE", iree_b200_builtin_pending_cda1_start,
       (size_t)(iree_b200_builtin_pending_cda1_end - iree_b200_builtin_pending_cda1_start),
       &executable));
-  static const char* const kNames[14] = {
+  static const char* const kNames[20] = {
       "iree_b200_matmul_generic_mxfp4_f32", "iree_b200_matmul_mxfp4_dequant_bf16",
       "iree_b200_mmt4d_generic_i8_i32",     "iree_b200_mmt4d_generic_f16_f32",
       "iree_b200_mmt4d_generic_bf16_f32",   "iree_b200_mmt4d_relayout_b8",
       "iree_b200_mmt4d_relayout_b16",       "iree_b200_mmt4d_relayout_b32",
       "iree_b200_matmul_mxfp4_f32",         "iree_b200_matmul_mxfp4_f32_1cta",
       "iree_b200_matmul_mxfp4_packed_f32",  "iree_b200_matmul_mxfp4_packed_f32_1cta",
-      "iree_b200_mxfp4_pack_scales",        "iree_b200_mmt4d_generic_f32_f32"};
-  int32_t ordinals[14];
-  for (int i = 0; i < 14; ++i) {
+      "iree_b200_mxfp4_pack_scales",        "iree_b200_mmt4d_generic_f32_f32",
+      // tiles read directly: [slot I8 / F16 / BF16][2-CTA, 1-CTA]
+      "iree_b200_mmt4d_i8_i32",             "iree_b200_mmt4d_i8_i32_1cta",
+      "iree_b200_mmt4d_f16_f32",            "iree_b200_mmt4d_f16_f32_1cta",
+      "iree_b200_mmt4d_bf16_f32",           "iree_b200_mmt4d_bf16_f32_1cta"};
+  int32_t ordinals[20];
+  for (int i = 0; i < 20; ++i) {
     ordinals[i] = lookup(executable, kNames[i]);
     if (ordinals[i] < 0) {
       iree_b200_executable_release(executable);
@@ -870,6 +875,7 @@ static iree_b200_status_t ensure_pending_executable(iree_b200_ops_t* ops) {
   ops->mxfp4_packed_1cta_export = ordinals[11];
   ops->mxfp4_pack_scales_export = ordinals[12];
   ops->mmt4d_generic_exports[3] = ordinals[13];
+  for (int i = 0; i < 6; ++i) ops->mmt4d_direct_exports[i / 2][i % 2] = ordinals[14 + i];
   for (int i = 0; i < 3; ++i) {
     ops->mmt4d_generic_exports[i] = ordinals[2 + i];
     ops->mmt4d_relayout_exports[i] = ordinals[5 + i];
@@ -1188,7 +1194,8 @@ iree_b200_status_t check_mmt4d(int32_t element_type, int64_t M1, int64_t N1, int
       return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                          "mmt4d takes i8, f16, bf16 or f32 operands (got element type %d)", element_type);
   }
-  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC)) {
+  if (flags & ~(uint32_t)(IREE_B200_MATMUL_FLAG_ACCUMULATE | IREE_B200_MATMUL_FLAG_FORCE_GENERIC |
+                          IREE_B200_MATMUL_FLAG_MMT4D_RELAYOUT)) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
                        "mmt4d takes FLAG_ACCUMULATE and FLAG_FORCE_GENERIC only");
   }
@@ -1250,6 +1257,20 @@ static iree_b200_status_t record_mmt4d_relayout(iree_b200_ops_t* ops, iree_b200_
   return IREE_B200_STATUS_OK;
 }
 
+// Shapes the tile-direct tcgen05 exports take: K0 rows of 16 bytes, M0 / N0 multiples of 8
+// dividing the 128-row boxes (8 tile rows are one UMMA core matrix), a problem that fills a
+// tile.
+static bool mmt4d_direct_shape(int32_t element_type, int64_t M1, int64_t N1, int64_t K1, int32_t M0,
+                               int32_t N0, int32_t K0, uint32_t flags) {
+  if (element_type == IREE_B200_ELEMENT_TYPE_F32 ||
+      (flags & (IREE_B200_MATMUL_FLAG_FORCE_GENERIC | IREE_B200_MATMUL_FLAG_MMT4D_RELAYOUT))) {
+    return false;
+  }
+  const int64_t es = (int64_t)matmul_elem_size(element_type);
+  return K0 * es == 16 && 128 % M0 == 0 && 128 % N0 == 0 && M0 % 8 == 0 && N0 % 8 == 0 &&
+         M1 * M0 >= 128 && N1 * N0 >= 128 && K1 * K0 >= 128;
+}
+
 static iree_b200_status_t record_mmt4d_impl(iree_b200_ops_t* ops, iree_b200_command_buffer_t* cb,
                                             int32_t element_type, int64_t M1, int64_t N1,
                                             int64_t K1, int32_t M0, int32_t N0, int32_t K0,
@@ -1287,6 +1308,41 @@ static iree_b200_status_t record_mmt4d_impl(iree_b200_ops_t* ops, iree_b200_comm
     }
   }
   B200_RETURN_IF_ERROR(ensure_pending_executable(ops));
+  // Tiles read and written directly by the tcgen05 GEMM (one dispatch, no workspace): K0 rows
+  // of 16 bytes, M0 / N0 multiples of 8 dividing the 128-row boxes (8 tile rows are one UMMA
+  // core matrix), 16-byte aligned bindings, a problem that fills a tile.
+  {
+    const int64_t M = M1 * M0, N = N1 * N0;
+    bool direct = mmt4d_direct_shape(element_type, M1, N1, K1, M0, N0, K0, flags);
+    for (int i = 0; i < 3 && direct; ++i) {
+      direct = (refs[i].buffer->device_ptr + refs[i].offset) % 16 == 0;
+    }
+    if (direct) {
+      const int64_t sms = std::max<int64_t>(2, ops->sm_count - ops->reserved_sms);
+      const int64_t tiles_2cta = ceil_div(M, 256) * ceil_div(N, 256);
+      const int64_t tiles_1cta = ceil_div(M, 128) * ceil_div(N, 256);
+      const bool pair = M > 128 && tiles_2cta * 2 >= sms;
+      const uint32_t grid[3] = {
+          (uint32_t)(pair ? std::min<int64_t>(tiles_2cta * 2, sms & ~1) : std::min<int64_t>(tiles_1cta, sms)),
+          1, 1};
+      const uint32_t c_cols = (uint32_t)std::min<int32_t>(N0, 32);  // result box row, in elements
+      const uint32_t c_swizzle = c_cols == 32 ? 3u : c_cols == 16 ? 2u : 1u;  // 128 / 64 / 32 B
+      const uint32_t constants[14] = {(uint32_t)M1, (uint32_t)N1, (uint32_t)K1, (uint32_t)M0,
+                                      (uint32_t)N0, (uint32_t)K0,
+                                      (flags & IREE_B200_MATMUL_FLAG_ACCUMULATE) |
+                                          (getenv("IREE_B200_MMT4D_DIAG")
+                                               ? (uint32_t)strtoul(getenv("IREE_B200_MMT4D_DIAG"), nullptr, 0)
+                                               : 0u),
+                                      (uint32_t)(M0 / 8), (uint32_t)(128 / M0), (uint32_t)(N0 / 8),
+                                      (uint32_t)((pair ? 128 : 256) / N0), c_cols, 32 / c_cols,
+                                      c_swizzle};
+      B200_RETURN_IF_ERROR(iree_b200_command_buffer_dispatch(
+          cb, ops->pending_executable, ops->mmt4d_direct_exports[shape.slot][pair ? 0 : 1], grid,
+          constants, 14, refs, 3, 0));
+      ops->dispatch_count.fetch_add(1);
+      return IREE_B200_STATUS_OK;
+    }
+  }
   const uint64_t ws_need =
       iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
   if (workspace && workspace->buffer && ws_need) {
@@ -1372,7 +1428,8 @@ iree_b200_status_t iree_b200_ops_mmt4d_host(iree_b200_ops_t* ops, int32_t elemen
   }
   // FORCE_GENERIC keeps the call on the single SIMT dispatch (k-ascending accumulation).
   const uint64_t ws_offset = total,
-                 ws_bytes = (flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC)
+                 ws_bytes = ((flags & IREE_B200_MATMUL_FLAG_FORCE_GENERIC) ||
+                             mmt4d_direct_shape(element_type, M1, N1, K1, M0, N0, K0, flags))
                                 ? 0
                                 : iree_b200_ops_mmt4d_workspace_size(element_type, M1, N1, K1, M0, N0, K0);
   total += ws_bytes;

@@ -72,6 +72,19 @@ int main() {
   emit("iree_b200_mmt4d_generic_f16_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_i8_i32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
   emit("iree_b200_mmt4d_generic_f32_f32", "mmt4d_kernels", 256, 0, 7, "1, 1, 0");
+  // ... on the tensor cores, tiles read and written directly (K0 rows of 16 bytes):
+  // + the seven map extents of make_gemm_tiled_recipe.
+  {
+    using C2 = GemmConfig<2, KIND_F16, FMT_BF16, true, 6, false, false, true>;
+    using C1 = GemmConfig<1, KIND_F16, FMT_BF16, true, 4, false, false, true>;
+    for (const char* t : {"bf16_f32", "f16_f32", "i8_i32"}) {
+      char name[96];
+      snprintf(name, sizeof(name), "iree_b200_mmt4d_%s", t);
+      emit(name, "mmt4d_kernels", C2::kThreads, C2::kSmemBytes, 14, "1, 1, 0");
+      snprintf(name, sizeof(name), "iree_b200_mmt4d_%s_1cta", t);
+      emit(name, "mmt4d_kernels", C1::kThreads, C1::kSmemBytes, 14, "1, 1, 0");
+    }
+  }
   // tiled <-> row-major relayout: src, dst; constants R1 C1 R0 C0 to_tiled.
   emit("iree_b200_mmt4d_relayout_b8", "mmt4d_kernels", 256, 0, 5, "1, 0");
   emit("iree_b200_mmt4d_relayout_b16", "mmt4d_kernels", 256, 0, 5, "1, 0");

@@ -31,7 +31,7 @@ MATMUL_FORCE_GENERIC = 1 << 8
 MATMUL_FORCE_1CTA = 1 << 9
 MATMUL_FORCE_2CTA = 1 << 10
 MATMUL_MX_EXPAND = 1 << 11
-MATMUL_MX_EXPAND = 1 << 11
+MATMUL_MMT4D_RELAYOUT = 1 << 12
 
 ATTENTION_MASK_NONE, ATTENTION_MASK_BOOL, ATTENTION_MASK_F32, ATTENTION_MASK_CAUSAL = 0, 1, 2, 3
 ATTENTION_FORCE_GENERIC = 1 << 8

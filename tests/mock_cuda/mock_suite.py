@@ -111,6 +111,47 @@ def test_sub_range_bindings_move_the_tensor_map_base(dev, dev_ops):
     assert tc["type"] == 3                                      # i32 result
 
 
+@pytest.mark.parametrize("t,M0,N0", [("bf16", 16, 16), ("i8", 8, 32), ("f16", 128, 64)])
+def test_mmt4d_tile_direct_maps_walk_the_tiles(dev, dev_ops, t, M0, N0):
+    """linalg.mmt4d with 16-byte K0 rows and tile rows in multiples of 8: ONE tcgen05 dispatch
+    whose rank-4 tensor maps read the tiled operands as UMMA core matrices (8 rows x 16 bytes =
+    128 contiguous bytes, unswizzled) and write result tiles with a swizzle as wide as the
+    tile row; outside the guard the call stays on the SIMT / relayout routes."""
+    es = 1 if t == "i8" else 2
+    K0 = 16 // es
+    M, N, K = 1024, 2048, 512
+    M1, N1, K1 = M // M0, N // N0, K // K0
+    a, b, c = dev.allocate(M * K * es), dev.allocate(N * K * es), dev.allocate(M * N * 4)
+    tensor_maps(), launches()
+    cb = H.CommandBuffer(dev).begin()
+    dev_ops.record_mmt4d(cb, t, M1, N1, K1, M0, N0, K0, a.ref(), b.ref(), c.ref())
+    cb.end()
+    ta, tb, tc = tensor_maps()
+    dev.execute(cb)
+    dev.wait_idle()
+    acc = "i32" if t == "i8" else "f32"
+    (name, grid, block, smem), = launches()
+    assert name == f"iree_b200_mmt4d_{t}_{acc}_1cta" and block == [256, 1, 1] and grid == [64, 1, 1]
+    inner = 128 // es          # 8 rows x K0 elements
+    for tm, R0, R1, rows in ((ta, M0, M1, 128), (tb, N0, N1, 256)):
+        assert (tm["rank"], tm["swizzle"]) == (4, 0)
+        assert tm["dims"][:4] == [inner, K1, R0 // 8, R1]
+        # byte strides of (k1, 8-row group, r1) in the tiled tensor [R1][K1][R0 / 8][8 x K0]
+        assert tm["strides"][:3] == [R0 * 16, 128, K1 * R0 * 16]
+        assert tm["box"][:4] == [inner, 8, R0 // 8, rows // R0]
+    cols = min(N0, 32)
+    assert (tc["rank"], tc["swizzle"], tc["type"]) == (4, {32: 3, 16: 2, 8: 1}[cols], 3 if t == "i8" else 7)
+    assert tc["dims"][:4] == [N0, N1, M0, M1]
+    assert tc["strides"][:3] == [M0 * N0 * 4, N0 * 4, N1 * M0 * N0 * 4]
+    assert tc["box"][:4] == [cols, 32 // cols, M0, 128 // M0]
+    # Outside the guard (tile rows not a multiple of 8; a K0 row that is not 16 bytes): no maps.
+    for m0, n0, k0 in ((4, 16, K0), (16, 16, K0 * 2)):
+        cb = H.CommandBuffer(dev).begin()
+        dev_ops.record_mmt4d(cb, t, M // m0, N // n0, K // k0, m0, n0, k0, a.ref(), b.ref(), c.ref())
+        cb.end()
+        assert tensor_maps() == []
+
+
 def test_fused_bias_dispatch_binds_the_result_fourth(dev, dev_ops):
     M, N, K = 1024, 1024, 256
     a, b, c = dev.allocate(M * K * 2), dev.allocate(K * N * 2), dev.allocate(M * N * 2)

@@ -36,9 +36,11 @@ def test_mmt4d_vs_oracle(ops, t, case):
     before = ops.dispatch_count
     ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, out.ctypes.data,
                    flags=H.MATMUL_ACCUMULATE if accumulate else 0)
-    # Tile-filling shapes take the tensor-core route: unpack lhs, rhs (, acc), GEMM, pack.
+    # Tile-filling shapes take a tensor-core route: tiles read directly (one dispatch) when
+    # the tile shape allows, else unpack lhs, rhs (, acc), GEMM, pack.
     routed = ops.mmt4d_workspace_size(t, M1, N1, K1, M0, N0, K0) != 0
-    assert ops.dispatch_count - before == ((5 if accumulate else 4) if routed else 1)
+    direct = _direct(t, M1, N1, K1, M0, N0, K0)
+    assert ops.dispatch_count - before == (1 if direct else (5 if accumulate else 4) if routed else 1)
     assert np.array_equal(out, oracle.mmt4d(t, l4, r4, acc=acc))
     if oracle.ref_available():
         assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
@@ -46,6 +48,50 @@ def test_mmt4d_vs_oracle(ops, t, case):
         want_mm = (lhs.astype(np.float64) @ rhs.astype(np.float64)).astype(np.float32) if t == "f32" \
             else oracle.matmul(t, lhs[None], rhs[None])[0]
         assert np.array_equal(oracle.unpack(out, M, N), want_mm)
+
+
+def _direct(t, M1, N1, K1, M0, N0, K0):
+    """iree_b200_ops_record_mmt4d's guard for the tile-direct tcgen05 export."""
+    es = {"i8": 1, "f16": 2, "bf16": 2}.get(t)
+    return (es is not None and K0 * es == 16 and 128 % M0 == 0 and 128 % N0 == 0 and M0 % 8 == 0
+            and N0 % 8 == 0 and min(M1 * M0, N1 * N0, K1 * K0) >= 128)
+
+
+@pytest.mark.parametrize("t", ["bf16", "f16", "i8"])
+@pytest.mark.parametrize("case", [
+    # M, K, N (logical), M0, N0, accumulate   (K0 = 16 bytes / element size)
+    (128, 128, 128, 16, 16, False), (1000, 528, 272, 16, 16, False), (300, 256, 520, 8, 32, True),
+    (257, 1032, 260, 32, 64, False), (2048, 2048, 2048, 16, 16, True), (4096, 512, 1024, 128, 8, False),
+    (520, 384, 1000, 64, 128, True),
+], ids=str)
+def test_mmt4d_tiles_read_directly_by_the_tcgen05_gemm(ops, t, case):
+    """iree_b200_mmt4d_*: rank-4 tensor maps walk the tiled operands / result, one dispatch, no
+    workspace; bit-exact against the oracle, the reference's iree_uk_mmt4d and the SIMT kernel."""
+    M, K, N, M0, N0, accumulate = case
+    K0 = 16 if t == "i8" else 8
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    l4 = oracle.pack(lhs, M0, K0)
+    r4 = oracle.pack(np.ascontiguousarray(rhs.T), N0, K0)
+    M1, K1, N1 = l4.shape[0], l4.shape[1], r4.shape[0]
+    assert _direct(t, M1, N1, K1, M0, N0, K0)
+    acc_t = "i32" if t == "i8" else "f32"
+    acc = oracle.generate_random_matrix(acc_t, (M1, N1, M0, N0), 3) if accumulate else None
+    dt = np.int32 if t == "i8" else np.float32
+    flags = H.MATMUL_ACCUMULATE if accumulate else 0
+    out = acc.copy() if accumulate else np.full((M1, N1, M0, N0), 77, dtype=dt)
+    before = ops.dispatch_count
+    ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, out.ctypes.data,
+                   flags=flags)
+    assert ops.dispatch_count - before == 1
+    want = oracle.mmt4d(t, l4, r4, acc=acc)
+    assert np.array_equal(out, want)
+    if oracle.ref_available():
+        assert np.array_equal(out, oracle.ref_mmt4d(t, l4, r4, acc=acc))
+    simt = acc.copy() if accumulate else np.zeros((M1, N1, M0, N0), dtype=dt)
+    ops.mmt4d_host(t, M1, N1, K1, M0, N0, K0, l4.ctypes.data, r4.ctypes.data, simt.ctypes.data,
+                   flags=flags | H.MATMUL_FORCE_GENERIC)
+    assert np.array_equal(simt, want)
 
 
 @pytest.mark.parametrize("t", ["f16", "bf16", "i8"])
