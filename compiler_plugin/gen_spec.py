@@ -346,14 +346,19 @@ def attention_rewriter(name: str) -> str:
 """
 
 
-def generate(objects_dir: str) -> str:
+def generate(objects_dir: str, stock_driver: bool = False) -> str:
+    """|stock_driver|: use the `*_dtm` exports (tensor maps built on the device), so the
+    compiled module runs on an UNMODIFIED IREE runtime — no `__tma` recipe, no driver hook.
+    Covers matmul / batch_matmul (bf16, f16, i8) and attention; the f8 and fused-consumer
+    dispatches exist host-fed only and are left to IREE's own codegen in that mode."""
     man = load_manifest(objects_dir)
     entries, matchers, rewriters, pairs = [], [], [], []
-    for et in ("bf16", "f16", "i8", "f8e4m3fn", "f8e5m2"):
+    dtm = "_dtm" if stock_driver else ""
+    for et in (("bf16", "f16", "i8") if stock_driver else ("bf16", "f16", "i8", "f8e4m3fn", "f8e5m2")):
         acc = ACC_TYPE[et]
         for batched in (False, True):
             for big, suffix, g in ((True, "", 2), (False, "_1cta", 1)):
-                kernel = f"iree_b200_matmul_{et}_{acc}{suffix}"
+                kernel = f"iree_b200_matmul_{et}_{acc}{dtm}{suffix}"
                 key = f"{kernel}{'_batch' if batched else ''}"
                 entries.append(matmul_entry(man[kernel], et, batched, g))
                 matchers.append(matmul_matcher(key, et, batched, big))
@@ -363,7 +368,7 @@ def generate(objects_dir: str) -> str:
     # Fused consumers first: foreach_match takes the first matcher that succeeds, and the
     # DAG roots (the elementwise generic) are visited independently of the matmul inside.
     linear = []
-    for et in ("bf16", "f16", "i8"):
+    for et in (() if stock_driver else ("bf16", "f16", "i8")):
         for truncate in ((False, True) if et != "i8" else (False,)):
             out_t = MLIR_TYPE[et] if truncate else ACC_TYPE[et]
             for relu in (False, True):
@@ -376,7 +381,7 @@ def generate(objects_dir: str) -> str:
                     linear.append(f"@match_{key} -> @rewrite_{key}")
     pairs = linear + pairs
     for et in ("f16", "bf16"):
-        kernel = f"iree_b200_attention_prefill_{et}"
+        kernel = f"iree_b200_attention_prefill_{et}{dtm}"
         entries.append(attention_entry(man[kernel], et))
         matchers.append(attention_matcher(kernel, et))
         rewriters.append(attention_rewriter(kernel))
@@ -411,8 +416,10 @@ def main(argv=None):
                                  formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--objects-dir", default=os.path.join(ROOT, "iree_b200", "_build"))
     ap.add_argument("-o", "--output", default="-")
+    ap.add_argument("--stock-driver", action="store_true",
+                    help="use the *_dtm exports: the module runs on an unmodified IREE runtime")
     args = ap.parse_args(argv)
-    text = generate(args.objects_dir)
+    text = generate(args.objects_dir, stock_driver=args.stock_driver)
     if args.output == "-":
         sys.stdout.write(text)
     else:

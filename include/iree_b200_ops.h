@@ -66,6 +66,11 @@ enum {
   // mmt4d only: take the relayout + row-major GEMM route (needs the workspace) even where the
   // tile-direct tcgen05 export applies (comparison runs, tools/mmt4d_bench.py).
   IREE_B200_MATMUL_FLAG_MMT4D_RELAYOUT = 1u << 12,
+  // Select the `*_dtm` exports: the same tcgen05 kernels building their tensor maps on the
+  // device (tensormap.replace), i.e. the exports an UNMODIFIED IREE CUDA driver can launch —
+  // bindings and push constants only, no `__tma` recipe. i8 / f16 / bf16 with the 32-bit
+  // result; launches of these exports must not overlap in time (gemm_dtm_kernels.cu).
+  IREE_B200_MATMUL_FLAG_DEVICE_MAPS = 1u << 13,
 };
 
 // The builtin executable ("CDA1" blob linked into this library: one cubin per kernel
@@ -284,6 +289,10 @@ enum {
   // Prefill kernel: keep the plain [ceil(M/256), B] grid even when the last wave of equal
   // units would be mostly empty (default: cut that wave's units over K2 and merge).
   IREE_B200_ATTENTION_FLAG_NO_TAIL_SPLIT = 1u << 16,
+  // Prefill kernel: the `*_dtm` export, which builds its tensor maps on the device and so is
+  // launchable by an unmodified IREE CUDA driver (see IREE_B200_MATMUL_FLAG_DEVICE_MAPS).
+  // Unmasked or MASK_CAUSAL; always one dispatch.
+  IREE_B200_ATTENTION_FLAG_DEVICE_MAPS = 1u << 17,
 };
 
 #define IREE_B200_ATTENTION_MAX_DISPATCHES 2

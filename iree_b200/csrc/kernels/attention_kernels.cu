@@ -62,6 +62,37 @@ B200_PREFILL(iree_b200_attention_prefill_bf16_p25, true, 1)
 B200_PREFILL(iree_b200_attention_prefill_f16_p50, false, 2)
 B200_PREFILL(iree_b200_attention_prefill_bf16_p50, true, 2)
 
+// Same kernel, launchable by an unmodified IREE CUDA driver: no tensor-map parameters; warp 3
+// patches the host-encoded templates of the twin export (tensormap_templates.inc) with this
+// dispatch's pointers and extents — Q [B, M, D], K and V [B, K2, D] — into the slots of the SM
+// it runs on (common.cuh, tensormap_build_rank3). flags bit 0 = causal, as in the twin.
+#define B200_TENSORMAP_TEMPLATE(NAME, ...) \
+  __device__ __align__(128) const uint64_t NAME##__tmt[3][16] = {__VA_ARGS__};
+#include "tensormap_templates.inc"
+#undef B200_TENSORMAP_TEMPLATE
+__device__ __align__(128) TensorMap iree_b200_attention_dtm_slots[kTensorMapSlotSms][4];
+
+#define B200_PREFILL_DTM(NAME, TEMPLATE_OF, BF16)                                              \
+  extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \
+      NAME(const void* __restrict__ q, const void* __restrict__ k, const void* __restrict__ v, \
+           void* __restrict__ out, int B, int M, int K2, int scale_bits, int flags) {          \
+    __shared__ __align__(128) TensorMap staging[3];                                            \
+    TensorMap* slots = iree_b200_attention_dtm_slots[tensormap_slot_index()];                  \
+    if ((threadIdx.x >> 5) == 3) {                                                             \
+      tensormap_build_rank3(slots + 0, staging + 0, TEMPLATE_OF##__tmt[0], q,                  \
+                            PrefillCfg::kHeadDim, M, B, 2);                                    \
+      tensormap_build_rank3(slots + 1, staging + 1, TEMPLATE_OF##__tmt[1], k,                  \
+                            PrefillCfg::kHeadDim, K2, B, 2);                                   \
+      tensormap_build_rank3(slots + 2, staging + 2, TEMPLATE_OF##__tmt[2], v,                  \
+                            PrefillCfg::kHeadDim, K2, B, 2);                                   \
+    }                                                                                          \
+    attention_prefill_body<PrefillCfg, BF16, 0, false, false, true>(                           \
+        out, B, M, K2, scale_bits, flags, slots, slots + 1, slots + 2);                        \
+  }
+
+B200_PREFILL_DTM(iree_b200_attention_prefill_f16_dtm, iree_b200_attention_prefill_f16, false)
+B200_PREFILL_DTM(iree_b200_attention_prefill_bf16_dtm, iree_b200_attention_prefill_bf16, true)
+
 #define B200_PREFILL_MASK(NAME, BF16)                                                          \
   extern "C" __device__ const iree_b200_tma_recipe_t NAME##__tma =                             \
       make_attention_prefill_recipe<PrefillCfg, BF16>();                                       \

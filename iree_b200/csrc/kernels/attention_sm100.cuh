@@ -130,7 +130,8 @@ B200_DEVICE float attention_q_multiplier(float scale) {
 // waves); splitting just those units makes the last wave short instead.
 constexpr int kAttnFlagCausal = 1;
 
-template <class Cfg, bool kBf16, int kPoly = 0, bool kSplit = false, bool kMask = false>
+template <class Cfg, bool kBf16, int kPoly = 0, bool kSplit = false, bool kMask = false,
+          bool kDeviceMaps = false>
 __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, int B, int M, int K2,
                                                        int scale_bits, int flags,
                                                        const TensorMap* tm_q, const TensorMap* tm_k,
@@ -196,7 +197,9 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     num_kv = min(num_kv, (uint32_t)((last_row + causal_shift + BN) / BN));
   }
 
-  if (warp == 0 && lane == 0) {
+  // kDeviceMaps: |tm_*| are global slots warp 3 filled before the call (attention_kernels.cu,
+  // `*_dtm`); the producer acquires them after the setup barrier.
+  if (!kDeviceMaps && warp == 0 && lane == 0) {
     tma_prefetch_desc(tm_q);
     tma_prefetch_desc(tm_k);
     tma_prefetch_desc(tm_v);
@@ -236,6 +239,11 @@ __device__ __forceinline__ void attention_prefill_body(void* __restrict__ out, i
     // TMA producer
     //===------------------------------------------------------------------===//
     if (elect_one()) {
+      if constexpr (kDeviceMaps) {
+        tensormap_fence_acquire(tm_q);
+        tensormap_fence_acquire(tm_k);
+        tensormap_fence_acquire(tm_v);
+      }
       for (int t = 0; t < Cfg::kTilesPerCta; ++t) {
         mbar_expect_tx(bar_q_full + 8 * t, Cfg::kTileBytes);
         for (int c = 0; c < Cfg::kChunks; ++c) {

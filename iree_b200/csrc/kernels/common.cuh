@@ -161,6 +161,67 @@ B200_DEVICE void tma_prefetch_desc(const TensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
 
+// ---- Tensor maps built on the device (kernels launched without trailing CUtensorMap
+// parameters, i.e. by an unmodified IREE CUDA driver) -----------------------------------------
+// A 128-byte template (encoded once on the host for a dummy shape) is copied to shared memory,
+// patched with tensormap.replace, and published to a global slot with the fused copy +
+// release fence; whoever then issues TMA through the slot first runs the acquire fence.
+
+// One warp, converged. |staging| (shared, 128-byte aligned) and |slot| (global, 128-byte
+// aligned) hold one map; rank 3, dense tensor: strides follow from the extents.
+B200_DEVICE void tensormap_build_rank3(TensorMap* slot, TensorMap* staging, const uint64_t* tmpl,
+                                       const void* base, uint32_t dim0, uint32_t dim1, uint32_t dim2,
+                                       uint32_t elem_size) {
+  const uint32_t lane = threadIdx.x & 31;
+  reinterpret_cast<uint32_t*>(staging)[lane] = reinterpret_cast<const uint32_t*>(tmpl)[lane];
+  __syncwarp();
+  if (lane == 0) {
+    const uint64_t s = static_cast<uint64_t>(smem_u32(staging));
+    const uint64_t stride0 = (uint64_t)dim0 * elem_size, stride1 = stride0 * dim1;
+    asm volatile("tensormap.replace.tile.global_address.shared::cta.b1024.b64 [%0], %1;" ::"l"(s),
+                 "l"(reinterpret_cast<uint64_t>(base))
+                 : "memory");
+    asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 0, %1;" ::"l"(s),
+                 "r"(dim0)
+                 : "memory");
+    asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 1, %1;" ::"l"(s),
+                 "r"(dim1)
+                 : "memory");
+    asm volatile("tensormap.replace.tile.global_dim.shared::cta.b1024.b32 [%0], 2, %1;" ::"l"(s),
+                 "r"(dim2)
+                 : "memory");
+    // Byte strides of dimensions 1 and 2 (multiples of 16; dimension 0 is dense).
+    asm volatile("tensormap.replace.tile.global_stride.shared::cta.b1024.b64 [%0], 0, %1;" ::"l"(s),
+                 "l"(stride0)
+                 : "memory");
+    asm volatile("tensormap.replace.tile.global_stride.shared::cta.b1024.b64 [%0], 1, %1;" ::"l"(s),
+                 "l"(stride1)
+                 : "memory");
+  }
+  __syncwarp();
+  asm volatile(
+      "tensormap.cp_fenceproxy.global.shared::cta.tensormap::generic.release.gpu.sync.aligned"
+      " [%0], [%1], 128;" ::"l"(reinterpret_cast<uint64_t>(slot)),
+      "r"(smem_u32(staging))
+      : "memory");
+}
+
+// Slot index of the calling CTA: its SM. The kernels that build maps need more than half an
+// SM's shared memory, so at most one of their CTAs is resident per SM and a slot has one
+// writer / reader at a time — also across back-to-back or overlapping launches.
+constexpr int kTensorMapSlotSms = 512;
+B200_DEVICE uint32_t tensormap_slot_index() {
+  uint32_t smid;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+  return smid % kTensorMapSlotSms;
+}
+
+B200_DEVICE void tensormap_fence_acquire(const TensorMap* slot) {
+  asm volatile("fence.proxy.tensormap::generic.acquire.gpu [%0], 128;" ::"l"(
+                   reinterpret_cast<uint64_t>(slot))
+               : "memory");
+}
+
 // 3-D tiled load into this CTA's shared memory; completes `bytes` on `bar`.
 // kCtaGroup == 2: `bar` is a shared::cluster address (the pair leader's barrier).
 template <int kCtaGroup>

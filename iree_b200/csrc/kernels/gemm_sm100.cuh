@@ -70,7 +70,7 @@ B200_DEVICE TileCoord decode_tile(uint32_t tile, uint32_t tiles_m, uint32_t tile
   return c;
 }
 
-template <class Cfg>
+template <class Cfg, bool kDeviceMaps = false>
 __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
                                                 const void* __restrict__ rhs, void* __restrict__ out,
                                                 int M, int N, int K, int batch, int flags,
@@ -125,7 +125,9 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
   // bits 8-15: raster group height override (tile rows walked before the column advances)
   const uint32_t group_rows = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : Cfg::kGroupM;
 
-  if (warp == 0 && lane == 0) {
+  // kDeviceMaps: |tm_*| are global slots another warp of this CTA filled before the call
+  // (gemm_dtm_kernels.cu); their users acquire them after the setup barrier below.
+  if (!kDeviceMaps && warp == 0 && lane == 0) {
     tma_prefetch_desc(tm_a);
     tma_prefetch_desc(tm_b);
     tma_prefetch_desc(tm_c);
@@ -161,6 +163,10 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     // TMA producer
     //===------------------------------------------------------------------===//
     if (!diag_no_load && elect_one()) {
+      if constexpr (kDeviceMaps) {
+        tensormap_fence_acquire(tm_a);
+        tensormap_fence_acquire(tm_b);
+      }
       // All loads of the pair complete on the LEADER's full barrier.
       const uint32_t full0 = (G == 2) ? map_to_cta(bar_full, 0) : bar_full;
       const uint64_t policy_keep = l2_policy_evict_last(), policy_stream = l2_policy_evict_first();
@@ -293,6 +299,9 @@ __device__ __forceinline__ void gemm_sm100_body(const void* __restrict__ lhs,
     };
     uint32_t acc = 0, acc_phase = 0;
     uint32_t buf = 0;
+    if constexpr (kDeviceMaps) {
+      if (epi_leader) tensormap_fence_acquire(tm_c);
+    }
     for (uint32_t tile = cluster_idx; tile < total_tiles; tile += cluster_cnt) {
       const TileCoord tc = decode_tile<Cfg>(tile, tiles_m, tiles_n, group_rows);
       const int m0 = tc.m_blk * Cfg::kTileM + (int)cta_rank * Cfg::kBlockM;

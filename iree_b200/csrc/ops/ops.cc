@@ -50,7 +50,8 @@ enum AttentionExport {
   kAttnPrefillPoly50 = 6,
   kAttnPrefillSplit = 7,
   kAttnPrefillMerge = 8,
-  kAttnPrefillMask = 9
+  kAttnPrefillMask = 9,
+  kAttnPrefillDeviceMaps = 10
 };
 
 }  // namespace
@@ -75,6 +76,7 @@ struct iree_b200_ops_t {
   int32_t sm_count = 0;  // device->sm_count, or the caller's for an offline (selection-only) object
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[6][2][kFamilyCount];
+  int32_t matmul_dtm_exports[6][2][kFamilyCount];    // tensor maps built on the device
   int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
   int32_t matmul_bias_exports[6][2][kFamilyCount];        // bias / activation epilogue
   int32_t matmul_bias_trunc_exports[6][2][kFamilyCount];  // ... then truncation
@@ -116,12 +118,15 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
     for (int nt = 0; nt < 2; ++nt) {
       for (int f = 0; f < kFamilyCount; ++f) {
         ops->matmul_exports[t][nt][f] = ops->matmul_trunc_exports[t][nt][f] = -1;
+        ops->matmul_dtm_exports[t][nt][f] = -1;
         ops->matmul_bias_exports[t][nt][f] = ops->matmul_bias_trunc_exports[t][nt][f] = -1;
       }
       if (!kTypeSuffix[t]) continue;
       const std::string base = std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTypeSuffix[t];
       ops->matmul_exports[t][nt][kFamily2Cta] = lookup(ops->executable, base);
       ops->matmul_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta");
+      ops->matmul_dtm_exports[t][nt][kFamily2Cta] = lookup(ops->executable, base + "_dtm");
+      ops->matmul_dtm_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_dtm_1cta");
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
       if (t <= IREE_B200_ELEMENT_TYPE_BF16) {  // i8, f16, bf16
@@ -166,6 +171,8 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
         lookup(ops->executable, "iree_b200_attention_prefill_merge_" + suffix);
     ops->attention_exports[t][kAttnPrefillMask] =
         lookup(ops->executable, "iree_b200_attention_prefill_mask_" + suffix);
+    ops->attention_exports[t][kAttnPrefillDeviceMaps] =
+        lookup(ops->executable, "iree_b200_attention_prefill_" + suffix + "_dtm");
     ops->attention_exports[t][kAttnDecodeSplit] =
         lookup(ops->executable, "iree_b200_attention_decode_split_" + suffix);
     ops->attention_exports[t][kAttnDecodeMerge] =
@@ -376,8 +383,16 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
     // SM pairs only pay off once there are enough 256x256 tiles to occupy them.
     family = (M > 128 && tiles_2cta * 2 >= sm_count) ? kFamily2Cta : kFamily1Cta;
   }
-  const auto& table = with_bias ? (truncate ? ops->matmul_bias_trunc_exports : ops->matmul_bias_exports)
-                                : (truncate ? ops->matmul_trunc_exports : ops->matmul_exports);
+  const bool device_maps = (flags & IREE_B200_MATMUL_FLAG_DEVICE_MAPS) != 0;
+  if (device_maps && (with_bias || truncate || element_type > IREE_B200_ELEMENT_TYPE_BF16 ||
+                      family == kFamilyGeneric)) {
+    return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                       "FLAG_DEVICE_MAPS: i8 / f16 / bf16 matmuls with the 32-bit result whose "
+                       "shape passes the TMA guards only");
+  }
+  const auto& table = device_maps ? ops->matmul_dtm_exports
+                      : with_bias ? (truncate ? ops->matmul_bias_trunc_exports : ops->matmul_bias_exports)
+                                  : (truncate ? ops->matmul_trunc_exports : ops->matmul_exports);
   const int32_t ordinal = table[element_type][transpose_rhs ? 1 : 0][family];
   if (ordinal < 0) {
     return make_status(IREE_B200_STATUS_NOT_FOUND,
@@ -1565,6 +1580,15 @@ iree_b200_status_t iree_b200_ops_select_attention(const iree_b200_ops_t* ops, in
       const int64_t tail_units = units - full_units;
       int64_t split = tail_units ? std::min<int64_t>(4, sms / tail_units) : 1;
       split = std::min(split, kv_blocks / 4);  // every part keeps >= 4 K2 blocks
+      const bool device_maps = (flags & IREE_B200_ATTENTION_FLAG_DEVICE_MAPS) != 0;
+      if (device_maps) {
+        // The export an unmodified IREE CUDA driver can launch: one dispatch, no mask tensor.
+        if (mask_kind == IREE_B200_ATTENTION_MASK_BOOL || variant != kAttnPrefill) {
+          return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
+                             "FLAG_DEVICE_MAPS: unmasked or causal prefill, default exp2 only");
+        }
+        variant = kAttnPrefillDeviceMaps;
+      }
       const bool use_split = !(flags & IREE_B200_ATTENTION_FLAG_NO_TAIL_SPLIT) && split >= 2 &&
                              variant == kAttnPrefill && mask_kind == IREE_B200_ATTENTION_MASK_NONE &&
                              full_units + tail_units * split <= 0x7fffffff;

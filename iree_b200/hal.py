@@ -32,6 +32,7 @@ MATMUL_FORCE_1CTA = 1 << 9
 MATMUL_FORCE_2CTA = 1 << 10
 MATMUL_MX_EXPAND = 1 << 11
 MATMUL_MMT4D_RELAYOUT = 1 << 12
+MATMUL_DEVICE_MAPS = 1 << 13
 
 ATTENTION_MASK_NONE, ATTENTION_MASK_BOOL, ATTENTION_MASK_F32, ATTENTION_MASK_CAUSAL = 0, 1, 2, 3
 ATTENTION_FORCE_GENERIC = 1 << 8
@@ -43,6 +44,7 @@ ATTENTION_EXP2_MUFU_ONLY = 1 << 13
 ATTENTION_EXP2_POLY_25 = 1 << 14
 ATTENTION_EXP2_POLY_50 = 1 << 15
 ATTENTION_NO_TAIL_SPLIT = 1 << 16
+ATTENTION_DEVICE_MAPS = 1 << 17
 
 MODE_GRAPH, MODE_STREAM = 0, 1
 MEMORY_DEVICE_LOCAL, MEMORY_HOST_LOCAL = 1, 2

@@ -426,3 +426,32 @@ def test_llama_prefill_shape_causal_sampled(ops, t):
         want = oracle.attention(t, q[b:b + 1, rows], k[b:b + 1], v[b:b + 1], scale, mask=mask,
                                 k2_tile=128)
         _assert_close(t, out[b:b + 1, rows], want, label=f"llama causal prefill head {b}")
+
+
+# ---------------------------------------------------------------------------------------
+# `*_dtm`: the tcgen05 prefill kernel without tensor-map parameters (tensormap.replace on the
+# device), i.e. the export an unmodified IREE CUDA driver can launch.
+# ---------------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("causal", [False, True], ids=["unmasked", "causal"])
+@pytest.mark.parametrize("shape", [(1, 256, 256), (3, 384, 640), (2, 200, 300), (5, 768, 768),
+                                   (40, 512, 1024)], ids=str)
+def test_prefill_with_device_built_tensor_maps_is_the_same_kernel(ops, t, causal, shape):
+    """Same bits as the host-fed export (same code after the maps exist), same tolerance
+    against the oracle; more CTAs than SMs, so slots are reused within one launch."""
+    B, M, K2 = shape
+    q, k, v = _random_qkv(t, B, M, K2, 128, seed=5 * M + K2)
+    scale = 1.0 / np.sqrt(128.0)
+    kind = H.ATTENTION_MASK_CAUSAL if causal else H.ATTENTION_MASK_NONE
+    assert _kernel_of(ops, t, B, M, K2, kind, flags=H.ATTENTION_DEVICE_MAPS) == \
+        [f"iree_b200_attention_prefill_{t}_dtm"]
+    got = np.zeros((B, M, 128), dtype=q.dtype)
+    ops.attention_host(t, B, M, 128, K2, 128, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       got.ctypes.data, mask_kind=kind, flags=H.ATTENTION_DEVICE_MAPS)
+    host_fed = np.zeros_like(got)
+    ops.attention_host(t, B, M, 128, K2, 128, scale, q.ctypes.data, k.ctypes.data, v.ctypes.data,
+                       host_fed.ctypes.data, mask_kind=kind, flags=H.ATTENTION_NO_TAIL_SPLIT)
+    assert np.array_equal(got, host_fed)
+    want = oracle.attention(t, q, k, v, scale, mask=_causal(B, M, K2) if causal else None, k2_tile=128)
+    _assert_close(t, got, want, label=f"dtm prefill {shape}")

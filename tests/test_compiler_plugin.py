@@ -72,3 +72,29 @@ def test_count_regions_match_host_selection():
     one_cta = text[text.index('hal.dispatch.extern "iree_b200_matmul_bf16_f32_1cta"'):]
     one_cta = one_cta[:one_cta.index("hal.return")]
     assert "%tile_m = arith.constant 128" in one_cta and "%g = arith.constant 1" in one_cta
+
+
+def test_stock_driver_spec_uses_only_recipe_free_exports():
+    """--stock-driver: every dispatched kernel is a `*_dtm` export (no `__tma` recipe, the
+    plain custom-dispatch ABI), so the compiled module needs no driver hook."""
+    build.build()
+    text = gen_spec.generate(os.path.join(ROOT, "iree_b200", "_build"), stock_driver=True)
+    for open_c, close_c in ("{}", "()", "[]"):
+        assert text.count(open_c) == text.count(close_c), open_c
+    with open(os.path.join(ROOT, "iree_b200", "_build", "exports.json")) as f:
+        exports = {e["name"]: e for e in json.load(f)["exports"]}
+    dispatched = set(re.findall(r'hal\.dispatch\.extern "(\w+)"', text))
+    assert len(dispatched) == 8         # 3 types x {2-CTA, 1-CTA} matmul + 2 attention
+    for name in dispatched:
+        assert "_dtm" in name, name
+        e = exports[name]
+        assert e["constants"] == 5
+        assert e["module"] in ("gemm_dtm_kernels", "attention_kernels")
+    from iree_b200 import hal as H
+    ops = H.Ops.offline(148)
+    for name in dispatched:
+        info = ops.executable.export_info(ops.executable.lookup(name))
+        assert info["tma_map_count"] == 0, name
+    matchers = re.findall(r"named_sequence @(match_\w+)", text)
+    for m in matchers:
+        assert f"@{m} -> @rewrite_{m[len('match_'):]}" in text

@@ -80,6 +80,28 @@ def test_every_kernel_family(ops, t, family, nt, shape):
     assert np.array_equal(out, want)
 
 
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("family", ["1cta", "2cta"])
+@pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
+@pytest.mark.parametrize("shape", TILED + [(4, 512, 384, 640, False)],
+                         ids=lambda s: "x".join(str(v) for v in s))
+def test_device_built_tensor_maps(ops, t, family, nt, shape):
+    """`*_dtm` exports (FLAG_DEVICE_MAPS): the tcgen05 GEMM with no tensor-map parameters — it
+    patches host-encoded templates with tensormap.replace — i.e. what an unmodified IREE CUDA
+    driver can launch. Same bits as the oracle, every family, ragged tiles, batch, accumulate;
+    back-to-back launches with different shapes reuse the per-CTA slots."""
+    batch, (M, K, N, accumulate) = (shape[0], shape[1:]) if len(shape) == 5 else (1, shape)
+    es = elem_size(t)
+    if (K * es) % 16 or (N * 4) % 16 or (not nt and (N * es) % 16):
+        pytest.skip("shape does not satisfy the TMA guards (goes to the generic kernel)")
+    flag = {"1cta": H.MATMUL_FORCE_1CTA, "2cta": H.MATMUL_FORCE_2CTA}[family] | H.MATMUL_DEVICE_MAPS
+    sel = ops.select_matmul(t, batch, M, N, K, flags=flag | (H.MATMUL_TRANSPOSE_RHS if nt else 0))
+    info = ops.executable.export_info(sel["export_ordinal"])
+    assert "_dtm" in info["kernel_name"] and info["tma_map_count"] == 0
+    out, want = _run(ops, t, batch, M, N, K, flags=flag, accumulate=accumulate, nt=nt)
+    assert np.array_equal(out, want)
+
+
 @pytest.mark.parametrize("t", ["i8", "bf16", "f8e4m3fn"])
 @pytest.mark.parametrize("bshape", [(32, 128, 128, 128), (32, 256, 64, 256), (32, 96, 96, 96),
                                     (3, 300, 136, 520)], ids=str)

@@ -139,6 +139,29 @@ def test_stock_reference_driver_runs_the_generic_matmul(ops, hal, tmp_path, t, s
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("t,shape,flags", [
+    ("bf16", (512, 512, 512), 0), ("i8", (1000, 272, 528), 0), ("f16", (384, 768, 1024), 0),
+    ("bf16", (2048, 1280, 2048), 0), ("i8", (4096, 512, 2048), "nt")])
+def test_stock_reference_driver_runs_the_tcgen05_matmul_with_device_built_maps(ops, hal, tmp_path, t,
+                                                                               shape, flags):
+    """The `*_dtm` exports: tcgen05 + TMA kernels that build their tensor maps on the device
+    (tensormap.replace on host-encoded templates), so the UNMODIFIED reference driver — binding
+    pointers and push constants only — launches them. Bit-exact."""
+    M, K, N = shape
+    nt = flags == "nt"
+    sel = ops.select_matmul(t, 1, M, N, K, flags=hal.MATMUL_DEVICE_MAPS |
+                            (hal.MATMUL_TRANSPOSE_RHS if nt else 0))
+    info = ops.executable.export_info(sel["export_ordinal"])
+    assert "_dtm" in info["kernel_name"] and info["tma_map_count"] == 0
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    raw, _ = run_harness("stock", tmp_path, sel["export_ordinal"], sel["workgroup_count"],
+                         sel["constants"], [lhs, np.ascontiguousarray(rhs.T) if nt else rhs, M * N * 4], 2)
+    out = raw.view(np.int32 if t == "i8" else np.float32).reshape(M, N)
+    assert np.array_equal(out, oracle.matmul(t, lhs, rhs))
+
+
+@pytest.mark.gpu
 def test_stock_reference_driver_runs_the_decode_cluster_attention(ops, hal, tmp_path):
     """One-dispatch split-KV decode: 8-CTA clusters + 1-D bulk copies, no tensor map, so the
     unmodified reference driver's cuLaunchKernel is enough."""
@@ -193,3 +216,27 @@ def test_patched_reference_driver_runs_the_tcgen05_prefill_attention(ops, hal, t
     got = oracle.to_f32("f16", raw.view(np.uint16).reshape(B, M, D))
     want = oracle.to_f32("f16", oracle.attention("f16", q, k, v, scale, k2_tile=128))
     assert np.abs(got - want).max() <= 2e-3 * np.abs(want).max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("t,causal", [("f16", False), ("bf16", True)])
+def test_stock_reference_driver_runs_the_tcgen05_prefill_attention(ops, hal, tmp_path, t, causal):
+    """`iree_b200_attention_prefill_*_dtm`: the tcgen05 prefill kernel building its Q / K / V
+    tensor maps on the device, launched by the UNMODIFIED reference driver."""
+    B, M, K2, D = 3, 640, 640, 128
+    g = np.random.Generator(np.random.PCG64(0xB200))
+    mk = lambda *s: oracle.from_f32(t, np.clip(g.standard_normal(s), -4, 4).astype(np.float32))
+    q, k, v = mk(B, M, D), mk(B, K2, D), mk(B, K2, D)
+    scale = 1.0 / np.sqrt(D)
+    sel = ops.select_attention(t, B, M, D, K2, D, scale, flags=hal.ATTENTION_DEVICE_MAPS,
+                               mask_kind=hal.ATTENTION_MASK_CAUSAL if causal else hal.ATTENTION_MASK_NONE)
+    assert len(sel["dispatches"]) == 1
+    d = sel["dispatches"][0]
+    info = ops.executable.export_info(d["export_ordinal"])
+    assert info["kernel_name"] == f"iree_b200_attention_prefill_{t}_dtm" and info["tma_map_count"] == 0
+    raw, _ = run_harness("stock", tmp_path, d["export_ordinal"], d["workgroup_count"],
+                         d["constants"], [q, k, v, B * M * D * 2], 3)
+    got = oracle.to_f32(t, raw.view(np.uint16).reshape(B, M, D))
+    mask = np.tril(np.ones((M, K2), dtype=bool))[None].repeat(B, 0) if causal else None
+    want = oracle.to_f32(t, oracle.attention(t, q, k, v, scale, k2_tile=128, mask=mask))
+    assert np.abs(got - want).max() <= (2e-2 if t == "bf16" else 2e-3) * np.abs(want).max()

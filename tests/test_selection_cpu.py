@@ -150,3 +150,38 @@ def test_spec_count_regions_restate_the_host_selection(ops, family, flag, g):
                 want = min(-(-M // tile_m) * -(-N // tile_n) * batch * group, sms)
                 got = ops.select_matmul("bf16", batch, M, N, 512, flags=flag)
                 assert got["workgroup_count"] == [want, 1, 1], (batch, M, N)
+
+
+def test_device_map_exports_are_selected_only_where_they_exist(ops):
+    """FLAG_DEVICE_MAPS: the recipe-free twins of the tcgen05 kernels (what a stock IREE CUDA
+    driver can launch) — same grids and constants as the host-fed exports."""
+    for t, acc in (("bf16", "f32"), ("f16", "f32"), ("i8", "i32")):
+        for flags, nt in ((0, ""), (H.MATMUL_TRANSPOSE_RHS, "nt_")):
+            big = ops.select_matmul(t, 1, 8192, 8192, 8192, flags=flags | H.MATMUL_DEVICE_MAPS)
+            ref = ops.select_matmul(t, 1, 8192, 8192, 8192, flags=flags)
+            assert _name(ops, big) == f"iree_b200_matmul_{nt}{t}_{acc}_dtm"
+            assert big["workgroup_count"] == ref["workgroup_count"] == [148, 1, 1]
+            assert big["constants"] == ref["constants"]
+            small = ops.select_matmul(t, 1, 256, 512, 128, flags=flags | H.MATMUL_DEVICE_MAPS)
+            assert _name(ops, small) == f"iree_b200_matmul_{nt}{t}_{acc}_dtm_1cta"
+            info = ops.executable.export_info(big["export_ordinal"])
+            assert info["tma_map_count"] == 0 and info["constant_count"] == 5
+    for bad in (dict(t="f8e4m3fn", flags=H.MATMUL_DEVICE_MAPS),
+                dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS | H.MATMUL_TRUNCATE_RESULT),
+                dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS | H.MATMUL_FORCE_GENERIC),
+                dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS, N=1001)):      # fails the TMA guards
+        with pytest.raises(H.Status) as e:
+            ops.select_matmul(bad["t"], 1, 1024, bad.get("N", 1024), 1024, flags=bad["flags"])
+        assert e.value.name == "INVALID_ARGUMENT"
+    for t in ("f16", "bf16"):
+        for kind, grid in ((H.ATTENTION_MASK_NONE, [16, 32, 1]), (H.ATTENTION_MASK_CAUSAL, [512, 1, 1])):
+            sel = ops.select_attention(t, 32, 4096, 128, 4096, 128, 0.088, mask_kind=kind,
+                                       flags=H.ATTENTION_DEVICE_MAPS)
+            (d,) = sel["dispatches"]
+            assert ops.executable.export_info(d["export_ordinal"])["kernel_name"] == \
+                f"iree_b200_attention_prefill_{t}_dtm"
+            assert d["workgroup_count"] == grid and sel["workspace_bytes"] == 0
+            assert d["constants"][4] == (1 if kind == H.ATTENTION_MASK_CAUSAL else 0)
+    with pytest.raises(H.Status):
+        ops.select_attention("f16", 2, 512, 128, 512, 128, 0.088, mask_kind=H.ATTENTION_MASK_BOOL,
+                             flags=H.ATTENTION_DEVICE_MAPS)

@@ -4,7 +4,8 @@
 runtime built by tools/build_ref_runtime.sh, loading iree_b200_kernels.cda1 with the reference's
 own loader and launching through its stream command buffer.
 
-  stock/  unmodified driver  -> recipe-free exports (decode-cluster attention, generic matmul)
+  stock/  unmodified driver  -> recipe-free exports: the `*_dtm` tcgen05 GEMMs (tensor maps built
+          on the device; bf16 / i8 8192^3), decode-cluster attention, generic matmul
   tma/    driver + integration/cuda_driver_tma.patch -> the tcgen05 exports (bf16 / i8 8192^3,
           prefill attention)
 
@@ -84,6 +85,14 @@ def main():
                   sel["constants"],
                   [f"{M}x{K}xi8=@{i8_file('ai.bin', (M, K))}", f"{K}x{N}xi8=@{i8_file('bi.bin', (K, N))}",
                    f"{M}x{N}xi32"], 20, 2.0 * M * N * K, None))
+    # The same two GEMMs through the UNMODIFIED driver: device-built tensor maps.
+    for t, acc in (("bf16", "f32"), ("i8", "i32")):
+        sel = ops.select_matmul(t, 1, M, N, K, flags=H.MATMUL_DEVICE_MAPS)
+        a, b = ("a.bin", "b.bin") if t == "bf16" else ("ai.bin", "bi.bin")
+        cases.append(("stock", f"matmul_{t}_8192_device_maps", sel["export_ordinal"],
+                      sel["workgroup_count"], sel["constants"],
+                      [f"{M}x{K}x{t}=@{os.path.join(tmp, a)}", f"{K}x{N}x{t}=@{os.path.join(tmp, b)}",
+                       f"{M}x{N}x{acc}"], 20, 2.0 * M * N * K, None))
     B, Mq, K2, D = 32, 4096, 4096, 128
     sel = ops.select_attention("f16", B, Mq, D, K2, D, 1.0 / D ** 0.5, flags=H.ATTENTION_NO_TAIL_SPLIT)
     d = sel["dispatches"][0]
@@ -92,6 +101,14 @@ def main():
                   [f"{B}x{Mq}x{D}xf16=@{f16_file('q.bin', (B, Mq, D))}",
                    f"{B}x{K2}x{D}xf16=@{f16_file('k.bin', (B, K2, D))}",
                    f"{B}x{K2}x{D}xf16=@{f16_file('v.bin', (B, K2, D))}", f"{B}x{Mq}x{D}xf16"],
+                  20, 4.0 * B * Mq * K2 * D, None))
+    sel = ops.select_attention("f16", B, Mq, D, K2, D, 1.0 / D ** 0.5, flags=H.ATTENTION_DEVICE_MAPS)
+    d = sel["dispatches"][0]
+    cases.append(("stock", "attention_prefill_f16_device_maps", d["export_ordinal"], d["workgroup_count"],
+                  d["constants"],
+                  [f"{B}x{Mq}x{D}xf16=@{os.path.join(tmp, 'q.bin')}",
+                   f"{B}x{K2}x{D}xf16=@{os.path.join(tmp, 'k.bin')}",
+                   f"{B}x{K2}x{D}xf16=@{os.path.join(tmp, 'v.bin')}", f"{B}x{Mq}x{D}xf16"],
                   20, 4.0 * B * Mq * K2 * D, None))
     B, Mq, K2 = 32, 1, 8192
     sel = ops.select_attention("f16", B, Mq, D, K2, D, 1.0 / D ** 0.5)
