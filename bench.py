@@ -228,10 +228,15 @@ def synth_matmul_inputs(torch, et, batch, M, N, K, seed):
 class MatmulStep:
     """One recorded command buffer holding the workload's dispatch; step() replays it."""
 
-    def __init__(self, torch, hal, dev, ops, spec, seed, fused=False):
+    def __init__(self, torch, hal, dev, ops, spec, seed, fused=False, mode=None):
+        """|mode| (the "also" lines): "device_maps" = the `*_dtm` export, which builds its tensor
+        maps on the device (what an unmodified IREE CUDA driver can launch); "mmt4d" = the same
+        contraction as linalg.mmt4d on 16x16xK0 data tiles, read directly by the tcgen05 GEMM
+        (operand bytes are synthetic, so the row-major tensors double as tiled ones)."""
         op, et, batch, M, N, K = spec
         self.spec = spec
         self.fused = fused
+        self.mode = mode
         self.tensors = synth_matmul_inputs(torch, et, batch, M, N, K, seed)
         if fused:   # result in the operand type, plus the bias vector
             a, b, _ = self.tensors
@@ -246,9 +251,14 @@ class MatmulStep:
             ops.record_matmul_bias(self.cb, et, batch, M, N, K, self.buffers[0].ref(),
                                    self.buffers[1].ref(), self.buffers[3].ref(),
                                    self.buffers[2].ref(), flags=self.flags)
+        elif mode == "mmt4d":
+            k0 = 16 // (2 if et in ("f16", "bf16") else 1)
+            ops.record_mmt4d(self.cb, et, M // 16, N // 16, K // k0, 16, 16, k0,
+                             self.buffers[0].ref(), self.buffers[1].ref(), self.buffers[2].ref())
         else:
             ops.record_matmul(self.cb, et, batch, M, N, K, self.buffers[0].ref(),
-                              self.buffers[1].ref(), self.buffers[2].ref())
+                              self.buffers[1].ref(), self.buffers[2].ref(),
+                              flags=hal.MATMUL_DEVICE_MAPS if mode == "device_maps" else 0)
         self.cb.end()
         self.launches_per_step = ops.dispatch_count - before
         self.dev = dev
@@ -287,6 +297,11 @@ class MatmulStep:
                     "h2d": int(batch * (M * K + K * N) * es + N * 4),
                     "d2h": int(batch * M * N * out_es),
                     "api": "iree_b200_ops_matmul_bias_host (pinned host buffers)"}
+        if self.mode == "mmt4d":
+            k0 = 16 // es
+            op = f"mmt4d (tiles 16x16x{k0}, read directly through rank-4 tensor maps)"
+        elif self.mode == "device_maps":
+            op += " (tensor maps built on the device: the stock-driver ABI)"
         return {"flop": flop, "bytes": nbytes, "bound": "tensor",
                 "workload": f"linalg.{op} {et} batch={batch} M={M} N={N} K={K} per GPU",
                 "dtype": {"bf16": "bf16 (f32 accumulate)", "f16": "f16 (f32 accumulate)",
@@ -721,6 +736,22 @@ def also_lines(torch, hal, dev, ops, stream, args, peaks):
                      "ms_per_step": ms, "steps": steps_n, "timed_region_ms": ms * steps_n,
                      "dtype": info["dtype"],
                      "launches_per_step": works[0].launches_per_step,
+                     "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "unit", "frac")}}
+        del works
+        torch.cuda.empty_cache()
+    # The headline contraction through the two other doors of the boundary: the export an
+    # unmodified IREE CUDA driver launches, and linalg.mmt4d on data-tiled operands.
+    for name, mode in (("matmul_bf16_device_maps", "device_maps"), ("mmt4d_bf16", "mmt4d")):
+        works = rotating_sets(lambda i: MatmulStep(torch, hal, dev, ops, MATMUL_WORKLOADS["matmul_bf16"],
+                                                   100 * i, mode=mode),
+                              lambda w: w.describe()["bytes"])
+        ms, steps_n = time_steps(torch, works, steps, warmup, stream, 1, min_ms=max(args.extra_min_ms, 1.0))
+        info = works[0].describe()
+        tflops = info["flop"] / (ms * 1e-3) / 1e12
+        roof = roofline_of(info, tflops, ms, peaks)
+        out[name] = {"workload": info["workload"], "value": tflops, "unit": "TFLOP/s",
+                     "ms_per_step": ms, "steps": steps_n, "timed_region_ms": ms * steps_n,
+                     "dtype": info["dtype"], "launches_per_step": works[0].launches_per_step,
                      "roofline": {k: roof[k] for k in ("bound", "achieved", "peak", "unit", "frac")}}
         del works
         torch.cuda.empty_cache()
