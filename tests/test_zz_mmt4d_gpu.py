@@ -61,7 +61,7 @@ def _direct(t, M1, N1, K1, M0, N0, K0):
 @pytest.mark.parametrize("case", [
     # M, K, N (logical), M0, N0, accumulate   (K0 = 16 bytes / element size)
     (128, 128, 128, 16, 16, False), (1000, 528, 272, 16, 16, False), (300, 256, 520, 8, 32, True),
-    (257, 1032, 260, 32, 64, False), (2048, 2048, 2048, 16, 16, True), (4096, 512, 1024, 128, 8, False),
+    (257, 1032, 260, 32, 64, False), (2048, 256, 2560, 16, 16, True), (4096, 512, 1024, 128, 8, False),
     (520, 384, 1000, 64, 128, True),
 ], ids=str)
 def test_mmt4d_tiles_read_directly_by_the_tcgen05_gemm(ops, t, case):
