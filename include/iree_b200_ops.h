@@ -335,6 +335,30 @@ IREE_B200_API iree_b200_status_t iree_b200_ops_attention_host(
     int64_t N, float scale, int32_t mask_kind, uint32_t flags, const void* q, const void* k,
     const void* v, const void* mask, void* out);
 
+// Split-KV decode attention (K1 == N == 128, no mask; f16 / bf16) for callers that cannot
+// allocate. NO COUNTERPART IN THE REFERENCE —
+// code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc
+// need an entry point that allocates nothing. The partial softmax records the split and merge
+// kernels exchange live in a static device array of IREE_B200_NO_ALLOC_SCRATCH_BYTES inside
+// the library (every GPU that loads the library holds it until the process exits); the call
+// makes no cudaMalloc / cudaFree / allocating library call, takes no ops object and no arena.
+//   q [B, M, 128], k, v [B, K2, 128], out [B, M, 128]: DEVICE pointers on |device_ordinal|
+//   (primary context), 16-byte aligned; |stream| a CUstream / cudaStream_t of that device
+//   (NULL = the default stream). Asynchronous: the two kernels are queued on |stream|.
+// Same kernels and split count as the split + merge form of iree_b200_ops_select_attention:
+// results are bit-identical to iree_b200_ops_attention_host(..., FLAG_FORCE_DECODE_SPLIT).
+// RESOURCE_EXHAUSTED when B * M * splits records of 520 bytes exceed the array (splits =
+// min(ceil(K2 / 256), max(1, 8 * SMs / (B * M)))), e.g. B * M > 8065 rows.
+// All calls on a device share the one array, which keeps the last call's contents (nothing
+// needs clearing: every record read is written first): calls that overlap on the GPU RACE —
+// keep them on one stream or order them with events. The first call per device does the
+// one-time set-up (cudaGetSymbolAddress): make it before starting a graph capture.
+// (iree_b200/csrc/no_alloc/attention_decode_no_alloc.cu)
+#define IREE_B200_NO_ALLOC_SCRATCH_BYTES (4u << 20)
+IREE_B200_API iree_b200_status_t iree_b200_attention_decode_no_alloc(
+    int32_t device_ordinal, int32_t element_type, int64_t B, int64_t M, int64_t K2, float scale,
+    const void* q, const void* k, const void* v, void* out, void* stream);
+
 #ifdef __cplusplus
 }  // extern "C"
 #endif

@@ -139,6 +139,17 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
         _run([cxx, *CXX_FLAGS, "-I", INCLUDE, "-I", cuda_inc, "-c", "-o", dst, src])
         return dst
 
+    def compile_no_alloc():
+        # The one nvcc OBJECT (not cubin) of the library: a static __device__ scratch array and
+        # its cudaGetSymbolAddress need the runtime's module registration; cudart is linked
+        # statically and loads libcuda lazily, so the library still loads without a GPU.
+        src = os.path.join(CSRC, "no_alloc", "attention_decode_no_alloc.cu")
+        dst = os.path.join(OUT, "attention_decode_no_alloc.o")
+        _run([nvcc, *[f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")], "-I", INCLUDE,
+              "--cudart", "static", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-c", "-o", dst, src],
+             "attention_decode_no_alloc.nvcc.log")
+        return dst
+
     def manifest():
         tool = os.path.join(OUT, "manifest_tool")
         _run([cxx, "-O1", "-std=c++17", "-I", INCLUDE, "-o", tool,
@@ -153,6 +164,7 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
         experimental_futs = [pool.submit(compile_cubin, u) for u in EXPERIMENTAL_UNITS]
         manifest_fut = pool.submit(manifest)
         host_futs = [pool.submit(compile_host, s) for s in HOST_SOURCES]
+        host_futs.append(pool.submit(compile_no_alloc))
         cubins = [f.result() for f in cubin_futs]
         experimental_cubins = [f.result() for f in experimental_futs]
         exports_json = manifest_fut.result()
@@ -194,7 +206,8 @@ def build(force: bool = False, jobs: int = 0, verbose: bool = False) -> str:
                 '.section .note.GNU-stack,"",@progbits\n' % (cda1_path(), experimental_path))
     blob_o = os.path.join(OUT, "builtin_blob.o")
     _run([cxx, "-c", "-o", blob_o, blob_s])
-    _run([cxx, "-shared", "-o", lib_path(), *objects, blob_o, "-ldl", "-lpthread"])
+    _run([cxx, "-shared", "-o", lib_path(), *objects, blob_o,
+          "-L", os.path.join(_cuda_home(), "lib64"), "-lcudart_static", "-lrt", "-ldl", "-lpthread"])
 
     with open(os.path.join(OUT, "stamp"), "w") as f:
         f.write(_tree_hash(_sources()))

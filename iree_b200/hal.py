@@ -207,6 +207,9 @@ _STATUS_FUNCS = {
     "iree_b200_ops_attention_host": [c_void_p, c_int32, c_int64, c_int64, c_int64, c_int64,
                                      c_int64, ctypes.c_float, c_int32, c_uint32, c_void_p,
                                      c_void_p, c_void_p, c_void_p, c_void_p],
+    "iree_b200_attention_decode_no_alloc": [c_int32, c_int32, c_int64, c_int64, c_int64,
+                                            ctypes.c_float, c_void_p, c_void_p, c_void_p, c_void_p,
+                                            c_void_p],
 }
 
 _OTHER_FUNCS = {
@@ -280,6 +283,19 @@ def check(status: int):
 
 def _ptr(obj):
     return obj._h if obj is not None else None
+
+
+NO_ALLOC_SCRATCH_BYTES = 4 << 20   # IREE_B200_NO_ALLOC_SCRATCH_BYTES
+
+
+def attention_decode_no_alloc(device_ordinal: int, element_type, B, M, K2, scale, q_ptr: int,
+                              k_ptr: int, v_ptr: int, out_ptr: int, stream: int = 0):
+    """iree_b200_attention_decode_no_alloc: split-KV decode attention on DEVICE pointers whose
+    scratch is a static device array inside the library — no allocation anywhere in the call.
+    Asynchronous on |stream| (a CUstream / cudaStream_t handle; 0 = the default stream)."""
+    check(lib().iree_b200_attention_decode_no_alloc(
+        device_ordinal, _etype(element_type), B, M, K2, scale, q_ptr or None, k_ptr or None,
+        v_ptr or None, out_ptr or None, stream or None))
 
 
 class Buffer:
