@@ -2,7 +2,9 @@
 # Builds the REFERENCE runtime from /root/reference (CPU box, offline, ~1-4 min on 8 cores) in
 # two flavours and leaves binaries only under oracle/_ref/iree-rt/ (git-ignored, shipped to
 # the GPU box by gpurun):
-#   stock/  the unmodified checkout: iree-benchmark-executable, iree-run-module, plus our two
+#   stock/  the unmodified checkout: iree-benchmark-executable, iree-run-module,
+#           iree-benchmark-module, iree-as-module (the VM assembler: iree_b200/vmasm.py turns our
+#           kernels into a real .vmfb with it), iree-dump-module, plus our two
 #           checkers linked against it (integration/ref_runtime/): cda1_ref_verify (the
 #           reference's flatcc verifier + header parser on a CDA1 file, CPU only) and
 #           ref_hal_harness (one dispatch through iree_hal_* with file-backed bindings).
@@ -16,7 +18,7 @@ REF="${IREE_B200_REFERENCE_DIR:-/root/reference}"
 WORK="${IREE_B200_REF_BUILD_DIR:-/tmp/iree_b200_ref_rt}"
 OUT="$ROOT/oracle/_ref/iree-rt"
 [ -d "$REF/runtime/src/iree/hal/drivers/cuda" ] || { echo "no reference checkout at $REF"; exit 3; }
-TARGETS="ref_hal_harness cda1_ref_verify iree-benchmark-executable iree-run-module"
+TARGETS="ref_hal_harness cda1_ref_verify iree-benchmark-executable iree-run-module iree-as-module iree-benchmark-module iree-dump-module"
 
 build() {  # <flavour> <source dir>
   local flavour="$1" src="$2" b="$WORK/$1"
@@ -26,7 +28,8 @@ build() {  # <flavour> <source dir>
   ninja -C "$b" $TARGETS > "$b/ninja.log" 2>&1 || { tail -40 "$b/ninja.log"; exit 1; }
   mkdir -p "$OUT/$flavour"
   cp "$b/ref_hal_harness" "$b/cda1_ref_verify" "$b/iree/tools/iree-benchmark-executable" \
-     "$b/iree/tools/iree-run-module" "$OUT/$flavour/"
+     "$b/iree/tools/iree-run-module" "$b/iree/tools/iree-as-module" \
+     "$b/iree/tools/iree-benchmark-module" "$b/iree/tools/iree-dump-module" "$OUT/$flavour/"
   strip "$OUT/$flavour"/* || true
 }
 
