@@ -96,7 +96,10 @@ def test_world_size_2_gloo():
     world = 2
     with tempfile.TemporaryDirectory() as tmp, mp.Manager() as manager:
         results = manager.dict()
-        port = 29600 + os.getpid() % 300
+        import socket
+        with socket.socket() as sock:      # a port the kernel says is free right now
+            sock.bind(("127.0.0.1", 0))
+            port = sock.getsockname()[1]
         # Leftovers of an "earlier run": a well-formed id file for exchanges #0 and #1 with
         # someone else's id and tokens, a stale hello and a stale ack of rank 1.
         import struct
