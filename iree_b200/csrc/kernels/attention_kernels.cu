@@ -71,6 +71,8 @@ B200_PREFILL(iree_b200_attention_prefill_bf16_p50, true, 2)
 #include "tensormap_templates.inc"
 #undef B200_TENSORMAP_TEMPLATE
 __device__ __align__(128) TensorMap iree_b200_attention_dtm_slots[kTensorMapSlotSms][4];
+static_assert(PrefillCfg::kSmemBytes > 232448 / 2 && PrefillCfg::kTmemCols == 512,
+              "per-SM tensor-map slots need one resident CTA per SM");
 
 #define B200_PREFILL_DTM(NAME, TEMPLATE_OF, BF16)                                              \
   extern "C" __global__ void __launch_bounds__(PrefillCfg::kThreads, 1)                        \

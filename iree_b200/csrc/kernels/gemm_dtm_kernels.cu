@@ -47,8 +47,10 @@ __device__ __forceinline__ void build_gemm_maps(TensorMap* slots, TensorMap* sta
   tensormap_build_rank3(slots + 2, staging + 2, tmpl[2], out, N, M, batch, 4);
 }
 
+// One CTA per SM (what makes the per-SM slots safe): more than half the SM's shared memory.
 #define X(NAME, TEMPLATE_OF, CLUSTER, ...)                                                     \
   using NAME##_cfg = GemmConfig<__VA_ARGS__>;                                                  \
+  static_assert(NAME##_cfg::kSmemBytes > 232448 / 2, "per-SM tensor-map slots need 1 CTA/SM"); \
   extern "C" __global__ void B200_CLUSTER_ATTR_##CLUSTER __launch_bounds__(256, 1)             \
       NAME(const void* __restrict__ lhs, const void* __restrict__ rhs, void* __restrict__ out, \
            int M, int N, int K, int batch, int flags) {                                        \

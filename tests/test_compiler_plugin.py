@@ -98,3 +98,30 @@ def test_stock_driver_spec_uses_only_recipe_free_exports():
     matchers = re.findall(r"named_sequence @(match_\w+)", text)
     for m in matchers:
         assert f"@{m} -> @rewrite_{m[len('match_'):]}" in text
+
+
+def test_known_target_patch_applies_to_the_reference(tmp_path):
+    """integration/known_targets_sm100.patch (the sm_100a / b200 entry of SURVEY §8(f) rank 4)
+    applies cleanly to the reference's KnownTargets.cpp, and the new WgpDetails initialiser has
+    the shape of its sm_120 neighbour (it cannot be compiled here: no LLVM tree)."""
+    import shutil
+    import subprocess
+    rel = "compiler/src/iree/compiler/Codegen/Dialect/GPU/TargetUtils/KnownTargets.cpp"
+    src = os.path.join("/root/reference", rel)
+    if not os.path.exists(src):
+        import pytest
+        pytest.skip("no reference checkout")
+    dst = tmp_path / rel
+    dst.parent.mkdir(parents=True)
+    shutil.copy(src, dst)
+    patch = os.path.join(ROOT, "integration", "known_targets_sm100.patch")
+    subprocess.run(["patch", "-s", "-p1", "-d", str(tmp_path)], stdin=open(patch), check=True)
+    text = dst.read_text()
+    body = lambda name: text[text.index(f"*get{name}WgpDetails() {{"):].split("\n}\n")[0]
+    new, old = body("SM100"), body("SM120")
+    assert new.count(",") == old.count(",") and new.count("MMAIntrinsic::") == old.count("MMAIntrinsic::")
+    assert "227 * 1024" in new and "b200Chip = {148}" in text
+    assert '.Cases({"b200", "sm_100", "sm_100a"}, TargetDetails{sm100Wgp, &b200Chip})' in text
+    assert '.Case("b200", "sm_100a")' in text
+    for open_c, close_c in ("{}", "()"):
+        assert text.count(open_c) == text.count(close_c)
