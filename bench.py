@@ -495,12 +495,19 @@ def make_step(torch, hal, dev, ops, workload, seed):
                          causal=workload in CAUSAL_WORKLOADS)
 
 
+SOAK_MS = 1000.0   # --extra-soak-ms
+
+
 def time_steps(torch, works, steps, warmup, stream, world, sampler=None, min_ms=0.0):
     """|warmup| untimed steps, then exactly |steps| between two CUDA events on |stream|,
     bracketed by barrier + synchronize; returns ms per step, max over ranks. |min_ms| > 0
     (the extra lines only, never the headline): |steps| is raised so that the timed region
-    lasts at least that long — a 20 ms burst runs at 1965 MHz, before the power limiter has
-    settled, and reads 30-40 % above what the same kernel sustains."""
+    lasts at least that long, and the GPU is first soaked with SOAK_MS of the same work,
+    untimed — a 20 ms burst runs at 1965 MHz, before the power limiter has settled, and reads
+    30-40 % above what the same kernel sustains; from a COLD GPU (the first line after the
+    host-link copies) even a 200 ms region stayed at the boost clock on some boxes
+    (batch_matmul 0.63 ms cold vs 0.92-0.94 ms warm), which made T(1) / (N T(N)) depend on
+    the order of the lines."""
     sets = len(works)
     with torch.cuda.stream(stream):
         for i in range(warmup):
@@ -515,6 +522,8 @@ def time_steps(torch, works, steps, warmup, stream, world, sampler=None, min_ms=
             barrier(world)
             pilot = max_over_ranks(p0.elapsed_time(p1), world) / 5
             steps = int(max(steps, min(5000, -(-min_ms // max(pilot, 1e-3)))))
+            for i in range(int(min(20000, SOAK_MS // max(pilot, 1e-3)))):
+                works[i % sets].step()
         barrier(world)
         if sampler is not None:
             sampler.start()
@@ -526,6 +535,26 @@ def time_steps(torch, works, steps, warmup, stream, world, sampler=None, min_ms=
         barrier(world)
     ms = max_over_ranks(ev0.elapsed_time(ev1), world) / steps
     return (ms, steps) if min_ms > 0 else ms
+
+
+def soak(torch, work, stream, world, seconds):
+    """Runs |work| back to back for |seconds| of wall clock, untimed. After seconds of
+    PCIe-bound phases (e2e, host-link copies) a B200 ran the FIRST tensor-bound line at the
+    boost clock for more than 1.4 s before the power limiter pulled it to the sustained clock
+    (batch_matmul 64 x 2048^3: 0.64 ms per step there, 0.93-0.97 ms on every later line and in
+    every isolated run — tools/power_budget_probe.py); with T(1) measured first that read as a
+    strong-scaling efficiency of 0.65 for a split that is 1.00. MEASURED_PEAKS.json's sustained
+    figure is "back to back for 4 s": the extra lines start from the same state."""
+    if seconds <= 0:
+        return
+    barrier(world)
+    t0 = time.perf_counter()
+    with torch.cuda.stream(stream):
+        while time.perf_counter() - t0 < seconds:
+            for _ in range(50):
+                work.step()
+            stream.synchronize()
+    barrier(world)
 
 
 def rotating_sets(make, info_bytes):
@@ -671,6 +700,7 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
     op, et, B, M, N, K = MATMUL_WORKLOADS["batch_matmul"]
     if B % world == 0:
         full = [MatmulStep(torch, hal, dev, ops, (op, et, B, M, N, K), seed=rank)]
+        soak(torch, full[0], stream, world, args.presoak_s)
         t1, _ = time_steps(torch, full, steps, warmup, stream, world, min_ms=MIN)
         del full
         torch.cuda.empty_cache()
@@ -740,6 +770,8 @@ def also_lines(torch, hal, dev, ops, stream, args, peaks):
     for name in ALSO_WORKLOADS:
         works = rotating_sets(lambda i: make_step(torch, hal, dev, ops, name, seed=100 * i),
                               lambda w: w.describe()["bytes"])
+        if name == ALSO_WORKLOADS[0]:
+            soak(torch, works[0], stream, 1, args.presoak_s)
         ms, steps_n = time_steps(torch, works, steps, warmup, stream, 1, min_ms=max(args.extra_min_ms, 1.0))
         info = works[0].describe()
         tflops = info["flop"] / (ms * 1e-3) / 1e12
@@ -1076,6 +1108,11 @@ def main():
                          "all-reduce launch per row-parallel GEMM (1)")
     ap.add_argument("--extra-min-ms", type=float, default=200.0,
                     help="minimum timed region of each `also` / `sharded` line")
+    ap.add_argument("--extra-soak-ms", type=float, default=1000.0,
+                    help="untimed soak of the same work before every extra line's timed region")
+    ap.add_argument("--presoak-s", type=float, default=4.0,
+                    help="seconds of untimed tensor-bound work before the first extra line "
+                         "(burns the boost budget a B200 accumulates while idle)")
     ap.add_argument("--no-extra", action="store_true",
                     help="skip the `also` (N=1) / `sharded` (N>1) lines of the default workload")
     ap.add_argument("--ar-blocks", type=int, default=0,
@@ -1085,6 +1122,8 @@ def main():
     ap.add_argument("--tp-chunks", type=int, default=0,
                     help="tp_decoder_layer: equal token chunks per row-parallel GEMM (0 = auto)")
     args = ap.parse_args()
+    global SOAK_MS
+    SOAK_MS = max(0.0, args.extra_soak_ms)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     _, world, _ = dist_env()
     if world != args.gpus and world == 1 and args.gpus > 1:
