@@ -347,18 +347,17 @@ def attention_rewriter(name: str) -> str:
 
 
 def generate(objects_dir: str, stock_driver: bool = False) -> str:
-    """|stock_driver|: use the `*_dtm` exports (tensor maps built on the device), so the
-    compiled module runs on an UNMODIFIED IREE runtime — no `__tma` recipe, no driver hook.
-    Covers matmul / batch_matmul (bf16, f16, i8) and attention; the f8 and fused-consumer
-    dispatches exist host-fed only and are left to IREE's own codegen in that mode."""
+    """|stock_driver|: use the `*_dtm` twins of every export (tensor maps built on the device),
+    so the compiled module runs on an UNMODIFIED IREE runtime — no `__tma` recipe, no driver
+    hook. Same matchers, same count regions, same layouts."""
     man = load_manifest(objects_dir)
     entries, matchers, rewriters, pairs = [], [], [], []
     dtm = "_dtm" if stock_driver else ""
-    for et in (("bf16", "f16", "i8") if stock_driver else ("bf16", "f16", "i8", "f8e4m3fn", "f8e5m2")):
+    for et in ("bf16", "f16", "i8", "f8e4m3fn", "f8e5m2"):
         acc = ACC_TYPE[et]
         for batched in (False, True):
             for big, suffix, g in ((True, "", 2), (False, "_1cta", 1)):
-                kernel = f"iree_b200_matmul_{et}_{acc}{dtm}{suffix}"
+                kernel = f"iree_b200_matmul_{et}_{acc}{suffix}{dtm}"
                 key = f"{kernel}{'_batch' if batched else ''}"
                 entries.append(matmul_entry(man[kernel], et, batched, g))
                 matchers.append(matmul_matcher(key, et, batched, big))
@@ -368,12 +367,12 @@ def generate(objects_dir: str, stock_driver: bool = False) -> str:
     # Fused consumers first: foreach_match takes the first matcher that succeeds, and the
     # DAG roots (the elementwise generic) are visited independently of the matmul inside.
     linear = []
-    for et in (() if stock_driver else ("bf16", "f16", "i8")):
+    for et in ("bf16", "f16", "i8"):
         for truncate in ((False, True) if et != "i8" else (False,)):
             out_t = MLIR_TYPE[et] if truncate else ACC_TYPE[et]
             for relu in (False, True):
                 for big, suffix, g in ((True, "", 2), (False, "_1cta", 1)):
-                    kernel = f"iree_b200_matmul_bias_{et}_{out_t}{suffix}"
+                    kernel = f"iree_b200_matmul_bias_{et}_{out_t}{suffix}{dtm}"
                     key = f"{kernel}{'_relu' if relu else ''}"
                     entries.append(linear_entry(man[kernel], key, et, relu, truncate, g))
                     matchers.append(linear_matcher(key, et, relu, truncate, big))

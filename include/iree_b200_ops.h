@@ -68,8 +68,8 @@ enum {
   IREE_B200_MATMUL_FLAG_MMT4D_RELAYOUT = 1u << 12,
   // Select the `*_dtm` exports: the same tcgen05 kernels building their tensor maps on the
   // device (tensormap.replace), i.e. the exports an UNMODIFIED IREE CUDA driver can launch —
-  // bindings and push constants only, no `__tma` recipe. i8 / f16 / bf16 with the 32-bit
-  // result; launches of these exports must not overlap in time (gemm_dtm_kernels.cu).
+  // bindings and push constants only, no `__tma` recipe. Every tcgen05 export has such a twin
+  // (all element types, truncating and bias / activation forms; gemm_dtm_kernels.cu).
   IREE_B200_MATMUL_FLAG_DEVICE_MAPS = 1u << 13,
 };
 

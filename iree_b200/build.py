@@ -30,7 +30,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "_build")
 INCLUDE = os.path.join(ROOT, "include")
 
-KERNEL_UNITS = ["gemm_kernels", "gemm_dtm_kernels", "gemm_bias_kernels", "generic_kernels", "attention_kernels", "collective_kernels"]
+KERNEL_UNITS = ["gemm_kernels", "gemm_dtm_kernels", "gemm_bias_kernels", "gemm_bias_dtm_kernels", "generic_kernels", "attention_kernels", "collective_kernels"]
 # Kernels that have not run on a GPU yet: packed into their own executable, which the ops layer
 # loads only when one of their entry points is called (the validated paths never touch it).
 EXPERIMENTAL_UNITS = ["mx_kernels", "mmt4d_kernels"]

@@ -156,7 +156,10 @@ iree_b200_status_t exchange_id(int32_t rank, int32_t count, uint8_t inout_id[IRE
   const auto deadline = std::chrono::steady_clock::now() + std::chrono::seconds(timeout_s);
   auto expired = [&] { return std::chrono::steady_clock::now() >= deadline; };
   auto nap = [] { std::this_thread::sleep_for(std::chrono::milliseconds(2)); };
-  // {magic, seq, count, reserved} + tokens[count] + id.
+  // {magic, seq, count, reserved} + tokens[count] + id. tokens[0] is rank 0's own nonce for
+  // THIS exchange: an acknowledgement must echo it, so that leftover hello + ack files of a
+  // dead run (same sequence number, mutually consistent) cannot complete an exchange for ranks
+  // that have not arrived yet.
   const size_t payload_size = 16 + 8 * (size_t)count + IREE_B200_CHANNEL_ID_SIZE;
   std::vector<uint8_t> payload(payload_size);
 
@@ -176,7 +179,9 @@ iree_b200_status_t exchange_id(int32_t rank, int32_t count, uint8_t inout_id[IRE
         if (head[0] == kIdFileMagic && head[1] == seq && head[2] == (uint32_t)count &&
             published == token) {
           memcpy(inout_id, payload.data() + 16 + 8 * (size_t)count, IREE_B200_CHANNEL_ID_SIZE);
-          if (!write_file_atomically(ack_path(rank), &token, sizeof(token))) {
+          uint64_t ack[2] = {token, 0};
+          memcpy(&ack[1], payload.data() + 16, sizeof(uint64_t));  // rank 0's nonce
+          if (!write_file_atomically(ack_path(rank), ack, sizeof(ack))) {
             return make_status(IREE_B200_STATUS_PERMISSION_DENIED, "cannot write %s",
                                ack_path(rank).c_str());
           }
@@ -195,6 +200,8 @@ iree_b200_status_t exchange_id(int32_t rank, int32_t count, uint8_t inout_id[IRE
   // Rank 0.
   unlink(id_path.c_str());
   std::vector<uint64_t> tokens(count, 0), published(count, 0);
+  const uint64_t nonce = fresh_token();
+  tokens[0] = nonce;
   for (;;) {
     bool all_hello = true, all_acked = true, changed = false;
     for (int r = 1; r < count; ++r) {
@@ -217,8 +224,9 @@ iree_b200_status_t exchange_id(int32_t rank, int32_t count, uint8_t inout_id[IRE
       published = tokens;
     }
     for (int r = 1; r < count; ++r) {
-      uint64_t t = 0;
-      if (!published[r] || !read_file_exactly(ack_path(r), &t, sizeof(t)) || t != published[r]) {
+      uint64_t ack[2] = {0, 0};
+      if (!published[r] || !read_file_exactly(ack_path(r), ack, sizeof(ack)) ||
+          ack[0] != published[r] || ack[1] != nonce) {
         all_acked = false;
       }
     }

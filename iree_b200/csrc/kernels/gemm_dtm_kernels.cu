@@ -37,31 +37,53 @@ __device__ __forceinline__ void build_gemm_maps(TensorMap* slots, TensorMap* sta
                                                 const void* rhs, void* out, int M, int N, int K,
                                                 int batch) {
   // The extents make_gemm_recipe<Cfg>() names: A [batch, M, K]; B [batch, K, N] or
-  // [batch, N, K]; C [batch, M, N] of 32-bit elements.
+  // [batch, N, K]; C [batch, M, N] of 32-bit elements (16-bit for the truncating exports).
   tensormap_build_rank3(slots + 0, staging, tmpl[0], lhs, K, M, batch, Cfg::kElemSize);
   if constexpr (Cfg::kBMajorK) {
     tensormap_build_rank3(slots + 1, staging + 1, tmpl[1], rhs, K, N, batch, Cfg::kElemSize);
   } else {
     tensormap_build_rank3(slots + 1, staging + 1, tmpl[1], rhs, N, K, batch, Cfg::kElemSize);
   }
-  tensormap_build_rank3(slots + 2, staging + 2, tmpl[2], out, N, M, batch, 4);
+  tensormap_build_rank3(slots + 2, staging + 2, tmpl[2], out, N, M, batch, Cfg::kOut16 ? 2 : 4);
 }
 
 // One CTA per SM (what makes the per-SM slots safe): more than half the SM's shared memory.
-#define X(NAME, TEMPLATE_OF, CLUSTER, ...)                                                     \
+// Every host-fed export of gemm_exports.inc gets a twin `<name>_dtm` (B200_DTM_BIAS: the
+// fused bias / activation exports of gemm_bias_exports.inc, gemm_bias_dtm_kernels.cu).
+#if !defined(B200_DTM_BIAS)
+#define X(NAME, CLUSTER, ...)                                                                  \
   using NAME##_cfg = GemmConfig<__VA_ARGS__>;                                                  \
   static_assert(NAME##_cfg::kSmemBytes > 232448 / 2, "per-SM tensor-map slots need 1 CTA/SM"); \
   extern "C" __global__ void B200_CLUSTER_ATTR_##CLUSTER __launch_bounds__(256, 1)             \
-      NAME(const void* __restrict__ lhs, const void* __restrict__ rhs, void* __restrict__ out, \
-           int M, int N, int K, int batch, int flags) {                                        \
+      NAME##_dtm(const void* __restrict__ lhs, const void* __restrict__ rhs,                   \
+                 void* __restrict__ out, int M, int N, int K, int batch, int flags) {          \
     __shared__ __align__(128) TensorMap staging[3];                                            \
-    TensorMap* slots = iree_b200_dtm_slots[tensormap_slot_index()];                                   \
+    TensorMap* slots = iree_b200_dtm_slots[tensormap_slot_index()];                            \
     if ((threadIdx.x >> 5) == 3) {                                                             \
-      build_gemm_maps<NAME##_cfg>(slots, staging, TEMPLATE_OF##__tmt, lhs, rhs, out, M, N, K,  \
-                                  batch);                                                      \
+      build_gemm_maps<NAME##_cfg>(slots, staging, NAME##__tmt, lhs, rhs, out, M, N, K, batch); \
     }                                                                                          \
     gemm_sm100_body<NAME##_cfg, true>(lhs, rhs, out, M, N, K, batch, flags, slots, slots + 1,  \
                                       slots + 2);                                              \
   }
-#include "gemm_dtm_exports.inc"
+#include "gemm_exports.inc"
 #undef X
+#else
+// bindings lhs, rhs, bias (read-only), out; constants M, N, K, batch, flags (bit 1: relu).
+#define X(NAME, CLUSTER, ...)                                                                  \
+  using NAME##_cfg = GemmConfig<__VA_ARGS__>;                                                  \
+  static_assert(NAME##_cfg::kSmemBytes > 232448 / 2, "per-SM tensor-map slots need 1 CTA/SM"); \
+  extern "C" __global__ void B200_CLUSTER_ATTR_##CLUSTER __launch_bounds__(256, 1)             \
+      NAME##_dtm(const void* __restrict__ lhs, const void* __restrict__ rhs,                   \
+                 const void* __restrict__ bias, void* __restrict__ out, int M, int N, int K,   \
+                 int batch, int flags) {                                                       \
+    __shared__ __align__(128) TensorMap staging[3];                                            \
+    TensorMap* slots = iree_b200_dtm_slots[tensormap_slot_index()];                            \
+    if ((threadIdx.x >> 5) == 3) {                                                             \
+      build_gemm_maps<NAME##_cfg>(slots, staging, NAME##__tmt, lhs, rhs, out, M, N, K, batch); \
+    }                                                                                          \
+    gemm_sm100_body<NAME##_cfg, true>(lhs, rhs, out, M, N, K, batch, flags, slots, slots + 1,  \
+                                      slots + 2, bias);                                        \
+  }
+#include "gemm_bias_exports.inc"
+#undef X
+#endif

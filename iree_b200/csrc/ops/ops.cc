@@ -76,7 +76,9 @@ struct iree_b200_ops_t {
   int32_t sm_count = 0;  // device->sm_count, or the caller's for an offline (selection-only) object
   // [element_type][transpose_rhs][family] → export ordinal (-1 if absent)
   int32_t matmul_exports[6][2][kFamilyCount];
-  int32_t matmul_dtm_exports[6][2][kFamilyCount];    // tensor maps built on the device
+  // The `_dtm` twins (tensor maps built on the device): [0] plain, [1] truncating,
+  // [2] bias, [3] bias + truncating.
+  int32_t matmul_dtm_exports[4][6][2][kFamilyCount];
   int32_t matmul_trunc_exports[6][2][kFamilyCount];  // truncating epilogue (f16 / bf16)
   int32_t matmul_bias_exports[6][2][kFamilyCount];        // bias / activation epilogue
   int32_t matmul_bias_trunc_exports[6][2][kFamilyCount];  // ... then truncation
@@ -118,15 +120,15 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
     for (int nt = 0; nt < 2; ++nt) {
       for (int f = 0; f < kFamilyCount; ++f) {
         ops->matmul_exports[t][nt][f] = ops->matmul_trunc_exports[t][nt][f] = -1;
-        ops->matmul_dtm_exports[t][nt][f] = -1;
+        for (int v = 0; v < 4; ++v) ops->matmul_dtm_exports[v][t][nt][f] = -1;
         ops->matmul_bias_exports[t][nt][f] = ops->matmul_bias_trunc_exports[t][nt][f] = -1;
       }
       if (!kTypeSuffix[t]) continue;
       const std::string base = std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTypeSuffix[t];
       ops->matmul_exports[t][nt][kFamily2Cta] = lookup(ops->executable, base);
       ops->matmul_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta");
-      ops->matmul_dtm_exports[t][nt][kFamily2Cta] = lookup(ops->executable, base + "_dtm");
-      ops->matmul_dtm_exports[t][nt][kFamily1Cta] = lookup(ops->executable, base + "_dtm_1cta");
+      ops->matmul_dtm_exports[0][t][nt][kFamily2Cta] = lookup(ops->executable, base + "_dtm");
+      ops->matmul_dtm_exports[0][t][nt][kFamily1Cta] = lookup(ops->executable, base + "_1cta_dtm");
       ops->matmul_exports[t][nt][kFamilyGeneric] =
           lookup(ops->executable, std::string("iree_b200_matmul_generic_") + kTypeSuffix[t]);
       if (t <= IREE_B200_ELEMENT_TYPE_BF16) {  // i8, f16, bf16
@@ -136,6 +138,9 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
         ops->matmul_bias_exports[t][nt][kFamily1Cta] = lookup(ops->executable, bbase + "_1cta");
         ops->matmul_bias_exports[t][nt][kFamilyGeneric] = lookup(
             ops->executable, std::string("iree_b200_matmul_generic_bias_") + kTypeSuffix[t]);
+        ops->matmul_dtm_exports[2][t][nt][kFamily2Cta] = lookup(ops->executable, bbase + "_dtm");
+        ops->matmul_dtm_exports[2][t][nt][kFamily1Cta] =
+            lookup(ops->executable, bbase + "_1cta_dtm");
       }
       if (!kTruncSuffix[t]) continue;
       const std::string btbase =
@@ -145,11 +150,16 @@ static void populate_export_tables(iree_b200_ops_t* ops) {
           lookup(ops->executable, btbase + "_1cta");
       ops->matmul_bias_trunc_exports[t][nt][kFamilyGeneric] =
           ops->matmul_bias_exports[t][nt][kFamilyGeneric];
+      ops->matmul_dtm_exports[3][t][nt][kFamily2Cta] = lookup(ops->executable, btbase + "_dtm");
+      ops->matmul_dtm_exports[3][t][nt][kFamily1Cta] =
+          lookup(ops->executable, btbase + "_1cta_dtm");
       const std::string tbase =
           std::string("iree_b200_matmul_") + (nt ? "nt_" : "") + kTruncSuffix[t];
       ops->matmul_trunc_exports[t][nt][kFamily2Cta] = lookup(ops->executable, tbase);
       ops->matmul_trunc_exports[t][nt][kFamily1Cta] = lookup(ops->executable, tbase + "_1cta");
       ops->matmul_trunc_exports[t][nt][kFamilyGeneric] = ops->matmul_exports[t][nt][kFamilyGeneric];
+      ops->matmul_dtm_exports[1][t][nt][kFamily2Cta] = lookup(ops->executable, tbase + "_dtm");
+      ops->matmul_dtm_exports[1][t][nt][kFamily1Cta] = lookup(ops->executable, tbase + "_1cta_dtm");
     }
   }
   for (int t = 0; t < 4; ++t) {
@@ -384,13 +394,12 @@ iree_b200_status_t iree_b200_ops_select_matmul(const iree_b200_ops_t* ops, int32
     family = (M > 128 && tiles_2cta * 2 >= sm_count) ? kFamily2Cta : kFamily1Cta;
   }
   const bool device_maps = (flags & IREE_B200_MATMUL_FLAG_DEVICE_MAPS) != 0;
-  if (device_maps && (with_bias || truncate || element_type > IREE_B200_ELEMENT_TYPE_BF16 ||
-                      family == kFamilyGeneric)) {
+  if (device_maps && family == kFamilyGeneric) {
     return make_status(IREE_B200_STATUS_INVALID_ARGUMENT,
-                       "FLAG_DEVICE_MAPS: i8 / f16 / bf16 matmuls with the 32-bit result whose "
-                       "shape passes the TMA guards only");
+                       "FLAG_DEVICE_MAPS: the shape must pass the TMA guards (the generic kernels "
+                       "take no tensor maps to begin with)");
   }
-  const auto& table = device_maps ? ops->matmul_dtm_exports
+  const auto& table = device_maps ? ops->matmul_dtm_exports[(with_bias ? 2 : 0) + (truncate ? 1 : 0)]
                       : with_bias ? (truncate ? ops->matmul_bias_trunc_exports : ops->matmul_bias_exports)
                                   : (truncate ? ops->matmul_trunc_exports : ops->matmul_exports);
   const int32_t ordinal = table[element_type][transpose_rhs ? 1 : 0][family];

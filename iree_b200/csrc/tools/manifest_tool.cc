@@ -34,10 +34,15 @@ int main() {
 #include "../kernels/gemm_exports.inc"
 #undef X
   // Same kernels, tensor maps built on the device: the stock custom-dispatch ABI, no recipe.
-#define X(NAME, TEMPLATE_OF, CLUSTER, ...)                                                 \
-  emit(#NAME, "gemm_dtm_kernels", GemmConfig<__VA_ARGS__>::kThreads,                       \
+#define X(NAME, CLUSTER, ...)                                                              \
+  emit(#NAME "_dtm", "gemm_dtm_kernels", GemmConfig<__VA_ARGS__>::kThreads,                \
        GemmConfig<__VA_ARGS__>::kSmemBytes, 5, "1, 1, 0");
-#include "../kernels/gemm_dtm_exports.inc"
+#include "../kernels/gemm_exports.inc"
+#undef X
+#define X(NAME, CLUSTER, ...)                                                              \
+  emit(#NAME "_dtm", "gemm_bias_dtm_kernels", GemmConfig<__VA_ARGS__>::kThreads,           \
+       GemmConfig<__VA_ARGS__>::kSmemBytes, 5, "1, 1, 1, 0");
+#include "../kernels/gemm_bias_exports.inc"
 #undef X
 #define X(NAME, CLUSTER, ...)                                                              \
   emit(#NAME, "gemm_bias_kernels", GemmConfig<__VA_ARGS__>::kThreads,                      \

@@ -191,6 +191,13 @@ def default_workloads(sm_count=148):
     sel = ops.select_matmul("i8", 1, 1000, 528, 272, flags=H.MATMUL_DEVICE_MAPS)
     out.append(Workload("matmul_i8_small", name_of(sel["export_ordinal"]), sel["workgroup_count"],
                         sel["constants"], [((1000, 272), "i8"), ((272, 528), "i8")], ((1000, 528), "i32")))
+    # The bf16 linear layer as ONE dispatch: matmul + bias[n] + relu + truncf.
+    fused = H.MATMUL_BIAS | H.MATMUL_RELU | H.MATMUL_TRUNCATE_RESULT | H.MATMUL_DEVICE_MAPS
+    for name, (M, K, N) in (("linear_bf16", (8192, 8192, 8192)), ("linear_bf16_small", (1000, 264, 520))):
+        sel = ops.select_matmul("bf16", 1, M, N, K, flags=fused)
+        out.append(Workload(name, name_of(sel["export_ordinal"]), sel["workgroup_count"],
+                            sel["constants"], [((M, K), "bf16"), ((K, N), "bf16"), ((N,), "f32")],
+                            ((M, N), "bf16")))
     sel = ops.select_attention("f16", 2, 384, D, 640, D, 1.0 / D ** 0.5, mask_kind=H.ATTENTION_MASK_CAUSAL,
                                flags=H.ATTENTION_DEVICE_MAPS)
     (d,) = sel["dispatches"]

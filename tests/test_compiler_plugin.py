@@ -84,12 +84,17 @@ def test_stock_driver_spec_uses_only_recipe_free_exports():
     with open(os.path.join(ROOT, "iree_b200", "_build", "exports.json")) as f:
         exports = {e["name"]: e for e in json.load(f)["exports"]}
     dispatched = set(re.findall(r'hal\.dispatch\.extern "(\w+)"', text))
-    assert len(dispatched) == 8         # 3 types x {2-CTA, 1-CTA} matmul + 2 attention
+    # the host-fed spec's kernels, one for one: 5 types x {2-CTA, 1-CTA} matmul, 5 bias forms x
+    # {2-CTA, 1-CTA}, 2 attention
+    host_fed = set(re.findall(r'hal\.dispatch\.extern "(\w+)"', _spec()))
+    assert dispatched == {n + "_dtm" for n in host_fed} and len(dispatched) == 22
     for name in dispatched:
-        assert "_dtm" in name, name
         e = exports[name]
         assert e["constants"] == 5
-        assert e["module"] in ("gemm_dtm_kernels", "attention_kernels")
+        assert e["module"] in ("gemm_dtm_kernels", "gemm_bias_dtm_kernels", "attention_kernels")
+        twin = exports[name[:-len("_dtm")]]
+        for key in ("block_dims", "shared_memory", "binding_flags"):
+            assert e[key] == twin[key], (name, key)
     from iree_b200 import hal as H
     ops = H.Ops.offline(148)
     for name in dispatched:

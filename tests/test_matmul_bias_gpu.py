@@ -24,7 +24,7 @@ def _acc_t(t):
 
 
 def _run(ops, t, batch, M, N, K, *, family="auto", nt=False, relu=False, accumulate=False,
-         truncate=False, bias=None):
+         truncate=False, bias=None, extra_flags=0):
     lhs = oracle.generate_random_matrix(t, (batch, M, K), 1)
     rhs = oracle.generate_random_matrix(t, (batch, N, K) if nt else (batch, K, N), 2)
     acc = oracle.generate_random_matrix(_acc_t(t), (batch, M, N), 3) if accumulate else None
@@ -36,7 +36,7 @@ def _run(ops, t, batch, M, N, K, *, family="auto", nt=False, relu=False, accumul
         out = acc.copy() if accumulate else np.full((batch, M, N), 77, dtype=bias.dtype)
     flags = (FAMILY[family] | (H.MATMUL_TRANSPOSE_RHS if nt else 0) | (H.MATMUL_RELU if relu else 0)
              | (H.MATMUL_ACCUMULATE if accumulate else 0)
-             | (H.MATMUL_TRUNCATE_RESULT if truncate else 0))
+             | (H.MATMUL_TRUNCATE_RESULT if truncate else 0) | extra_flags)
     ops.matmul_bias_host(t, batch, M, N, K, lhs.ctypes.data, rhs.ctypes.data, bias.ctypes.data,
                          out.ctypes.data, flags)
     want = oracle.matmul_bias(t, lhs, rhs, bias, acc=acc, transpose_rhs=nt, relu=relu,
@@ -197,3 +197,29 @@ def test_bias_selection_and_guards(ops):
         ops.select_matmul("f8e4m3fn", 1, 256, 256, 256, flags=B)        # no f8 bias exports
     with pytest.raises(H.Status):
         ops.matmul_host("bf16", 1, 16, 16, 16, 0, 0, 0, flags=B)        # wrong entry point
+
+
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("family", ["1cta", "2cta"])
+@pytest.mark.parametrize("case", [dict(nt=False, relu=True, truncate=True), dict(nt=True, relu=False),
+                                  dict(nt=False, relu=True, accumulate=True)], ids=str)
+@pytest.mark.parametrize("shape", [(1, 256, 256, 64), (1, 1000, 264, 520), (3, 300, 520, 136)], ids=str)
+def test_fused_epilogue_with_device_built_tensor_maps(ops, t, family, case, shape):
+    """`iree_b200_matmul_bias_*_dtm`: the fused bias / activation / truncation dispatches in
+    the form an unmodified IREE CUDA driver launches (FLAG_DEVICE_MAPS). Bit-exact."""
+    batch, M, N, K = shape
+    case = dict(case)
+    if case.get("truncate") and t == "i8":
+        case.pop("truncate")
+    if case.get("truncate") and case.get("accumulate"):
+        case.pop("accumulate")
+    if not _tma_ok(t, N, K, case.get("nt", False), out_es=2 if case.get("truncate") else 4):
+        pytest.skip("shape does not satisfy the TMA guards")
+    flags = (FAMILY[family] | H.MATMUL_BIAS | H.MATMUL_DEVICE_MAPS
+             | (H.MATMUL_TRANSPOSE_RHS if case.get("nt") else 0) | (H.MATMUL_RELU if case.get("relu") else 0)
+             | (H.MATMUL_TRUNCATE_RESULT if case.get("truncate") else 0))
+    info = ops.executable.export_info(ops.select_matmul(t, batch, M, N, K, flags=flags)["export_ordinal"])
+    assert info["kernel_name"].startswith("iree_b200_matmul_bias_") and info["kernel_name"].endswith("_dtm")
+    assert info["tma_map_count"] == 0 and info["binding_count"] == 4
+    out, want = _run(ops, t, batch, M, N, K, family=family, extra_flags=H.MATMUL_DEVICE_MAPS, **case)
+    assert np.array_equal(out, want)

@@ -80,7 +80,7 @@ def test_every_kernel_family(ops, t, family, nt, shape):
     assert np.array_equal(out, want)
 
 
-@pytest.mark.parametrize("t", ["i8", "f16", "bf16"])
+@pytest.mark.parametrize("t", ["i8", "f16", "bf16", "f8e4m3fn", "f8e5m2"])
 @pytest.mark.parametrize("family", ["1cta", "2cta"])
 @pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
 @pytest.mark.parametrize("shape", TILED + [(4, 512, 384, 640, False)],
@@ -100,6 +100,24 @@ def test_device_built_tensor_maps(ops, t, family, nt, shape):
     assert "_dtm" in info["kernel_name"] and info["tma_map_count"] == 0
     out, want = _run(ops, t, batch, M, N, K, flags=flag, accumulate=accumulate, nt=nt)
     assert np.array_equal(out, want)
+
+
+@pytest.mark.parametrize("t", ["f16", "bf16"])
+@pytest.mark.parametrize("family", ["1cta", "2cta"])
+@pytest.mark.parametrize("nt", [False, True], ids=["nn", "nt"])
+@pytest.mark.parametrize("shape", [(256, 64, 256), (1000, 520, 264), (2048, 256, 1280)], ids=str)
+def test_device_built_tensor_maps_truncating_epilogue(ops, t, family, nt, shape):
+    """The truncating `*_dtm` twins: the 16-bit result map is patched from its own template."""
+    M, K, N = shape
+    flag = {"1cta": H.MATMUL_FORCE_1CTA, "2cta": H.MATMUL_FORCE_2CTA}[family]
+    f = flag | H.MATMUL_TRUNCATE_RESULT | H.MATMUL_DEVICE_MAPS | (H.MATMUL_TRANSPOSE_RHS if nt else 0)
+    name = ops.executable.export_info(ops.select_matmul(t, 1, M, N, K, flags=f)["export_ordinal"])
+    assert name["kernel_name"].endswith("_dtm") and f"_{t}_{t}" in name["kernel_name"]
+    lhs = oracle.generate_random_matrix(t, (1, M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (1, N, K) if nt else (1, K, N), 2)
+    out = np.full((1, M, N), 0x7777, dtype=np.uint16)
+    ops.matmul_host(t, 1, M, N, K, lhs.ctypes.data, rhs.ctypes.data, out.ctypes.data, f)
+    assert np.array_equal(out, oracle.from_f32(t, oracle.matmul(t, lhs, rhs, transpose_rhs=nt)))
 
 
 @pytest.mark.parametrize("t", ["i8", "bf16", "f8e4m3fn"])

@@ -49,6 +49,12 @@ def _worker(rank, world, port, tmp, results):
         assert hal.default_rank_and_count() == (rank, world)
         # 2. id exchange without MPI: rank 0 publishes 128 bytes, the others receive them.
         ident = bytes(range(128)) if rank == 0 else bytes(128)
+        if rank != 0:
+            # Let rank 0 get there first: it then finds only the planted leftovers (a stale
+            # hello AND a matching stale ack of "rank 1") and must keep waiting for the real
+            # rank 1 — acknowledgements echo rank 0's per-exchange nonce.
+            import time
+            time.sleep(1.0)
         assert hal.exchange_default_id(rank, ident) == bytes(range(128))
         # ... a second channel in the same run gets ITS id (per-process sequence number), and
         # neither exchange is fooled by the stale files the test planted (a leftover
@@ -108,8 +114,9 @@ def test_world_size_2_gloo():
                 + bytes([0xEE]) * 128
             with open(os.path.join(tmp, f"id.{seq}.id"), "wb") as f:
                 f.write(stale)
-            for kind in ("hello", "ack"):
-                with open(os.path.join(tmp, f"id.{seq}.{kind}.1"), "wb") as f:
-                    f.write(struct.pack("<Q", 0x1234567))
+            with open(os.path.join(tmp, f"id.{seq}.hello.1"), "wb") as f:
+                f.write(struct.pack("<Q", 0x1234567))
+            with open(os.path.join(tmp, f"id.{seq}.ack.1"), "wb") as f:   # {token, rank 0's nonce}
+                f.write(struct.pack("<2Q", 0x1234567, 0x7654321) if seq else struct.pack("<Q", 0x1234567))
         mp.spawn(_worker, args=(world, port, tmp, results), nprocs=world, join=True)
         assert dict(results) == {0: "ok", 1: "ok"}

@@ -162,6 +162,32 @@ def test_stock_reference_driver_runs_the_tcgen05_matmul_with_device_built_maps(o
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("t", ["bf16", "f8e4m3fn"])
+def test_stock_reference_driver_runs_the_other_device_map_twins(ops, hal, tmp_path, t):
+    """f8 operands, and the fused bias + relu + truncf dispatch (four bindings), as `*_dtm`
+    exports through the unmodified reference driver."""
+    M, K, N = 1000, 272, 528
+    lhs = oracle.generate_random_matrix(t, (M, K), 1)
+    rhs = oracle.generate_random_matrix(t, (K, N), 2)
+    if t == "bf16":
+        flags = hal.MATMUL_BIAS | hal.MATMUL_RELU | hal.MATMUL_TRUNCATE_RESULT | hal.MATMUL_DEVICE_MAPS
+        bias = oracle.generate_random_matrix("f32", (N,), 4)
+        bindings, out_index, out_bytes = [lhs, rhs, bias, M * N * 2], 3, 2
+        want = oracle.matmul_bias(t, lhs, rhs, bias, relu=True, truncate=True)
+    else:
+        flags = hal.MATMUL_DEVICE_MAPS
+        bindings, out_index, out_bytes = [lhs, rhs, M * N * 4], 2, 4
+        want = oracle.matmul(t, lhs, rhs)
+    sel = ops.select_matmul(t, 1, M, N, K, flags=flags)
+    info = ops.executable.export_info(sel["export_ordinal"])
+    assert info["kernel_name"].endswith("_dtm") and info["tma_map_count"] == 0
+    raw, _ = run_harness("stock", tmp_path, sel["export_ordinal"], sel["workgroup_count"],
+                         sel["constants"], bindings, out_index)
+    got = raw.view(np.uint16 if out_bytes == 2 else np.float32).reshape(M, N)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
 def test_stock_reference_driver_runs_the_decode_cluster_attention(ops, hal, tmp_path):
     """One-dispatch split-KV decode: 8-CTA clusters + 1-D bulk copies, no tensor map, so the
     unmodified reference driver's cuLaunchKernel is enough."""

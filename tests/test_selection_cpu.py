@@ -163,12 +163,21 @@ def test_device_map_exports_are_selected_only_where_they_exist(ops):
             assert big["workgroup_count"] == ref["workgroup_count"] == [148, 1, 1]
             assert big["constants"] == ref["constants"]
             small = ops.select_matmul(t, 1, 256, 512, 128, flags=flags | H.MATMUL_DEVICE_MAPS)
-            assert _name(ops, small) == f"iree_b200_matmul_{nt}{t}_{acc}_dtm_1cta"
+            assert _name(ops, small) == f"iree_b200_matmul_{nt}{t}_{acc}_1cta_dtm"
             info = ops.executable.export_info(big["export_ordinal"])
             assert info["tma_map_count"] == 0 and info["constant_count"] == 5
-    for bad in (dict(t="f8e4m3fn", flags=H.MATMUL_DEVICE_MAPS),
-                dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS | H.MATMUL_TRUNCATE_RESULT),
-                dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS | H.MATMUL_FORCE_GENERIC),
+    # ... every tcgen05 export has its twin: f8, truncating, bias / activation forms.
+    for t, flags, want in (("f8e4m3fn", 0, "iree_b200_matmul_f8e4m3fn_f32_dtm"),
+                           ("bf16", H.MATMUL_TRUNCATE_RESULT, "iree_b200_matmul_bf16_bf16_dtm"),
+                           ("f16", H.MATMUL_BIAS | H.MATMUL_RELU, "iree_b200_matmul_bias_f16_f32_dtm"),
+                           ("bf16", H.MATMUL_BIAS | H.MATMUL_TRUNCATE_RESULT | H.MATMUL_TRANSPOSE_RHS,
+                            "iree_b200_matmul_bias_nt_bf16_bf16_dtm")):
+        sel = ops.select_matmul(t, 1, 4096, 4096, 4096, flags=flags | H.MATMUL_DEVICE_MAPS)
+        ref = ops.select_matmul(t, 1, 4096, 4096, 4096, flags=flags)
+        assert _name(ops, sel) == want == _name(ops, ref) + "_dtm"
+        assert (sel["workgroup_count"], sel["constants"]) == (ref["workgroup_count"], ref["constants"])
+        assert ops.executable.export_info(sel["export_ordinal"])["tma_map_count"] == 0
+    for bad in (dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS | H.MATMUL_FORCE_GENERIC),
                 dict(t="bf16", flags=H.MATMUL_DEVICE_MAPS, N=1001)):      # fails the TMA guards
         with pytest.raises(H.Status) as e:
             ops.select_matmul(bad["t"], 1, 1024, bad.get("N", 1024), 1024, flags=bad["flags"])

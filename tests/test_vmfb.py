@@ -117,6 +117,19 @@ def test_stock_iree_run_module_runs_the_tcgen05_matmul(module_path, tmp_path, t,
 
 
 @pytest.mark.gpu
+def test_stock_iree_run_module_runs_the_fused_linear_layer(module_path, tmp_path):
+    """matmul + bias[n] + relu + truncf as one tcgen05 dispatch (`iree_b200_matmul_bias_bf16_bf16_
+    1cta_dtm`), four bindings, through the stock tool. Bit-exact."""
+    M, K, N = 1000, 264, 520
+    lhs = oracle.generate_random_matrix("bf16", (M, K), 1)
+    rhs = oracle.generate_random_matrix("bf16", (K, N), 2)
+    bias = oracle.generate_random_matrix("f32", (N,), 4)
+    got = _run(module_path, tmp_path, "linear_bf16_small", [(lhs, "bf16"), (rhs, "bf16"), (bias, "f32")],
+               np.uint16, (M, N))
+    assert np.array_equal(got, oracle.matmul_bias("bf16", lhs, rhs, bias, relu=True, truncate=True))
+
+
+@pytest.mark.gpu
 def test_stock_iree_run_module_runs_attention(module_path, tmp_path):
     g = np.random.Generator(np.random.PCG64(0xB200))
     mk = lambda *s: oracle.from_f32("f16", np.clip(g.standard_normal(s), -4, 4).astype(np.float32))

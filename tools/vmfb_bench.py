@@ -51,7 +51,7 @@ def main():
     tmp = tempfile.mkdtemp(prefix="vmfb_")
     rng = np.random.Generator(np.random.PCG64(0xB200))
     work = {"matmul_bf16": 2.0 * 8192 ** 3, "matmul_i8": 2.0 * 8192 ** 3,
-            "batch_matmul_bf16": 2.0 * 64 * 2048 ** 3,
+            "batch_matmul_bf16": 2.0 * 64 * 2048 ** 3, "linear_bf16": 2.0 * 8192 ** 3,
             "attention_prefill_f16": 4.0 * 32 * 4096 * 4096 * 128,
             "attention_prefill_causal_f16": 4.0 * 32 * 128 * (4096 * 4097 / 2),
             "attention_decode_f16": None}
