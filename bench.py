@@ -698,7 +698,7 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
     ops = hal.Ops(dev)
     # ---- configs[2]
     op, et, B, M, N, K = MATMUL_WORKLOADS["batch_matmul"]
-    if B % world == 0:
+    if B % world == 0:   # (every N the driver runs divides 64)
         full = [MatmulStep(torch, hal, dev, ops, (op, et, B, M, N, K), seed=rank)]
         soak(torch, full[0], stream, world, args.presoak_s)
         t1, _ = time_steps(torch, full, steps, warmup, stream, world, min_ms=MIN)
@@ -719,6 +719,33 @@ def sharded_lines(torch, hal, args, world, rank, local, peaks):
             "roofline_frac_of_sustained": flop / world / (tn * 1e-3) / 1e12 / peaks["bf16_tflops_sustained"]}
         del part
         torch.cuda.empty_cache()
+    # ---- configs[3]: attention, heads (= batch entries) split 32/N, no collective
+    try:
+        aop, aet, AB, AM, AK2, AD = ATTENTION_WORKLOADS["attention_prefill"]
+        if AB % world == 0:
+            full = [AttentionStep(torch, hal, dev, ops, (aop, aet, AB, AM, AK2, AD), seed=rank)]
+            t1, _ = time_steps(torch, full, steps, warmup, stream, world, min_ms=MIN)
+            del full
+            torch.cuda.empty_cache()
+            part = rotating_sets(lambda i: AttentionStep(torch, hal, dev, ops,
+                                                         (aop, aet, AB // world, AM, AK2, AD),
+                                                         seed=rank + 100 * i),
+                                 lambda w: w.describe()["bytes"])
+            tn, steps_n = time_steps(torch, part, steps, warmup, stream, world, min_ms=MIN)
+            aflop = 4.0 * AB * AM * AK2 * AD
+            out["attention_prefill"] = {
+                "workload": f"iree_linalg_ext.attention {aet} batch*heads={AB} M={AM} K2={AK2} K1=N={AD}, "
+                            f"heads split {AB // world} per GPU over {world} GPUs, no collective",
+                "scaling": "strong", "value": aflop / (tn * 1e-3) / 1e12, "unit": "TFLOP/s",
+                "ms_per_step": tn, "n1_ms_per_step": t1, "n1_value": aflop / (t1 * 1e-3) / 1e12,
+                "efficiency": t1 / (world * tn), "steps": steps_n, "timed_region_ms": tn * steps_n,
+                "launches_per_step": part[0].launches_per_step,
+                "note": f"{AB // world * ((AM + 255) // 256)} CTA-units of work per GPU on 148 SMs: "
+                        "below one full wave the tail split cuts units over K2 (+ a merge dispatch)"}
+            del part
+            torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001 - an extra line must never cost the headline
+        out["attention_prefill"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     # ---- configs[4]
     solo = TpLayerStep(torch, hal, dev, ops, 1, 0, None, seed=rank)
     t1, _ = time_steps(torch, [solo], steps, warmup, stream, world, min_ms=MIN)
