@@ -111,6 +111,35 @@ def test_sub_range_bindings_move_the_tensor_map_base(dev, dev_ops):
     assert tc["type"] == 3                                      # i32 result
 
 
+def test_device_map_twins_reach_the_driver_without_tensor_maps(dev, dev_ops):
+    """FLAG_DEVICE_MAPS: the `<name>_dtm` export is launched with the ABI parameters only —
+    nothing is encoded on the host (no cuTensorMapEncodeTiled call), same grid, block and
+    shared memory as the host-fed twin. This is what the stock IREE CUDA driver does."""
+    M, N, K = 4096, 4096, 1024
+    a, b, c = dev.allocate(M * K * 2), dev.allocate(K * N * 2), dev.allocate(M * N * 4)
+    bias = dev.allocate(N * 4)
+    tensor_maps(), launches()
+    for flags, record in ((0, None), (H.MATMUL_RELU | H.MATMUL_TRUNCATE_RESULT, "bias")):
+        got = {}
+        for device_maps in (False, True):
+            f = flags | (H.MATMUL_DEVICE_MAPS if device_maps else 0)
+            cb = H.CommandBuffer(dev).begin()
+            if record == "bias":
+                dev_ops.record_matmul_bias(cb, "bf16", 1, M, N, K, a.ref(), b.ref(), bias.ref(), c.ref(0, M * N * 2),
+                                           flags=f)
+            else:
+                dev_ops.record_matmul(cb, "bf16", 1, M, N, K, a.ref(), b.ref(), c.ref(), flags=f)
+            cb.end()
+            maps = tensor_maps()
+            dev.execute(cb)
+            dev.wait_idle()
+            (launch,) = launches()
+            got[device_maps] = (launch, len(maps))
+        (host_fed, n_host), (twin, n_twin) = got[False], got[True]
+        assert n_host == 3 and n_twin == 0
+        assert twin[0] == host_fed[0] + "_dtm" and twin[1:] == host_fed[1:]
+
+
 @pytest.mark.parametrize("t,M0,N0", [("bf16", 16, 16), ("i8", 8, 32), ("f16", 128, 64)])
 def test_mmt4d_tile_direct_maps_walk_the_tiles(dev, dev_ops, t, M0, N0):
     """linalg.mmt4d with 16-byte K0 rows and tile rows in multiples of 8: ONE tcgen05 dispatch
