@@ -128,3 +128,32 @@ def test_cda1_reader_survives_mutations():
             assert e.code != 0
             rejected += 1
     assert rejected > 500
+
+
+def _build_c_smoke(tmp_path):
+    import shutil
+    import subprocess
+    cc = "/usr/bin/gcc" if os.path.exists("/usr/bin/gcc") else shutil.which("gcc")
+    exe = tmp_path / "cabi_smoke"
+    lib_dir = os.path.dirname(build.build())
+    subprocess.run([cc, "-std=c11", "-Wall", "-Wextra", "-Werror", "-pedantic",
+                    "-I", os.path.join(ROOT, "include"), "-o", str(exe),
+                    os.path.join(ROOT, "tests", "c", "cabi_smoke.c"), "-L", lib_dir, "-liree_b200",
+                    f"-Wl,-rpath,{lib_dir}"], check=True)
+    return exe
+
+
+@pytest.mark.skipif(_have_gpu(), reason="the GPU variant below runs instead")
+def test_headers_are_c11_and_the_library_links_from_c(tmp_path):
+    """tests/c/cabi_smoke.c: include/*.h under -std=c11 -Wall -Wextra -Werror -pedantic (the
+    reference's host language is C), linked against the library, run without a GPU."""
+    import subprocess
+    r = subprocess.run([str(_build_c_smoke(tmp_path))], capture_output=True, text=True)
+    assert r.returncode == 0 and "cabi_smoke ok (no gpu)" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_c_program_creates_a_device(tmp_path):
+    import subprocess
+    r = subprocess.run([str(_build_c_smoke(tmp_path)), "gpu"], capture_output=True, text=True)
+    assert r.returncode == 0 and "cabi_smoke ok (gpu)" in r.stdout, r.stdout + r.stderr
