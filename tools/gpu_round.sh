@@ -13,6 +13,11 @@ pending)  # code written without GPU time: first thing to run next round
   run pending_bench 300 python tools/pending_bench.py --out $O/${TAG}_pending_bench.json
   run bench_linear_bf16 300 python bench.py --workload linear_bf16 --no-cpu-baseline --steps 100 ;;
 smoke) run smoke 300 python -c "import __graft_entry__ as g; g.smoke()" ;;
+boundary)  # the drop-in boundary through the reference's own runtime and stock tools
+  run pytest_boundary 400 python -m pytest tests/test_ref_runtime.py tests/test_vmfb.py tests/test_cabi.py -m gpu -x -q
+  run ref_runtime_bench 600 python tools/ref_runtime_bench.py
+  run vmfb_bench 700 python tools/vmfb_bench.py
+  run mmt4d_bench 300 python tools/mmt4d_bench.py --min-ms 150 ;;
 bench)
   run bench_matmul_bf16 400 python bench.py
   for w in matmul_i8 batch_matmul attention_prefill attention_prefill_bf16 attention_decode; do
